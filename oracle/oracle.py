@@ -1,0 +1,175 @@
+"""ctypes binding of the CPU oracle (oracle/liborb_oracle.so). TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and the cpu_baseline / --impl reference legs of bench.py may
+import this module. The product package orb_slam2_2021_b200 never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "liborb_oracle.so")
+
+KP_DTYPE = np.dtype(
+    [("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"),
+     ("class_id", "<i4")]
+)
+assert KP_DTYPE.itemsize == 28
+
+
+def build(force=False):
+    """Compile the oracle with the committed Makefile (g++, no external dependency)."""
+    if force or not os.path.exists(_SO):
+        subprocess.check_call(["make", "-C", _HERE, "-B" if force else "-s", "liborb_oracle.so"])
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_SO)
+        u8p, f32p, i32p, vp = C.POINTER(C.c_uint8), C.POINTER(C.c_float), C.POINTER(C.c_int), C.c_void_p
+        L.orc_create.restype = vp
+        L.orc_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orc_destroy.argtypes = [vp]
+        L.orc_tables.argtypes = [vp, f32p, f32p, f32p, f32p, i32p, i32p]
+        L.orc_extract.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int]
+        L.orc_level_size.argtypes = [vp, C.c_int, i32p, i32p]
+        L.orc_level_copy.argtypes = [vp, C.c_int, vp, C.c_int]
+        L.orc_level_blur_copy.argtypes = [vp, C.c_int, vp, C.c_int]
+        L.orc_level_candidates.argtypes = [vp, C.c_int, vp, C.c_int]
+        L.orc_stereo_match.argtypes = [vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_float, C.c_float, vp, vp]
+        L.orc_resize_linear.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int]
+        L.orc_gaussian7.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int]
+        L.orc_fast9.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int]
+        L.orc_fast_atan2.restype = C.c_float
+        L.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.orc_sincos.argtypes = [C.c_float, f32p, f32p]
+        L.orc_hamming256.argtypes = [vp, vp]
+        L.orc_reflect101.argtypes = [C.c_int, C.c_int]
+        L.orc_distribute.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int]
+        _lib = L
+    return _lib
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _u8(img):
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    assert img.ndim == 2
+    return img
+
+
+class OracleExtractor:
+    """Mirror of ORB_SLAM2::ORBextractor (include/ORBextractor.h:56-100) over the CPU oracle."""
+
+    def __init__(self, nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast):
+        self.nfeatures, self.nlevels = nfeatures, nlevels
+        self._h = lib().orc_create(nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast)
+        if not self._h:
+            raise ValueError("orc_create failed")
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_destroy(self._h)
+            self._h = None
+
+    def tables(self):
+        n = self.nlevels
+        f = [np.zeros(n, np.float32) for _ in range(4)]
+        q = np.zeros(n, np.int32)
+        um = np.zeros(16, np.int32)
+        fp = [a.ctypes.data_as(C.POINTER(C.c_float)) for a in f]
+        lib().orc_tables(self._h, *fp, q.ctypes.data_as(C.POINTER(C.c_int)), um.ctypes.data_as(C.POINTER(C.c_int)))
+        return dict(scale=f[0], inv_scale=f[1], sigma2=f[2], inv_sigma2=f[3], quotas=q, umax=um)
+
+    def __call__(self, image):
+        """operator()(image, mask, keypoints, descriptors) -> (keypoints[KP_DTYPE], descriptors[N,32])."""
+        img = _u8(image)
+        cap = self.nfeatures + 64 * self.nlevels + 64
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = lib().orc_extract(self._h, _ptr(img), img.shape[0], img.shape[1], img.strides[0], _ptr(kps), _ptr(desc), cap)
+        if n < 0:
+            raise RuntimeError(f"orc_extract error {n}")
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level(self, l, blurred=False):
+        r, c = C.c_int(), C.c_int()
+        lib().orc_level_size(self._h, l, C.byref(r), C.byref(c))
+        out = np.zeros((r.value, c.value), np.uint8)
+        fn = lib().orc_level_blur_copy if blurred else lib().orc_level_copy
+        fn(self._h, l, _ptr(out), out.strides[0])
+        return out
+
+    def candidates(self, l):
+        n = lib().orc_level_candidates(self._h, l, None, 0)
+        out = np.zeros(max(n, 1), KP_DTYPE)
+        lib().orc_level_candidates(self._h, l, _ptr(out), n)
+        return out[:n]
+
+
+def stereo_match(ex_l, ex_r, kps_l, desc_l, kps_r, desc_r, mbf, mb):
+    """Frame::ComputeStereoMatches -> (mvuRight, mvDepth)."""
+    kps_l, kps_r = np.ascontiguousarray(kps_l), np.ascontiguousarray(kps_r)
+    desc_l, desc_r = np.ascontiguousarray(desc_l), np.ascontiguousarray(desc_r)
+    n = len(kps_l)
+    ur = np.full(max(n, 1), -1, np.float32)
+    dp = np.full(max(n, 1), -1, np.float32)
+    lib().orc_stereo_match(ex_l._h, ex_r._h, _ptr(kps_l), _ptr(desc_l), n, _ptr(kps_r), _ptr(desc_r), len(kps_r),
+                           mbf, mb, _ptr(ur), _ptr(dp))
+    return ur[:n], dp[:n]
+
+
+def resize_linear(src, dw, dh):
+    src = _u8(src)
+    dst = np.zeros((dh, dw), np.uint8)
+    lib().orc_resize_linear(_ptr(src), src.shape[1], src.shape[0], src.strides[0], _ptr(dst), dw, dh, dst.strides[0])
+    return dst
+
+
+def gaussian7(src):
+    src = _u8(src)
+    dst = np.zeros_like(src)
+    lib().orc_gaussian7(_ptr(src), src.shape[1], src.shape[0], src.strides[0], _ptr(dst), dst.strides[0])
+    return dst
+
+
+def fast9(roi, threshold):
+    """cv::FAST(roi, kps, threshold, true) on a (possibly non-contiguous) 2-D uint8 view."""
+    assert roi.dtype == np.uint8 and roi.strides[1] == 1
+    cap = roi.shape[0] * roi.shape[1] // 4 + 16
+    out = np.zeros(cap, KP_DTYPE)
+    n = lib().orc_fast9(_ptr(roi), roi.shape[1], roi.shape[0], roi.strides[0], threshold, _ptr(out), cap)
+    return out[:n]
+
+
+def fast_atan2(y, x):
+    return lib().orc_fast_atan2(float(y), float(x))
+
+
+def sincos(rad):
+    s, c = C.c_float(), C.c_float()
+    lib().orc_sincos(float(rad), C.byref(s), C.byref(c))
+    return s.value, c.value
+
+
+def hamming256(a, b):
+    a, b = np.ascontiguousarray(a, np.uint8), np.ascontiguousarray(b, np.uint8)
+    return lib().orc_hamming256(_ptr(a), _ptr(b))
+
+
+def distribute(cand, min_x, max_x, min_y, max_y, n_target):
+    cand = np.ascontiguousarray(cand)
+    cap = len(cand) + 8
+    out = np.zeros(cap, KP_DTYPE)
+    n = lib().orc_distribute(_ptr(cand), len(cand), min_x, max_x, min_y, max_y, n_target, _ptr(out), cap)
+    return out[:n]

@@ -1,0 +1,87 @@
+/* orb_oracle.h — CPU ORACLE for the ORB front-end hot path.  TEST INFRASTRUCTURE ONLY.
+ *
+ * This library is the checker, never the product: only tests/, __graft_entry__.smoke() and the
+ * cpu_baseline / --impl reference legs of bench.py may load it. The shipped path
+ * (orb_slam2_2021_b200/, liborbx.so) never links, imports or calls anything in oracle/.
+ *
+ * It is a from-scratch sequential restatement of
+ *   ORBextractor::ORBextractor / operator() / ComputePyramid / ComputeKeyPointsOctTree /
+ *   DistributeOctTree / ExtractorNode::DivideNode / IC_Angle / computeOrbDescriptor
+ *                                               (/root/reference/src/ORBextractor.cc:75-151, 413-856, 1032-1135)
+ *   Frame::ComputeStereoMatches                 (/root/reference/src/Frame.cc:522-700)
+ *   ORBmatcher::DescriptorDistance              (/root/reference/src/ORBmatcher.cc:1672-1688)
+ * and of the OpenCV primitives those call (OpenCV is an un-vendored dependency of the reference,
+ * CMakeLists.txt:15-21 "OpenCV 4.2", README.md:12 "tested with 4.5.4"; absent from /root/reference):
+ *   cv::resize INTER_LINEAR 8UC1, cv::GaussianBlur 7x7 sigma 2 8UC1, cv::FAST TYPE_9_16 + NMS,
+ *   cv::fastAtan2, cvRound, BORDER_REFLECT_101.
+ *
+ * PARITY PIN: the reference has no tests or golden vectors for this path and cannot be compiled
+ * here (no OpenCV C++ headers). The oracle is pinned instead against the real OpenCV kernels
+ * through cv2 4.13.0 (tests/test_oracle_kat.py: resize, blur, FAST, fastAtan2 bit-exact) and
+ * against golden vectors produced by a cv2-driven pipeline (tests/golden/make_golden.py).
+ * Two choices are pinned by decision because the reference itself is not deterministic there
+ * (DESIGN.md §oracle): the quadtree tie-break (creation order instead of heap address) and
+ * cos/sin (orbx_sincosf instead of libm).
+ */
+#ifndef ORB_ORACLE_H
+#define ORB_ORACLE_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Same 28-byte layout as cv::KeyPoint (pt.x, pt.y, size, angle, response, octave, class_id). */
+typedef struct {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orc_keypoint;
+
+typedef struct orc_extractor orc_extractor;
+
+/* ORBextractor::ORBextractor, src/ORBextractor.cc:413-473 */
+orc_extractor* orc_create(int nfeatures, float scale_factor, int nlevels, int ini_th_fast, int min_th_fast);
+void orc_destroy(orc_extractor* e);
+/* scale tables / quotas / umax; any pointer may be NULL. Arrays of nlevels (umax: 16). */
+void orc_tables(const orc_extractor* e, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                int* quotas, int* umax);
+
+/* ORBextractor::operator(), src/ORBextractor.cc:1041-1103. Returns the number of keypoints
+ * (>=0) or a negative error: -1 capacity too small, -2 bad arguments, -3 degenerate geometry
+ * (level too small or nIni == 0: the reference has undefined behaviour there). An empty image
+ * (rows==0 or cols==0) returns 0 and touches nothing. */
+int orc_extract(orc_extractor* e, const uint8_t* img, int rows, int cols, int stride,
+                orc_keypoint* kps, uint8_t* desc, int capacity);
+
+/* mvImagePyramid[level] of the last extract (without the unused 19-px border). */
+int orc_level_size(const orc_extractor* e, int level, int* rows, int* cols);
+int orc_level_copy(const orc_extractor* e, int level, uint8_t* dst, int dst_stride);
+/* blurred working copy of a level (src/ORBextractor.cc:1083-1084), for tests */
+int orc_level_blur_copy(const orc_extractor* e, int level, uint8_t* dst, int dst_stride);
+/* vToDistributeKeys of a level of the last extract (x,y relative to minBorder), for tests */
+int orc_level_candidates(const orc_extractor* e, int level, orc_keypoint* out, int capacity);
+
+/* Frame::ComputeStereoMatches, src/Frame.cc:522-700. left/right are the extractors that produced
+ * the keypoints (their un-blurred pyramids are read, :620-639). mb is explicit because the
+ * reference reads it uninitialised (:552 vs :149). Returns the number of valid matches. */
+int orc_stereo_match(const orc_extractor* left, const orc_extractor* right,
+                     const orc_keypoint* kps_l, const uint8_t* desc_l, int n_l,
+                     const orc_keypoint* kps_r, const uint8_t* desc_r, int n_r,
+                     float mbf, float mb, float* u_right, float* depth);
+
+/* ---- primitives, exported for the known-answer tests against cv2 ---- */
+void orc_resize_linear(const uint8_t* src, int sw, int sh, int sstride, uint8_t* dst, int dw, int dh, int dstride);
+void orc_gaussian7(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride);
+int orc_fast9(const uint8_t* roi, int w, int h, int stride, int threshold, orc_keypoint* out, int capacity);
+float orc_fast_atan2(float y, float x);
+void orc_sincos(float rad, float* s, float* c);
+int orc_hamming256(const uint8_t* a, const uint8_t* b);
+int orc_reflect101(int p, int n);
+/* DistributeOctTree on arbitrary candidates (x,y,response used), src/ORBextractor.cc:542-766 */
+int orc_distribute(const orc_keypoint* cand, int n, int min_x, int max_x, int min_y, int max_y, int n_target,
+                   orc_keypoint* out, int capacity);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
