@@ -1,0 +1,131 @@
+/* orbx.h — C-ABI of the B200-native ORB front-end (liborbx.so).
+ *
+ * Drop-in boundary for ONE hot path of lreithmayr/ORB_SLAM2_2021: ORBextractor::operator() and
+ * Frame::ComputeStereoMatches(). Plain pointers and sizes only; no C++/torch/OpenCV types. Every
+ * entry point names the reference interface it replaces (paths relative to /root/reference).
+ * All functions return ORBX_OK (0) or a negative orbx_status; none throws. A handle is
+ * single-threaded; different handles may be used from different threads concurrently (each owns
+ * its CUDA stream), which is how Frame::Frame runs left and right (src/Frame.cc:113-116).
+ * There is no CPU fallback: every call fails with ORBX_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef ORBX_H
+#define ORBX_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    ORBX_OK = 0,
+    ORBX_ERR_ARG = -1,      /* null pointer, bad size, bad level ...                              */
+    ORBX_ERR_CAPACITY = -2, /* caller's output buffers too small (need orbx_max_keypoints())       */
+    ORBX_ERR_GEOMETRY = -3, /* a pyramid level is smaller than 62 px or taller than 2x its width:  */
+                            /* the reference divides by zero there (src/ORBextractor.cc:546,786)   */
+    ORBX_ERR_CUDA = -4,     /* CUDA runtime error; text in orbx_last_error()                       */
+    ORBX_ERR_STATE = -5     /* e.g. stereo match before both extractors ran on equal-size images   */
+} orbx_status;
+
+/* Same 28-byte layout as cv::KeyPoint {Point2f pt; float size, angle, response; int octave, class_id}. */
+typedef struct {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orbx_keypoint;
+
+typedef struct orbx_extractor orbx_extractor; /* one ORBextractor instance                       */
+typedef struct orbx_batch orbx_batch;         /* frame-batch engine for throughput                */
+
+const char* orbx_last_error(void);            /* thread-local text of the last failure            */
+int orbx_device_count(void);
+
+/* ---- ORBextractor ------------------------------------------------------------------------------ */
+
+/* Replaces ORBextractor::ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST,
+ * int minThFAST) — include/ORBextractor.h:65-66, src/ORBextractor.cc:413-473 (constructed at
+ * src/Tracking.cc:125-131). `device` is the CUDA ordinal. */
+int orbx_create(int nfeatures, float scale_factor, int nlevels, int ini_th_fast, int min_th_fast, int device,
+                orbx_extractor** out);
+void orbx_destroy(orbx_extractor* e);
+
+/* Replaces GetLevels/GetScaleFactor(s)/GetInverseScaleFactors/GetScaleSigmaSquares/
+ * GetInverseScaleSigmaSquares — include/ORBextractor.h:75-98 — plus mnFeaturesPerLevel (:117).
+ * Each array has nlevels entries; any pointer may be NULL. */
+int orbx_get_levels(const orbx_extractor* e);
+int orbx_get_tables(const orbx_extractor* e, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                    int* features_per_level);
+/* Upper bound of keypoints one extract can return: sum over levels of max(quota, 4*nIni) + 4. */
+int orbx_max_keypoints(const orbx_extractor* e, int rows, int cols);
+
+/* Replaces void ORBextractor::operator()(InputArray image, InputArray mask, vector<KeyPoint>&,
+ * OutputArray descriptors) — include/ORBextractor.h:75-77, src/ORBextractor.cc:1041-1103; called from
+ * Frame::ExtractORB, src/Frame.cc:296-302. `image` is host CV_8UC1, `stride` bytes per row; the mask
+ * is ignored by the reference and has no parameter here. Writes *n keypoints (levels concatenated
+ * 0..L-1, coordinates scaled to level 0) and n x 32 descriptor bytes. An empty image (rows or cols
+ * == 0) returns ORBX_OK and leaves kps/desc/n untouched, like :1044-1045. */
+int orbx_extract(orbx_extractor* e, const uint8_t* image, int rows, int cols, size_t stride, orbx_keypoint* kps,
+                 uint8_t* desc, int capacity, int* n);
+
+/* Replaces the public member std::vector<cv::Mat> mvImagePyramid — include/ORBextractor.h:100 —
+ * read by Frame::ComputeStereoMatches (src/Frame.cc:529,620,634,639). Levels live on the device until
+ * the next extract on this handle; this copies one level (without the unused 19-px border) to the host. */
+int orbx_pyramid_level_size(const orbx_extractor* e, int level, int* rows, int* cols);
+int orbx_pyramid_level(const orbx_extractor* e, int level, uint8_t* dst, size_t dst_stride);
+
+/* ---- Frame::ComputeStereoMatches ------------------------------------------------------------------ */
+
+/* Replaces void Frame::ComputeStereoMatches() — include/Frame.h:92, src/Frame.cc:522-700 — with
+ * ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1672-1688) inside. left/right are the extractors
+ * that produced kps_l/kps_r (their device-resident pyramids are read). mbf = baseline*fx, mb = baseline
+ * (explicit because the reference reads Frame::mb before assigning it, :552 vs :149). Writes mvuRight /
+ * mvDepth (n_l floats each, -1 = no match). */
+int orbx_stereo_match(orbx_extractor* left, orbx_extractor* right, const orbx_keypoint* kps_l, const uint8_t* desc_l,
+                      int n_l, const orbx_keypoint* kps_r, const uint8_t* desc_r, int n_r, float mbf, float mb,
+                      float* u_right, float* depth);
+
+/* ---- frame batches (throughput path; what Frame::Frame(stereo) does, N frames per call) ----------- */
+
+/* One engine for `max_frames` frames of rows x cols. stereo != 0: each frame is a left/right pair and
+ * the stereo match runs; stereo == 0: mono extraction only (src/Frame.cc:216-260). */
+int orbx_batch_create(int nfeatures, float scale_factor, int nlevels, int ini_th_fast, int min_th_fast, int rows,
+                      int cols, int max_frames, int stereo, int device, orbx_batch** out);
+void orbx_batch_destroy(orbx_batch* b);
+int orbx_batch_max_keypoints(const orbx_batch* b); /* per image: row pitch of the output arrays   */
+
+/* Host -> device copy of n_frames tightly packed images (left[n][rows][cols], right likewise or NULL). */
+int orbx_batch_upload(orbx_batch* b, const uint8_t* left, const uint8_t* right, int n_frames);
+/* Same, but the sources are DEVICE pointers (device-to-device copy). */
+int orbx_batch_upload_device(orbx_batch* b, const void* left_dev, const void* right_dev, int n_frames);
+/* Run extract(L) [+ extract(R) + stereo match] on the resident frames. Asynchronous on the engine's
+ * stream unless `sync` != 0. */
+int orbx_batch_run(orbx_batch* b, int n_frames, float mbf, float mb, int sync);
+/* Device -> host copy of the results. Row pitch of every array is orbx_batch_max_keypoints():
+ *   n_left[n], kps_left[n][P], desc_left[n][P][32], (right likewise), u_right[n][P], depth[n][P].
+ * Any pointer may be NULL (skipped). Synchronises the stream. */
+int orbx_batch_download(orbx_batch* b, int n_frames, int* n_left, orbx_keypoint* kps_left, uint8_t* desc_left,
+                        int* n_right, orbx_keypoint* kps_right, uint8_t* desc_right, float* u_right, float* depth);
+/* Sum of keypoint counts of the last run (left, right) and of valid stereo matches; synchronises. */
+int orbx_batch_stats(orbx_batch* b, int n_frames, long long* n_left, long long* n_right, long long* n_matched);
+/* upload + run + download in one call (the end-to-end path). */
+int orbx_batch_process(orbx_batch* b, const uint8_t* left, const uint8_t* right, int n_frames, float mbf, float mb,
+                       int* n_left, orbx_keypoint* kps_left, uint8_t* desc_left, int* n_right,
+                       orbx_keypoint* kps_right, uint8_t* desc_right, float* u_right, float* depth);
+/* The CUDA stream the engine launches on (cudaStream_t as void*), for event timing by the caller. */
+void* orbx_batch_stream(orbx_batch* b);
+/* Number of kernels one orbx_batch_run launches (for bench.py's gpu_launches). */
+int orbx_batch_launches_per_run(const orbx_batch* b);
+/* Bytes of HBM the engine holds. */
+long long orbx_batch_device_bytes(const orbx_batch* b);
+/* Page-locked host memory for the end-to-end path (cudaHostAlloc / cudaFreeHost). */
+void* orbx_host_alloc(size_t bytes);
+void orbx_host_free(void* p);
+/* Debug/test taps on frame f, side s (0 left, 1 right): pyramid level, blurred level, FAST candidates
+ * of a level in reference order (x,y relative to minBorder; response). */
+int orbx_batch_level_size(const orbx_batch* b, int level, int* rows, int* cols);
+int orbx_batch_level(orbx_batch* b, int frame, int side, int level, int blurred, uint8_t* dst, size_t dst_stride);
+int orbx_batch_candidates(orbx_batch* b, int frame, int side, int level, orbx_keypoint* out, int capacity, int* n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

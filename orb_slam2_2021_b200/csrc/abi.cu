@@ -1,0 +1,343 @@
+// abi.cu — the C-ABI of liborbx.so (declared in include/orbx.h). No CPU fallback anywhere: every
+// compute entry point needs a CUDA device and reports ORBX_ERR_CUDA otherwise.
+#include <cstring>
+#include <memory>
+#include <string>
+
+#include "../../include/orbx.h"
+#include "engine.h"
+
+static thread_local std::string g_err;
+#define TRY(x) do { int rc_ = (x); if (rc_) return rc_; } while (0)
+static int fail(int code, const char* msg) { g_err = msg; return code; }
+
+struct orbx_extractor {
+    ExtractorConfig cfg;
+    int device = 0;
+    std::unique_ptr<Engine> eng;  // capacity 1, rebuilt when the image size changes
+    bool hasRun = false;
+    // stereo scratch (used when this handle is the LEFT one)
+    float* dU = nullptr; float* dD = nullptr; int* dSad = nullptr; int* dNm = nullptr;
+    int scratchKp = 0;
+};
+
+struct orbx_batch {
+    ExtractorConfig cfg;
+    Engine eng;
+    int maxFrames = 0;
+    bool stereo = false;
+};
+
+extern "C" const char* orbx_last_error(void) { return g_err.c_str(); }
+
+extern "C" int orbx_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+static int check_cfg(int nfeatures, float sf, int nlevels, int ini, int mn)
+{
+    if (nfeatures < 1 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !(sf > 1.0f) || ini < 1 || mn < 1 || ini > 254 || mn > ini)
+        return fail(ORBX_ERR_ARG, "bad extractor parameters (need nfeatures>=1, 1<=nlevels<=12, scaleFactor>1, 1<=minTh<=iniTh<=254)");
+    return ORBX_OK;
+}
+
+extern "C" int orbx_create(int nfeatures, float sf, int nlevels, int ini, int mn, int device, orbx_extractor** out)
+{
+    if (!out) return fail(ORBX_ERR_ARG, "out is NULL");
+    *out = nullptr;
+    TRY(check_cfg(nfeatures, sf, nlevels, ini, mn));
+    orbx_extractor* e = new orbx_extractor();
+    e->cfg.init(nfeatures, sf, nlevels, ini, mn);
+    e->device = device;
+    *out = e;
+    return ORBX_OK;
+}
+
+extern "C" void orbx_destroy(orbx_extractor* e)
+{
+    if (!e) return;
+    if (e->dU) { cudaSetDevice(e->device); cudaFree(e->dU); cudaFree(e->dD); cudaFree(e->dSad); cudaFree(e->dNm); }
+    delete e;
+}
+
+extern "C" int orbx_get_levels(const orbx_extractor* e) { return e ? e->cfg.nlevels : ORBX_ERR_ARG; }
+
+extern "C" int orbx_get_tables(const orbx_extractor* e, float* scale, float* inv, float* sig2, float* invSig2, int* quotas)
+{
+    if (!e) return fail(ORBX_ERR_ARG, "handle is NULL");
+    for (int i = 0; i < e->cfg.nlevels; ++i) {
+        if (scale) scale[i] = e->cfg.scale[i];
+        if (inv) inv[i] = e->cfg.invScale[i];
+        if (sig2) sig2[i] = e->cfg.sigma2[i];
+        if (invSig2) invSig2[i] = e->cfg.invSigma2[i];
+        if (quotas) quotas[i] = e->cfg.quota[i];
+    }
+    return ORBX_OK;
+}
+
+extern "C" int orbx_max_keypoints(const orbx_extractor* e, int rows, int cols)
+{
+    if (!e) return fail(ORBX_ERR_ARG, "handle is NULL");
+    OrbxParams p;
+    TRY(Engine::plan(e->cfg, rows, cols, p, g_err));
+    return p.maxKp;
+}
+
+extern "C" int orbx_extract(orbx_extractor* e, const uint8_t* image, int rows, int cols, size_t stride, orbx_keypoint* kps,
+                            uint8_t* desc, int capacity, int* n)
+{
+    if (!e) return fail(ORBX_ERR_ARG, "handle is NULL");
+    if (rows == 0 || cols == 0 || !image) return ORBX_OK;  // src/ORBextractor.cc:1044-1045: silent return
+    if (rows < 0 || cols < 0 || stride < (size_t)cols || !kps || !desc || !n) return fail(ORBX_ERR_ARG, "bad arguments");
+    if (!e->eng || e->eng->rows != rows || e->eng->cols != cols) {
+        e->hasRun = false;
+        std::unique_ptr<Engine> ne(new Engine());
+        TRY(ne->init(e->cfg, rows, cols, 1, false, e->device, g_err));
+        e->eng = std::move(ne);
+    }
+    Engine& E = *e->eng;
+    TRY(E.uploadSingle(image, stride, g_err));
+    TRY(E.runExtract(1, g_err));
+    int cnt = 0;
+    TRY(orbx_check(cudaMemcpyAsync(&cnt, E.P.outCnt, sizeof(int), cudaMemcpyDeviceToHost, E.stream), "D2H count", g_err));
+    TRY(E.sync(g_err));
+    e->hasRun = true;
+    if (cnt > capacity) return fail(ORBX_ERR_CAPACITY, "keypoint capacity too small (see orbx_max_keypoints)");
+    if (cnt > 0) {
+        TRY(orbx_check(cudaMemcpyAsync(kps, E.P.outKp, (size_t)cnt * 28, cudaMemcpyDeviceToHost, E.stream), "D2H kps", g_err));
+        TRY(orbx_check(cudaMemcpyAsync(desc, E.P.outDesc, (size_t)cnt * 32, cudaMemcpyDeviceToHost, E.stream), "D2H desc", g_err));
+        TRY(E.sync(g_err));
+    }
+    *n = cnt;
+    return ORBX_OK;
+}
+
+extern "C" int orbx_pyramid_level_size(const orbx_extractor* e, int level, int* rows, int* cols)
+{
+    if (!e || !rows || !cols) return fail(ORBX_ERR_ARG, "bad arguments");
+    if (!e->eng || !e->hasRun) return fail(ORBX_ERR_STATE, "no image extracted yet");
+    if (level < 0 || level >= e->cfg.nlevels) return fail(ORBX_ERR_ARG, "bad level");
+    *rows = e->eng->P.lv[level].h;
+    *cols = e->eng->P.lv[level].w;
+    return ORBX_OK;
+}
+
+static int copy_level(Engine& E, int img, int level, bool blurred, uint8_t* dst, size_t dstStride)
+{
+    const OrbxLevel& L = E.P.lv[level];
+    const uint8_t* src;
+    size_t pitch;
+    if (blurred) { src = E.P.blur + (size_t)img * E.P.blurStride + L.boff; pitch = L.bpitch; }
+    else if (level == 0) { src = E.P.img0 + (size_t)img * E.P.img0Stride; pitch = E.P.cols; }
+    else { src = E.P.pyr + (size_t)img * E.P.pyrStride + L.off; pitch = L.pitch; }
+    TRY(orbx_check(cudaSetDevice(E.device), "cudaSetDevice", g_err));
+    TRY(orbx_check(cudaMemcpy2DAsync(dst, dstStride, src, pitch, L.w, L.h, cudaMemcpyDeviceToHost, E.stream), "D2H level", g_err));
+    return E.sync(g_err);
+}
+
+extern "C" int orbx_pyramid_level(const orbx_extractor* e, int level, uint8_t* dst, size_t dstStride)
+{
+    if (!e || !dst) return fail(ORBX_ERR_ARG, "bad arguments");
+    if (!e->eng || !e->hasRun) return fail(ORBX_ERR_STATE, "no image extracted yet");
+    if (level < 0 || level >= e->cfg.nlevels || dstStride < (size_t)e->eng->P.lv[level].w) return fail(ORBX_ERR_ARG, "bad level or stride");
+    return copy_level(*e->eng, 0, level, false, dst, dstStride);
+}
+
+extern "C" int orbx_stereo_match(orbx_extractor* l, orbx_extractor* r, const orbx_keypoint* kpsL, const uint8_t* descL, int nL,
+                                 const orbx_keypoint* kpsR, const uint8_t* descR, int nR, float mbf, float mb, float* uRight,
+                                 float* depth)
+{
+    if (!l || !r || nL < 0 || nR < 0 || (nL && (!kpsL || !descL || !uRight || !depth)) || (nR && (!kpsR || !descR)))
+        return fail(ORBX_ERR_ARG, "bad arguments");
+    if (!l->eng || !r->eng || !l->hasRun || !r->hasRun) return fail(ORBX_ERR_STATE, "both extractors must have run");
+    Engine &EL = *l->eng, &ER = *r->eng;
+    if (EL.rows != ER.rows || EL.cols != ER.cols || EL.P.nlevels != ER.P.nlevels || l->device != r->device)
+        return fail(ORBX_ERR_STATE, "left/right extractors differ in image size, levels or device");
+    if (nL > EL.P.maxKp || nR > ER.P.maxKp) return fail(ORBX_ERR_ARG, "more keypoints than the extractor can produce");
+    for (int i = 0; i < nL; ++i) uRight[i] = depth[i] = -1.f;  // src/Frame.cc:524-525
+    if (nL == 0) return ORBX_OK;
+    TRY(orbx_check(cudaSetDevice(l->device), "cudaSetDevice", g_err));
+    if (l->scratchKp < EL.P.maxKp) {
+        if (l->dU) { cudaFree(l->dU); cudaFree(l->dD); cudaFree(l->dSad); cudaFree(l->dNm); l->dU = nullptr; }
+        const size_t k = EL.P.maxKp;
+        TRY(orbx_check(cudaMalloc(&l->dU, k * 4), "stereo scratch", g_err));
+        TRY(orbx_check(cudaMalloc(&l->dD, k * 4), "stereo scratch", g_err));
+        TRY(orbx_check(cudaMalloc(&l->dSad, k * 4), "stereo scratch", g_err));
+        TRY(orbx_check(cudaMalloc(&l->dNm, 4), "stereo scratch", g_err));
+        l->scratchKp = EL.P.maxKp;
+    }
+    cudaStream_t s = EL.stream;
+    // the caller's keypoints/descriptors are authoritative (Frame::mvKeys etc.): put them on the device
+    TRY(orbx_check(cudaMemcpyAsync(EL.P.outKp, kpsL, (size_t)nL * 28, cudaMemcpyHostToDevice, s), "H2D kpsL", g_err));
+    TRY(orbx_check(cudaMemcpyAsync(EL.P.outDesc, descL, (size_t)nL * 32, cudaMemcpyHostToDevice, s), "H2D descL", g_err));
+    TRY(orbx_check(cudaMemcpyAsync(EL.P.outCnt, &nL, 4, cudaMemcpyHostToDevice, s), "H2D nL", g_err));
+    if (nR) {
+        TRY(orbx_check(cudaMemcpyAsync(ER.P.outKp, kpsR, (size_t)nR * 28, cudaMemcpyHostToDevice, s), "H2D kpsR", g_err));
+        TRY(orbx_check(cudaMemcpyAsync(ER.P.outDesc, descR, (size_t)nR * 32, cudaMemcpyHostToDevice, s), "H2D descR", g_err));
+    }
+    TRY(orbx_check(cudaMemcpyAsync(ER.P.outCnt, &nR, 4, cudaMemcpyHostToDevice, s), "H2D nR", g_err));
+    OrbxParams pl = EL.P, pr = ER.P;
+    pl.imgs = pr.imgs = 1;
+    OrbxStereoParams sp{};
+    sp.frames = 1; sp.nlevels = pl.nlevels; sp.rows0 = EL.rows; sp.maxKp = pl.maxKp; sp.mbf = mbf; sp.mb = mb;
+    sp.imgStep = 1; sp.imgOfsL = 0; sp.imgOfsR = 0;
+    sp.uRight = l->dU; sp.depth = l->dD; sp.sad = l->dSad; sp.nMatched = l->dNm;
+    orbx_launch_stereo(pl, pr, sp, s);
+    TRY(orbx_check(cudaGetLastError(), "stereo launch", g_err));
+    TRY(orbx_check(cudaMemcpyAsync(uRight, l->dU, (size_t)nL * 4, cudaMemcpyDeviceToHost, s), "D2H uRight", g_err));
+    TRY(orbx_check(cudaMemcpyAsync(depth, l->dD, (size_t)nL * 4, cudaMemcpyDeviceToHost, s), "D2H depth", g_err));
+    return EL.sync(g_err);
+}
+
+// ---- frame batches ---------------------------------------------------------------------------------
+
+extern "C" int orbx_batch_create(int nfeatures, float sf, int nlevels, int ini, int mn, int rows, int cols, int maxFrames,
+                                 int stereo, int device, orbx_batch** out)
+{
+    if (!out) return fail(ORBX_ERR_ARG, "out is NULL");
+    *out = nullptr;
+    TRY(check_cfg(nfeatures, sf, nlevels, ini, mn));
+    if (maxFrames < 1) return fail(ORBX_ERR_ARG, "max_frames < 1");
+    std::unique_ptr<orbx_batch> b(new orbx_batch());
+    b->cfg.init(nfeatures, sf, nlevels, ini, mn);
+    b->maxFrames = maxFrames;
+    b->stereo = stereo != 0;
+    TRY(b->eng.init(b->cfg, rows, cols, maxFrames * (b->stereo ? 2 : 1), b->stereo, device, g_err));
+    *out = b.release();
+    return ORBX_OK;
+}
+
+extern "C" void orbx_batch_destroy(orbx_batch* b) { delete b; }
+extern "C" int orbx_batch_max_keypoints(const orbx_batch* b) { return b ? b->eng.P.maxKp : ORBX_ERR_ARG; }
+extern "C" void* orbx_batch_stream(orbx_batch* b) { return b ? (void*)b->eng.stream : nullptr; }
+extern "C" int orbx_batch_launches_per_run(const orbx_batch* b)
+{
+    return b ? b->eng.launchesPerExtract + (b->stereo ? 2 : 0) : ORBX_ERR_ARG;
+}
+extern "C" long long orbx_batch_device_bytes(const orbx_batch* b) { return b ? (long long)b->eng.bytesAllocated : 0; }
+
+extern "C" int orbx_batch_upload(orbx_batch* b, const uint8_t* left, const uint8_t* right, int nFrames)
+{
+    if (!b) return fail(ORBX_ERR_ARG, "handle is NULL");
+    return b->eng.uploadImages(left, right, nFrames, false, g_err);
+}
+
+extern "C" int orbx_batch_upload_device(orbx_batch* b, const void* left, const void* right, int nFrames)
+{
+    if (!b) return fail(ORBX_ERR_ARG, "handle is NULL");
+    return b->eng.uploadImages((const uint8_t*)left, (const uint8_t*)right, nFrames, true, g_err);
+}
+
+extern "C" int orbx_batch_run(orbx_batch* b, int nFrames, float mbf, float mb, int sync)
+{
+    if (!b || nFrames < 1 || nFrames > b->maxFrames) return fail(ORBX_ERR_ARG, "bad frame count");
+    TRY(b->eng.runExtract(nFrames * (b->stereo ? 2 : 1), g_err));
+    if (b->stereo) TRY(b->eng.runStereo(nFrames, mbf, mb, g_err));
+    return sync ? b->eng.sync(g_err) : ORBX_OK;
+}
+
+// one strided D2H copy: host [n][rowBytes] <- device rows of stride devStride starting at src
+static int d2h_rows(Engine& E, void* dst, const void* src, size_t rowBytes, size_t devStride, int n, const char* what)
+{
+    if (!dst) return ORBX_OK;
+    return orbx_check(cudaMemcpy2DAsync(dst, rowBytes, src, devStride, rowBytes, n, cudaMemcpyDeviceToHost, E.stream), what, g_err);
+}
+
+extern "C" int orbx_batch_download(orbx_batch* b, int nFrames, int* nLeft, orbx_keypoint* kpsLeft, uint8_t* descLeft, int* nRight,
+                                   orbx_keypoint* kpsRight, uint8_t* descRight, float* uRight, float* depth)
+{
+    if (!b || nFrames < 1 || nFrames > b->maxFrames) return fail(ORBX_ERR_ARG, "bad frame count");
+    Engine& E = b->eng;
+    TRY(orbx_check(cudaSetDevice(E.device), "cudaSetDevice", g_err));
+    const size_t per = b->stereo ? 2 : 1, P = E.P.maxKp;
+    const uint8_t* kp = (const uint8_t*)E.P.outKp;
+    TRY(d2h_rows(E, nLeft, E.P.outCnt, 4, per * 4, nFrames, "D2H nLeft"));
+    TRY(d2h_rows(E, kpsLeft, kp, P * 28, per * P * 28, nFrames, "D2H kpsLeft"));
+    TRY(d2h_rows(E, descLeft, E.P.outDesc, P * 32, per * P * 32, nFrames, "D2H descLeft"));
+    if (b->stereo) {
+        TRY(d2h_rows(E, nRight, E.P.outCnt + 1, 4, per * 4, nFrames, "D2H nRight"));
+        TRY(d2h_rows(E, kpsRight, kp + P * 28, P * 28, per * P * 28, nFrames, "D2H kpsRight"));
+        TRY(d2h_rows(E, descRight, E.P.outDesc + P * 32, P * 32, per * P * 32, nFrames, "D2H descRight"));
+        TRY(d2h_rows(E, uRight, E.SP.uRight, P * 4, P * 4, nFrames, "D2H uRight"));
+        TRY(d2h_rows(E, depth, E.SP.depth, P * 4, P * 4, nFrames, "D2H depth"));
+    }
+    return E.sync(g_err);
+}
+
+extern "C" int orbx_batch_process(orbx_batch* b, const uint8_t* left, const uint8_t* right, int nFrames, float mbf, float mb,
+                                  int* nLeft, orbx_keypoint* kpsLeft, uint8_t* descLeft, int* nRight, orbx_keypoint* kpsRight,
+                                  uint8_t* descRight, float* uRight, float* depth)
+{
+    TRY(orbx_batch_upload(b, left, right, nFrames));
+    TRY(orbx_batch_run(b, nFrames, mbf, mb, 0));
+    return orbx_batch_download(b, nFrames, nLeft, kpsLeft, descLeft, nRight, kpsRight, descRight, uRight, depth);
+}
+
+extern "C" int orbx_batch_stats(orbx_batch* b, int nFrames, long long* nLeft, long long* nRight, long long* nMatched)
+{
+    if (!b || nFrames < 1 || nFrames > b->maxFrames) return fail(ORBX_ERR_ARG, "bad frame count");
+    Engine& E = b->eng;
+    const int per = b->stereo ? 2 : 1;
+    std::vector<int> cnt((size_t)nFrames * per), nm(nFrames, 0);
+    TRY(orbx_check(cudaSetDevice(E.device), "cudaSetDevice", g_err));
+    TRY(orbx_check(cudaMemcpyAsync(cnt.data(), E.P.outCnt, cnt.size() * 4, cudaMemcpyDeviceToHost, E.stream), "D2H counts", g_err));
+    if (b->stereo) TRY(orbx_check(cudaMemcpyAsync(nm.data(), E.SP.nMatched, nm.size() * 4, cudaMemcpyDeviceToHost, E.stream), "D2H matched", g_err));
+    TRY(E.sync(g_err));
+    long long l = 0, r = 0, m = 0;
+    for (int f = 0; f < nFrames; ++f) { l += cnt[(size_t)f * per]; if (b->stereo) { r += cnt[(size_t)f * 2 + 1]; m += nm[f]; } }
+    if (nLeft) *nLeft = l;
+    if (nRight) *nRight = r;
+    if (nMatched) *nMatched = m;
+    return ORBX_OK;
+}
+
+extern "C" int orbx_batch_level_size(const orbx_batch* b, int level, int* rows, int* cols)
+{
+    if (!b || level < 0 || level >= b->cfg.nlevels || !rows || !cols) return fail(ORBX_ERR_ARG, "bad arguments");
+    *rows = b->eng.P.lv[level].h;
+    *cols = b->eng.P.lv[level].w;
+    return ORBX_OK;
+}
+
+extern "C" int orbx_batch_level(orbx_batch* b, int frame, int side, int level, int blurred, uint8_t* dst, size_t dstStride)
+{
+    if (!b || !dst || level < 0 || level >= b->cfg.nlevels || frame < 0 || frame >= b->maxFrames || side < 0 || side > (b->stereo ? 1 : 0))
+        return fail(ORBX_ERR_ARG, "bad arguments");
+    return copy_level(b->eng, frame * (b->stereo ? 2 : 1) + side, level, blurred != 0, dst, dstStride);
+}
+
+extern "C" int orbx_batch_candidates(orbx_batch* b, int frame, int side, int level, orbx_keypoint* out, int capacity, int* n)
+{
+    if (!b || !n || level < 0 || level >= b->cfg.nlevels || frame < 0 || frame >= b->maxFrames || side < 0 || side > (b->stereo ? 1 : 0))
+        return fail(ORBX_ERR_ARG, "bad arguments");
+    Engine& E = b->eng;
+    const int img = frame * (b->stereo ? 2 : 1) + side;
+    const OrbxLevel& L = E.P.lv[level];
+    int cnt = 0;
+    TRY(orbx_check(cudaSetDevice(E.device), "cudaSetDevice", g_err));
+    TRY(orbx_check(cudaMemcpy(&cnt, E.P.candCnt + (size_t)img * E.P.nlevels + level, 4, cudaMemcpyDeviceToHost), "D2H candCnt", g_err));
+    *n = cnt;
+    const int m = cnt < capacity ? cnt : capacity;
+    if (m <= 0 || !out) return ORBX_OK;
+    std::vector<uint32_t> xy(m);
+    std::vector<uint8_t> rs(m);
+    TRY(orbx_check(cudaMemcpy(xy.data(), E.P.candXY + (size_t)img * E.P.candTotal + L.candBase, (size_t)m * 4, cudaMemcpyDeviceToHost), "D2H candXY", g_err));
+    TRY(orbx_check(cudaMemcpy(rs.data(), E.P.candRs + (size_t)img * E.P.candTotal + L.candBase, (size_t)m, cudaMemcpyDeviceToHost), "D2H candRs", g_err));
+    for (int i = 0; i < m; ++i) {
+        out[i].x = (float)(xy[i] & 0xFFFF); out[i].y = (float)(xy[i] >> 16); out[i].size = 7.f; out[i].angle = -1.f;
+        out[i].response = (float)rs[i]; out[i].octave = 0; out[i].class_id = -1;
+    }
+    return ORBX_OK;
+}
+
+// pinned host memory for the end-to-end path
+extern "C" void* orbx_host_alloc(size_t bytes)
+{
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { g_err = "cudaHostAlloc failed"; cudaGetLastError(); return nullptr; }
+    return p;
+}
+extern "C" void orbx_host_free(void* p) { if (p) cudaFreeHost(p); }

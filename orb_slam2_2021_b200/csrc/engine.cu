@@ -1,0 +1,312 @@
+// engine.cu — host side: extractor tables, level/cell/tile geometry, HBM buffers, launch sequence.
+#include "engine.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/orbx.h"
+
+int orbx_check(cudaError_t e, const char* what, std::string& err)
+{
+    if (e == cudaSuccess) return ORBX_OK;
+    err = std::string(what) + ": " + cudaGetErrorString(e);
+    return ORBX_ERR_CUDA;
+}
+
+// ORBextractor::ORBextractor, /root/reference/src/ORBextractor.cc:413-449. scaleFactor is stored in a
+// double member initialised from the float argument (include/ORBextractor.h:113), so products and
+// quotients below are taken in double and rounded to float exactly where the reference does.
+void ExtractorConfig::init(int nf, float sf, int nl, int ini, int mn)
+{
+    nfeatures = nf; scaleFactor = sf; nlevels = nl; iniTh = ini; minTh = mn;
+    const double sfd = (double)sf;
+    scale.assign(nl, 1.f); sigma2.assign(nl, 1.f); invScale.assign(nl, 1.f); invSigma2.assign(nl, 1.f);
+    for (int i = 1; i < nl; ++i) {
+        scale[i] = (float)((double)scale[i - 1] * sfd);
+        sigma2[i] = scale[i] * scale[i];
+    }
+    for (int i = 0; i < nl; ++i) {
+        invScale[i] = 1.0f / scale[i];
+        invSigma2[i] = 1.0f / sigma2[i];
+    }
+    quota.assign(nl, 0);
+    const float factor = (float)(1.0 / sfd);
+    float desired = nf * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; ++l) {
+        quota[l] = orbx_cvround(desired);
+        sum += quota[l];
+        desired *= factor;
+    }
+    quota[nl - 1] = nf - sum > 0 ? nf - sum : 0;
+}
+
+static inline unsigned align_up(unsigned v, unsigned a) { return (v + a - 1) / a * a; }
+
+struct HostCell {
+    short x0, y0;
+    uint8_t rw, rh, level, pad;
+};
+struct HostTile {
+    short x0, y0;
+    uint8_t level, pad[3];
+};
+
+// Cell grid of one level, /root/reference/src/ORBextractor.cc:776-809 (float arithmetic kept).
+static void level_cells(int w, int h, int level, OrbxLevel& L, std::vector<HostCell>* out)
+{
+    const int minBX = ORBX_EDGE - 3, minBY = minBX, maxBX = w - ORBX_EDGE + 3, maxBY = h - ORBX_EDGE + 3;
+    const float W = 30;
+    const float width = (float)(maxBX - minBX), height = (float)(maxBY - minBY);
+    L.nCols = (int)(width / W);
+    L.nRows = (int)(height / W);
+    L.wCell = (int)std::ceil(width / L.nCols);
+    L.hCell = (int)std::ceil(height / L.nRows);
+    L.nCells = 0;
+    for (int i = 0; i < L.nRows; ++i) {
+        const float iniY = (float)(minBY + i * L.hCell);
+        float maxY = iniY + L.hCell + 6;
+        if (iniY >= maxBY - 3) continue;
+        if (maxY > maxBY) maxY = (float)maxBY;
+        for (int j = 0; j < L.nCols; ++j) {
+            const float iniX = (float)(minBX + j * L.wCell);
+            float maxX = iniX + L.wCell + 6;
+            if (iniX >= maxBX - 6) continue;
+            if (maxX > maxBX) maxX = (float)maxBX;
+            if (out) {
+                HostCell c;
+                c.x0 = (short)iniX; c.y0 = (short)iniY;
+                c.rw = (uint8_t)((int)maxX - (int)iniX); c.rh = (uint8_t)((int)maxY - (int)iniY);
+                c.level = (uint8_t)level; c.pad = 0;
+                out->push_back(c);
+            }
+            ++L.nCells;
+        }
+    }
+}
+
+int Engine::plan(const ExtractorConfig& cfg, int rows, int cols, OrbxParams& p, std::string& err)
+{
+    if (cfg.nlevels < 1 || cfg.nlevels > ORBX_MAX_LEVELS) { err = "nlevels out of range (1..12)"; return ORBX_ERR_ARG; }
+    if (rows <= 0 || cols <= 0 || cols > 32000 || rows > 32000) { err = "bad image size"; return ORBX_ERR_ARG; }
+    std::memset(&p, 0, sizeof(p));
+    p.nlevels = cfg.nlevels; p.iniTh = cfg.iniTh; p.minTh = cfg.minTh; p.rows = rows; p.cols = cols;
+    unsigned off = 0, boff = 0, slot = 0, cand = 0;
+    int cellBase = 0, keepBase = 0;
+    for (int l = 0; l < cfg.nlevels; ++l) {
+        OrbxLevel& L = p.lv[l];
+        L.w = orbx_cvround((float)cols * cfg.invScale[l]);  // :1110
+        L.h = orbx_cvround((float)rows * cfg.invScale[l]);
+        if (L.w - 32 < 30 || L.h - 32 < 30) {
+            err = "pyramid level " + std::to_string(l) + " smaller than 62 px: the reference divides by zero here";
+            return ORBX_ERR_GEOMETRY;
+        }
+        L.pitch = l == 0 ? cols : (int)align_up(L.w, 16);
+        L.bpitch = (int)align_up(L.w, 16);
+        L.off = off;
+        if (l > 0) off += align_up((unsigned)L.pitch * L.h, 256);
+        L.boff = boff;
+        boff += align_up((unsigned)L.bpitch * L.h, 256);
+        level_cells(L.w, L.h, l, L, nullptr);
+        L.cellBase = cellBase; cellBase += L.nCells;
+        L.slotCap = ((L.wCell + 1) / 2) * ((L.hCell + 1) / 2);
+        L.slotBase = slot; slot += (unsigned)L.nCells * L.slotCap;
+        L.candBase = cand; L.candCap = L.nCells * L.slotCap; cand += L.candCap;
+        if (L.candCap >= (1 << 24)) { err = "level too large (candidate index needs 24 bits)"; return ORBX_ERR_GEOMETRY; }
+        L.quota = cfg.quota[l];
+        const int bw = L.w - 32, bh = L.h - 32;
+        L.nIni = (int)std::round((float)bw / bh);  // :546
+        if (L.nIni < 1) { err = "portrait level: nIni == 0, the reference divides by zero here"; return ORBX_ERR_GEOMETRY; }
+        L.hX = (float)bw / L.nIni;  // :548
+        int cap = (L.quota > 4 * L.nIni ? L.quota : 4 * L.nIni) + 4;
+        L.keepCap = (cap + 3) & ~3;
+        if (L.keepCap > 65000) { err = "per-level quota too large"; return ORBX_ERR_ARG; }
+        L.keepBase = keepBase; keepBase += L.keepCap;
+        L.scale = cfg.scale[l]; L.invScale = cfg.invScale[l];
+        L.patchSize = (int)(31 * cfg.scale[l]);  // :836
+    }
+    p.img0Stride = (size_t)rows * cols;
+    p.pyrStride = off; p.blurStride = boff;
+    p.cellsTotal = cellBase; p.slotTotal = slot; p.candTotal = cand;
+    p.keepTotal = keepBase; p.maxKp = keepBase;
+    if (p.maxKp > 65535) { err = "more than 65535 keypoints per image not supported"; return ORBX_ERR_ARG; }
+    return ORBX_OK;
+}
+
+// cv::resize(INTER_LINEAR) coefficient tables for one axis (OpenCV imgproc/resize.cpp): 11-bit fixed
+// point, computed in the same float64/float32 steps on the host so the kernel only does integer math.
+static void axis_table(int src, int dst, bool clampFrac, int* ofs, int* coef)
+{
+    const double scale = 1.0 / ((double)dst / src);
+    for (int d = 0; d < dst; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)std::floor(f);
+        f -= s;
+        if (clampFrac) {
+            if (s < 0) { s = 0; f = 0.f; }
+            if (s >= src - 1) { s = src - 1; f = 0.f; }
+        }
+        const int c0 = (short)orbx_cvround((1.f - f) * 2048.f), c1 = (short)orbx_cvround(f * 2048.f);
+        ofs[d] = s;
+        coef[d] = (c0 & 0xFFFF) | (c1 << 16);
+    }
+}
+
+Engine::~Engine() { release(); }
+
+void Engine::release()
+{
+    if (allocs.empty() && !stream) return;
+    cudaSetDevice(device);
+    for (void* a : allocs) cudaFree(a);
+    allocs.clear();
+    if (stream) cudaStreamDestroy(stream);
+    stream = nullptr;
+    bytesAllocated = 0;
+}
+
+template <typename T>
+static int dalloc(Engine* e, T** ptr, size_t count, const char* what, std::string& err)
+{
+    void* d = nullptr;
+    const size_t bytes = (count ? count : 1) * sizeof(T);
+    int rc = orbx_check(cudaMalloc(&d, bytes), what, err);
+    if (rc) return rc;
+    e->allocs.push_back(d);
+    e->bytesAllocated += bytes;
+    *ptr = (T*)d;
+    return ORBX_OK;
+}
+
+#define TRY(x) do { int rc_ = (x); if (rc_) return rc_; } while (0)
+
+int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int dev, std::string& err)
+{
+    release();
+    cfg = c; rows = r; cols = w; maxImgs = nImgs; stereo = st; device = dev;
+    if (nImgs < 1 || nImgs > 65535) { err = "image capacity must be 1..65535"; return ORBX_ERR_ARG; }
+    TRY(plan(cfg, rows, cols, P, err));
+    P.imgs = nImgs;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { err = "no CUDA device: liborbx has no CPU path"; return ORBX_ERR_CUDA; }
+    TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
+    TRY(orbx_check(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking), "cudaStreamCreate", err));
+
+    const size_t n = (size_t)nImgs;
+    TRY(dalloc(this, &P.img0, n * P.img0Stride + 64, "img0", err));
+    TRY(dalloc(this, &P.pyr, n * P.pyrStride + 64, "pyr", err));
+    TRY(dalloc(this, &P.blur, n * P.blurStride + 64, "blur", err));
+    TRY(dalloc(this, &P.cellCnt, n * P.cellsTotal, "cellCnt", err));
+    TRY(dalloc(this, &P.cellKp, n * P.slotTotal, "cellKp", err));
+    TRY(dalloc(this, &P.candXY, n * P.candTotal, "candXY", err));
+    TRY(dalloc(this, &P.candRs, n * P.candTotal, "candRs", err));
+    TRY(dalloc(this, &P.label, n * P.candTotal, "label", err));
+    TRY(dalloc(this, &P.keep, n * P.keepTotal, "keep", err));
+    TRY(dalloc(this, &P.keepCnt, n * P.nlevels, "keepCnt", err));
+    TRY(dalloc(this, &P.candCnt, n * P.nlevels, "candCnt", err));
+    uint8_t* okp = nullptr;
+    TRY(dalloc(this, &okp, n * P.maxKp * 28, "outKp", err));
+    P.outKp = okp;
+    TRY(dalloc(this, &P.outDesc, n * P.maxKp * 32, "outDesc", err));
+    TRY(dalloc(this, &P.outCnt, n, "outCnt", err));
+    TRY(orbx_check(cudaMemsetAsync(P.outCnt, 0, n * sizeof(int), stream), "memset", err));
+
+    // cell table and blur tile table
+    std::vector<HostCell> cells;
+    std::vector<HostTile> tiles;
+    for (int l = 0; l < P.nlevels; ++l) {
+        OrbxLevel tmp = P.lv[l];
+        level_cells(P.lv[l].w, P.lv[l].h, l, tmp, &cells);
+        for (int y = 0; y < P.lv[l].h; y += 32)
+            for (int x = 0; x < P.lv[l].w; x += 64) {
+                HostTile t; t.x0 = (short)x; t.y0 = (short)y; t.level = (uint8_t)l; t.pad[0] = t.pad[1] = t.pad[2] = 0;
+                tiles.push_back(t);
+            }
+    }
+    nTiles = (int)tiles.size();
+    HostCell* dc = nullptr; HostTile* dt = nullptr;
+    TRY(dalloc(this, &dc, cells.size(), "cells", err));
+    TRY(dalloc(this, &dt, tiles.size(), "tiles", err));
+    dCells = dc; dTiles = dt;
+    TRY(orbx_check(cudaMemcpy(dc, cells.data(), cells.size() * sizeof(HostCell), cudaMemcpyHostToDevice), "cells H2D", err));
+    TRY(orbx_check(cudaMemcpy(dt, tiles.data(), tiles.size() * sizeof(HostTile), cudaMemcpyHostToDevice), "tiles H2D", err));
+
+    // resize tables: per level >= 1: xofs[w] xcoef[w] yofs[h] ycoef[h]
+    std::vector<int> tab;
+    std::vector<size_t> tabOff(P.nlevels, 0);
+    for (int l = 1; l < P.nlevels; ++l) {
+        const OrbxLevel &S = P.lv[l - 1], &D = P.lv[l];
+        tabOff[l] = tab.size();
+        tab.resize(tab.size() + 2 * D.w + 2 * D.h);
+        int* base = tab.data() + tabOff[l];
+        axis_table(S.w, D.w, true, base, base + D.w);
+        axis_table(S.h, D.h, false, base + 2 * D.w, base + 2 * D.w + D.h);
+    }
+    TRY(dalloc(this, &dResizeTab, tab.size(), "resizeTab", err));
+    TRY(orbx_check(cudaMemcpy(dResizeTab, tab.data(), tab.size() * sizeof(int), cudaMemcpyHostToDevice), "tab H2D", err));
+    resizeTabs.assign(P.nlevels, nullptr);
+    for (int l = 1; l < P.nlevels; ++l) resizeTabs[l] = dResizeTab + tabOff[l];
+
+    if (stereo) {
+        const size_t fr = n / 2;
+        SP.maxKp = P.maxKp; SP.nlevels = P.nlevels; SP.rows0 = rows;
+        SP.imgStep = 2; SP.imgOfsL = 0; SP.imgOfsR = 1;
+        TRY(dalloc(this, &SP.uRight, fr * P.maxKp, "uRight", err));
+        TRY(dalloc(this, &SP.depth, fr * P.maxKp, "depth", err));
+        TRY(dalloc(this, &SP.sad, fr * P.maxKp, "sad", err));
+        TRY(dalloc(this, &SP.nMatched, fr, "nMatched", err));
+    }
+    launchesPerExtract = (P.nlevels - 1) + 1 + 1 + 1 + 2;
+    return orbx_check(cudaStreamSynchronize(stream), "init sync", err);
+}
+
+int Engine::uploadImages(const uint8_t* left, const uint8_t* right, int nFrames, bool fromDevice, std::string& err)
+{
+    const int per = stereo ? 2 : 1;
+    if (nFrames < 1 || nFrames * per > maxImgs || !left || (stereo && !right)) { err = "bad upload arguments"; return ORBX_ERR_ARG; }
+    TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
+    const size_t img = P.img0Stride;
+    const cudaMemcpyKind kind = fromDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    // image 2f+s <- side s of frame f: one strided 2-D copy per side
+    TRY(orbx_check(cudaMemcpy2DAsync(P.img0, per * img, left, img, img, nFrames, kind, stream), "upload left", err));
+    if (stereo)
+        TRY(orbx_check(cudaMemcpy2DAsync(P.img0 + img, per * img, right, img, img, nFrames, kind, stream), "upload right", err));
+    return ORBX_OK;
+}
+
+int Engine::uploadSingle(const uint8_t* image, size_t stride, std::string& err)
+{
+    TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
+    return orbx_check(cudaMemcpy2DAsync(P.img0, cols, image, stride, cols, rows, cudaMemcpyHostToDevice, stream), "upload image", err);
+}
+
+int Engine::runExtract(int nImgs, std::string& err)
+{
+    if (nImgs < 1 || nImgs > maxImgs) { err = "bad image count"; return ORBX_ERR_ARG; }
+    TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
+    OrbxParams p = P;
+    p.imgs = nImgs;
+    orbx_launch_pyramid(p, resizeTabs.data(), stream);
+    orbx_launch_fast(p, dCells, stream);
+    orbx_launch_octree(p, dCells, stream);
+    orbx_launch_blur(p, dTiles, nTiles, stream);
+    orbx_launch_describe(p, stream);
+    return orbx_check(cudaGetLastError(), "extract launch", err);
+}
+
+int Engine::runStereo(int nFrames, float mbf, float mb, std::string& err)
+{
+    if (!stereo || nFrames < 1 || nFrames * 2 > maxImgs) { err = "bad stereo arguments"; return ORBX_ERR_ARG; }
+    OrbxParams p = P;
+    p.imgs = nFrames * 2;
+    OrbxStereoParams sp = SP;
+    sp.frames = nFrames; sp.mbf = mbf; sp.mb = mb;
+    orbx_launch_stereo(p, p, sp, stream);
+    return orbx_check(cudaGetLastError(), "stereo launch", err);
+}
+
+int Engine::sync(std::string& err)
+{
+    return orbx_check(cudaStreamSynchronize(stream), "stream sync", err);
+}

@@ -1,0 +1,56 @@
+// engine.h — host side of the device pipeline: geometry tables, HBM buffers, launch sequence.
+// One Engine serves a fixed (extractor parameters, image size, max images) configuration. The
+// single-image handle (orbx_extractor) owns an Engine of capacity 1 that is rebuilt when the image
+// size changes; the batch handle (orbx_batch) owns one of capacity max_frames*(1|2).
+#pragma once
+#include <string>
+#include <vector>
+
+#include "orbx_dev.cuh"
+
+struct ExtractorConfig {
+    int nfeatures, nlevels, iniTh, minTh;
+    float scaleFactor;
+    // ORBextractor::ORBextractor tables (src/ORBextractor.cc:413-449)
+    std::vector<float> scale, invScale, sigma2, invSigma2;
+    std::vector<int> quota;
+    void init(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh);
+};
+
+class Engine {
+public:
+    Engine() = default;
+    ~Engine();
+    Engine(const Engine&) = delete;
+    Engine& operator=(const Engine&) = delete;
+
+    // returns 0 or an orbx_status; err receives the text
+    int init(const ExtractorConfig& cfg, int rows, int cols, int maxImgs, bool stereo, int device, std::string& err);
+    void release();
+
+    // level geometry without allocating anything (for orbx_max_keypoints)
+    static int plan(const ExtractorConfig& cfg, int rows, int cols, OrbxParams& p, std::string& err);
+
+    int uploadImages(const uint8_t* left, const uint8_t* right, int nFrames, bool fromDevice, std::string& err);
+    int uploadSingle(const uint8_t* img, size_t stride, std::string& err);
+    int runExtract(int nImgs, std::string& err);                         // pyramid .. describe
+    int runStereo(int nFrames, float mbf, float mb, std::string& err);   // both sides in this engine
+    int sync(std::string& err);
+
+    OrbxParams P{};          // device pointers + geometry (imgs = capacity)
+    OrbxStereoParams SP{};   // stereo outputs (batch engines with stereo == true)
+    ExtractorConfig cfg;
+    int device = 0, maxImgs = 0, rows = 0, cols = 0;
+    bool stereo = false;
+    cudaStream_t stream = nullptr;
+    int nTiles = 0;
+    void* dCells = nullptr;
+    void* dTiles = nullptr;
+    int* dResizeTab = nullptr;
+    std::vector<const int*> resizeTabs;  // per level device pointers into dResizeTab
+    std::vector<void*> allocs;
+    size_t bytesAllocated = 0;
+    int launchesPerExtract = 0;
+};
+
+int orbx_check(cudaError_t e, const char* what, std::string& err);

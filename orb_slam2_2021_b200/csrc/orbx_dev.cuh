@@ -1,0 +1,100 @@
+// orbx_dev.cuh — device-side data layout shared by all kernels and the host engine.
+//
+// HBM layout for a chunk of `imgs` images (stereo: image 2f = left of frame f, 2f+1 = right):
+//   img0   [imgs][H*W]            u8  level 0 = the uploaded image, tight rows (pitch W)
+//   pyr    [imgs][pyrStride]      u8  levels 1..L-1 packed, row pitch = align16(w_l)
+//   blur   [imgs][blurStride]     u8  7x7 Gaussian of levels 0..L-1, row pitch = align16(w_l)
+//   cellCnt[imgs][cellsTotal]     i32 FAST keypoints per 30-px cell
+//   cellKp [imgs][slotTotal]      u32 per-cell slots (x | y<<8 | score<<16), ROI coordinates
+//   candXY [imgs][candTotal]      u32 level candidates in reference order (x | y<<16, rel. minBorder)
+//   candRs [imgs][candTotal]      u8  FAST score
+//   label  [imgs][candTotal]      u16 quadtree node (list position) of each candidate
+//   keep   [imgs][keepTotal]      u32x2 kept keypoints per level in final list order (xy, score)
+//   keepCnt[imgs][L]              i32
+//   outKp  [imgs][maxKp] 28 B, outDesc [imgs][maxKp][32], outCnt [imgs]
+//   uRight/depth [frames][maxKp]  f32, matchSad [frames][maxKp] i32 (scratch for the median cut)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "orbx_math.h"
+
+#define ORBX_MAX_LEVELS 12
+#define ORBX_EDGE 19
+#define ORBX_HALF_PATCH 15
+
+struct OrbxLevel {
+    int w, h, pitch;      // level size; row pitch in pyr (level 0: pitch == w in img0)
+    int bpitch;           // row pitch in blur
+    unsigned off;         // byte offset inside one image's pyr block (levels >= 1)
+    unsigned boff;        // byte offset inside one image's blur block
+    int nCols, nRows, wCell, hCell;  // FAST cell grid (src/ORBextractor.cc:784-790)
+    int cellBase, nCells;            // index of the first cell of this level in cellCnt
+    int slotCap;                     // per-cell slot capacity = ceil(wCell/2)*ceil(hCell/2)
+    unsigned slotBase;               // first slot of this level in cellKp
+    unsigned candBase;               // first candidate of this level in candXY/candRs/label
+    int candCap;
+    int quota, nIni, keepCap, keepBase;
+    float scale, invScale;
+    int patchSize;                   // (int)(31*scale) as float size of the keypoint
+    float hX;                        // (float)(maxBX-minBX)/nIni
+};
+
+struct OrbxParams {
+    int nlevels, iniTh, minTh;
+    int rows, cols;
+    int imgs;  // images in this launch
+    OrbxLevel lv[ORBX_MAX_LEVELS];
+    // per-image strides (elements of the respective type)
+    size_t img0Stride, pyrStride, blurStride;
+    int cellsTotal;
+    unsigned slotTotal, candTotal;
+    int keepTotal, maxKp;
+    // buffers
+    uint8_t* img0;
+    uint8_t* pyr;
+    uint8_t* blur;
+    int* cellCnt;
+    uint32_t* cellKp;
+    uint32_t* candXY;
+    uint8_t* candRs;
+    uint16_t* label;
+    uint2* keep;
+    int* keepCnt;
+    int* candCnt;  // [imgs][L] number of candidates per level (written by the quadtree kernel)
+    void* outKp;   // orbx_keypoint[imgs][maxKp]
+    uint8_t* outDesc;
+    int* outCnt;
+};
+
+__device__ __forceinline__ const uint8_t* orbx_level_ptr(const OrbxParams& p, int img, int l, int* pitch)
+{
+    if (l == 0) {
+        *pitch = p.cols;
+        return p.img0 + (size_t)img * p.img0Stride;
+    }
+    *pitch = p.lv[l].pitch;
+    return p.pyr + (size_t)img * p.pyrStride + p.lv[l].off;
+}
+
+// Stereo stage parameters: left/right images may live in two different engines (two handles).
+struct OrbxStereoParams {
+    int frames, nlevels, rows0;
+    int maxKp;
+    float mbf, mb;
+    // per-side image geometry comes from the side's OrbxParams; image index of frame f on side s is
+    // f*imgStep + imgOfs[s] (batch engine: step 2, ofs {0,1}; two handles: step 1, ofs {0,0}).
+    int imgStep, imgOfsL, imgOfsR;
+    float* uRight;  // [frames][maxKp]
+    float* depth;
+    int* sad;       // [frames][maxKp] best SAD of accepted matches, -1 otherwise
+    int* nMatched;  // [frames]
+};
+
+// Launch wrappers (one per kernel group), defined in the .cu files.
+void orbx_launch_pyramid(const OrbxParams& p, const int* const* tabs, cudaStream_t s);
+void orbx_launch_fast(const OrbxParams& p, const void* cellTable, cudaStream_t s);
+void orbx_launch_octree(const OrbxParams& p, const void* cellTable, cudaStream_t s);
+void orbx_launch_blur(const OrbxParams& p, const void* tileTable, int nTiles, cudaStream_t s);
+void orbx_launch_describe(const OrbxParams& p, cudaStream_t s);
+void orbx_launch_stereo(const OrbxParams& pl, const OrbxParams& pr, const OrbxStereoParams& sp, cudaStream_t s);

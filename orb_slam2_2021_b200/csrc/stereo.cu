@@ -1,0 +1,215 @@
+// stereo.cu — Frame::ComputeStereoMatches on the device (/root/reference/src/Frame.cc:522-700) with
+// ORBmatcher::DescriptorDistance (/root/reference/src/ORBmatcher.cc:1672-1688).
+//
+// Kernel 1, one warp per LEFT keypoint:
+//   * row-band candidate test without materialising vRowIndices (:532-549): right keypoint iR is a
+//     candidate of row (int)vL iff floor(yR - 2*s_oct) <= row <= ceil(yR + 2*s_oct); plus the octave
+//     (:588) and disparity-range (:593) tests;
+//   * 256-bit Hamming as 8 x __popc on two uint4 loads; the reference keeps the FIRST strictly
+//     smaller distance while scanning iR ascending from TH_HIGH=100, i.e. the lexicographic minimum
+//     of (dist, iR): each lane keeps min(dist<<16 | iR), then a warp shuffle-min;
+//   * if best < 75: 11x11 SAD against 11 horizontal offsets on the un-blurred pyramid level of the
+//     left keypoint (:608-652): 121 pixels spread over the lanes, 11 accumulators per lane, warp
+//     reductions; then parabola sub-pixel fit, disparity and depth (:657-683) as single IEEE ops.
+// Kernel 2, one CTA per frame: median of the accepted matches' SAD by a two-pass 8-bit radix select
+// (SAD <= 121*510 < 2^16) and invalidation of SAD >= 1.5*1.4*median (:686-699).
+#include "orbx_dev.cuh"
+
+#define ST_WARPS 8
+
+struct KpRec {
+    float x, y, size, angle, response;
+    int octave, class_id;
+};
+
+__device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint8_t* b)
+{
+    const uint4 b0 = *reinterpret_cast<const uint4*>(b), b1 = *reinterpret_cast<const uint4*>(b + 16);
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+__global__ void __launch_bounds__(ST_WARPS * 32) orbx_stereo_match_kernel(OrbxParams pl, OrbxParams pr, OrbxStereoParams sp)
+{
+    const int f = blockIdx.y, lane = threadIdx.x & 31;
+    const int iL = blockIdx.x * ST_WARPS + (threadIdx.x >> 5);
+    const int imgL = f * sp.imgStep + sp.imgOfsL, imgR = f * sp.imgStep + sp.imgOfsR;
+    const int nL = pl.outCnt[imgL], nR = pr.outCnt[imgR];
+    if (iL >= nL) return;
+    const size_t o = (size_t)f * sp.maxKp + iL;
+    // defaults (:524-525)
+    float outU = -1.f, outD = -1.f;
+    int outSad = -1;
+
+    const KpRec* kpsL = reinterpret_cast<const KpRec*>(pl.outKp) + (size_t)imgL * pl.maxKp;
+    const KpRec* kpsR = reinterpret_cast<const KpRec*>(pr.outKp) + (size_t)imgR * pr.maxKp;
+    const uint8_t* descL = pl.outDesc + (size_t)imgL * pl.maxKp * 32;
+    const uint8_t* descR = pr.outDesc + (size_t)imgR * pr.maxKp * 32;
+
+    const float uL = kpsL[iL].x, vL = kpsL[iL].y;
+    const int levelL = kpsL[iL].octave;
+    const int row = (int)vL;
+    const float maxD = orbx_fdiv(sp.mbf, sp.mb);  // :552-554 (mb == 0 -> +inf, as in the reference)
+    const float minU = orbx_fsub(uL, maxD), maxU = uL;
+
+    unsigned best = (100u << 16);  // TH_HIGH, iR 0
+    if (!(maxU < 0) && row >= 0 && row < sp.rows0) {
+        const uint4 a0 = *reinterpret_cast<const uint4*>(descL + (size_t)iL * 32);
+        const uint4 a1 = *reinterpret_cast<const uint4*>(descL + (size_t)iL * 32 + 16);
+        for (int iR = lane; iR < nR; iR += 32) {
+            const KpRec& kr = kpsR[iR];
+            const int octR = kr.octave;
+            if (octR < levelL - 1 || octR > levelL + 1) continue;
+            const float uR = kr.x;
+            if (!(uR >= minU && uR <= maxU)) continue;
+            const float y = kr.y;
+            const float r = orbx_fmul(2.0f, pl.lv[octR].scale);  // Frame copies the LEFT extractor's scale table
+            const int maxr = (int)ceilf(orbx_fadd(y, r)), minr = (int)floorf(orbx_fsub(y, r));
+            if (row < minr || row > maxr) continue;
+            const unsigned d = (unsigned)hamming256(a0, a1, descR + (size_t)iR * 32);
+            best = min(best, (d << 16) | (unsigned)iR);
+        }
+    }
+#pragma unroll
+    for (int s = 16; s; s >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, s));
+    const int bestDist = (int)(best >> 16), bestR = (int)(best & 0xFFFF);
+
+    if (bestDist < 75) {  // thOrbDist = (TH_HIGH + TH_LOW)/2, :527, :606
+        const float uR0 = kpsR[bestR].x;
+        const float s = pl.lv[levelL].invScale;
+        const float su = roundf(orbx_fmul(uL, s)), sv = roundf(orbx_fmul(vL, s)), sr = roundf(orbx_fmul(uR0, s));
+        const int cu = (int)su, cv = (int)sv, cr = (int)sr;
+        const int wl = pl.lv[levelL].w, hl = pl.lv[levelL].h, wr = pr.lv[levelL].w, hr = pr.lv[levelL].h;
+        const bool ok = !(sr < 0.f || orbx_fadd(sr, 11.f) >= (float)wr) &&  // :632-635
+                        !(cv - 5 < 0 || cv + 5 >= hl || cu - 5 < 0 || cu + 5 >= wl || cv + 5 >= hr || cr - 10 < 0 ||
+                          cr + 10 >= wr);  // windows outside the level: the reference's rowRange/colRange would throw
+        if (ok) {
+            int pitchL, pitchR;
+            const uint8_t* IL = orbx_level_ptr(pl, imgL, levelL, &pitchL);
+            const uint8_t* IR = orbx_level_ptr(pr, imgR, levelL, &pitchR);
+            const int cl = IL[(size_t)cv * pitchL + cu];
+            int crv[11], sad[11];
+#pragma unroll
+            for (int k = 0; k < 11; ++k) {
+                crv[k] = IR[(size_t)cv * pitchR + cr + k - 5];
+                sad[k] = 0;
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int pidx = lane + 32 * q;
+                if (pidx < 121) {
+                    const int dy = pidx / 11 - 5, dx = pidx % 11 - 5;
+                    const int a = (int)IL[(size_t)(cv + dy) * pitchL + cu + dx] - cl;
+                    const uint8_t* rrow = IR + (size_t)(cv + dy) * pitchR + cr + dx - 5;
+#pragma unroll
+                    for (int k = 0; k < 11; ++k) sad[k] += abs(a - ((int)rrow[k] - crv[k]));
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 11; ++k)
+#pragma unroll
+                for (int sft = 16; sft; sft >>= 1) sad[k] += __shfl_xor_sync(0xffffffffu, sad[k], sft);
+            int bestSad = 0x7fffffff, bestInc = 0;
+#pragma unroll
+            for (int k = 0; k < 11; ++k)
+                if (sad[k] < bestSad) { bestSad = sad[k]; bestInc = k - 5; }
+            if (bestInc != -5 && bestInc != 5) {  // :654
+                float d1 = 0.f, d2 = 0.f, d3 = 0.f;
+#pragma unroll
+                for (int k = 1; k < 10; ++k)
+                    if (k - 5 == bestInc) { d1 = (float)sad[k - 1]; d2 = (float)sad[k]; d3 = (float)sad[k + 1]; }
+                const float denom = orbx_fmul(2.0f, orbx_fsub(orbx_fadd(d1, d3), orbx_fmul(2.0f, d2)));
+                const float deltaR = orbx_fdiv(orbx_fsub(d1, d3), denom);  // :662
+                if (!(deltaR < -1.f || deltaR > 1.f)) {
+                    float bestuR = orbx_fmul(pl.lv[levelL].scale, orbx_fadd(orbx_fadd(sr, (float)bestInc), deltaR));
+                    float disparity = orbx_fsub(uL, bestuR);
+                    if (disparity >= 0.f && disparity < maxD) {  // :672
+                        if (disparity <= 0.f) {
+                            disparity = 0.01f;
+                            bestuR = (float)((double)uL - 0.01);
+                        }
+                        outD = orbx_fdiv(sp.mbf, disparity);
+                        outU = bestuR;
+                        outSad = bestSad;
+                    }
+                }
+            }
+        }
+    }
+    if (lane == 0) {
+        sp.uRight[o] = outU;
+        sp.depth[o] = outD;
+        sp.sad[o] = outSad;
+    }
+}
+
+// Median cut (:686-699): one CTA per frame.
+__global__ void __launch_bounds__(256) orbx_stereo_median_kernel(OrbxParams pl, OrbxStereoParams sp)
+{
+    __shared__ int hist[256];
+    __shared__ int sh_n, sh_bin, sh_rank, sh_valid;
+    const int f = blockIdx.x, tid = threadIdx.x;
+    const int nL = pl.outCnt[f * sp.imgStep + sp.imgOfsL];
+    const int* sad = sp.sad + (size_t)f * sp.maxKp;
+    hist[tid] = 0;
+    if (tid == 0) { sh_n = 0; sh_valid = 0; }
+    __syncthreads();
+    int cnt = 0;
+    for (int i = tid; i < nL; i += 256) {
+        const int v = sad[i];
+        if (v >= 0) { atomicAdd(&hist[v >> 8], 1); ++cnt; }
+    }
+    if (cnt) atomicAdd(&sh_n, cnt);
+    __syncthreads();
+    const int n = sh_n;
+    if (n == 0) {  // reference: undefined behaviour on an empty vector; defined as "nothing to cut"
+        if (tid == 0) sp.nMatched[f] = 0;
+        return;
+    }
+    if (tid == 0) {
+        int k = n / 2, b = 0;
+        while (k >= hist[b]) { k -= hist[b]; ++b; }
+        sh_bin = b;
+        sh_rank = k;
+    }
+    __syncthreads();
+    const int hb = sh_bin;
+    __syncthreads();
+    hist[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < nL; i += 256) {
+        const int v = sad[i];
+        if (v >= 0 && (v >> 8) == hb) atomicAdd(&hist[v & 255], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int k = sh_rank, b = 0;
+        while (k >= hist[b]) { k -= hist[b]; ++b; }
+        sh_bin = (hb << 8) | b;
+    }
+    __syncthreads();
+    const float median = (float)sh_bin;
+    const float th = orbx_fmul(orbx_fmul(1.5f, 1.4f), median);
+    int valid = 0;
+    for (int i = tid; i < nL; i += 256) {
+        const int v = sad[i];
+        if (v >= 0) {
+            if ((float)v >= th) {
+                sp.uRight[(size_t)f * sp.maxKp + i] = -1.f;
+                sp.depth[(size_t)f * sp.maxKp + i] = -1.f;
+            } else {
+                ++valid;
+            }
+        }
+    }
+    if (valid) atomicAdd(&sh_valid, valid);
+    __syncthreads();
+    if (tid == 0) sp.nMatched[f] = sh_valid;
+}
+
+void orbx_launch_stereo(const OrbxParams& pl, const OrbxParams& pr, const OrbxStereoParams& sp, cudaStream_t s)
+{
+    dim3 grid((sp.maxKp + ST_WARPS - 1) / ST_WARPS, sp.frames);
+    orbx_stereo_match_kernel<<<grid, ST_WARPS * 32, 0, s>>>(pl, pr, sp);
+    orbx_stereo_median_kernel<<<sp.frames, 256, 0, s>>>(pl, sp);
+}
