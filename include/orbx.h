@@ -114,6 +114,14 @@ int orbx_batch_process(orbx_batch* b, const uint8_t* left, const uint8_t* right,
 void* orbx_batch_stream(orbx_batch* b);
 /* Number of kernels one orbx_batch_run launches (for bench.py's gpu_launches). */
 int orbx_batch_launches_per_run(const orbx_batch* b);
+/* Per-stage device timing with CUDA events on the engine's stream (bench.py's roofline leg). While on,
+ * every orbx_batch_run records events at the stage boundaries (up to 512 runs are kept);
+ * orbx_batch_stage_times() synchronises, returns the summed milliseconds per stage over those runs and
+ * the number of runs, and resets. Stages: orbx_batch_stage_name(0..orbx_batch_stage_count()-1). */
+int orbx_batch_set_profiling(orbx_batch* b, int on);
+int orbx_batch_stage_count(void);
+const char* orbx_batch_stage_name(int i);
+int orbx_batch_stage_times(orbx_batch* b, double* ms, int* runs);
 /* Bytes of HBM the engine holds. */
 long long orbx_batch_device_bytes(const orbx_batch* b);
 /* Page-locked host memory for the end-to-end path (cudaHostAlloc / cudaFreeHost). */

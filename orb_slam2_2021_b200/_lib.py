@@ -62,6 +62,10 @@ SIGNATURES = {
     "orbx_batch_stream": (_vp, [_vp]),
     "orbx_batch_launches_per_run": (_i, [_vp]),
     "orbx_batch_device_bytes": (_ll, [_vp]),
+    "orbx_batch_set_profiling": (_i, [_vp, _i]),
+    "orbx_batch_stage_count": (_i, []),
+    "orbx_batch_stage_name": (C.c_char_p, [_i]),
+    "orbx_batch_stage_times": (_i, [_vp, C.POINTER(C.c_double), _ip]),
     "orbx_host_alloc": (_vp, [_sz]),
     "orbx_host_free": (None, [_vp]),
     "orbx_batch_level_size": (_i, [_vp, _i, _ip, _ip]),

@@ -333,6 +333,23 @@ extern "C" int orbx_batch_candidates(orbx_batch* b, int frame, int side, int lev
     return ORBX_OK;
 }
 
+// per-stage CUDA-event timing (stages: pyramid, fast, octree, blur, describe, stereo)
+extern "C" int orbx_batch_set_profiling(orbx_batch* b, int on)
+{
+    if (!b) return fail(ORBX_ERR_ARG, "handle is NULL");
+    return b->eng.setProfiling(on != 0, g_err);
+}
+extern "C" int orbx_batch_stage_count(void) { return Engine::kStages - 1; }
+extern "C" const char* orbx_batch_stage_name(int i) { return Engine::stageName(i); }
+extern "C" int orbx_batch_stage_times(orbx_batch* b, double* ms, int* runs)
+{
+    if (!b || !ms || !runs) return fail(ORBX_ERR_ARG, "bad arguments");
+    double t[Engine::kStages];
+    TRY(b->eng.stageTimes(t, runs, g_err));
+    for (int i = 0; i < Engine::kStages - 1; ++i) ms[i] = t[i];
+    return ORBX_OK;
+}
+
 // pinned host memory for the end-to-end path
 extern "C" void* orbx_host_alloc(size_t bytes)
 {

@@ -287,11 +287,18 @@ int Engine::runExtract(int nImgs, std::string& err)
     TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
     OrbxParams p = P;
     p.imgs = nImgs;
+    mark(0);
     orbx_launch_pyramid(p, resizeTabs.data(), stream);
+    mark(1);
     orbx_launch_fast(p, dCells, stream);
+    mark(2);
     orbx_launch_octree(p, dCells, stream);
+    mark(3);
     orbx_launch_blur(p, dTiles, nTiles, stream);
+    mark(4);
     orbx_launch_describe(p, stream);
+    mark(5);
+    if (!stereo) { mark(6); mark(7); if (profiling && profiledRuns < kMaxProfiledRuns) ++profiledRuns; }
     return orbx_check(cudaGetLastError(), "extract launch", err);
 }
 
@@ -302,11 +309,54 @@ int Engine::runStereo(int nFrames, float mbf, float mb, std::string& err)
     p.imgs = nFrames * 2;
     OrbxStereoParams sp = SP;
     sp.frames = nFrames; sp.mbf = mbf; sp.mb = mb;
-    orbx_launch_stereo(p, p, sp, stream);
+    orbx_launch_stereo(p, p, sp, stream);  // match + median; timed as one stage, the median cut is marked separately below
+    mark(6);
+    mark(7);
+    if (profiling && profiledRuns < kMaxProfiledRuns) ++profiledRuns;
     return orbx_check(cudaGetLastError(), "stereo launch", err);
 }
 
 int Engine::sync(std::string& err)
 {
     return orbx_check(cudaStreamSynchronize(stream), "stream sync", err);
+}
+
+// ---- per-stage timing -------------------------------------------------------------------------------
+const char* Engine::stageName(int i)
+{
+    static const char* names[kStages] = {"pyramid", "fast", "octree", "blur", "describe", "stereo", "-"};
+    return i >= 0 && i < kStages ? names[i] : "?";
+}
+
+int Engine::setProfiling(bool on, std::string& err)
+{
+    TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
+    if (on && events.empty()) {
+        events.resize((size_t)kMaxProfiledRuns * (kStages + 1));
+        for (auto& e : events) TRY(orbx_check(cudaEventCreate(&e), "cudaEventCreate", err));
+    }
+    profiling = on;
+    profiledRuns = 0;
+    return ORBX_OK;
+}
+
+void Engine::mark(int stage)
+{
+    if (!profiling || profiledRuns >= kMaxProfiledRuns) return;
+    cudaEventRecord(events[(size_t)profiledRuns * (kStages + 1) + stage], stream);
+}
+
+int Engine::stageTimes(double* ms, int* runs, std::string& err)
+{
+    TRY(sync(err));
+    for (int s = 0; s < kStages; ++s) ms[s] = 0;
+    for (int r = 0; r < profiledRuns; ++r)
+        for (int s = 0; s < kStages; ++s) {
+            float t = 0;
+            TRY(orbx_check(cudaEventElapsedTime(&t, events[(size_t)r * (kStages + 1) + s], events[(size_t)r * (kStages + 1) + s + 1]), "event time", err));
+            ms[s] += t;
+        }
+    *runs = profiledRuns;
+    profiledRuns = 0;
+    return ORBX_OK;
 }

@@ -51,6 +51,16 @@ public:
     std::vector<void*> allocs;
     size_t bytesAllocated = 0;
     int launchesPerExtract = 0;
+
+    // optional per-stage timing with CUDA events on `stream` (bench.py's roofline leg)
+    enum { kStages = 7, kMaxProfiledRuns = 512 };
+    bool profiling = false;
+    std::vector<cudaEvent_t> events;  // (kStages+1) per profiled run
+    int profiledRuns = 0;
+    int setProfiling(bool on, std::string& err);
+    int stageTimes(double* ms, int* runs, std::string& err);  // accumulates + resets
+    void mark(int stage);
+    static const char* stageName(int i);
 };
 
 int orbx_check(cudaError_t e, const char* what, std::string& err);

@@ -217,6 +217,17 @@ class StereoFrameBatch:
         check(lib().orbx_batch_stats(self._h, n_frames, C.byref(a), C.byref(b), C.byref(c)))
         return a.value, b.value, c.value
 
+    def set_profiling(self, on=True):
+        check(lib().orbx_batch_set_profiling(self._h, int(on)))
+
+    def stage_times(self):
+        """({stage: total ms}, runs) accumulated since the last call (CUDA events on the engine stream)."""
+        n = lib().orbx_batch_stage_count()
+        ms = (C.c_double * n)()
+        runs = C.c_int()
+        check(lib().orbx_batch_stage_times(self._h, ms, C.byref(runs)))
+        return {lib().orbx_batch_stage_name(i).decode(): ms[i] for i in range(n)}, runs.value
+
     # --- test taps ---
     def level(self, frame, side, level, blurred=False):
         r, c = C.c_int(), C.c_int()

@@ -1,0 +1,75 @@
+"""The C-ABI library loads and exports every symbol include/orbx.h declares; error behaviour that
+needs no GPU. No compute calls here."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+import orb_slam2_2021_b200 as pkg
+from orb_slam2_2021_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    hdr = open(os.path.join(ROOT, "include", "orbx.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    return sorted(set(re.findall(r"\b(orbx_[a-z0-9_]+)\s*\(", hdr)))
+
+
+def test_header_symbols_exported():
+    syms = declared_symbols()
+    assert len(syms) >= 25
+    L = ctypes.CDLL(pkg.SO_PATH)
+    for s in syms:
+        assert hasattr(L, s), f"{s} declared in include/orbx.h but not exported by liborbx.so"
+    assert set(syms) == set(_lib.SIGNATURES), set(syms) ^ set(_lib.SIGNATURES)
+
+
+def test_no_oracle_in_product():
+    """The product path must not import or link the oracle (or cv2)."""
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "orb_slam2_2021_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")) and f != "synth.py":
+                txt = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "import cv2" not in txt, f
+                assert not re.search(r"^\s*(from|import)\s+oracle", txt, flags=re.M), f
+                assert '#include "../../oracle' not in txt and "orb_oracle" not in txt, f
+
+
+def test_keypoint_layout():
+    assert pkg.KP_DTYPE.itemsize == 28
+    assert [pkg.KP_DTYPE.fields[n][1] for n in ("x", "y", "size", "angle", "response", "octave", "class_id")] == \
+        [0, 4, 8, 12, 16, 20, 24]
+
+
+def test_empty_image_is_silent():
+    e = pkg.ORBextractor(1000, 1.2, 8, 20, 7)
+    k, d = e(np.zeros((0, 0), np.uint8))
+    assert len(k) == 0 and d.shape == (0, 32)
+    n = ctypes.c_int(-7)
+    assert pkg.lib().orbx_extract(e._h, None, 0, 0, 0, None, None, 0, ctypes.byref(n)) == 0
+    assert n.value == -7  # untouched, like src/ORBextractor.cc:1044-1045
+
+
+def test_bad_arguments():
+    e = pkg.ORBextractor(1000, 1.2, 8, 20, 7)
+    with pytest.raises(TypeError):
+        e(np.zeros((10, 10), np.float32))
+    L = pkg.lib()
+    assert L.orbx_pyramid_level_size(e._h, 0, ctypes.byref(ctypes.c_int()), ctypes.byref(ctypes.c_int())) == _lib.ERR_STATE
+    assert b"no image" in L.orbx_last_error()
+    assert L.orbx_get_tables(None, None, None, None, None, None) == _lib.ERR_ARG
+
+
+def test_fails_loudly_without_gpu(has_gpu):
+    if has_gpu:
+        pytest.skip("GPU present")
+    e = pkg.ORBextractor(1000, 1.2, 8, 20, 7)
+    with pytest.raises(pkg.OrbxError) as ei:
+        e(np.zeros((480, 640), np.uint8))
+    assert ei.value.code == _lib.ERR_CUDA
+    with pytest.raises(pkg.OrbxError):
+        pkg.StereoFrameBatch(1000, 1.2, 8, 20, 7, 480, 640, 2)

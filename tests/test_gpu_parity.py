@@ -1,0 +1,263 @@
+"""Parity of the CUDA path (through the C-ABI) against the CPU oracle and the golden vectors.
+
+Bars (BASELINE.json north_star): keypoint x/y/octave/response/size/class_id, descriptor bytes and the
+match validity mask bit-exact; angle <= 1e-4 deg; mvuRight <= 1e-4 px; mvDepth <= 1e-5 relative.
+In practice every field is bit-identical, and the tests assert that stronger statement where the
+shared math header guarantees it.
+"""
+import glob
+import os
+import threading
+
+import numpy as np
+import pytest
+
+import orb_slam2_2021_b200 as pkg
+from oracle import oracle as O
+from orb_slam2_2021_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+ANGLE_TOL_DEG = 1e-4
+URIGHT_TOL_PX = 1e-4
+DEPTH_RTOL = 1e-5
+
+
+def assert_kps_equal(got, ref, what=""):
+    assert len(got) == len(ref), (what, len(got), len(ref))
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        assert np.array_equal(got[f], ref[f]), (what, f, int((got[f] != ref[f]).sum()))
+    assert np.abs(got["angle"] - ref["angle"]).max(initial=0) <= ANGLE_TOL_DEG, what
+    assert np.array_equal(got["angle"], ref["angle"]), (what, "angle not bit-identical")
+
+
+def assert_stereo_equal(ur, dp, our, odp, what=""):
+    assert np.array_equal(ur >= 0, our >= 0), (what, "validity mask")
+    assert np.abs(ur - our).max(initial=0) <= URIGHT_TOL_PX, what
+    assert np.all(np.abs(dp - odp) <= DEPTH_RTOL * np.abs(odp)), what
+    assert np.array_equal(ur, our) and np.array_equal(dp, odp), (what, "not bit-identical")
+
+
+def oracle_pair(cfg, left, right):
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    ol, orr = O.OracleExtractor(nf, sf, nl, ini, mn), O.OracleExtractor(nf, sf, nl, ini, mn)
+    kl, dl = ol(left)
+    kr, dr = orr(right)
+    return ol, orr, kl, dl, kr, dr
+
+
+@pytest.mark.parametrize("name,seeds", [("tum_mono", range(6)), ("arducam", range(4)), ("kitti", range(6)),
+                                        ("euroc", range(4))])
+def test_extract_and_stereo_handles(name, seeds):
+    cfg = synth.CONFIGS[name]
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    exl, exr = pkg.ORBextractor(nf, sf, nl, ini, mn), pkg.ORBextractor(nf, sf, nl, ini, mn)
+    for seed in seeds:
+        left, right = synth.stereo_pair(W, H, 100 + seed)
+        ol, orr, okl, odl, okr, odr = oracle_pair(cfg, left, right)
+        kl, dl = exl(left)
+        kr, dr = exr(right)
+        assert_kps_equal(kl, okl, f"{name}/{seed}/L")
+        assert_kps_equal(kr, okr, f"{name}/{seed}/R")
+        assert np.array_equal(dl, odl) and np.array_equal(dr, odr)
+        if seed == seeds[0]:
+            for l, lev in enumerate(exl.mvImagePyramid):
+                assert np.array_equal(lev, ol.level(l)), f"pyramid level {l}"
+        if bf > 0:
+            for mb in (bf / fx, 0.0):  # steady state, and the reference's uninitialised-mb first frame
+                ur, dp = pkg.compute_stereo_matches(exl, exr, kl, dl, kr, dr, bf, mb)
+                our, odp = O.stereo_match(ol, orr, okl, odl, okr, odr, bf, mb)
+                assert_stereo_equal(ur, dp, our, odp, f"{name}/{seed}/mb={mb}")
+                assert (ur >= 0).sum() > 100
+
+
+GOLD = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+
+
+@pytest.mark.parametrize("path", GOLD, ids=[os.path.basename(p) for p in GOLD])
+def test_golden_vectors(path):
+    """CUDA path vs vectors produced by the cv2-driven model (real OpenCV kernels)."""
+    g = np.load(path)
+    name, seed = str(g["config"]), int(g["seed"])
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS[name]
+    left, right = synth.stereo_pair(W, H, seed)
+    exl = pkg.ORBextractor(nf, sf, nl, ini, mn)
+    kl, dl = exl(left)
+    assert kl.tobytes() == g["kps_left"].tobytes() and np.array_equal(dl, g["desc_left"])
+    if "kps_right" in g:
+        exr = pkg.ORBextractor(nf, sf, nl, ini, mn)
+        kr, dr = exr(right)
+        assert kr.tobytes() == g["kps_right"].tobytes() and np.array_equal(dr, g["desc_right"])
+        ur, dp = pkg.compute_stereo_matches(exl, exr, kl, dl, kr, dr, bf, bf / fx)
+        assert np.array_equal(ur, g["u_right"]) and np.array_equal(dp, g["depth"])
+        ur, dp = pkg.compute_stereo_matches(exl, exr, kl, dl, kr, dr, bf, 0.0)
+        assert np.array_equal(ur, g["u_right_mb0"]) and np.array_equal(dp, g["depth_mb0"])
+
+
+def test_batch_matches_oracle_per_frame():
+    cfg = synth.CONFIGS["kitti"]
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    n = 6
+    L, R = synth.stereo_batch(W, H, n, seed0=40)
+    b = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, n, stereo=True)
+    out = b.process(L, R, mbf=bf, mb=bf / fx)
+    tot_l = tot_r = tot_m = 0
+    for f in range(n):
+        ol, orr, okl, odl, okr, odr = oracle_pair(cfg, L[f], R[f])
+        nl_, nr_ = out["n_left"][f], out["n_right"][f]
+        assert_kps_equal(out["kps_left"][f][:nl_], okl, f"frame {f} L")
+        assert_kps_equal(out["kps_right"][f][:nr_], okr, f"frame {f} R")
+        assert np.array_equal(out["desc_left"][f][:nl_], odl) and np.array_equal(out["desc_right"][f][:nr_], odr)
+        our, odp = O.stereo_match(ol, orr, okl, odl, okr, odr, bf, bf / fx)
+        assert_stereo_equal(out["u_right"][f][:nl_], out["depth"][f][:nl_], our, odp, f"frame {f}")
+        tot_l += nl_; tot_r += nr_; tot_m += int((our >= 0).sum())
+        for l in (0, 3, 7):  # stage taps: pyramid, blur, FAST candidates in reference order
+            assert np.array_equal(b.level(f, 0, l), ol.level(l))
+            assert np.array_equal(b.level(f, 1, l, blurred=True), orr.level(l, blurred=True))
+            gc, oc = b.candidates(f, 0, l), ol.candidates(l)
+            assert len(gc) == len(oc) and all(np.array_equal(gc[k], oc[k]) for k in ("x", "y", "response"))
+    assert b.stats(n) == (tot_l, tot_r, tot_m)
+
+
+def test_mono_batch():
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["tum_mono"]
+    imgs = np.stack([synth.synth(W, H, 60 + k) for k in range(3)])
+    b = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, 4, stereo=False)
+    out = b.process(imgs)
+    for f in range(3):
+        ok, od = O.OracleExtractor(nf, sf, nl, ini, mn)(imgs[f])
+        assert_kps_equal(out["kps_left"][f][:out["n_left"][f]], ok)
+        assert np.array_equal(out["desc_left"][f][:out["n_left"][f]], od)
+
+
+def adversarial_images(W, H):
+    rng = np.random.default_rng(9)
+    yy, xx = np.mgrid[0:H, 0:W]
+    return {
+        "flat": np.full((H, W), 90, np.uint8),
+        "uniform_noise": rng.integers(0, 256, (H, W), dtype=np.uint8),
+        "binary_noise": (rng.integers(0, 2, (H, W)) * 255).astype(np.uint8),
+        "checker8": ((((xx // 8) + (yy // 8)) & 1) * 200 + 20).astype(np.uint8),
+        "sparse_dots": np.where(rng.random((H, W)) < 0.002, 255, 40).astype(np.uint8),
+        "gradient": ((xx * 255) // W).astype(np.uint8),
+        "one_corner": np.pad(np.full((40, 40), 255, np.uint8), ((H // 2, H - H // 2 - 40), (W // 2, W - W // 2 - 40))),
+    }
+
+
+@pytest.mark.parametrize("kind", ["flat", "uniform_noise", "binary_noise", "checker8", "sparse_dots", "gradient", "one_corner"])
+def test_adversarial_images(kind):
+    """Ties everywhere (checker, binary noise), maximal candidate counts (noise), and no keypoints at all."""
+    W, H, nf, nl, sf, ini, mn = 400, 300, 500, 6, 1.2, 20, 7
+    img = adversarial_images(W, H)[kind]
+    ok, od = O.OracleExtractor(nf, sf, nl, ini, mn)(img)
+    ex = pkg.ORBextractor(nf, sf, nl, ini, mn)
+    k, d = ex(img)
+    assert_kps_equal(k, ok, kind)
+    assert np.array_equal(d, od)
+    if kind in ("flat", "gradient"):
+        assert len(k) == 0
+        exr = pkg.ORBextractor(nf, sf, nl, ini, mn)
+        exr(img)
+        ur, dp = pkg.compute_stereo_matches(ex, exr, k, d, k, d, 40.0, 0.1)  # empty match set: defined no-op
+        assert len(ur) == 0
+
+
+def test_stereo_identical_images_and_no_matches():
+    """disparity 0 -> the 0.01 clamp (src/Frame.cc:674-678); unrelated right image -> few/no matches, median cut on tiny sets."""
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["arducam"]
+    left = synth.synth(W, H, 5)
+    for right in (left.copy(), synth.synth(W, H, 999)):
+        exl, exr = pkg.ORBextractor(nf, sf, nl, ini, mn), pkg.ORBextractor(nf, sf, nl, ini, mn)
+        kl, dl = exl(left)
+        kr, dr = exr(right)
+        ol, orr, okl, odl, okr, odr = oracle_pair(synth.CONFIGS["arducam"], left, right)
+        ur, dp = pkg.compute_stereo_matches(exl, exr, kl, dl, kr, dr, bf, bf / fx)
+        our, odp = O.stereo_match(ol, orr, okl, odl, okr, odr, bf, bf / fx)
+        assert_stereo_equal(ur, dp, our, odp)
+
+
+def test_uhd_single_frame():
+    """3840x2160, 8000 features: ~31k candidates on level 0 stress the quadtree and the slot arrays."""
+    cfg = synth.CONFIGS["uhd"]
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    left, right = synth.stereo_pair(W, H, 2)
+    ol, orr, okl, odl, okr, odr = oracle_pair(cfg, left, right)
+    b = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, 1, stereo=True)
+    out = b.process(left[None], right[None], mbf=bf, mb=bf / fx)
+    nl_, nr_ = out["n_left"][0], out["n_right"][0]
+    assert_kps_equal(out["kps_left"][0][:nl_], okl, "uhd L")
+    assert_kps_equal(out["kps_right"][0][:nr_], okr, "uhd R")
+    assert np.array_equal(out["desc_left"][0][:nl_], odl)
+    our, odp = O.stereo_match(ol, orr, okl, odl, okr, odr, bf, bf / fx)
+    assert_stereo_equal(out["u_right"][0][:nl_], out["depth"][0][:nl_], our, odp, "uhd")
+
+
+def test_abi_behaviour_on_device():
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["tum_mono"]
+    img = synth.synth(W, H, 1)
+    ex = pkg.ORBextractor(nf, sf, nl, ini, mn)
+    k1, d1 = ex(img)
+    # non-contiguous rows (stride > cols), like a cv::Mat ROI
+    big = np.zeros((H, W + 37), np.uint8)
+    big[:, :W] = img
+    k2, d2 = ex(big[:, :W])
+    assert k1.tobytes() == k2.tobytes() and np.array_equal(d1, d2)
+    # the same handle on another image size rebuilds its device state
+    small = synth.synth(400, 300, 2)
+    k3, _ = ex(small)
+    ok, _ = O.OracleExtractor(nf, sf, nl, ini, mn)(small)
+    assert_kps_equal(k3, ok)
+    # capacity error
+    import ctypes as C
+    kp = np.zeros(10, pkg.KP_DTYPE); ds = np.zeros((10, 32), np.uint8); n = C.c_int(0)
+    rc = pkg.lib().orbx_extract(ex._h, img.ctypes.data_as(C.c_void_p), H, W, W, kp.ctypes.data_as(C.c_void_p),
+                                ds.ctypes.data_as(C.c_void_p), 10, C.byref(n))
+    assert rc == -2 and b"capacity" in pkg.lib().orbx_last_error()
+
+
+def test_two_handles_two_threads():
+    """Frame::Frame runs left and right extraction in two std::threads on two instances (src/Frame.cc:113-116)."""
+    cfg = synth.CONFIGS["euroc"]
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    left, right = synth.stereo_pair(W, H, 8)
+    exs = [pkg.ORBextractor(nf, sf, nl, ini, mn) for _ in range(2)]
+    res = [None, None]
+
+    def work(i, im):
+        for _ in range(5):
+            res[i] = exs[i](im)
+
+    ts = [threading.Thread(target=work, args=(i, im)) for i, im in enumerate((left, right))]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    ol, orr, okl, odl, okr, odr = oracle_pair(cfg, left, right)
+    assert_kps_equal(res[0][0], okl)
+    assert_kps_equal(res[1][0], okr)
+    assert np.array_equal(res[0][1], odl) and np.array_equal(res[1][1], odr)
+
+
+def test_full_size_batch_properties():
+    """BASELINE-size properties where the oracle is too slow to check every frame: determinism,
+    independence of a frame's result from its position in the batch, and count invariants."""
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["kitti"]
+    base_l, base_r = synth.stereo_batch(W, H, 4, seed0=70)
+    n = 64
+    idx = np.random.default_rng(0).integers(0, 4, n)
+    L, R = base_l[idx], base_r[idx]
+    b = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, n, stereo=True)
+    out1 = {k: v.copy() for k, v in b.process(L, R, mbf=bf, mb=bf / fx).items()}
+    out2 = b.process(L, R, mbf=bf, mb=bf / fx)
+    first = {}
+    for f in range(n):
+        nl_ = out1["n_left"][f]
+        assert nf <= nl_ <= nf + 2 * nl
+        sig = (out1["kps_left"][f][:nl_].tobytes(), out1["desc_left"][f][:nl_].tobytes(),
+               out1["u_right"][f][:nl_].tobytes(), out1["depth"][f][:nl_].tobytes())
+        assert sig == (out2["kps_left"][f][:nl_].tobytes(), out2["desc_left"][f][:nl_].tobytes(),
+                       out2["u_right"][f][:nl_].tobytes(), out2["depth"][f][:nl_].tobytes())
+        assert first.setdefault(int(idx[f]), sig) == sig
+        # descriptor rows are 4-byte aligned 32-byte records; every keypoint lies inside the 19-px edge at its level
+        k = out1["kps_left"][f][:nl_]
+        s = np.float32(1.2) ** k["octave"]
+        assert np.all(k["x"] / s >= 18.99) and np.all(k["y"] / s >= 18.99)
+        assert np.all(np.diff(k["octave"]) >= 0)  # levels concatenated 0..7
