@@ -18,6 +18,8 @@ struct orbx_extractor {
     bool hasRun = false;
     // stereo scratch (used when this handle is the LEFT one)
     float* dU = nullptr; float* dD = nullptr; int* dSad = nullptr; int* dNm = nullptr;
+    uint4* dSorted = nullptr; int* dBin = nullptr;
+    int scratchRows = 0;
     int scratchKp = 0;
 };
 
@@ -59,7 +61,7 @@ extern "C" int orbx_create(int nfeatures, float sf, int nlevels, int ini, int mn
 extern "C" void orbx_destroy(orbx_extractor* e)
 {
     if (!e) return;
-    if (e->dU) { cudaSetDevice(e->device); cudaFree(e->dU); cudaFree(e->dD); cudaFree(e->dSad); cudaFree(e->dNm); }
+    if (e->dU) { cudaSetDevice(e->device); cudaFree(e->dU); cudaFree(e->dD); cudaFree(e->dSad); cudaFree(e->dNm); cudaFree(e->dSorted); cudaFree(e->dBin); }
     delete e;
 }
 
@@ -160,14 +162,17 @@ extern "C" int orbx_stereo_match(orbx_extractor* l, orbx_extractor* r, const orb
     for (int i = 0; i < nL; ++i) uRight[i] = depth[i] = -1.f;  // src/Frame.cc:524-525
     if (nL == 0) return ORBX_OK;
     TRY(orbx_check(cudaSetDevice(l->device), "cudaSetDevice", g_err));
-    if (l->scratchKp < EL.P.maxKp) {
-        if (l->dU) { cudaFree(l->dU); cudaFree(l->dD); cudaFree(l->dSad); cudaFree(l->dNm); l->dU = nullptr; }
+    if (l->scratchKp < EL.P.maxKp || l->scratchRows < EL.rows) {
+        if (l->dU) { cudaFree(l->dU); cudaFree(l->dD); cudaFree(l->dSad); cudaFree(l->dNm); cudaFree(l->dSorted); cudaFree(l->dBin); l->dU = nullptr; }
         const size_t k = EL.P.maxKp;
         TRY(orbx_check(cudaMalloc(&l->dU, k * 4), "stereo scratch", g_err));
         TRY(orbx_check(cudaMalloc(&l->dD, k * 4), "stereo scratch", g_err));
         TRY(orbx_check(cudaMalloc(&l->dSad, k * 4), "stereo scratch", g_err));
         TRY(orbx_check(cudaMalloc(&l->dNm, 4), "stereo scratch", g_err));
+        TRY(orbx_check(cudaMalloc(&l->dSorted, k * sizeof(uint4)), "stereo scratch", g_err));
+        TRY(orbx_check(cudaMalloc(&l->dBin, ((size_t)EL.rows + 1) * 4), "stereo scratch", g_err));
         l->scratchKp = EL.P.maxKp;
+        l->scratchRows = EL.rows;
     }
     cudaStream_t s = EL.stream;
     // the caller's keypoints/descriptors are authoritative (Frame::mvKeys etc.): put them on the device
@@ -185,6 +190,7 @@ extern "C" int orbx_stereo_match(orbx_extractor* l, orbx_extractor* r, const orb
     sp.frames = 1; sp.nlevels = pl.nlevels; sp.rows0 = EL.rows; sp.maxKp = pl.maxKp; sp.mbf = mbf; sp.mb = mb;
     sp.imgStep = 1; sp.imgOfsL = 0; sp.imgOfsR = 0;
     sp.uRight = l->dU; sp.depth = l->dD; sp.sad = l->dSad; sp.nMatched = l->dNm;
+    sp.rsorted = l->dSorted; sp.binStart = l->dBin; sp.binR = orbx_stereo_bin_radius(l->cfg.scale.data(), l->cfg.nlevels);
     orbx_launch_stereo(pl, pr, sp, s);
     TRY(orbx_check(cudaGetLastError(), "stereo launch", g_err));
     TRY(orbx_check(cudaMemcpyAsync(uRight, l->dU, (size_t)nL * 4, cudaMemcpyDeviceToHost, s), "D2H uRight", g_err));
@@ -215,7 +221,7 @@ extern "C" int orbx_batch_max_keypoints(const orbx_batch* b) { return b ? b->eng
 extern "C" void* orbx_batch_stream(orbx_batch* b) { return b ? (void*)b->eng.stream : nullptr; }
 extern "C" int orbx_batch_launches_per_run(const orbx_batch* b)
 {
-    return b ? b->eng.launchesPerExtract + (b->stereo ? 2 : 0) : ORBX_ERR_ARG;
+    return b ? b->eng.launchesPerExtract + (b->stereo ? 3 : 0) : ORBX_ERR_ARG;
 }
 extern "C" long long orbx_batch_device_bytes(const orbx_batch* b) { return b ? (long long)b->eng.bytesAllocated : 0; }
 

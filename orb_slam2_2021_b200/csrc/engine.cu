@@ -42,6 +42,15 @@ void ExtractorConfig::init(int nf, float sf, int nl, int ini, int mn)
     quota[nl - 1] = nf - sum > 0 ? nf - sum : 0;
 }
 
+// Rows a right keypoint can serve: floor(y-r)..ceil(y+r), r = 2*scale[octave] (src/Frame.cc:539-549); a left
+// keypoint on row v therefore only needs right keypoints with |(int)y - v| <= ceil(2*max scale) + 1.
+int orbx_stereo_bin_radius(const float* scale, int nlevels)
+{
+    float m = 1.f;
+    for (int i = 0; i < nlevels; ++i) m = scale[i] > m ? scale[i] : m;
+    return (int)std::ceil(2.0f * m) + 1;
+}
+
 static inline unsigned align_up(unsigned v, unsigned a) { return (v + a - 1) / a * a; }
 
 struct HostCell {
@@ -256,6 +265,9 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
         TRY(dalloc(this, &SP.depth, fr * P.maxKp, "depth", err));
         TRY(dalloc(this, &SP.sad, fr * P.maxKp, "sad", err));
         TRY(dalloc(this, &SP.nMatched, fr, "nMatched", err));
+        TRY(dalloc(this, &SP.rsorted, fr * P.maxKp, "rsorted", err));
+        TRY(dalloc(this, &SP.binStart, fr * (rows + 1), "binStart", err));
+        SP.binR = orbx_stereo_bin_radius(cfg.scale.data(), cfg.nlevels);
     }
     launchesPerExtract = (P.nlevels - 1) + 1 + 1 + 1 + 2;
     return orbx_check(cudaStreamSynchronize(stream), "init sync", err);

@@ -64,3 +64,4 @@ public:
 };
 
 int orbx_check(cudaError_t e, const char* what, std::string& err);
+int orbx_stereo_bin_radius(const float* scale, int nlevels);

@@ -339,11 +339,8 @@ void orbx_launch_octree(const OrbxParams& p, const void* cellTable, cudaStream_t
     int cap = 0;
     for (int l = 0; l < p.nlevels; ++l) cap = p.lv[l].keepCap > cap ? p.lv[l].keepCap : cap;
     const size_t smem = octree_smem_bytes(cap);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
+    if (smem > 48 * 1024)  // per-device attribute: set on every launch that needs it
         cudaFuncSetAttribute(orbx_octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
     dim3 grid(p.nlevels, p.imgs);
     orbx_octree_kernel<<<grid, OCT_THREADS, smem, s>>>(p, (const OrbxCellRec*)cellTable);
 }

@@ -89,6 +89,11 @@ struct OrbxStereoParams {
     float* depth;
     int* sad;       // [frames][maxKp] best SAD of accepted matches, -1 otherwise
     int* nMatched;  // [frames]
+    // right keypoints of each frame counting-sorted by (int)y (the row-band table of src/Frame.cc:532-549 in
+    // data-parallel form): rsorted[j] = {x bits, minr | maxr<<16, octave, iR}; bin b = binStart[b]..binStart[b+1]
+    uint4* rsorted;  // [frames][maxKp]
+    int* binStart;   // [frames][rows0 + 1]
+    int binR;        // a left keypoint on row v can only match right keypoints binned in [v-binR, v+binR]
 };
 
 // Launch wrappers (one per kernel group), defined in the .cu files.

@@ -29,12 +29,70 @@ __device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const 
            __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
+// Row-band table (:532-549) in data-parallel form, one CTA per frame: counting sort of the right
+// keypoints by (int)y. The exact band test floor(y-r) <= row <= ceil(y+r) is evaluated here once per
+// right keypoint and carried in the record, so the matcher only touches ~19 rows' worth of candidates.
+__global__ void __launch_bounds__(256) orbx_stereo_bin_kernel(OrbxParams pl, OrbxParams pr, OrbxStereoParams sp)
+{
+    extern __shared__ int hist[];  // rows0 + 1
+    __shared__ int wsum[9];
+    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int imgR = f * sp.imgStep + sp.imgOfsR;
+    const int nR = min(pr.outCnt[imgR], sp.maxKp);
+    const KpRec* kpsR = reinterpret_cast<const KpRec*>(pr.outKp) + (size_t)imgR * pr.maxKp;
+    const int rows = sp.rows0;
+    for (int i = tid; i <= rows; i += 256) hist[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < nR; i += 256) {
+        const int yb = min(max((int)floorf(kpsR[i].y), 0), rows - 1);
+        atomicAdd(&hist[yb], 1);
+    }
+    __syncthreads();
+    // exclusive scan of hist[0..rows), total in hist[rows]
+    const int chunk = (rows + 255) / 256;
+    const int b = min(tid * chunk, rows), e = min(b + chunk, rows);
+    int s = 0;
+    for (int i = b; i < e; ++i) s += hist[i];
+    int inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (tid == 0) {
+        int run = 0;
+        for (int w = 0; w < 8; ++w) { const int v = wsum[w]; wsum[w] = run; run += v; }
+        wsum[8] = run;
+    }
+    __syncthreads();
+    int run = wsum[warp] + inc - s;
+    for (int i = b; i < e; ++i) { const int v = hist[i]; hist[i] = run; run += v; }
+    if (tid == 0) hist[rows] = wsum[8];
+    __syncthreads();
+    int* bs = sp.binStart + (size_t)f * (rows + 1);
+    for (int i = tid; i <= rows; i += 256) bs[i] = hist[i];
+    __syncthreads();
+    uint4* rs = sp.rsorted + (size_t)f * sp.maxKp;
+    for (int i = tid; i < nR; i += 256) {
+        const KpRec kr = kpsR[i];
+        const int yb = min(max((int)floorf(kr.y), 0), rows - 1);
+        const int oc = min(max(kr.octave, 0), sp.nlevels - 1);
+        const float r = orbx_fmul(2.0f, pl.lv[oc].scale);  // Frame copies the LEFT extractor's scale table (:104-110, :541)
+        const int maxr = min(max((int)ceilf(orbx_fadd(kr.y, r)), -32768), 32767);
+        const int minr = min(max((int)floorf(orbx_fsub(kr.y, r)), -32768), 32767);
+        const int pos = atomicAdd(&hist[yb], 1);
+        rs[pos] = make_uint4(__float_as_uint(kr.x), ((unsigned)minr & 0xFFFFu) | ((unsigned)maxr << 16), (unsigned)kr.octave, (unsigned)i);
+    }
+}
+
 __global__ void __launch_bounds__(ST_WARPS * 32) orbx_stereo_match_kernel(OrbxParams pl, OrbxParams pr, OrbxStereoParams sp)
 {
     const int f = blockIdx.y, lane = threadIdx.x & 31;
     const int iL = blockIdx.x * ST_WARPS + (threadIdx.x >> 5);
     const int imgL = f * sp.imgStep + sp.imgOfsL, imgR = f * sp.imgStep + sp.imgOfsR;
-    const int nL = pl.outCnt[imgL], nR = pr.outCnt[imgR];
+    const int nL = pl.outCnt[imgL];
     if (iL >= nL) return;
     const size_t o = (size_t)f * sp.maxKp + iL;
     // defaults (:524-525)
@@ -56,18 +114,20 @@ __global__ void __launch_bounds__(ST_WARPS * 32) orbx_stereo_match_kernel(OrbxPa
     if (!(maxU < 0) && row >= 0 && row < sp.rows0) {
         const uint4 a0 = *reinterpret_cast<const uint4*>(descL + (size_t)iL * 32);
         const uint4 a1 = *reinterpret_cast<const uint4*>(descL + (size_t)iL * 32 + 16);
-        for (int iR = lane; iR < nR; iR += 32) {
-            const KpRec& kr = kpsR[iR];
-            const int octR = kr.octave;
-            if (octR < levelL - 1 || octR > levelL + 1) continue;
-            const float uR = kr.x;
-            if (!(uR >= minU && uR <= maxU)) continue;
-            const float y = kr.y;
-            const float r = orbx_fmul(2.0f, pl.lv[octR].scale);  // Frame copies the LEFT extractor's scale table
-            const int maxr = (int)ceilf(orbx_fadd(y, r)), minr = (int)floorf(orbx_fsub(y, r));
-            if (row < minr || row > maxr) continue;
-            const unsigned d = (unsigned)hamming256(a0, a1, descR + (size_t)iR * 32);
-            best = min(best, (d << 16) | (unsigned)iR);
+        const int rlo = max(row - sp.binR, 0), rhi = min(row + sp.binR + 1, sp.rows0);
+        const int* bs = sp.binStart + (size_t)f * (sp.rows0 + 1);
+        const uint4* rs = sp.rsorted + (size_t)f * sp.maxKp;
+        const int jEnd = bs[rhi];
+        for (int j = bs[rlo] + lane; j < jEnd; j += 32) {
+            const uint4 rec = rs[j];
+            const int octR = (int)rec.z;
+            if (octR < levelL - 1 || octR > levelL + 1) continue;  // :588
+            const float uR = __uint_as_float(rec.x);
+            if (!(uR >= minU && uR <= maxU)) continue;  // :593
+            const int minr = (int)(short)(rec.y & 0xFFFFu), maxr = (int)(short)(rec.y >> 16);
+            if (row < minr || row > maxr) continue;  // iR is listed in vRowIndices[row] (:539-549)
+            const unsigned d = (unsigned)hamming256(a0, a1, descR + (size_t)rec.w * 32);
+            best = min(best, (d << 16) | rec.w);
         }
     }
 #pragma unroll
@@ -209,6 +269,10 @@ __global__ void __launch_bounds__(256) orbx_stereo_median_kernel(OrbxParams pl, 
 
 void orbx_launch_stereo(const OrbxParams& pl, const OrbxParams& pr, const OrbxStereoParams& sp, cudaStream_t s)
 {
+    const size_t binSmem = (size_t)(sp.rows0 + 1) * sizeof(int);
+    if (binSmem > 48 * 1024)  // per-device attribute: set on every launch that needs it
+        cudaFuncSetAttribute(orbx_stereo_bin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)binSmem);
+    orbx_stereo_bin_kernel<<<sp.frames, 256, binSmem, s>>>(pl, pr, sp);
     dim3 grid((sp.maxKp + ST_WARPS - 1) / ST_WARPS, sp.frames);
     orbx_stereo_match_kernel<<<grid, ST_WARPS * 32, 0, s>>>(pl, pr, sp);
     orbx_stereo_median_kernel<<<sp.frames, 256, 0, s>>>(pl, sp);
