@@ -133,7 +133,7 @@ static int copy_level(Engine& E, int img, int level, bool blurred, uint8_t* dst,
     const uint8_t* src;
     size_t pitch;
     if (blurred) { src = E.P.blur + (size_t)img * E.P.blurStride + L.boff; pitch = L.bpitch; }
-    else if (level == 0) { src = E.P.img0 + (size_t)img * E.P.img0Stride; pitch = E.P.cols; }
+    else if (level == 0) { src = E.P.img0 + (size_t)img * E.P.img0Stride; pitch = E.P.lv[0].pitch; }
     else { src = E.P.pyr + (size_t)img * E.P.pyrStride + L.off; pitch = L.pitch; }
     TRY(orbx_check(cudaSetDevice(E.device), "cudaSetDevice", g_err));
     TRY(orbx_check(cudaMemcpy2DAsync(dst, dstStride, src, pitch, L.w, L.h, cudaMemcpyDeviceToHost, E.stream), "D2H level", g_err));

@@ -5,6 +5,8 @@
 #include <cstdio>
 #include <cstring>
 
+#include <cuda.h>  // CUtensorMap types only; the encoder is fetched from the driver at run time (no -lcuda)
+
 #include "../../include/orbx.h"
 
 int orbx_check(cudaError_t e, const char* what, std::string& err)
@@ -111,7 +113,7 @@ int Engine::plan(const ExtractorConfig& cfg, int rows, int cols, OrbxParams& p, 
             err = "pyramid level " + std::to_string(l) + " smaller than 62 px: the reference divides by zero here";
             return ORBX_ERR_GEOMETRY;
         }
-        L.pitch = l == 0 ? cols : (int)align_up(L.w, 16);
+        L.pitch = (int)align_up(L.w, 16);
         L.bpitch = (int)align_up(L.w, 16);
         L.off = off;
         if (l > 0) off += align_up((unsigned)L.pitch * L.h, 256);
@@ -135,7 +137,7 @@ int Engine::plan(const ExtractorConfig& cfg, int rows, int cols, OrbxParams& p, 
         L.scale = cfg.scale[l]; L.invScale = cfg.invScale[l];
         L.patchSize = (int)(31 * cfg.scale[l]);  // :836
     }
-    p.img0Stride = (size_t)rows * cols;
+    p.img0Stride = (size_t)rows * p.lv[0].pitch;
     p.pyrStride = off; p.blurStride = boff;
     p.cellsTotal = cellBase; p.slotTotal = slot; p.candTotal = cand;
     p.keepTotal = keepBase; p.maxKp = keepBase;
@@ -190,6 +192,36 @@ static int dalloc(Engine* e, T** ptr, size_t count, const char* what, std::strin
 
 #define TRY(x) do { int rc_ = (x); if (rc_) return rc_; } while (0)
 
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int Engine::makeLevelMaps(int boxW, int boxH, void** dMaps, std::string& err)
+{
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    TRY(orbx_check(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q), "cudaGetDriverEntryPoint", err));
+    if (!fn || q != cudaDriverEntryPointSuccess) { err = "driver has no cuTensorMapEncodeTiled"; return ORBX_ERR_CUDA; }
+    std::vector<CUtensorMap> maps(P.nlevels);
+    for (int l = 0; l < P.nlevels; ++l) {
+        const OrbxLevel& L = P.lv[l];
+        void* base = l == 0 ? (void*)P.img0 : (void*)(P.pyr + L.off);
+        const cuuint64_t dims[3] = {(cuuint64_t)L.w, (cuuint64_t)L.h, (cuuint64_t)maxImgs};
+        const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)(l == 0 ? P.img0Stride : P.pyrStride)};
+        const cuuint32_t box[3] = {(cuuint32_t)boxW, (cuuint32_t)boxH, 1u};
+        const cuuint32_t es[3] = {1u, 1u, 1u};
+        const CUresult r = ((EncodeTiledFn)fn)(&maps[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, es,
+                                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { err = "cuTensorMapEncodeTiled failed for level " + std::to_string(l) + " (CUresult " + std::to_string((int)r) + ")"; return ORBX_ERR_CUDA; }
+    }
+    CUtensorMap* d = nullptr;
+    TRY(dalloc(this, &d, maps.size(), "tensor maps", err));
+    TRY(orbx_check(cudaMemcpy(d, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice), "tensor maps H2D", err));
+    *dMaps = d;
+    return ORBX_OK;
+}
+
 int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int dev, std::string& err)
 {
     release();
@@ -204,6 +236,7 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
 
     const size_t n = (size_t)nImgs;
     TRY(dalloc(this, &P.img0, n * P.img0Stride + 64, "img0", err));
+    TRY(dalloc(this, &dStage, n * rows * cols + 64, "stage", err));
     TRY(dalloc(this, &P.pyr, n * P.pyrStride + 64, "pyr", err));
     TRY(dalloc(this, &P.blur, n * P.blurStride + 64, "blur", err));
     TRY(dalloc(this, &P.cellCnt, n * P.cellsTotal, "cellCnt", err));
@@ -227,8 +260,8 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     for (int l = 0; l < P.nlevels; ++l) {
         OrbxLevel tmp = P.lv[l];
         level_cells(P.lv[l].w, P.lv[l].h, l, tmp, &cells);
-        for (int y = 0; y < P.lv[l].h; y += 32)
-            for (int x = 0; x < P.lv[l].w; x += 64) {
+        for (int y = 0; y < P.lv[l].h; y += ORBX_BLUR_TH)
+            for (int x = 0; x < P.lv[l].w; x += ORBX_BLUR_TW) {
                 HostTile t; t.x0 = (short)x; t.y0 = (short)y; t.level = (uint8_t)l; t.pad[0] = t.pad[1] = t.pad[2] = 0;
                 tiles.push_back(t);
             }
@@ -257,6 +290,8 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     resizeTabs.assign(P.nlevels, nullptr);
     for (int l = 1; l < P.nlevels; ++l) resizeTabs[l] = dResizeTab + tabOff[l];
 
+    TRY(makeLevelMaps(128, ORBX_BLUR_TH + 6, &dBlurMaps, err));
+
     if (stereo) {
         const size_t fr = n / 2;
         SP.maxKp = P.maxKp; SP.nlevels = P.nlevels; SP.rows0 = rows;
@@ -278,19 +313,26 @@ int Engine::uploadImages(const uint8_t* left, const uint8_t* right, int nFrames,
     const int per = stereo ? 2 : 1;
     if (nFrames < 1 || nFrames * per > maxImgs || !left || (stereo && !right)) { err = "bad upload arguments"; return ORBX_ERR_ARG; }
     TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
-    const size_t img = P.img0Stride;
-    const cudaMemcpyKind kind = fromDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
-    // image 2f+s <- side s of frame f: one strided 2-D copy per side
-    TRY(orbx_check(cudaMemcpy2DAsync(P.img0, per * img, left, img, img, nFrames, kind, stream), "upload left", err));
-    if (stereo)
-        TRY(orbx_check(cudaMemcpy2DAsync(P.img0 + img, per * img, right, img, img, nFrames, kind, stream), "upload right", err));
+    // image 2f+s <- side s of frame f. Host images arrive with ONE linear copy per side into a staging buffer
+    // (a strided 3-D copy runs far below PCIe rate); a kernel then re-pitches the tight rows into level 0.
+    const size_t tight = (size_t)rows * cols * nFrames;
+    for (int side = 0; side < per; ++side) {
+        const uint8_t* src = side ? right : left;
+        if (!fromDevice) {
+            uint8_t* st = dStage + (size_t)side * rows * cols * (maxImgs / per);
+            TRY(orbx_check(cudaMemcpyAsync(st, src, tight, cudaMemcpyHostToDevice, stream), side ? "upload right" : "upload left", err));
+            src = st;
+        }
+        orbx_launch_ingest(P, src, nFrames, per, side, stream);
+    }
+    TRY(orbx_check(cudaGetLastError(), "ingest launch", err));
     return ORBX_OK;
 }
 
 int Engine::uploadSingle(const uint8_t* image, size_t stride, std::string& err)
 {
     TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
-    return orbx_check(cudaMemcpy2DAsync(P.img0, cols, image, stride, cols, rows, cudaMemcpyHostToDevice, stream), "upload image", err);
+    return orbx_check(cudaMemcpy2DAsync(P.img0, (size_t)P.lv[0].pitch, image, stride, cols, rows, cudaMemcpyHostToDevice, stream), "upload image", err);
 }
 
 int Engine::runExtract(int nImgs, std::string& err)
@@ -306,7 +348,7 @@ int Engine::runExtract(int nImgs, std::string& err)
     mark(2);
     orbx_launch_octree(p, dCells, stream);
     mark(3);
-    orbx_launch_blur(p, dTiles, nTiles, stream);
+    orbx_launch_blur(p, dTiles, nTiles, dBlurMaps, stream);
     mark(4);
     orbx_launch_describe(p, stream);
     mark(5);

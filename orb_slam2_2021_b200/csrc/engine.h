@@ -29,6 +29,8 @@ public:
     void release();
 
     // level geometry without allocating anything (for orbx_max_keypoints)
+    // TMA descriptors of the un-blurred levels with the given box (device array of nlevels CUtensorMap)
+    int makeLevelMaps(int boxW, int boxH, void** dMaps, std::string& err);
     static int plan(const ExtractorConfig& cfg, int rows, int cols, OrbxParams& p, std::string& err);
 
     int uploadImages(const uint8_t* left, const uint8_t* right, int nFrames, bool fromDevice, std::string& err);
@@ -47,6 +49,8 @@ public:
     void* dCells = nullptr;
     void* dTiles = nullptr;
     int* dResizeTab = nullptr;
+    uint8_t* dStage = nullptr;  // tight-row landing buffer of host uploads ([side][frame][rows*cols])
+    void* dBlurMaps = nullptr;  // CUtensorMap[nlevels]: un-blurred level l as a (w, h, image) u8 tensor, box 128 x 70 x 1
     std::vector<const int*> resizeTabs;  // per level device pointers into dResizeTab
     std::vector<void*> allocs;
     size_t bytesAllocated = 0;

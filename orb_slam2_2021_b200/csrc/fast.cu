@@ -23,7 +23,10 @@
 //     unsigned u16x2 with the 3-input DPX instructions (__vimin3_u16x2 / __vimax3_u16x2):
 //     16+16 ops for the 9-windows and 8 for the reduction, per polarity, per pixel PAIR;
 //   * lanes are laid out 8 pairs x 4 rows with a row stride of 24 (or 40) words, which makes every
-//     ring load bank-conflict free.
+//     ring load bank-conflict free;
+//   * staging reads aligned 32-bit words from the level (the ROI origin is not aligned; the tile keeps
+//     the x0&3 offset and the A/B roles swap with its parity), and the strength map is kept as u16 so
+//     that NMS runs four pixels per thread on the same packed max instructions.
 #include "orbx_dev.cuh"
 
 struct OrbxCell {
@@ -34,7 +37,7 @@ struct OrbxCell {
 
 #define FAST_THREADS 128
 #define FAST_WARPS (FAST_THREADS / 32)
-#define FAST_MAX_ITERS 32  // 128-pixel chunks of one cell interior (<= 60x60 px)
+#define FAST_MAX_ITERS 8   // 128-quad steps of one cell interior (<= 60x60 px = 900 quads)
 
 __device__ __forceinline__ int imax3(int a, int b, int c) { return max(a, max(b, c)); }
 
@@ -78,15 +81,38 @@ __device__ __forceinline__ void fast_strength2(const uint16_t* a, const uint16_t
     m1 = max((int)(br >> 16) - 256, 256 - (int)(dk >> 16));
 }
 
+// One interior pixel quad (4 consecutive pixels of one row) per thread and step: bit k of the result
+// = pixel k is a strict 3x3 maximum of the strength map; `ini` gets the subset above iniTh.
+// s points at smap[row y][col 4q] (u16, 8-byte aligned); MS = row stride in elements.
+template <int MS>
+__device__ __forceinline__ unsigned nms_quad(const uint16_t* s, int tini, unsigned& ini)
+{
+    const uint2 r0a = *reinterpret_cast<const uint2*>(s), r0b = *reinterpret_cast<const uint2*>(s + 4);
+    const uint2 r1a = *reinterpret_cast<const uint2*>(s + MS), r1b = *reinterpret_cast<const uint2*>(s + MS + 4);
+    const uint2 r2a = *reinterpret_cast<const uint2*>(s + 2 * MS), r2b = *reinterpret_cast<const uint2*>(s + 2 * MS + 4);
+    ini = 0;
+    if ((r1a.y | r1b.x) == 0) return 0;  // no corner among the four centres
+    const uint32_t cm0 = __vimax3_u16x2(r0a.x, r1a.x, r2a.x), cm1 = __vimax3_u16x2(r0a.y, r1a.y, r2a.y);
+    const uint32_t cm2 = __vimax3_u16x2(r0b.x, r1b.x, r2b.x), cm3 = __vimax3_u16x2(r0b.y, r1b.y, r2b.y);
+    const uint32_t L1 = __funnelshift_r(cm0, cm1, 16), R1 = __funnelshift_r(cm1, cm2, 16), R2 = __funnelshift_r(cm2, cm3, 16);
+    const uint32_t ud1 = __vimax3_u16x2(r0a.y, r2a.y, r2a.y), ud2 = __vimax3_u16x2(r0b.x, r2b.x, r2b.x);
+    const uint32_t nb1 = __vimax3_u16x2(L1, R1, ud1), nb2 = __vimax3_u16x2(R1, R2, ud2);
+    const int m0 = r1a.y & 0xFFFFu, m1 = r1a.y >> 16, m2 = r1b.x & 0xFFFFu, m3 = r1b.x >> 16;
+    const int n0 = nb1 & 0xFFFFu, n1 = nb1 >> 16, n2 = nb2 & 0xFFFFu, n3 = nb2 >> 16;
+    const unsigned mx = (m0 > n0 ? 1u : 0u) | (m1 > n1 ? 2u : 0u) | (m2 > n2 ? 4u : 0u) | (m3 > n3 ? 8u : 0u);
+    ini = mx & ((m0 > tini ? 1u : 0u) | (m1 > tini ? 2u : 0u) | (m2 > tini ? 4u : 0u) | (m3 > tini ? 8u : 0u));
+    return mx;
+}
+
 template <int SA>
 __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, int rhMax)
 {
     extern __shared__ __align__(16) uint8_t fast_smem[];
-    __shared__ int warpCnt[FAST_MAX_ITERS][FAST_WARPS];
+    __shared__ __align__(16) int warpCnt[FAST_MAX_ITERS][FAST_WARPS];
 
-    uint16_t* A = reinterpret_cast<uint16_t*>(fast_smem);
-    uint16_t* B = A + rhMax * SA;
-    uint8_t* smap = reinterpret_cast<uint8_t*>(B + rhMax * SA);  // strength map with a 1-px zero frame
+    uint16_t* A = reinterpret_cast<uint16_t*>(fast_smem);       // A[y][j] = I(xa + j, y0 + y), xa = x0 & ~3
+    uint16_t* B = A + rhMax * SA;                                // B[y][j] = I(xa + j + 1, y0 + y)
+    uint16_t* smap = B + rhMax * SA;  // strength map: interior pixel (ix,iy) at [iy+1][ix+2], zero elsewhere
 
     const int cellId = blockIdx.x, img = blockIdx.y;
     const OrbxCell cell = cells[cellId];
@@ -101,17 +127,28 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int pitch;
     const uint8_t* lvl = orbx_level_ptr(p, img, cell.level, &pitch);
-    const uint8_t* src = lvl + (size_t)cell.y0 * pitch + cell.x0;
-    for (int y = warp; y < rh; y += FAST_WARPS) {
-        const uint8_t* row = src + (size_t)y * pitch;
-        for (int x = lane; x < rw; x += 32) {
-            const uint16_t v = row[x];
-            A[y * SA + x] = v;
-            if (x) B[y * SA + x - 1] = v;
+    const int o = cell.x0 & 3;
+    {
+        // aligned 32-bit words of the level (base and pitch are multiples of 16); 16 words x 2 rows per warp step
+        const uint8_t* src = lvl + (size_t)cell.y0 * pitch + (cell.x0 - o);
+        const int nw = (o + rw + 4) >> 2;  // covers tile columns 0 .. o+rw (one past the ROI, read by odd-width pairs)
+        const int j0 = lane & 15;
+        for (int y = warp * 2 + (lane >> 4); y < rh; y += 2 * FAST_WARPS) {
+            const uint32_t* row = reinterpret_cast<const uint32_t*>(src + (size_t)y * pitch);
+            for (int j = j0; j < nw; j += 16) {
+                const uint32_t w = __ldg(row + j);
+                const uint32_t wn = j + 1 < nw ? __ldg(row + j + 1) : 0u;
+                const uint32_t t = __funnelshift_r(w, wn, 8);
+                *reinterpret_cast<uint2*>(A + y * SA + 4 * j) = make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
+                *reinterpret_cast<uint2*>(B + y * SA + 4 * j) = make_uint2(__byte_perm(t, 0, 0x4140), __byte_perm(t, 0, 0x4342));
+            }
         }
     }
-    const int mw = iw + 2;
-    for (int i = threadIdx.x; i < mw * (ih + 2); i += FAST_THREADS) smap[i] = 0;
+    {
+        uint32_t* z = reinterpret_cast<uint32_t*>(smap);
+        const int nz = (ih + 2) * (SA / 2);
+        for (int i = threadIdx.x; i < nz; i += FAST_THREADS) z[i] = 0;
+    }
     __syncthreads();
 
     // ---- strength map: lane = (pair lx, row ly) in an 8x4 patch; warp w owns rows 4w.. (+16 per step)
@@ -119,47 +156,49 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     {
         const int lx = lane & 7, ly = lane >> 3;
         const int npairs = (iw + 1) >> 1;
+        // centre tile column of pair xp is c = o + 3 + 2*xp. The array whose pair at (c + dx) is word aligned serves
+        // dx: o even -> c odd: odd dx from A, even dx from B (at index c-1+dx); o odd -> c even: roles swap.
+        const uint16_t* podd = (o & 1) ? B + (o + 2) : A + (o + 3);
+        const uint16_t* pevn = (o & 1) ? A + (o + 3) : B + (o + 2);
         for (int y = warp * 4 + ly; y < ih; y += 4 * FAST_WARPS) {
-            const uint16_t* arow = A + (y + 3) * SA + 3;
-            const uint16_t* brow = B + (y + 3) * SA + 2;
-            uint8_t* srow = smap + (y + 1) * mw + 1;
+            const uint16_t* arow = podd + (y + 3) * SA;
+            const uint16_t* brow = pevn + (y + 3) * SA;
+            uint32_t* srow = reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + 2);
             for (int xp = lx; xp < npairs; xp += 8) {
                 int m0, m1;
                 fast_strength2<SA>(arow + 2 * xp, brow + 2 * xp, m0, m1);
-                if (m0 > tmin) srow[2 * xp] = (uint8_t)m0;
-                if (m1 > tmin && 2 * xp + 1 < iw) srow[2 * xp + 1] = (uint8_t)m1;
+                m0 = m0 > tmin ? m0 : 0;
+                m1 = (m1 > tmin && 2 * xp + 1 < iw) ? m1 : 0;
+                srow[xp] = (uint32_t)m0 | ((uint32_t)m1 << 16);
             }
         }
     }
     __syncthreads();
 
-    // ---- NMS once; bit `it` of isMax / isIni = pixel (it*128 + tid) is a maximum (> minTh / > iniTh)
-    const int npx = iw * ih;
-    const float invw = __frcp_rn((float)iw);
+    // ---- NMS once: 4 bits per step; quad i = step*128 + tid in row-major order, nq quads per row
+    const int nq = (iw + 3) >> 2, nquads = nq * ih;
+    const int iters = (nquads + FAST_THREADS - 1) / FAST_THREADS;  // <= 8 (60x60 interior)
+    const float invq = __frcp_rn((float)nq);
     unsigned isMax = 0, isIni = 0;
-    for (int it = 0, base = 0; base < npx; ++it, base += FAST_THREADS) {
-        const int i = base + threadIdx.x;
-        if (i < npx) {
-            const int y = (int)(((float)i + 0.5f) * invw), x = i - y * iw;
-            const uint8_t* s = smap + (y + 1) * mw + (x + 1);
-            const int m = s[0];
-            if (m) {
-                const int nb = max(max(imax3(s[-mw - 1], s[-mw], s[-mw + 1]), imax3(s[mw - 1], s[mw], s[mw + 1])),
-                                   max(s[-1], s[1]));
-                if (m > nb) {
-                    isMax |= 1u << it;
-                    if (m > tini) isIni |= 1u << it;
-                }
-            }
+    for (int it = 0; it < iters; ++it) {
+        const int i = it * FAST_THREADS + threadIdx.x;
+        if (i < nquads) {
+            const int y = (int)(((float)i + 0.5f) * invq), q = i - y * nq;
+            unsigned ini;
+            const unsigned mx = nms_quad<SA>(smap + y * SA + 4 * q, tini, ini);
+            isMax |= mx << (4 * it);
+            isIni |= ini << (4 * it);
         }
     }
     const unsigned sel = __syncthreads_or(isIni != 0) ? isIni : isMax;  // :814 fallback to minTh iff FAST(ini) is empty
 
     // ---- ordered (row-major) emission
-    const int iters = (npx + FAST_THREADS - 1) / FAST_THREADS;
+    const unsigned lt = (1u << lane) - 1;
     for (int it = 0; it < iters; ++it) {
-        const unsigned bal = __ballot_sync(0xffffffffu, (sel >> it) & 1u);
-        if (lane == 0) warpCnt[it][warp] = __popc(bal);
+        const unsigned k4 = (sel >> (4 * it)) & 15u;
+        const int c = __popc(__ballot_sync(0xffffffffu, k4 & 1u)) + __popc(__ballot_sync(0xffffffffu, k4 & 2u)) +
+                      __popc(__ballot_sync(0xffffffffu, k4 & 4u)) + __popc(__ballot_sync(0xffffffffu, k4 & 8u));
+        if (lane == 0) warpCnt[it][warp] = c;
     }
     __syncthreads();
     const uint32_t slot0 = L.slotBase + (uint32_t)(cellId - L.cellBase) * L.slotCap;
@@ -167,15 +206,21 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     int running = 0;
     for (int it = 0; it < iters; ++it) {
         const int4 c = *reinterpret_cast<const int4*>(warpCnt[it]);
-        const unsigned keep = (sel >> it) & 1u;
-        const unsigned bal = __ballot_sync(0xffffffffu, keep);
-        if (keep) {
+        const unsigned k4 = (sel >> (4 * it)) & 15u;
+        const unsigned b0 = __ballot_sync(0xffffffffu, k4 & 1u), b1 = __ballot_sync(0xffffffffu, k4 & 2u);
+        const unsigned b2 = __ballot_sync(0xffffffffu, k4 & 4u), b3 = __ballot_sync(0xffffffffu, k4 & 8u);
+        if (k4) {
             const int i = it * FAST_THREADS + threadIdx.x;
-            const int y = (int)(((float)i + 0.5f) * invw), x = i - y * iw;
-            const int m = smap[(y + 1) * mw + (x + 1)];
-            int ofs = running + __popc(bal & ((1u << lane) - 1));
+            const int y = (int)(((float)i + 0.5f) * invq), q = i - y * nq;
+            int ofs = running + __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt);
             ofs += (warp > 0 ? c.x : 0) + (warp > 1 ? c.y : 0) + (warp > 2 ? c.z : 0);
-            out[ofs] = (uint32_t)(x + 3) | ((uint32_t)(y + 3) << 8) | ((uint32_t)(m - 1) << 16);
+            const uint16_t* s = smap + (y + 1) * SA + 4 * q + 2;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (k4 & (1u << k)) {
+                    const int m = s[k];
+                    out[ofs++] = (uint32_t)(4 * q + k + 3) | ((uint32_t)(y + 3) << 8) | ((uint32_t)(m - 1) << 16);
+                }
         }
         running += c.x + c.y + c.z + c.w;
     }
@@ -190,14 +235,12 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, cudaStream_t s
         rwMax = p.lv[l].wCell + 6 > rwMax ? p.lv[l].wCell + 6 : rwMax;
         rhMax = p.lv[l].hCell + 6 > rhMax ? p.lv[l].hCell + 6 : rhMax;
     }
-    rhMax += 1;  // pairs of an odd-width interior read one element past the ROI; keep that inside the buffer
     dim3 grid(p.cellsTotal, p.imgs);
-    const size_t smapBytes = (size_t)(rwMax - 4) * (rhMax - 4);
-    if (rwMax + 2 <= 48) {
-        const size_t smem = (size_t)2 * rhMax * 48 * 2 + smapBytes;
+    // tile columns: 3 (alignment) + ROI + 1, rounded up to whole words; strength-map columns: interior + 8
+    const int sa = rwMax + 8 <= 48 ? 48 : 80;
+    const size_t smem = (size_t)2 * rhMax * sa * 2 + (size_t)(rhMax - 4) * sa * 2;
+    if (sa == 48)
         orbx_fast_kernel<48><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, rhMax);
-    } else {
-        const size_t smem = (size_t)2 * rhMax * 80 * 2 + smapBytes;  // ROI <= 66 px (cells of levels narrower than 90 px)
+    else
         orbx_fast_kernel<80><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, rhMax);
-    }
 }

@@ -1,7 +1,7 @@
 // orbx_dev.cuh — device-side data layout shared by all kernels and the host engine.
 //
 // HBM layout for a chunk of `imgs` images (stereo: image 2f = left of frame f, 2f+1 = right):
-//   img0   [imgs][H*W]            u8  level 0 = the uploaded image, tight rows (pitch W)
+//   img0   [imgs][H*pitch0]       u8  level 0 = the uploaded image, row pitch = align16(W) (TMA needs 16-B strides)
 //   pyr    [imgs][pyrStride]      u8  levels 1..L-1 packed, row pitch = align16(w_l)
 //   blur   [imgs][blurStride]     u8  7x7 Gaussian of levels 0..L-1, row pitch = align16(w_l)
 //   cellCnt[imgs][cellsTotal]     i32 FAST keypoints per 30-px cell
@@ -22,9 +22,11 @@
 #define ORBX_MAX_LEVELS 12
 #define ORBX_EDGE 19
 #define ORBX_HALF_PATCH 15
+#define ORBX_BLUR_TW 96   // blur output tile (a 128 x 70 TMA box: 16 px left, 3 px above/below)
+#define ORBX_BLUR_TH 64
 
 struct OrbxLevel {
-    int w, h, pitch;      // level size; row pitch in pyr (level 0: pitch == w in img0)
+    int w, h, pitch;      // level size; row pitch = align16(w) (level 0 lives in img0, levels >= 1 in pyr)
     int bpitch;           // row pitch in blur
     unsigned off;         // byte offset inside one image's pyr block (levels >= 1)
     unsigned boff;        // byte offset inside one image's blur block
@@ -70,7 +72,7 @@ struct OrbxParams {
 __device__ __forceinline__ const uint8_t* orbx_level_ptr(const OrbxParams& p, int img, int l, int* pitch)
 {
     if (l == 0) {
-        *pitch = p.cols;
+        *pitch = p.lv[0].pitch;
         return p.img0 + (size_t)img * p.img0Stride;
     }
     *pitch = p.lv[l].pitch;
@@ -97,9 +99,11 @@ struct OrbxStereoParams {
 };
 
 // Launch wrappers (one per kernel group), defined in the .cu files.
+// tight [frame][rows][cols] images of one side -> pitched level 0 of image frame*per + side
+void orbx_launch_ingest(const OrbxParams& p, const uint8_t* src, int nFrames, int per, int side, cudaStream_t s);
 void orbx_launch_pyramid(const OrbxParams& p, const int* const* tabs, cudaStream_t s);
 void orbx_launch_fast(const OrbxParams& p, const void* cellTable, cudaStream_t s);
 void orbx_launch_octree(const OrbxParams& p, const void* cellTable, cudaStream_t s);
-void orbx_launch_blur(const OrbxParams& p, const void* tileTable, int nTiles, cudaStream_t s);
+void orbx_launch_blur(const OrbxParams& p, const void* tileTable, int nTiles, const void* levelMaps, cudaStream_t s);
 void orbx_launch_describe(const OrbxParams& p, cudaStream_t s);
 void orbx_launch_stereo(const OrbxParams& pl, const OrbxParams& pr, const OrbxStereoParams& sp, cudaStream_t s);

@@ -54,6 +54,32 @@ __global__ void __launch_bounds__(256) orbx_resize_kernel(OrbxParams p, int l, R
     *reinterpret_cast<uint32_t*>(dst + x0) = packed;  // pitch is a multiple of 16: in-row padding absorbs the tail
 }
 
+// Level 0 ingest: tight rows (pitch = cols, any alignment) -> pitched rows (16-B multiple, TMA-legal).
+// One thread per aligned 16-byte destination chunk; the source bytes come through L1 (rows are contiguous).
+__global__ void __launch_bounds__(256) orbx_ingest_kernel(OrbxParams p, const uint8_t* src, int per, int side)
+{
+    const int chunksPerRow = p.lv[0].pitch >> 4;
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= chunksPerRow * p.rows) return;
+    const int y = i / chunksPerRow, cx = (i - y * chunksPerRow) << 4;
+    const int f = blockIdx.y;
+    const uint8_t* s = src + ((size_t)f * p.rows + y) * p.cols + cx;
+    uint32_t w[4] = {0, 0, 0, 0};
+    const int n = min(16, p.cols - cx);
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+        if (k < n) w[k >> 2] |= (uint32_t)s[k] << (8 * (k & 3));
+    uint8_t* d = p.img0 + (size_t)(f * per + side) * p.img0Stride + (size_t)y * p.lv[0].pitch + cx;
+    *reinterpret_cast<uint4*>(d) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+void orbx_launch_ingest(const OrbxParams& p, const uint8_t* src, int nFrames, int per, int side, cudaStream_t s)
+{
+    const int chunks = (p.lv[0].pitch >> 4) * p.rows;
+    dim3 grid((chunks + 255) / 256, nFrames);
+    orbx_ingest_kernel<<<grid, 256, 0, s>>>(p, src, per, side);
+}
+
 // tabs[l] points at the level's table block: xofs[w] xcoef[w] yofs[h] ycoef[h]
 void orbx_launch_pyramid(const OrbxParams& p, const int* const* tabs, cudaStream_t s)
 {
