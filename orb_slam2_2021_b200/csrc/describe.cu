@@ -48,14 +48,16 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) orbx_describe_kernel(OrbxPara
     if (lane < 31) {
         const int au = abs(u);
         const uint8_t* c = im + (size_t)cy * pitch + cx + u;
-#pragma unroll 1
+        // fully unrolled: 31 independent loads in flight (the rolled loop was bound by load latency, ncu long_scoreboard)
+        int colSum = 0;
+#pragma unroll
         for (int v = -ORBX_HALF_PATCH; v <= ORBX_HALF_PATCH; ++v) {
-            if (au <= c_umax[abs(v)]) {
-                const int I = c[v * pitch];
-                m10 += u * I;
-                m01 += v * I;
-            }
+            constexpr int kUmax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+            const int I = au <= kUmax[v < 0 ? -v : v] ? (int)c[v * pitch] : 0;
+            colSum += I;
+            m01 += v * I;
         }
+        m10 = u * colSum;
     }
 #pragma unroll
     for (int o = 16; o; o >>= 1) {

@@ -291,6 +291,11 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     for (int l = 1; l < P.nlevels; ++l) resizeTabs[l] = dResizeTab + tabOff[l];
 
     TRY(makeLevelMaps(128, ORBX_BLUR_TH + 6, &dBlurMaps, err));
+    {
+        int bw, rh;
+        orbx_fast_geometry(P, &bw, &rh);
+        TRY(makeLevelMaps(bw, rh, &dFastMaps, err));
+    }
 
     if (stereo) {
         const size_t fr = n / 2;
@@ -344,7 +349,7 @@ int Engine::runExtract(int nImgs, std::string& err)
     mark(0);
     orbx_launch_pyramid(p, resizeTabs.data(), stream);
     mark(1);
-    orbx_launch_fast(p, dCells, stream);
+    orbx_launch_fast(p, dCells, dFastMaps, stream);
     mark(2);
     orbx_launch_octree(p, dCells, stream);
     mark(3);

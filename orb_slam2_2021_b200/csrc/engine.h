@@ -50,6 +50,7 @@ public:
     void* dTiles = nullptr;
     int* dResizeTab = nullptr;
     uint8_t* dStage = nullptr;  // tight-row landing buffer of host uploads ([side][frame][rows*cols])
+    void* dFastMaps = nullptr;  // same tensors, box = (64|96) x (largest cell ROI height) x 1
     void* dBlurMaps = nullptr;  // CUtensorMap[nlevels]: un-blurred level l as a (w, h, image) u8 tensor, box 128 x 70 x 1
     std::vector<const int*> resizeTabs;  // per level device pointers into dResizeTab
     std::vector<void*> allocs;

@@ -24,10 +24,13 @@
 //     16+16 ops for the 9-windows and 8 for the reduction, per polarity, per pixel PAIR;
 //   * lanes are laid out 8 pairs x 4 rows with a row stride of 24 (or 40) words, which makes every
 //     ring load bank-conflict free;
-//   * staging reads aligned 32-bit words from the level (the ROI origin is not aligned; the tile keeps
-//     the x0&3 offset and the A/B roles swap with its parity), and the strength map is kept as u16 so
-//     that NMS runs four pixels per thread on the same packed max instructions.
+//   * the ROI arrives by ONE TMA box load (cp.async.bulk.tensor.3d, 64 or 96 columns starting at x0 & ~15 —
+//     the copy engine addresses the innermost dimension in 16-byte units — by rhMax rows) signalled on an
+//     mbarrier; a short shared-to-shared pass widens it into A/B (the tile keeps the x0&3 offset and the
+//     A/B roles swap with its parity); the strength map is kept as u16 so that NMS runs four pixels per
+//     thread on the same packed max instructions.
 #include "orbx_dev.cuh"
+#include "orbx_tma.cuh"
 
 struct OrbxCell {
     short x0, y0;        // ROI origin in level coordinates (iniX, iniY)
@@ -105,13 +108,17 @@ __device__ __forceinline__ unsigned nms_quad(const uint16_t* s, int tini, unsign
 }
 
 template <int SA>
-__global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, int rhMax)
+__global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax)
 {
-    extern __shared__ __align__(16) uint8_t fast_smem[];
+    constexpr int BW = SA == 48 ? 64 : 96;      // TMA box width in bytes
+    constexpr int WSLOT = SA == 48 ? 16 : 32;   // word slots per row in the widening pass
+    extern __shared__ __align__(128) uint8_t fast_smem[];
     __shared__ __align__(16) int warpCnt[FAST_MAX_ITERS][FAST_WARPS];
+    __shared__ __align__(8) uint64_t bar;
 
-    uint16_t* A = reinterpret_cast<uint16_t*>(fast_smem);       // A[y][j] = I(xa + j, y0 + y), xa = x0 & ~3
-    uint16_t* B = A + rhMax * SA;                                // B[y][j] = I(xa + j + 1, y0 + y)
+    uint8_t* T = fast_smem;                                                     // raw box [rhMax][BW]
+    uint16_t* A = reinterpret_cast<uint16_t*>(fast_smem + ((rhMax * BW + 127) & ~127));  // A[y][j] = I(xa + j, y0 + y), xa = x0 & ~3
+    uint16_t* B = A + rhMax * SA;                                                // B[y][j] = I(xa + j + 1, y0 + y)
     uint16_t* smap = B + rhMax * SA;  // strength map: interior pixel (ix,iy) at [iy+1][ix+2], zero elsewhere
 
     const int cellId = blockIdx.x, img = blockIdx.y;
@@ -125,29 +132,37 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         return;
     }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int pitch;
-    const uint8_t* lvl = orbx_level_ptr(p, img, cell.level, &pitch);
-    const int o = cell.x0 & 3;
-    {
-        // aligned 32-bit words of the level (base and pitch are multiples of 16); 16 words x 2 rows per warp step
-        const uint8_t* src = lvl + (size_t)cell.y0 * pitch + (cell.x0 - o);
-        const int nw = (o + rw + 4) >> 2;  // covers tile columns 0 .. o+rw (one past the ROI, read by odd-width pairs)
-        const int j0 = lane & 15;
-        for (int y = warp * 2 + (lane >> 4); y < rh; y += 2 * FAST_WARPS) {
-            const uint32_t* row = reinterpret_cast<const uint32_t*>(src + (size_t)y * pitch);
-            for (int j = j0; j < nw; j += 16) {
-                const uint32_t w = __ldg(row + j);
-                const uint32_t wn = j + 1 < nw ? __ldg(row + j + 1) : 0u;
-                const uint32_t t = __funnelshift_r(w, wn, 8);
-                *reinterpret_cast<uint2*>(A + y * SA + 4 * j) = make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
-                *reinterpret_cast<uint2*>(B + y * SA + 4 * j) = make_uint2(__byte_perm(t, 0, 0x4140), __byte_perm(t, 0, 0x4342));
-            }
-        }
+    if (threadIdx.x == 0) {
+        orbx_mbar_init(&bar, 1);
+        orbx_fence_mbar_init();
+        orbx_mbar_expect_tx(&bar, rhMax * BW);
+        orbx_tma_load_3d(T, maps + cell.level, cell.x0 & ~15, cell.y0, img, &bar);
     }
     {
         uint32_t* z = reinterpret_cast<uint32_t*>(smap);
         const int nz = (ih + 2) * (SA / 2);
         for (int i = threadIdx.x; i < nz; i += FAST_THREADS) z[i] = 0;
+    }
+    __syncthreads();  // barrier initialised (and armed) before anybody polls it
+    orbx_mbar_wait(&bar, 0);
+
+    // ---- widen the raw bytes into the two u16 pair layouts
+    const int o = cell.x0 & 3;
+    {
+        const int nw = (o + rw + 4) >> 2;  // covers tile columns 0 .. o+rw (one past the ROI, read by odd-width pairs)
+        const uint32_t* T32 = reinterpret_cast<const uint32_t*>(T) + ((cell.x0 & 15) >> 2);
+        const int total = rh * WSLOT;
+#pragma unroll 1
+        for (int i = threadIdx.x; i < total; i += FAST_THREADS) {
+            const int y = i / WSLOT, j = i % WSLOT;
+            if (j < nw) {
+                const uint32_t w = T32[y * (BW / 4) + j];
+                const uint32_t wn = T32[y * (BW / 4) + j + 1];  // inside the box: (x0&15)/4 + nw + 1 <= BW/4
+                const uint32_t t = __funnelshift_r(w, wn, 8);
+                *reinterpret_cast<uint2*>(A + y * SA + 4 * j) = make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
+                *reinterpret_cast<uint2*>(B + y * SA + 4 * j) = make_uint2(__byte_perm(t, 0, 0x4140), __byte_perm(t, 0, 0x4342));
+            }
+        }
     }
     __syncthreads();
 
@@ -160,10 +175,12 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         // dx: o even -> c odd: odd dx from A, even dx from B (at index c-1+dx); o odd -> c even: roles swap.
         const uint16_t* podd = (o & 1) ? B + (o + 2) : A + (o + 3);
         const uint16_t* pevn = (o & 1) ? A + (o + 3) : B + (o + 2);
+#pragma unroll 1
         for (int y = warp * 4 + ly; y < ih; y += 4 * FAST_WARPS) {
             const uint16_t* arow = podd + (y + 3) * SA;
             const uint16_t* brow = pevn + (y + 3) * SA;
             uint32_t* srow = reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + 2);
+#pragma unroll 1
             for (int xp = lx; xp < npairs; xp += 8) {
                 int m0, m1;
                 fast_strength2<SA>(arow + 2 * xp, brow + 2 * xp, m0, m1);
@@ -175,59 +192,65 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     }
     __syncthreads();
 
-    // ---- NMS once: 4 bits per step; quad i = step*128 + tid in row-major order, nq quads per row
+    // ---- NMS once: 4 bits per step; quad i = step*128 + tid in row-major order, nq quads per row.
+    // Per (step, warp) the number of maxima above minTh and above iniTh goes to warpCnt (lo/hi 16 bits).
     const int nq = (iw + 3) >> 2, nquads = nq * ih;
     const int iters = (nquads + FAST_THREADS - 1) / FAST_THREADS;  // <= 8 (60x60 interior)
     const float invq = __frcp_rn((float)nq);
     unsigned isMax = 0, isIni = 0;
+#pragma unroll 1
     for (int it = 0; it < iters; ++it) {
         const int i = it * FAST_THREADS + threadIdx.x;
+        unsigned mx = 0, ini = 0;
         if (i < nquads) {
             const int y = (int)(((float)i + 0.5f) * invq), q = i - y * nq;
-            unsigned ini;
-            const unsigned mx = nms_quad<SA>(smap + y * SA + 4 * q, tini, ini);
+            mx = nms_quad<SA>(smap + y * SA + 4 * q, tini, ini);
             isMax |= mx << (4 * it);
             isIni |= ini << (4 * it);
         }
+        const unsigned packed = __reduce_add_sync(0xffffffffu, (unsigned)__popc(mx) | ((unsigned)__popc(ini) << 16));
+        if (lane == 0) warpCnt[it][warp] = (int)packed;
     }
-    const unsigned sel = __syncthreads_or(isIni != 0) ? isIni : isMax;  // :814 fallback to minTh iff FAST(ini) is empty
+    const bool useIni = __syncthreads_or(isIni != 0);  // :814 fallback to minTh iff FAST(ini) is empty; also publishes warpCnt
+    const unsigned sel = useIni ? isIni : isMax;
+    const int cshift = useIni ? 16 : 0;
 
-    // ---- ordered (row-major) emission
-    const unsigned lt = (1u << lane) - 1;
-    for (int it = 0; it < iters; ++it) {
-        const unsigned k4 = (sel >> (4 * it)) & 15u;
-        const int c = __popc(__ballot_sync(0xffffffffu, k4 & 1u)) + __popc(__ballot_sync(0xffffffffu, k4 & 2u)) +
-                      __popc(__ballot_sync(0xffffffffu, k4 & 4u)) + __popc(__ballot_sync(0xffffffffu, k4 & 8u));
-        if (lane == 0) warpCnt[it][warp] = c;
-    }
-    __syncthreads();
+    // ---- ordered (row-major) emission; a warp whose step holds no keypoint only advances the running count
     const uint32_t slot0 = L.slotBase + (uint32_t)(cellId - L.cellBase) * L.slotCap;
     uint32_t* out = p.cellKp + (size_t)img * p.slotTotal + slot0;
     int running = 0;
+#pragma unroll 1
     for (int it = 0; it < iters; ++it) {
-        const int4 c = *reinterpret_cast<const int4*>(warpCnt[it]);
-        const unsigned k4 = (sel >> (4 * it)) & 15u;
-        const unsigned b0 = __ballot_sync(0xffffffffu, k4 & 1u), b1 = __ballot_sync(0xffffffffu, k4 & 2u);
-        const unsigned b2 = __ballot_sync(0xffffffffu, k4 & 4u), b3 = __ballot_sync(0xffffffffu, k4 & 8u);
-        if (k4) {
-            const int i = it * FAST_THREADS + threadIdx.x;
-            const int y = (int)(((float)i + 0.5f) * invq), q = i - y * nq;
-            int ofs = running + __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt);
-            ofs += (warp > 0 ? c.x : 0) + (warp > 1 ? c.y : 0) + (warp > 2 ? c.z : 0);
-            const uint16_t* s = smap + (y + 1) * SA + 4 * q + 2;
+        const int4 c4 = *reinterpret_cast<const int4*>(warpCnt[it]);
+        const int c0 = (c4.x >> cshift) & 0xFFFF, c1 = (c4.y >> cshift) & 0xFFFF, c2 = (c4.z >> cshift) & 0xFFFF, c3 = (c4.w >> cshift) & 0xFFFF;
+        const int mine = warp == 0 ? c0 : warp == 1 ? c1 : warp == 2 ? c2 : c3;
+        if (mine) {  // warp-uniform
+            const unsigned k4 = (sel >> (4 * it)) & 15u;
+            // exclusive prefix of popc(k4) over the lanes
+            const int pc = __popc(k4);
+            int inc = pc;
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                if (k4 & (1u << k)) {
-                    const int m = s[k];
-                    out[ofs++] = (uint32_t)(4 * q + k + 3) | ((uint32_t)(y + 3) << 8) | ((uint32_t)(m - 1) << 16);
-                }
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += t;
+            }
+            if (k4) {
+                const int i = it * FAST_THREADS + threadIdx.x;
+                const int y = (int)(((float)i + 0.5f) * invq), q = i - y * nq;
+                int ofs = running + inc - pc + (warp > 0 ? c0 : 0) + (warp > 1 ? c1 : 0) + (warp > 2 ? c2 : 0);
+                const uint16_t* sm = smap + (y + 1) * SA + 4 * q + 2;
+                const uint32_t base = (uint32_t)(4 * q + 3) | ((uint32_t)(y + 3) << 8);
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (k4 & (1u << k)) out[ofs++] = (base + k) | ((uint32_t)(sm[k] - 1) << 16);
+            }
         }
-        running += c.x + c.y + c.z + c.w;
+        running += c0 + c1 + c2 + c3;
     }
     if (threadIdx.x == 0) *cntOut = running;
 }
 
-void orbx_launch_fast(const OrbxParams& p, const void* cellTable, cudaStream_t s)
+void orbx_fast_geometry(const OrbxParams& p, int* boxW, int* rhMaxOut)
 {
     // largest ROI over the levels (ROI = cell + 6, src/ORBextractor.cc:797-808)
     int rwMax = 0, rhMax = 0;
@@ -235,12 +258,20 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, cudaStream_t s
         rwMax = p.lv[l].wCell + 6 > rwMax ? p.lv[l].wCell + 6 : rwMax;
         rhMax = p.lv[l].hCell + 6 > rhMax ? p.lv[l].hCell + 6 : rhMax;
     }
-    dim3 grid(p.cellsTotal, p.imgs);
     // tile columns: 3 (alignment) + ROI + 1, rounded up to whole words; strength-map columns: interior + 8
-    const int sa = rwMax + 8 <= 48 ? 48 : 80;
-    const size_t smem = (size_t)2 * rhMax * sa * 2 + (size_t)(rhMax - 4) * sa * 2;
+    *boxW = rwMax + 8 <= 48 ? 64 : 96;
+    *rhMaxOut = rhMax;
+}
+
+void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* levelMaps, cudaStream_t s)
+{
+    int boxW, rhMax;
+    orbx_fast_geometry(p, &boxW, &rhMax);
+    dim3 grid(p.cellsTotal, p.imgs);
+    const int sa = boxW == 64 ? 48 : 80;
+    const size_t smem = (size_t)((rhMax * boxW + 127) & ~127) + (size_t)2 * rhMax * sa * 2 + (size_t)(rhMax - 4) * sa * 2;
     if (sa == 48)
-        orbx_fast_kernel<48><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, rhMax);
+        orbx_fast_kernel<48><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax);
     else
-        orbx_fast_kernel<80><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, rhMax);
+        orbx_fast_kernel<80><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax);
 }

@@ -102,7 +102,8 @@ struct OrbxStereoParams {
 // tight [frame][rows][cols] images of one side -> pitched level 0 of image frame*per + side
 void orbx_launch_ingest(const OrbxParams& p, const uint8_t* src, int nFrames, int per, int side, cudaStream_t s);
 void orbx_launch_pyramid(const OrbxParams& p, const int* const* tabs, cudaStream_t s);
-void orbx_launch_fast(const OrbxParams& p, const void* cellTable, cudaStream_t s);
+void orbx_fast_geometry(const OrbxParams& p, int* boxW, int* rhMax);  // TMA box of the FAST kernel
+void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* levelMaps, cudaStream_t s);
 void orbx_launch_octree(const OrbxParams& p, const void* cellTable, cudaStream_t s);
 void orbx_launch_blur(const OrbxParams& p, const void* tileTable, int nTiles, const void* levelMaps, cudaStream_t s);
 void orbx_launch_describe(const OrbxParams& p, cudaStream_t s);
