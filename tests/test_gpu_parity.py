@@ -261,3 +261,40 @@ def test_full_size_batch_properties():
         s = np.float32(1.2) ** k["octave"]
         assert np.all(k["x"] / s >= 18.99) and np.all(k["y"] / s >= 18.99)
         assert np.all(np.diff(k["octave"]) >= 0)  # levels concatenated 0..7
+
+
+def test_cpp_shim_reference_signature(tmp_path):
+    """include/ORBextractorGPU.h (the C++ class with the reference's constructor/operator()/getters) driven like
+    Frame::Frame(stereo): two extractors on two std::threads, then ComputeStereoMatches — compiled here with g++."""
+    import subprocess
+
+    from orb_slam2_2021_b200._lib import KP_DTYPE
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "shim_main")
+    libdir = os.path.join(root, "orb_slam2_2021_b200")
+    subprocess.run(["g++", "-std=c++17", "-O2", "-o", exe, os.path.join(root, "tests", "cpp", "shim_main.cpp"), f"-L{libdir}", "-lorbx",
+                    f"-Wl,-rpath,{libdir}", "-lpthread"], check=True)
+    cfg = synth.CONFIGS["kitti"]
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    left, right = synth.stereo_pair(W, H, 321)
+    left.tofile(tmp_path / "l.raw")
+    right.tofile(tmp_path / "r.raw")
+    out = tmp_path / "out.bin"
+    subprocess.run([exe, str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), str(H), str(W), str(nf), repr(float(sf)), str(nl), str(ini),
+                    str(mn), repr(float(np.float32(bf))), repr(float(np.float32(bf / fx))), str(out)], check=True)
+    raw = out.read_bytes()
+    nL, nR = np.frombuffer(raw, np.int32, 2)
+    off = 8
+    kl = np.frombuffer(raw, KP_DTYPE, nL, off); off += 28 * nL
+    dl = np.frombuffer(raw, np.uint8, 32 * nL, off).reshape(-1, 32); off += 32 * nL
+    kr = np.frombuffer(raw, KP_DTYPE, nR, off); off += 28 * nR
+    dr = np.frombuffer(raw, np.uint8, 32 * nR, off).reshape(-1, 32); off += 32 * nR
+    ur = np.frombuffer(raw, np.float32, nL, off); off += 4 * nL
+    dp = np.frombuffer(raw, np.float32, nL, off)
+    ol, orr, okl, odl, okr, odr = oracle_pair(cfg, left, right)
+    assert_kps_equal(kl, okl, "shim/L")
+    assert_kps_equal(kr, okr, "shim/R")
+    assert np.array_equal(dl, odl) and np.array_equal(dr, odr)
+    our, odp = O.stereo_match(ol, orr, okl, odl, okr, odr, bf, bf / fx)
+    assert_stereo_equal(ur, dp, our, odp, "shim/stereo")
