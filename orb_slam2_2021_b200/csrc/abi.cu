@@ -277,9 +277,11 @@ extern "C" int orbx_batch_process(orbx_batch* b, const uint8_t* left, const uint
                                   int* nLeft, orbx_keypoint* kpsLeft, uint8_t* descLeft, int* nRight, orbx_keypoint* kpsRight,
                                   uint8_t* descRight, float* uRight, float* depth)
 {
-    TRY(orbx_batch_upload(b, left, right, nFrames));
-    TRY(orbx_batch_run(b, nFrames, mbf, mb, 0));
-    return orbx_batch_download(b, nFrames, nLeft, kpsLeft, descLeft, nRight, kpsRight, descRight, uRight, depth);
+    if (!b || nFrames < 1 || nFrames > b->maxFrames) return fail(ORBX_ERR_ARG, "bad frame count");
+    Engine::HostOutputs o{nLeft, kpsLeft, descLeft, nRight, kpsRight, descRight, uRight, depth};
+    // chunks of >= 16 frames keep every kernel's grid well above one wave while the copies of the neighbouring chunks overlap
+    const int chunk = nFrames >= 64 ? (nFrames + 7) / 8 : nFrames >= 32 ? 16 : nFrames;
+    return b->eng.processPipelined(left, right, nFrames, mbf, mb, o, chunk, g_err);
 }
 
 extern "C" int orbx_batch_stats(orbx_batch* b, int nFrames, long long* nLeft, long long* nRight, long long* nMatched)

@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(BL_WARPS * 32) orbx_blur_kernel(OrbxParams p, 
     __syncthreads();
     if (tid == 0) {
         orbx_mbar_expect_tx(&bar, BL_SH * BL_SW);
-        orbx_tma_load_3d(src, maps + t.level, x0 - BL_XH, y0 - 3, img, &bar);
+        orbx_tma_load_3d(src, maps + t.level, x0 - BL_XH, y0 - 3, img + p.imgBase, &bar);
     }
     orbx_mbar_wait(&bar, 0);
 

@@ -1,6 +1,7 @@
 // engine.cu — host side: extractor tables, level/cell/tile geometry, HBM buffers, launch sequence.
 #include "engine.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -173,7 +174,11 @@ void Engine::release()
     for (void* a : allocs) cudaFree(a);
     allocs.clear();
     if (stream) cudaStreamDestroy(stream);
-    stream = nullptr;
+    if (upStream) cudaStreamDestroy(upStream);
+    if (downStream) cudaStreamDestroy(downStream);
+    for (cudaEvent_t e : chunkEvents) cudaEventDestroy(e);
+    chunkEvents.clear();
+    stream = upStream = downStream = nullptr;
     bytesAllocated = 0;
 }
 
@@ -233,6 +238,8 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { err = "no CUDA device: liborbx has no CPU path"; return ORBX_ERR_CUDA; }
     TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
     TRY(orbx_check(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking), "cudaStreamCreate", err));
+    TRY(orbx_check(cudaStreamCreateWithFlags(&upStream, cudaStreamNonBlocking), "cudaStreamCreate", err));
+    TRY(orbx_check(cudaStreamCreateWithFlags(&downStream, cudaStreamNonBlocking), "cudaStreamCreate", err));
 
     const size_t n = (size_t)nImgs;
     TRY(dalloc(this, &P.img0, n * P.img0Stride + 64, "img0", err));
@@ -344,8 +351,7 @@ int Engine::runExtract(int nImgs, std::string& err)
 {
     if (nImgs < 1 || nImgs > maxImgs) { err = "bad image count"; return ORBX_ERR_ARG; }
     TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
-    OrbxParams p = P;
-    p.imgs = nImgs;
+    OrbxParams p = slice(0, nImgs);
     mark(0);
     orbx_launch_pyramid(p, resizeTabs.data(), stream);
     mark(1);
@@ -364,15 +370,100 @@ int Engine::runExtract(int nImgs, std::string& err)
 int Engine::runStereo(int nFrames, float mbf, float mb, std::string& err)
 {
     if (!stereo || nFrames < 1 || nFrames * 2 > maxImgs) { err = "bad stereo arguments"; return ORBX_ERR_ARG; }
-    OrbxParams p = P;
-    p.imgs = nFrames * 2;
-    OrbxStereoParams sp = SP;
-    sp.frames = nFrames; sp.mbf = mbf; sp.mb = mb;
-    orbx_launch_stereo(p, p, sp, stream);  // match + median; timed as one stage, the median cut is marked separately below
+    launchStereo(0, nFrames, mbf, mb, stream);
     mark(6);
     mark(7);
     if (profiling && profiledRuns < kMaxProfiledRuns) ++profiledRuns;
     return orbx_check(cudaGetLastError(), "stereo launch", err);
+}
+
+OrbxParams Engine::slice(int b, int nImgs) const
+{
+    OrbxParams p = P;
+    const size_t o = (size_t)b;
+    p.imgs = nImgs; p.imgBase = b;
+    p.img0 += o * P.img0Stride; p.pyr += o * P.pyrStride; p.blur += o * P.blurStride;
+    p.cellCnt += o * P.cellsTotal; p.cellKp += o * P.slotTotal;
+    p.candXY += o * P.candTotal; p.candRs += o * P.candTotal; p.label += o * P.candTotal;
+    p.keep += o * P.keepTotal; p.keepCnt += o * P.nlevels; p.candCnt += o * P.nlevels;
+    p.outKp = (uint8_t*)P.outKp + o * P.maxKp * 28; p.outDesc += o * P.maxKp * 32; p.outCnt += o;
+    return p;
+}
+
+void Engine::launchExtract(const OrbxParams& p, cudaStream_t s)
+{
+    orbx_launch_pyramid(p, resizeTabs.data(), s);
+    orbx_launch_fast(p, dCells, dFastMaps, s);
+    orbx_launch_octree(p, dCells, s);
+    orbx_launch_blur(p, dTiles, nTiles, dBlurMaps, s);
+    orbx_launch_describe(p, s);
+}
+
+void Engine::launchStereo(int f0, int nFrames, float mbf, float mb, cudaStream_t s)
+{
+    const OrbxParams p = slice(2 * f0, 2 * nFrames);
+    OrbxStereoParams sp = SP;
+    const size_t o = (size_t)f0;
+    sp.frames = nFrames; sp.mbf = mbf; sp.mb = mb;
+    sp.uRight += o * SP.maxKp; sp.depth += o * SP.maxKp; sp.sad += o * SP.maxKp; sp.nMatched += o;
+    sp.rsorted += o * SP.maxKp; sp.binStart += o * (rows + 1);
+    orbx_launch_stereo(p, p, sp, s);
+}
+
+// Chunked end-to-end pipeline: chunk c's images go up on `upStream` while chunk c-1 computes on `stream` and chunk
+// c-2's results come down on `downStream` (H2D and D2H use separate copy engines; PCIe is full duplex).
+int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFrames, float mbf, float mb, const HostOutputs& out,
+                             int chunkFrames, std::string& err)
+{
+    const int per = stereo ? 2 : 1;
+    if (nFrames < 1 || nFrames * per > maxImgs || !left || (stereo && !right)) { err = "bad process arguments"; return ORBX_ERR_ARG; }
+    TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
+    if (chunkFrames < 1) chunkFrames = nFrames;
+    const int nChunks = (nFrames + chunkFrames - 1) / chunkFrames;
+    while ((int)chunkEvents.size() < 2 * nChunks) {
+        cudaEvent_t e;
+        TRY(orbx_check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate", err));
+        chunkEvents.push_back(e);
+    }
+    const size_t tight = (size_t)rows * cols, Pk = (size_t)P.maxKp;
+    const size_t sideStride = tight * (maxImgs / per);
+    for (int c = 0; c < nChunks; ++c) {
+        const int f0 = c * chunkFrames, n = std::min(chunkFrames, nFrames - f0);
+        cudaEvent_t up = chunkEvents[2 * c], done = chunkEvents[2 * c + 1];
+        for (int side = 0; side < per; ++side) {
+            const uint8_t* src = (side ? right : left) + f0 * tight;
+            TRY(orbx_check(cudaMemcpyAsync(dStage + side * sideStride + f0 * tight, src, n * tight, cudaMemcpyHostToDevice, upStream), "H2D chunk", err));
+        }
+        TRY(orbx_check(cudaEventRecord(up, upStream), "event", err));
+        TRY(orbx_check(cudaStreamWaitEvent(stream, up, 0), "wait", err));
+        const OrbxParams p = slice(per * f0, per * n);
+        for (int side = 0; side < per; ++side)
+            orbx_launch_ingest(p, dStage + side * sideStride + f0 * tight, n, per, side, stream);
+        launchExtract(p, stream);
+        if (stereo) launchStereo(f0, n, mbf, mb, stream);
+        TRY(orbx_check(cudaGetLastError(), "chunk launch", err));
+        TRY(orbx_check(cudaEventRecord(done, stream), "event", err));
+        TRY(orbx_check(cudaStreamWaitEvent(downStream, done, 0), "wait", err));
+        auto rowsD2H = [&](void* dst, const void* src, size_t rowBytes, size_t devStride) -> int {
+            if (!dst) return ORBX_OK;
+            return orbx_check(cudaMemcpy2DAsync(dst, rowBytes, src, devStride, rowBytes, n, cudaMemcpyDeviceToHost, downStream), "D2H chunk", err);
+        };
+        const uint8_t* kp = (const uint8_t*)P.outKp + (size_t)per * f0 * Pk * 28;
+        const uint8_t* ds = P.outDesc + (size_t)per * f0 * Pk * 32;
+        const int* cn = P.outCnt + per * f0;
+        TRY(rowsD2H(out.nLeft ? out.nLeft + f0 : nullptr, cn, 4, per * 4));
+        TRY(rowsD2H(out.kpsLeft ? (uint8_t*)out.kpsLeft + f0 * Pk * 28 : nullptr, kp, Pk * 28, per * Pk * 28));
+        TRY(rowsD2H(out.descLeft ? out.descLeft + f0 * Pk * 32 : nullptr, ds, Pk * 32, per * Pk * 32));
+        if (stereo) {
+            TRY(rowsD2H(out.nRight ? out.nRight + f0 : nullptr, cn + 1, 4, per * 4));
+            TRY(rowsD2H(out.kpsRight ? (uint8_t*)out.kpsRight + f0 * Pk * 28 : nullptr, kp + Pk * 28, Pk * 28, per * Pk * 28));
+            TRY(rowsD2H(out.descRight ? out.descRight + f0 * Pk * 32 : nullptr, ds + Pk * 32, Pk * 32, per * Pk * 32));
+            TRY(rowsD2H(out.uRight ? out.uRight + f0 * Pk : nullptr, SP.uRight + f0 * Pk, Pk * 4, Pk * 4));
+            TRY(rowsD2H(out.depth ? out.depth + f0 * Pk : nullptr, SP.depth + f0 * Pk, Pk * 4, Pk * 4));
+        }
+    }
+    TRY(orbx_check(cudaStreamSynchronize(downStream), "down sync", err));
+    return orbx_check(cudaStreamSynchronize(stream), "stream sync", err);
 }
 
 int Engine::sync(std::string& err)

@@ -37,6 +37,18 @@ public:
     int uploadSingle(const uint8_t* img, size_t stride, std::string& err);
     int runExtract(int nImgs, std::string& err);                         // pyramid .. describe
     int runStereo(int nFrames, float mbf, float mb, std::string& err);   // both sides in this engine
+    // The same on images [imgBase, imgBase+nImgs) / frames [f0, f0+nFrames) only (chunked pipeline; no stage timing)
+    OrbxParams slice(int imgBase, int nImgs) const;
+    void launchExtract(const OrbxParams& p, cudaStream_t s);
+    void launchStereo(int f0, int nFrames, float mbf, float mb, cudaStream_t s);
+    // upload + run + download with H2D, kernels and D2H of successive frame chunks overlapped on three streams
+    struct HostOutputs {
+        int* nLeft; void* kpsLeft; uint8_t* descLeft; int* nRight; void* kpsRight; uint8_t* descRight; float* uRight; float* depth;
+    };
+    int processPipelined(const uint8_t* left, const uint8_t* right, int nFrames, float mbf, float mb, const HostOutputs& out,
+                         int chunkFrames, std::string& err);
+    cudaStream_t upStream = nullptr, downStream = nullptr;
+    std::vector<cudaEvent_t> chunkEvents;
     int sync(std::string& err);
 
     OrbxParams P{};          // device pointers + geometry (imgs = capacity)

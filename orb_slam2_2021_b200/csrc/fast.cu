@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         orbx_mbar_init(&bar, 1);
         orbx_fence_mbar_init();
         orbx_mbar_expect_tx(&bar, rhMax * BW);
-        orbx_tma_load_3d(T, maps + cell.level, cell.x0 & ~15, cell.y0, img, &bar);
+        orbx_tma_load_3d(T, maps + cell.level, cell.x0 & ~15, cell.y0, img + p.imgBase, &bar);
     }
     {
         uint32_t* z = reinterpret_cast<uint32_t*>(smap);

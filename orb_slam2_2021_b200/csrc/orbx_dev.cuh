@@ -46,6 +46,7 @@ struct OrbxParams {
     int nlevels, iniTh, minTh;
     int rows, cols;
     int imgs;  // images in this launch
+    int imgBase;  // index of image 0 of this launch inside the engine (buffer pointers are already advanced; TMA z needs it)
     OrbxLevel lv[ORBX_MAX_LEVELS];
     // per-image strides (elements of the respective type)
     size_t img0Stride, pyrStride, blurStride;
