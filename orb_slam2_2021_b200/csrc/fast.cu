@@ -115,6 +115,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     extern __shared__ __align__(128) uint8_t fast_smem[];
     __shared__ __align__(16) int warpCnt[FAST_MAX_ITERS][FAST_WARPS];
     __shared__ __align__(8) uint64_t bar;
+    __shared__ int listCnt;
 
     uint8_t* T = fast_smem;                                                     // raw box [rhMax][BW]
     uint16_t* A = reinterpret_cast<uint16_t*>(fast_smem + ((rhMax * BW + 127) & ~127));  // A[y][j] = I(xa + j, y0 + y), xa = x0 & ~3
@@ -133,6 +134,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) {
+        listCnt = 0;
         orbx_mbar_init(&bar, 1);
         orbx_fence_mbar_init();
         orbx_mbar_expect_tx(&bar, rhMax * BW);
@@ -166,28 +168,60 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     }
     __syncthreads();
 
-    // ---- strength map: lane = (pair lx, row ly) in an 8x4 patch; warp w owns rows 4w.. (+16 per step)
+    // ---- strength map, phase A: cheap necessary test on every pixel pair. Any 9 contiguous ring positions contain two
+    // ADJACENT compass points (0,4,8,12), so a corner at minTh needs (p0|p8)&(p4|p12) for "brighter" or for "darker".
+    // Lane = (pair lx, row ly) in an 8x4 patch (conflict-free LDS); survivors (~29 % on the synthetic scenes, far fewer on
+    // low-texture images) are appended to a task list that reuses the raw TMA tile.
     const int tmin = p.minTh, tini = p.iniTh;
+    // centre tile column of pair xp is c = o + 3 + 2*xp. The array whose pair at (c + dx) is word aligned serves
+    // dx: o even -> c odd: odd dx from A, even dx from B (at index c-1+dx); o odd -> c even: roles swap.
+    const uint16_t* podd = (o & 1) ? B + (o + 2) : A + (o + 3);
+    const uint16_t* pevn = (o & 1) ? A + (o + 3) : B + (o + 2);
+    uint16_t* list = reinterpret_cast<uint16_t*>(T);
     {
         const int lx = lane & 7, ly = lane >> 3;
         const int npairs = (iw + 1) >> 1;
-        // centre tile column of pair xp is c = o + 3 + 2*xp. The array whose pair at (c + dx) is word aligned serves
-        // dx: o even -> c odd: odd dx from A, even dx from B (at index c-1+dx); o odd -> c even: roles swap.
-        const uint16_t* podd = (o & 1) ? B + (o + 2) : A + (o + 3);
-        const uint16_t* pevn = (o & 1) ? A + (o + 3) : B + (o + 2);
+        const uint32_t cb = 0x7FFF7FFFu - 0x01000100u - 0x00010001u * (uint32_t)tmin;  // d' + cb has bit 15 set iff d' > 256 + t
+        const uint32_t cd = 0x80008000u + 0x00FF00FFu - 0x00010001u * (uint32_t)tmin;  // cd - d' has bit 15 set iff d' < 256 - t
 #pragma unroll 1
-        for (int y = warp * 4 + ly; y < ih; y += 4 * FAST_WARPS) {
-            const uint16_t* arow = podd + (y + 3) * SA;
-            const uint16_t* brow = pevn + (y + 3) * SA;
-            uint32_t* srow = reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + 2);
+        for (int y0 = warp * 4; y0 < ih; y0 += 4 * FAST_WARPS) {
+            const int y = y0 + ly;
 #pragma unroll 1
-            for (int xp = lx; xp < npairs; xp += 8) {
-                int m0, m1;
-                fast_strength2<SA>(arow + 2 * xp, brow + 2 * xp, m0, m1);
-                m0 = m0 > tmin ? m0 : 0;
-                m1 = (m1 > tmin && 2 * xp + 1 < iw) ? m1 : 0;
-                srow[xp] = (uint32_t)m0 | ((uint32_t)m1 << 16);
+            for (int x0 = 0; x0 < npairs; x0 += 8) {
+                const int xp = x0 + lx;
+                bool keep = false;
+                if (y < ih && xp < npairs) {
+                    const uint16_t* a = podd + (y + 3) * SA + 2 * xp;
+                    const uint16_t* b = pevn + (y + 3) * SA + 2 * xp;
+                    const uint32_t nc = 0x01000100u - *reinterpret_cast<const uint32_t*>(b);
+                    const uint32_t d0 = *reinterpret_cast<const uint32_t*>(b + 3 * SA) + nc, d8 = *reinterpret_cast<const uint32_t*>(b - 3 * SA) + nc;
+                    const uint32_t d4 = *reinterpret_cast<const uint32_t*>(a + 3) + nc, d12 = *reinterpret_cast<const uint32_t*>(a - 3) + nc;
+                    const uint32_t br = ((d0 + cb) | (d8 + cb)) & ((d4 + cb) | (d12 + cb));
+                    const uint32_t dk = ((cd - d0) | (cd - d8)) & ((cd - d4) | (cd - d12));
+                    keep = ((br | dk) & 0x80008000u) != 0;
+                }
+                const unsigned bal = __ballot_sync(0xffffffffu, keep);
+                if (bal) {
+                    int base = 0;
+                    if (lane == 0) base = atomicAdd(&listCnt, __popc(bal));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (keep) list[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)((y << 8) | xp);
+                }
             }
+        }
+    }
+    __syncthreads();
+    // ---- phase B: the min/max network on the surviving pairs only (order is irrelevant: results go to the map by position)
+    {
+        const int ntask = listCnt;
+#pragma unroll 1
+        for (int i = threadIdx.x; i < ntask; i += FAST_THREADS) {
+            const int task = list[i], y = task >> 8, xp = task & 255;
+            int m0, m1;
+            fast_strength2<SA>(podd + (y + 3) * SA + 2 * xp, pevn + (y + 3) * SA + 2 * xp, m0, m1);
+            m0 = m0 > tmin ? m0 : 0;
+            m1 = (m1 > tmin && 2 * xp + 1 < iw) ? m1 : 0;
+            *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + 2 + 2 * xp) = (uint32_t)m0 | ((uint32_t)m1 << 16);
         }
     }
     __syncthreads();

@@ -7,8 +7,8 @@
 // sy,(b0,b1) are precomputed on the host in float64/float32 exactly as OpenCV does, then
 //   H(r) = I[r][sx]*c0 + I[r][sx+1]*c1          (int, < 2^19)
 //   out  = (((b0*(H(sy)>>4))>>16) + ((b1*(H(sy+1)>>4))>>16) + 2) >> 2
-// HBM-bound: reads 1.44x and writes 1x the destination level; each thread produces 4 px (one
-// aligned 32-bit store), source taps come through L1.
+// Reads 1.44x and writes 1x the destination level; each thread produces 4 px x 16 rows (one aligned
+// 32-bit store per row), source taps come through L1.
 #include "orbx_dev.cuh"
 
 struct ResizeTab {
@@ -18,40 +18,68 @@ struct ResizeTab {
     const int* ycoef;  // [dh] b0 | b1<<16
 };
 
-__global__ void __launch_bounds__(256) orbx_resize_kernel(OrbxParams p, int l, ResizeTab t)
+#define RS_TX 32   // threads along x (4 columns each)
+#define RS_TY 4    // row chunks per CTA
+#define RS_ROWS 16  // destination rows per thread
+
+// A thread owns 4 adjacent destination columns and walks down RS_ROWS destination rows: the column
+// tables are read once, and a horizontally interpolated source row that serves two consecutive
+// destination rows (scale 1.2: most of them) is computed once and kept in registers. The row pattern
+// depends on y only, so the reuse test is warp-uniform.
+__global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(OrbxParams p, int l, ResizeTab t)
 {
     const OrbxLevel& D = p.lv[l];
     const int img = blockIdx.z;
-    const int x0 = (blockIdx.x * 32 + threadIdx.x) * 4;
-    const int y = blockIdx.y * 8 + threadIdx.y;
-    if (x0 >= D.w || y >= D.h) return;
+    const int x0 = (blockIdx.x * RS_TX + threadIdx.x) * 4;
+    if (x0 >= D.w) return;
     int sp;
     const uint8_t* src = orbx_level_ptr(p, img, l - 1, &sp);
     const int sw = p.lv[l - 1].w, sh = p.lv[l - 1].h;
-    const int yo = t.yofs[y];
-    const int sy0 = min(max(yo, 0), sh - 1), sy1 = min(max(yo + 1, 0), sh - 1);
-    const int yc = t.ycoef[y];
-    const int b0 = yc & 0xFFFF, b1 = yc >> 16;
-    const uint8_t* r0 = src + (size_t)sy0 * sp;
-    const uint8_t* r1 = src + (size_t)sy1 * sp;
-    uint32_t packed = 0;
+    int sx[4], sx1[4], c0[4], c1[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const int x = x0 + i;
-        if (x < D.w) {
-            const int sx = t.xofs[x];
-            const int sx1 = min(sx + 1, sw - 1);
-            const int xc = t.xcoef[x];
-            const int c0 = xc & 0xFFFF, c1 = xc >> 16;
-            const int h0 = r0[sx] * c0 + r0[sx1] * c1;
-            const int h1 = r1[sx] * c0 + r1[sx1] * c1;
-            int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-            v = min(max(v, 0), 255);
-            packed |= (uint32_t)v << (8 * i);
-        }
+        const int x = min(x0 + i, D.w - 1);  // columns past the level land in the row padding; keep their reads in range
+        sx[i] = t.xofs[x];
+        sx1[i] = min(sx[i] + 1, sw - 1);
+        const int xc = t.xcoef[x];
+        c0[i] = xc & 0xFFFF;
+        c1[i] = xc >> 16;
     }
-    uint8_t* dst = p.pyr + (size_t)img * p.pyrStride + D.off + (size_t)y * D.pitch;
-    *reinterpret_cast<uint32_t*>(dst + x0) = packed;  // pitch is a multiple of 16: in-row padding absorbs the tail
+    const int yBeg = (blockIdx.y * RS_TY + threadIdx.y) * RS_ROWS, yEnd = min(yBeg + RS_ROWS, D.h);
+    uint8_t* dst = p.pyr + (size_t)img * p.pyrStride + D.off + (size_t)yBeg * D.pitch + x0;
+    int hKeep[4] = {0, 0, 0, 0}, keepRow = -1;
+#pragma unroll 1
+    for (int y = yBeg; y < yEnd; ++y, dst += D.pitch) {
+        const int yo = t.yofs[y], yc = t.ycoef[y];
+        const int sy0 = min(max(yo, 0), sh - 1), sy1 = min(max(yo + 1, 0), sh - 1);
+        const int b0 = yc & 0xFFFF, b1 = yc >> 16;
+        int h0[4], h1[4];
+        if (sy0 == keepRow) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) h0[i] = hKeep[i];
+        } else {
+            const uint8_t* r = src + (size_t)sy0 * sp;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) h0[i] = r[sx[i]] * c0[i] + r[sx1[i]] * c1[i];
+        }
+        if (sy1 == sy0) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) h1[i] = h0[i];
+        } else {
+            const uint8_t* r = src + (size_t)sy1 * sp;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) h1[i] = r[sx[i]] * c0[i] + r[sx1[i]] * c1[i];
+        }
+        uint32_t packed = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int v = (((b0 * (h0[i] >> 4)) >> 16) + ((b1 * (h1[i] >> 4)) >> 16) + 2) >> 2;  // in [0,255]: b0 + b1 = 2048
+            packed |= (uint32_t)v << (8 * i);
+            hKeep[i] = h1[i];
+        }
+        keepRow = sy1;
+        *reinterpret_cast<uint32_t*>(dst) = packed;  // pitch is a multiple of 16: in-row padding absorbs the tail
+    }
 }
 
 // Level 0 ingest: tight rows (pitch = cols, any alignment) -> pitched rows (16-B multiple, TMA-legal).
@@ -90,7 +118,7 @@ void orbx_launch_pyramid(const OrbxParams& p, const int* const* tabs, cudaStream
         t.xcoef = t.xofs + D.w;
         t.yofs = t.xcoef + D.w;
         t.ycoef = t.yofs + D.h;
-        dim3 block(32, 8), grid((D.w + 127) / 128, (D.h + 7) / 8, p.imgs);
+        dim3 block(RS_TX, RS_TY), grid((D.w + 4 * RS_TX - 1) / (4 * RS_TX), (D.h + RS_ROWS * RS_TY - 1) / (RS_ROWS * RS_TY), p.imgs);
         orbx_resize_kernel<<<grid, block, 0, s>>>(p, l, t);
     }
 }
