@@ -113,7 +113,6 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     constexpr int BW = SA == 48 ? 64 : 96;      // TMA box width in bytes
     constexpr int WSLOT = SA == 48 ? 16 : 32;   // word slots per row in the widening pass
     extern __shared__ __align__(128) uint8_t fast_smem[];
-    __shared__ __align__(16) int warpCnt[FAST_MAX_ITERS][FAST_WARPS];
     __shared__ __align__(8) uint64_t bar;
     __shared__ int listCnt;
 
@@ -141,9 +140,9 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         orbx_tma_load_3d(T, maps + cell.level, cell.x0 & ~15, cell.y0, img + p.imgBase, &bar);
     }
     {
-        uint32_t* z = reinterpret_cast<uint32_t*>(smap);
-        const int nz = (ih + 2) * (SA / 2);
-        for (int i = threadIdx.x; i < nz; i += FAST_THREADS) z[i] = 0;
+        uint4* z = reinterpret_cast<uint4*>(smap);  // 16-byte aligned: 4*rhMax*SA bytes past A, SA % 8 == 0
+        const int nz = (ih + 2) * (SA / 8);
+        for (int i = threadIdx.x; i < nz; i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
     }
     __syncthreads();  // barrier initialised (and armed) before anybody polls it
     orbx_mbar_wait(&bar, 0);
@@ -170,19 +169,22 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
 
     // ---- strength map, phase A: cheap necessary test on every pixel pair. Any 9 contiguous ring positions contain two
     // ADJACENT compass points (0,4,8,12), so a corner at minTh needs (p0|p8)&(p4|p12) for "brighter" or for "darker".
-    // Lane = (pair lx, row ly) in an 8x4 patch (conflict-free LDS); survivors (~29 % on the synthetic scenes, far fewer on
-    // low-texture images) are appended to a task list that reuses the raw TMA tile.
+    // Lane = (pair lx, row ly) in an 8x4 patch (conflict-free LDS). Survivors (~29 % of the pairs on the synthetic
+    // scenes, far fewer on low-texture images) go to a WARP-PRIVATE task list in the (now free) raw tile: no atomics,
+    // and phases A and B of a warp need no CTA barrier between them.
     const int tmin = p.minTh, tini = p.iniTh;
     // centre tile column of pair xp is c = o + 3 + 2*xp. The array whose pair at (c + dx) is word aligned serves
     // dx: o even -> c odd: odd dx from A, even dx from B (at index c-1+dx); o odd -> c even: roles swap.
     const uint16_t* podd = (o & 1) ? B + (o + 2) : A + (o + 3);
     const uint16_t* pevn = (o & 1) ? A + (o + 3) : B + (o + 2);
-    uint16_t* list = reinterpret_cast<uint16_t*>(T);
+    const int npairs = (iw + 1) >> 1;
+    uint16_t* list = reinterpret_cast<uint16_t*>(T) + warp * (4 * ((ih + 15) >> 4) * npairs);
+    int ntask = 0;  // warp-uniform
     {
         const int lx = lane & 7, ly = lane >> 3;
-        const int npairs = (iw + 1) >> 1;
         const uint32_t cb = 0x7FFF7FFFu - 0x01000100u - 0x00010001u * (uint32_t)tmin;  // d' + cb has bit 15 set iff d' > 256 + t
         const uint32_t cd = 0x80008000u + 0x00FF00FFu - 0x00010001u * (uint32_t)tmin;  // cd - d' has bit 15 set iff d' < 256 - t
+        const unsigned lt = (1u << lane) - 1;
 #pragma unroll 1
         for (int y0 = warp * 4; y0 < ih; y0 += 4 * FAST_WARPS) {
             const int y = y0 + ly;
@@ -201,87 +203,74 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
                     keep = ((br | dk) & 0x80008000u) != 0;
                 }
                 const unsigned bal = __ballot_sync(0xffffffffu, keep);
-                if (bal) {
-                    int base = 0;
-                    if (lane == 0) base = atomicAdd(&listCnt, __popc(bal));
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (keep) list[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)((y << 8) | xp);
-                }
+                if (keep) list[ntask + __popc(bal & lt)] = (uint16_t)((y << 8) | xp);
+                ntask += __popc(bal);
             }
         }
     }
-    __syncthreads();
-    // ---- phase B: the min/max network on the surviving pairs only (order is irrelevant: results go to the map by position)
-    {
-        const int ntask = listCnt;
+    __syncwarp();
+    // ---- phase B: the min/max network on the warp's surviving pairs (results go to the map by position)
 #pragma unroll 1
-        for (int i = threadIdx.x; i < ntask; i += FAST_THREADS) {
-            const int task = list[i], y = task >> 8, xp = task & 255;
-            int m0, m1;
-            fast_strength2<SA>(podd + (y + 3) * SA + 2 * xp, pevn + (y + 3) * SA + 2 * xp, m0, m1);
-            m0 = m0 > tmin ? m0 : 0;
-            m1 = (m1 > tmin && 2 * xp + 1 < iw) ? m1 : 0;
-            *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + 2 + 2 * xp) = (uint32_t)m0 | ((uint32_t)m1 << 16);
-        }
+    for (int i = lane; i < ntask; i += 32) {
+        const int task = list[i], y = task >> 8, xp = task & 255;
+        int m0, m1;
+        fast_strength2<SA>(podd + (y + 3) * SA + 2 * xp, pevn + (y + 3) * SA + 2 * xp, m0, m1);
+        m0 = m0 > tmin ? m0 : 0;
+        m1 = (m1 > tmin && 2 * xp + 1 < iw) ? m1 : 0;
+        *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + 2 + 2 * xp) = (uint32_t)m0 | ((uint32_t)m1 << 16);
     }
     __syncthreads();
 
-    // ---- NMS once: 4 bits per step; quad i = step*128 + tid in row-major order, nq quads per row.
-    // Per (step, warp) the number of maxima above minTh and above iniTh goes to warpCnt (lo/hi 16 bits).
-    const int nq = (iw + 3) >> 2, nquads = nq * ih;
-    const int iters = (nquads + FAST_THREADS - 1) / FAST_THREADS;  // <= 8 (60x60 interior)
-    const float invq = __frcp_rn((float)nq);
-    unsigned isMax = 0, isIni = 0;
+    // ---- NMS, driven by the same task lists (only listed pairs can hold a corner): strict maximum over the 8
+    // neighbours in the strength map. Maxima go to a CTA list kept[] = key | m << 16, key = y*64 + x (interior coords).
+    uint32_t* kept = reinterpret_cast<uint32_t*>(A);  // A/B are dead after phase B
+    bool anyIni = false;
 #pragma unroll 1
-    for (int it = 0; it < iters; ++it) {
-        const int i = it * FAST_THREADS + threadIdx.x;
-        unsigned mx = 0, ini = 0;
-        if (i < nquads) {
-            const int y = (int)(((float)i + 0.5f) * invq), q = i - y * nq;
-            mx = nms_quad<SA>(smap + y * SA + 4 * q, tini, ini);
-            isMax |= mx << (4 * it);
-            isIni |= ini << (4 * it);
+    for (int i = lane; i < ntask; i += 32) {
+        const int task = list[i], y = task >> 8, xp = task & 255;
+        const uint16_t* c = smap + (y + 1) * SA + 2 + 2 * xp;  // centre pair, word aligned
+        const uint32_t mm = *reinterpret_cast<const uint32_t*>(c);
+        if (mm == 0) continue;
+        const uint32_t u0 = *reinterpret_cast<const uint32_t*>(c - SA - 2), u1 = *reinterpret_cast<const uint32_t*>(c - SA), u2 = *reinterpret_cast<const uint32_t*>(c - SA + 2);
+        const uint32_t l0 = *reinterpret_cast<const uint32_t*>(c - 2), l2 = *reinterpret_cast<const uint32_t*>(c + 2);
+        const uint32_t d0 = *reinterpret_cast<const uint32_t*>(c + SA - 2), d1 = *reinterpret_cast<const uint32_t*>(c + SA), d2 = *reinterpret_cast<const uint32_t*>(c + SA + 2);
+        // column maxima over the three rows, as pairs (x-2,x-1) (x,x+1) (x+2,x+3)
+        const uint32_t cm0 = __vimax3_u16x2(u0, l0, d0), cm1 = __vimax3_u16x2(u1, mm, d1), cm2 = __vimax3_u16x2(u2, l2, d2);
+        const uint32_t ud = __vimax3_u16x2(u1, d1, d1);
+        // neighbours of pixel 0 (x): columns x-1, x+1 (all rows) and rows above/below in column x; pixel 1 likewise
+        const int m0 = mm & 0xFFFFu, m1 = mm >> 16;
+        const int n0 = max(max((int)(cm0 >> 16), (int)(cm1 >> 16)), (int)(ud & 0xFFFFu));
+        const int n1 = max(max((int)(cm1 & 0xFFFFu), (int)(cm2 & 0xFFFFu)), (int)(ud >> 16));
+        if (m0 > n0) {
+            kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + 2 * xp) | ((uint32_t)m0 << 16);
+            anyIni |= m0 > tini;
         }
-        const unsigned packed = __reduce_add_sync(0xffffffffu, (unsigned)__popc(mx) | ((unsigned)__popc(ini) << 16));
-        if (lane == 0) warpCnt[it][warp] = (int)packed;
+        if (m1 > n1) {
+            kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + 2 * xp + 1) | ((uint32_t)m1 << 16);
+            anyIni |= m1 > tini;
+        }
     }
-    const bool useIni = __syncthreads_or(isIni != 0);  // :814 fallback to minTh iff FAST(ini) is empty; also publishes warpCnt
-    const unsigned sel = useIni ? isIni : isMax;
-    const int cshift = useIni ? 16 : 0;
+    const bool useIni = __syncthreads_or(anyIni);  // :814 fallback to minTh iff FAST(ini) is empty; also publishes kept[]
 
-    // ---- ordered (row-major) emission; a warp whose step holds no keypoint only advances the running count
+    // ---- ordered emission: rank of a selected maximum = number of selected maxima with a smaller row-major key
+    const int nkept = listCnt;
+    const int thr = useIni ? tini : 0;
     const uint32_t slot0 = L.slotBase + (uint32_t)(cellId - L.cellBase) * L.slotCap;
     uint32_t* out = p.cellKp + (size_t)img * p.slotTotal + slot0;
-    int running = 0;
 #pragma unroll 1
-    for (int it = 0; it < iters; ++it) {
-        const int4 c4 = *reinterpret_cast<const int4*>(warpCnt[it]);
-        const int c0 = (c4.x >> cshift) & 0xFFFF, c1 = (c4.y >> cshift) & 0xFFFF, c2 = (c4.z >> cshift) & 0xFFFF, c3 = (c4.w >> cshift) & 0xFFFF;
-        const int mine = warp == 0 ? c0 : warp == 1 ? c1 : warp == 2 ? c2 : c3;
-        if (mine) {  // warp-uniform
-            const unsigned k4 = (sel >> (4 * it)) & 15u;
-            // exclusive prefix of popc(k4) over the lanes
-            const int pc = __popc(k4);
-            int inc = pc;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const int t = __shfl_up_sync(0xffffffffu, inc, d);
-                if (lane >= d) inc += t;
-            }
-            if (k4) {
-                const int i = it * FAST_THREADS + threadIdx.x;
-                const int y = (int)(((float)i + 0.5f) * invq), q = i - y * nq;
-                int ofs = running + inc - pc + (warp > 0 ? c0 : 0) + (warp > 1 ? c1 : 0) + (warp > 2 ? c2 : 0);
-                const uint16_t* sm = smap + (y + 1) * SA + 4 * q + 2;
-                const uint32_t base = (uint32_t)(4 * q + 3) | ((uint32_t)(y + 3) << 8);
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (k4 & (1u << k)) out[ofs++] = (base + k) | ((uint32_t)(sm[k] - 1) << 16);
-            }
+    for (int i = threadIdx.x; i < nkept || i == 0; i += FAST_THREADS) {
+        const uint32_t e = i < nkept ? kept[i] : 0u;
+        const int key = e & 0xFFFFu, m = e >> 16;
+        int rank = 0, total = 0;
+        for (int j = 0; j < nkept; ++j) {
+            const uint32_t f = kept[j];
+            const bool sel = (int)(f >> 16) > thr;
+            total += sel;
+            rank += sel && (int)(f & 0xFFFFu) < key;
         }
-        running += c0 + c1 + c2 + c3;
+        if (i < nkept && m > thr) out[rank] = (uint32_t)((key & 63) + 3) | ((uint32_t)((key >> 6) + 3) << 8) | ((uint32_t)(m - 1) << 16);
+        if (i == 0) *cntOut = total;
     }
-    if (threadIdx.x == 0) *cntOut = running;
 }
 
 void orbx_fast_geometry(const OrbxParams& p, int* boxW, int* rhMaxOut)
