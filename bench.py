@@ -300,6 +300,15 @@ def ours_arm(args, rank, local_rank, world):
     top_ms = stages[top] / max(runs, 1)
     achieved = alg[top] / (top_ms / 1e3) / 1e9
     balg = b_alg_per_frame(W, H, nl, sf, n_l / F, n_r / F)
+    # DRAM traffic of the dominant stage per launch, from the committed ncu capture (profiles/), scaled to this batch
+    traffic, traffic_src = None, None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        if args.config == "kitti":
+            traffic = tj["stages"][top]["dram_bytes_per_frame"] * F
+            traffic_src = "profiles/r01_traffic.json (ncu dram__bytes_read+write per stereo frame x frames per launch)"
+    except Exception:
+        pass
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -314,7 +323,7 @@ def ours_arm(args, rank, local_rank, world):
                 "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": b.launches_per_run * args.steps,
         "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                      "alg_bytes_per_launch": alg[top], "ms_per_launch": top_ms,
                      "stage_ms_per_step": {k: v / max(runs, 1) for k, v in stages.items()},
                      "path": {"alg_bytes_per_frame": balg, "achieved": value / world * balg / 1e9,
