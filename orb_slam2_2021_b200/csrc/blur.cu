@@ -8,18 +8,19 @@
 // sums are exact, so the two 1-D passes may run in either order; here the VERTICAL pass runs first
 // because its sums (<= 65280) fit 16 bits and two pixels share one IMAD on a packed u16x2 register.
 //
-// One CTA per 96 x 64 output tile, all levels and images in one launch:
-//   * one thread issues a TMA box load (cp.async.bulk.tensor.3d, 128 x 70 x 1 u8, 8960 B) of the tile
-//     plus its halo (x0-16 .. x0+111, y0-3 .. y0+66; the copy engine addresses the innermost dimension
+// One CTA per 128 x 64 output tile, all levels and images in one launch:
+//   * one thread issues a TMA box load (cp.async.bulk.tensor.3d, 160 x 70 x 1 u8, 11200 B) of the tile
+//     plus its halo (x0-16 .. x0+143, y0-3 .. y0+66; the copy engine addresses the innermost dimension
 //     in 16-byte units, so the box starts 16 px left of the tile, measured with tools/ubench/tma_test2.cu)
 //     and the CTA waits on an mbarrier; the engine zero-fills what lies outside the level, and tiles on
 //     a level edge then mirror the reflect-101 halo in shared memory (columns first, then whole rows);
-//   * warp w owns output rows 8w..8w+7, lane L the four tile columns 4L..4L+3: it walks down 14 rows
-//     with a 7-row window of packed (u16x2) pixel pairs in registers (1 LDS.32 + 2 PRMT per 4 px per
-//     row), and the vertical sums are exchanged with the neighbouring lanes by warp shuffles, so no
-//     second shared-memory pass and no second barrier are needed; every lane produces 4 output pixels
-//     each for lanes 4..27 (one aligned 32-bit store, 96 B contiguous per warp and row).
-// HBM traffic: reads 1.46x the level (halo; mostly L2 hits between neighbouring tiles), writes it once.
+//   * warp w owns output rows 8w..8w+7, lane L the four output columns 4L..4L+3. It walks down 14 rows;
+//     per row the HORIZONTAL 7-tap sums of its 4 pixels come straight from the raw bytes of three
+//     32-bit words with 10 byte dot products (IDP.4A: measured full rate, on the FMA pipe, so no unpacking
+//     on the ALU pipe that bounds the other kernels); a 7-row register window of those sums feeds the
+//     vertical pass (4 IMAD + 3 IADD per pixel) and one aligned 32-bit store per lane and row
+//     (128 B contiguous per warp). No second shared-memory pass, no shuffles, every lane produces output.
+// HBM traffic: reads 1.37x the level (halo; mostly L2 hits between neighbouring tiles), writes it once.
 #include "orbx_dev.cuh"
 #include "orbx_tma.cuh"
 
@@ -31,7 +32,7 @@ struct OrbxTile {
 #define BL_WARPS 8
 #define BL_RS (ORBX_BLUR_TH / BL_WARPS)  // output rows per warp
 #define BL_SH (ORBX_BLUR_TH + 6)         // tile rows incl. halo
-#define BL_SW 128                        // tile columns incl. halo (TMA box width)
+#define BL_SW 160                        // tile columns incl. halo (TMA box width)
 #define BL_XH 16                         // columns left of the tile in the box
 
 __global__ void __launch_bounds__(BL_WARPS * 32) orbx_blur_kernel(OrbxParams p, const OrbxTile* tiles, const CUtensorMap* maps)
@@ -41,7 +42,7 @@ __global__ void __launch_bounds__(BL_WARPS * 32) orbx_blur_kernel(OrbxParams p, 
     const OrbxTile t = tiles[blockIdx.x];
     const int img = blockIdx.y, tid = threadIdx.x;
     const OrbxLevel& L = p.lv[t.level];
-    const int x0 = t.x0, y0 = t.y0, w = L.w, h = L.h;
+    const int x0 = t.x0, y0 = t.y0, w = L.w, h_ = L.h;
     if (tid == 0) {
         orbx_mbar_init(&bar, 1);
         orbx_fence_mbar_init();
@@ -54,7 +55,7 @@ __global__ void __launch_bounds__(BL_WARPS * 32) orbx_blur_kernel(OrbxParams p, 
     orbx_mbar_wait(&bar, 0);
 
     // ---- reflect-101 halo on level edges (tile column c <-> level column x0-16+c, row r <-> y0-3+r)
-    const bool edgeX = x0 == 0 || x0 + BL_SW - BL_XH > w, edgeY = y0 == 0 || y0 + BL_SH - 3 > h;
+    const bool edgeX = x0 == 0 || x0 + BL_SW - BL_XH > w, edgeY = y0 == 0 || y0 + BL_SH - 3 > h_;
     if (edgeX) {
         for (int i = tid; i < BL_SH * 6; i += BL_WARPS * 32) {
             const int r = i / 6, k = i - r * 6;
@@ -68,52 +69,50 @@ __global__ void __launch_bounds__(BL_WARPS * 32) orbx_blur_kernel(OrbxParams p, 
     }
     if (edgeX || edgeY) __syncthreads();
     if (edgeY) {
-        if (tid < 6 * 32) {
-            const int k = tid >> 5, c4 = tid & 31;
-            const int gy = k < 3 ? -(k + 1) : h + (k - 3);
+        for (int i = tid; i < 6 * (BL_SW / 4); i += BL_WARPS * 32) {
+            const int k = i / (BL_SW / 4), c4 = i - k * (BL_SW / 4);
+            const int gy = k < 3 ? -(k + 1) : h_ + (k - 3);
             const int r = gy - y0 + 3;
             if (r >= 0 && r < BL_SH) {
-                const int gs = gy < 0 ? -gy : 2 * (h - 1) - gy;
+                const int gs = gy < 0 ? -gy : 2 * (h_ - 1) - gy;
                 reinterpret_cast<uint32_t*>(src)[r * (BL_SW / 4) + c4] = reinterpret_cast<const uint32_t*>(src)[(gs - y0 + 3) * (BL_SW / 4) + c4];
             }
         }
         __syncthreads();
     }
 
-    // ---- vertical pass on packed pairs with a sliding 7-row window, horizontal pass through shuffles
+    // ---- horizontal pass by byte dot products, vertical pass over a sliding 7-row register window
     const int lane = tid & 31, warp = tid >> 5;
-    const uint32_t* col = reinterpret_cast<const uint32_t*>(src) + (warp * BL_RS) * (BL_SW / 4) + lane;
-    const int gx = x0 - BL_XH + 4 * lane;
-    const bool store = lane >= BL_XH / 4 && lane < (BL_XH + ORBX_BLUR_TW) / 4 && gx < w;
+    const uint32_t* col = reinterpret_cast<const uint32_t*>(src) + (warp * BL_RS) * (BL_SW / 4) + (BL_XH / 4 - 1) + lane;
+    const int gx = x0 + 4 * lane;
+    const bool store = gx < w;
     uint8_t* dst = p.blur + (size_t)img * p.blurStride + L.boff + (size_t)(y0 + warp * BL_RS) * L.bpitch + gx;
-    uint32_t wa[7], wb[7];  // window: pixel pairs (0,1) and (2,3) of the lane's 4 columns
+#define PK(a, b, c, d) ((uint32_t)(a) | ((uint32_t)(b) << 8) | ((uint32_t)(c) << 16) | ((uint32_t)(d) << 24))
+    uint32_t h[7][4];  // horizontal sums (<= 256*255) of the lane's 4 pixels, last 7 rows
 #pragma unroll
     for (int s = 0; s < BL_RS + 6; ++s) {
-        const uint32_t v = col[s * (BL_SW / 4)];
+        const uint32_t wm = col[s * (BL_SW / 4)], w0 = col[s * (BL_SW / 4) + 1], w1 = col[s * (BL_SW / 4) + 2];
 #pragma unroll
-        for (int k = 0; k < 6; ++k) { wa[k] = wa[k + 1]; wb[k] = wb[k + 1]; }
-        wa[6] = __byte_perm(v, 0, 0x4140);
-        wb[6] = __byte_perm(v, 0, 0x4342);
+        for (int k = 0; k < 6; ++k)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) h[k][i] = h[k + 1][i];
+        // pixel i of word w0 has its 7 taps at bytes i-3 .. i+3 relative to w0's byte 0
+        h[6][0] = __dp4a(w0, PK(56, 48, 34, 18), __dp4a(wm, PK(0, 18, 34, 48), 0u));
+        h[6][1] = __dp4a(w1, PK(18, 0, 0, 0), __dp4a(w0, PK(48, 56, 48, 34), __dp4a(wm, PK(0, 0, 18, 34), 0u)));
+        h[6][2] = __dp4a(w1, PK(34, 18, 0, 0), __dp4a(w0, PK(34, 48, 56, 48), __dp4a(wm, PK(0, 0, 0, 18), 0u)));
+        h[6][3] = __dp4a(w1, PK(48, 34, 18, 0), __dp4a(w0, PK(18, 34, 48, 56), 0u));
         if (s >= 6) {
-            // V = sum_j k_j I(y+j-3): per lane <= 256*255, no carry between the two 16-bit lanes
-            const uint32_t va = 18u * (wa[0] + wa[6]) + 34u * (wa[1] + wa[5]) + 48u * (wa[2] + wa[4]) + 56u * wa[3];
-            const uint32_t vb = 18u * (wb[0] + wb[6]) + 34u * (wb[1] + wb[5]) + 48u * (wb[2] + wb[4]) + 56u * wb[3];
-            const uint32_t la = __shfl_up_sync(0xffffffffu, va, 1), lb = __shfl_up_sync(0xffffffffu, vb, 1);
-            const uint32_t ra = __shfl_down_sync(0xffffffffu, va, 1), rb = __shfl_down_sync(0xffffffffu, vb, 1);
-            // columns -3 .. 6 relative to the lane's first pixel
-            const uint32_t cm3 = la >> 16, cm2 = lb & 0xFFFFu, cm1 = lb >> 16;
-            const uint32_t c0 = va & 0xFFFFu, c1 = va >> 16, c2 = vb & 0xFFFFu, c3 = vb >> 16;
-            const uint32_t c4 = ra & 0xFFFFu, c5 = ra >> 16, c6 = rb & 0xFFFFu;
-            const uint32_t s0 = 18u * (cm3 + c3) + 34u * (cm2 + c2) + 48u * (cm1 + c1) + 56u * c0 + 32768u;
-            const uint32_t s1 = 18u * (cm2 + c4) + 34u * (cm1 + c3) + 48u * (c0 + c2) + 56u * c1 + 32768u;
-            const uint32_t s2 = 18u * (cm1 + c5) + 34u * (c0 + c4) + 48u * (c1 + c3) + 56u * c2 + 32768u;
-            const uint32_t s3 = 18u * (c0 + c6) + 34u * (c1 + c5) + 48u * (c2 + c4) + 56u * c3 + 32768u;
+            uint32_t v[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                v[i] = 18u * (h[0][i] + h[6][i]) + 34u * (h[1][i] + h[5][i]) + 48u * (h[2][i] + h[4][i]) + 56u * h[3][i] + 32768u;
             // byte 2 of each sum (sums < 2^24)
-            const uint32_t packed = __byte_perm(__byte_perm(s0, s1, 0x0062), __byte_perm(s2, s3, 0x0062), 0x5410);
+            const uint32_t packed = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
             const int oy = s - 6;
-            if (store && y0 + warp * BL_RS + oy < h) *reinterpret_cast<uint32_t*>(dst + (size_t)oy * L.bpitch) = packed;
+            if (store && y0 + warp * BL_RS + oy < h_) *reinterpret_cast<uint32_t*>(dst + (size_t)oy * L.bpitch) = packed;
         }
     }
+#undef PK
 }
 
 void orbx_launch_blur(const OrbxParams& p, const void* tileTable, int nTiles, const void* levelMaps, cudaStream_t s)

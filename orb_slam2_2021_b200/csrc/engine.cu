@@ -297,7 +297,7 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     resizeTabs.assign(P.nlevels, nullptr);
     for (int l = 1; l < P.nlevels; ++l) resizeTabs[l] = dResizeTab + tabOff[l];
 
-    TRY(makeLevelMaps(128, ORBX_BLUR_TH + 6, &dBlurMaps, err));
+    TRY(makeLevelMaps(ORBX_BLUR_TW + 32, ORBX_BLUR_TH + 6, &dBlurMaps, err));
     {
         int bw, rh;
         orbx_fast_geometry(P, &bw, &rh);

@@ -22,7 +22,7 @@
 #define ORBX_MAX_LEVELS 12
 #define ORBX_EDGE 19
 #define ORBX_HALF_PATCH 15
-#define ORBX_BLUR_TW 96   // blur output tile (a 128 x 70 TMA box: 16 px left, 3 px above/below)
+#define ORBX_BLUR_TW 128  // blur output tile (a 160 x 70 TMA box: 16 px left and right, 3 px above/below)
 #define ORBX_BLUR_TH 64
 
 struct OrbxLevel {

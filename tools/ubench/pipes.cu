@@ -36,6 +36,13 @@ __global__ void __launch_bounds__(256) k(unsigned* out, unsigned seed, long long
             if (MODE == 13) a[i] = __vmaxu4(a[i], b[i]);
             if (MODE == 14) a[i] = __vcmpgtu4(a[i], b[i]);
             if (MODE == 15) a[i] = __vsub2(a[i], b[i]);
+            if (MODE == 16) a[i] = __dp4a(b[i], 0x03020100u, a[i]);
+            if (MODE == 17) { if (i & 1) a[i] = __vimin3_u16x2(a[i], b[i], c); else a[i] = __dp4a(b[i], 0x03020100u, a[i]); }
+            if (MODE == 18) { if (i & 1) a[i] = a[i] * 3u + b[i]; else a[i] = __dp4a(b[i], 0x03020100u, a[i]); }
+            if (MODE == 19) a[i] = __float_as_uint(__uint_as_float(a[i]) + 12582912.0f);
+            if (MODE == 20) a[i] = (unsigned)__float2int_rn(__uint_as_float(a[i] & 0x3fffffffu));
+            if (MODE == 21) a[i] = __vsadu4(a[i], b[i]);
+            if (MODE == 22) a[i] = __funnelshift_r(a[i], b[i], c);
         }
     }
     long long t1 = clock64();
@@ -81,5 +88,12 @@ int main()
     run<13>("vmaxu4", out, dcyc);
     run<14>("vcmpgtu4", out, dcyc);
     run<15>("vsub2", out, dcyc);
+    run<16>("dp4a", out, dcyc);
+    run<17>("dp4a + vimin3 mix", out, dcyc);
+    run<18>("dp4a + imad mix", out, dcyc);
+    run<19>("fadd", out, dcyc);
+    run<20>("f2i.rn", out, dcyc);
+    run<21>("vsadu4", out, dcyc);
+    run<22>("funnelshift", out, dcyc);
     return 0;
 }
