@@ -3,9 +3,12 @@
 // computeOrbDescriptor / computeDescriptors (:104-151, 1032-1039), the post-distribution fix-up
 // (:836-850) and the output assembly of operator() (:1070-1101).
 //
-//  * IC_Angle: lane u (-15..15) owns one column of the radius-15 disc on the UN-blurred level and
-//    accumulates u*I and v*I over the rows where |u| <= umax[|v|]; integer warp reduction gives
-//    m10, m01 exactly; angle = fastAtan2((float)m01, (float)m10) with OpenCV's polynomial.
+//  * both pixel neighbourhoods of a keypoint arrive by TMA box loads into the warp's shared-memory slice
+//    (un-blurred 48x31 box for the disc, blurred 64x37 box for the samples), signalled on a per-warp mbarrier;
+//  * IC_Angle: lane v (-15..15) owns one ROW of the radius-15 disc on the UN-blurred level: its span
+//    |u| <= umax[|v|] is realigned with funnel shifts and summed with byte dot products (IDP.4A) —
+//    sum(I) and sum(u*I) for 4 pixels per instruction; integer warp reduction gives m10, m01 exactly;
+//    angle = fastAtan2((float)m01, (float)m10) with OpenCV's polynomial.
 //  * rBRIEF: pair p = 32*j + lane; both sample points are rotated with the un-fused float
 //    expressions of :116-117 and rounded half-to-even, read from the BLURRED level; the ballot of
 //    "first < second" over the warp IS 32-bit word j of the descriptor (bit order of :119-148).
@@ -13,17 +16,29 @@
 //    mvScaleFactor[level] for level > 0 (:1093-1099), size = (int)(31*scale), class_id = -1.
 #include "orbx_dev.cuh"
 #include "orbx_pattern.h"
+#include "orbx_tma.cuh"
 
 __device__ const int8_t g_pattern[1024] = {ORBX_PATTERN_VALUES};
 __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
 
 #define DESC_WARPS 8
+#define DESC_P0_BYTES (ORBX_DESC_BOX0_W * ORBX_DESC_BOX0_H)  // 1488
+#define DESC_P1_BYTES (ORBX_DESC_BOX1_W * ORBX_DESC_BOX1_H)  // 2368
+#define DESC_P0_PITCH 1536                                   // 128-byte multiples per warp
+#define DESC_P1_PITCH 2432
 
-__global__ void __launch_bounds__(DESC_WARPS * 32) orbx_describe_kernel(OrbxParams p)
+// cvRound for |v| < 2^22: adding 1.5*2^23 in round-to-nearest-even leaves round-half-even(v) in the low mantissa
+// bits — the same result as __float2int_rn (orbx_cvround), but one FADD + IADD instead of an F2I on the slow XU pipe.
+__device__ __forceinline__ int cvround_small(float v) { return __float_as_int(__fadd_rn(v, 12582912.0f)) - 0x4B400000; }
+
+__global__ void __launch_bounds__(DESC_WARPS * 32) orbx_describe_kernel(OrbxParams p, const CUtensorMap* mapsPlain, const CUtensorMap* mapsBlur)
 {
+    __shared__ __align__(128) uint8_t patch0[DESC_WARPS * DESC_P0_PITCH];  // un-blurred disc boxes, row pitch 48
+    __shared__ __align__(128) uint8_t patch1[DESC_WARPS * DESC_P1_PITCH];  // blurred boxes, row pitch 64
+    __shared__ __align__(8) uint64_t bars[DESC_WARPS];
     const int img = blockIdx.y;
-    const int lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int slot = blockIdx.x * DESC_WARPS + warp;
     if (slot >= p.keepTotal) return;
     // slot -> (level, k)
     int level = 0;
@@ -40,24 +55,44 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) orbx_describe_kernel(OrbxPara
     const uint2 kp = p.keep[(size_t)img * p.keepTotal + slot];
     const int cx = (int)(kp.x & 0xFFFF) + (ORBX_EDGE - 3), cy = (int)(kp.x >> 16) + (ORBX_EDGE - 3);  // :843-844
 
-    // ---- IC_Angle on the un-blurred level
-    int pitch;
-    const uint8_t* im = orbx_level_ptr(p, img, level, &pitch);
-    const int u = lane - ORBX_HALF_PATCH;
+    // ---- both patches by TMA (the warp is the unit: its own mbarrier, no CTA barrier anywhere)
+    uint8_t* P0 = patch0 + warp * DESC_P0_PITCH;
+    uint8_t* P1 = patch1 + warp * DESC_P1_PITCH;
+    uint64_t* bar = bars + warp;
+    const int bx0 = (cx - ORBX_HALF_PATCH) & ~15, bx1 = (cx - 18) & ~15;
+    if (lane == 0) {
+        orbx_mbar_init(bar, 1);
+        orbx_fence_mbar_init();
+        orbx_mbar_expect_tx(bar, DESC_P0_BYTES + DESC_P1_BYTES);
+        orbx_tma_load_3d(P0, mapsPlain + level, bx0, cy - ORBX_HALF_PATCH, img + p.imgBase, bar);
+        orbx_tma_load_3d(P1, mapsBlur + level, bx1, cy - 18, img + p.imgBase, bar);
+    }
+    __syncwarp();
+    orbx_mbar_wait(bar, 0);
+
+    // ---- IC_Angle on the un-blurred level: lane = disc row v = lane-15, its contiguous span |u| <= umax[|v|].
+    // The span is realigned to byte 0 with funnel shifts; sum(I) and sum((u+umax)*I) are byte dot products (IDP.4A).
     int m10 = 0, m01 = 0;
-    if (lane < 31) {
-        const int au = abs(u);
-        const uint8_t* c = im + (size_t)cy * pitch + cx + u;
-        // fully unrolled: 31 independent loads in flight (the rolled loop was bound by load latency, ncu long_scoreboard)
-        int colSum = 0;
+    {
+        const int v = lane - ORBX_HALF_PATCH;
+        const int um = lane < 31 ? c_umax[v < 0 ? -v : v] : -1;  // lane 31: empty span
+        const int len8 = 8 * (2 * um + 1);                      // span length in bits of bytes
+        const int c0 = cx - ORBX_HALF_PATCH - bx0 + ORBX_HALF_PATCH - (um < 0 ? 0 : um);  // first span column in the box
+        const uint32_t* row = reinterpret_cast<const uint32_t*>(P0 + min(lane, 30) * ORBX_DESC_BOX0_W) + (c0 >> 2);
+        const int sh = (c0 & 3) * 8;
+        uint32_t w[9];
 #pragma unroll
-        for (int v = -ORBX_HALF_PATCH; v <= ORBX_HALF_PATCH; ++v) {
-            constexpr int kUmax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
-            const int I = au <= kUmax[v < 0 ? -v : v] ? (int)c[v * pitch] : 0;
-            colSum += I;
-            m01 += v * I;
+        for (int j = 0; j < 9; ++j) w[j] = row[j];  // may run into the next row / the pad: masked below
+        uint32_t accS = 0, accU = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint32_t mask = __funnelshift_lc(0xFFFFFFFFu, 0u, max(len8 - 32 * j, 0));  // low min(len-4j,4) bytes
+            const uint32_t x = __funnelshift_r(w[j], w[j + 1], sh) & mask;
+            accS = __dp4a(x, 0x01010101u, accS);
+            accU = __dp4a(x, 0x03020100u + 0x04040404u * j, accU);  // weight = byte index in the span = u + um
         }
-        m10 = u * colSum;
+        m10 = (int)accU - um * (int)accS;
+        m01 = v * (int)accS;
     }
 #pragma unroll
     for (int o = 16; o; o >>= 1) {
@@ -66,24 +101,23 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) orbx_describe_kernel(OrbxPara
     }
     const float angle = orbx_fast_atan2((float)m01, (float)m10);
 
-    // ---- rBRIEF on the blurred level
+    // ---- rBRIEF on the blurred level (samples from the shared-memory box: 32-bit addresses, no 64-bit pointer math)
     const float factorPI = (float)(3.14159265358979323846 / 180.f);
     float a, b;
     orbx_sincosf(orbx_fmul(angle, factorPI), &b, &a);
-    const uint8_t* bc = p.blur + (size_t)img * p.blurStride + L.boff + (size_t)cy * L.bpitch + cx;
-    const int step = L.bpitch;
+    const uint8_t* bc = P1 + 18 * ORBX_DESC_BOX1_W + (cx - bx1);  // centre of the box
     uint32_t myword = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const char4 pt = *reinterpret_cast<const char4*>(g_pattern + 4 * (32 * j + lane));
         const float x0 = (float)pt.x, y0 = (float)pt.y, x1 = (float)pt.z, y1 = (float)pt.w;
-        const int r0 = orbx_cvround(orbx_fadd(orbx_fmul(x0, b), orbx_fmul(y0, a)));
-        const int c0 = orbx_cvround(orbx_fsub(orbx_fmul(x0, a), orbx_fmul(y0, b)));
-        const int r1 = orbx_cvround(orbx_fadd(orbx_fmul(x1, b), orbx_fmul(y1, a)));
-        const int c1 = orbx_cvround(orbx_fsub(orbx_fmul(x1, a), orbx_fmul(y1, b)));
-        const int t0 = bc[r0 * step + c0], t1 = bc[r1 * step + c1];
-        const uint32_t w = __ballot_sync(0xffffffffu, t0 < t1);
-        if (lane == j) myword = w;
+        const int r0 = cvround_small(orbx_fadd(orbx_fmul(x0, b), orbx_fmul(y0, a)));
+        const int c0 = cvround_small(orbx_fsub(orbx_fmul(x0, a), orbx_fmul(y0, b)));
+        const int r1 = cvround_small(orbx_fadd(orbx_fmul(x1, b), orbx_fmul(y1, a)));
+        const int c1 = cvround_small(orbx_fsub(orbx_fmul(x1, a), orbx_fmul(y1, b)));
+        const int t0 = bc[r0 * ORBX_DESC_BOX1_W + c0], t1 = bc[r1 * ORBX_DESC_BOX1_W + c1];
+        const uint32_t wd = __ballot_sync(0xffffffffu, t0 < t1);
+        if (lane == j) myword = wd;
     }
     uint32_t* desc = reinterpret_cast<uint32_t*>(p.outDesc + ((size_t)img * p.maxKp + outIdx) * 32);
     if (lane < 8) desc[lane] = myword;
@@ -118,9 +152,9 @@ __global__ void orbx_count_kernel(OrbxParams p)
     p.outCnt[img] = total;
 }
 
-void orbx_launch_describe(const OrbxParams& p, cudaStream_t s)
+void orbx_launch_describe(const OrbxParams& p, const void* mapsPlain, const void* mapsBlur, cudaStream_t s)
 {
     orbx_count_kernel<<<(p.imgs + 127) / 128, 128, 0, s>>>(p);
     dim3 grid((p.keepTotal + DESC_WARPS - 1) / DESC_WARPS, p.imgs);
-    orbx_describe_kernel<<<grid, DESC_WARPS * 32, 0, s>>>(p);
+    orbx_describe_kernel<<<grid, DESC_WARPS * 32, 0, s>>>(p, (const CUtensorMap*)mapsPlain, (const CUtensorMap*)mapsBlur);
 }

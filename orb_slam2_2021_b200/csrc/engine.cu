@@ -201,7 +201,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-int Engine::makeLevelMaps(int boxW, int boxH, void** dMaps, std::string& err)
+int Engine::makeLevelMaps(int boxW, int boxH, bool blurred, void** dMaps, std::string& err)
 {
     void* fn = nullptr;
     cudaDriverEntryPointQueryResult q;
@@ -210,9 +210,10 @@ int Engine::makeLevelMaps(int boxW, int boxH, void** dMaps, std::string& err)
     std::vector<CUtensorMap> maps(P.nlevels);
     for (int l = 0; l < P.nlevels; ++l) {
         const OrbxLevel& L = P.lv[l];
-        void* base = l == 0 ? (void*)P.img0 : (void*)(P.pyr + L.off);
+        void* base = blurred ? (void*)(P.blur + L.boff) : l == 0 ? (void*)P.img0 : (void*)(P.pyr + L.off);
         const cuuint64_t dims[3] = {(cuuint64_t)L.w, (cuuint64_t)L.h, (cuuint64_t)maxImgs};
-        const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)(l == 0 ? P.img0Stride : P.pyrStride)};
+        const cuuint64_t strides[2] = {(cuuint64_t)(blurred ? L.bpitch : L.pitch),
+                                       (cuuint64_t)(blurred ? P.blurStride : l == 0 ? P.img0Stride : P.pyrStride)};
         const cuuint32_t box[3] = {(cuuint32_t)boxW, (cuuint32_t)boxH, 1u};
         const cuuint32_t es[3] = {1u, 1u, 1u};
         const CUresult r = ((EncodeTiledFn)fn)(&maps[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, es,
@@ -297,11 +298,13 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     resizeTabs.assign(P.nlevels, nullptr);
     for (int l = 1; l < P.nlevels; ++l) resizeTabs[l] = dResizeTab + tabOff[l];
 
-    TRY(makeLevelMaps(ORBX_BLUR_TW + 32, ORBX_BLUR_TH + 6, &dBlurMaps, err));
+    TRY(makeLevelMaps(ORBX_BLUR_TW + 32, ORBX_BLUR_TH + 6, false, &dBlurMaps, err));
+    TRY(makeLevelMaps(ORBX_DESC_BOX0_W, ORBX_DESC_BOX0_H, false, &dDescMaps0, err));
+    TRY(makeLevelMaps(ORBX_DESC_BOX1_W, ORBX_DESC_BOX1_H, true, &dDescMaps1, err));
     {
         int bw, rh;
         orbx_fast_geometry(P, &bw, &rh);
-        TRY(makeLevelMaps(bw, rh, &dFastMaps, err));
+        TRY(makeLevelMaps(bw, rh, false, &dFastMaps, err));
     }
 
     if (stereo) {
@@ -361,7 +364,7 @@ int Engine::runExtract(int nImgs, std::string& err)
     mark(3);
     orbx_launch_blur(p, dTiles, nTiles, dBlurMaps, stream);
     mark(4);
-    orbx_launch_describe(p, stream);
+    orbx_launch_describe(p, dDescMaps0, dDescMaps1, stream);
     mark(5);
     if (!stereo) { mark(6); mark(7); if (profiling && profiledRuns < kMaxProfiledRuns) ++profiledRuns; }
     return orbx_check(cudaGetLastError(), "extract launch", err);
@@ -396,7 +399,7 @@ void Engine::launchExtract(const OrbxParams& p, cudaStream_t s)
     orbx_launch_fast(p, dCells, dFastMaps, s);
     orbx_launch_octree(p, dCells, s);
     orbx_launch_blur(p, dTiles, nTiles, dBlurMaps, s);
-    orbx_launch_describe(p, s);
+    orbx_launch_describe(p, dDescMaps0, dDescMaps1, s);
 }
 
 void Engine::launchStereo(int f0, int nFrames, float mbf, float mb, cudaStream_t s)

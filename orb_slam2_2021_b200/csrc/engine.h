@@ -30,7 +30,7 @@ public:
 
     // level geometry without allocating anything (for orbx_max_keypoints)
     // TMA descriptors of the un-blurred levels with the given box (device array of nlevels CUtensorMap)
-    int makeLevelMaps(int boxW, int boxH, void** dMaps, std::string& err);
+    int makeLevelMaps(int boxW, int boxH, bool blurred, void** dMaps, std::string& err);
     static int plan(const ExtractorConfig& cfg, int rows, int cols, OrbxParams& p, std::string& err);
 
     int uploadImages(const uint8_t* left, const uint8_t* right, int nFrames, bool fromDevice, std::string& err);
@@ -63,6 +63,8 @@ public:
     int* dResizeTab = nullptr;
     uint8_t* dStage = nullptr;  // tight-row landing buffer of host uploads ([side][frame][rows*cols])
     void* dFastMaps = nullptr;  // same tensors, box = (64|96) x (largest cell ROI height) x 1
+    void* dDescMaps0 = nullptr;  // un-blurred levels, box 48 x 31 (IC_Angle disc)
+    void* dDescMaps1 = nullptr;  // BLURRED levels, box 64 x 37 (rBRIEF samples)
     void* dBlurMaps = nullptr;  // CUtensorMap[nlevels]: un-blurred level l as a (w, h, image) u8 tensor, box 128 x 70 x 1
     std::vector<const int*> resizeTabs;  // per level device pointers into dResizeTab
     std::vector<void*> allocs;

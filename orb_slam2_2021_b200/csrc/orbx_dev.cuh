@@ -24,6 +24,10 @@
 #define ORBX_HALF_PATCH 15
 #define ORBX_BLUR_TW 128  // blur output tile (a 160 x 70 TMA box: 16 px left and right, 3 px above/below)
 #define ORBX_BLUR_TH 64
+#define ORBX_DESC_BOX0_W 48  // describe: TMA box of the radius-15 disc ((cx-15)&15 + 31 <= 46 columns)
+#define ORBX_DESC_BOX0_H 31
+#define ORBX_DESC_BOX1_W 64  // describe: TMA box of the rotated pattern's reach, radius 18 ((cx-18)&15 + 37 <= 52 columns)
+#define ORBX_DESC_BOX1_H 37
 
 struct OrbxLevel {
     int w, h, pitch;      // level size; row pitch = align16(w) (level 0 lives in img0, levels >= 1 in pyr)
@@ -107,5 +111,5 @@ void orbx_fast_geometry(const OrbxParams& p, int* boxW, int* rhMax);  // TMA box
 void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* levelMaps, cudaStream_t s);
 void orbx_launch_octree(const OrbxParams& p, const void* cellTable, cudaStream_t s);
 void orbx_launch_blur(const OrbxParams& p, const void* tileTable, int nTiles, const void* levelMaps, cudaStream_t s);
-void orbx_launch_describe(const OrbxParams& p, cudaStream_t s);
+void orbx_launch_describe(const OrbxParams& p, const void* mapsPlain, const void* mapsBlur, cudaStream_t s);
 void orbx_launch_stereo(const OrbxParams& pl, const OrbxParams& pr, const OrbxStereoParams& sp, cudaStream_t s);
