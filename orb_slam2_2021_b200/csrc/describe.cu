@@ -18,7 +18,8 @@
 #include "orbx_pattern.h"
 #include "orbx_tma.cuh"
 
-__device__ const int8_t g_pattern[1024] = {ORBX_PATTERN_VALUES};
+// the 256 point pairs as float4 (x0, y0, x1, y1): one coalesced 16-byte load per lane, no I2F in the loop
+__device__ __align__(16) const float g_patternF[1024] = {ORBX_PATTERN_VALUES};
 __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
 
 #define DESC_WARPS 8
@@ -39,18 +40,15 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) orbx_describe_kernel(OrbxPara
     const int img = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int slot = blockIdx.x * DESC_WARPS + warp;
-    if (slot >= p.keepTotal) return;
-    // slot -> (level, k)
+    // slot -> (level, k): keepBase/keepCap are multiples of 8, so a CTA never straddles two levels (uniform search)
     int level = 0;
 #pragma unroll 1
     for (int l = 1; l < p.nlevels; ++l)
-        if (slot >= p.lv[l].keepBase) level = l;
+        if ((int)blockIdx.x * DESC_WARPS >= p.lv[l].keepBase) level = l;
     const OrbxLevel& L = p.lv[level];
     const int k = slot - L.keepBase;
-    const int* kc = p.keepCnt + img * p.nlevels;
-    if (k >= kc[level]) return;
-    int outIdx = k;
-    for (int l = 0; l < level; ++l) outIdx += kc[l];
+    if (k >= p.keepCnt[img * p.nlevels + level]) return;
+    const int outIdx = k + p.keepOfs[img * p.nlevels + level];
 
     const uint2 kp = p.keep[(size_t)img * p.keepTotal + slot];
     const int cx = (int)(kp.x & 0xFFFF) + (ORBX_EDGE - 3), cy = (int)(kp.x >> 16) + (ORBX_EDGE - 3);  // :843-844
@@ -105,17 +103,21 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) orbx_describe_kernel(OrbxPara
     const float factorPI = (float)(3.14159265358979323846 / 180.f);
     float a, b;
     orbx_sincosf(orbx_fmul(angle, factorPI), &b, &a);
-    const uint8_t* bc = P1 + 18 * ORBX_DESC_BOX1_W + (cx - bx1);  // centre of the box
+    // cvRound(v) = bits(v + 1.5*2^23) - 0x4B400000 (see cvround_small); the two constants of a (row, col) pair fold into
+    // the base address: row*64 + col = bits_r*64 + bits_c - 65*0x4B400000 (mod 2^32, like the 32-bit shared address)
+    const uint32_t bc = orbx_smem_addr(P1) + 18 * ORBX_DESC_BOX1_W + (cx - bx1) - 65u * 0x4B400000u;
+    const float4* pat = reinterpret_cast<const float4*>(g_patternF) + lane;
     uint32_t myword = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        const char4 pt = *reinterpret_cast<const char4*>(g_pattern + 4 * (32 * j + lane));
-        const float x0 = (float)pt.x, y0 = (float)pt.y, x1 = (float)pt.z, y1 = (float)pt.w;
-        const int r0 = cvround_small(orbx_fadd(orbx_fmul(x0, b), orbx_fmul(y0, a)));
-        const int c0 = cvround_small(orbx_fsub(orbx_fmul(x0, a), orbx_fmul(y0, b)));
-        const int r1 = cvround_small(orbx_fadd(orbx_fmul(x1, b), orbx_fmul(y1, a)));
-        const int c1 = cvround_small(orbx_fsub(orbx_fmul(x1, a), orbx_fmul(y1, b)));
-        const int t0 = bc[r0 * ORBX_DESC_BOX1_W + c0], t1 = bc[r1 * ORBX_DESC_BOX1_W + c1];
+        const float4 pt = pat[32 * j];
+        const uint32_t r0 = __float_as_uint(__fadd_rn(orbx_fadd(orbx_fmul(pt.x, b), orbx_fmul(pt.y, a)), 12582912.0f));
+        const uint32_t c0 = __float_as_uint(__fadd_rn(orbx_fsub(orbx_fmul(pt.x, a), orbx_fmul(pt.y, b)), 12582912.0f));
+        const uint32_t r1 = __float_as_uint(__fadd_rn(orbx_fadd(orbx_fmul(pt.z, b), orbx_fmul(pt.w, a)), 12582912.0f));
+        const uint32_t c1 = __float_as_uint(__fadd_rn(orbx_fsub(orbx_fmul(pt.z, a), orbx_fmul(pt.w, b)), 12582912.0f));
+        uint32_t t0, t1;
+        asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t0) : "r"(bc + r0 * ORBX_DESC_BOX1_W + c0));
+        asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t1) : "r"(bc + r1 * ORBX_DESC_BOX1_W + c1));
         const uint32_t wd = __ballot_sync(0xffffffffu, t0 < t1);
         if (lane == j) myword = wd;
     }
@@ -148,7 +150,10 @@ __global__ void orbx_count_kernel(OrbxParams p)
     const int img = blockIdx.x * blockDim.x + threadIdx.x;
     if (img >= p.imgs) return;
     int total = 0;
-    for (int l = 0; l < p.nlevels; ++l) total += p.keepCnt[img * p.nlevels + l];
+    for (int l = 0; l < p.nlevels; ++l) {
+        p.keepOfs[img * p.nlevels + l] = total;
+        total += p.keepCnt[img * p.nlevels + l];
+    }
     p.outCnt[img] = total;
 }
 

@@ -132,7 +132,7 @@ int Engine::plan(const ExtractorConfig& cfg, int rows, int cols, OrbxParams& p, 
         if (L.nIni < 1) { err = "portrait level: nIni == 0, the reference divides by zero here"; return ORBX_ERR_GEOMETRY; }
         L.hX = (float)bw / L.nIni;  // :548
         int cap = (L.quota > 4 * L.nIni ? L.quota : 4 * L.nIni) + 4;
-        L.keepCap = (cap + 3) & ~3;
+        L.keepCap = (cap + 7) & ~7;  // whole describe CTAs (8 warps = 8 slots) per level
         if (L.keepCap > 65000) { err = "per-level quota too large"; return ORBX_ERR_ARG; }
         L.keepBase = keepBase; keepBase += L.keepCap;
         L.scale = cfg.scale[l]; L.invScale = cfg.invScale[l];
@@ -255,6 +255,7 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     TRY(dalloc(this, &P.keep, n * P.keepTotal, "keep", err));
     TRY(dalloc(this, &P.keepCnt, n * P.nlevels, "keepCnt", err));
     TRY(dalloc(this, &P.candCnt, n * P.nlevels, "candCnt", err));
+    TRY(dalloc(this, &P.keepOfs, n * P.nlevels, "keepOfs", err));
     uint8_t* okp = nullptr;
     TRY(dalloc(this, &okp, n * P.maxKp * 28, "outKp", err));
     P.outKp = okp;
@@ -388,7 +389,7 @@ OrbxParams Engine::slice(int b, int nImgs) const
     p.img0 += o * P.img0Stride; p.pyr += o * P.pyrStride; p.blur += o * P.blurStride;
     p.cellCnt += o * P.cellsTotal; p.cellKp += o * P.slotTotal;
     p.candXY += o * P.candTotal; p.candRs += o * P.candTotal; p.label += o * P.candTotal;
-    p.keep += o * P.keepTotal; p.keepCnt += o * P.nlevels; p.candCnt += o * P.nlevels;
+    p.keep += o * P.keepTotal; p.keepCnt += o * P.nlevels; p.candCnt += o * P.nlevels; p.keepOfs += o * P.nlevels;
     p.outKp = (uint8_t*)P.outKp + o * P.maxKp * 28; p.outDesc += o * P.maxKp * 32; p.outCnt += o;
     return p;
 }

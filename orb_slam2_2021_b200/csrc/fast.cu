@@ -108,18 +108,19 @@ __device__ __forceinline__ unsigned nms_quad(const uint16_t* s, int tini, unsign
 }
 
 template <int SA>
-__global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax)
+__global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap)
 {
     constexpr int BW = SA == 48 ? 64 : 96;      // TMA box width in bytes
-    constexpr int WSLOT = SA == 48 ? 16 : 32;   // word slots per row in the widening pass
     extern __shared__ __align__(128) uint8_t fast_smem[];
     __shared__ __align__(8) uint64_t bar;
     __shared__ int listCnt;
+    __shared__ int warpTasks[FAST_WARPS];
 
     uint8_t* T = fast_smem;                                                     // raw box [rhMax][BW]
     uint16_t* A = reinterpret_cast<uint16_t*>(fast_smem + ((rhMax * BW + 127) & ~127));  // A[y][j] = I(xa + j, y0 + y), xa = x0 & ~3
-    uint16_t* B = A + rhMax * SA;                                                // B[y][j] = I(xa + j + 1, y0 + y)
-    uint16_t* smap = B + rhMax * SA;  // strength map: interior pixel (ix,iy) at [iy+1][ix+2], zero elsewhere
+    uint16_t* B = A + rhMax * SA;                                                // B[y][j] = I(xa + j - 1, y0 + y)
+    uint16_t* smap = B + rhMax * SA;  // strength map: interior pixel (ix,iy) at [iy+1][A-column + SD], zero elsewhere
+    uint16_t* lists = smap + (rhMax - 4) * SA;  // FAST_WARPS task lists of listCap entries
 
     const int cellId = blockIdx.x, img = blockIdx.y;
     const OrbxCell cell = cells[cellId];
@@ -147,88 +148,98 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     __syncthreads();  // barrier initialised (and armed) before anybody polls it
     orbx_mbar_wait(&bar, 0);
 
-    // ---- widen the raw bytes into the two u16 pair layouts
-    const int o = cell.x0 & 3;
-    {
-        const int nw = (o + rw + 4) >> 2;  // covers tile columns 0 .. o+rw (one past the ROI, read by odd-width pairs)
-        const uint32_t* T32 = reinterpret_cast<const uint32_t*>(T) + ((cell.x0 & 15) >> 2);
-        const int total = rh * WSLOT;
-#pragma unroll 1
-        for (int i = threadIdx.x; i < total; i += FAST_THREADS) {
-            const int y = i / WSLOT, j = i % WSLOT;
-            if (j < nw) {
-                const uint32_t w = T32[y * (BW / 4) + j];
-                const uint32_t wn = T32[y * (BW / 4) + j + 1];  // inside the box: (x0&15)/4 + nw + 1 <= BW/4
-                const uint32_t t = __funnelshift_r(w, wn, 8);
-                *reinterpret_cast<uint2*>(A + y * SA + 4 * j) = make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
-                *reinterpret_cast<uint2*>(B + y * SA + 4 * j) = make_uint2(__byte_perm(t, 0, 0x4140), __byte_perm(t, 0, 0x4342));
-            }
-        }
-    }
-    __syncthreads();
-
-    // ---- strength map, phase A: cheap necessary test on every pixel pair. Any 9 contiguous ring positions contain two
-    // ADJACENT compass points (0,4,8,12), so a corner at minTh needs (p0|p8)&(p4|p12) for "brighter" or for "darker".
-    // Lane = (pair lx, row ly) in an 8x4 patch (conflict-free LDS). Survivors (~29 % of the pairs on the synthetic
-    // scenes, far fewer on low-texture images) go to a WARP-PRIVATE task list in the (now free) raw tile: no atomics,
-    // and phases A and B of a warp need no CTA barrier between them.
+    // ---- pass 1 over the raw tile, one aligned 32-bit word (4 pixels) per thread and step:
+    //  (a) widen the bytes into the two u16 pair layouts A/B used by the min/max network;
+    //  (b) on interior words, a cheap NECESSARY test for "corner at minTh": any 9 contiguous ring positions contain two
+    //      ADJACENT compass points (0,4,8,12), so a corner needs (|d0|>t or |d8|>t) and (|d4|>t or |d12|>t). Four
+    //      VABSDIFF4 + a SWAR byte compare test 4 pixels at once; surviving pixel PAIRS (~30 % on the synthetic scenes,
+    //      far fewer on low-texture images) go to a WARP-PRIVATE task list (no atomics).
+    // Pairs are aligned to even tile columns, so even ring offsets always read A and odd ones B.
     const int tmin = p.minTh, tini = p.iniTh;
-    // centre tile column of pair xp is c = o + 3 + 2*xp. The array whose pair at (c + dx) is word aligned serves
-    // dx: o even -> c odd: odd dx from A, even dx from B (at index c-1+dx); o odd -> c even: roles swap.
-    const uint16_t* podd = (o & 1) ? B + (o + 2) : A + (o + 3);
-    const uint16_t* pevn = (o & 1) ? A + (o + 3) : B + (o + 2);
-    const int npairs = (iw + 1) >> 1;
-    uint16_t* list = reinterpret_cast<uint16_t*>(T) + warp * (4 * ((ih + 15) >> 4) * npairs);
+    const int o = cell.x0 & 3;
+    const int ca0 = o + 3;                        // A-column of interior pixel 0
+    const int SD = 2 + ((o + 1) & 1) - ca0;       // strength-map column = A-column + SD (even, keeps pairs word aligned)
+    uint16_t* list = lists + warp * listCap;
     int ntask = 0;  // warp-uniform
     {
-        const int lx = lane & 7, ly = lane >> 3;
-        const uint32_t cb = 0x7FFF7FFFu - 0x01000100u - 0x00010001u * (uint32_t)tmin;  // d' + cb has bit 15 set iff d' > 256 + t
-        const uint32_t cd = 0x80008000u + 0x00FF00FFu - 0x00010001u * (uint32_t)tmin;  // cd - d' has bit 15 set iff d' < 256 - t
+        const int nw = (o + rw + 4) >> 2;  // words covering A-columns 0 .. o+rw (one past the ROI, read by boundary pairs)
+        const uint32_t* T32 = reinterpret_cast<const uint32_t*>(T) + ((cell.x0 & 15) >> 2);
+        const int total = rh * nw;
+        const float invw = __frcp_rn((float)nw);
+        const uint32_t K = 0x01010101u * (uint32_t)(0x7F - min(tmin, 0x7F));
         const unsigned lt = (1u << lane) - 1;
+        const int steps = (total + FAST_THREADS - 1) / FAST_THREADS;
 #pragma unroll 1
-        for (int y0 = warp * 4; y0 < ih; y0 += 4 * FAST_WARPS) {
-            const int y = y0 + ly;
-#pragma unroll 1
-            for (int x0 = 0; x0 < npairs; x0 += 8) {
-                const int xp = x0 + lx;
-                bool keep = false;
-                if (y < ih && xp < npairs) {
-                    const uint16_t* a = podd + (y + 3) * SA + 2 * xp;
-                    const uint16_t* b = pevn + (y + 3) * SA + 2 * xp;
-                    const uint32_t nc = 0x01000100u - *reinterpret_cast<const uint32_t*>(b);
-                    const uint32_t d0 = *reinterpret_cast<const uint32_t*>(b + 3 * SA) + nc, d8 = *reinterpret_cast<const uint32_t*>(b - 3 * SA) + nc;
-                    const uint32_t d4 = *reinterpret_cast<const uint32_t*>(a + 3) + nc, d12 = *reinterpret_cast<const uint32_t*>(a - 3) + nc;
-                    const uint32_t br = ((d0 + cb) | (d8 + cb)) & ((d4 + cb) | (d12 + cb));
-                    const uint32_t dk = ((cd - d0) | (cd - d8)) & ((cd - d4) | (cd - d12));
-                    keep = ((br | dk) & 0x80008000u) != 0;
+        for (int st = 0; st < steps; ++st) {
+            const int i = st * FAST_THREADS + threadIdx.x;
+            bool k0 = false, k1 = false;
+            int y = 0, j = 0;
+            if (i < total) {
+                y = (int)(((float)i + 0.5f) * invw);
+                j = i - y * nw;
+                const uint32_t* tw = T32 + y * (BW / 4) + j;
+                const uint32_t w = tw[0], wn = tw[1], wp = tw[-1];  // inside the box: (x0&15)/4 + nw + 1 <= BW/4; tw[-1] of the
+                const uint32_t t = __funnelshift_r(wp, w, 24);     // first word is junk that only feeds masked pixels
+                *reinterpret_cast<uint2*>(A + y * SA + 4 * j) = make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
+                *reinterpret_cast<uint2*>(B + y * SA + 4 * j) = make_uint2(__byte_perm(t, 0, 0x4140), __byte_perm(t, 0, 0x4342));
+                const int iy = y - 3;
+                // pair q (A-columns 4j+2q, +1) holds an interior pixel iff 4j+2q+1 >= ca0 and 4j+2q < ca0+iw
+                const bool v0 = 4 * j + 1 >= ca0 && 4 * j < ca0 + iw, v1 = 4 * j + 3 >= ca0 && 4 * j + 2 < ca0 + iw;
+                if (iy >= 0 && iy < ih && (v0 || v1)) {
+                    uint32_t m = 0x80808080u;
+                    if (tmin < 0x7F) {  // (thresholds >= 127 skip the pre-test: every interior pair is a task)
+                        const uint32_t up = tw[-3 * (BW / 4)], dn = tw[3 * (BW / 4)];
+                        const uint32_t lf = __funnelshift_r(wp, w, 8), rt = __funnelshift_r(w, wn, 24);  // columns -3 / +3
+                        const uint32_t a0 = __vabsdiffu4(dn, w), a8 = __vabsdiffu4(up, w), a4 = __vabsdiffu4(rt, w), a12 = __vabsdiffu4(lf, w);
+                        // bit 7 of each byte of f(x) = ((x & 0x7F..) + K) | x is set iff x > t
+                        const uint32_t f0 = ((a0 & 0x7F7F7F7Fu) + K) | a0, f8 = ((a8 & 0x7F7F7F7Fu) + K) | a8;
+                        const uint32_t f4 = ((a4 & 0x7F7F7F7Fu) + K) | a4, f12 = ((a12 & 0x7F7F7F7Fu) + K) | a12;
+                        m = (f0 | f8) & (f4 | f12);
+                    }
+                    k0 = v0 && (m & 0x00008080u);
+                    k1 = v1 && (m & 0x80800000u);
                 }
-                const unsigned bal = __ballot_sync(0xffffffffu, keep);
-                if (keep) list[ntask + __popc(bal & lt)] = (uint16_t)((y << 8) | xp);
-                ntask += __popc(bal);
             }
+            const unsigned b0 = __ballot_sync(0xffffffffu, k0), b1 = __ballot_sync(0xffffffffu, k1);
+            const int n0 = __popc(b0);
+            if (k0) list[ntask + __popc(b0 & lt)] = (uint16_t)(((y - 3) << 8) | (2 * j));
+            if (k1) list[ntask + n0 + __popc(b1 & lt)] = (uint16_t)(((y - 3) << 8) | (2 * j + 1));
+            ntask += n0 + __popc(b1);
         }
     }
-    __syncwarp();
-    // ---- phase B: the min/max network on the warp's surviving pairs (results go to the map by position)
+    if (lane == 0) warpTasks[warp] = ntask;
+    __syncthreads();
+    // ---- pass 2: the min/max network on the surviving pairs (results go to the map by position). The four warp lists
+    // are walked as one sequence so that every warp step but the last is full.
+    const int nt0 = warpTasks[0], nt1 = nt0 + warpTasks[1], nt2 = nt1 + warpTasks[2], ntAll = nt2 + warpTasks[3];
+    {
+        const uint16_t* pevn = A;      // even dx: pair (A[c+dx], A[c+dx+1]), c even
+        const uint16_t* podd = B + 1;  // odd dx:  pair (B[c+dx+1], B[c+dx+2]) = (I(c+dx), I(c+dx+1))
 #pragma unroll 1
-    for (int i = lane; i < ntask; i += 32) {
-        const int task = list[i], y = task >> 8, xp = task & 255;
-        int m0, m1;
-        fast_strength2<SA>(podd + (y + 3) * SA + 2 * xp, pevn + (y + 3) * SA + 2 * xp, m0, m1);
-        m0 = m0 > tmin ? m0 : 0;
-        m1 = (m1 > tmin && 2 * xp + 1 < iw) ? m1 : 0;
-        *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + 2 + 2 * xp) = (uint32_t)m0 | ((uint32_t)m1 << 16);
+        for (int g = threadIdx.x; g < ntAll; g += FAST_THREADS) {
+            const int lw = (g >= nt0) + (g >= nt1) + (g >= nt2);
+            const int li = g - (lw == 0 ? 0 : lw == 1 ? nt0 : lw == 2 ? nt1 : nt2);
+            const int task = lists[lw * listCap + li], y = task >> 8, c = 2 * (task & 255);
+            int m0, m1;
+            fast_strength2<SA>(podd + (y + 3) * SA + c, pevn + (y + 3) * SA + c, m0, m1);
+            const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
+            m0 = (m0 > tmin && ix >= 0) ? m0 : 0;
+            m1 = (m1 > tmin && ix + 1 < iw) ? m1 : 0;
+            *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + c + SD) = (uint32_t)m0 | ((uint32_t)m1 << 16);
+        }
     }
     __syncthreads();
 
     // ---- NMS, driven by the same task lists (only listed pairs can hold a corner): strict maximum over the 8
     // neighbours in the strength map. Maxima go to a CTA list kept[] = key | m << 16, key = y*64 + x (interior coords).
-    uint32_t* kept = reinterpret_cast<uint32_t*>(A);  // A/B are dead after phase B
+    uint32_t* kept = reinterpret_cast<uint32_t*>(A);  // A/B are dead after pass 2
     bool anyIni = false;
 #pragma unroll 1
-    for (int i = lane; i < ntask; i += 32) {
-        const int task = list[i], y = task >> 8, xp = task & 255;
-        const uint16_t* c = smap + (y + 1) * SA + 2 + 2 * xp;  // centre pair, word aligned
+    for (int g = threadIdx.x; g < ntAll; g += FAST_THREADS) {
+        const int lw = (g >= nt0) + (g >= nt1) + (g >= nt2);
+        const int li = g - (lw == 0 ? 0 : lw == 1 ? nt0 : lw == 2 ? nt1 : nt2);
+        const int task = lists[lw * listCap + li], y = task >> 8, cc = 2 * (task & 255);
+        const uint16_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair, word aligned
         const uint32_t mm = *reinterpret_cast<const uint32_t*>(c);
         if (mm == 0) continue;
         const uint32_t u0 = *reinterpret_cast<const uint32_t*>(c - SA - 2), u1 = *reinterpret_cast<const uint32_t*>(c - SA), u2 = *reinterpret_cast<const uint32_t*>(c - SA + 2);
@@ -241,12 +252,13 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         const int m0 = mm & 0xFFFFu, m1 = mm >> 16;
         const int n0 = max(max((int)(cm0 >> 16), (int)(cm1 >> 16)), (int)(ud & 0xFFFFu));
         const int n1 = max(max((int)(cm1 & 0xFFFFu), (int)(cm2 & 0xFFFFu)), (int)(ud >> 16));
+        const int ix = cc - ca0;
         if (m0 > n0) {
-            kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + 2 * xp) | ((uint32_t)m0 << 16);
+            kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + ix) | ((uint32_t)m0 << 16);
             anyIni |= m0 > tini;
         }
         if (m1 > n1) {
-            kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + 2 * xp + 1) | ((uint32_t)m1 << 16);
+            kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + ix + 1) | ((uint32_t)m1 << 16);
             anyIni |= m1 > tini;
         }
     }
@@ -292,9 +304,13 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     orbx_fast_geometry(p, &boxW, &rhMax);
     dim3 grid(p.cellsTotal, p.imgs);
     const int sa = boxW == 64 ? 48 : 80;
-    const size_t smem = (size_t)((rhMax * boxW + 127) & ~127) + (size_t)2 * rhMax * sa * 2 + (size_t)(rhMax - 4) * sa * 2;
+    // per-warp task list: at most 2 pairs per thread and step of pass 1
+    const int nwMax = (3 + (sa == 48 ? 40 : 66) + 4) >> 2;
+    const int listCap = 64 * ((rhMax * nwMax + FAST_THREADS - 1) / FAST_THREADS);
+    const size_t smem = (size_t)((rhMax * boxW + 127) & ~127) + (size_t)2 * rhMax * sa * 2 + (size_t)(rhMax - 4) * sa * 2 +
+                        (size_t)FAST_WARPS * listCap * 2;
     if (sa == 48)
-        orbx_fast_kernel<48><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax);
+        orbx_fast_kernel<48><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax, listCap);
     else
-        orbx_fast_kernel<80><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax);
+        orbx_fast_kernel<80><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax, listCap);
 }

@@ -69,6 +69,7 @@ struct OrbxParams {
     uint2* keep;
     int* keepCnt;
     int* candCnt;  // [imgs][L] number of candidates per level (written by the quadtree kernel)
+    int* keepOfs;  // [imgs][L] exclusive prefix of keepCnt = first output index of a level (written by the count kernel)
     void* outKp;   // orbx_keypoint[imgs][maxKp]
     uint8_t* outDesc;
     int* outCnt;

@@ -21,10 +21,11 @@ __device__ __forceinline__ void orbx_mbar_init(uint64_t* bar, unsigned count)
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(orbx_smem_addr(bar)), "r"(count));
 }
 
-// make the barrier initialisation visible to the async (TMA) proxy
+// Make the barrier initialisation (a generic-proxy shared-memory write) visible to the async (TMA) proxy.
+// Deliberately NOT fence.mbarrier_init.release.cluster: no other CTA touches these barriers, and a
+// cluster-scope fence compiles to CCTL.IVALL, which invalidates the SM's whole L1 on every call (seen in ncu).
 __device__ __forceinline__ void orbx_fence_mbar_init()
 {
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
