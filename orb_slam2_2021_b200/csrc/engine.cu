@@ -176,9 +176,10 @@ void Engine::release()
     if (stream) cudaStreamDestroy(stream);
     if (upStream) cudaStreamDestroy(upStream);
     if (downStream) cudaStreamDestroy(downStream);
+    if (stream2) cudaStreamDestroy(stream2);
     for (cudaEvent_t e : chunkEvents) cudaEventDestroy(e);
     chunkEvents.clear();
-    stream = upStream = downStream = nullptr;
+    stream = stream2 = upStream = downStream = nullptr;
     bytesAllocated = 0;
 }
 
@@ -241,6 +242,7 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     TRY(orbx_check(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking), "cudaStreamCreate", err));
     TRY(orbx_check(cudaStreamCreateWithFlags(&upStream, cudaStreamNonBlocking), "cudaStreamCreate", err));
     TRY(orbx_check(cudaStreamCreateWithFlags(&downStream, cudaStreamNonBlocking), "cudaStreamCreate", err));
+    TRY(orbx_check(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking), "cudaStreamCreate", err));
 
     const size_t n = (size_t)nImgs;
     TRY(dalloc(this, &P.img0, n * P.img0Stride + 64, "img0", err));
@@ -439,14 +441,17 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
             TRY(orbx_check(cudaMemcpyAsync(dStage + side * sideStride + f0 * tight, src, n * tight, cudaMemcpyHostToDevice, upStream), "H2D chunk", err));
         }
         TRY(orbx_check(cudaEventRecord(up, upStream), "event", err));
-        TRY(orbx_check(cudaStreamWaitEvent(stream, up, 0), "wait", err));
+        // chunks alternate between two compute streams: the low-occupancy kernels of one chunk (quadtree, small
+        // pyramid levels) overlap with the wide kernels of the next
+        cudaStream_t cs = (c & 1) ? stream2 : stream;
+        TRY(orbx_check(cudaStreamWaitEvent(cs, up, 0), "wait", err));
         const OrbxParams p = slice(per * f0, per * n);
         for (int side = 0; side < per; ++side)
-            orbx_launch_ingest(p, dStage + side * sideStride + f0 * tight, n, per, side, stream);
-        launchExtract(p, stream);
-        if (stereo) launchStereo(f0, n, mbf, mb, stream);
+            orbx_launch_ingest(p, dStage + side * sideStride + f0 * tight, n, per, side, cs);
+        launchExtract(p, cs);
+        if (stereo) launchStereo(f0, n, mbf, mb, cs);
         TRY(orbx_check(cudaGetLastError(), "chunk launch", err));
-        TRY(orbx_check(cudaEventRecord(done, stream), "event", err));
+        TRY(orbx_check(cudaEventRecord(done, cs), "event", err));
         TRY(orbx_check(cudaStreamWaitEvent(downStream, done, 0), "wait", err));
         auto rowsD2H = [&](void* dst, const void* src, size_t rowBytes, size_t devStride) -> int {
             if (!dst) return ORBX_OK;
@@ -467,6 +472,7 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
         }
     }
     TRY(orbx_check(cudaStreamSynchronize(downStream), "down sync", err));
+    TRY(orbx_check(cudaStreamSynchronize(stream2), "stream sync", err));
     return orbx_check(cudaStreamSynchronize(stream), "stream sync", err);
 }
 

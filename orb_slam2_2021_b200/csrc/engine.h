@@ -47,7 +47,7 @@ public:
     };
     int processPipelined(const uint8_t* left, const uint8_t* right, int nFrames, float mbf, float mb, const HostOutputs& out,
                          int chunkFrames, std::string& err);
-    cudaStream_t upStream = nullptr, downStream = nullptr;
+    cudaStream_t upStream = nullptr, downStream = nullptr, stream2 = nullptr;
     std::vector<cudaEvent_t> chunkEvents;
     int sync(std::string& err);
 
