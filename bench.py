@@ -342,6 +342,11 @@ def ours_arm(args, rank, local_rank, world):
 
 
 def main():
+    # Keep stdout clean for the ONE JSON line: libraries (NCCL prints its version banner to stdout) write to fd 1,
+    # so fd 1 is pointed at stderr for the duration of the run and the line goes to the saved descriptor.
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -351,7 +356,8 @@ def main():
     else:
         line = ours_arm(args, rank, local_rank, world)
     if rank == 0 and line is not None:
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(saved_stdout, (json.dumps(line) + "\n").encode())
     if world > 1 and args.impl == "ours":
         import torch.distributed as dist
 
