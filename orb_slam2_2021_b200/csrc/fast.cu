@@ -15,20 +15,21 @@
 //
 // Blackwell mapping (measured with tools/ubench/pipes.cu: VIMNMX3.U16x2 issues at the same rate as a
 // 32-bit IMNMX, so packing two pixels per register halves the ALU-pipe work that bounds this kernel):
-//   * the ROI is staged in shared memory as 16-bit pixels, twice: A[y][x] = I(x,y) and
-//     B[y][x] = I(x+1,y). A thread owns two horizontally adjacent pixels; for every ring offset the
-//     pair (ring(x), ring(x+1)) is ONE aligned 32-bit LDS (from A for odd dx, from B for even dx)
-//     that is already a u16x2 vector — no byte extraction;
-//   * d'_k = ring_k + 256 - centre stays in [1,511] per lane, so the whole min/max network runs on
-//     unsigned u16x2 with the 3-input DPX instructions (__vimin3_u16x2 / __vimax3_u16x2):
-//     16+16 ops for the 9-windows and 8 for the reduction, per polarity, per pixel PAIR;
-//   * lanes are laid out 8 pairs x 4 rows with a row stride of 24 (or 40) words, which makes every
-//     ring load bank-conflict free;
 //   * the ROI arrives by ONE TMA box load (cp.async.bulk.tensor.3d, 64 or 96 columns starting at x0 & ~15 —
 //     the copy engine addresses the innermost dimension in 16-byte units — by rhMax rows) signalled on an
-//     mbarrier; a short shared-to-shared pass widens it into A/B (the tile keeps the x0&3 offset and the
-//     A/B roles swap with its parity); the strength map is kept as u16 so that NMS runs four pixels per
-//     thread on the same packed max instructions.
+//     mbarrier;
+//   * pass 1 walks the raw tile one aligned 32-bit word per thread: it widens the bytes into two 16-bit
+//     layouts, A[y][j] = I(xa+j, y) and B[y][j] = I(xa+j-1, y) (xa = x0 & ~3), and runs a byte-wise NECESSARY
+//     test for a corner at minTh on 4 pixels at once (VABSDIFF4 + SWAR compare against the compass points);
+//     surviving pixel PAIRS are appended to a warp-private task list by ballot (no atomics);
+//   * pass 2 runs the exact test on the listed pairs only. A thread owns two horizontally adjacent pixels
+//     (even tile column first); for every ring offset the pair (ring(x), ring(x+1)) is ONE aligned 32-bit
+//     LDS (from A for even dx, from B+1 for odd dx) that is already a u16x2 vector — no byte extraction;
+//     d'_k = ring_k + 256 - centre stays in [1,511] per lane, so the whole min/max network runs on unsigned
+//     u16x2 with the 3-input DPX instructions (__vimin3_u16x2 / __vimax3_u16x2): 16+16 ops for the
+//     9-windows and 8 for the reduction, per polarity, per pixel PAIR;
+//   * strengths go to a u16 map; NMS is driven by the same task lists and uses packed column maxima;
+//     maxima are collected in a CTA list and emitted at their row-major rank (the reference order).
 #include "orbx_dev.cuh"
 #include "orbx_tma.cuh"
 
@@ -40,12 +41,10 @@ struct OrbxCell {
 
 #define FAST_THREADS 128
 #define FAST_WARPS (FAST_THREADS / 32)
-#define FAST_MAX_ITERS 8   // 128-quad steps of one cell interior (<= 60x60 px = 900 quads)
-
-__device__ __forceinline__ int imax3(int a, int b, int c) { return max(a, max(b, c)); }
 
 // Corner strengths of the two pixels whose centre pair is *(u32*)b (see the layout note above).
-// a points at A[row][c] with c odd, b at B[row][c-1]; SA = row stride in u16 elements.
+// b points at the pair itself in A (even column c), a at B + 1 + the same offset, so that a[dx] for odd dx and
+// b[dx] for even dx are word aligned; SA = row stride in u16 elements.
 template <int SA>
 __device__ __forceinline__ void fast_strength2(const uint16_t* a, const uint16_t* b, int& m0, int& m1)
 {
@@ -82,29 +81,6 @@ __device__ __forceinline__ void fast_strength2(const uint16_t* a, const uint16_t
     // bright = br - 256, dark = dk - 256 (per lane); strength = max(bright, -dark)
     m0 = max((int)(br & 0xFFFFu) - 256, 256 - (int)(dk & 0xFFFFu));
     m1 = max((int)(br >> 16) - 256, 256 - (int)(dk >> 16));
-}
-
-// One interior pixel quad (4 consecutive pixels of one row) per thread and step: bit k of the result
-// = pixel k is a strict 3x3 maximum of the strength map; `ini` gets the subset above iniTh.
-// s points at smap[row y][col 4q] (u16, 8-byte aligned); MS = row stride in elements.
-template <int MS>
-__device__ __forceinline__ unsigned nms_quad(const uint16_t* s, int tini, unsigned& ini)
-{
-    const uint2 r0a = *reinterpret_cast<const uint2*>(s), r0b = *reinterpret_cast<const uint2*>(s + 4);
-    const uint2 r1a = *reinterpret_cast<const uint2*>(s + MS), r1b = *reinterpret_cast<const uint2*>(s + MS + 4);
-    const uint2 r2a = *reinterpret_cast<const uint2*>(s + 2 * MS), r2b = *reinterpret_cast<const uint2*>(s + 2 * MS + 4);
-    ini = 0;
-    if ((r1a.y | r1b.x) == 0) return 0;  // no corner among the four centres
-    const uint32_t cm0 = __vimax3_u16x2(r0a.x, r1a.x, r2a.x), cm1 = __vimax3_u16x2(r0a.y, r1a.y, r2a.y);
-    const uint32_t cm2 = __vimax3_u16x2(r0b.x, r1b.x, r2b.x), cm3 = __vimax3_u16x2(r0b.y, r1b.y, r2b.y);
-    const uint32_t L1 = __funnelshift_r(cm0, cm1, 16), R1 = __funnelshift_r(cm1, cm2, 16), R2 = __funnelshift_r(cm2, cm3, 16);
-    const uint32_t ud1 = __vimax3_u16x2(r0a.y, r2a.y, r2a.y), ud2 = __vimax3_u16x2(r0b.x, r2b.x, r2b.x);
-    const uint32_t nb1 = __vimax3_u16x2(L1, R1, ud1), nb2 = __vimax3_u16x2(R1, R2, ud2);
-    const int m0 = r1a.y & 0xFFFFu, m1 = r1a.y >> 16, m2 = r1b.x & 0xFFFFu, m3 = r1b.x >> 16;
-    const int n0 = nb1 & 0xFFFFu, n1 = nb1 >> 16, n2 = nb2 & 0xFFFFu, n3 = nb2 >> 16;
-    const unsigned mx = (m0 > n0 ? 1u : 0u) | (m1 > n1 ? 2u : 0u) | (m2 > n2 ? 4u : 0u) | (m3 > n3 ? 8u : 0u);
-    ini = mx & ((m0 > tini ? 1u : 0u) | (m1 > tini ? 2u : 0u) | (m2 > tini ? 4u : 0u) | (m3 > tini ? 8u : 0u));
-    return mx;
 }
 
 template <int SA>
