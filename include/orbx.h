@@ -112,7 +112,8 @@ int orbx_batch_process(orbx_batch* b, const uint8_t* left, const uint8_t* right,
                        orbx_keypoint* kps_right, uint8_t* desc_right, float* u_right, float* depth);
 /* The CUDA stream the engine launches on (cudaStream_t as void*), for event timing by the caller. */
 void* orbx_batch_stream(orbx_batch* b);
-/* Number of kernels one orbx_batch_run launches (for bench.py's gpu_launches). */
+/* Number of kernels the most recent orbx_batch_run launched (a batch of 32+ frames runs as 2 chunks on two streams;
+ * before any run: the launches of one chunk). For bench.py's gpu_launches. */
 int orbx_batch_launches_per_run(const orbx_batch* b);
 /* Per-stage device timing with CUDA events on the engine's stream (bench.py's roofline leg). While on,
  * every orbx_batch_run records events at the stage boundaries (up to 512 runs are kept);

@@ -1,5 +1,6 @@
 // abi.cu — the C-ABI of liborbx.so (declared in include/orbx.h). No CPU fallback anywhere: every
 // compute entry point needs a CUDA device and reports ORBX_ERR_CUDA otherwise.
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -221,7 +222,7 @@ extern "C" int orbx_batch_max_keypoints(const orbx_batch* b) { return b ? b->eng
 extern "C" void* orbx_batch_stream(orbx_batch* b) { return b ? (void*)b->eng.stream : nullptr; }
 extern "C" int orbx_batch_launches_per_run(const orbx_batch* b)
 {
-    return b ? b->eng.launchesPerExtract + (b->stereo ? 3 : 0) : ORBX_ERR_ARG;
+    return b ? (b->eng.launchesPerExtract + (b->stereo ? 3 : 0)) * b->eng.lastRunChunks : ORBX_ERR_ARG;
 }
 extern "C" long long orbx_batch_device_bytes(const orbx_batch* b) { return b ? (long long)b->eng.bytesAllocated : 0; }
 
@@ -237,11 +238,18 @@ extern "C" int orbx_batch_upload_device(orbx_batch* b, const void* left, const v
     return b->eng.uploadImages((const uint8_t*)left, (const uint8_t*)right, nFrames, true, g_err);
 }
 
+// chunks of a device-resident run (see Engine::runBatch); ORBX_RUN_CHUNKS overrides for experiments
+static int run_chunks(int nFrames)
+{
+    static const int forced = [] { const char* e = getenv("ORBX_RUN_CHUNKS"); return e ? atoi(e) : 0; }();
+    if (forced > 0) return forced;
+    return nFrames >= 32 ? 2 : 1;
+}
+
 extern "C" int orbx_batch_run(orbx_batch* b, int nFrames, float mbf, float mb, int sync)
 {
     if (!b || nFrames < 1 || nFrames > b->maxFrames) return fail(ORBX_ERR_ARG, "bad frame count");
-    TRY(b->eng.runExtract(nFrames * (b->stereo ? 2 : 1), g_err));
-    if (b->stereo) TRY(b->eng.runStereo(nFrames, mbf, mb, g_err));
+    TRY(b->eng.runBatch(nFrames, mbf, mb, run_chunks(nFrames), g_err));
     return sync ? b->eng.sync(g_err) : ORBX_OK;
 }
 

@@ -416,6 +416,39 @@ void Engine::launchStereo(int f0, int nFrames, float mbf, float mb, cudaStream_t
     orbx_launch_stereo(p, p, sp, s);
 }
 
+// Device-resident run of a whole batch as interleaved chunks on the two compute streams: the low-occupancy stages of
+// one chunk (quadtree, stereo search, top pyramid levels) fill the issue slots the wide stages of the other chunk leave
+// idle. `stream` forks to `stream2` and joins it again, so callers keep ordering and timing on `stream` alone.
+int Engine::runBatch(int nFrames, float mbf, float mb, int nChunks, std::string& err)
+{
+    const int per = stereo ? 2 : 1;
+    if (nFrames < 1 || nFrames * per > maxImgs) { err = "bad frame count"; return ORBX_ERR_ARG; }
+    lastRunChunks = 1;
+    if (profiling || nChunks < 2 || nFrames < 2 * nChunks) {  // per-stage events need the serial order
+        TRY(runExtract(nFrames * per, err));
+        return stereo ? runStereo(nFrames, mbf, mb, err) : ORBX_OK;
+    }
+    TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
+    while ((int)chunkEvents.size() < 2) {
+        cudaEvent_t e;
+        TRY(orbx_check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate", err));
+        chunkEvents.push_back(e);
+    }
+    TRY(orbx_check(cudaEventRecord(chunkEvents[0], stream), "event", err));
+    TRY(orbx_check(cudaStreamWaitEvent(stream2, chunkEvents[0], 0), "wait", err));
+    const int chunkFrames = (nFrames + nChunks - 1) / nChunks;
+    for (int c = 0, f0 = 0; f0 < nFrames; ++c, f0 += chunkFrames) {
+        const int n = std::min(chunkFrames, nFrames - f0);
+        cudaStream_t cs = (c & 1) ? stream2 : stream;
+        launchExtract(slice(per * f0, per * n), cs);
+        if (stereo) launchStereo(f0, n, mbf, mb, cs);
+    }
+    lastRunChunks = (nFrames + chunkFrames - 1) / chunkFrames;
+    TRY(orbx_check(cudaGetLastError(), "batch launch", err));
+    TRY(orbx_check(cudaEventRecord(chunkEvents[1], stream2), "event", err));
+    return orbx_check(cudaStreamWaitEvent(stream, chunkEvents[1], 0), "wait", err);
+}
+
 // Chunked end-to-end pipeline: chunk c's images go up on `upStream` while chunk c-1 computes on `stream` and chunk
 // c-2's results come down on `downStream` (H2D and D2H use separate copy engines; PCIe is full duplex).
 int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFrames, float mbf, float mb, const HostOutputs& out,

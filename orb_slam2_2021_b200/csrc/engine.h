@@ -37,6 +37,7 @@ public:
     int uploadSingle(const uint8_t* img, size_t stride, std::string& err);
     int runExtract(int nImgs, std::string& err);                         // pyramid .. describe
     int runStereo(int nFrames, float mbf, float mb, std::string& err);   // both sides in this engine
+    int runBatch(int nFrames, float mbf, float mb, int nChunks, std::string& err);  // extract (+ stereo), chunks on two streams
     // The same on images [imgBase, imgBase+nImgs) / frames [f0, f0+nFrames) only (chunked pipeline; no stage timing)
     OrbxParams slice(int imgBase, int nImgs) const;
     void launchExtract(const OrbxParams& p, cudaStream_t s);
@@ -49,6 +50,7 @@ public:
                          int chunkFrames, std::string& err);
     cudaStream_t upStream = nullptr, downStream = nullptr, stream2 = nullptr;
     std::vector<cudaEvent_t> chunkEvents;
+    int lastRunChunks = 1;  // chunks of the most recent runBatch (kernel launches = chunks x launches per chunk)
     int sync(std::string& err);
 
     OrbxParams P{};          // device pointers + geometry (imgs = capacity)

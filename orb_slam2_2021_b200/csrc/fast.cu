@@ -51,7 +51,7 @@ __device__ __forceinline__ void fast_strength2(const uint16_t* a, const uint16_t
 #define RING_A(dx, dy) (*reinterpret_cast<const uint32_t*>(a + (dy) * SA + (dx)))
 #define RING_B(dx, dy) (*reinterpret_cast<const uint32_t*>(b + (dy) * SA + (dx)))
     const uint32_t nc = 0x01000100u - RING_B(0, 0);  // 256 - centre per lane, in [1,256]: no borrow between lanes
-    uint32_t d[16];
+    uint32_t d[16];  // (ptxas issues these packed additions as IMAD.IADD on the FMA pipe, off the ALU pipe that bounds the kernel)
     d[0] = RING_B(0, 3) + nc;    d[1] = RING_A(1, 3) + nc;    d[2] = RING_B(2, 2) + nc;    d[3] = RING_A(3, 1) + nc;
     d[4] = RING_A(3, 0) + nc;    d[5] = RING_A(3, -1) + nc;   d[6] = RING_B(2, -2) + nc;   d[7] = RING_A(1, -3) + nc;
     d[8] = RING_B(0, -3) + nc;   d[9] = RING_A(-1, -3) + nc;  d[10] = RING_B(-2, -2) + nc; d[11] = RING_A(-3, -1) + nc;
@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     uint16_t* A = reinterpret_cast<uint16_t*>(fast_smem + ((rhMax * BW + 127) & ~127));  // A[y][j] = I(xa + j, y0 + y), xa = x0 & ~3
     uint16_t* B = A + rhMax * SA;                                                // B[y][j] = I(xa + j - 1, y0 + y)
     uint16_t* smap = B + rhMax * SA;  // strength map: interior pixel (ix,iy) at [iy+1][A-column + SD], zero elsewhere
-    uint16_t* lists = smap + (rhMax - 4) * SA;  // FAST_WARPS task lists of listCap entries
+    uint16_t* lists = smap + (rhMax - 4) * SA;  // 2 x FAST_WARPS lists of listCap entries: pass-1 tasks, then non-zero pairs
 
     const int cellId = blockIdx.x, img = blockIdx.y;
     const OrbxCell cell = cells[cellId];
@@ -141,7 +141,10 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         const int nw = (o + rw + 4) >> 2;  // words covering A-columns 0 .. o+rw (one past the ROI, read by boundary pairs)
         const uint32_t* T32 = reinterpret_cast<const uint32_t*>(T) + ((cell.x0 & 15) >> 2);
         const int total = rh * nw;
-        const float invw = __frcp_rn((float)nw);
+        // (row, word) of this thread's element, advanced by FAST_THREADS elements per step without a division
+        const int qStep = FAST_THREADS / nw, rStep = FAST_THREADS - qStep * nw;
+        int y = (int)(((float)threadIdx.x + 0.5f) * __frcp_rn((float)nw));
+        int j = threadIdx.x - y * nw;
         const uint32_t K = 0x01010101u * (uint32_t)(0x7F - min(tmin, 0x7F));
         const unsigned lt = (1u << lane) - 1;
         const int steps = (total + FAST_THREADS - 1) / FAST_THREADS;
@@ -149,10 +152,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         for (int st = 0; st < steps; ++st) {
             const int i = st * FAST_THREADS + threadIdx.x;
             bool k0 = false, k1 = false;
-            int y = 0, j = 0;
             if (i < total) {
-                y = (int)(((float)i + 0.5f) * invw);
-                j = i - y * nw;
                 const uint32_t* tw = T32 + y * (BW / 4) + j;
                 const uint32_t w = tw[0], wn = tw[1], wp = tw[-1];  // inside the box: (x0&15)/4 + nw + 1 <= BW/4; tw[-1] of the
                 const uint32_t t = __funnelshift_r(wp, w, 24);     // first word is junk that only feeds masked pixels
@@ -181,6 +181,9 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
             if (k0) list[ntask + __popc(b0 & lt)] = (uint16_t)(((y - 3) << 8) | (2 * j));
             if (k1) list[ntask + n0 + __popc(b1 & lt)] = (uint16_t)(((y - 3) << 8) | (2 * j + 1));
             ntask += n0 + __popc(b1);
+            j += rStep;
+            y += qStep;
+            if (j >= nw) { j -= nw; ++y; }
         }
     }
     if (lane == 0) warpTasks[warp] = ntask;
@@ -191,33 +194,48 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     {
         const uint16_t* pevn = A;      // even dx: pair (A[c+dx], A[c+dx+1]), c even
         const uint16_t* podd = B + 1;  // odd dx:  pair (B[c+dx+1], B[c+dx+2]) = (I(c+dx), I(c+dx+1))
+        uint16_t* nz = lists + (FAST_WARPS + warp) * listCap;  // this warp's list of pairs with a non-zero strength
+        int nnz = 0;                                           // warp-uniform
+        const unsigned lt = (1u << lane) - 1;
 #pragma unroll 1
-        for (int g = threadIdx.x; g < ntAll; g += FAST_THREADS) {
-            const int lw = (g >= nt0) + (g >= nt1) + (g >= nt2);
-            const int li = g - (lw == 0 ? 0 : lw == 1 ? nt0 : lw == 2 ? nt1 : nt2);
-            const int task = lists[lw * listCap + li], y = task >> 8, c = 2 * (task & 255);
-            int m0, m1;
-            fast_strength2<SA>(podd + (y + 3) * SA + c, pevn + (y + 3) * SA + c, m0, m1);
-            const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
-            m0 = (m0 > tmin && ix >= 0) ? m0 : 0;
-            m1 = (m1 > tmin && ix + 1 < iw) ? m1 : 0;
-            *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + c + SD) = (uint32_t)m0 | ((uint32_t)m1 << 16);
+        for (int g0 = warp * 32; g0 < ntAll; g0 += FAST_THREADS) {
+            const int g = g0 + lane;
+            bool hit = false;
+            int task = 0;
+            if (g < ntAll) {
+                const int lw = (g >= nt0) + (g >= nt1) + (g >= nt2);
+                const int li = g - (lw == 0 ? 0 : lw == 1 ? nt0 : lw == 2 ? nt1 : nt2);
+                task = lists[lw * listCap + li];
+                const int y = task >> 8, c = 2 * (task & 255);
+                int m0, m1;
+                fast_strength2<SA>(podd + (y + 3) * SA + c, pevn + (y + 3) * SA + c, m0, m1);
+                const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
+                m0 = (m0 > tmin && ix >= 0) ? m0 : 0;
+                m1 = (m1 > tmin && ix + 1 < iw) ? m1 : 0;
+                hit = (m0 | m1) != 0;
+                if (hit) *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + c + SD) = (uint32_t)m0 | ((uint32_t)m1 << 16);  // map is pre-zeroed
+            }
+            const unsigned bh = __ballot_sync(0xffffffffu, hit);
+            if (hit) nz[nnz + __popc(bh & lt)] = (uint16_t)task;
+            nnz += __popc(bh);
         }
+        __syncthreads();  // every warp is done reading warpTasks[] / lists of pass 1
+        if (lane == 0) warpTasks[warp] = nnz;
     }
     __syncthreads();
 
-    // ---- NMS, driven by the same task lists (only listed pairs can hold a corner): strict maximum over the 8
+    // ---- NMS over the pairs that hold a non-zero strength (second set of warp lists): strict maximum over the 8
     // neighbours in the strength map. Maxima go to a CTA list kept[] = key | m << 16, key = y*64 + x (interior coords).
     uint32_t* kept = reinterpret_cast<uint32_t*>(A);  // A/B are dead after pass 2
     bool anyIni = false;
+    const int nz0 = warpTasks[0], nz1 = nz0 + warpTasks[1], nz2 = nz1 + warpTasks[2], nzAll = nz2 + warpTasks[3];
 #pragma unroll 1
-    for (int g = threadIdx.x; g < ntAll; g += FAST_THREADS) {
-        const int lw = (g >= nt0) + (g >= nt1) + (g >= nt2);
-        const int li = g - (lw == 0 ? 0 : lw == 1 ? nt0 : lw == 2 ? nt1 : nt2);
-        const int task = lists[lw * listCap + li], y = task >> 8, cc = 2 * (task & 255);
+    for (int g = threadIdx.x; g < nzAll; g += FAST_THREADS) {
+        const int lw = (g >= nz0) + (g >= nz1) + (g >= nz2);
+        const int li = g - (lw == 0 ? 0 : lw == 1 ? nz0 : lw == 2 ? nz1 : nz2);
+        const int task = lists[(FAST_WARPS + lw) * listCap + li], y = task >> 8, cc = 2 * (task & 255);
         const uint16_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair, word aligned
         const uint32_t mm = *reinterpret_cast<const uint32_t*>(c);
-        if (mm == 0) continue;
         const uint32_t u0 = *reinterpret_cast<const uint32_t*>(c - SA - 2), u1 = *reinterpret_cast<const uint32_t*>(c - SA), u2 = *reinterpret_cast<const uint32_t*>(c - SA + 2);
         const uint32_t l0 = *reinterpret_cast<const uint32_t*>(c - 2), l2 = *reinterpret_cast<const uint32_t*>(c + 2);
         const uint32_t d0 = *reinterpret_cast<const uint32_t*>(c + SA - 2), d1 = *reinterpret_cast<const uint32_t*>(c + SA), d2 = *reinterpret_cast<const uint32_t*>(c + SA + 2);
@@ -284,7 +302,7 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     const int nwMax = (3 + (sa == 48 ? 40 : 66) + 4) >> 2;
     const int listCap = 64 * ((rhMax * nwMax + FAST_THREADS - 1) / FAST_THREADS);
     const size_t smem = (size_t)((rhMax * boxW + 127) & ~127) + (size_t)2 * rhMax * sa * 2 + (size_t)(rhMax - 4) * sa * 2 +
-                        (size_t)FAST_WARPS * listCap * 2;
+                        (size_t)2 * FAST_WARPS * listCap * 2;
     if (sa == 48)
         orbx_fast_kernel<48><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax, listCap);
     else

@@ -263,6 +263,33 @@ def test_full_size_batch_properties():
         assert np.all(np.diff(k["octave"]) >= 0)  # levels concatenated 0..7
 
 
+def test_device_resident_run_in_chunks():
+    """upload + run + download (a batch of >= 32 frames runs as interleaved chunks on two streams) gives the oracle's
+    results for every distinct frame, wherever the frame sits in the batch, including a ragged last chunk."""
+    cfg = synth.CONFIGS["arducam"]
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    base_l, base_r = synth.stereo_batch(W, H, 3, seed0=90)
+    n = 37  # 2 chunks of 19 and 18
+    idx = np.arange(n) % 3
+    L, R = np.ascontiguousarray(base_l[idx]), np.ascontiguousarray(base_r[idx])
+    b = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, 40, stereo=True)
+    b.upload(L, R)
+    b.run(n, bf, bf / fx)
+    out = b.download(n)
+    assert b.launches_per_run > 15  # more than one chunk's worth of kernels
+    ref = []
+    for k in range(3):
+        ol, orr, okl, odl, okr, odr = oracle_pair(cfg, base_l[k], base_r[k])
+        ref.append((okl, odl, okr, odr) + O.stereo_match(ol, orr, okl, odl, okr, odr, bf, bf / fx))
+    for f in range(n):
+        okl, odl, okr, odr, our, odp = ref[idx[f]]
+        nl_, nr_ = out["n_left"][f], out["n_right"][f]
+        assert_kps_equal(out["kps_left"][f][:nl_], okl, f"frame {f} L")
+        assert_kps_equal(out["kps_right"][f][:nr_], okr, f"frame {f} R")
+        assert np.array_equal(out["desc_left"][f][:nl_], odl) and np.array_equal(out["desc_right"][f][:nr_], odr)
+        assert_stereo_equal(out["u_right"][f][:nl_], out["depth"][f][:nl_], our, odp, f"frame {f}")
+
+
 def test_cpp_shim_reference_signature(tmp_path):
     """include/ORBextractorGPU.h (the C++ class with the reference's constructor/operator()/getters) driven like
     Frame::Frame(stereo): two extractors on two std::threads, then ComputeStereoMatches — compiled here with g++."""
