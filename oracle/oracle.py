@@ -173,3 +173,110 @@ def distribute(cand, min_x, max_x, min_y, max_y, n_target):
     out = np.zeros(cap, KP_DTYPE)
     n = lib().orc_distribute(_ptr(cand), len(cand), min_x, max_x, min_y, max_y, n_target, _ptr(out), cap)
     return out[:n]
+
+
+# ---- rows right after the hot path: oracle/frame.cpp --------------------------------
+
+class _OrcFrame(C.Structure):
+    _fields_ = [("n", C.c_int), ("keys_un", C.c_void_p), ("desc", C.c_void_p), ("u_right", C.c_void_p),
+                ("Tcw", C.c_float * 12), ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("mbf", C.c_float), ("mb", C.c_float), ("min_x", C.c_float), ("max_x", C.c_float),
+                ("min_y", C.c_float), ("max_y", C.c_float), ("scale_factors", C.c_void_p)]
+
+
+class _OrcMapPoints(C.Structure):
+    _fields_ = [("has_point", C.c_void_p), ("world_pos", C.c_void_p), ("point_desc", C.c_void_p),
+                ("observed", C.c_void_p)]
+
+
+class FrameView:
+    """What SearchByProjection / GetFeaturesInArea read from a Frame (see orc_frame in orb_oracle.h)."""
+
+    def __init__(self, keys_un, desc, u_right, Tcw, fx, fy, cx, cy, mbf, mb, bounds, scale_factors):
+        self.keys_un = np.ascontiguousarray(keys_un, dtype=KP_DTYPE)
+        self.desc = None if desc is None else np.ascontiguousarray(desc, dtype=np.uint8).reshape(-1, 32)
+        self.u_right = None if u_right is None else np.ascontiguousarray(u_right, dtype=np.float32)
+        self.Tcw = np.ascontiguousarray(np.asarray(Tcw, dtype=np.float32)[:3, :4])
+        self.scale_factors = np.ascontiguousarray(scale_factors, dtype=np.float32)
+        s = _OrcFrame()
+        s.n = len(self.keys_un)
+        s.keys_un = self.keys_un.ctypes.data
+        s.desc = None if self.desc is None else self.desc.ctypes.data
+        s.u_right = None if self.u_right is None else self.u_right.ctypes.data
+        s.Tcw[:] = [float(v) for v in self.Tcw.ravel()]
+        s.fx, s.fy, s.cx, s.cy, s.mbf, s.mb = fx, fy, cx, cy, mbf, mb
+        s.min_x, s.max_x, s.min_y, s.max_y = bounds
+        s.scale_factors = self.scale_factors.ctypes.data
+        self.c = s
+
+
+def _frame_sigs():
+    L = lib()
+    if getattr(L, "_frame_sigs_done", False):
+        return L
+    vp = C.c_void_p
+    L.orc_stereo_from_rgbd.argtypes = [vp, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_float, vp, vp]
+    L.orc_assign_features_to_grid.argtypes = [C.POINTER(_OrcFrame), vp, vp]
+    L.orc_features_in_area.argtypes = [C.POINTER(_OrcFrame), C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, vp, C.c_int]
+    L.orc_project.argtypes = [vp, vp, vp]
+    L.orc_tlc_z.argtypes = [vp, vp]
+    L.orc_tlc_z.restype = C.c_float
+    L.orc_search_by_projection.argtypes = [C.POINTER(_OrcFrame), C.POINTER(_OrcFrame), C.POINTER(_OrcMapPoints), C.c_float,
+                                           C.c_int, C.c_int, vp]
+    L._frame_sigs_done = True
+    return L
+
+
+def stereo_from_rgbd(keys, depth, mbf, keys_un_x=None):
+    """Frame::ComputeStereoFromRGBD -> (mvuRight, mvDepth)."""
+    keys = np.ascontiguousarray(keys, dtype=KP_DTYPE)
+    depth = np.ascontiguousarray(depth, dtype=np.float32)
+    n = len(keys)
+    ux = None if keys_un_x is None else np.ascontiguousarray(keys_un_x, dtype=np.float32)
+    ur, dp = np.zeros(max(n, 1), np.float32), np.zeros(max(n, 1), np.float32)
+    _frame_sigs().orc_stereo_from_rgbd(_ptr(keys), None if ux is None else _ptr(ux), n, _ptr(depth), depth.shape[0],
+                                       depth.shape[1], depth.strides[0] // 4, mbf, _ptr(ur), _ptr(dp))
+    return ur[:n], dp[:n]
+
+
+def assign_features_to_grid(frame):
+    """Frame::AssignFeaturesToGrid -> (cell_start[64*48+1], items); cell (ix, iy) at ix*48+iy."""
+    start = np.zeros(64 * 48 + 1, np.int32)
+    items = np.zeros(max(frame.c.n, 1), np.int32)
+    k = _frame_sigs().orc_assign_features_to_grid(C.byref(frame.c), _ptr(start), _ptr(items))
+    return start, items[:k]
+
+
+def features_in_area(frame, x, y, r, min_level=-1, max_level=-1):
+    out = np.zeros(max(frame.c.n, 1), np.int32)
+    k = _frame_sigs().orc_features_in_area(C.byref(frame.c), x, y, r, min_level, max_level, _ptr(out), len(out))
+    assert k >= 0
+    return out[:k]
+
+
+def project(Tcw, xw):
+    T = np.ascontiguousarray(np.asarray(Tcw, dtype=np.float32)[:3, :4])
+    xw = np.ascontiguousarray(xw, dtype=np.float32)
+    out = np.zeros(3, np.float32)
+    _frame_sigs().orc_project(_ptr(T), _ptr(xw), _ptr(out))
+    return out
+
+
+def tlc_z(Tcw, Tlw):
+    a = np.ascontiguousarray(np.asarray(Tcw, dtype=np.float32)[:3, :4])
+    b = np.ascontiguousarray(np.asarray(Tlw, dtype=np.float32)[:3, :4])
+    return float(_frame_sigs().orc_tlc_z(_ptr(a), _ptr(b)))
+
+
+def search_by_projection(cur, last, has_point, world_pos, point_desc, observed, th, b_mono=False, check_orientation=True):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) -> (match_of_cur[int32, cur.n], nmatches)."""
+    hp = np.ascontiguousarray(has_point, dtype=np.uint8)
+    wp = np.ascontiguousarray(world_pos, dtype=np.float32).reshape(-1, 3)
+    pd = np.ascontiguousarray(point_desc, dtype=np.uint8).reshape(-1, 32)
+    ob = np.ascontiguousarray(observed, dtype=np.uint8)
+    assert len(hp) == len(wp) == len(pd) == len(ob) == last.c.n
+    m = _OrcMapPoints(hp.ctypes.data, wp.ctypes.data, pd.ctypes.data, ob.ctypes.data)
+    out = np.full(max(cur.c.n, 1), -1, np.int32)
+    n = _frame_sigs().orc_search_by_projection(C.byref(cur.c), C.byref(last.c), C.byref(m), th, int(b_mono),
+                                               int(check_orientation), _ptr(out))
+    return out[:cur.c.n], n

@@ -81,6 +81,45 @@ int orc_reflect101(int p, int n);
 int orc_distribute(const orc_keypoint* cand, int n, int min_x, int max_x, int min_y, int max_y, int n_target,
                    orc_keypoint* out, int capacity);
 
+/* ---- rows right after the hot path, oracle/frame.cpp ---- */
+
+/* What ORBmatcher::SearchByProjection / Frame::GetFeaturesInArea read from a Frame. */
+typedef struct {
+    int n;                       /* Frame::N */
+    const orc_keypoint* keys_un; /* mvKeysUn (x, y, octave, angle are read) */
+    const uint8_t* desc;         /* mDescriptors, n x 32 (current frame only) */
+    const float* u_right;        /* mvuRight (current frame only; NULL = no stereo information) */
+    float Tcw[12];               /* rows 0..2 of mTcw: [R | t] */
+    float fx, fy, cx, cy, mbf, mb;
+    float min_x, max_x, min_y, max_y; /* mnMinX, mnMaxX, mnMinY, mnMaxY */
+    const float* scale_factors;  /* mvScaleFactors */
+} orc_frame;
+
+/* Per keypoint i of the LAST frame: its map point, as far as SearchByProjection reads it. */
+typedef struct {
+    const uint8_t* has_point;  /* mvpMapPoints[i] != NULL && !mvbOutlier[i] */
+    const float* world_pos;    /* n x 3, MapPoint::GetWorldPos() */
+    const uint8_t* point_desc; /* n x 32, MapPoint::GetDescriptor() */
+    const uint8_t* observed;   /* MapPoint::Observations() > 0 */
+} orc_mappoints;
+
+/* Frame::ComputeStereoFromRGBD, src/Frame.cc:702-723. keys_un_x may be NULL (no distortion: mvKeysUn == mvKeys).
+ * Keypoints outside the depth image are left at -1 (the reference would read out of bounds). Returns #valid. */
+int orc_stereo_from_rgbd(const orc_keypoint* keys, const float* keys_un_x, int n, const float* depth, int rows, int cols,
+                         int stride_floats, float mbf, float* u_right, float* depth_out);
+/* Frame::AssignFeaturesToGrid, src/Frame.cc:279-294: CSR form of mGrid, cell (ix, iy) at index ix*48+iy. */
+int orc_assign_features_to_grid(const orc_frame* f, int* cell_start, int* cell_items);
+/* Frame::GetFeaturesInArea, src/Frame.cc:376-433. Returns the count or -1 if capacity is too small. */
+int orc_features_in_area(const orc_frame* f, float x, float y, float r, int min_level, int max_level, int* out, int capacity);
+/* x3Dc = Rcw * x3Dw + tcw with OpenCV's 32-bit gemm arithmetic (src/ORBmatcher.cc:1381-1382) */
+void orc_project(const float* Tcw, const float* xw, float* xc);
+float orc_tlc_z(const float* Tcw, const float* Tlw);
+/* ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono), src/ORBmatcher.cc:1348-1491, with
+ * CurrentFrame.mvpMapPoints all NULL on entry (src/Tracking.cc:897). match_of_cur[i2] = index of the last-frame
+ * keypoint whose map point ends up in CurrentFrame.mvpMapPoints[i2], or -1. Returns nmatches. */
+int orc_search_by_projection(const orc_frame* cur, const orc_frame* last, const orc_mappoints* mp, float th, int b_mono,
+                             int check_orientation, int* match_of_cur);
+
 #ifdef __cplusplus
 }
 #endif

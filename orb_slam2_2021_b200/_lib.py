@@ -35,7 +35,7 @@ def build(force=False):
 
 _lib = None
 
-# name -> (restype, argtypes); the complete export list of include/orbx.h
+# name -> (restype, argtypes); the complete export list of include/orbx.h and include/orbx_frame.h
 _vp, _i, _f, _sz, _ll = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_longlong
 _ip = C.POINTER(C.c_int)
 SIGNATURES = {
@@ -71,6 +71,13 @@ SIGNATURES = {
     "orbx_batch_level_size": (_i, [_vp, _i, _ip, _ip]),
     "orbx_batch_level": (_i, [_vp, _i, _i, _i, _i, _vp, _sz]),
     "orbx_batch_candidates": (_i, [_vp, _i, _i, _i, _vp, _i, _ip]),
+    # include/orbx_frame.h
+    "orbx_matcher_create": (_i, [_i, C.POINTER(_vp)]),
+    "orbx_matcher_destroy": (None, [_vp]),
+    "orbx_stereo_from_rgbd": (_i, [_vp, _vp, _vp, _i, _vp, _i, _i, _sz, _f, _vp, _vp]),
+    "orbx_assign_features_to_grid": (_i, [_vp, _vp, _vp, _vp, _ip]),
+    "orbx_get_features_in_area": (_i, [_vp, _vp, _f, _f, _f, _i, _i, _vp, _i, _ip]),
+    "orbx_search_by_projection": (_i, [_vp, _vp, _vp, _vp, _i, _f, _i, _i, _vp, _vp]),
 }
 
 

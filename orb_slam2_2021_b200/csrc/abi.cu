@@ -11,6 +11,7 @@
 static thread_local std::string g_err;
 #define TRY(x) do { int rc_ = (x); if (rc_) return rc_; } while (0)
 static int fail(int code, const char* msg) { g_err = msg; return code; }
+std::string& orbx_err_slot() { return g_err; }  // for frame.cu
 
 struct orbx_extractor {
     ExtractorConfig cfg;

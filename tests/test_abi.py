@@ -1,4 +1,4 @@
-"""The C-ABI library loads and exports every symbol include/orbx.h declares; error behaviour that
+"""The C-ABI library loads and exports every symbol include/orbx.h and include/orbx_frame.h declare; error behaviour that
 needs no GPU. No compute calls here."""
 import ctypes
 import os
@@ -14,9 +14,12 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def declared_symbols():
-    hdr = open(os.path.join(ROOT, "include", "orbx.h")).read()
-    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
-    return sorted(set(re.findall(r"\b(orbx_[a-z0-9_]+)\s*\(", hdr)))
+    syms = set()
+    for name in ("orbx.h", "orbx_frame.h"):  # the C-ABI headers (ORBextractorGPU.h is a C++ shim over them)
+        hdr = open(os.path.join(ROOT, "include", name)).read()
+        hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+        syms |= set(re.findall(r"\b(orbx_[a-z0-9_]+)\s*\(", hdr))
+    return sorted(syms)
 
 
 def test_header_symbols_exported():
@@ -24,7 +27,7 @@ def test_header_symbols_exported():
     assert len(syms) >= 25
     L = ctypes.CDLL(pkg.SO_PATH)
     for s in syms:
-        assert hasattr(L, s), f"{s} declared in include/orbx.h but not exported by liborbx.so"
+        assert hasattr(L, s), f"{s} declared in include/*.h but not exported by liborbx.so"
     assert set(syms) == set(_lib.SIGNATURES), set(syms) ^ set(_lib.SIGNATURES)
 
 

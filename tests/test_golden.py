@@ -9,7 +9,7 @@ import pytest
 from oracle import oracle as O
 from orb_slam2_2021_b200 import synth
 
-GOLD = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+GOLD = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*_seed*.npz")))
 
 
 def test_fixtures_present():

@@ -1,0 +1,160 @@
+"""GPU parity for the frame-level rows through the C-ABI of include/orbx_frame.h:
+every integer output bit-exact against the oracle, floats bit-exact (single IEEE operations)."""
+import os
+
+import numpy as np
+import pytest
+
+import orb_slam2_2021_b200 as pkg
+from oracle import oracle as O
+from orb_slam2_2021_b200 import synth
+
+from . import frames_util as U
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "frame_search.npz")
+
+
+def oracle_search(cur, last, has, world, pdesc, obs, th, mono, ori):
+    return O.search_by_projection(U.view(O.FrameView, cur), U.view(O.FrameView, last), has, world, pdesc, obs, th, mono, ori)
+
+
+def gpu_search(m, cur, last, has, world, pdesc, obs, th, mono):
+    return m.SearchByProjection(U.view(pkg.FrameView, cur), U.view(pkg.FrameView, last), pkg.MapPointView(has, world, pdesc, obs), th, mono)
+
+
+@pytest.mark.parametrize("seed,tz,mono,ori,ur,n_last,clones", [
+    (0, 0.0, False, True, True, 300, 30), (1, 0.5, False, True, True, 300, 30), (2, -0.5, False, True, False, 300, 30),
+    (3, 0.5, True, False, True, 300, 30), (4, 0.0, False, False, False, 300, 30), (5, 0.0, False, True, True, 2000, 400),
+    (6, 0.5, False, True, True, 8000, 1500), (7, 0.0, False, True, True, 300, 200)])
+def test_search_by_projection_parity(seed, tz, mono, ori, ur, n_last, clones):
+    cur, last, has, world, pdesc, obs = U.random_scenario(seed, n_last=n_last, n_extra=n_last // 2, tz=tz, clones=clones, with_uright=ur,
+                                                          W=1241 if n_last > 1000 else 640, H=376 if n_last > 1000 else 400)
+    m = pkg.Matcher(checkOrientation=ori)
+    for th in (7, 15):
+        ref, nref = oracle_search(cur, last, has, world, pdesc, obs, th, mono, ori)
+        got, n = gpu_search(m, cur, last, has, world, pdesc, obs, th, mono)
+        assert n == nref and np.array_equal(got, ref), f"th {th}: {n} vs {nref}, {(got != ref).sum()} keypoints differ"
+        assert nref > 20
+
+
+def test_search_golden_fixture():
+    g = np.load(GOLD)
+    m_on, m_off = pkg.Matcher(checkOrientation=True), pkg.Matcher(checkOrientation=False)
+    for k in range(int(g["n_cases"])):
+        seed, tz, th, mono, ori = [g[f"case{k}_{n}"].item() for n in ("seed", "tz", "th", "mono", "ori")]
+        cur, last, has, world, pdesc, obs = U.random_scenario(int(seed), tz=float(tz))
+        got, n = gpu_search(m_on if ori else m_off, cur, last, has, world, pdesc, obs, float(th), bool(mono))
+        assert n == int(g[f"case{k}_nmatches"]) and np.array_equal(got, g[f"case{k}_match"])
+
+
+def test_search_batch_of_pairs_and_ragged_sizes():
+    """Many pairs in one call, different sizes, one with no map points and one with an empty current frame."""
+    scen = [U.random_scenario(20 + k, n_last=[50, 700, 0, 333, 1200, 64][k], n_extra=[10, 300, 40, 0, 500, 7][k], clones=[5, 80, 0, 30, 100, 8][k],
+                              tz=[0, 0.5, 0, -0.5, 0, 0.5][k]) for k in range(6)]
+    # pair 5: empty current frame
+    c5 = dict(scen[5][0])
+    c5["keys_un"], c5["desc"], c5["u_right"] = c5["keys_un"][:0], c5["desc"][:0], c5["u_right"][:0]
+    scen[5] = (c5,) + scen[5][1:]
+    m = pkg.Matcher()
+    res = m.SearchByProjection([U.view(pkg.FrameView, s[0]) for s in scen], [U.view(pkg.FrameView, s[1]) for s in scen],
+                               [pkg.MapPointView(s[2], s[3], s[4], s[5]) for s in scen], 7)
+    for k, s in enumerate(scen):
+        ref, nref = oracle_search(*s, 7, False, True)
+        assert res[k][1] == nref and np.array_equal(res[k][0], ref), k
+    assert res[2][1] == 0 and res[5][1] == 0 and len(res[5][0]) == 0
+
+
+def test_search_on_extracted_frames():
+    """End to end with the extractor's own output: last frame = stereo frame k (map points from its stereo depth),
+    current frame = the same scene shifted by a few pixels and re-extracted."""
+    import cv2
+
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["arducam"]
+    cx, cy = W / 2.0, H / 2.0
+    L, R = synth.stereo_pair(W, H, 300)
+    M = np.float32([[1, 0, 3.4], [0, 1, -1.7]])
+    L2 = cv2.warpAffine(L, M, (W, H), flags=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT_101)
+    R2 = synth.synth_right(L2, 301)
+    el, er = pkg.ORBextractor(nf, sf, nl, ini, mn), pkg.ORBextractor(nf, sf, nl, ini, mn)
+    kl, dl = el(L)
+    kr, dr = er(R)
+    ur, dp = pkg.compute_stereo_matches(el, er, kl, dl, kr, dr, bf, bf / fx)
+    kl2, dl2 = el(L2)
+    kr2, dr2 = er(R2)
+    ur2, _ = pkg.compute_stereo_matches(el, er, kl2, dl2, kr2, dr2, bf, bf / fx)
+    z = np.where(dp > 0, dp, 1).astype(np.float32)
+    world = np.stack([(kl["x"] - cx) * z / fx, (kl["y"] - cy) * z / fx, z], 1).astype(np.float32)
+    has = (dp > 0).astype(np.uint8)
+    obs = (np.arange(len(kl)) % 3 != 0).astype(np.uint8)
+    sfs = el.GetScaleFactors()
+    common = dict(fx=fx, fy=fx, cx=cx, cy=cy, mbf=bf, mb=bf / fx, bounds=(0.0, float(W), 0.0, float(H)), scale_factors=sfs)
+    Tlw = np.hstack([np.eye(3, dtype=np.float32), np.zeros((3, 1), np.float32)])
+    Tcw = Tlw.copy()
+    Tcw[:, 3] = [0.02, -0.01, 0.0]
+    cur = dict(keys_un=kl2, desc=dl2, u_right=ur2, Tcw=Tcw, **common)
+    last = dict(keys_un=kl, desc=None, u_right=None, Tcw=Tlw, **common)
+    m = pkg.Matcher()
+    for th in (7, 15):
+        ref, nref = oracle_search(cur, last, has, world, dl, obs, th, False, True)
+        got, n = gpu_search(m, cur, last, has, world, dl, obs, th, False)
+        assert n == nref and np.array_equal(got, ref)
+    assert nref > 300  # most map points are found again
+
+
+def test_grid_and_area_parity():
+    rng = np.random.default_rng(5)
+    m = pkg.Matcher()
+    for n, (W, H) in [(0, (640, 400)), (1, (640, 400)), (700, (640, 400)), (2000, (1241, 376)), (8000, (3840, 2160))]:
+        keys = np.zeros(n, pkg.KP_DTYPE)
+        keys["x"], keys["y"] = rng.uniform(-8, W + 8, n), rng.uniform(-8, H + 8, n)
+        if n > 10:
+            keys["x"][:5] = [0, W, W / 64 * 0.5, W / 64 * 1.5, W - 1e-3]
+            keys["y"][:5] = [0, H, H / 48 * 0.5, H / 48 * 2.5, H - 1e-3]
+            keys["x"][5:40], keys["y"][5:40] = 100.25, 50.75  # one crowded cell
+        keys["octave"] = rng.integers(0, 8, n)
+        args = (np.eye(4), 500, 500, W / 2, H / 2, 40, 0.08, (0.0, float(W), 0.0, float(H)), 1.2 ** np.arange(8))
+        fo, fg = O.FrameView(keys, None, None, *args), pkg.FrameView(keys, None, None, *args)
+        s0, i0 = O.assign_features_to_grid(fo)
+        s1, i1 = m.AssignFeaturesToGrid(fg)
+        assert np.array_equal(s0, s1) and np.array_equal(i0, i1)
+        for q in range(25):
+            x, y, r = rng.uniform(-30, W + 30), rng.uniform(-30, H + 30), float(rng.choice([0.5, 7, 25, 60, 400]))
+            if q == 0:
+                x, y, r = 100.0, 50.0, 5.0
+            lv = [(-1, -1), (0, 3), (2, -1), (3, 3), (1, 0)][q % 5]
+            assert np.array_equal(m.GetFeaturesInArea(fg, x, y, r, *lv), O.features_in_area(fo, x, y, r, *lv))
+
+
+def test_stereo_from_rgbd_parity():
+    rng = np.random.default_rng(6)
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["tum_mono"]
+    img = synth.synth(W, H, 77)
+    keys, _ = pkg.ORBextractor(2 * nf, sf, nl, ini, mn)(img)  # mpIniORBextractor: 2x features (src/Tracking.cc:131)
+    assert len(keys) >= 2 * nf
+    depth = rng.uniform(-0.5, 8, (H, W + 5)).astype(np.float32)[:, :W]  # strided rows
+    depth[rng.random((H, W)) < 0.1] = np.nan
+    depth[rng.random((H, W)) < 0.05] = 0
+    m = pkg.Matcher()
+    for unx in (None, (keys["x"] + rng.normal(0, 0.4, len(keys))).astype(np.float32)):
+        ur, dp = m.ComputeStereoFromRGBD(keys, depth, 40.0, unx)
+        our, odp = O.stereo_from_rgbd(keys, depth, 40.0, unx)
+        assert np.array_equal(ur, our) and np.array_equal(dp, odp)
+        assert (dp > 0).sum() > 0.5 * len(keys)
+    e, _ = m.ComputeStereoFromRGBD(keys[:0], depth, 40.0)
+    assert len(e) == 0
+
+
+def test_frame_abi_errors():
+    m = pkg.Matcher()
+    keys = np.zeros(4, pkg.KP_DTYPE)
+    keys["octave"] = 9
+    args = (np.eye(4), 500, 500, 320, 200, 40, 0.08, (0.0, 640.0, 0.0, 400.0), 1.2 ** np.arange(8))
+    cur = pkg.FrameView(keys, np.zeros((4, 32), np.uint8), None, *args)
+    last = pkg.FrameView(keys, None, None, *args)
+    pts = pkg.MapPointView(np.ones(4), np.ones((4, 3)), np.zeros((4, 32)), np.ones(4))
+    with pytest.raises(pkg.OrbxError) as ei:  # octave 9 does not index an 8-level scale table
+        m.SearchByProjection(cur, last, pts, 7)
+    assert ei.value.code == pkg._lib.ERR_ARG
+    with pytest.raises(TypeError):
+        m.ComputeStereoFromRGBD(keys, np.zeros((4, 4), np.float64), 40.0)

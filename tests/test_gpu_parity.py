@@ -71,7 +71,7 @@ def test_extract_and_stereo_handles(name, seeds):
                 assert (ur >= 0).sum() > 100
 
 
-GOLD = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+GOLD = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*_seed*.npz")))
 
 
 @pytest.mark.parametrize("path", GOLD, ids=[os.path.basename(p) for p in GOLD])
