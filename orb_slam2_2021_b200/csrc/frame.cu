@@ -215,36 +215,60 @@ __global__ void __launch_bounds__(32) orbx_resolve_kernel(const FrameDev* frames
     if (lane < HISTO) bins[lane] = 0;
     __syncwarp();
     int nmatches = 0, nev = 0;
+    const unsigned lt = (1u << lane) - 1;
+    // One accepted match: CurrentFrame.mvpMapPoints[i2] = pMP (:1445), rotation bin (:1448-1458), and the blocking rule.
+    auto commit = [&](int i, int i2, int slot) {
+        P.assigned[i2] = i;
+        if (P.checkOri) {
+            float rot = P.lastKeys[i].angle - P.curKeys[i2].angle;
+            if (rot < 0.0f) rot += 360.0f;
+            int bin = (int)roundf(rot * (1.0f / HISTO));
+            if (bin == HISTO) bin = 0;
+            P.events[slot] = (bin << 20) | i2;
+            atomicAdd(&bins[bin], 1);
+        }
+        if (P.observed[i]) atomicOr(&blocked[i2 >> 5], 1u << (i2 & 31));
+    };
+    unsigned long long next = lane < P.nLast ? P.best[lane] : NOKEY;
     for (int i0 = 0; i0 < P.nLast; i0 += 32) {
-        const unsigned long long mine = i0 + lane < P.nLast ? P.best[i0 + lane] : NOKEY;
-        unsigned todo = __ballot_sync(0xffffffffu, mine != NOKEY);
-        while (todo) {
-            const int k = __ffs(todo) - 1, i = i0 + k;
-            todo &= todo - 1;
-            unsigned long long key = __shfl_sync(0xffffffffu, mine, k);
-            int i2 = (int)(key & 0xFFFFFu);
-            if (blocked[i2 >> 5] >> (i2 & 31) & 1u) {
-                const float4 pr = P.proj[i];
-                key = search_point(P, i, pr.x, pr.y, pr.z, pr.w, blocked, lane);
-                if (key == NOKEY) continue;
-                i2 = (int)(key & 0xFFFFFu);
-            }
-            if ((int)(key >> 52) > TH_HIGH) continue;  // :1443
-            if (lane == 0) {
-                P.assigned[i2] = i;
-                if (P.checkOri) {  // :1448-1458
-                    float rot = P.lastKeys[i].angle - P.curKeys[i2].angle;
-                    if (rot < 0.0f) rot += 360.0f;
-                    int bin = (int)roundf(rot * (1.0f / HISTO));
-                    if (bin == HISTO) bin = 0;
-                    P.events[nev] = (bin << 20) | i2;
-                    bins[bin]++;
-                }
-                if (P.observed[i]) blocked[i2 >> 5] |= 1u << (i2 & 31);
-            }
-            ++nmatches;
-            ++nev;
+        const unsigned long long mine = next;
+        next = i0 + 32 + lane < P.nLast ? P.best[i0 + 32 + lane] : NOKEY;
+        // Only points whose unconstrained best is within TH_HIGH can ever match (blocking removes candidates, the
+        // best distance can only grow). 32 points are settled per step: those ahead of the first "problem" lane —
+        // best keypoint already blocked, or shared with an earlier lane of the step — commit in parallel (distinct
+        // keypoints, no order dependence); the problem lane is then handled alone, exactly like the reference's loop.
+        unsigned pending = __ballot_sync(0xffffffffu, mine != NOKEY && (int)(mine >> 52) <= TH_HIGH);
+        const int i2 = (int)(mine & 0xFFFFFu);
+        while (pending) {
+            const bool isPend = pending >> lane & 1u;
+            const bool blk = isPend && (blocked[i2 >> 5] >> (i2 & 31) & 1u);
+            const unsigned grp = __match_any_sync(0xffffffffu, isPend ? i2 : (int)(0x40000000u | lane));
+            const bool dup = isPend && (grp & lt) != 0;
+            const unsigned prob = __ballot_sync(0xffffffffu, blk || dup);
+            const int first = prob ? __ffs(prob) - 1 : 32;
+            const unsigned cm = first == 32 ? pending : pending & ((1u << first) - 1);
+            if (cm >> lane & 1u) commit(i0 + lane, i2, nev + __popc(cm & lt));
+            nmatches += __popc(cm);
+            nev += __popc(cm);
+            pending &= ~cm;
             __syncwarp();
+            if (first < 32) {
+                const int i = i0 + first;
+                unsigned long long key = __shfl_sync(0xffffffffu, mine, first);
+                int k2 = (int)(key & 0xFFFFFu);
+                if (blocked[k2 >> 5] >> (k2 & 31) & 1u) {
+                    const float4 pr = P.proj[i];
+                    key = search_point(P, i, pr.x, pr.y, pr.z, pr.w, blocked, lane);
+                    k2 = (int)(key & 0xFFFFFu);
+                }
+                if (key != NOKEY && (int)(key >> 52) <= TH_HIGH) {  // :1443
+                    if (lane == 0) commit(i, k2, nev);
+                    ++nmatches;
+                    ++nev;
+                }
+                pending &= ~(1u << first);
+                __syncwarp();
+            }
         }
     }
     if (P.checkOri) {
