@@ -280,3 +280,36 @@ def search_by_projection(cur, last, has_point, world_pos, point_desc, observed, 
     n = _frame_sigs().orc_search_by_projection(C.byref(cur.c), C.byref(last.c), C.byref(m), th, int(b_mono),
                                                int(check_orientation), _ptr(out))
     return out[:cur.c.n], n
+
+
+# ---- input staging: oracle/input.cpp -------------------------------------------------------
+
+def cvt_gray(img, rgb_order=False):
+    """cvtColor(img, CV_BGR2GRAY | CV_RGB2GRAY | CV_BGRA2GRAY | CV_RGBA2GRAY) on uint8 [H,W,C]; C == 1 copies."""
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    if img.ndim == 2:
+        img = img[:, :, None]
+    h, w, c = img.shape
+    out = np.zeros((h, w), np.uint8)
+    L = lib()
+    L.orc_cvt_gray.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+    L.orc_cvt_gray(_ptr(img), h, w, img.strides[0], c, int(rgb_order), _ptr(out), out.strides[0])
+    return out
+
+
+def remap_linear(img, mapx, mapy):
+    """cv::remap(img, mapx, mapy, INTER_LINEAR), CV_32FC1 maps, BORDER_CONSTANT 0; uint8 [H,W] or [H,W,C]."""
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    squeeze = img.ndim == 2
+    if squeeze:
+        img = img[:, :, None]
+    mapx, mapy = np.ascontiguousarray(mapx, dtype=np.float32), np.ascontiguousarray(mapy, dtype=np.float32)
+    assert mapx.shape == mapy.shape
+    h, w, c = img.shape
+    dh, dw = mapx.shape
+    out = np.zeros((dh, dw, c), np.uint8)
+    L = lib()
+    L.orc_remap_linear.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                   C.c_void_p, C.c_int]
+    L.orc_remap_linear(_ptr(img), h, w, img.strides[0], c, _ptr(mapx), _ptr(mapy), mapx.strides[0] // 4, dh, dw, _ptr(out), out.strides[0])
+    return out[:, :, 0] if squeeze else out

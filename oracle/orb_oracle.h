@@ -120,6 +120,14 @@ float orc_tlc_z(const float* Tcw, const float* Tlw);
 int orc_search_by_projection(const orc_frame* cur, const orc_frame* last, const orc_mappoints* mp, float th, int b_mono,
                              int check_orientation, int* match_of_cur);
 
+/* ---- input staging right before the hot path, oracle/input.cpp ---- */
+/* cvtColor(..., CV_RGB2GRAY / CV_BGR2GRAY / CV_RGBA2GRAY / CV_BGRA2GRAY), src/Tracking.cc:183-208; channels 1 copies. */
+void orc_cvt_gray(const uint8_t* src, int rows, int cols, int stride, int channels, int rgb_order, uint8_t* dst, int dstride);
+/* cv::remap(src, dst, mapx, mapy, INTER_LINEAR) with CV_32FC1 maps, BORDER_CONSTANT 0, 8-bit, 1/3/4 channels
+ * (Examples/Stereo/arducam_images.cpp:127-128). */
+void orc_remap_linear(const uint8_t* src, int srows, int scols, int sstride, int channels, const float* mapx, const float* mapy,
+                      int mstride_floats, int drows, int dcols, uint8_t* dst, int dstride);
+
 #ifdef __cplusplus
 }
 #endif

@@ -35,7 +35,7 @@ def build(force=False):
 
 _lib = None
 
-# name -> (restype, argtypes); the complete export list of include/orbx.h and include/orbx_frame.h
+# name -> (restype, argtypes); the complete export list of include/orbx.h, include/orbx_frame.h and include/orbx_input.h
 _vp, _i, _f, _sz, _ll = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_longlong
 _ip = C.POINTER(C.c_int)
 SIGNATURES = {
@@ -78,6 +78,10 @@ SIGNATURES = {
     "orbx_assign_features_to_grid": (_i, [_vp, _vp, _vp, _vp, _ip]),
     "orbx_get_features_in_area": (_i, [_vp, _vp, _f, _f, _f, _i, _i, _vp, _i, _ip]),
     "orbx_search_by_projection": (_i, [_vp, _vp, _vp, _vp, _i, _f, _i, _i, _vp, _vp]),
+    # include/orbx_input.h
+    "orbx_rectify_gray": (_i, [_vp, _vp, _i, _i, _sz, _i, _i, _vp, _vp, _i, _i, _sz, _i, _i, _vp, _sz]),
+    "orbx_batch_set_rectification": (_i, [_vp, _i, _vp, _vp, _i, _i, _sz, _i]),
+    "orbx_batch_upload_raw": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i]),
 }
 
 

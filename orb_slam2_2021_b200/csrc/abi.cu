@@ -375,3 +375,62 @@ extern "C" void* orbx_host_alloc(size_t bytes)
     return p;
 }
 extern "C" void orbx_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+// ---- raw-frame input path (include/orbx_input.h; kernel in input.cu) -----------------------------------------
+#include "../../include/orbx_input.h"
+
+extern "C" int orbx_batch_set_rectification(orbx_batch* b, int side, const float* map1, const float* map2, int mapRows, int mapCols,
+                                            size_t mapStrideBytes, int cropTop)
+{
+    if (!b || side < 0 || side > (b->stereo ? 1 : 0)) return fail(ORBX_ERR_ARG, "bad handle or side");
+    Engine& E = b->eng;
+    TRY(orbx_check(cudaSetDevice(E.device), "cudaSetDevice", g_err));
+    TRY(E.sync(g_err));
+    if (E.dMap1[side]) { cudaFree(E.dMap1[side]); cudaFree(E.dMap2[side]); E.dMap1[side] = E.dMap2[side] = nullptr; }
+    E.mapRows[side] = E.mapCols[side] = 0;
+    E.cropTop[side] = cropTop;
+    if (!map1 && !map2) return cropTop >= 0 ? ORBX_OK : fail(ORBX_ERR_ARG, "negative crop");
+    if (!map1 || !map2 || mapRows < 1 || mapCols != E.cols || cropTop < 0 || cropTop + E.rows > mapRows || mapStrideBytes < (size_t)mapCols * 4 ||
+        (mapStrideBytes & 3))
+        return fail(ORBX_ERR_ARG, "maps must be map_rows x (engine cols) CV_32FC1 with crop_top + engine rows <= map_rows");
+    const size_t bytes = (size_t)mapRows * mapCols * 4;
+    TRY(orbx_check(cudaMalloc(&E.dMap1[side], bytes), "map alloc", g_err));
+    TRY(orbx_check(cudaMalloc(&E.dMap2[side], bytes), "map alloc", g_err));
+    TRY(orbx_check(cudaMemcpy2D(E.dMap1[side], (size_t)mapCols * 4, map1, mapStrideBytes, (size_t)mapCols * 4, mapRows, cudaMemcpyHostToDevice), "map H2D", g_err));
+    TRY(orbx_check(cudaMemcpy2D(E.dMap2[side], (size_t)mapCols * 4, map2, mapStrideBytes, (size_t)mapCols * 4, mapRows, cudaMemcpyHostToDevice), "map H2D", g_err));
+    E.mapRows[side] = mapRows;
+    E.mapCols[side] = mapCols;
+    return ORBX_OK;
+}
+
+extern "C" int orbx_batch_upload_raw(orbx_batch* b, const uint8_t* left, const uint8_t* right, int nFrames, int srcRows, int srcCols,
+                                     int channels, int rgbOrder)
+{
+    if (!b || nFrames < 1 || nFrames > b->maxFrames || !left || (b->stereo && !right)) return fail(ORBX_ERR_ARG, "bad upload arguments");
+    if (srcRows < 1 || srcCols < 1 || (channels != 1 && channels != 3 && channels != 4)) return fail(ORBX_ERR_ARG, "bad raw frame format");
+    Engine& E = b->eng;
+    const int per = b->stereo ? 2 : 1;
+    for (int s = 0; s < per; ++s)
+        if (!E.dMap1[s] && (srcCols != E.cols || E.cropTop[s] + E.rows > srcRows))
+            return fail(ORBX_ERR_ARG, "without maps the raw frame must contain the engine's image (same width, crop inside)");
+    TRY(orbx_check(cudaSetDevice(E.device), "cudaSetDevice", g_err));
+    const size_t frame = (size_t)srcRows * srcCols * channels, need = frame * nFrames * per;
+    if (need > E.rawCap) {
+        TRY(E.sync(g_err));
+        if (E.dRaw) cudaFree(E.dRaw);
+        E.dRaw = nullptr; E.rawCap = 0;
+        TRY(orbx_check(cudaMalloc(&E.dRaw, frame * b->maxFrames * per), "raw frame buffer", g_err));
+        E.rawCap = frame * b->maxFrames * per;
+    }
+    for (int s = 0; s < per; ++s) {
+        uint8_t* d = E.dRaw + (size_t)s * frame * nFrames;
+        TRY(orbx_check(cudaMemcpyAsync(d, s ? right : left, frame * nFrames, cudaMemcpyHostToDevice, E.stream), "H2D raw frames", g_err));
+        OrbxStageArgs a{};
+        a.src = d; a.srcImgStride = frame; a.srcRows = srcRows; a.srcCols = srcCols; a.srcStride = srcCols * channels;
+        a.map1 = E.dMap1[s]; a.map2 = E.dMap2[s]; a.mapStride = E.mapCols[s];
+        a.cropTop = E.cropTop[s]; a.rows = E.rows; a.cols = E.cols;
+        a.dst = E.P.img0; a.dstImgStride = E.P.img0Stride; a.dstPitch = E.P.lv[0].pitch; a.imgStep = per; a.imgOfs = s; a.rgbOrder = rgbOrder;
+        orbx_launch_stage(a, channels, nFrames, E.stream);
+    }
+    return orbx_check(cudaGetLastError(), "stage launch", g_err);
+}

@@ -174,6 +174,12 @@ void Engine::release()
     for (void* a : allocs) cudaFree(a);
     allocs.clear();
     if (stream) cudaStreamDestroy(stream);
+    if (dRaw) { cudaFree(dRaw); dRaw = nullptr; rawCap = 0; }
+    for (int s = 0; s < 2; ++s) {
+        if (dMap1[s]) cudaFree(dMap1[s]);
+        if (dMap2[s]) cudaFree(dMap2[s]);
+        dMap1[s] = dMap2[s] = nullptr;
+    }
     if (upStream) cudaStreamDestroy(upStream);
     if (downStream) cudaStreamDestroy(downStream);
     if (stream2) cudaStreamDestroy(stream2);

@@ -49,6 +49,10 @@ public:
     int processPipelined(const uint8_t* left, const uint8_t* right, int nFrames, float mbf, float mb, const HostOutputs& out,
                          int chunkFrames, std::string& err);
     cudaStream_t upStream = nullptr, downStream = nullptr, stream2 = nullptr;
+    // raw-frame input path (include/orbx_input.h): raw frames and per-side rectification maps on the device
+    uint8_t* dRaw = nullptr; size_t rawCap = 0;
+    float* dMap1[2] = {nullptr, nullptr}; float* dMap2[2] = {nullptr, nullptr};
+    int mapRows[2] = {0, 0}, mapCols[2] = {0, 0}, cropTop[2] = {0, 0};
     std::vector<cudaEvent_t> chunkEvents;
     int lastRunChunks = 1;  // chunks of the most recent runBatch (kernel launches = chunks x launches per chunk)
     int sync(std::string& err);

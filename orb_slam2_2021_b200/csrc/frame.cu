@@ -22,9 +22,8 @@
 
 #include "../../include/orbx_frame.h"
 #include "engine.h"
+#include "matcher.h"
 
-#define TRY(x) do { int rc_ = (x); if (rc_) return rc_; } while (0)
-std::string& orbx_err_slot();  // abi.cu: the thread's orbx_last_error() text
 
 namespace {
 
@@ -343,41 +342,7 @@ __global__ void orbx_rgbd_kernel(const orbx_keypoint* keys, const float* keysUnX
 }  // namespace
 
 // ======================================= host side / C-ABI ===================================================
-struct orbx_matcher {
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    uint8_t* dBuf = nullptr; size_t dCap = 0;   // packed inputs | scratch | outputs
-    uint8_t* hIn = nullptr; size_t hInCap = 0;  // pinned staging of the inputs
-    uint8_t* hOut = nullptr; size_t hOutCap = 0;
-};
-
 namespace {
-
-int fail(int code, const char* msg) { orbx_err_slot() = msg; return code; }
-
-int grow(orbx_matcher* m, size_t dBytes, size_t inBytes, size_t outBytes)
-{
-    std::string& err = orbx_err_slot();
-    if (dBytes > m->dCap) {
-        if (m->dBuf) cudaFree(m->dBuf);
-        m->dBuf = nullptr; m->dCap = 0;
-        TRY(orbx_check(cudaMalloc(&m->dBuf, dBytes + dBytes / 2), "matcher device buffer", err));
-        m->dCap = dBytes + dBytes / 2;
-    }
-    if (inBytes > m->hInCap) {
-        if (m->hIn) cudaFreeHost(m->hIn);
-        m->hIn = nullptr; m->hInCap = 0;
-        TRY(orbx_check(cudaHostAlloc(&m->hIn, inBytes + inBytes / 2, cudaHostAllocDefault), "matcher pinned input", err));
-        m->hInCap = inBytes + inBytes / 2;
-    }
-    if (outBytes > m->hOutCap) {
-        if (m->hOut) cudaFreeHost(m->hOut);
-        m->hOut = nullptr; m->hOutCap = 0;
-        TRY(orbx_check(cudaHostAlloc(&m->hOut, outBytes + outBytes / 2, cudaHostAllocDefault), "matcher pinned output", err));
-        m->hOutCap = outBytes + outBytes / 2;
-    }
-    return ORBX_OK;
-}
 
 // z of tlc = Rlw * (-Rcw^T * tcw) + tlw (src/ORBmatcher.cc:1358-1367) in OpenCV's arithmetic: `-Rcw.t() * tcw` is the
 // general gemm path (double accumulation, one rounding), `Rlw * twc + tlw` the small-matrix path (float products and
@@ -396,16 +361,11 @@ float tlc_z(const float* Tcw, const float* Tlw)
     return (float)((double)s + (double)Tlw[11]);
 }
 
-struct Packer {
-    size_t off = 0;
-    size_t take(size_t bytes) { const size_t o = off; off = (off + bytes + 15) & ~(size_t)15; return o; }
-};
-
 int check_frame(const orbx_frame_view* f, bool needDesc)
 {
-    if (!f || f->n < 0 || f->n >= (1 << 20) || (f->n && !f->keys_un) || (needDesc && f->n && !f->desc)) return fail(ORBX_ERR_ARG, "bad frame view");
-    if (!f->scale_factors || f->nlevels < 1 || f->nlevels > ORBX_MAX_LEVELS) return fail(ORBX_ERR_ARG, "bad scale factor table");
-    if (!(f->max_x > f->min_x) || !(f->max_y > f->min_y)) return fail(ORBX_ERR_ARG, "empty image bounds");
+    if (!f || f->n < 0 || f->n >= (1 << 20) || (f->n && !f->keys_un) || (needDesc && f->n && !f->desc)) return orbx_fail(ORBX_ERR_ARG, "bad frame view");
+    if (!f->scale_factors || f->nlevels < 1 || f->nlevels > ORBX_MAX_LEVELS) return orbx_fail(ORBX_ERR_ARG, "bad scale factor table");
+    if (!(f->max_x > f->min_x) || !(f->max_y > f->min_y)) return orbx_fail(ORBX_ERR_ARG, "empty image bounds");
     return ORBX_OK;
 }
 
@@ -427,12 +387,12 @@ int stage_single_frame(orbx_matcher* m, const orbx_frame_view* f, FrameDev& D, s
 {
     std::string& err = orbx_err_slot();
     TRY(orbx_check(cudaSetDevice(m->device), "cudaSetDevice", err));
-    Packer pk;
+    OrbxPacker pk;
     const size_t oDev = pk.take(sizeof(FrameDev)), oKeys = pk.take((size_t)f->n * 28);
     const size_t inBytes = pk.off;
     const size_t oStart = pk.take((NCELL + 1) * 4), oItems = pk.take((size_t)f->n * 4 + 4);
     *scratchOff = pk.take(extraScratch);
-    TRY(grow(m, pk.off, inBytes, (NCELL + 1) * 4 + (size_t)f->n * 4 + 64));
+    TRY(orbx_matcher_grow(m, pk.off, inBytes, (NCELL + 1) * 4 + (size_t)f->n * 4 + 64));
     fill_frame(D, *f);
     D.curKeys = (const orbx_keypoint*)(m->dBuf + oKeys);
     D.cellStart = (int*)(m->dBuf + oStart);
@@ -448,7 +408,7 @@ int stage_single_frame(orbx_matcher* m, const orbx_frame_view* f, FrameDev& D, s
 
 extern "C" int orbx_matcher_create(int device, orbx_matcher** out)
 {
-    if (!out) return fail(ORBX_ERR_ARG, "out is NULL");
+    if (!out) return orbx_fail(ORBX_ERR_ARG, "out is NULL");
     *out = nullptr;
     std::string& err = orbx_err_slot();
     TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
@@ -476,15 +436,15 @@ extern "C" int orbx_stereo_from_rgbd(orbx_matcher* m, const orbx_keypoint* keys,
 {
     if (!m || n < 0 || (n && (!keys || !uRight || !depthOut)) || !depth || rows < 1 || cols < 1 || strideBytes < (size_t)cols * 4 ||
         (strideBytes & 3))
-        return fail(ORBX_ERR_ARG, "bad arguments");
+        return orbx_fail(ORBX_ERR_ARG, "bad arguments");
     if (n == 0) return ORBX_OK;
     std::string& err = orbx_err_slot();
     TRY(orbx_check(cudaSetDevice(m->device), "cudaSetDevice", err));
-    Packer pk;
+    OrbxPacker pk;
     const size_t oKeys = pk.take((size_t)n * 28), oUx = pk.take(keysUnX ? (size_t)n * 4 : 0), oDepth = pk.take((size_t)rows * cols * 4);
     const size_t inBytes = pk.off;
     const size_t oUr = pk.take((size_t)n * 4), oDp = pk.take((size_t)n * 4);
-    TRY(grow(m, pk.off, inBytes, (size_t)n * 8 + 32));
+    TRY(orbx_matcher_grow(m, pk.off, inBytes, (size_t)n * 8 + 32));
     std::memcpy(m->hIn + oKeys, keys, (size_t)n * 28);
     if (keysUnX) std::memcpy(m->hIn + oUx, keysUnX, (size_t)n * 4);
     for (int r = 0; r < rows; ++r) std::memcpy(m->hIn + oDepth + (size_t)r * cols * 4, (const uint8_t*)depth + r * strideBytes, (size_t)cols * 4);
@@ -503,7 +463,7 @@ extern "C" int orbx_stereo_from_rgbd(orbx_matcher* m, const orbx_keypoint* keys,
 
 extern "C" int orbx_assign_features_to_grid(orbx_matcher* m, const orbx_frame_view* f, int* cellStart, int* cellItems, int* nItems)
 {
-    if (!m || !cellStart || !nItems || (f && f->n && !cellItems)) return fail(ORBX_ERR_ARG, "bad arguments");
+    if (!m || !cellStart || !nItems || (f && f->n && !cellItems)) return orbx_fail(ORBX_ERR_ARG, "bad arguments");
     TRY(check_frame(f, false));
     std::string& err = orbx_err_slot();
     FrameDev D;
@@ -521,7 +481,7 @@ extern "C" int orbx_assign_features_to_grid(orbx_matcher* m, const orbx_frame_vi
 extern "C" int orbx_get_features_in_area(orbx_matcher* m, const orbx_frame_view* f, float x, float y, float r, int minLevel, int maxLevel,
                                          int* indices, int capacity, int* nIndices)
 {
-    if (!m || !nIndices || capacity < 0 || (capacity && !indices)) return fail(ORBX_ERR_ARG, "bad arguments");
+    if (!m || !nIndices || capacity < 0 || (capacity && !indices)) return orbx_fail(ORBX_ERR_ARG, "bad arguments");
     TRY(check_frame(f, false));
     std::string& err = orbx_err_slot();
     FrameDev D;
@@ -537,7 +497,7 @@ extern "C" int orbx_get_features_in_area(orbx_matcher* m, const orbx_frame_view*
     TRY(orbx_check(cudaStreamSynchronize(m->stream), "sync", err));
     const int n = *(const int*)m->hOut;
     *nIndices = n;
-    if (n > capacity) return fail(ORBX_ERR_CAPACITY, "more features in the area than the index buffer holds");
+    if (n > capacity) return orbx_fail(ORBX_ERR_CAPACITY, "more features in the area than the index buffer holds");
     if (n) std::memcpy(indices, m->hOut + 16, (size_t)n * 4);
     return ORBX_OK;
 }
@@ -546,18 +506,18 @@ extern "C" int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view*
                                          const orbx_mappoint_view* lastPoints, int nPairs, float th, int bMono, int checkOrientation,
                                          int* const* matchOfCur, int* nmatches)
 {
-    if (!m || !cur || !last || !lastPoints || nPairs < 1 || !matchOfCur || !nmatches) return fail(ORBX_ERR_ARG, "bad arguments");
+    if (!m || !cur || !last || !lastPoints || nPairs < 1 || !matchOfCur || !nmatches) return orbx_fail(ORBX_ERR_ARG, "bad arguments");
     std::string& err = orbx_err_slot();
     int maxLast = 0, maxCur = 0;
     for (int p = 0; p < nPairs; ++p) {
         TRY(check_frame(cur + p, true));
         TRY(check_frame(last + p, false));
         const orbx_mappoint_view& mp = lastPoints[p];
-        if (last[p].n && (!mp.has_point || !mp.world_pos || !mp.point_desc || !mp.observed)) return fail(ORBX_ERR_ARG, "bad map point view");
-        if (cur[p].n && !matchOfCur[p]) return fail(ORBX_ERR_ARG, "match_of_cur is NULL");
+        if (last[p].n && (!mp.has_point || !mp.world_pos || !mp.point_desc || !mp.observed)) return orbx_fail(ORBX_ERR_ARG, "bad map point view");
+        if (cur[p].n && !matchOfCur[p]) return orbx_fail(ORBX_ERR_ARG, "match_of_cur is NULL");
         for (int i = 0; i < last[p].n; ++i)
             if (last[p].keys_un[i].octave < 0 || last[p].keys_un[i].octave >= cur[p].nlevels)
-                return fail(ORBX_ERR_ARG, "last-frame keypoint octave outside the current frame's scale table");
+                return orbx_fail(ORBX_ERR_ARG, "last-frame keypoint octave outside the current frame's scale table");
         maxLast = last[p].n > maxLast ? last[p].n : maxLast;
         maxCur = cur[p].n > maxCur ? cur[p].n : maxCur;
     }
@@ -566,7 +526,7 @@ extern "C" int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view*
     // ---- layout: [FrameDev x nPairs | inputs of every pair] (one H2D) | scratch | [assigned of every pair | nmatches] (one D2H)
     struct Off { size_t curKeys, curDesc, curUR, lastKeys, has, pos, pdesc, obs, cellStart, cellItems, best, proj, events, assigned; };
     std::vector<Off> off(nPairs);
-    Packer pk;
+    OrbxPacker pk;
     const size_t oDev = pk.take(sizeof(FrameDev) * (size_t)nPairs);
     for (int p = 0; p < nPairs; ++p) {
         const size_t nc = cur[p].n, nl = last[p].n;
@@ -584,7 +544,7 @@ extern "C" int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view*
     for (int p = 0; p < nPairs; ++p) off[p].assigned = pk.take((size_t)cur[p].n * 4);
     const size_t oNm = pk.take((size_t)nPairs * 4);
     const size_t outBytes = pk.off - outBase;
-    TRY(grow(m, pk.off, inBytes, outBytes));
+    TRY(orbx_matcher_grow(m, pk.off, inBytes, outBytes));
 
     FrameDev* hd = reinterpret_cast<FrameDev*>(m->hIn + oDev);
     for (int p = 0; p < nPairs; ++p) {

@@ -106,6 +106,17 @@ struct OrbxStereoParams {
 
 // Launch wrappers (one per kernel group), defined in the .cu files.
 // tight [frame][rows][cols] images of one side -> pitched level 0 of image frame*per + side
+// input.cu: fused rectification (remap) + crop + gray conversion into level 0
+struct OrbxStageArgs {
+    const uint8_t* src; size_t srcImgStride; int srcRows, srcCols, srcStride;  // raw frames, bytes
+    const float* map1; const float* map2; int mapStride;                      // floats per map row; NULL = identity
+    int cropTop, rows, cols;                                                   // output geometry
+    uint8_t* dst; size_t dstImgStride; int dstPitch;
+    int imgStep, imgOfs;  // output image index = imgStep * blockIdx.z + imgOfs (stereo engines interleave L/R)
+    int rgbOrder;
+};
+
+void orbx_launch_stage(const OrbxStageArgs& a, int channels, int nImgs, cudaStream_t s);
 void orbx_launch_ingest(const OrbxParams& p, const uint8_t* src, int nFrames, int per, int side, cudaStream_t s);
 void orbx_launch_pyramid(const OrbxParams& p, const int* const* tabs, cudaStream_t s);
 void orbx_fast_geometry(const OrbxParams& p, int* boxW, int* rhMax);  // TMA box of the FAST kernel

@@ -186,6 +186,31 @@ class StereoFrameBatch:
         check(lib().orbx_batch_upload(self._h, ptr(left), ptr(right), n))
         return n
 
+    def set_rectification(self, side, map1, map2, crop_top=0):
+        """CV_32FC1 maps of initUndistortRectifyMap for one side (0 left, 1 right); None clears them."""
+        if map1 is None:
+            check(lib().orbx_batch_set_rectification(self._h, side, None, None, 0, 0, 0, crop_top))
+            return
+        map1, map2 = np.ascontiguousarray(map1, dtype=np.float32), np.ascontiguousarray(map2, dtype=np.float32)
+        if map1.shape != map2.shape or map1.ndim != 2:
+            raise ValueError("maps must be two float32 arrays of one 2-D shape")
+        check(lib().orbx_batch_set_rectification(self._h, side, ptr(map1), ptr(map2), map1.shape[0], map1.shape[1], map1.strides[0], crop_top))
+
+    def upload_raw(self, left, right=None, rgb=False):
+        """Raw camera frames uint8 [n,H,W] or [n,H,W,3|4]: rectified (if maps are set), cropped and converted to gray on
+        the device, straight into level 0 (cv::remap + crop + cvtColor of the reference's input path)."""
+        left = np.asarray(left)
+        if left.dtype != np.uint8 or left.ndim not in (3, 4) or not left.flags.c_contiguous:
+            raise TypeError("raw frames must be C-contiguous uint8 [n,H,W] or [n,H,W,C]")
+        if self.stereo:
+            right = np.asarray(right)
+            if right.dtype != np.uint8 or right.shape != left.shape or not right.flags.c_contiguous:
+                raise TypeError("right frames must match the left frames")
+        n, h, w = left.shape[:3]
+        ch = 1 if left.ndim == 3 else left.shape[3]
+        check(lib().orbx_batch_upload_raw(self._h, ptr(left), ptr(right) if self.stereo else None, n, h, w, ch, int(rgb)))
+        return n
+
     def upload_device(self, left_ptr, right_ptr, n_frames):
         check(lib().orbx_batch_upload_device(self._h, left_ptr, right_ptr, n_frames))
 

@@ -99,6 +99,28 @@ class Matcher:
                                           ptr(ur), ptr(dp)))
         return ur, dp
 
+    def RectifyGray(self, image, map1=None, map2=None, rgb=False, crop_top=0, crop_rows=None):
+        """gray(crop(remap(image, map1, map2, INTER_LINEAR))) — cv::remap (Examples/Stereo/arducam_images.cpp:127-133)
+        followed by cvtColor(..., CV_RGB2GRAY if rgb else CV_BGR2GRAY) (src/Tracking.cc:183-208). image: uint8 [H,W] or
+        [H,W,3|4]; maps: float32 [h,w] or None."""
+        img = np.asarray(image)
+        if img.dtype != np.uint8 or img.ndim not in (2, 3):
+            raise TypeError("image must be uint8 [H,W] or [H,W,C]")
+        img = np.ascontiguousarray(img)
+        ch = 1 if img.ndim == 2 else img.shape[2]
+        if (map1 is None) != (map2 is None):
+            raise ValueError("need both maps or none")
+        if map1 is not None:
+            map1, map2 = np.ascontiguousarray(map1, dtype=np.float32), np.ascontiguousarray(map2, dtype=np.float32)
+            if map1.shape != map2.shape or map1.ndim != 2:
+                raise ValueError("maps must be two float32 arrays of one 2-D shape")
+        mrows, mcols = map1.shape if map1 is not None else img.shape[:2]
+        rows = mrows - crop_top if crop_rows is None else crop_rows
+        out = np.zeros((max(rows, 0), mcols), np.uint8)
+        check(lib().orbx_rectify_gray(self._h, ptr(img), img.shape[0], img.shape[1], img.strides[0], ch, int(rgb), ptr(map1), ptr(map2),
+                                      mrows, mcols, mcols * 4, crop_top, rows, ptr(out), out.strides[0] if out.size else mcols))
+        return out
+
     def AssignFeaturesToGrid(self, frame):
         """-> (cell_start[64*48+1], cell_items): mGrid[ix][iy] = cell_items[cell_start[ix*48+iy] : cell_start[ix*48+iy+1]]."""
         start = np.zeros(GRID_COLS * GRID_ROWS + 1, np.int32)

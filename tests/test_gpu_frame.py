@@ -158,3 +158,71 @@ def test_frame_abi_errors():
     assert ei.value.code == pkg._lib.ERR_ARG
     with pytest.raises(TypeError):
         m.ComputeStereoFromRGBD(keys, np.zeros((4, 4), np.float64), 40.0)
+
+
+# ---- N3: input staging (include/orbx_input.h) ---------------------------------------------------------------
+from .test_input_oracle import rectification_maps  # noqa: E402
+
+
+def oracle_stage(img, m1, m2, rgb, top, rows):
+    r = img if m1 is None else O.remap_linear(img, m1, m2)
+    r = r[top:top + rows]
+    return O.cvt_gray(r, rgb_order=rgb) if r.ndim == 3 else np.ascontiguousarray(r)
+
+
+@pytest.mark.parametrize("channels,rgb", [(1, False), (3, False), (3, True), (4, True), (4, False)])
+def test_rectify_gray_parity(channels, rgb):
+    rng = np.random.default_rng(channels)
+    m = pkg.Matcher()
+    for (W, H), top, rows in [((640, 480), 0, 400), ((1241, 376), 0, 376), ((333, 97), 5, 80), ((64, 20), 0, 20)]:
+        img = rng.integers(0, 256, (H, W, channels), dtype=np.uint8)
+        img[:, :, 0] = synth.synth(W, H, 9)
+        if channels == 1:
+            img = img[:, :, 0]
+        m1, m2 = rectification_maps(W, H, seed=W)
+        if W == 333:  # extreme maps: far outside, exact integers, ties
+            m1, m2 = (m1 * 1.4 - 30).astype(np.float32), (np.round(m2 * 64) / 64 - 3).astype(np.float32)
+        assert np.array_equal(m.RectifyGray(img, m1, m2, rgb=rgb, crop_top=top, crop_rows=rows), oracle_stage(img, m1, m2, rgb, top, rows))
+        assert np.array_equal(m.RectifyGray(img, rgb=rgb, crop_top=top, crop_rows=rows), oracle_stage(img, None, None, rgb, top, rows))
+
+
+def test_batch_from_raw_frames():
+    """Raw distorted BGR frames in -> the same keypoints, descriptors and stereo matches as extracting the images
+    that cv::remap + crop + cvtColor produce (oracle path), i.e. the reference's arducam pipeline end to end."""
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["arducam"]
+    RH = 480  # raw height; the reference crops rows 0..400 after rectification (arducam_images.cpp:105-133)
+    n = 3
+    rng = np.random.default_rng(8)
+    raws_l, raws_r = np.zeros((n, RH, W, 3), np.uint8), np.zeros((n, RH, W, 3), np.uint8)
+    for k in range(n):
+        l, r = synth.stereo_pair(W, RH, 500 + 2 * k)
+        for c in range(3):
+            raws_l[k, :, :, c] = np.clip(l.astype(np.int32) + rng.integers(-6, 7, l.shape), 0, 255)
+            raws_r[k, :, :, c] = np.clip(r.astype(np.int32) + rng.integers(-6, 7, r.shape), 0, 255)
+    ml, mr = rectification_maps(W, RH, seed=1), rectification_maps(W, RH, seed=2)
+    b = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, n, stereo=True)
+    b.set_rectification(0, ml[0], ml[1], crop_top=0)
+    b.set_rectification(1, mr[0], mr[1], crop_top=0)
+    b.upload_raw(raws_l, raws_r, rgb=False)
+    b.run(n, bf, bf / fx)
+    out = b.download(n)
+    for k in range(n):
+        gl, gr = oracle_stage(raws_l[k], ml[0], ml[1], False, 0, H), oracle_stage(raws_r[k], mr[0], mr[1], False, 0, H)
+        assert np.array_equal(b.level(k, 0, 0), gl) and np.array_equal(b.level(k, 1, 0), gr)
+        el, er = O.OracleExtractor(nf, sf, nl, ini, mn), O.OracleExtractor(nf, sf, nl, ini, mn)
+        okl, odl = el(gl)
+        okr, odr = er(gr)
+        our, odp = O.stereo_match(el, er, okl, odl, okr, odr, bf, bf / fx)
+        nl_, nr_ = out["n_left"][k], out["n_right"][k]
+        assert nl_ == len(okl) and nr_ == len(okr)
+        assert np.array_equal(out["kps_left"][k][:nl_]["x"], okl["x"]) and np.array_equal(out["desc_left"][k][:nl_], odl)
+        assert np.array_equal(out["desc_right"][k][:nr_], odr)
+        assert np.array_equal(out["u_right"][k][:nl_], our) and np.array_equal(out["depth"][k][:nl_], odp)
+    # gray-only path (no maps): mono engine fed with RGBA frames
+    mono = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, n, stereo=False)
+    mono.set_rectification(0, None, None, crop_top=40)
+    rgba = np.concatenate([raws_l, np.full((n, RH, W, 1), 255, np.uint8)], axis=3)
+    mono.upload_raw(rgba, rgb=True)
+    mono.run(n)
+    for k in range(n):
+        assert np.array_equal(mono.level(k, 0, 0), oracle_stage(rgba[k], None, None, True, 40, H))
