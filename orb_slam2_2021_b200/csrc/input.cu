@@ -24,58 +24,64 @@ __device__ __forceinline__ int gray_of(const int* v, int rgbOrder)
     return (r * 9798 + g * 19235 + b * 3735 + (1 << 14)) >> 15;
 }
 
+#define STAGE_NI 8  // images per thread: the maps, weights and source offsets of a pixel are shared by all images of a side
+
 template <int C>
-__global__ void __launch_bounds__(128) orbx_stage_kernel(OrbxStageArgs a)
+__global__ void __launch_bounds__(128) orbx_stage_kernel(OrbxStageArgs a, int nImgs)
 {
-    const int x0 = (blockIdx.x * 128 + threadIdx.x) * 4, y = blockIdx.y, img = blockIdx.z;
+    const int x0 = (blockIdx.x * 128 + threadIdx.x) * 4, y = blockIdx.y, img0 = blockIdx.z * STAGE_NI;
     if (x0 >= a.cols) return;
-    const uint8_t* src = a.src + (size_t)img * a.srcImgStride;
-    uint32_t packed = 0;
+    // per pixel: source offset of the top-left neighbour, the four weights, and which neighbours lie inside the image
+    int ofs[4], w00[4], w01[4], w10[4], w11[4];
+    unsigned in[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const int x = x0 + k;
-        int g = 0;
-        if (x < a.cols) {
-            int v[C];
-            if (a.map1) {
-                const size_t mi = (size_t)(y + a.cropTop) * a.mapStride + x;
-                const int sx = __float2int_rn(__fmul_rn(__ldg(a.map1 + mi), 32.0f)), sy = __float2int_rn(__fmul_rn(__ldg(a.map2 + mi), 32.0f));
-                const int fx = sx & 31, fy = sy & 31;
-                const int ix = min(max(sx >> 5, -32768), 32767), iy = min(max(sy >> 5, -32768), 32767);
-                int w00 = (32 - fx) * (32 - fy) * 32, w11 = fx * fy * 32;
-                const int w01 = fx * (32 - fy) * 32, w10 = (32 - fx) * fy * 32;
-                if (w00 > 32767) { w00 = 32767; w11 += 1; }
-                const bool x0in = ix >= 0 && ix < a.srcCols, x1in = ix + 1 >= 0 && ix + 1 < a.srcCols;
-                const bool y0in = iy >= 0 && iy < a.srcRows, y1in = iy + 1 >= 0 && iy + 1 < a.srcRows;
-                const uint8_t* p0 = src + (ptrdiff_t)iy * a.srcStride + (ptrdiff_t)ix * C;
-                const uint8_t* p1 = p0 + a.srcStride;
-#pragma unroll
-                for (int c = 0; c < C; ++c) {
-                    const int p00 = (x0in && y0in) ? p0[c] : 0, p01 = (x1in && y0in) ? p0[C + c] : 0;
-                    const int p10 = (x0in && y1in) ? p1[c] : 0, p11 = (x1in && y1in) ? p1[C + c] : 0;
-                    v[c] = (w00 * p00 + w01 * p01 + w10 * p10 + w11 * p11 + (1 << 14)) >> 15;
-                }
-            } else {
-                const uint8_t* p = src + (size_t)(y + a.cropTop) * a.srcStride + (size_t)x * C;
-#pragma unroll
-                for (int c = 0; c < C; ++c) v[c] = p[c];
-            }
-            g = gray_of<C>(v, a.rgbOrder);
+        const int x = min(x0 + k, a.cols - 1);  // lanes past the last column repeat it; their bytes land in the row padding
+        if (a.map1) {
+            const size_t mi = (size_t)(y + a.cropTop) * a.mapStride + x;
+            const int sx = __float2int_rn(__fmul_rn(__ldg(a.map1 + mi), 32.0f)), sy = __float2int_rn(__fmul_rn(__ldg(a.map2 + mi), 32.0f));
+            const int fx = sx & 31, fy = sy & 31;
+            const int ix = min(max(sx >> 5, -32768), 32767), iy = min(max(sy >> 5, -32768), 32767);
+            w00[k] = (32 - fx) * (32 - fy) * 32; w01[k] = fx * (32 - fy) * 32; w10[k] = (32 - fx) * fy * 32; w11[k] = fx * fy * 32;
+            if (w00[k] > 32767) { w00[k] = 32767; w11[k] += 1; }
+            const bool x0in = ix >= 0 && ix < a.srcCols, x1in = ix + 1 >= 0 && ix + 1 < a.srcCols;
+            const bool y0in = iy >= 0 && iy < a.srcRows, y1in = iy + 1 >= 0 && iy + 1 < a.srcRows;
+            in[k] = (x0in && y0in ? 1u : 0u) | (x1in && y0in ? 2u : 0u) | (x0in && y1in ? 4u : 0u) | (x1in && y1in ? 8u : 0u);
+            ofs[k] = iy * a.srcStride + ix * C;
+        } else {
+            w00[k] = 32768; w01[k] = w10[k] = w11[k] = 0;  // identity: (32768 p + 2^14) >> 15 == p
+            in[k] = 1u;
+            ofs[k] = (y + a.cropTop) * a.srcStride + x * C;
         }
-        packed |= (uint32_t)g << (8 * k);
     }
-    uint8_t* d = a.dst + (size_t)(a.imgStep * img + a.imgOfs) * a.dstImgStride + (size_t)y * a.dstPitch + x0;
-    if (x0 + 3 < a.dstPitch) *reinterpret_cast<uint32_t*>(d) = packed;  // the pitch is a multiple of 16: the padding may be written
-    else
-        for (int k = 0; k < 4 && x0 + k < a.cols; ++k) d[k] = (uint8_t)(packed >> (8 * k));
+    const int iEnd = min(img0 + STAGE_NI, nImgs);
+    for (int img = img0; img < iEnd; ++img) {
+        const uint8_t* src = a.src + (size_t)img * a.srcImgStride;
+        uint32_t packed = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint8_t* p0 = src + ofs[k];
+            const uint8_t* p1 = p0 + a.srcStride;
+            int v[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                const int p00 = (in[k] & 1u) ? p0[c] : 0, p01 = (in[k] & 2u) ? p0[C + c] : 0;
+                const int p10 = (in[k] & 4u) ? p1[c] : 0, p11 = (in[k] & 8u) ? p1[C + c] : 0;
+                v[c] = (w00[k] * p00 + w01[k] * p01 + w10[k] * p10 + w11[k] * p11 + (1 << 14)) >> 15;
+            }
+            packed |= (uint32_t)gray_of<C>(v, a.rgbOrder) << (8 * k);
+        }
+        // the pitch is a multiple of 16 and x0 of 4: the whole word lies inside the row (padding may be written)
+        *reinterpret_cast<uint32_t*>(a.dst + (size_t)(a.imgStep * img + a.imgOfs) * a.dstImgStride + (size_t)y * a.dstPitch + x0) = packed;
+    }
 }
 
 void orbx_launch_stage(const OrbxStageArgs& a, int channels, int nImgs, cudaStream_t s)
 {
-    dim3 grid((a.cols + 511) / 512, a.rows, nImgs);
-    if (channels == 1) orbx_stage_kernel<1><<<grid, 128, 0, s>>>(a);
-    else if (channels == 3) orbx_stage_kernel<3><<<grid, 128, 0, s>>>(a);
-    else orbx_stage_kernel<4><<<grid, 128, 0, s>>>(a);
+    dim3 grid((a.cols + 511) / 512, a.rows, (nImgs + STAGE_NI - 1) / STAGE_NI);
+    if (channels == 1) orbx_stage_kernel<1><<<grid, 128, 0, s>>>(a, nImgs);
+    else if (channels == 3) orbx_stage_kernel<3><<<grid, 128, 0, s>>>(a, nImgs);
+    else orbx_stage_kernel<4><<<grid, 128, 0, s>>>(a, nImgs);
 }
 
 extern "C" int orbx_rectify_gray(orbx_matcher* m, const uint8_t* src, int rows, int cols, size_t stride, int channels, int rgbOrder,
