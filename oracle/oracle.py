@@ -313,3 +313,45 @@ def remap_linear(img, mapx, mapy):
                                    C.c_void_p, C.c_int]
     L.orc_remap_linear(_ptr(img), h, w, img.strides[0], c, _ptr(mapx), _ptr(mapy), mapx.strides[0] // 4, dh, dw, _ptr(out), out.strides[0])
     return out[:, :, 0] if squeeze else out
+
+
+# ---- bag of words: oracle/bow.cpp ------------------------------------------------------------
+
+class Vocabulary:
+    """The DBoW2 ORB vocabulary as loadFromTextFile builds it: entry i = node i+1 (parent, leaf flag, descriptor, weight)."""
+
+    def __init__(self, L, parent, is_leaf, desc, weight):
+        self.parent = np.ascontiguousarray(parent, dtype=np.int32)
+        self.is_leaf = np.ascontiguousarray(is_leaf, dtype=np.uint8)
+        self.desc = np.ascontiguousarray(desc, dtype=np.uint8).reshape(-1, 32)
+        self.weight = np.ascontiguousarray(weight, dtype=np.float64)
+        lb = lib()
+        lb.orc_voc_create.restype = C.c_void_p
+        lb.orc_voc_create.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        lb.orc_voc_destroy.argtypes = [C.c_void_p]
+        lb.orc_voc_words.argtypes = [C.c_void_p]
+        lb.orc_compute_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 7
+        self.L = L
+        self._h = lb.orc_voc_create(L, len(self.parent), _ptr(self.parent), _ptr(self.is_leaf), _ptr(self.desc), _ptr(self.weight))
+        if not self._h:
+            raise ValueError("bad vocabulary")
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            lib().orc_voc_destroy(h)
+
+    @property
+    def n_words(self):
+        return lib().orc_voc_words(self._h)
+
+    def transform(self, desc, levelsup=4):
+        """-> (word_ids, word_vals, fv_nodes, fv_start, fv_feats): BowVector and FeatureVector (CSR) of the features."""
+        desc = np.ascontiguousarray(desc, dtype=np.uint8).reshape(-1, 32)
+        n = len(desc)
+        wi, wv = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.float64)
+        fn, fs, ff = np.zeros(max(n, 1), np.int32), np.zeros(n + 1, np.int32), np.zeros(max(n, 1), np.int32)
+        nw, nf = C.c_int(), C.c_int()
+        lib().orc_compute_bow(self._h, _ptr(desc), n, levelsup, _ptr(wi), _ptr(wv), C.addressof(nw), _ptr(fn), _ptr(fs), _ptr(ff),
+                              C.addressof(nf))
+        return wi[: nw.value], wv[: nw.value], fn[: nf.value], fs[: nf.value + 1], ff[: fs[nf.value]]

@@ -128,6 +128,19 @@ void orc_cvt_gray(const uint8_t* src, int rows, int cols, int stride, int channe
 void orc_remap_linear(const uint8_t* src, int srows, int scols, int sstride, int channels, const float* mapx, const float* mapy,
                       int mstride_floats, int drows, int dcols, uint8_t* dst, int dstride);
 
+/* ---- bag of words, oracle/bow.cpp ---- */
+typedef struct orc_vocabulary orc_vocabulary;
+/* The vocabulary as TemplatedVocabulary::loadFromTextFile builds it (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1351-1436):
+ * entry i describes node id i+1 (the root is node 0): parent id, leaf flag, 32-byte descriptor, weight. NULL on bad parents. */
+orc_vocabulary* orc_voc_create(int L, int n_nodes, const int* parent, const uint8_t* is_leaf, const uint8_t* desc, const double* weight);
+void orc_voc_destroy(orc_vocabulary* v);
+int orc_voc_words(const orc_vocabulary* v);
+/* Frame::ComputeBoW = transform(features, BowVector, FeatureVector, levelsup), TF_IDF + L1_NORM (src/Frame.cc:447-454).
+ * BowVector -> word_ids/word_vals ascending by word id (capacity n); FeatureVector -> CSR ascending by node id:
+ * fv_nodes[m], fv_start[m+1], fv_feats (capacity n, n+1, n). */
+int orc_compute_bow(const orc_vocabulary* voc, const uint8_t* desc, int n, int levelsup, int* word_ids, double* word_vals,
+                    int* n_words, int* fv_nodes, int* fv_start, int* fv_feats, int* n_fv_nodes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -35,7 +35,7 @@ def build(force=False):
 
 _lib = None
 
-# name -> (restype, argtypes); the complete export list of include/orbx.h, include/orbx_frame.h and include/orbx_input.h
+# name -> (restype, argtypes); the complete export list of include/orbx.h, orbx_frame.h, orbx_input.h and orbx_bow.h
 _vp, _i, _f, _sz, _ll = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_longlong
 _ip = C.POINTER(C.c_int)
 SIGNATURES = {
@@ -82,6 +82,11 @@ SIGNATURES = {
     "orbx_rectify_gray": (_i, [_vp, _vp, _i, _i, _sz, _i, _i, _vp, _vp, _i, _i, _sz, _i, _i, _vp, _sz]),
     "orbx_batch_set_rectification": (_i, [_vp, _i, _vp, _vp, _i, _i, _sz, _i]),
     "orbx_batch_upload_raw": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i]),
+    # include/orbx_bow.h
+    "orbx_vocabulary_create": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, C.POINTER(_vp)]),
+    "orbx_vocabulary_destroy": (None, [_vp]),
+    "orbx_vocabulary_words": (_i, [_vp]),
+    "orbx_compute_bow": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
 }
 
 

@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def declared_symbols():
     syms = set()
-    for name in ("orbx.h", "orbx_frame.h", "orbx_input.h"):  # the C-ABI headers (ORBextractorGPU.h is a C++ shim over them)
+    for name in ("orbx.h", "orbx_frame.h", "orbx_input.h", "orbx_bow.h"):  # the C-ABI headers (ORBextractorGPU.h is a C++ shim over them)
         hdr = open(os.path.join(ROOT, "include", name)).read()
         hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
         syms |= set(re.findall(r"\b(orbx_[a-z0-9_]+)\s*\(", hdr))
