@@ -5,6 +5,8 @@
  *       Frame::GetFeaturesInArea                              /root/reference/src/Frame.cc:376-433
  *       ORBmatcher::SearchByProjection(Frame&, const Frame&, float th, bool bMono)
  *                                                             /root/reference/src/ORBmatcher.cc:1348-1491
+ *       ORBmatcher::SearchByProjection(Frame&, const std::vector<MapPoint*>&, float th)
+ *                                                             /root/reference/src/ORBmatcher.cc:45-127
  *
  * Same conventions as orbx.h: plain pointers and sizes, int status codes (ORBX_OK / ORBX_ERR_*),
  * orbx_last_error() for the message, no CPU fallback (ORBX_ERR_CUDA without a device). Part of liborbx.so.
@@ -73,6 +75,27 @@ int orbx_get_features_in_area(orbx_matcher* m, const orbx_frame_view* f, float x
 int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view* cur, const orbx_frame_view* last,
                               const orbx_mappoint_view* last_points, int n_pairs, float th, int b_mono, int check_orientation,
                               int* const* match_of_cur, int* nmatches);
+
+/* Per map point of the local map, as far as the local-map SearchByProjection reads it (MapPoint members set by
+ * Frame::isInFrustum, src/Frame.cc:304-374). */
+typedef struct {
+    int n;
+    const uint8_t* valid;      /* pMP->mbTrackInView && !pMP->isBad() */
+    const float* proj;         /* n x 3: mTrackProjX, mTrackProjY, mTrackProjXR */
+    const int* level;          /* mnTrackScaleLevel; must index the frame's scale table */
+    const float* view_cos;     /* mTrackViewCos */
+    const uint8_t* point_desc; /* n x 32, MapPoint::GetDescriptor() */
+    const uint8_t* observed;   /* MapPoint::Observations() > 0 */
+} orbx_trackpoint_view;
+
+/* ORBmatcher::SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th) with
+ * mfNNratio = nnratio (src/ORBmatcher.cc:45-127; caller Tracking::SearchLocalPoints, src/Tracking.cc:1205-1215), for
+ * n_pairs independent (frame, local map) pairs. occupied[p][i] != 0 iff F.mvpMapPoints[i] holds a point with
+ * Observations() > 0 on entry (occupied or occupied[p] may be NULL = none). match_of_key[p][i] = index of the map point
+ * the call stores in F.mvpMapPoints[i], or -1 (entry unchanged); nmatches[p] = the reference's return value. */
+int orbx_search_local_points(orbx_matcher* m, const orbx_frame_view* frames, const uint8_t* const* occupied,
+                             const orbx_trackpoint_view* points, int n_pairs, float th, float nnratio, int* const* match_of_key,
+                             int* nmatches);
 
 #ifdef __cplusplus
 }

@@ -225,3 +225,54 @@ extern "C" int orc_search_by_projection(const orc_frame* cur, const orc_frame* l
     for (int i = 0; i < cur->n; ++i) match_of_cur[i] = assigned[i];
     return nmatches;
 }
+
+// ORBmatcher::SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, const float th)
+// /root/reference/src/ORBmatcher.cc:45-127 (caller Tracking::SearchLocalPoints, src/Tracking.cc:1205-1215).
+// occupied[i] = F.mvpMapPoints[i] != NULL && F.mvpMapPoints[i]->Observations() > 0 on entry (may be NULL).
+extern "C" int orc_search_local_points(const orc_frame* F, const uint8_t* occupied, const orc_trackpoints* tp, float th, float nnratio,
+                                       int* match_of_key)
+{
+    int nmatches = 0;
+    Grid g;
+    build_grid(F, g);
+    const bool bFactor = th != 1.0;
+    std::vector<int> assigned(F->n, -1);
+    std::vector<uint8_t> blocked(F->n, 0);
+    for (int i = 0; i < F->n; ++i) blocked[i] = occupied ? occupied[i] : 0;
+    std::vector<int> vIndices;
+    for (int iMP = 0; iMP < tp->n; iMP++) {
+        if (!tp->valid[iMP]) continue;  // mbTrackInView && !isBad()
+        const int nPredictedLevel = tp->level[iMP];
+        float r = ((double)tp->view_cos[iMP] > 0.998) ? 2.5f : 4.0f;  // RadiusByViewingCos :134-140
+        if (bFactor) r *= th;
+        const float radius = r * F->scale_factors[nPredictedLevel];
+        features_in_area(F, g, tp->proj[3 * iMP], tp->proj[3 * iMP + 1], radius, nPredictedLevel - 1, nPredictedLevel, vIndices);
+        if (vIndices.empty()) continue;
+        const uint8_t* dMP = tp->point_desc + 32 * (size_t)iMP;
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int idx : vIndices) {
+            if (blocked[idx]) continue;  // F.mvpMapPoints[idx] && Observations() > 0
+            if (F->u_right && F->u_right[idx] > 0) {
+                const float er = std::fabs(tp->proj[3 * iMP + 2] - F->u_right[idx]);
+                if (er > radius) continue;
+            }
+            const int dist = orc_hamming256(dMP, F->desc + 32 * (size_t)idx);
+            if (dist < bestDist) {
+                bestDist2 = bestDist; bestDist = dist;
+                bestLevel2 = bestLevel; bestLevel = F->keys_un[idx].octave;
+                bestIdx = idx;
+            } else if (dist < bestDist2) {
+                bestLevel2 = F->keys_un[idx].octave;
+                bestDist2 = dist;
+            }
+        }
+        if (bestDist <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && (float)bestDist > nnratio * (float)bestDist2) continue;
+            assigned[bestIdx] = iMP;
+            blocked[bestIdx] = tp->observed[iMP];
+            nmatches++;
+        }
+    }
+    for (int i = 0; i < F->n; ++i) match_of_key[i] = assigned[i];
+    return nmatches;
+}

@@ -355,3 +355,25 @@ class Vocabulary:
         lib().orc_compute_bow(self._h, _ptr(desc), n, levelsup, _ptr(wi), _ptr(wv), C.addressof(nw), _ptr(fn), _ptr(fs), _ptr(ff),
                               C.addressof(nf))
         return wi[: nw.value], wv[: nw.value], fn[: nf.value], fs[: nf.value + 1], ff[: fs[nf.value]]
+
+
+class _OrcTrackPoints(C.Structure):
+    _fields_ = [("n", C.c_int), ("valid", C.c_void_p), ("proj", C.c_void_p), ("level", C.c_void_p), ("view_cos", C.c_void_p),
+                ("point_desc", C.c_void_p), ("observed", C.c_void_p)]
+
+
+def search_local_points(frame, occupied, valid, proj, level, view_cos, point_desc, observed, th, nnratio=0.8):
+    """ORBmatcher::SearchByProjection(F, vpMapPoints, th) (src/ORBmatcher.cc:45-127) -> (match_of_key, nmatches)."""
+    va = np.ascontiguousarray(valid, dtype=np.uint8)
+    pr = np.ascontiguousarray(proj, dtype=np.float32).reshape(-1, 3)
+    lv = np.ascontiguousarray(level, dtype=np.int32)
+    vc = np.ascontiguousarray(view_cos, dtype=np.float32)
+    pd = np.ascontiguousarray(point_desc, dtype=np.uint8).reshape(-1, 32)
+    ob = np.ascontiguousarray(observed, dtype=np.uint8)
+    oc = None if occupied is None else np.ascontiguousarray(occupied, dtype=np.uint8)
+    t = _OrcTrackPoints(len(va), va.ctypes.data, pr.ctypes.data, lv.ctypes.data, vc.ctypes.data, pd.ctypes.data, ob.ctypes.data)
+    L = _frame_sigs()
+    L.orc_search_local_points.argtypes = [C.POINTER(_OrcFrame), C.c_void_p, C.POINTER(_OrcTrackPoints), C.c_float, C.c_float, C.c_void_p]
+    out = np.full(max(frame.c.n, 1), -1, np.int32)
+    n = L.orc_search_local_points(C.byref(frame.c), None if oc is None else _ptr(oc), C.byref(t), th, nnratio, _ptr(out))
+    return out[: frame.c.n], n

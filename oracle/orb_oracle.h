@@ -120,6 +120,22 @@ float orc_tlc_z(const float* Tcw, const float* Tlw);
 int orc_search_by_projection(const orc_frame* cur, const orc_frame* last, const orc_mappoints* mp, float th, int b_mono,
                              int check_orientation, int* match_of_cur);
 
+/* Per map point of the local map, as far as the local-map SearchByProjection reads it. */
+typedef struct {
+    int n;
+    const uint8_t* valid;      /* pMP->mbTrackInView && !pMP->isBad() */
+    const float* proj;         /* n x 3: mTrackProjX, mTrackProjY, mTrackProjXR */
+    const int* level;          /* mnTrackScaleLevel */
+    const float* view_cos;     /* mTrackViewCos */
+    const uint8_t* point_desc; /* n x 32, GetDescriptor() */
+    const uint8_t* observed;   /* Observations() > 0 */
+} orc_trackpoints;
+/* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th), src/ORBmatcher.cc:45-127; nnratio = mfNNratio.
+ * occupied[i] = F.mvpMapPoints[i] holds a point with Observations() > 0 on entry (NULL = none). match_of_key[i] = index
+ * of the map point newly stored in F.mvpMapPoints[i], or -1 (entry left as it was). Returns nmatches. */
+int orc_search_local_points(const orc_frame* F, const uint8_t* occupied, const orc_trackpoints* tp, float th, float nnratio,
+                            int* match_of_key);
+
 /* ---- input staging right before the hot path, oracle/input.cpp ---- */
 /* cvtColor(..., CV_RGB2GRAY / CV_BGR2GRAY / CV_RGBA2GRAY / CV_BGRA2GRAY), src/Tracking.cc:183-208; channels 1 copies. */
 void orc_cvt_gray(const uint8_t* src, int rows, int cols, int stride, int channels, int rgb_order, uint8_t* dst, int dstride);

@@ -294,6 +294,146 @@ __global__ void __launch_bounds__(32) orbx_resolve_kernel(const FrameDev* frames
     if (lane == 0) *P.nmatches = nmatches;
 }
 
+// ---- local-map SearchByProjection (src/ORBmatcher.cc:45-127): best AND second-best candidate per map point --------
+struct MapDev {  // the map-point side of one (frame, local map) pair; the frame side is a FrameDev (grid, keys, descriptors)
+    int nPts;
+    const uint8_t* valid; const float* proj; const int* level; const float* viewCos; const uint8_t* pdesc; const uint8_t* observed;
+    const uint8_t* occupied;  // per keypoint, may be NULL
+    float th, nnratio;
+    unsigned long long* best2;  // per point: second-best key (best is FrameDev::best)
+};
+
+__device__ __forceinline__ float map_radius(const FrameDev& P, const MapDev& X, int i)
+{
+    float r = ((double)X.viewCos[i] > 0.998) ? 2.5f : 4.0f;  // RadiusByViewingCos :134-140
+    if (X.th != 1.0f) r = __fmul_rn(r, X.th);                // bFactor :49, :66-67
+    return __fmul_rn(r, P.scale[X.level[i]]);
+}
+
+// Two smallest keys (distance, candidate order) of map point i over the candidates the reference's loop would visit.
+__device__ void search_top2(const FrameDev& P, const MapDev& X, int i, const uint32_t* blocked, int lane, unsigned long long& k1,
+                            unsigned long long& k2)
+{
+    const int lvl = X.level[i];
+    const float x = X.proj[3 * i], y = X.proj[3 * i + 1], xr = X.proj[3 * i + 2], radius = map_radius(P, X, i);
+    k1 = k2 = NOKEY;
+    int x0, x1, y0, y1;
+    if (area_cells(P, x, y, radius, x0, x1, y0, y1)) {
+        const uint4* dm = reinterpret_cast<const uint4*>(X.pdesc + 32 * (size_t)i);
+        const uint4 a0 = dm[0], a1 = dm[1];
+        const int ny = y1 - y0 + 1, ncell = (x1 - x0 + 1) * ny;
+        for (int c = lane; c < ncell; c += 32) {
+            const int ix = x0 + c / ny, iy = y0 + c % ny;
+            const int b = P.cellStart[ix * GR + iy], e = P.cellStart[ix * GR + iy + 1];
+            for (int j = b; j < e; ++j) {
+                const int i2 = P.cellItems[j];
+                if (!in_area(P.curKeys[i2], x, y, radius, lvl - 1, lvl)) continue;
+                if (blocked ? (blocked[i2 >> 5] >> (i2 & 31) & 1u) : (X.occupied && X.occupied[i2])) continue;  // :92-94
+                if (P.curUR) {
+                    const float r2 = P.curUR[i2];
+                    if (r2 > 0 && fabsf(xr - r2) > radius) continue;  // :96-101
+                }
+                const uint4* dc = reinterpret_cast<const uint4*>(P.curDesc + 32 * (size_t)i2);
+                const uint4 b0 = dc[0], b1 = dc[1];
+                const int dist = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+                                 __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+                const unsigned long long k = ((unsigned long long)dist << 52) | ((unsigned long long)c << 40) |
+                                             ((unsigned long long)(j - b) << 20) | (unsigned long long)i2;
+                if (k < k1) { k2 = k1; k1 = k; } else if (k < k2) k2 = k;
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        const unsigned long long o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
+        const unsigned long long lo = k1 < o1 ? k1 : o1, hi = k1 < o1 ? o1 : k1, s2 = k2 < o2 ? k2 : o2;
+        k1 = lo;
+        k2 = hi < s2 ? hi : s2;
+    }
+}
+
+__global__ void __launch_bounds__(256) orbx_map_search_kernel(const FrameDev* frames, const MapDev* maps)
+{
+    const FrameDev& P = frames[blockIdx.y];
+    const MapDev& X = maps[blockIdx.y];
+    const int lane = threadIdx.x & 31, i = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (i >= X.nPts) return;
+    unsigned long long k1 = NOKEY, k2 = NOKEY;
+    if (X.valid[i]) search_top2(P, X, i, nullptr, lane, k1, k2);
+    if (lane == 0) { P.best[i] = k1; X.best2[i] = k2; }
+}
+
+// :113-123 — accept the best candidate unless the second-best has the same level and is too close
+__device__ __forceinline__ bool map_accept(const FrameDev& P, const MapDev& X, unsigned long long k1, unsigned long long k2)
+{
+    if (k1 == NOKEY) return false;
+    const int bestDist = (int)(k1 >> 52);
+    if (bestDist > TH_HIGH) return false;
+    const int bestLevel = P.curKeys[(int)(k1 & 0xFFFFFu)].octave;
+    const int bestDist2 = k2 == NOKEY ? 256 : (int)(k2 >> 52), bestLevel2 = k2 == NOKEY ? -1 : P.curKeys[(int)(k2 & 0xFFFFFu)].octave;
+    return !(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(X.nnratio, (float)bestDist2));
+}
+
+__global__ void __launch_bounds__(32) orbx_map_resolve_kernel(const FrameDev* frames, const MapDev* maps)
+{
+    extern __shared__ uint32_t blocked[];
+    const FrameDev& P = frames[blockIdx.y];
+    const MapDev& X = maps[blockIdx.y];
+    const int lane = threadIdx.x;
+    const unsigned lt = (1u << lane) - 1;
+    for (int w = lane; w < (P.nCur + 31) / 32; w += 32) {
+        uint32_t bits = 0;
+        if (X.occupied)
+            for (int b = 0; b < 32 && 32 * w + b < P.nCur; ++b) bits |= X.occupied[32 * w + b] ? 1u << b : 0u;
+        blocked[w] = bits;
+    }
+    for (int i = lane; i < P.nCur; i += 32) P.assigned[i] = -1;
+    __syncwarp();
+    auto isBlocked = [&](unsigned long long k) { const int q = (int)(k & 0xFFFFFu); return k != NOKEY && (blocked[q >> 5] >> (q & 31) & 1u); };
+    auto commit = [&](int i, int i2) {
+        P.assigned[i2] = i;  // F.mvpMapPoints[bestIdx] = pMP :120
+        if (X.observed[i]) atomicOr(&blocked[i2 >> 5], 1u << (i2 & 31));
+    };
+    int nmatches = 0;
+    for (int i0 = 0; i0 < X.nPts; i0 += 32) {
+        const int i = i0 + lane;
+        const unsigned long long k1 = i < X.nPts ? P.best[i] : NOKEY, k2 = i < X.nPts ? X.best2[i] : NOKEY;
+        // only points whose unconstrained best is within TH_HIGH can ever match; a point's result is final when neither its
+        // best nor its second-best keypoint is blocked or taken by an earlier point of this step
+        unsigned pending = __ballot_sync(0xffffffffu, k1 != NOKEY && (int)(k1 >> 52) <= TH_HIGH);
+        const int b1 = (int)(k1 & 0xFFFFFu), b2 = k2 == NOKEY ? -1 : (int)(k2 & 0xFFFFFu);
+        while (pending) {
+            const bool isPend = pending >> lane & 1u;
+            bool prob = isPend && (isBlocked(k1) || isBlocked(k2));
+            for (unsigned rest = pending; rest; rest &= rest - 1) {
+                const int j = __ffs(rest) - 1;
+                const int bj = __shfl_sync(0xffffffffu, b1, j);
+                prob |= isPend && j < lane && (bj == b1 || bj == b2);
+            }
+            const unsigned pm = __ballot_sync(0xffffffffu, prob);
+            const int first = pm ? __ffs(pm) - 1 : 32;
+            const unsigned cm = first == 32 ? pending : pending & ((1u << first) - 1);
+            const bool acc = (cm >> lane & 1u) && map_accept(P, X, k1, k2);
+            if (acc) commit(i, b1);
+            nmatches += __popc(__ballot_sync(0xffffffffu, acc));
+            pending &= ~cm;
+            __syncwarp();
+            if (first < 32) {
+                const int ip = i0 + first;
+                unsigned long long q1 = __shfl_sync(0xffffffffu, k1, first), q2 = __shfl_sync(0xffffffffu, k2, first);
+                if (isBlocked(q1) || isBlocked(q2)) search_top2(P, X, ip, blocked, lane, q1, q2);
+                if (map_accept(P, X, q1, q2)) {
+                    if (lane == 0) commit(ip, (int)(q1 & 0xFFFFFu));
+                    ++nmatches;
+                }
+                pending &= ~(1u << first);
+                __syncwarp();
+            }
+        }
+    }
+    if (lane == 0) *P.nmatches = nmatches;
+}
+
 // ---- GetFeaturesInArea as a query kernel (parity surface; SearchByProjection uses search_point) -----------
 __global__ void __launch_bounds__(32) orbx_area_kernel(const FrameDev* frames, float x, float y, float r, int minLevel, int maxLevel,
                                                        int* out, int capacity, int* nOut)
@@ -595,6 +735,99 @@ extern "C" int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view*
     TRY(orbx_check(cudaStreamSynchronize(s), "sync", err));
     for (int p = 0; p < nPairs; ++p) {
         if (cur[p].n) std::memcpy(matchOfCur[p], m->hOut + (off[p].assigned - outBase), (size_t)cur[p].n * 4);
+        nmatches[p] = *(const int*)(m->hOut + (oNm - outBase) + (size_t)p * 4);
+    }
+    return ORBX_OK;
+}
+
+extern "C" int orbx_search_local_points(orbx_matcher* m, const orbx_frame_view* frames, const uint8_t* const* occupied,
+                                        const orbx_trackpoint_view* points, int nPairs, float th, float nnratio, int* const* matchOfKey,
+                                        int* nmatches)
+{
+    if (!m || !frames || !points || nPairs < 1 || !matchOfKey || !nmatches) return orbx_fail(ORBX_ERR_ARG, "bad arguments");
+    std::string& err = orbx_err_slot();
+    int maxPts = 0, maxKeys = 0;
+    for (int p = 0; p < nPairs; ++p) {
+        TRY(check_frame(frames + p, true));
+        const orbx_trackpoint_view& t = points[p];
+        if (t.n < 0 || (t.n && (!t.valid || !t.proj || !t.level || !t.view_cos || !t.point_desc || !t.observed))) return orbx_fail(ORBX_ERR_ARG, "bad map point view");
+        if (frames[p].n && !matchOfKey[p]) return orbx_fail(ORBX_ERR_ARG, "match_of_key is NULL");
+        for (int i = 0; i < t.n; ++i)
+            if (t.valid[i] && (t.level[i] < 0 || t.level[i] >= frames[p].nlevels)) return orbx_fail(ORBX_ERR_ARG, "predicted level outside the frame's scale table");
+        maxPts = t.n > maxPts ? t.n : maxPts;
+        maxKeys = frames[p].n > maxKeys ? frames[p].n : maxKeys;
+    }
+    TRY(orbx_check(cudaSetDevice(m->device), "cudaSetDevice", err));
+    struct Off { size_t keys, desc, ur, occ, valid, proj, level, vc, pdesc, obs, cellStart, cellItems, best, best2, assigned; };
+    std::vector<Off> off(nPairs);
+    OrbxPacker pk;
+    const size_t oF = pk.take(sizeof(FrameDev) * (size_t)nPairs), oM = pk.take(sizeof(MapDev) * (size_t)nPairs);
+    for (int p = 0; p < nPairs; ++p) {
+        const size_t nk = frames[p].n, np = points[p].n;
+        off[p].keys = pk.take(nk * 28); off[p].desc = pk.take(nk * 32); off[p].ur = pk.take(frames[p].u_right ? nk * 4 : 0);
+        off[p].occ = pk.take(occupied && occupied[p] ? nk : 0);
+        off[p].valid = pk.take(np); off[p].proj = pk.take(np * 12); off[p].level = pk.take(np * 4); off[p].vc = pk.take(np * 4);
+        off[p].pdesc = pk.take(np * 32); off[p].obs = pk.take(np);
+    }
+    const size_t inBytes = pk.off;
+    for (int p = 0; p < nPairs; ++p) {
+        const size_t nk = frames[p].n, np = points[p].n;
+        off[p].cellStart = pk.take((NCELL + 1) * 4); off[p].cellItems = pk.take(nk * 4 + 4);
+        off[p].best = pk.take(np * 8 + 8); off[p].best2 = pk.take(np * 8 + 8);
+    }
+    const size_t outBase = pk.off;
+    for (int p = 0; p < nPairs; ++p) off[p].assigned = pk.take((size_t)frames[p].n * 4);
+    const size_t oNm = pk.take((size_t)nPairs * 4);
+    const size_t outBytes = pk.off - outBase;
+    TRY(orbx_matcher_grow(m, pk.off, inBytes, outBytes));
+    FrameDev* hf = reinterpret_cast<FrameDev*>(m->hIn + oF);
+    MapDev* hm = reinterpret_cast<MapDev*>(m->hIn + oM);
+    for (int p = 0; p < nPairs; ++p) {
+        const orbx_frame_view& c = frames[p];
+        const orbx_trackpoint_view& t = points[p];
+        const bool occ = occupied && occupied[p];
+        uint8_t *d = m->dBuf, *h = m->hIn;
+        FrameDev D;
+        fill_frame(D, c);
+        D.curKeys = (const orbx_keypoint*)(d + off[p].keys); D.curDesc = d + off[p].desc;
+        D.curUR = c.u_right ? (const float*)(d + off[p].ur) : nullptr;
+        D.cellStart = (int*)(d + off[p].cellStart); D.cellItems = (int*)(d + off[p].cellItems);
+        D.best = (unsigned long long*)(d + off[p].best); D.assigned = (int*)(d + off[p].assigned); D.nmatches = (int*)(d + oNm) + p;
+        hf[p] = D;
+        MapDev X{};
+        X.nPts = t.n; X.th = th; X.nnratio = nnratio;
+        X.valid = d + off[p].valid; X.proj = (const float*)(d + off[p].proj); X.level = (const int*)(d + off[p].level);
+        X.viewCos = (const float*)(d + off[p].vc); X.pdesc = d + off[p].pdesc; X.observed = d + off[p].obs;
+        X.occupied = occ ? d + off[p].occ : nullptr;
+        X.best2 = (unsigned long long*)(d + off[p].best2);
+        hm[p] = X;
+        const size_t nk = c.n, np = t.n;
+        if (nk) {
+            std::memcpy(h + off[p].keys, c.keys_un, nk * 28);
+            std::memcpy(h + off[p].desc, c.desc, nk * 32);
+            if (c.u_right) std::memcpy(h + off[p].ur, c.u_right, nk * 4);
+            if (occ) std::memcpy(h + off[p].occ, occupied[p], nk);
+        }
+        if (np) {
+            std::memcpy(h + off[p].valid, t.valid, np); std::memcpy(h + off[p].proj, t.proj, np * 12);
+            std::memcpy(h + off[p].level, t.level, np * 4); std::memcpy(h + off[p].vc, t.view_cos, np * 4);
+            std::memcpy(h + off[p].pdesc, t.point_desc, np * 32); std::memcpy(h + off[p].obs, t.observed, np);
+        }
+    }
+    cudaStream_t s = m->stream;
+    TRY(orbx_check(cudaMemcpyAsync(m->dBuf, m->hIn, inBytes, cudaMemcpyHostToDevice, s), "H2D local map", err));
+    const FrameDev* df = (const FrameDev*)(m->dBuf + oF);
+    const MapDev* dm = (const MapDev*)(m->dBuf + oM);
+    orbx_grid_kernel<<<dim3(1, nPairs), 256, 0, s>>>(df);
+    if (maxPts) orbx_map_search_kernel<<<dim3((maxPts + 7) / 8, nPairs), 256, 0, s>>>(df, dm);
+    const size_t smem = (size_t)((maxKeys + 31) / 32 + 1) * 4;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(orbx_map_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    orbx_map_resolve_kernel<<<dim3(1, nPairs), 32, smem, s>>>(df, dm);
+    TRY(orbx_check(cudaGetLastError(), "local map search launch", err));
+    TRY(orbx_check(cudaMemcpyAsync(m->hOut, m->dBuf + outBase, outBytes, cudaMemcpyDeviceToHost, s), "D2H matches", err));
+    TRY(orbx_check(cudaStreamSynchronize(s), "sync", err));
+    for (int p = 0; p < nPairs; ++p) {
+        if (frames[p].n) std::memcpy(matchOfKey[p], m->hOut + (off[p].assigned - outBase), (size_t)frames[p].n * 4);
         nmatches[p] = *(const int*)(m->hOut + (oNm - outBase) + (size_t)p * 4);
     }
     return ORBX_OK;

@@ -73,6 +73,29 @@ class MapPointView:
                                  self.observed.ctypes.data)
 
 
+class _TrackPointStruct(C.Structure):  # orbx_trackpoint_view
+    _fields_ = [("n", C.c_int), ("valid", C.c_void_p), ("proj", C.c_void_p), ("level", C.c_void_p), ("view_cos", C.c_void_p),
+                ("point_desc", C.c_void_p), ("observed", C.c_void_p)]
+
+
+class TrackPointView:
+    """The local map as Tracking::SearchLocalPoints hands it to the matcher: per map point mbTrackInView && !isBad(),
+    (mTrackProjX, mTrackProjY, mTrackProjXR), mnTrackScaleLevel, mTrackViewCos, descriptor, Observations() > 0."""
+
+    def __init__(self, valid, proj, level, view_cos, point_desc, observed):
+        self.valid = np.ascontiguousarray(valid, dtype=np.uint8)
+        self.proj = np.ascontiguousarray(proj, dtype=np.float32).reshape(-1, 3)
+        self.level = np.ascontiguousarray(level, dtype=np.int32)
+        self.view_cos = np.ascontiguousarray(view_cos, dtype=np.float32)
+        self.point_desc = np.ascontiguousarray(point_desc, dtype=np.uint8).reshape(-1, 32)
+        self.observed = np.ascontiguousarray(observed, dtype=np.uint8)
+        n = len(self.valid)
+        if not all(len(a) == n for a in (self.proj, self.level, self.view_cos, self.point_desc, self.observed)):
+            raise ValueError("map point arrays differ in length")
+        self.c = _TrackPointStruct(n, self.valid.ctypes.data, self.proj.ctypes.data, self.level.ctypes.data, self.view_cos.ctypes.data,
+                                   self.point_desc.ctypes.data, self.observed.ctypes.data)
+
+
 class Matcher:
     """Owns the device scratch and the CUDA stream of the frame-level functions (orbx_matcher)."""
 
@@ -135,6 +158,30 @@ class Matcher:
         check(lib().orbx_get_features_in_area(self._h, C.addressof(frame.c), float(x), float(y), float(r), int(minLevel), int(maxLevel),
                                               ptr(out), frame.N, C.byref(n)))
         return out[: n.value]
+
+    def SearchLocalPoints(self, F, points, th, occupied=None, nnratio=0.8):
+        """ORBmatcher(nnratio).SearchByProjection(F, vpMapPoints, th) (src/ORBmatcher.cc:45-127). One (frame, local map) pair or
+        lists of pairs -> (match_of_key int32[N], nmatches) per pair. occupied: per keypoint, F.mvpMapPoints[i] holds a point
+        with Observations() > 0 on entry."""
+        single = isinstance(F, FrameView)
+        fr = [F] if single else list(F)
+        pts = [points] if single else list(points)
+        occ = [occupied] if single else (list(occupied) if occupied is not None else [None] * len(fr))
+        if not (len(fr) == len(pts) == len(occ)) or not fr:
+            raise ValueError("need equally many frames, map point views and occupancy arrays")
+        occ = [None if o is None else np.ascontiguousarray(o, dtype=np.uint8) for o in occ]
+        for f, o in zip(fr, occ):
+            if o is not None and len(o) != f.N:
+                raise ValueError("occupied and frame differ in length")
+        n = len(fr)
+        fa, pa = (_FrameStruct * n)(*[f.c for f in fr]), (_TrackPointStruct * n)(*[p.c for p in pts])
+        oa = (C.c_void_p * n)(*[None if o is None else o.ctypes.data for o in occ])
+        outs = [np.full(max(f.N, 1), -1, np.int32) for f in fr]
+        op = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
+        nm = np.zeros(n, np.int32)
+        check(lib().orbx_search_local_points(self._h, fa, oa, pa, n, float(th), float(nnratio), op, ptr(nm)))
+        res = [(o[: f.N], int(k)) for o, f, k in zip(outs, fr, nm)]
+        return res[0] if single else res
 
     def SearchByProjection(self, CurrentFrame, LastFrame, lastPoints, th, bMono=False):
         """One (current, last) pair, or lists of pairs -> (match_of_cur int32[N_cur], nmatches) per pair."""

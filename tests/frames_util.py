@@ -218,3 +218,98 @@ def random_scenario(seed, n_last=300, n_extra=200, W=640, H=400, tz=0.0, yaw=0.0
 def view(cls, d):
     return cls(d["keys_un"], d["desc"], d["u_right"], d["Tcw"], d["fx"], d["fy"], d["cx"], d["cy"], d["mbf"], d["mb"], d["bounds"],
                d["scale_factors"])
+
+
+def py_search_local_points(F, occupied, valid, proj, level, view_cos, point_desc, observed, th, nnratio):
+    """Second restatement of ORBmatcher::SearchByProjection(F, vpMapPoints, th), src/ORBmatcher.cc:45-127."""
+    grid, inv_w, inv_h = py_grid(F["keys_un"], F["bounds"])
+    n = len(F["keys_un"])
+    assigned = [-1] * n
+    blocked = [bool(occupied[i]) if occupied is not None else False for i in range(n)]
+    nmatches = 0
+    for i in range(len(valid)):
+        if not valid[i]:
+            continue
+        lvl = int(level[i])
+        r = f32(2.5) if float(view_cos[i]) > 0.998 else f32(4.0)
+        if th != 1.0:
+            r = f32(r * f32(th))
+        radius = f32(r * f32(F["scale_factors"][lvl]))
+        cand = py_features_in_area(F["keys_un"], grid, inv_w, inv_h, F["bounds"], proj[i][0], proj[i][1], radius, lvl - 1, lvl)
+        if not cand:
+            continue
+        best, best_l, best2, best_l2, best_idx = 256, -1, 256, -1, -1
+        for idx in cand:
+            if blocked[idx]:
+                continue
+            if F["u_right"] is not None and F["u_right"][idx] > 0:
+                if abs(f32(f32(proj[i][2]) - f32(F["u_right"][idx]))) > radius:
+                    continue
+            d = hamming(point_desc[i], F["desc"][idx])
+            if d < best:
+                best2, best, best_l2, best_l, best_idx = best, d, best_l, int(F["keys_un"][idx]["octave"]), idx
+            elif d < best2:
+                best_l2, best2 = int(F["keys_un"][idx]["octave"]), d
+        if best <= 100:
+            if best_l == best_l2 and f32(best) > f32(f32(nnratio) * f32(best2)):
+                continue
+            assigned[best_idx] = i
+            blocked[best_idx] = bool(observed[i])
+            nmatches += 1
+    return np.array(assigned, np.int32), nmatches
+
+
+def local_map_scenario(seed, n_points=400, n_extra=200, W=640, H=400, clones=40, with_uright=True):
+    """A frame and a local map: every map point projects near one keypoint (and near decoys of similar appearance, so
+    the ratio test matters); clones compete for the same keypoint."""
+    rng = np.random.default_rng(seed)
+    sf = (f32(1.2) ** np.arange(8)).astype(f32)
+    proj = np.stack([rng.uniform(0, W, n_points), rng.uniform(0, H, n_points), np.zeros(n_points)], 1).astype(f32)
+    level = rng.integers(0, 8, n_points).astype(np.int32)
+    pdesc = rng.integers(0, 256, (n_points, 32), dtype=np.uint8)
+    if clones:
+        src = rng.integers(0, n_points - clones, clones)
+        proj[n_points - clones:] = proj[src] + rng.normal(0, 0.5, (clones, 3)).astype(f32)
+        level[n_points - clones:] = level[src]
+        pdesc[n_points - clones:] = pdesc[src]
+        pdesc[n_points - clones:, 0] ^= rng.integers(0, 4, clones).astype(np.uint8)
+    n_dec = n_points // 2
+    n_cur = n_points + n_dec + n_extra
+    keys = np.zeros(n_cur, O.KP_DTYPE)
+    desc = np.empty((n_cur, 32), np.uint8)
+
+    def noisy(d, lo, hi):
+        out = d.copy()
+        for k in range(len(out)):
+            for b in rng.choice(256, int(rng.integers(lo, hi)), replace=False):
+                out[k, b >> 3] ^= np.uint8(1 << (b & 7))
+        return out
+
+    keys["x"][:n_points] = proj[:, 0] + rng.normal(0, 1.5, n_points)
+    keys["y"][:n_points] = proj[:, 1] + rng.normal(0, 1.5, n_points)
+    keys["octave"][:n_points] = np.clip(level - rng.integers(0, 2, n_points), 0, 7)
+    desc[:n_points] = noisy(pdesc, 0, 60)
+    dsrc = rng.integers(0, n_points, n_dec)  # decoys: same place, similar descriptor, same or neighbouring level
+    keys["x"][n_points:n_points + n_dec] = proj[dsrc, 0] + rng.normal(0, 2.0, n_dec)
+    keys["y"][n_points:n_points + n_dec] = proj[dsrc, 1] + rng.normal(0, 2.0, n_dec)
+    keys["octave"][n_points:n_points + n_dec] = np.clip(level[dsrc] - rng.integers(0, 2, n_dec), 0, 7)
+    desc[n_points:n_points + n_dec] = noisy(pdesc[dsrc], 20, 80)
+    keys["x"][n_points + n_dec:] = rng.uniform(-5, W + 5, n_extra)
+    keys["y"][n_points + n_dec:] = rng.uniform(-5, H + 5, n_extra)
+    keys["octave"][n_points + n_dec:] = rng.integers(0, 8, n_extra)
+    desc[n_points + n_dec:] = rng.integers(0, 256, (n_extra, 32), dtype=np.uint8)
+    perm = rng.permutation(n_cur)
+    keys, desc = keys[perm], desc[perm]
+    u_right = None
+    if with_uright:
+        u_right = np.where(rng.random(n_cur) < 0.6, keys["x"] - rng.uniform(1, 20, n_cur), -1).astype(f32)
+        inv = np.argsort(perm)
+        proj[:, 2] = u_right[inv[:n_points]] + rng.normal(0, 2.0, n_points)  # mTrackProjXR near the keypoint's uRight
+    bounds = (0.0, float(W), 0.0, float(H))
+    F = dict(keys_un=keys, desc=desc, u_right=u_right, Tcw=np.eye(4, dtype=f32)[:3], fx=500.0, fy=500.0, cx=W / 2, cy=H / 2, mbf=40.0,
+             mb=0.08, bounds=bounds, scale_factors=sf)
+    occupied = (rng.random(n_cur) < 0.1).astype(np.uint8)
+    valid = (rng.random(n_points) < 0.9).astype(np.uint8)
+    view_cos = np.where(rng.random(n_points) < 0.5, 0.9995, 0.97).astype(f32)
+    observed = (rng.random(n_points) < 0.8).astype(np.uint8)
+    return F, occupied, valid, proj, level, view_cos, pdesc, observed

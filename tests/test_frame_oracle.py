@@ -117,3 +117,18 @@ def test_golden_search_fixture():
         got, n = O.search_by_projection(U.view(O.FrameView, cur), U.view(O.FrameView, last), has, world, pdesc, obs, float(th), bool(mono),
                                         bool(ori))
         assert n == int(g[f"case{k}_nmatches"]) and np.array_equal(got, g[f"case{k}_match"])
+
+
+@pytest.mark.parametrize("seed,th,ur,occ", [(0, 1.0, True, True), (1, 3.0, True, False), (2, 5.0, False, True), (3, 1.0, False, False)])
+def test_search_local_points_against_python(seed, th, ur, occ):
+    F, occupied, valid, proj, level, vc, pdesc, obs = U.local_map_scenario(seed, n_points=200, n_extra=100, clones=30, with_uright=ur)
+    occupied = occupied if occ else None
+    got, n = O.search_local_points(U.view(O.FrameView, F), occupied, valid, proj, level, vc, pdesc, obs, th, 0.8)
+    ref, nref = U.py_search_local_points(F, occupied, valid, proj, level, vc, pdesc, obs, th, 0.8)
+    assert n == nref and np.array_equal(got, ref)
+    assert n > 30
+    # the ratio test and the blocking rule are both exercised
+    loose, nl = O.search_local_points(U.view(O.FrameView, F), occupied, valid, proj, level, vc, pdesc, obs, th, 10.0)
+    assert nl > n
+    free, _ = O.search_local_points(U.view(O.FrameView, F), occupied, valid, proj, level, vc, pdesc, np.zeros_like(obs), th, 0.8)
+    assert not np.array_equal(free, got)

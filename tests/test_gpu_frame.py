@@ -226,3 +226,30 @@ def test_batch_from_raw_frames():
     mono.run(n)
     for k in range(n):
         assert np.array_equal(mono.level(k, 0, 0), oracle_stage(rgba[k], None, None, True, 40, H))
+
+
+# ---- N1, second overload: local-map SearchByProjection (src/ORBmatcher.cc:45-127) ------------------------------
+@pytest.mark.parametrize("seed,th,ur,occ,n_points,clones", [(0, 1.0, True, True, 400, 40), (1, 3.0, True, False, 400, 40), (2, 5.0, False, True, 400, 40),
+                                                            (3, 1.0, False, False, 400, 200), (4, 1.0, True, True, 3000, 500), (5, 5.0, True, True, 6000, 1500)])
+def test_search_local_points_parity(seed, th, ur, occ, n_points, clones):
+    big = n_points > 1000
+    F, occupied, valid, proj, level, vc, pdesc, obs = U.local_map_scenario(seed, n_points=n_points, n_extra=n_points // 2, clones=clones, with_uright=ur,
+                                                                          W=1241 if big else 640, H=376 if big else 400)
+    occupied = occupied if occ else None
+    m = pkg.Matcher()
+    for ratio in (0.8, 0.6, 10.0):
+        ref, nref = O.search_local_points(U.view(O.FrameView, F), occupied, valid, proj, level, vc, pdesc, obs, th, ratio)
+        got, n = m.SearchLocalPoints(U.view(pkg.FrameView, F), pkg.TrackPointView(valid, proj, level, vc, pdesc, obs), th, occupied, ratio)
+        assert n == nref and np.array_equal(got, ref), f"ratio {ratio}: {n} vs {nref}, {(got != ref).sum()} keypoints differ"
+    assert nref > 30
+
+
+def test_search_local_points_batch():
+    scen = [U.local_map_scenario(30 + k, n_points=[60, 900, 0, 350][k], n_extra=[10, 200, 30, 0][k], clones=[6, 100, 0, 35][k]) for k in range(4)]
+    m = pkg.Matcher()
+    res = m.SearchLocalPoints([U.view(pkg.FrameView, s[0]) for s in scen], [pkg.TrackPointView(*s[2:]) for s in scen], 3.0,
+                              [s[1] if k % 2 == 0 else None for k, s in enumerate(scen)])
+    for k, s in enumerate(scen):
+        ref, nref = O.search_local_points(U.view(O.FrameView, s[0]), s[1] if k % 2 == 0 else None, *s[2:], 3.0, 0.8)
+        assert res[k][1] == nref and np.array_equal(res[k][0], ref), k
+    assert res[2][1] == 0
