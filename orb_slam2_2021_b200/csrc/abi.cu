@@ -43,8 +43,8 @@ extern "C" int orbx_device_count(void)
 
 static int check_cfg(int nfeatures, float sf, int nlevels, int ini, int mn)
 {
-    if (nfeatures < 1 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !(sf > 1.0f) || ini < 1 || mn < 1 || ini > 254 || mn > ini)
-        return fail(ORBX_ERR_ARG, "bad extractor parameters (need nfeatures>=1, 1<=nlevels<=12, scaleFactor>1, 1<=minTh<=iniTh<=254)");
+    if (nfeatures < 1 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !(sf > 1.0f) || !(sf <= 2.0f) || ini < 1 || mn < 1 || ini > 254 || mn > ini)
+        return fail(ORBX_ERR_ARG, "bad extractor parameters (need nfeatures>=1, 1<=nlevels<=12, 1<scaleFactor<=2, 1<=minTh<=iniTh<=254)");
     return ORBX_OK;
 }
 
@@ -289,7 +289,8 @@ extern "C" int orbx_batch_process(orbx_batch* b, const uint8_t* left, const uint
     if (!b || nFrames < 1 || nFrames > b->maxFrames) return fail(ORBX_ERR_ARG, "bad frame count");
     Engine::HostOutputs o{nLeft, kpsLeft, descLeft, nRight, kpsRight, descRight, uRight, depth};
     // chunks of >= 16 frames keep every kernel's grid well above one wave while the copies of the neighbouring chunks overlap
-    const int chunk = nFrames >= 64 ? (nFrames + 7) / 8 : nFrames >= 32 ? 16 : nFrames;
+    static const int forcedChunks = [] { const char* e = getenv("ORBX_E2E_CHUNKS"); return e ? atoi(e) : 0; }();
+    const int chunk = forcedChunks > 0 ? (nFrames + forcedChunks - 1) / forcedChunks : nFrames >= 64 ? (nFrames + 7) / 8 : nFrames >= 32 ? 16 : nFrames;
     return b->eng.processPipelined(left, right, nFrames, mbf, mb, o, chunk, g_err);
 }
 

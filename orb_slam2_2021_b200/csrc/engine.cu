@@ -464,7 +464,17 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
     if (nFrames < 1 || nFrames * per > maxImgs || !left || (stereo && !right)) { err = "bad process arguments"; return ORBX_ERR_ARG; }
     TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
     if (chunkFrames < 1) chunkFrames = nFrames;
-    const int nChunks = (nFrames + chunkFrames - 1) / chunkFrames;
+    // chunk boundaries: equal chunks, except that the first one may be split so that compute starts after a short copy
+    std::vector<int> bounds{0};
+    {
+        static const int firstDiv = [] { const char* e = getenv("ORBX_E2E_FIRST_DIV"); return e ? atoi(e) : 2; }();
+        if (firstDiv > 1 && chunkFrames >= 2 * firstDiv && nFrames > chunkFrames) {
+            for (int k = 1; k < firstDiv; ++k) bounds.push_back(chunkFrames * k / firstDiv);
+        }
+        for (int f = chunkFrames; f < nFrames; f += chunkFrames) bounds.push_back(f);
+        bounds.push_back(nFrames);
+    }
+    const int nChunks = (int)bounds.size() - 1;
     while ((int)chunkEvents.size() < 2 * nChunks) {
         cudaEvent_t e;
         TRY(orbx_check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate", err));
@@ -473,7 +483,7 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
     const size_t tight = (size_t)rows * cols, Pk = (size_t)P.maxKp;
     const size_t sideStride = tight * (maxImgs / per);
     for (int c = 0; c < nChunks; ++c) {
-        const int f0 = c * chunkFrames, n = std::min(chunkFrames, nFrames - f0);
+        const int f0 = bounds[c], n = bounds[c + 1] - bounds[c];
         cudaEvent_t up = chunkEvents[2 * c], done = chunkEvents[2 * c + 1];
         for (int side = 0; side < per; ++side) {
             const uint8_t* src = (side ? right : left) + f0 * tight;

@@ -8,7 +8,7 @@
 //   H(r) = I[r][sx]*c0 + I[r][sx+1]*c1          (int, < 2^19)
 //   out  = (((b0*(H(sy)>>4))>>16) + ((b1*(H(sy+1)>>4))>>16) + 2) >> 2
 // Reads 1.44x and writes 1x the destination level; each thread produces 4 px x 16 rows (one aligned
-// 32-bit store per row), source taps come through L1.
+// 32-bit store per row).
 #include "orbx_dev.cuh"
 
 struct ResizeTab {
@@ -22,10 +22,20 @@ struct ResizeTab {
 #define RS_TY 4    // row chunks per CTA
 #define RS_ROWS 16  // destination rows per thread
 
-// A thread owns 4 adjacent destination columns and walks down RS_ROWS destination rows: the column
-// tables are read once, and a horizontally interpolated source row that serves two consecutive
-// destination rows (scale 1.2: most of them) is computed once and kept in registers. The row pattern
-// depends on y only, so the reuse test is warp-uniform.
+// A thread owns 4 adjacent destination columns and RS_ROWS destination rows. It walks DOWN THE SOURCE ROWS that
+// those destination rows need (consecutive, because every destination row uses two adjacent source rows and the
+// row step is below 2): each source row is interpolated horizontally exactly once and a destination row is emitted
+// when its second source row arrives. Per source row the thread loads three aligned 32-bit words (they cover
+// the <= 11 bytes its four column pairs can span for scale factors up to 2), realigns them with two funnel
+// shifts, picks the four byte pairs with two PRMT and gets the four horizontal taps from four IDP.2A
+// (16-bit coefficient pair x byte pair, on the FMA pipe). Loads are non-coherent (__ldg) and issued two source
+// rows ahead of their use, so their latency overlaps the arithmetic of the rows before.
+__device__ __forceinline__ void rs_load(const uint8_t* row, int aw, uint32_t& w0, uint32_t& w1, uint32_t& w2)
+{
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(row) + aw;
+    w0 = __ldg(p); w1 = __ldg(p + 1); w2 = __ldg(p + 2);
+}
+
 __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(OrbxParams p, int l, ResizeTab t)
 {
     const OrbxLevel& D = p.lv[l];
@@ -35,50 +45,71 @@ __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(OrbxParams p
     int sp;
     const uint8_t* src = orbx_level_ptr(p, img, l - 1, &sp);
     const int sw = p.lv[l - 1].w, sh = p.lv[l - 1].h;
-    int sx[4], sx1[4], c0[4], c1[4];
+    // column geometry: aligned word index of the first source column, byte shift, PRMT selectors, packed coefficients
+    uint32_t coef[4];
+    int d[4], sx0 = 0;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const int x = min(x0 + i, D.w - 1);  // columns past the level land in the row padding; keep their reads in range
-        sx[i] = t.xofs[x];
-        sx1[i] = min(sx[i] + 1, sw - 1);
-        const int xc = t.xcoef[x];
-        c0[i] = xc & 0xFFFF;
-        c1[i] = xc >> 16;
+        const int sx = t.xofs[x];
+        if (i == 0) sx0 = sx;
+        d[i] = sx - sx0;                      // 0 .. 6 for scale factors up to 2 (checked by the launcher)
+        // the right neighbour is clamped to the last column (there c1 == 0 anyway, OpenCV sets f = 0 for sx >= sw-1):
+        // selecting the same byte twice keeps the read inside the row
+        const int d1 = sx + 1 <= sw - 1 ? d[i] + 1 : d[i];
+        d[i] |= d1 << 4;
+        coef[i] = (uint32_t)t.xcoef[x];       // c0 | c1 << 16
     }
+    // words are read from the aligned address below sx0, but never past the last whole word of the source row pitch
+    const int aw = min(sx0 >> 2, (sp >> 2) - 3);
+    const int sh8 = (sx0 - 4 * aw) * 8;       // 0..24 normally; larger only in the clamped last words of a row
+    const uint32_t selA = (uint32_t)(d[0] & 15) | ((uint32_t)(d[0] >> 4) << 4) | ((uint32_t)(d[1] & 15) << 8) | ((uint32_t)(d[1] >> 4) << 12);
+    const uint32_t selB = (uint32_t)(d[2] & 15) | ((uint32_t)(d[2] >> 4) << 4) | ((uint32_t)(d[3] & 15) << 8) | ((uint32_t)(d[3] >> 4) << 12);
     const int yBeg = (blockIdx.y * RS_TY + threadIdx.y) * RS_ROWS, yEnd = min(yBeg + RS_ROWS, D.h);
+    if (yBeg >= yEnd) return;
     uint8_t* dst = p.pyr + (size_t)img * p.pyrStride + D.off + (size_t)yBeg * D.pitch + x0;
-    int hKeep[4] = {0, 0, 0, 0}, keepRow = -1;
+    const int rBeg = min(max(t.yofs[yBeg], 0), sh - 1), rEnd = min(max(t.yofs[yEnd - 1] + 1, 0), sh - 1);
+    int y = yBeg, yo = t.yofs[y], yc = t.ycoef[y];
+    int sy0 = min(max(yo, 0), sh - 1), sy1 = min(max(yo + 1, 0), sh - 1);
+    uint32_t a0, a1, a2, b0, b1, b2;  // source rows r and r+1 in flight
+    rs_load(src + (size_t)rBeg * sp, aw, a0, a1, a2);
+    rs_load(src + (size_t)min(rBeg + 1, rEnd) * sp, aw, b0, b1, b2);
+    uint32_t hPrev[4] = {0, 0, 0, 0};
 #pragma unroll 1
-    for (int y = yBeg; y < yEnd; ++y, dst += D.pitch) {
-        const int yo = t.yofs[y], yc = t.ycoef[y];
-        const int sy0 = min(max(yo, 0), sh - 1), sy1 = min(max(yo + 1, 0), sh - 1);
-        const int b0 = yc & 0xFFFF, b1 = yc >> 16;
-        int h0[4], h1[4];
-        if (sy0 == keepRow) {
+    for (int r = rBeg; r <= rEnd; ++r) {
+        uint32_t c0w, c1w, c2w;  // row r+2
+        rs_load(src + (size_t)min(r + 2, rEnd) * sp, aw, c0w, c1w, c2w);
+        // bytes sx0 .. sx0+7 of row r
+        uint32_t lo, hi;
+        if (sh8 < 32) { lo = __funnelshift_r(a0, a1, sh8); hi = __funnelshift_r(a1, a2, sh8); }
+        else if (sh8 < 64) { lo = __funnelshift_r(a1, a2, sh8 - 32); hi = a2 >> (sh8 - 32); }
+        else { lo = a2 >> (sh8 - 64); hi = 0; }  // (only in the clamped last words of a row)
+        const uint32_t pA = __byte_perm(lo, hi, selA), pB = __byte_perm(lo, hi, selB);
+        uint32_t hCur[4];
+        hCur[0] = __dp2a_lo(coef[0], pA, 0u);
+        hCur[1] = __dp2a_hi(coef[1], pA, 0u);
+        hCur[2] = __dp2a_lo(coef[2], pB, 0u);
+        hCur[3] = __dp2a_hi(coef[3], pB, 0u);
+        while (y < yEnd && sy1 == r) {  // (at most one destination row per source row for scale factors > 1, two at the clamped edges)
+            const uint32_t bb0 = (uint32_t)(yc & 0xFFFF) << 12, bb1 = (uint32_t)(yc >> 16) << 12;
+            uint32_t v[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) h0[i] = hKeep[i];
-        } else {
-            const uint8_t* r = src + (size_t)sy0 * sp;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) h0[i] = r[sx[i]] * c0[i] + r[sx1[i]] * c1[i];
+            for (int i = 0; i < 4; ++i) {
+                const uint32_t h0 = sy0 == sy1 ? hCur[i] : hPrev[i];
+                // (b * (h >> 4)) >> 16  ==  mulhi(b << 12, h & ~15): h - (h & 15) = 16 (h >> 4), and b << 12 < 2^24
+                v[i] = (__umulhi(bb0, h0 & ~15u) + __umulhi(bb1, hCur[i] & ~15u) + 2u) >> 2;  // in [0,255]: b0 + b1 = 2048
+            }
+            *reinterpret_cast<uint32_t*>(dst) = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
+            dst += D.pitch;  // pitch is a multiple of 16: in-row padding absorbs the tail
+            if (++y < yEnd) {
+                yo = t.yofs[y]; yc = t.ycoef[y];
+                sy0 = min(max(yo, 0), sh - 1); sy1 = min(max(yo + 1, 0), sh - 1);
+            }
         }
-        if (sy1 == sy0) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) h1[i] = h0[i];
-        } else {
-            const uint8_t* r = src + (size_t)sy1 * sp;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) h1[i] = r[sx[i]] * c0[i] + r[sx1[i]] * c1[i];
-        }
-        uint32_t packed = 0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int v = (((b0 * (h0[i] >> 4)) >> 16) + ((b1 * (h1[i] >> 4)) >> 16) + 2) >> 2;  // in [0,255]: b0 + b1 = 2048
-            packed |= (uint32_t)v << (8 * i);
-            hKeep[i] = h1[i];
-        }
-        keepRow = sy1;
-        *reinterpret_cast<uint32_t*>(dst) = packed;  // pitch is a multiple of 16: in-row padding absorbs the tail
+        for (int i = 0; i < 4; ++i) hPrev[i] = hCur[i];
+        a0 = b0; a1 = b1; a2 = b2;
+        b0 = c0w; b1 = c1w; b2 = c2w;
     }
 }
 
