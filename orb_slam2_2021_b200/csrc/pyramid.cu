@@ -41,6 +41,18 @@ __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(OrbxParams p
     const OrbxLevel& D = p.lv[l];
     const int img = blockIdx.z;
     const int x0 = (blockIdx.x * RS_TX + threadIdx.x) * 4;
+    const int yBeg = (blockIdx.y * RS_TY + threadIdx.y) * RS_ROWS, yEnd = min(yBeg + RS_ROWS, D.h);
+    if (yBeg >= yEnd) return;
+    // row tables of this warp's RS_ROWS destination rows, staged in shared memory: the emit loop below reads them with a
+    // dependent compare right behind, which as global loads stalled every destination row
+    __shared__ int ytab[RS_TY][2 * RS_ROWS];
+    if (threadIdx.x < 2 * RS_ROWS) {
+        const int k = threadIdx.x & (RS_ROWS - 1), yy = min(yBeg + k, D.h - 1);
+        ytab[threadIdx.y][threadIdx.x] = threadIdx.x < RS_ROWS ? t.yofs[yy] : t.ycoef[yy];
+    }
+    __syncwarp();
+    const int* yofsS = ytab[threadIdx.y];
+    const int* ycoefS = yofsS + RS_ROWS;
     if (x0 >= D.w) return;
     int sp;
     const uint8_t* src = orbx_level_ptr(p, img, l - 1, &sp);
@@ -65,11 +77,9 @@ __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(OrbxParams p
     const int sh8 = (sx0 - 4 * aw) * 8;       // 0..24 normally; larger only in the clamped last words of a row
     const uint32_t selA = (uint32_t)(d[0] & 15) | ((uint32_t)(d[0] >> 4) << 4) | ((uint32_t)(d[1] & 15) << 8) | ((uint32_t)(d[1] >> 4) << 12);
     const uint32_t selB = (uint32_t)(d[2] & 15) | ((uint32_t)(d[2] >> 4) << 4) | ((uint32_t)(d[3] & 15) << 8) | ((uint32_t)(d[3] >> 4) << 12);
-    const int yBeg = (blockIdx.y * RS_TY + threadIdx.y) * RS_ROWS, yEnd = min(yBeg + RS_ROWS, D.h);
-    if (yBeg >= yEnd) return;
     uint8_t* dst = p.pyr + (size_t)img * p.pyrStride + D.off + (size_t)yBeg * D.pitch + x0;
-    const int rBeg = min(max(t.yofs[yBeg], 0), sh - 1), rEnd = min(max(t.yofs[yEnd - 1] + 1, 0), sh - 1);
-    int y = yBeg, yo = t.yofs[y], yc = t.ycoef[y];
+    const int rBeg = min(max(yofsS[0], 0), sh - 1), rEnd = min(max(yofsS[yEnd - 1 - yBeg] + 1, 0), sh - 1);
+    int y = yBeg, yo = yofsS[0], yc = ycoefS[0];
     int sy0 = min(max(yo, 0), sh - 1), sy1 = min(max(yo + 1, 0), sh - 1);
     uint32_t a0, a1, a2, b0, b1, b2;  // source rows r and r+1 in flight
     rs_load(src + (size_t)rBeg * sp, aw, a0, a1, a2);
@@ -102,7 +112,7 @@ __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(OrbxParams p
             *reinterpret_cast<uint32_t*>(dst) = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
             dst += D.pitch;  // pitch is a multiple of 16: in-row padding absorbs the tail
             if (++y < yEnd) {
-                yo = t.yofs[y]; yc = t.ycoef[y];
+                yo = yofsS[y - yBeg]; yc = ycoefS[y - yBeg];
                 sy0 = min(max(yo, 0), sh - 1); sy1 = min(max(yo + 1, 0), sh - 1);
             }
         }
