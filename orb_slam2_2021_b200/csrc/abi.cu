@@ -171,7 +171,7 @@ extern "C" int orbx_stereo_match(orbx_extractor* l, orbx_extractor* r, const orb
         TRY(orbx_check(cudaMalloc(&l->dD, k * 4), "stereo scratch", g_err));
         TRY(orbx_check(cudaMalloc(&l->dSad, k * 4), "stereo scratch", g_err));
         TRY(orbx_check(cudaMalloc(&l->dNm, 4), "stereo scratch", g_err));
-        TRY(orbx_check(cudaMalloc(&l->dSorted, k * sizeof(uint4)), "stereo scratch", g_err));
+        TRY(orbx_check(cudaMalloc(&l->dSorted, 3 * k * sizeof(uint4)), "stereo scratch", g_err));
         TRY(orbx_check(cudaMalloc(&l->dBin, ((size_t)EL.rows + 1) * 4), "stereo scratch", g_err));
         l->scratchKp = EL.P.maxKp;
         l->scratchRows = EL.rows;

@@ -324,7 +324,7 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
         TRY(dalloc(this, &SP.depth, fr * P.maxKp, "depth", err));
         TRY(dalloc(this, &SP.sad, fr * P.maxKp, "sad", err));
         TRY(dalloc(this, &SP.nMatched, fr, "nMatched", err));
-        TRY(dalloc(this, &SP.rsorted, fr * P.maxKp, "rsorted", err));
+        TRY(dalloc(this, &SP.rsorted, fr * P.maxKp * 3, "rsorted", err));  // record + descriptor: 3 x uint4
         TRY(dalloc(this, &SP.binStart, fr * (rows + 1), "binStart", err));
         SP.binR = orbx_stereo_bin_radius(cfg.scale.data(), cfg.nlevels);
     }
@@ -418,7 +418,7 @@ void Engine::launchStereo(int f0, int nFrames, float mbf, float mb, cudaStream_t
     const size_t o = (size_t)f0;
     sp.frames = nFrames; sp.mbf = mbf; sp.mb = mb;
     sp.uRight += o * SP.maxKp; sp.depth += o * SP.maxKp; sp.sad += o * SP.maxKp; sp.nMatched += o;
-    sp.rsorted += o * SP.maxKp; sp.binStart += o * (rows + 1);
+    sp.rsorted += o * SP.maxKp * 3; sp.binStart += o * (rows + 1);
     orbx_launch_stereo(p, p, sp, s);
 }
 

@@ -98,8 +98,8 @@ struct OrbxStereoParams {
     int* sad;       // [frames][maxKp] best SAD of accepted matches, -1 otherwise
     int* nMatched;  // [frames]
     // right keypoints of each frame counting-sorted by (int)y (the row-band table of src/Frame.cc:532-549 in
-    // data-parallel form): rsorted[j] = {x bits, minr | maxr<<16, octave, iR}; bin b = binStart[b]..binStart[b+1]
-    uint4* rsorted;  // [frames][maxKp]
+    // data-parallel form): rsorted[3j] = {x bits, minr | maxr<<16, octave, iR}, rsorted[3j+1..3j+2] = descriptor; bin b = binStart[b]..binStart[b+1]
+    uint4* rsorted;  // [frames][maxKp][3]
     int* binStart;   // [frames][rows0 + 1]
     int binR;        // a left keypoint on row v can only match right keypoints binned in [v-binR, v+binR]
 };

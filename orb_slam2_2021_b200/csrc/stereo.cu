@@ -74,7 +74,8 @@ __global__ void __launch_bounds__(256) orbx_stereo_bin_kernel(OrbxParams pl, Orb
     int* bs = sp.binStart + (size_t)f * (rows + 1);
     for (int i = tid; i <= rows; i += 256) bs[i] = hist[i];
     __syncthreads();
-    uint4* rs = sp.rsorted + (size_t)f * sp.maxKp;
+    uint4* rs = sp.rsorted + (size_t)f * sp.maxKp * 3;  // record = {x, row band, octave, iR} + the 32-byte descriptor
+    const uint4* descR = reinterpret_cast<const uint4*>(pr.outDesc + (size_t)imgR * pr.maxKp * 32);
     for (int i = tid; i < nR; i += 256) {
         const KpRec kr = kpsR[i];
         const int yb = min(max((int)floorf(kr.y), 0), rows - 1);
@@ -83,7 +84,9 @@ __global__ void __launch_bounds__(256) orbx_stereo_bin_kernel(OrbxParams pl, Orb
         const int maxr = min(max((int)ceilf(orbx_fadd(kr.y, r)), -32768), 32767);
         const int minr = min(max((int)floorf(orbx_fsub(kr.y, r)), -32768), 32767);
         const int pos = atomicAdd(&hist[yb], 1);
-        rs[pos] = make_uint4(__float_as_uint(kr.x), ((unsigned)minr & 0xFFFFu) | ((unsigned)maxr << 16), (unsigned)kr.octave, (unsigned)i);
+        rs[3 * pos] = make_uint4(__float_as_uint(kr.x), ((unsigned)minr & 0xFFFFu) | ((unsigned)maxr << 16), (unsigned)kr.octave, (unsigned)i);
+        rs[3 * pos + 1] = descR[2 * i];
+        rs[3 * pos + 2] = descR[2 * i + 1];
     }
 }
 
@@ -100,9 +103,7 @@ __global__ void __launch_bounds__(ST_WARPS * 32) orbx_stereo_match_kernel(OrbxPa
     int outSad = -1;
 
     const KpRec* kpsL = reinterpret_cast<const KpRec*>(pl.outKp) + (size_t)imgL * pl.maxKp;
-    const KpRec* kpsR = reinterpret_cast<const KpRec*>(pr.outKp) + (size_t)imgR * pr.maxKp;
     const uint8_t* descL = pl.outDesc + (size_t)imgL * pl.maxKp * 32;
-    const uint8_t* descR = pr.outDesc + (size_t)imgR * pr.maxKp * 32;
 
     const float uL = kpsL[iL].x, vL = kpsL[iL].y;
     const int levelL = kpsL[iL].octave;
@@ -111,31 +112,37 @@ __global__ void __launch_bounds__(ST_WARPS * 32) orbx_stereo_match_kernel(OrbxPa
     const float minU = orbx_fsub(uL, maxD), maxU = uL;
 
     unsigned best = (100u << 16);  // TH_HIGH, iR 0
+    float bestX = 0.f;             // uR of this lane's best candidate
     if (!(maxU < 0) && row >= 0 && row < sp.rows0) {
         const uint4 a0 = *reinterpret_cast<const uint4*>(descL + (size_t)iL * 32);
         const uint4 a1 = *reinterpret_cast<const uint4*>(descL + (size_t)iL * 32 + 16);
         const int rlo = max(row - sp.binR, 0), rhi = min(row + sp.binR + 1, sp.rows0);
         const int* bs = sp.binStart + (size_t)f * (sp.rows0 + 1);
-        const uint4* rs = sp.rsorted + (size_t)f * sp.maxKp;
+        const uint4* rs = sp.rsorted + (size_t)f * sp.maxKp * 3;
         const int jEnd = bs[rhi];
         for (int j = bs[rlo] + lane; j < jEnd; j += 32) {
-            const uint4 rec = rs[j];
+            const uint4 rec = rs[3 * j];
             const int octR = (int)rec.z;
             if (octR < levelL - 1 || octR > levelL + 1) continue;  // :588
             const float uR = __uint_as_float(rec.x);
             if (!(uR >= minU && uR <= maxU)) continue;  // :593
             const int minr = (int)(short)(rec.y & 0xFFFFu), maxr = (int)(short)(rec.y >> 16);
             if (row < minr || row > maxr) continue;  // iR is listed in vRowIndices[row] (:539-549)
-            const unsigned d = (unsigned)hamming256(a0, a1, descR + (size_t)rec.w * 32);
-            best = min(best, (d << 16) | rec.w);
+            // the descriptor travels with the record (same or next cache line): no dependent trip to the descriptor array
+            const unsigned d = (unsigned)hamming256(a0, a1, reinterpret_cast<const uint8_t*>(rs + 3 * j + 1));
+            const unsigned key = (d << 16) | rec.w;
+            if (key < best) { best = key; bestX = uR; }
         }
     }
+    const unsigned mine = best;
 #pragma unroll
     for (int s = 16; s; s >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, s));
-    const int bestDist = (int)(best >> 16), bestR = (int)(best & 0xFFFF);
+    const int bestDist = (int)(best >> 16);
+    // uR of the winner comes from the lane that found it (iR is unique, so exactly one lane holds the minimum)
+    const unsigned won = __ballot_sync(0xffffffffu, mine == best);
+    const float uR0 = __shfl_sync(0xffffffffu, bestX, __ffs(won) - 1);
 
     if (bestDist < 75) {  // thOrbDist = (TH_HIGH + TH_LOW)/2, :527, :606
-        const float uR0 = kpsR[bestR].x;
         const float s = pl.lv[levelL].invScale;
         const float su = roundf(orbx_fmul(uL, s)), sv = roundf(orbx_fmul(vL, s)), sr = roundf(orbx_fmul(uR0, s));
         const int cu = (int)su, cv = (int)sv, cr = (int)sr;
