@@ -21,6 +21,7 @@
 #include "orbx_dev.cuh"
 
 #define OCT_THREADS 256
+#define OCT_K 8  // candidates per thread kept in registers (levels with up to OCT_THREADS*OCT_K candidates)
 
 struct OctSmem {
     short4* box[2];     // x0,y0,x1,y1 per list position (ping-pong)
@@ -132,6 +133,10 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
     S.inV[0] = ptr; ptr += cap;
     S.inV[1] = ptr; ptr += cap;
 
+    // ping-pong node arrays as plain pointers (indexing S.box[cur] with a run-time `cur` put the struct in local memory)
+    short4 *boxC = S.box[0], *boxN = S.box[1];
+    int *cntC = S.cnt[0], *cntN = S.cnt[1];
+    uint8_t *inVC = S.inV[0], *inVN = S.inV[1];
     uint32_t* candXY = p.candXY + (size_t)img * p.candTotal + L.candBase;
     uint8_t* candRs = p.candRs + (size_t)img * p.candTotal + L.candBase;
     uint16_t* label = p.label + (size_t)img * p.candTotal + L.candBase;
@@ -179,18 +184,44 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
             const int k = S.childCnt[i];
             S.newPos[i] = (uint16_t)m;
             if (k > 0) {
-                S.box[0][m] = make_short4((short)(int)orbx_fmul(hX, (float)i), 0, (short)(int)orbx_fmul(hX, (float)(i + 1)),
+                boxC[m] = make_short4((short)(int)orbx_fmul(hX, (float)i), 0, (short)(int)orbx_fmul(hX, (float)(i + 1)),
                                           (short)(L.h - 2 * (ORBX_EDGE - 3)));
-                S.cnt[0][m] = k;
-                S.inV[0][m] = 0;
+                cntC[m] = k;
+                inVC[m] = 0;
                 ++m;
             }
         }
         sh_m = m;
     }
     __syncthreads();
-    for (int i = tid; i < n; i += OCT_THREADS) label[i] = S.newPos[label[i]];
-    int m = sh_m, cur = 0, phase = 1;
+    // Candidates of this thread (i = tid + k*OCT_THREADS) live in registers for the passes below: position and node label
+    // are read and rewritten in every pass, and as global-memory traffic their latency was most of the kernel's time.
+    // Levels with more candidates than fit (large images) take the same loops through global memory.
+    const bool inReg = n <= OCT_THREADS * OCT_K;
+    uint32_t rxy[OCT_K];
+    int rlb[OCT_K];
+#pragma unroll
+    for (int k = 0; k < OCT_K; ++k) {
+        const int i = tid + k * OCT_THREADS;
+        rxy[k] = (inReg && i < n) ? candXY[i] : 0u;
+        rlb[k] = (inReg && i < n) ? (int)S.newPos[label[i]] : 0;
+    }
+    if (!inReg)
+        for (int i = tid; i < n; i += OCT_THREADS) label[i] = S.newPos[label[i]];
+// BODY sees the candidate index i, its packed position XY and its label LB (assignable)
+#define OCT_FOR_CANDIDATES(BODY)                                                            \
+    if (inReg) {                                                                            \
+        _Pragma("unroll") for (int k_ = 0; k_ < OCT_K; ++k_) {                              \
+            const int i = tid + k_ * OCT_THREADS;                                           \
+            if (i < n) { const uint32_t XY = rxy[k_]; int& LB = rlb[k_]; BODY }             \
+        }                                                                                   \
+    } else {                                                                                \
+        for (int i = tid; i < n; i += OCT_THREADS) {                                        \
+            const uint32_t XY = candXY[i]; int LB = label[i]; const int lb0_ = LB; BODY     \
+            if (LB != lb0_) label[i] = (uint16_t)LB;                                        \
+        }                                                                                   \
+    }
+    int m = sh_m, phase = 1;
     __syncthreads();
 
     // ---- passes
@@ -198,25 +229,25 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
         // (1) nodes to split and their creation order
         int Sn;
         if (phase == 1) {
-            for (int i = tid; i < m; i += OCT_THREADS) S.scan[i] = S.cnt[cur][i] > 1;
+            for (int i = tid; i < m; i += OCT_THREADS) S.scan[i] = cntC[i] > 1;
             __syncthreads();
             block_excl_scan(S.scan, m, wsum);
             Sn = S.scan[m];
             for (int i = tid; i < m; i += OCT_THREADS) {
-                const bool f = S.cnt[cur][i] > 1;
+                const bool f = cntC[i] > 1;
                 S.rankOf[i] = f ? S.scan[i] : -1;
                 if (f) S.byRank[S.scan[i]] = i;
             }
         } else {
-            for (int i = tid; i < m; i += OCT_THREADS) S.scan[i] = S.inV[cur][i];
+            for (int i = tid; i < m; i += OCT_THREADS) S.scan[i] = inVC[i];
             __syncthreads();
             block_excl_scan(S.scan, m, wsum);
             Sn = S.scan[m];
             for (int i = tid; i < m; i += OCT_THREADS) {
                 S.rankOf[i] = -1;
-                if (S.inV[cur][i]) {
+                if (inVC[i]) {
                     S.vlist[S.scan[i]] = i;
-                    tmp[S.scan[i]] = S.cnt[cur][i];
+                    tmp[S.scan[i]] = cntC[i];
                 }
             }
             __syncthreads();
@@ -241,10 +272,7 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
             *(int4*)&S.childCnt[pos * 4] = make_int4(0, 0, 0, 0);
         }
         __syncthreads();
-        for (int i = tid; i < n; i += OCT_THREADS) {
-            const int lb = label[i];
-            if (S.rankOf[lb] >= 0) atomicAdd(&S.childCnt[lb * 4 + quadrant(candXY[i], S.box[cur][lb])], 1);
-        }
+        OCT_FOR_CANDIDATES(if (S.rankOf[LB] >= 0) atomicAdd(&S.childCnt[LB * 4 + quadrant(XY, boxC[LB])], 1);)
         __syncthreads();
 
         // (3) growth per node in creation order, stop index t*
@@ -262,23 +290,22 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
         }
         const int tstar = sh_tstar;
         const int T = S.scan[tstar] + tstar;
-        const int nxt = cur ^ 1;
 
         // (4) new list: reversed children first, then the unsplit nodes in their old order
         for (int r = tid; r < tstar; r += OCT_THREADS) {
             const int pos = S.byRank[r];
             const int4 c = *(int4*)&S.childCnt[pos * 4];
             const int cc[4] = {c.x, c.y, c.z, c.w};
-            const short4 pb = S.box[cur][pos];
+            const short4 pb = boxC[pos];
             int k = S.scan[r] + r, multi = 0;
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 if (cc[q] > 0) {
                     const int np = T - 1 - k;
                     S.newPos[pos * 4 + q] = (uint16_t)np;
-                    S.box[nxt][np] = child_box(pb, q);
-                    S.cnt[nxt][np] = cc[q];
-                    S.inV[nxt][np] = cc[q] > 1;
+                    boxN[np] = child_box(pb, q);
+                    cntN[np] = cc[q];
+                    inVN[np] = cc[q] > 1;
                     multi += cc[q] > 1;
                     ++k;
                 }
@@ -296,22 +323,19 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
             if (!(r >= 0 && r < tstar)) {
                 const int np = T + S.vlist[i];
                 S.movePos[i] = (uint16_t)np;
-                S.box[nxt][np] = S.box[cur][i];
-                S.cnt[nxt][np] = S.cnt[cur][i];
-                S.inV[nxt][np] = 0;
+                boxN[np] = boxC[i];
+                cntN[np] = cntC[i];
+                inVN[np] = 0;
             }
         }
         __syncthreads();
         // (5) relabel the candidates
-        for (int i = tid; i < n; i += OCT_THREADS) {
-            const int lb = label[i];
-            const int r = S.rankOf[lb];
-            label[i] = (r >= 0 && r < tstar) ? S.newPos[lb * 4 + quadrant(candXY[i], S.box[cur][lb])] : S.movePos[lb];
-        }
+        OCT_FOR_CANDIDATES(const int r = S.rankOf[LB];
+                           LB = (r >= 0 && r < tstar) ? S.newPos[LB * 4 + quadrant(XY, boxC[LB])] : S.movePos[LB];)
         const int prev = m;
         m = T + (m - tstar);
         const int nexp = sh_nexp;
-        cur = nxt;
+        { short4* tb = boxC; boxC = boxN; boxN = tb; int* tc = cntC; cntC = cntN; cntN = tc; uint8_t* tv = inVC; inVC = inVN; inVN = tv; }
         __syncthreads();
         if (m >= N || m == prev) break;                    // :672, :737
         if (phase == 1 && m + 3 * nexp > N) phase = 2;      // :676
@@ -320,8 +344,8 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
     // ---- best response per node, first candidate wins ties (:744-763); output in list order
     for (int i = tid; i < m; i += OCT_THREADS) S.best[i] = 0;
     __syncthreads();
-    for (int i = tid; i < n; i += OCT_THREADS)
-        atomicMax(&S.best[label[i]], ((unsigned)candRs[i] << 24) | (0xFFFFFFu - (unsigned)i));
+    OCT_FOR_CANDIDATES((void)XY; atomicMax(&S.best[LB], ((unsigned)candRs[i] << 24) | (0xFFFFFFu - (unsigned)i));)
+#undef OCT_FOR_CANDIDATES
     __syncthreads();
     uint2* keep = p.keep + (size_t)img * p.keepTotal + L.keepBase;
     for (int i = tid; i < m; i += OCT_THREADS) {
