@@ -14,7 +14,7 @@
 //     in 16-byte units, so the box starts 16 px left of the tile, measured with tools/ubench/tma_test2.cu)
 //     and the CTA waits on an mbarrier; the engine zero-fills what lies outside the level, and tiles on
 //     a level edge then mirror the reflect-101 halo in shared memory (columns first, then whole rows);
-//   * warp w owns output rows 8w..8w+7, lane L the four output columns 4L..4L+3. It walks down 14 rows;
+//   * warp w owns output rows 16w..16w+15, lane L the four output columns 4L..4L+3. It walks down 22 rows;
 //     per row the HORIZONTAL 7-tap sums of its 4 pixels come straight from the raw bytes of three
 //     32-bit words with 10 byte dot products (IDP.4A: measured full rate, on the FMA pipe, so no unpacking
 //     on the ALU pipe that bounds the other kernels); a 7-row register window of those sums feeds the
@@ -29,7 +29,7 @@ struct OrbxTile {
     uint8_t level, pad[3];
 };
 
-#define BL_WARPS 8
+#define BL_WARPS 4
 #define BL_RS (ORBX_BLUR_TH / BL_WARPS)  // output rows per warp
 #define BL_SH (ORBX_BLUR_TH + 6)         // tile rows incl. halo
 #define BL_SW 160                        // tile columns incl. halo (TMA box width)
