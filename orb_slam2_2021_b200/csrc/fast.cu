@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     extern __shared__ __align__(128) uint8_t fast_smem[];
     __shared__ __align__(8) uint64_t bar;
     __shared__ int listCnt;
-    __shared__ int warpTasks[FAST_WARPS];
+    __shared__ int warpTasks[FAST_WARPS], warpNz[FAST_WARPS];
 
     uint8_t* T = fast_smem;                                                     // raw box [rhMax][BW]
     uint16_t* A = reinterpret_cast<uint16_t*>(fast_smem + ((rhMax * BW + 127) & ~127));  // A[y][j] = I(xa + j, y0 + y), xa = x0 & ~3
@@ -219,8 +219,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
             if (hit) nz[nnz + __popc(bh & lt)] = (uint16_t)task;
             nnz += __popc(bh);
         }
-        __syncthreads();  // every warp is done reading warpTasks[] / lists of pass 1
-        if (lane == 0) warpTasks[warp] = nnz;
+        if (lane == 0) warpNz[warp] = nnz;
     }
     __syncthreads();
 
@@ -228,7 +227,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     // neighbours in the strength map. Maxima go to a CTA list kept[] = key | m << 16, key = y*64 + x (interior coords).
     uint32_t* kept = reinterpret_cast<uint32_t*>(A);  // A/B are dead after pass 2
     bool anyIni = false;
-    const int nz0 = warpTasks[0], nz1 = nz0 + warpTasks[1], nz2 = nz1 + warpTasks[2], nzAll = nz2 + warpTasks[3];
+    const int nz0 = warpNz[0], nz1 = nz0 + warpNz[1], nz2 = nz1 + warpNz[2], nzAll = nz2 + warpNz[3];
 #pragma unroll 1
     for (int g = threadIdx.x; g < nzAll; g += FAST_THREADS) {
         const int lw = (g >= nz0) + (g >= nz1) + (g >= nz2);
