@@ -46,9 +46,9 @@ __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(OrbxParams p
     // row tables of this warp's RS_ROWS destination rows, staged in shared memory: the emit loop below reads them with a
     // dependent compare right behind, which as global loads stalled every destination row
     __shared__ int ytab[RS_TY][2 * RS_ROWS];
-    if (threadIdx.x < 2 * RS_ROWS) {
-        const int k = threadIdx.x & (RS_ROWS - 1), yy = min(yBeg + k, D.h - 1);
-        ytab[threadIdx.y][threadIdx.x] = threadIdx.x < RS_ROWS ? t.yofs[yy] : t.ycoef[yy];
+    for (int e = threadIdx.x; e < 2 * RS_ROWS; e += RS_TX) {
+        const int k = e & (RS_ROWS - 1), yy = min(yBeg + k, D.h - 1);
+        ytab[threadIdx.y][e] = e < RS_ROWS ? t.yofs[yy] : t.ycoef[yy];
     }
     __syncwarp();
     const int* yofsS = ytab[threadIdx.y];
