@@ -284,7 +284,7 @@ extern "C" int orbx_compute_bow(orbx_vocabulary* v, const uint8_t* const* desc, 
     int cap = 32;
     while (cap < maxN) cap <<= 1;
     const size_t smem = (size_t)cap * 12;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(orbx_bow_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 32 * 1024) cudaFuncSetAttribute(orbx_bow_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     orbx_bow_reduce_kernel<<<nFrames, 1024, smem, s>>>(df, cap);
     TRY(orbx_check(cudaGetLastError(), "bow launch", err));
     TRY(orbx_check(cudaMemcpyAsync(m->hOut, m->dBuf + outBase, outBytes, cudaMemcpyDeviceToHost, s), "D2H bow", err));

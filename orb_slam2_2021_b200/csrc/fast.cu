@@ -302,6 +302,10 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     const int listCap = 64 * ((rhMax * nwMax + FAST_THREADS - 1) / FAST_THREADS);
     const size_t smem = (size_t)((rhMax * boxW + 127) & ~127) + (size_t)2 * rhMax * sa * 2 + (size_t)(rhMax - 4) * sa * 2 +
                         (size_t)2 * FAST_WARPS * listCap * 2;
+    if (smem > 32 * 1024) {  // tall cells on small levels: static + dynamic may pass 48 KB; per-device attribute, set on every such launch
+        if (sa == 48) cudaFuncSetAttribute(orbx_fast_kernel<48>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        else cudaFuncSetAttribute(orbx_fast_kernel<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    }
     if (sa == 48)
         orbx_fast_kernel<48><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax, listCap);
     else

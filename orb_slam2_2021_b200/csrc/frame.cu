@@ -728,7 +728,7 @@ extern "C" int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view*
     orbx_grid_kernel<<<dim3(1, nPairs), 256, 0, s>>>(dd);
     if (maxLast) orbx_project_search_kernel<<<dim3((maxLast + 7) / 8, nPairs), 256, 0, s>>>(dd);
     const size_t smem = (size_t)((maxCur + 31) / 32 + 1) * 4;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(orbx_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 32 * 1024) cudaFuncSetAttribute(orbx_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     orbx_resolve_kernel<<<dim3(1, nPairs), 32, smem, s>>>(dd);
     TRY(orbx_check(cudaGetLastError(), "search launch", err));
     TRY(orbx_check(cudaMemcpyAsync(m->hOut, m->dBuf + outBase, outBytes, cudaMemcpyDeviceToHost, s), "D2H matches", err));
@@ -821,7 +821,7 @@ extern "C" int orbx_search_local_points(orbx_matcher* m, const orbx_frame_view* 
     orbx_grid_kernel<<<dim3(1, nPairs), 256, 0, s>>>(df);
     if (maxPts) orbx_map_search_kernel<<<dim3((maxPts + 7) / 8, nPairs), 256, 0, s>>>(df, dm);
     const size_t smem = (size_t)((maxKeys + 31) / 32 + 1) * 4;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(orbx_map_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 32 * 1024) cudaFuncSetAttribute(orbx_map_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     orbx_map_resolve_kernel<<<dim3(1, nPairs), 32, smem, s>>>(df, dm);
     TRY(orbx_check(cudaGetLastError(), "local map search launch", err));
     TRY(orbx_check(cudaMemcpyAsync(m->hOut, m->dBuf + outBase, outBytes, cudaMemcpyDeviceToHost, s), "D2H matches", err));

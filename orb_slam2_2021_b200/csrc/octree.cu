@@ -363,7 +363,7 @@ void orbx_launch_octree(const OrbxParams& p, const void* cellTable, cudaStream_t
     int cap = 0;
     for (int l = 0; l < p.nlevels; ++l) cap = p.lv[l].keepCap > cap ? p.lv[l].keepCap : cap;
     const size_t smem = octree_smem_bytes(cap);
-    if (smem > 48 * 1024)  // per-device attribute: set on every launch that needs it
+    if (smem > 32 * 1024)  // static + dynamic above 48 KB needs the opt-in; per-device attribute, set on every such launch
         cudaFuncSetAttribute(orbx_octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 grid(p.nlevels, p.imgs);
     orbx_octree_kernel<<<grid, OCT_THREADS, smem, s>>>(p, (const OrbxCellRec*)cellTable);

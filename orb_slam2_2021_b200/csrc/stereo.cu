@@ -298,7 +298,7 @@ __global__ void __launch_bounds__(256) orbx_stereo_median_kernel(OrbxParams pl, 
 void orbx_launch_stereo(const OrbxParams& pl, const OrbxParams& pr, const OrbxStereoParams& sp, cudaStream_t s)
 {
     const size_t binSmem = (size_t)(sp.rows0 + 1) * sizeof(int);
-    if (binSmem > 48 * 1024)  // per-device attribute: set on every launch that needs it
+    if (binSmem > 32 * 1024)  // static + dynamic above 48 KB needs the opt-in; per-device attribute, set on every such launch
         cudaFuncSetAttribute(orbx_stereo_bin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)binSmem);
     orbx_stereo_bin_kernel<<<sp.frames, 256, binSmem, s>>>(pl, pr, sp);
     dim3 grid((sp.maxKp + ST_WARPS - 1) / ST_WARPS, sp.frames);

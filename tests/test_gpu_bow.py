@@ -24,7 +24,7 @@ def test_compute_bow_parity(k, L, levelsup, ragged):
     ov, gv = O.Vocabulary(L, *voc_arrays), pkg.ORBVocabulary(L, *voc_arrays)
     assert gv.n_words == ov.n_words
     sets = [B.features_near_words(voc_arrays[2], voc_arrays[1], n, seed=n) if n else np.zeros((0, 32), np.uint8)
-            for n in (0, 1, 33, 500, 2000, 8192)]
+            for n in (0, 1, 33, 500, 2000, 3000, 8192)]  # 3000: 48 KB of dynamic shared memory exactly
     for d in sets:  # one frame per call
         same(gv.transform(d, levelsup), ov.transform(d, levelsup))
     for got, d in zip(gv.transform(sets, levelsup), sets):  # all frames in one call (ragged sizes)

@@ -325,3 +325,43 @@ def test_cpp_shim_reference_signature(tmp_path):
     assert np.array_equal(dl, odl) and np.array_equal(dr, odr)
     our, odp = O.stereo_match(ol, orr, okl, odl, okr, odr, bf, bf / fx)
     assert_stereo_equal(ur, dp, our, odp, "shim/stereo")
+
+
+@pytest.mark.parametrize("nf,sf,nl,ini,mn,W,H", [
+    (500, 1.1, 8, 20, 7, 640, 480),      # fine pyramid
+    (800, 1.5, 5, 20, 7, 752, 480),      # coarse pyramid: source windows of the resize span up to 7 bytes
+    (600, 2.0, 4, 12, 7, 800, 600),      # the largest supported scale factor
+    (300, 1.2, 1, 20, 7, 320, 240),      # a single level: no resize at all
+    (3000, 1.2, 12, 30, 30, 1024, 768),  # 12 levels (the ABI maximum), minTh == iniTh
+    (50, 1.3, 6, 254, 1, 640, 400),      # threshold extremes: the fallback to minTh fires in almost every cell
+    (1500, 1.25, 8, 20, 7, 1023, 511),   # odd sizes: pitches with padding, ragged tiles and cells
+    (1200, 1.2, 8, 20, 7, 1280, 720),    # width a multiple of 16: no row padding anywhere
+])
+def test_extractor_parameter_space(nf, sf, nl, ini, mn, W, H):
+    """Other extractor parameters than the BASELINE configs, bit-exact against the oracle incl. every pyramid level."""
+    cfg = (W, H, nf, nl, sf, ini, mn, 500.0, 40.0)
+    left, right = synth.stereo_pair(W, H, 200 + nl)
+    ex_l, ex_r = pkg.ORBextractor(nf, sf, nl, ini, mn), pkg.ORBextractor(nf, sf, nl, ini, mn)
+    ol, orr, okl, odl, okr, odr = oracle_pair(cfg, left, right)
+    kl, dl = ex_l(left)
+    kr, dr = ex_r(right)
+    assert_kps_equal(kl, okl, "L")
+    assert_kps_equal(kr, okr, "R")
+    assert np.array_equal(dl, odl) and np.array_equal(dr, odr)
+    for l, lev in enumerate(ex_l.mvImagePyramid):
+        assert np.array_equal(lev, ol.level(l)), f"pyramid level {l}"
+    ur, dp = pkg.compute_stereo_matches(ex_l, ex_r, kl, dl, kr, dr, 40.0, 40.0 / 500.0)
+    our, odp = O.stereo_match(ol, orr, okl, odl, okr, odr, 40.0, 40.0 / 500.0)
+    assert_stereo_equal(ur, dp, our, odp, "stereo")
+    # the same through the batch engine (other launch geometry: two images per launch)
+    b = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, 1, stereo=True)
+    out = b.process(left[None], right[None], mbf=40.0, mb=40.0 / 500.0)
+    assert_kps_equal(out["kps_left"][0][:out["n_left"][0]], okl, "batch L")
+    assert np.array_equal(out["desc_right"][0][:out["n_right"][0]], odr)
+    assert_stereo_equal(out["u_right"][0][:len(okl)], out["depth"][0][:len(okl)], our, odp, "batch stereo")
+
+
+def test_scale_factor_above_two_is_rejected():
+    with pytest.raises(pkg.OrbxError) as ei:
+        pkg.ORBextractor(1000, 2.5, 4, 20, 7)
+    assert ei.value.code == pkg._lib.ERR_ARG
