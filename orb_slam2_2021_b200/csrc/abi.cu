@@ -23,6 +23,7 @@ struct orbx_extractor {
     uint4* dSorted = nullptr; int* dBin = nullptr;
     int scratchRows = 0;
     int scratchKp = 0;
+    uint8_t* hOut = nullptr; size_t hOutCap = 0;  // pinned staging of orbx_extract's results
 };
 
 struct orbx_batch {
@@ -64,6 +65,7 @@ extern "C" void orbx_destroy(orbx_extractor* e)
 {
     if (!e) return;
     if (e->dU) { cudaSetDevice(e->device); cudaFree(e->dU); cudaFree(e->dD); cudaFree(e->dSad); cudaFree(e->dNm); cudaFree(e->dSorted); cudaFree(e->dBin); }
+    if (e->hOut) { cudaSetDevice(e->device); cudaFreeHost(e->hOut); }
     delete e;
 }
 
@@ -105,15 +107,28 @@ extern "C" int orbx_extract(orbx_extractor* e, const uint8_t* image, int rows, i
     Engine& E = *e->eng;
     TRY(E.uploadSingle(image, stride, g_err));
     TRY(E.runExtract(1, g_err));
-    int cnt = 0;
-    TRY(orbx_check(cudaMemcpyAsync(&cnt, E.P.outCnt, sizeof(int), cudaMemcpyDeviceToHost, E.stream), "D2H count", g_err));
+    // One round trip: the count and (speculatively) every record the caller's buffers can take come down together into
+    // pinned staging; the second dependent copy + synchronisation of a count-first protocol costs more than the bytes.
+    const int take = capacity < E.P.maxKp ? capacity : E.P.maxKp;
+    const size_t need = 16 + (size_t)take * 60;
+    if (need > e->hOutCap) {
+        if (e->hOut) cudaFreeHost(e->hOut);
+        e->hOut = nullptr; e->hOutCap = 0;
+        TRY(orbx_check(cudaHostAlloc(&e->hOut, need, cudaHostAllocDefault), "pinned output staging", g_err));
+        e->hOutCap = need;
+    }
+    TRY(orbx_check(cudaMemcpyAsync(e->hOut, E.P.outCnt, sizeof(int), cudaMemcpyDeviceToHost, E.stream), "D2H count", g_err));
+    if (take > 0) {
+        TRY(orbx_check(cudaMemcpyAsync(e->hOut + 16, E.P.outKp, (size_t)take * 28, cudaMemcpyDeviceToHost, E.stream), "D2H kps", g_err));
+        TRY(orbx_check(cudaMemcpyAsync(e->hOut + 16 + (size_t)take * 28, E.P.outDesc, (size_t)take * 32, cudaMemcpyDeviceToHost, E.stream), "D2H desc", g_err));
+    }
     TRY(E.sync(g_err));
     e->hasRun = true;
+    const int cnt = *reinterpret_cast<const int*>(e->hOut);
     if (cnt > capacity) return fail(ORBX_ERR_CAPACITY, "keypoint capacity too small (see orbx_max_keypoints)");
     if (cnt > 0) {
-        TRY(orbx_check(cudaMemcpyAsync(kps, E.P.outKp, (size_t)cnt * 28, cudaMemcpyDeviceToHost, E.stream), "D2H kps", g_err));
-        TRY(orbx_check(cudaMemcpyAsync(desc, E.P.outDesc, (size_t)cnt * 32, cudaMemcpyDeviceToHost, E.stream), "D2H desc", g_err));
-        TRY(E.sync(g_err));
+        std::memcpy(kps, e->hOut + 16, (size_t)cnt * 28);
+        std::memcpy(desc, e->hOut + 16 + (size_t)take * 28, (size_t)cnt * 32);
     }
     *n = cnt;
     return ORBX_OK;

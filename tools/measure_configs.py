@@ -164,6 +164,22 @@ def gpu_legs(cfg, stereo, L, R, batch):
             ts.append(time.perf_counter() - t0)
     out["single_frame_ms"] = round(statistics.median(ts) * 1e3, 3)
     del el, er
+    # the same frame through the batch engine with a batch of one: both images share every launch, one round trip
+    one = StereoFrameBatch(nf, sf, nl, ini, mn, H, W, 1, stereo=stereo)
+    p1l, p1r = PinnedArray((1, H, W), np.uint8), PinnedArray((1, H, W), np.uint8)
+    o1 = one.alloc_outputs(1, pinned=True)
+    ts = []
+    for i in range(44):
+        k = i % len(L)
+        p1l.array[0] = L[k]
+        if stereo:
+            p1r.array[0] = R[k]
+        t0 = time.perf_counter()
+        one.process(p1l.array, p1r.array if stereo else None, bf if stereo else 0.0, bf / fx if stereo else 1.0, out=o1)
+        if i >= 4:
+            ts.append(time.perf_counter() - t0)
+    out["single_frame_batch_engine_ms"] = round(statistics.median(ts) * 1e3, 3)
+    del one
     # batch engine: device-resident and end to end
     idx = np.arange(batch) % len(L)
     bl = np.ascontiguousarray(L[idx])
