@@ -58,8 +58,7 @@ __global__ void __launch_bounds__(256) orbx_bow_descend_kernel(VocDev V, const B
                              __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
             key = ((unsigned)dist << 8) | (unsigned)lane;
         }
-#pragma unroll
-        for (int o = 16; o; o >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, o));
+        key = __reduce_min_sync(0xffffffffu, key);  // REDUX.MIN: first minimum in child order
         node = V.children[b + (int)(key & 255u)];
         if (lvl == V.nidLevel) nid = node;
         if (V.childStart[node + 1] == V.childStart[node]) break;  // isLeaf() = no children

@@ -40,17 +40,20 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) orbx_describe_kernel(OrbxPara
     const int img = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int slot = blockIdx.x * DESC_WARPS + warp;
-    // slot -> (level, k): keepBase/keepCap are multiples of 8, so a CTA never straddles two levels (uniform search)
-    int level = 0;
-#pragma unroll 1
-    for (int l = 1; l < p.nlevels; ++l)
-        if ((int)blockIdx.x * DESC_WARPS >= p.lv[l].keepBase) level = l;
+    // slot -> (level, k): keepBase/keepCap are multiples of 8, so a CTA never straddles two levels. Lane l looks at level l
+    // (keepBase is ascending): the highest set bit of the ballot is the level — one indexed constant load instead of a loop.
+    const int kbase = lane < p.nlevels ? p.lv[lane].keepBase : 0x7fffffff;
+    const int level = 31 - __clz((int)__ballot_sync(0xffffffffu, (int)blockIdx.x * DESC_WARPS >= kbase));
     const OrbxLevel& L = p.lv[level];
     const int k = slot - L.keepBase;
-    if (k >= p.keepCnt[img * p.nlevels + level]) return;
-    const int outIdx = k + p.keepOfs[img * p.nlevels + level];
-
+    // the three loads are independent: issue them together, before the exit test (slot < keepTotal always)
+    // (the exit test reads all three — offsets, coordinates and scores are never negative — or ptxas sinks two of the loads below the
+    // exit and the round trips serialise)
+    const int kcnt = p.keepCnt[img * p.nlevels + level];
+    const int kofs = p.keepOfs[img * p.nlevels + level];
     const uint2 kp = p.keep[(size_t)img * p.keepTotal + slot];
+    if (((kcnt - 1 - k) | kofs | (int)kp.x | (int)kp.y) < 0) return;  // k >= kcnt
+    const int outIdx = k + kofs;
     const int cx = (int)(kp.x & 0xFFFF) + (ORBX_EDGE - 3), cy = (int)(kp.x >> 16) + (ORBX_EDGE - 3);  // :843-844
 
     // ---- both patches by TMA (the warp is the unit: its own mbarrier, no CTA barrier anywhere)
@@ -92,11 +95,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) orbx_describe_kernel(OrbxPara
         m10 = (int)accU - um * (int)accS;
         m01 = v * (int)accS;
     }
-#pragma unroll
-    for (int o = 16; o; o >>= 1) {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-    }
+    m10 = __reduce_add_sync(0xffffffffu, m10);  // REDUX.SUM: one instruction instead of a 5-step butterfly
+    m01 = __reduce_add_sync(0xffffffffu, m01);
     const float angle = orbx_fast_atan2((float)m01, (float)m10);
 
     // ---- rBRIEF on the blurred level (samples from the shared-memory box: 32-bit addresses, no 64-bit pointer math)
@@ -130,16 +130,12 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) orbx_describe_kernel(OrbxPara
         fx = orbx_fmul(fx, L.scale);
         fy = orbx_fmul(fy, L.scale);
     }
-    uint32_t word;
-    switch (lane) {
-        case 0: word = __float_as_uint(fx); break;
-        case 1: word = __float_as_uint(fy); break;
-        case 2: word = __float_as_uint((float)L.patchSize); break;
-        case 3: word = __float_as_uint(angle); break;
-        case 4: word = __float_as_uint((float)kp.y); break;
-        case 5: word = (uint32_t)level; break;
-        default: word = 0xFFFFFFFFu; break;  // class_id = -1
-    }
+    // (a select tree on the lane bits: a switch compiles to a divergent jump table)
+    const uint32_t w01 = (lane & 1) ? __float_as_uint(fy) : __float_as_uint(fx);
+    const uint32_t w23 = (lane & 1) ? __float_as_uint(angle) : __float_as_uint((float)L.patchSize);
+    const uint32_t w45 = (lane & 1) ? (uint32_t)level : __float_as_uint((float)kp.y);
+    const uint32_t w03 = (lane & 2) ? w23 : w01, w47 = (lane & 2) ? 0xFFFFFFFFu : w45;  // word 6: class_id = -1
+    const uint32_t word = (lane & 4) ? w47 : w03;
     uint32_t* okp = reinterpret_cast<uint32_t*>((uint8_t*)p.outKp + ((size_t)img * p.maxKp + outIdx) * 28);
     if (lane < 7) okp[lane] = word;
 }

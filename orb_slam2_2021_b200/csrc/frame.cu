@@ -287,8 +287,7 @@ __global__ void __launch_bounds__(32) orbx_resolve_kernel(const FrameDev* frames
             const int ev = P.events[e], bin = ev >> 20;
             if (bin != ind1 && bin != ind2 && bin != ind3) { P.assigned[ev & 0xFFFFF] = -1; ++removed; }
         }
-#pragma unroll
-        for (int o = 16; o; o >>= 1) removed += __shfl_xor_sync(0xffffffffu, removed, o);
+        removed = __reduce_add_sync(0xffffffffu, removed);
         nmatches -= removed;
     }
     if (lane == 0) *P.nmatches = nmatches;

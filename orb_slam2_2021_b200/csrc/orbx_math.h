@@ -78,17 +78,26 @@ ORBX_HD float orbx_fast_atan2(float y, float x)
 // by pi/2 and the classic degree-13/14 minimax kernels, all in float64 with explicit fma, then one
 // rounding to float32. The float64 result is accurate to <1 ulp(double), so the float32 value is
 // the correctly rounded sin/cos except for ~1e-8 of inputs (tests/test_math.py measures it).
+// (device: the 15 double constants sit in constant memory so that DMUL/DFMA take them as c[][] operands; as literals each
+// costs two moves into a register pair, and the whole warp runs this once per keypoint)
+#define ORBX_SINCOS_CONSTANTS                                                                                            \
+    6.36619772367581382433e-01, 1.57079632679489655800e+00, 6.12323399573676603587e-17, -1.66666666666666324348e-01,     \
+        8.33333333332248946124e-03, -1.98412698298579493134e-04, 2.75573137070700676789e-06, -2.50507602534068634195e-08, \
+        1.58969099521155010221e-10, 4.16666666666666019037e-02, -1.38888888888741095749e-03, 2.48015872894767294178e-05,  \
+        -2.75573143513906633035e-07, 2.08757232129817482790e-09, -1.13596475577881948265e-11
+#if defined(__CUDACC__)
+static __constant__ double orbx_sincos_dev[15] = {ORBX_SINCOS_CONSTANTS};
+#endif
 ORBX_HD void orbx_sincosf(float xf, float* s_out, float* c_out)
 {
-    const double TWO_OVER_PI = 6.36619772367581382433e-01;
-    const double PIO2_HI = 1.57079632679489655800e+00;
-    const double PIO2_LO = 6.12323399573676603587e-17;
-    const double S1 = -1.66666666666666324348e-01, S2 = 8.33333333332248946124e-03,
-                 S3 = -1.98412698298579493134e-04, S4 = 2.75573137070700676789e-06,
-                 S5 = -2.50507602534068634195e-08, S6 = 1.58969099521155010221e-10;
-    const double C1 = 4.16666666666666019037e-02, C2 = -1.38888888888741095749e-03,
-                 C3 = 2.48015872894767294178e-05, C4 = -2.75573143513906633035e-07,
-                 C5 = 2.08757232129817482790e-09, C6 = -1.13596475577881948265e-11;
+#if defined(__CUDA_ARCH__)
+    const double* K = orbx_sincos_dev;
+#else
+    static const double K[15] = {ORBX_SINCOS_CONSTANTS};
+#endif
+    const double TWO_OVER_PI = K[0], PIO2_HI = K[1], PIO2_LO = K[2];
+    const double S1 = K[3], S2 = K[4], S3 = K[5], S4 = K[6], S5 = K[7], S6 = K[8];
+    const double C1 = K[9], C2 = K[10], C3 = K[11], C4 = K[12], C5 = K[13], C6 = K[14];
     double x = (double)xf;
     double kd = rint(orbx_dmul(x, TWO_OVER_PI));
     int k = (int)kd;

@@ -135,8 +135,7 @@ __global__ void __launch_bounds__(ST_WARPS * 32) orbx_stereo_match_kernel(OrbxPa
         }
     }
     const unsigned mine = best;
-#pragma unroll
-    for (int s = 16; s; s >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, s));
+    best = __reduce_min_sync(0xffffffffu, best);  // REDUX.MIN
     const int bestDist = (int)(best >> 16);
     // uR of the winner comes from the lane that found it (iR is unique, so exactly one lane holds the minimum)
     const unsigned won = __ballot_sync(0xffffffffu, mine == best);
@@ -191,9 +190,7 @@ __global__ void __launch_bounds__(ST_WARPS * 32) orbx_stereo_match_kernel(OrbxPa
                 }
             }
 #pragma unroll
-            for (int j = 0; j < 6; ++j)
-#pragma unroll
-                for (int sft = 16; sft; sft >>= 1) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], sft);
+            for (int j = 0; j < 6; ++j) acc[j] = __reduce_add_sync(0xffffffffu, acc[j]);  // REDUX.SUM; the halves cannot carry (see above)
             int sad[11];
 #pragma unroll
             for (int k = 0; k < 11; ++k) sad[k] = (int)((k & 1) ? acc[k >> 1] >> 16 : acc[k >> 1] & 0xFFFFu);
