@@ -35,6 +35,17 @@ struct OrbxTile {
 #define BL_SW 160                        // tile columns incl. halo (TMA box width)
 #define BL_XH 16                         // columns left of the tile in the box
 
+// byte weights of the horizontal dot products, as constant-bank operands of IDP.4A (no moves into registers)
+#define PK(a, b, c, d) ((uint32_t)(a) | ((uint32_t)(b) << 8) | ((uint32_t)(c) << 16) | ((uint32_t)(d) << 24))
+__constant__ uint32_t c_blurW[10] = {PK(0, 18, 34, 48), PK(56, 48, 34, 18),                    // pixel 0: wm, w0
+                                     PK(0, 0, 18, 34),  PK(48, 56, 48, 34), PK(18, 0, 0, 0),    // pixel 1: wm, w0, w1
+                                     PK(0, 0, 0, 18),   PK(34, 48, 56, 48), PK(34, 18, 0, 0),   // pixel 2
+                                     PK(18, 34, 48, 56), PK(48, 34, 18, 0)};                    // pixel 3: w0, w1
+// vertical weights for IDP.2A (low / high byte pair of a word): rows 2t..2t+6 of the window -> {18,34 | 48,56} {48,34 | 18,0};
+// rows 2t+1..2t+7 -> {0,18 | 34,48} {56,48 | 34,18}
+__constant__ uint32_t c_blurV[4] = {PK(18, 34, 48, 56), PK(48, 34, 18, 0), PK(0, 18, 34, 48), PK(56, 48, 34, 18)};
+#undef PK
+
 __global__ void __launch_bounds__(BL_WARPS * 32) orbx_blur_kernel(OrbxParams p, const OrbxTile* tiles, const CUtensorMap* maps)
 {
     __shared__ __align__(128) uint8_t src[BL_SH * BL_SW];
@@ -85,34 +96,48 @@ __global__ void __launch_bounds__(BL_WARPS * 32) orbx_blur_kernel(OrbxParams p, 
     const int lane = tid & 31, warp = tid >> 5;
     const uint32_t* col = reinterpret_cast<const uint32_t*>(src) + (warp * BL_RS) * (BL_SW / 4) + (BL_XH / 4 - 1) + lane;
     const int gx = x0 + 4 * lane;
-    const bool store = gx < w;
-    uint8_t* dst = p.blur + (size_t)img * p.blurStride + L.boff + (size_t)(y0 + warp * BL_RS) * L.bpitch + gx;
-#define PK(a, b, c, d) ((uint32_t)(a) | ((uint32_t)(b) << 8) | ((uint32_t)(c) << 16) | ((uint32_t)(d) << 24))
-    uint32_t h[7][4];  // horizontal sums (<= 256*255) of the lane's 4 pixels, last 7 rows
+    // rows this lane stores: none for columns right of the level, else up to the level's last row
+    const int nst = gx < w ? min(BL_RS, h_ - (y0 + warp * BL_RS)) : 0;
+    const int bpitch = L.bpitch;
+    uint8_t* dst = p.blur + (size_t)img * p.blurStride + L.boff + (size_t)(y0 + warp * BL_RS) * bpitch + gx;
+    // Two tile rows per step: their horizontal sums (+128, <= 65408) are packed per pixel as u16x2 (even row low, odd row high);
+    // four such pairs P[0..3] = tile rows 2t .. 2t+7 are the window of output rows 2t (rows 2t..2t+6) and 2t+1 (rows
+    // 2t+1..2t+7), and the vertical pass is four 2-term dot products (IDP.2A) per pixel instead of 3 additions + 4 multiply-adds.
+    uint32_t P[4][4];
 #pragma unroll
-    for (int s = 0; s < BL_RS + 6; ++s) {
-        const uint32_t wm = col[s * (BL_SW / 4)], w0 = col[s * (BL_SW / 4) + 1], w1 = col[s * (BL_SW / 4) + 2];
+    for (int m = 0; m < (BL_RS + 6) / 2; ++m) {
+        uint32_t hh[2][4];
 #pragma unroll
-        for (int k = 0; k < 6; ++k)
+        for (int r = 0; r < 2; ++r) {
+            const int s = 2 * m + r;
+            const uint32_t wm = col[s * (BL_SW / 4)], w0 = col[s * (BL_SW / 4) + 1], w1 = col[s * (BL_SW / 4) + 2];
+            // pixel i of word w0 has its 7 taps at bytes i-3 .. i+3 relative to w0's byte 0 (weights: c_blurW). Every sum
+            // starts at 128: the weights add up to 256, so the vertical pass comes out 2^15 high — the rounding term
+            hh[r][0] = __dp4a(w0, c_blurW[1], __dp4a(wm, c_blurW[0], 128u));
+            hh[r][1] = __dp4a(w1, c_blurW[4], __dp4a(w0, c_blurW[3], __dp4a(wm, c_blurW[2], 128u)));
+            hh[r][2] = __dp4a(w1, c_blurW[7], __dp4a(w0, c_blurW[6], __dp4a(wm, c_blurW[5], 128u)));
+            hh[r][3] = __dp4a(w1, c_blurW[9], __dp4a(w0, c_blurW[8], 128u));
+        }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) h[k][i] = h[k + 1][i];
-        // pixel i of word w0 has its 7 taps at bytes i-3 .. i+3 relative to w0's byte 0
-        h[6][0] = __dp4a(w0, PK(56, 48, 34, 18), __dp4a(wm, PK(0, 18, 34, 48), 0u));
-        h[6][1] = __dp4a(w1, PK(18, 0, 0, 0), __dp4a(w0, PK(48, 56, 48, 34), __dp4a(wm, PK(0, 0, 18, 34), 0u)));
-        h[6][2] = __dp4a(w1, PK(34, 18, 0, 0), __dp4a(w0, PK(34, 48, 56, 48), __dp4a(wm, PK(0, 0, 0, 18), 0u)));
-        h[6][3] = __dp4a(w1, PK(48, 34, 18, 0), __dp4a(w0, PK(18, 34, 48, 56), 0u));
-        if (s >= 6) {
-            uint32_t v[4];
+        for (int i = 0; i < 4; ++i) {
+            P[0][i] = P[1][i]; P[1][i] = P[2][i]; P[2][i] = P[3][i];
+            P[3][i] = __byte_perm(hh[0][i], hh[1][i], 0x5410);
+        }
+        if (m >= 3) {
+            uint32_t va[4], vb[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-                v[i] = 18u * (h[0][i] + h[6][i]) + 34u * (h[1][i] + h[5][i]) + 48u * (h[2][i] + h[4][i]) + 56u * h[3][i] + 32768u;
+            for (int i = 0; i < 4; ++i) {
+                va[i] = __dp2a_hi(P[3][i], c_blurV[1], __dp2a_lo(P[2][i], c_blurV[1], __dp2a_hi(P[1][i], c_blurV[0], __dp2a_lo(P[0][i], c_blurV[0], 0u))));
+                vb[i] = __dp2a_hi(P[3][i], c_blurV[3], __dp2a_lo(P[2][i], c_blurV[3], __dp2a_hi(P[1][i], c_blurV[2], __dp2a_lo(P[0][i], c_blurV[2], 0u))));
+            }
             // byte 2 of each sum (sums < 2^24)
-            const uint32_t packed = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
-            const int oy = s - 6;
-            if (store && y0 + warp * BL_RS + oy < h_) *reinterpret_cast<uint32_t*>(dst + (size_t)oy * L.bpitch) = packed;
+            const uint32_t pa = __byte_perm(__byte_perm(va[0], va[1], 0x0062), __byte_perm(va[2], va[3], 0x0062), 0x5410);
+            const uint32_t pb = __byte_perm(__byte_perm(vb[0], vb[1], 0x0062), __byte_perm(vb[2], vb[3], 0x0062), 0x5410);
+            if (2 * (m - 3) < nst) *reinterpret_cast<uint32_t*>(dst) = pa;
+            if (2 * (m - 3) + 1 < nst) *reinterpret_cast<uint32_t*>(dst + bpitch) = pb;
+            dst += 2 * bpitch;
         }
     }
-#undef PK
 }
 
 void orbx_launch_blur(const OrbxParams& p, const void* tileTable, int nTiles, const void* levelMaps, cudaStream_t s)
