@@ -83,6 +83,9 @@ __device__ __forceinline__ void fast_strength2(const uint16_t* a, const uint16_t
     m1 = max((int)(br >> 16) - 256, 256 - (int)(dk >> 16));
 }
 
+// c_recip[n] = ceil(65536 / n): floor(t / n) = (t * c_recip[n]) >> 16 exactly while t * n < 65536 (here t <= 128, n <= 31)
+__constant__ uint32_t c_recip[32] = {0, 65536, 32768, 21846, 16384, 13108, 10923, 9363, 8192, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4096, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115};
+
 template <int SA>
 __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap)
 {
@@ -138,30 +141,32 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     uint16_t* list = lists + warp * listCap;
     int ntask = 0;  // warp-uniform
     {
+        // thread = (word column j, row y) with j fixed: 128/nw rows per step, so that the column tests and all addresses are
+        // loop invariant or advance by a constant (threads past the last whole row idle: < nw of 128)
         const int nw = (o + rw + 4) >> 2;  // words covering A-columns 0 .. o+rw (one past the ROI, read by boundary pairs)
-        const uint32_t* T32 = reinterpret_cast<const uint32_t*>(T) + ((cell.x0 & 15) >> 2);
-        const int total = rh * nw;
-        // (row, word) of this thread's element, advanced by FAST_THREADS elements per step without a division
-        const int qStep = FAST_THREADS / nw, rStep = FAST_THREADS - qStep * nw;
-        int y = (int)(((float)threadIdx.x + 0.5f) * __frcp_rn((float)nw));
-        int j = threadIdx.x - y * nw;
+        const uint32_t rcp = c_recip[nw];
+        const int qStep = (int)((FAST_THREADS * rcp) >> 16);  // rows per step
+        const int yq = (int)((threadIdx.x * rcp) >> 16);
+        const int j = threadIdx.x - yq * nw;
+        const bool active = yq < qStep;
+        // pair q (A-columns 4j+2q, +1) holds an interior pixel iff 4j+2q+1 >= ca0 and 4j+2q < ca0+iw
+        const bool v0 = active && 4 * j + 1 >= ca0 && 4 * j < ca0 + iw, v1 = active && 4 * j + 3 >= ca0 && 4 * j + 2 < ca0 + iw;
+        const uint32_t* tw = reinterpret_cast<const uint32_t*>(T) + ((cell.x0 & 15) >> 2) + yq * (BW / 4) + j;
+        uint2* pa = reinterpret_cast<uint2*>(A + yq * SA + 4 * j);
+        uint2* pb = reinterpret_cast<uint2*>(B + yq * SA + 4 * j);
         const uint32_t K = 0x01010101u * (uint32_t)(0x7F - min(tmin, 0x7F));
         const unsigned lt = (1u << lane) - 1;
-        const int steps = (total + FAST_THREADS - 1) / FAST_THREADS;
+        const int yEnd = active ? rh : 0;
+        uint32_t code = (uint32_t)((yq - 3) * 256 + 2 * j);  // list entry of pair 0: (y - 3) << 8 | pair column
 #pragma unroll 1
-        for (int st = 0; st < steps; ++st) {
-            const int i = st * FAST_THREADS + threadIdx.x;
-            bool k0 = false, k1 = false;
-            if (i < total) {
-                const uint32_t* tw = T32 + y * (BW / 4) + j;
+        for (int y = yq, ys = 0; ys < rh; ys += qStep, y += qStep) {  // (ys: uniform trip count for the ballots)
+            unsigned kk = 0;
+            if (y < yEnd) {
                 const uint32_t w = tw[0], wn = tw[1], wp = tw[-1];  // inside the box: (x0&15)/4 + nw + 1 <= BW/4; tw[-1] of the
                 const uint32_t t = __funnelshift_r(wp, w, 24);     // first word is junk that only feeds masked pixels
-                *reinterpret_cast<uint2*>(A + y * SA + 4 * j) = make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
-                *reinterpret_cast<uint2*>(B + y * SA + 4 * j) = make_uint2(__byte_perm(t, 0, 0x4140), __byte_perm(t, 0, 0x4342));
-                const int iy = y - 3;
-                // pair q (A-columns 4j+2q, +1) holds an interior pixel iff 4j+2q+1 >= ca0 and 4j+2q < ca0+iw
-                const bool v0 = 4 * j + 1 >= ca0 && 4 * j < ca0 + iw, v1 = 4 * j + 3 >= ca0 && 4 * j + 2 < ca0 + iw;
-                if (iy >= 0 && iy < ih && (v0 || v1)) {
+                pa[0] = make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
+                pb[0] = make_uint2(__byte_perm(t, 0, 0x4140), __byte_perm(t, 0, 0x4342));
+                if ((unsigned)(y - 3) < (unsigned)ih && (v0 || v1)) {
                     uint32_t m = 0x80808080u;
                     if (tmin < 0x7F) {  // (thresholds >= 127 skip the pre-test: every interior pair is a task)
                         const uint32_t up = tw[-3 * (BW / 4)], dn = tw[3 * (BW / 4)];
@@ -172,25 +177,27 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
                         const uint32_t f4 = ((a4 & 0x7F7F7F7Fu) + K) | a4, f12 = ((a12 & 0x7F7F7F7Fu) + K) | a12;
                         m = (f0 | f8) & (f4 | f12);
                     }
-                    k0 = v0 && (m & 0x00008080u);
-                    k1 = v1 && (m & 0x80800000u);
+                    kk = (v0 && (m & 0x00008080u) ? 1u : 0u) | (v1 && (m & 0x80800000u) ? 2u : 0u);
                 }
             }
-            const unsigned b0 = __ballot_sync(0xffffffffu, k0), b1 = __ballot_sync(0xffffffffu, k1);
+            const unsigned b0 = __ballot_sync(0xffffffffu, kk & 1), b1 = __ballot_sync(0xffffffffu, kk & 2);
             const int n0 = __popc(b0);
-            if (k0) list[ntask + __popc(b0 & lt)] = (uint16_t)(((y - 3) << 8) | (2 * j));
-            if (k1) list[ntask + n0 + __popc(b1 & lt)] = (uint16_t)(((y - 3) << 8) | (2 * j + 1));
+            if (kk & 1) list[ntask + __popc(b0 & lt)] = (uint16_t)code;
+            if (kk & 2) list[ntask + n0 + __popc(b1 & lt)] = (uint16_t)(code + 1);
             ntask += n0 + __popc(b1);
-            j += rStep;
-            y += qStep;
-            if (j >= nw) { j -= nw; ++y; }
+            tw += qStep * (BW / 4);
+            pa += qStep * (SA / 4);
+            pb += qStep * (SA / 4);
+            code += (uint32_t)qStep << 8;
         }
     }
     if (lane == 0) warpTasks[warp] = ntask;
     __syncthreads();
     // ---- pass 2: the min/max network on the surviving pairs (results go to the map by position). The four warp lists
     // are walked as one sequence so that every warp step but the last is full.
+    // position g of the concatenated sequence lives at lists[g + adj], adj = (list index) * listCap - (tasks in the lists before)
     const int nt0 = warpTasks[0], nt1 = nt0 + warpTasks[1], nt2 = nt1 + warpTasks[2], ntAll = nt2 + warpTasks[3];
+    const int ta1 = listCap - nt0, ta2 = 2 * listCap - nt1, ta3 = 3 * listCap - nt2;
     {
         const uint16_t* pevn = A;      // even dx: pair (A[c+dx], A[c+dx+1]), c even
         const uint16_t* podd = B + 1;  // odd dx:  pair (B[c+dx+1], B[c+dx+2]) = (I(c+dx), I(c+dx+1))
@@ -203,9 +210,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
             bool hit = false;
             int task = 0;
             if (g < ntAll) {
-                const int lw = (g >= nt0) + (g >= nt1) + (g >= nt2);
-                const int li = g - (lw == 0 ? 0 : lw == 1 ? nt0 : lw == 2 ? nt1 : nt2);
-                task = lists[lw * listCap + li];
+                task = lists[g + (g >= nt2 ? ta3 : g >= nt1 ? ta2 : g >= nt0 ? ta1 : 0)];
                 const int y = task >> 8, c = 2 * (task & 255);
                 int m0, m1;
                 fast_strength2<SA>(podd + (y + 3) * SA + c, pevn + (y + 3) * SA + c, m0, m1);
@@ -228,11 +233,11 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     uint32_t* kept = reinterpret_cast<uint32_t*>(A);  // A/B are dead after pass 2
     bool anyIni = false;
     const int nz0 = warpNz[0], nz1 = nz0 + warpNz[1], nz2 = nz1 + warpNz[2], nzAll = nz2 + warpNz[3];
+    const uint16_t* nzLists = lists + FAST_WARPS * listCap;
+    const int za1 = listCap - nz0, za2 = 2 * listCap - nz1, za3 = 3 * listCap - nz2;
 #pragma unroll 1
     for (int g = threadIdx.x; g < nzAll; g += FAST_THREADS) {
-        const int lw = (g >= nz0) + (g >= nz1) + (g >= nz2);
-        const int li = g - (lw == 0 ? 0 : lw == 1 ? nz0 : lw == 2 ? nz1 : nz2);
-        const int task = lists[(FAST_WARPS + lw) * listCap + li], y = task >> 8, cc = 2 * (task & 255);
+        const int task = nzLists[g + (g >= nz2 ? za3 : g >= nz1 ? za2 : g >= nz0 ? za1 : 0)], y = task >> 8, cc = 2 * (task & 255);
         const uint16_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair, word aligned
         const uint32_t mm = *reinterpret_cast<const uint32_t*>(c);
         const uint32_t u0 = *reinterpret_cast<const uint32_t*>(c - SA - 2), u1 = *reinterpret_cast<const uint32_t*>(c - SA), u2 = *reinterpret_cast<const uint32_t*>(c - SA + 2);
@@ -297,9 +302,10 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     orbx_fast_geometry(p, &boxW, &rhMax);
     dim3 grid(p.cellsTotal, p.imgs);
     const int sa = boxW == 64 ? 48 : 80;
-    // per-warp task list: at most 2 pairs per thread and step of pass 1
+    // per-warp task list: at most 2 pairs per thread and step of pass 1, which covers FAST_THREADS / nw whole rows per step
     const int nwMax = (3 + (sa == 48 ? 40 : 66) + 4) >> 2;
-    const int listCap = 64 * ((rhMax * nwMax + FAST_THREADS - 1) / FAST_THREADS);
+    const int rowsPerStep = FAST_THREADS / nwMax;
+    const int listCap = 64 * ((rhMax + rowsPerStep - 1) / rowsPerStep);
     const size_t smem = (size_t)((rhMax * boxW + 127) & ~127) + (size_t)2 * rhMax * sa * 2 + (size_t)(rhMax - 4) * sa * 2 +
                         (size_t)2 * FAST_WARPS * listCap * 2;
     if (smem > 32 * 1024) {  // tall cells on small levels: static + dynamic may pass 48 KB; per-device attribute, set on every such launch
