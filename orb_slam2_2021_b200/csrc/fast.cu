@@ -26,8 +26,8 @@
 //     (even tile column first); for every ring offset the pair (ring(x), ring(x+1)) is ONE aligned 32-bit
 //     LDS (from A for even dx, from B+1 for odd dx) that is already a u16x2 vector — no byte extraction;
 //     d'_k = ring_k + 256 - centre stays in [1,511] per lane, so the whole min/max network runs on unsigned
-//     u16x2 with the 3-input DPX instructions (__vimin3_u16x2 / __vimax3_u16x2): 16+16 ops for the
-//     9-windows and 8 for the reduction, per polarity, per pixel PAIR;
+//     u16x2 with the 3-input DPX instructions (__vimin3_u16x2 / __vimax3_u16x2): 36 ops per polarity and
+//     pixel PAIR (pair and quad minima shared by the two arcs that start at k and k+1);
 //   * strengths go to a u16 map; NMS is driven by the same task lists and uses packed column maxima;
 //     maxima are collected in a CTA list and emitted at their row-major rank (the reference order).
 #include "orbx_dev.cuh"
@@ -58,26 +58,31 @@ __device__ __forceinline__ void fast_strength2(const uint16_t* a, const uint16_t
     d[12] = RING_A(-3, 0) + nc;  d[13] = RING_A(-3, 1) + nc;  d[14] = RING_B(-2, 2) + nc;  d[15] = RING_A(-1, 3) + nc;
 #undef RING_A
 #undef RING_B
-    uint32_t lo3[16], hi3[16];
+    // Arcs k and k+1 (k even) share the 8 values d[k+1..k+8]: max(min arc k, min arc k+1) = min(min8, max(d[k], d[k+9])).
+    // Pair minima P (odd starts), quad minima Q = 4 contiguous values, then one 3-input op per even k: 36 operations per
+    // polarity instead of 40 with 3/9-windows. The dark side is the dual (min <-> max).
+    uint32_t pl[8], ph[8];  // j = 2i+1: min / max of d[j], d[j+1]
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        lo3[k] = __vimin3_u16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-        hi3[k] = __vimax3_u16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+    for (int i = 0; i < 8; ++i) {
+        pl[i] = __vimin3_u16x2(d[2 * i + 1], d[(2 * i + 2) & 15], d[(2 * i + 2) & 15]);
+        ph[i] = __vimax3_u16x2(d[2 * i + 1], d[(2 * i + 2) & 15], d[(2 * i + 2) & 15]);
     }
-    uint32_t lo9[16], hi9[16];
+    uint32_t ql[8], qh[8];  // d[j .. j+3], j = 2i+1
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        lo9[k] = __vimin3_u16x2(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
-        hi9[k] = __vimax3_u16x2(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]);
+    for (int i = 0; i < 8; ++i) {
+        ql[i] = __vimin3_u16x2(pl[i], pl[(i + 1) & 7], pl[(i + 1) & 7]);
+        qh[i] = __vimax3_u16x2(ph[i], ph[(i + 1) & 7], ph[(i + 1) & 7]);
     }
-    uint32_t br = __vimax3_u16x2(lo9[0], lo9[1], lo9[2]), dk = __vimin3_u16x2(hi9[0], hi9[1], hi9[2]);
+    uint32_t tl[8], th[8];  // k = 2i: best of arcs k and k+1
 #pragma unroll
-    for (int k = 3; k < 15; k += 2) {
-        br = __vimax3_u16x2(br, lo9[k], lo9[k + 1]);
-        dk = __vimin3_u16x2(dk, hi9[k], hi9[k + 1]);
+    for (int i = 0; i < 8; ++i) {
+        const uint32_t el = __vimax3_u16x2(d[2 * i], d[(2 * i + 9) & 15], d[(2 * i + 9) & 15]);
+        const uint32_t eh = __vimin3_u16x2(d[2 * i], d[(2 * i + 9) & 15], d[(2 * i + 9) & 15]);
+        tl[i] = __vimin3_u16x2(ql[i], ql[(i + 2) & 7], el);  // d[k+1..k+4], d[k+5..k+8]
+        th[i] = __vimax3_u16x2(qh[i], qh[(i + 2) & 7], eh);
     }
-    br = __vimax3_u16x2(br, lo9[15], lo9[15]);
-    dk = __vimin3_u16x2(dk, hi9[15], hi9[15]);
+    uint32_t br = __vimax3_u16x2(__vimax3_u16x2(tl[0], tl[1], tl[2]), __vimax3_u16x2(tl[3], tl[4], tl[5]), __vimax3_u16x2(tl[6], tl[7], tl[7]));
+    uint32_t dk = __vimin3_u16x2(__vimin3_u16x2(th[0], th[1], th[2]), __vimin3_u16x2(th[3], th[4], th[5]), __vimin3_u16x2(th[6], th[7], th[7]));
     // bright = br - 256, dark = dk - 256 (per lane); strength = max(bright, -dark)
     m0 = max((int)(br & 0xFFFFu) - 256, 256 - (int)(dk & 0xFFFFu));
     m1 = max((int)(br >> 16) - 256, 256 - (int)(dk >> 16));
