@@ -25,8 +25,8 @@
 //   * pass 2 runs the exact test on the listed pairs only. A thread owns two horizontally adjacent pixels
 //     (even tile column first); for every ring offset the pair (ring(x), ring(x+1)) is ONE aligned 32-bit
 //     LDS (from A for even dx, from B+1 for odd dx) that is already a u16x2 vector — no byte extraction;
-//     d'_k = ring_k + 256 - centre stays in [1,511] per lane, so the whole min/max network runs on unsigned
-//     u16x2 with the 3-input DPX instructions (__vimin3_u16x2 / __vimax3_u16x2): 36 ops per polarity and
+//     min and max commute with subtracting the centre, so the whole min/max network runs on the raw unsigned
+//     u16x2 ring values with the 3-input DPX instructions (__vimin3_u16x2 / __vimax3_u16x2): 36 ops per polarity and
 //     pixel PAIR (pair and quad minima shared by the two arcs that start at k and k+1);
 //   * strengths go to a u16 map; NMS is driven by the same task lists and uses packed column maxima;
 //     maxima are collected in a CTA list and emitted at their row-major rank (the reference order).
@@ -50,12 +50,13 @@ __device__ __forceinline__ void fast_strength2(const uint16_t* a, const uint16_t
 {
 #define RING_A(dx, dy) (*reinterpret_cast<const uint32_t*>(a + (dy) * SA + (dx)))
 #define RING_B(dx, dy) (*reinterpret_cast<const uint32_t*>(b + (dy) * SA + (dx)))
-    const uint32_t nc = 0x01000100u - RING_B(0, 0);  // 256 - centre per lane, in [1,256]: no borrow between lanes
-    uint32_t d[16];  // (ptxas issues these packed additions as IMAD.IADD on the FMA pipe, off the ALU pipe that bounds the kernel)
-    d[0] = RING_B(0, 3) + nc;    d[1] = RING_A(1, 3) + nc;    d[2] = RING_B(2, 2) + nc;    d[3] = RING_A(3, 1) + nc;
-    d[4] = RING_A(3, 0) + nc;    d[5] = RING_A(3, -1) + nc;   d[6] = RING_B(2, -2) + nc;   d[7] = RING_A(1, -3) + nc;
-    d[8] = RING_B(0, -3) + nc;   d[9] = RING_A(-1, -3) + nc;  d[10] = RING_B(-2, -2) + nc; d[11] = RING_A(-3, -1) + nc;
-    d[12] = RING_A(-3, 0) + nc;  d[13] = RING_A(-3, 1) + nc;  d[14] = RING_B(-2, 2) + nc;  d[15] = RING_A(-1, 3) + nc;
+    // the network runs on the raw ring values (min and max commute with subtracting the centre): no per-value arithmetic
+    const uint32_t cc = RING_B(0, 0);
+    uint32_t d[16];
+    d[0] = RING_B(0, 3);    d[1] = RING_A(1, 3);    d[2] = RING_B(2, 2);    d[3] = RING_A(3, 1);
+    d[4] = RING_A(3, 0);    d[5] = RING_A(3, -1);   d[6] = RING_B(2, -2);   d[7] = RING_A(1, -3);
+    d[8] = RING_B(0, -3);   d[9] = RING_A(-1, -3);  d[10] = RING_B(-2, -2); d[11] = RING_A(-3, -1);
+    d[12] = RING_A(-3, 0);  d[13] = RING_A(-3, 1);  d[14] = RING_B(-2, 2);  d[15] = RING_A(-1, 3);
 #undef RING_A
 #undef RING_B
     // Arcs k and k+1 (k even) share the 8 values d[k+1..k+8]: max(min arc k, min arc k+1) = min(min8, max(d[k], d[k+9])).
@@ -83,9 +84,10 @@ __device__ __forceinline__ void fast_strength2(const uint16_t* a, const uint16_t
     }
     uint32_t br = __vimax3_u16x2(__vimax3_u16x2(tl[0], tl[1], tl[2]), __vimax3_u16x2(tl[3], tl[4], tl[5]), __vimax3_u16x2(tl[6], tl[7], tl[7]));
     uint32_t dk = __vimin3_u16x2(__vimin3_u16x2(th[0], th[1], th[2]), __vimin3_u16x2(th[3], th[4], th[5]), __vimin3_u16x2(th[6], th[7], th[7]));
-    // bright = br - 256, dark = dk - 256 (per lane); strength = max(bright, -dark)
-    m0 = max((int)(br & 0xFFFFu) - 256, 256 - (int)(dk & 0xFFFFu));
-    m1 = max((int)(br >> 16) - 256, 256 - (int)(dk >> 16));
+    // strength = max(brightest arc minimum - centre, centre - darkest arc maximum), per lane
+    const int c0 = (int)(cc & 0xFFFFu), c1 = (int)(cc >> 16);
+    m0 = max((int)(br & 0xFFFFu) - c0, c0 - (int)(dk & 0xFFFFu));
+    m1 = max((int)(br >> 16) - c1, c1 - (int)(dk >> 16));
 }
 
 // c_recip[n] = ceil(65536 / n): floor(t / n) = (t * c_recip[n]) >> 16 exactly while t * n < 65536 (here t <= 128, n <= 31)
