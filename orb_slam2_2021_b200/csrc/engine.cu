@@ -183,9 +183,11 @@ void Engine::release()
     if (upStream) cudaStreamDestroy(upStream);
     if (downStream) cudaStreamDestroy(downStream);
     if (stream2) cudaStreamDestroy(stream2);
+    if (stream3) cudaStreamDestroy(stream3);
+    if (stream4) cudaStreamDestroy(stream4);
     for (cudaEvent_t e : chunkEvents) cudaEventDestroy(e);
     chunkEvents.clear();
-    stream = stream2 = upStream = downStream = nullptr;
+    stream = stream2 = stream3 = stream4 = upStream = downStream = nullptr;
     bytesAllocated = 0;
 }
 
@@ -249,6 +251,8 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     TRY(orbx_check(cudaStreamCreateWithFlags(&upStream, cudaStreamNonBlocking), "cudaStreamCreate", err));
     TRY(orbx_check(cudaStreamCreateWithFlags(&downStream, cudaStreamNonBlocking), "cudaStreamCreate", err));
     TRY(orbx_check(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking), "cudaStreamCreate", err));
+    TRY(orbx_check(cudaStreamCreateWithFlags(&stream3, cudaStreamNonBlocking), "cudaStreamCreate", err));
+    TRY(orbx_check(cudaStreamCreateWithFlags(&stream4, cudaStreamNonBlocking), "cudaStreamCreate", err));
 
     const size_t n = (size_t)nImgs;
     TRY(dalloc(this, &P.img0, n * P.img0Stride + 64, "img0", err));
@@ -296,11 +300,21 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     std::vector<size_t> tabOff(P.nlevels, 0);
     for (int l = 1; l < P.nlevels; ++l) {
         const OrbxLevel &S = P.lv[l - 1], &D = P.lv[l];
+        tab.resize((tab.size() + 3) & ~(size_t)3);  // int4 alignment of the row table below
         tabOff[l] = tab.size();
-        tab.resize(tab.size() + 2 * D.w + 2 * D.h);
+        const size_t yOff = (2 * (size_t)D.w + 3) & ~(size_t)3;
+        tab.resize(tab.size() + yOff + 4 * (size_t)D.h);
         int* base = tab.data() + tabOff[l];
         axis_table(S.w, D.w, true, base, base + D.w);
-        axis_table(S.h, D.h, false, base + 2 * D.w, base + 2 * D.w + D.h);
+        std::vector<int> yofs(D.h), ycoef(D.h);
+        axis_table(S.h, D.h, false, yofs.data(), ycoef.data());
+        for (int y = 0; y < D.h; ++y) {  // {source row, b0 << 12, b1 << 12, 0}: the kernel multiplies with mulhi
+            int* e4 = base + yOff + 4 * (size_t)y;
+            e4[0] = yofs[y];
+            e4[1] = (ycoef[y] & 0xFFFF) << 12;
+            e4[2] = ((unsigned)ycoef[y] >> 16) << 12;
+            e4[3] = 0;
+        }
     }
     TRY(dalloc(this, &dResizeTab, tab.size(), "resizeTab", err));
     TRY(orbx_check(cudaMemcpy(dResizeTab, tab.data(), tab.size() * sizeof(int), cudaMemcpyHostToDevice), "tab H2D", err));
@@ -482,18 +496,34 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
     }
     const size_t tight = (size_t)rows * cols, Pk = (size_t)P.maxKp;
     const size_t sideStride = tight * (maxImgs / per);
+    // ORBX_E2E_TRACE=1: timed events around every chunk's copy-in, compute and copy-out, printed to stderr after the call
+    static const bool trace = [] { const char* e = getenv("ORBX_E2E_TRACE"); return e && atoi(e) != 0; }();
+    std::vector<cudaEvent_t> tev;
+    auto tmark = [&](cudaStream_t s) {
+        if (!trace) return;
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        cudaEventRecord(e, s);
+        tev.push_back(e);
+    };
+    static const int nStreams = [] { const char* e = getenv("ORBX_E2E_STREAMS"); const int v = e ? atoi(e) : 3; return v < 1 ? 1 : v > 4 ? 4 : v; }();
+    cudaStream_t pool[4] = {stream, stream2, stream3, stream4};
+    tmark(upStream);  // t0
     for (int c = 0; c < nChunks; ++c) {
         const int f0 = bounds[c], n = bounds[c + 1] - bounds[c];
         cudaEvent_t up = chunkEvents[2 * c], done = chunkEvents[2 * c + 1];
+        tmark(upStream);
         for (int side = 0; side < per; ++side) {
             const uint8_t* src = (side ? right : left) + f0 * tight;
             TRY(orbx_check(cudaMemcpyAsync(dStage + side * sideStride + f0 * tight, src, n * tight, cudaMemcpyHostToDevice, upStream), "H2D chunk", err));
         }
         TRY(orbx_check(cudaEventRecord(up, upStream), "event", err));
+        tmark(upStream);
         // chunks alternate between two compute streams: the low-occupancy kernels of one chunk (quadtree, small
         // pyramid levels) overlap with the wide kernels of the next
-        cudaStream_t cs = (c & 1) ? stream2 : stream;
+        cudaStream_t cs = pool[c % nStreams];
         TRY(orbx_check(cudaStreamWaitEvent(cs, up, 0), "wait", err));
+        tmark(cs);
         const OrbxParams p = slice(per * f0, per * n);
         for (int side = 0; side < per; ++side)
             orbx_launch_ingest(p, dStage + side * sideStride + f0 * tight, n, per, side, cs);
@@ -501,7 +531,9 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
         if (stereo) launchStereo(f0, n, mbf, mb, cs);
         TRY(orbx_check(cudaGetLastError(), "chunk launch", err));
         TRY(orbx_check(cudaEventRecord(done, cs), "event", err));
+        tmark(cs);
         TRY(orbx_check(cudaStreamWaitEvent(downStream, done, 0), "wait", err));
+        tmark(downStream);
         auto rowsD2H = [&](void* dst, const void* src, size_t rowBytes, size_t devStride) -> int {
             if (!dst) return ORBX_OK;
             return orbx_check(cudaMemcpy2DAsync(dst, rowBytes, src, devStride, rowBytes, n, cudaMemcpyDeviceToHost, downStream), "D2H chunk", err);
@@ -519,10 +551,18 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
             TRY(rowsD2H(out.uRight ? out.uRight + f0 * Pk : nullptr, SP.uRight + f0 * Pk, Pk * 4, Pk * 4));
             TRY(rowsD2H(out.depth ? out.depth + f0 * Pk : nullptr, SP.depth + f0 * Pk, Pk * 4, Pk * 4));
         }
+        tmark(downStream);
     }
     TRY(orbx_check(cudaStreamSynchronize(downStream), "down sync", err));
-    TRY(orbx_check(cudaStreamSynchronize(stream2), "stream sync", err));
-    return orbx_check(cudaStreamSynchronize(stream), "stream sync", err);
+    for (int i = nStreams - 1; i >= 0; --i) TRY(orbx_check(cudaStreamSynchronize(pool[i]), "stream sync", err));
+    if (trace) {  // 6 events per chunk after t0: up begin/end, compute begin/end, down begin/end
+        auto at = [&](size_t i) { float t = 0; cudaEventElapsedTime(&t, tev[0], tev[i]); return t; };
+        for (int c = 0; c < nChunks; ++c)
+            fprintf(stderr, "[orbx e2e] chunk %d frames %d..%d  up %.3f-%.3f  compute %.3f-%.3f  down %.3f-%.3f ms\n", c, bounds[c], bounds[c + 1],
+                    at(1 + 6 * c), at(2 + 6 * c), at(3 + 6 * c), at(4 + 6 * c), at(5 + 6 * c), at(6 + 6 * c));
+        for (auto e : tev) cudaEventDestroy(e);
+    }
+    return ORBX_OK;
 }
 
 int Engine::sync(std::string& err)

@@ -49,6 +49,7 @@ public:
     int processPipelined(const uint8_t* left, const uint8_t* right, int nFrames, float mbf, float mb, const HostOutputs& out,
                          int chunkFrames, std::string& err);
     cudaStream_t upStream = nullptr, downStream = nullptr, stream2 = nullptr;
+    cudaStream_t stream3 = nullptr, stream4 = nullptr;  // further compute streams of the end-to-end pipeline
     // raw-frame input path (include/orbx_input.h): raw frames and per-side rectification maps on the device
     uint8_t* dRaw = nullptr; size_t rawCap = 0;
     float* dMap1[2] = {nullptr, nullptr}; float* dMap2[2] = {nullptr, nullptr};
