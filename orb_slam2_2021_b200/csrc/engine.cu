@@ -506,7 +506,7 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
         cudaEventRecord(e, s);
         tev.push_back(e);
     };
-    static const int nStreams = [] { const char* e = getenv("ORBX_E2E_STREAMS"); const int v = e ? atoi(e) : 3; return v < 1 ? 1 : v > 4 ? 4 : v; }();
+    static const int nStreams = [] { const char* e = getenv("ORBX_E2E_STREAMS"); const int v = e ? atoi(e) : 2; return v < 1 ? 1 : v > 4 ? 4 : v; }();
     cudaStream_t pool[4] = {stream, stream2, stream3, stream4};
     tmark(upStream);  // t0
     for (int c = 0; c < nChunks; ++c) {

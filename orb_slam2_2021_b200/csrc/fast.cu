@@ -33,7 +33,7 @@
 #include "orbx_dev.cuh"
 #include "orbx_tma.cuh"
 
-struct OrbxCell {
+struct __align__(8) OrbxCell {  // 8 bytes, loaded as one 64-bit word
     short x0, y0;        // ROI origin in level coordinates (iniX, iniY)
     uint8_t rw, rh;      // ROI size (maxX-iniX, maxY-iniY)
     uint8_t level, pad;
