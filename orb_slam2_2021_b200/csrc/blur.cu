@@ -24,7 +24,7 @@
 #include "orbx_dev.cuh"
 #include "orbx_tma.cuh"
 
-struct OrbxTile {
+struct __align__(8) OrbxTile {  // 8 bytes, loaded as one uniform 64-bit word
     short x0, y0;
     uint8_t level, pad[3];
 };

@@ -95,7 +95,7 @@ __device__ __forceinline__ short4 child_box(short4 b, int q)
     return c;
 }
 
-struct OrbxCellRec {  // same layout as OrbxCell in fast.cu
+struct __align__(8) OrbxCellRec {  // same layout as OrbxCell in fast.cu
     short x0, y0;
     uint8_t rw, rh, level, pad;
 };
