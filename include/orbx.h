@@ -110,6 +110,16 @@ int orbx_batch_stats(orbx_batch* b, int n_frames, long long* n_left, long long* 
 int orbx_batch_process(orbx_batch* b, const uint8_t* left, const uint8_t* right, int n_frames, float mbf, float mb,
                        int* n_left, orbx_keypoint* kps_left, uint8_t* desc_left, int* n_right,
                        orbx_keypoint* kps_right, uint8_t* desc_right, float* u_right, float* depth);
+/* Streaming form of orbx_batch_process for a continuous feed of batches: returns as soon as the copies and kernels are
+ * enqueued, so that the uploads of call k+1 overlap the kernels of call k (per chunk, call k+1 waits only for call k's use
+ * of the same staging area and result rows). The host buffers of a call (inputs AND outputs, pinned for real overlap) must
+ * not be touched until orbx_batch_wait() returns; use two output sets to alternate. Any other orbx_batch_* call on the
+ * same batch drains the pipeline first. */
+int orbx_batch_process_async(orbx_batch* b, const uint8_t* left, const uint8_t* right, int n_frames, float mbf, float mb,
+                             int* n_left, orbx_keypoint* kps_left, uint8_t* desc_left, int* n_right,
+                             orbx_keypoint* kps_right, uint8_t* desc_right, float* u_right, float* depth);
+/* Blocks until every orbx_batch_process_async of this batch has finished and its outputs are in host memory. */
+int orbx_batch_wait(orbx_batch* b);
 /* The CUDA stream the engine launches on (cudaStream_t as void*), for event timing by the caller. */
 void* orbx_batch_stream(orbx_batch* b);
 /* Number of kernels the most recent orbx_batch_run launched (a batch of 32+ frames runs as 2 chunks on two streams;

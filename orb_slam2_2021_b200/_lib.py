@@ -59,6 +59,8 @@ SIGNATURES = {
     "orbx_batch_download": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "orbx_batch_stats": (_i, [_vp, _i, C.POINTER(_ll), C.POINTER(_ll), C.POINTER(_ll)]),
     "orbx_batch_process": (_i, [_vp, _vp, _vp, _i, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "orbx_batch_process_async": (_i, [_vp, _vp, _vp, _i, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "orbx_batch_wait": (_i, [_vp]),
     "orbx_batch_stream": (_vp, [_vp]),
     "orbx_batch_launches_per_run": (_i, [_vp]),
     "orbx_batch_device_bytes": (_ll, [_vp]),

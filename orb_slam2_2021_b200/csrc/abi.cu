@@ -217,6 +217,16 @@ extern "C" int orbx_stereo_match(orbx_extractor* l, orbx_extractor* r, const orb
 
 // ---- frame batches ---------------------------------------------------------------------------------
 
+// an asynchronous orbx_batch_process_async may still be in flight: every other entry point drains it first
+#define ORBX_DRAIN(b) do { if (!(b)->eng.lastBounds.empty()) TRY((b)->eng.waitPipelined(g_err)); } while (0)
+
+// chunks of >= 16 frames keep every kernel's grid well above one wave while the copies of the neighbouring chunks overlap
+static int e2e_chunk_frames(int nFrames)
+{
+    static const int forcedChunks = [] { const char* e = getenv("ORBX_E2E_CHUNKS"); return e ? atoi(e) : 0; }();
+    return forcedChunks > 0 ? (nFrames + forcedChunks - 1) / forcedChunks : nFrames >= 64 ? (nFrames + 7) / 8 : nFrames >= 32 ? 16 : nFrames;
+}
+
 extern "C" int orbx_batch_create(int nfeatures, float sf, int nlevels, int ini, int mn, int rows, int cols, int maxFrames,
                                  int stereo, int device, orbx_batch** out)
 {
@@ -245,12 +255,14 @@ extern "C" long long orbx_batch_device_bytes(const orbx_batch* b) { return b ? (
 extern "C" int orbx_batch_upload(orbx_batch* b, const uint8_t* left, const uint8_t* right, int nFrames)
 {
     if (!b) return fail(ORBX_ERR_ARG, "handle is NULL");
+    ORBX_DRAIN(b);
     return b->eng.uploadImages(left, right, nFrames, false, g_err);
 }
 
 extern "C" int orbx_batch_upload_device(orbx_batch* b, const void* left, const void* right, int nFrames)
 {
     if (!b) return fail(ORBX_ERR_ARG, "handle is NULL");
+    ORBX_DRAIN(b);
     return b->eng.uploadImages((const uint8_t*)left, (const uint8_t*)right, nFrames, true, g_err);
 }
 
@@ -265,6 +277,7 @@ static int run_chunks(int nFrames)
 extern "C" int orbx_batch_run(orbx_batch* b, int nFrames, float mbf, float mb, int sync)
 {
     if (!b || nFrames < 1 || nFrames > b->maxFrames) return fail(ORBX_ERR_ARG, "bad frame count");
+    ORBX_DRAIN(b);
     TRY(b->eng.runBatch(nFrames, mbf, mb, run_chunks(nFrames), g_err));
     return sync ? b->eng.sync(g_err) : ORBX_OK;
 }
@@ -280,6 +293,7 @@ extern "C" int orbx_batch_download(orbx_batch* b, int nFrames, int* nLeft, orbx_
                                    orbx_keypoint* kpsRight, uint8_t* descRight, float* uRight, float* depth)
 {
     if (!b || nFrames < 1 || nFrames > b->maxFrames) return fail(ORBX_ERR_ARG, "bad frame count");
+    ORBX_DRAIN(b);
     Engine& E = b->eng;
     TRY(orbx_check(cudaSetDevice(E.device), "cudaSetDevice", g_err));
     const size_t per = b->stereo ? 2 : 1, P = E.P.maxKp;
@@ -297,21 +311,39 @@ extern "C" int orbx_batch_download(orbx_batch* b, int nFrames, int* nLeft, orbx_
     return E.sync(g_err);
 }
 
+// Asynchronous orbx_batch_process: returns when the work is enqueued; consecutive calls pipeline (the uploads of call k+1
+// overlap the kernels of call k). orbx_batch_wait() drains; every other orbx_batch_* call drains first by itself.
+extern "C" int orbx_batch_process_async(orbx_batch* b, const uint8_t* left, const uint8_t* right, int nFrames, float mbf, float mb,
+                                        int* nLeft, orbx_keypoint* kpsLeft, uint8_t* descLeft, int* nRight, orbx_keypoint* kpsRight,
+                                        uint8_t* descRight, float* uRight, float* depth)
+{
+    if (!b || nFrames < 1 || nFrames > b->maxFrames) return fail(ORBX_ERR_ARG, "bad frame count");
+    Engine::HostOutputs o{nLeft, kpsLeft, descLeft, nRight, kpsRight, descRight, uRight, depth};
+    // four large chunks: without a ramp to hide, fewer and larger launches run closer to the device-resident rate
+    static const int forcedChunks = [] { const char* e = getenv("ORBX_E2E_CHUNKS"); return e ? atoi(e) : 0; }();
+    const int chunk = forcedChunks > 0 ? (nFrames + forcedChunks - 1) / forcedChunks : nFrames >= 64 ? (nFrames + 3) / 4 : nFrames >= 32 ? 16 : nFrames;
+    return b->eng.processPipelined(left, right, nFrames, mbf, mb, o, chunk, g_err, false);
+}
+
+extern "C" int orbx_batch_wait(orbx_batch* b)
+{
+    if (!b) return fail(ORBX_ERR_ARG, "null batch");
+    return b->eng.waitPipelined(g_err);
+}
+
 extern "C" int orbx_batch_process(orbx_batch* b, const uint8_t* left, const uint8_t* right, int nFrames, float mbf, float mb,
                                   int* nLeft, orbx_keypoint* kpsLeft, uint8_t* descLeft, int* nRight, orbx_keypoint* kpsRight,
                                   uint8_t* descRight, float* uRight, float* depth)
 {
     if (!b || nFrames < 1 || nFrames > b->maxFrames) return fail(ORBX_ERR_ARG, "bad frame count");
     Engine::HostOutputs o{nLeft, kpsLeft, descLeft, nRight, kpsRight, descRight, uRight, depth};
-    // chunks of >= 16 frames keep every kernel's grid well above one wave while the copies of the neighbouring chunks overlap
-    static const int forcedChunks = [] { const char* e = getenv("ORBX_E2E_CHUNKS"); return e ? atoi(e) : 0; }();
-    const int chunk = forcedChunks > 0 ? (nFrames + forcedChunks - 1) / forcedChunks : nFrames >= 64 ? (nFrames + 7) / 8 : nFrames >= 32 ? 16 : nFrames;
-    return b->eng.processPipelined(left, right, nFrames, mbf, mb, o, chunk, g_err);
+    return b->eng.processPipelined(left, right, nFrames, mbf, mb, o, e2e_chunk_frames(nFrames), g_err);
 }
 
 extern "C" int orbx_batch_stats(orbx_batch* b, int nFrames, long long* nLeft, long long* nRight, long long* nMatched)
 {
     if (!b || nFrames < 1 || nFrames > b->maxFrames) return fail(ORBX_ERR_ARG, "bad frame count");
+    ORBX_DRAIN(b);
     Engine& E = b->eng;
     const int per = b->stereo ? 2 : 1;
     std::vector<int> cnt((size_t)nFrames * per), nm(nFrames, 0);
@@ -339,6 +371,7 @@ extern "C" int orbx_batch_level(orbx_batch* b, int frame, int side, int level, i
 {
     if (!b || !dst || level < 0 || level >= b->cfg.nlevels || frame < 0 || frame >= b->maxFrames || side < 0 || side > (b->stereo ? 1 : 0))
         return fail(ORBX_ERR_ARG, "bad arguments");
+    ORBX_DRAIN(b);
     return copy_level(b->eng, frame * (b->stereo ? 2 : 1) + side, level, blurred != 0, dst, dstStride);
 }
 
@@ -346,6 +379,7 @@ extern "C" int orbx_batch_candidates(orbx_batch* b, int frame, int side, int lev
 {
     if (!b || !n || level < 0 || level >= b->cfg.nlevels || frame < 0 || frame >= b->maxFrames || side < 0 || side > (b->stereo ? 1 : 0))
         return fail(ORBX_ERR_ARG, "bad arguments");
+    ORBX_DRAIN(b);
     Engine& E = b->eng;
     const int img = frame * (b->stereo ? 2 : 1) + side;
     const OrbxLevel& L = E.P.lv[level];
@@ -377,6 +411,7 @@ extern "C" const char* orbx_batch_stage_name(int i) { return Engine::stageName(i
 extern "C" int orbx_batch_stage_times(orbx_batch* b, double* ms, int* runs)
 {
     if (!b || !ms || !runs) return fail(ORBX_ERR_ARG, "bad arguments");
+    ORBX_DRAIN(b);
     double t[Engine::kStages];
     TRY(b->eng.stageTimes(t, runs, g_err));
     for (int i = 0; i < Engine::kStages - 1; ++i) ms[i] = t[i];
@@ -399,6 +434,7 @@ extern "C" int orbx_batch_set_rectification(orbx_batch* b, int side, const float
                                             size_t mapStrideBytes, int cropTop)
 {
     if (!b || side < 0 || side > (b->stereo ? 1 : 0)) return fail(ORBX_ERR_ARG, "bad handle or side");
+    ORBX_DRAIN(b);
     Engine& E = b->eng;
     TRY(orbx_check(cudaSetDevice(E.device), "cudaSetDevice", g_err));
     TRY(E.sync(g_err));
@@ -423,6 +459,7 @@ extern "C" int orbx_batch_upload_raw(orbx_batch* b, const uint8_t* left, const u
                                      int channels, int rgbOrder)
 {
     if (!b || nFrames < 1 || nFrames > b->maxFrames || !left || (b->stereo && !right)) return fail(ORBX_ERR_ARG, "bad upload arguments");
+    ORBX_DRAIN(b);
     if (srcRows < 1 || srcCols < 1 || (channels != 1 && channels != 3 && channels != 4)) return fail(ORBX_ERR_ARG, "bad raw frame format");
     Engine& E = b->eng;
     const int per = b->stereo ? 2 : 1;

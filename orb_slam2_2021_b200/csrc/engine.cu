@@ -187,6 +187,9 @@ void Engine::release()
     if (stream4) cudaStreamDestroy(stream4);
     for (cudaEvent_t e : chunkEvents) cudaEventDestroy(e);
     chunkEvents.clear();
+    for (cudaEvent_t e : ingestEvents) cudaEventDestroy(e);
+    for (cudaEvent_t e : downEvents) cudaEventDestroy(e);
+    ingestEvents.clear(); downEvents.clear(); lastBounds.clear();
     stream = stream2 = stream3 = stream4 = upStream = downStream = nullptr;
     bytesAllocated = 0;
 }
@@ -471,8 +474,11 @@ int Engine::runBatch(int nFrames, float mbf, float mb, int nChunks, std::string&
 
 // Chunked end-to-end pipeline: chunk c's images go up on `upStream` while chunk c-1 computes on `stream` and chunk
 // c-2's results come down on `downStream` (H2D and D2H use separate copy engines; PCIe is full duplex).
+// With wait == false the call returns once everything is enqueued: the next call's uploads then overlap this call's
+// compute (chunk c of the next call waits only for chunk c of this one: its staging area consumed, its results copied out),
+// and waitPipelined() drains. Host buffers must stay untouched until then.
 int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFrames, float mbf, float mb, const HostOutputs& out,
-                             int chunkFrames, std::string& err)
+                             int chunkFrames, std::string& err, bool wait)
 {
     const int per = stereo ? 2 : 1;
     if (nFrames < 1 || nFrames * per > maxImgs || !left || (stereo && !right)) { err = "bad process arguments"; return ORBX_ERR_ARG; }
@@ -481,7 +487,9 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
     // chunk boundaries: equal chunks, except that the first one may be split so that compute starts after a short copy
     std::vector<int> bounds{0};
     {
-        static const int firstDiv = [] { const char* e = getenv("ORBX_E2E_FIRST_DIV"); return e ? atoi(e) : 2; }();
+        // (a streamed call has no ramp to shorten: the previous call is still computing while its first chunk uploads)
+        static const int firstDivEnv = [] { const char* e = getenv("ORBX_E2E_FIRST_DIV"); return e ? atoi(e) : 2; }();
+        const int firstDiv = wait ? firstDivEnv : 1;
         if (firstDiv > 1 && chunkFrames >= 2 * firstDiv && nFrames > chunkFrames) {
             for (int k = 1; k < firstDiv; ++k) bounds.push_back(chunkFrames * k / firstDiv);
         }
@@ -489,6 +497,16 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
         bounds.push_back(nFrames);
     }
     const int nChunks = (int)bounds.size() - 1;
+    // a call still in flight with a different chunk layout: no per-chunk correspondence, drain it first
+    const bool chained = !lastBounds.empty() && lastBounds == bounds;
+    if (!lastBounds.empty() && !chained) TRY(waitPipelined(err));
+    while ((int)ingestEvents.size() < nChunks) {
+        cudaEvent_t e1, e2;
+        TRY(orbx_check(cudaEventCreateWithFlags(&e1, cudaEventDisableTiming), "cudaEventCreate", err));
+        TRY(orbx_check(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming), "cudaEventCreate", err));
+        ingestEvents.push_back(e1);
+        downEvents.push_back(e2);
+    }
     while ((int)chunkEvents.size() < 2 * nChunks) {
         cudaEvent_t e;
         TRY(orbx_check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate", err));
@@ -513,6 +531,7 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
         const int f0 = bounds[c], n = bounds[c + 1] - bounds[c];
         cudaEvent_t up = chunkEvents[2 * c], done = chunkEvents[2 * c + 1];
         tmark(upStream);
+        if (chained) TRY(orbx_check(cudaStreamWaitEvent(upStream, ingestEvents[c], 0), "wait", err));  // staging area free again
         for (int side = 0; side < per; ++side) {
             const uint8_t* src = (side ? right : left) + f0 * tight;
             TRY(orbx_check(cudaMemcpyAsync(dStage + side * sideStride + f0 * tight, src, n * tight, cudaMemcpyHostToDevice, upStream), "H2D chunk", err));
@@ -524,9 +543,11 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
         cudaStream_t cs = pool[c % nStreams];
         TRY(orbx_check(cudaStreamWaitEvent(cs, up, 0), "wait", err));
         tmark(cs);
+        if (chained) TRY(orbx_check(cudaStreamWaitEvent(cs, downEvents[c], 0), "wait", err));  // previous results of these frames are out
         const OrbxParams p = slice(per * f0, per * n);
         for (int side = 0; side < per; ++side)
             orbx_launch_ingest(p, dStage + side * sideStride + f0 * tight, n, per, side, cs);
+        TRY(orbx_check(cudaEventRecord(ingestEvents[c], cs), "event", err));
         launchExtract(p, cs);
         if (stereo) launchStereo(f0, n, mbf, mb, cs);
         TRY(orbx_check(cudaGetLastError(), "chunk launch", err));
@@ -551,8 +572,12 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
             TRY(rowsD2H(out.uRight ? out.uRight + f0 * Pk : nullptr, SP.uRight + f0 * Pk, Pk * 4, Pk * 4));
             TRY(rowsD2H(out.depth ? out.depth + f0 * Pk : nullptr, SP.depth + f0 * Pk, Pk * 4, Pk * 4));
         }
+        TRY(orbx_check(cudaEventRecord(downEvents[c], downStream), "event", err));
         tmark(downStream);
     }
+    lastBounds = bounds;
+    if (!wait && !trace) return ORBX_OK;
+    lastBounds.clear();
     TRY(orbx_check(cudaStreamSynchronize(downStream), "down sync", err));
     for (int i = nStreams - 1; i >= 0; --i) TRY(orbx_check(cudaStreamSynchronize(pool[i]), "stream sync", err));
     if (trace) {  // 6 events per chunk after t0: up begin/end, compute begin/end, down begin/end
@@ -562,6 +587,17 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
                     at(1 + 6 * c), at(2 + 6 * c), at(3 + 6 * c), at(4 + 6 * c), at(5 + 6 * c), at(6 + 6 * c));
         for (auto e : tev) cudaEventDestroy(e);
     }
+    return ORBX_OK;
+}
+
+int Engine::waitPipelined(std::string& err)
+{
+    TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
+    lastBounds.clear();
+    TRY(orbx_check(cudaStreamSynchronize(upStream), "up sync", err));
+    TRY(orbx_check(cudaStreamSynchronize(downStream), "down sync", err));
+    cudaStream_t pool[4] = {stream, stream2, stream3, stream4};
+    for (int i = 3; i >= 0; --i) TRY(orbx_check(cudaStreamSynchronize(pool[i]), "stream sync", err));
     return ORBX_OK;
 }
 

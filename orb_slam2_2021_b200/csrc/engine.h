@@ -47,7 +47,8 @@ public:
         int* nLeft; void* kpsLeft; uint8_t* descLeft; int* nRight; void* kpsRight; uint8_t* descRight; float* uRight; float* depth;
     };
     int processPipelined(const uint8_t* left, const uint8_t* right, int nFrames, float mbf, float mb, const HostOutputs& out,
-                         int chunkFrames, std::string& err);
+                         int chunkFrames, std::string& err, bool wait = true);
+    int waitPipelined(std::string& err);  // drains an asynchronous processPipelined
     cudaStream_t upStream = nullptr, downStream = nullptr, stream2 = nullptr;
     cudaStream_t stream3 = nullptr, stream4 = nullptr;  // further compute streams of the end-to-end pipeline
     // raw-frame input path (include/orbx_input.h): raw frames and per-side rectification maps on the device
@@ -55,6 +56,9 @@ public:
     float* dMap1[2] = {nullptr, nullptr}; float* dMap2[2] = {nullptr, nullptr};
     int mapRows[2] = {0, 0}, mapCols[2] = {0, 0}, cropTop[2] = {0, 0};
     std::vector<cudaEvent_t> chunkEvents;
+    // cross-call ordering of the asynchronous end-to-end pipeline: per chunk, "staging consumed" and "results copied out"
+    std::vector<cudaEvent_t> ingestEvents, downEvents;
+    std::vector<int> lastBounds;  // chunk boundaries of the previous pipelined call still in flight (empty = none)
     int lastRunChunks = 1;  // chunks of the most recent runBatch (kernel launches = chunks x launches per chunk)
     int sync(std::string& err);
 

@@ -169,8 +169,9 @@ class StereoFrameBatch:
                           desc_right=((n_frames, P, 32), np.uint8), u_right=((n_frames, P), np.float32),
                           depth=((n_frames, P), np.float32))
         if pinned:
-            self._pins = {k: PinnedArray(s, d) for k, (s, d) in shapes.items()}
-            return {k: v.array for k, v in self._pins.items()}
+            pins = {k: PinnedArray(s, d) for k, (s, d) in shapes.items()}
+            self._pins = getattr(self, "_pins", []) + [pins]  # every set stays alive as long as the batch (streaming uses two)
+            return {k: v.array for k, v in pins.items()}
         return {k: np.zeros(s, d) for k, (s, d) in shapes.items()}
 
     def _check_imgs(self, a, n):
@@ -236,6 +237,25 @@ class StereoFrameBatch:
                                        ptr(g("kps_left")), ptr(g("desc_left")), ptr(g("n_right")), ptr(g("kps_right")),
                                        ptr(g("desc_right")), ptr(g("u_right")), ptr(g("depth"))))
         return out
+
+    def process_async(self, left, right, mbf, mb, out):
+        """Streaming form of process(): enqueue and return; call wait() before reading `out` or reusing the buffers.
+
+        `left`, `right` and every array of `out` should be pinned (PinnedArray / alloc_outputs(pinned=True)); the
+        caller keeps them alive and untouched until wait() returns."""
+        n = len(left)
+        left = self._check_imgs(left, n)
+        right = self._check_imgs(right, n) if self.stereo else None
+        g = out.get
+        check(lib().orbx_batch_process_async(self._h, ptr(left), ptr(right), n, float(mbf), float(mb), ptr(g("n_left")),
+                                             ptr(g("kps_left")), ptr(g("desc_left")), ptr(g("n_right")), ptr(g("kps_right")),
+                                             ptr(g("desc_right")), ptr(g("u_right")), ptr(g("depth"))))
+        self._inflight = (left, right, out)  # keep the buffers alive
+        return out
+
+    def wait(self):
+        check(lib().orbx_batch_wait(self._h))
+        self._inflight = None
 
     def stats(self, n_frames):
         a, b, c = C.c_longlong(), C.c_longlong(), C.c_longlong()

@@ -290,6 +290,51 @@ def test_device_resident_run_in_chunks():
         assert_stereo_equal(out["u_right"][f][:nl_], out["depth"][f][:nl_], our, odp, f"frame {f}")
 
 
+def test_streamed_process_matches_synchronous_calls():
+    """process_async x4 back to back with changing inputs (the uploads of call k+1 overlap the kernels of call k), then
+    wait(): every call's results equal those of the synchronous process() on the same inputs; a call with another frame
+    count (different chunk layout) and other entry points in between drain the pipeline by themselves."""
+    cfg = synth.CONFIGS["arducam"]
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    base_l, base_r = synth.stereo_batch(W, H, 4, seed0=300)
+    n = 70  # 8 chunks + split first chunk
+    b = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, n, stereo=True)
+    ins = []
+    for k in range(4):
+        idx = (np.arange(n) + k) % 4
+        pl, pr = pkg.PinnedArray((n, H, W), np.uint8), pkg.PinnedArray((n, H, W), np.uint8)
+        pl.array[...] = base_l[idx]
+        pr.array[...] = base_r[idx]
+        ins.append((pl, pr))
+    want = []
+    for pl, pr in ins:
+        o = b.process(pl.array, pr.array, bf, bf / fx)
+        want.append({k: v.copy() for k, v in o.items()})
+    outs = [b.alloc_outputs(n, pinned=True) for _ in range(4)]
+    for k, (pl, pr) in enumerate(ins):  # four calls in flight back to back
+        b.process_async(pl.array, pr.array, bf, bf / fx, outs[k])
+    b.wait()
+    res = outs
+    for k in range(4):
+        for key in ("n_left", "n_right"):
+            assert np.array_equal(res[k][key], want[k][key]), (k, key)
+        for f in range(n):
+            a, c = res[k]["n_left"][f], res[k]["n_right"][f]
+            assert np.array_equal(res[k]["kps_left"][f][:a], want[k]["kps_left"][f][:a]), (k, f)
+            assert np.array_equal(res[k]["desc_left"][f][:a], want[k]["desc_left"][f][:a]), (k, f)
+            assert np.array_equal(res[k]["kps_right"][f][:c], want[k]["kps_right"][f][:c]), (k, f)
+            assert np.array_equal(res[k]["u_right"][f][:a], want[k]["u_right"][f][:a]), (k, f)
+            assert np.array_equal(res[k]["depth"][f][:a], want[k]["depth"][f][:a]), (k, f)
+    # in flight + another layout + another entry point
+    b.process_async(ins[0][0].array, ins[0][1].array, bf, bf / fx, outs[0])
+    small = b.process(ins[1][0].array[:20], ins[1][1].array[:20], bf, bf / fx)
+    assert np.array_equal(small["n_left"], want[1]["n_left"][:20])
+    assert np.array_equal(outs[0]["n_left"], want[0]["n_left"])  # the async call was drained before the layout changed
+    b.process_async(ins[2][0].array, ins[2][1].array, bf, bf / fx, outs[1])
+    nl_, nr_, nm_ = b.stats(n)  # drains
+    assert nl_ == int(want[2]["n_left"].sum()) and np.array_equal(outs[1]["n_right"], want[2]["n_right"])
+
+
 def test_cpp_shim_reference_signature(tmp_path):
     """include/ORBextractorGPU.h (the C++ class with the reference's constructor/operator()/getters) driven like
     Frame::Frame(stereo): two extractors on two std::threads, then ComputeStereoMatches — compiled here with g++."""
