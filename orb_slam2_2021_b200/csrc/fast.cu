@@ -8,20 +8,21 @@
 // which is threshold independent: the pixel is a FAST corner at threshold t iff m > t and OpenCV's
 // score is m-1. NMS keeps a pixel iff m is strictly greater than the strengths of its 8 neighbours
 // (pixels outside the ROI interior count 0). Because a neighbour that is not a corner at t has
-// m <= t < m_centre, the kept set at threshold t is {NMS maxima of the minTh map with m > t}: one
-// pass yields both thresholds, and the cell falls back to minTh iff no maximum exceeds iniTh —
-// exactly "FAST(ini) came back empty" (:814). Keypoints are written row-major into the cell's slot
-// array, so cells concatenated in table order give the reference's candidate order.
+// m <= t < m_centre, the NMS at threshold t only needs the strengths above t. The cell is first run at
+// iniTh (cheap pre-test, network, map and NMS all on the pixels that can be corners at iniTh); only a
+// cell whose FAST(iniTh) comes back empty (:814) repeats at minTh. Keypoints are written row-major into
+// the cell's slot array, so cells concatenated in table order give the reference's candidate order.
 //
 // Blackwell mapping (measured with tools/ubench/pipes.cu: VIMNMX3.U16x2 issues at the same rate as a
 // 32-bit IMNMX, so packing two pixels per register halves the ALU-pipe work that bounds this kernel):
 //   * the ROI arrives by ONE TMA box load (cp.async.bulk.tensor.3d, 64 or 96 columns starting at x0 & ~15 —
 //     the copy engine addresses the innermost dimension in 16-byte units — by rhMax rows) signalled on an
 //     mbarrier;
-//   * pass 1 walks the raw tile one aligned 32-bit word per thread: it widens the bytes into two 16-bit
-//     layouts, A[y][j] = I(xa+j, y) and B[y][j] = I(xa+j-1, y) (xa = x0 & ~3), and runs a byte-wise NECESSARY
-//     test for a corner at minTh on 4 pixels at once (VABSDIFF4 + SWAR compare against the compass points);
-//     surviving pixel PAIRS are appended to a warp-private task list by ballot (no atomics);
+//   * a widening pass walks the raw tile one aligned 32-bit word per thread into two 16-bit layouts,
+//     A[y][j] = I(xa+j, y) and B[y][j] = I(xa+j-1, y) (xa = x0 & ~3); pass 1 runs a byte-wise NECESSARY test for a
+//     corner at the attempt's threshold on the interior words, 4 pixels at once (VABSDIFF4 + SWAR compare against
+//     the compass points); a thread keeps its surviving pixel PAIRS as bits and appends them to the CTA's task
+//     list once (one warp scan and one shared atomic per warp);
 //   * pass 2 runs the exact test on the listed pairs only. A thread owns two horizontally adjacent pixels
 //     (even tile column first); for every ring offset the pair (ring(x), ring(x+1)) is ONE aligned 32-bit
 //     LDS (from A for even dx, from B+1 for odd dx) that is already a u16x2 vector — no byte extraction;
@@ -99,8 +100,8 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     constexpr int BW = SA == 48 ? 64 : 96;      // TMA box width in bytes
     extern __shared__ __align__(128) uint8_t fast_smem[];
     __shared__ __align__(8) uint64_t bar;
-    __shared__ int listCnt;
-    __shared__ int warpTasks[FAST_WARPS], warpNz[FAST_WARPS];
+    __shared__ int listCnt, taskCnt;
+    __shared__ int warpNz[FAST_WARPS];
 
     uint8_t* T = fast_smem;                                                     // raw box [rhMax][BW]
     uint16_t* A = reinterpret_cast<uint16_t*>(fast_smem + ((rhMax * BW + 127) & ~127));  // A[y][j] = I(xa + j, y0 + y), xa = x0 & ~3
@@ -121,6 +122,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) {
         listCnt = 0;
+        taskCnt = 0;
         orbx_mbar_init(&bar, 1);
         orbx_fence_mbar_init();
         orbx_mbar_expect_tx(&bar, rhMax * BW);
@@ -134,48 +136,71 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     __syncthreads();  // barrier initialised (and armed) before anybody polls it
     orbx_mbar_wait(&bar, 0);
 
-    // ---- pass 1 over the raw tile, one aligned 32-bit word (4 pixels) per thread and step:
-    //  (a) widen the bytes into the two u16 pair layouts A/B used by the min/max network;
-    //  (b) on interior words, a cheap NECESSARY test for "corner at minTh": any 9 contiguous ring positions contain two
-    //      ADJACENT compass points (0,4,8,12), so a corner needs (|d0|>t or |d8|>t) and (|d4|>t or |d12|>t). Four
-    //      VABSDIFF4 + a SWAR byte compare test 4 pixels at once; surviving pixel PAIRS (~30 % on the synthetic scenes,
-    //      far fewer on low-texture images) go to a WARP-PRIVATE task list (no atomics).
-    // Pairs are aligned to even tile columns, so even ring offsets always read A and odd ones B.
+    // ---- widening pass over the raw tile, one aligned 32-bit word (4 pixels) per thread and step: the bytes go into the two
+    // u16 pair layouts A/B used by the min/max network. Thread = (word column j, row y) with j fixed: 128/nw rows per step, so
+    // that all addresses advance by a constant (threads past the last whole row idle: < nw of 128).
     const int tmin = p.minTh, tini = p.iniTh;
     const int o = cell.x0 & 3;
     const int ca0 = o + 3;                        // A-column of interior pixel 0
     const int SD = 2 + ((o + 1) & 1) - ca0;       // strength-map column = A-column + SD (even, keeps pairs word aligned)
-    uint16_t* list = lists + warp * listCap;
-    int ntask = 0;  // warp-uniform
+    const uint32_t* tw0 = reinterpret_cast<const uint32_t*>(T) + ((cell.x0 & 15) >> 2);  // word of A-columns 0..3, row 0
     {
-        // thread = (word column j, row y) with j fixed: 128/nw rows per step, so that the column tests and all addresses are
-        // loop invariant or advance by a constant (threads past the last whole row idle: < nw of 128)
         const int nw = (o + rw + 4) >> 2;  // words covering A-columns 0 .. o+rw (one past the ROI, read by boundary pairs)
         const uint32_t rcp = c_recip[nw];
         const int qStep = (int)((FAST_THREADS * rcp) >> 16);  // rows per step
         const int yq = (int)((threadIdx.x * rcp) >> 16);
         const int j = threadIdx.x - yq * nw;
-        const bool active = yq < qStep;
-        // pair q (A-columns 4j+2q, +1) holds an interior pixel iff 4j+2q+1 >= ca0 and 4j+2q < ca0+iw
-        const bool v0 = active && 4 * j + 1 >= ca0 && 4 * j < ca0 + iw, v1 = active && 4 * j + 3 >= ca0 && 4 * j + 2 < ca0 + iw;
-        const uint32_t* tw = reinterpret_cast<const uint32_t*>(T) + ((cell.x0 & 15) >> 2) + yq * (BW / 4) + j;
+        const uint32_t* tw = tw0 + yq * (BW / 4) + j;
         uint2* pa = reinterpret_cast<uint2*>(A + yq * SA + 4 * j);
         uint2* pb = reinterpret_cast<uint2*>(B + yq * SA + 4 * j);
-        const uint32_t K = 0x01010101u * (uint32_t)(0x7F - min(tmin, 0x7F));
-        const unsigned lt = (1u << lane) - 1;
-        const int yEnd = active ? rh : 0;
-        uint32_t code = (uint32_t)((yq - 3) * 256 + 2 * j);  // list entry of pair 0: (y - 3) << 8 | pair column
+        const int yEnd = yq < qStep ? rh : 0;
 #pragma unroll 1
-        for (int y = yq, ys = 0; ys < rh; ys += qStep, y += qStep) {  // (ys: uniform trip count for the ballots)
-            unsigned kk = 0;
-            if (y < yEnd) {
-                const uint32_t w = tw[0], wn = tw[1], wp = tw[-1];  // inside the box: (x0&15)/4 + nw + 1 <= BW/4; tw[-1] of the
-                const uint32_t t = __funnelshift_r(wp, w, 24);     // first word is junk that only feeds masked pixels
-                pa[0] = make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
-                pb[0] = make_uint2(__byte_perm(t, 0, 0x4140), __byte_perm(t, 0, 0x4342));
-                if ((unsigned)(y - 3) < (unsigned)ih && (v0 || v1)) {
+        for (int y = yq; y < yEnd; y += qStep) {
+            const uint32_t w = tw[0], wp = tw[-1];           // inside the box; tw[-1] of the first word is junk that only
+            const uint32_t t = __funnelshift_r(wp, w, 24);   // feeds masked pixels
+            pa[0] = make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
+            pb[0] = make_uint2(__byte_perm(t, 0, 0x4140), __byte_perm(t, 0, 0x4342));
+            tw += qStep * (BW / 4);
+            pa += qStep * (SA / 4);
+            pb += qStep * (SA / 4);
+        }
+    }
+    // ---- threshold attempts (:812-819): first iniTh; only a cell whose FAST(iniTh) comes back empty repeats at minTh. A
+    // neighbour that is not a corner at t has m <= t < m_centre, so the NMS at threshold t only needs the strengths m > t:
+    // everything below (pre-test, network, map, NMS) runs on the pixels that can be corners at the attempt's threshold.
+    // The strength map of a failed first attempt needs no clearing: the minTh attempt rewrites a superset with equal values.
+    uint16_t* tasks = lists;                                  // CTA-wide list of surviving pixel pairs (4 * listCap entries)
+    uint32_t* kept = reinterpret_cast<uint32_t*>(T);          // NMS maxima: key | m << 16 (the raw tile is dead by then)
+    const unsigned lt = (1u << lane) - 1;
+    // pre-test thread mapping: fixed interior word column j per thread, 128/nwi interior rows per step
+    const int jmin = ca0 >> 2, nwi = ((ca0 + iw - 1) >> 2) - jmin + 1;
+    const uint32_t rcpi = c_recip[nwi];
+    const int pStep = (int)((FAST_THREADS * rcpi) >> 16);
+    const int pyq = (int)((threadIdx.x * rcpi) >> 16);
+    const int pj = jmin + (int)threadIdx.x - pyq * nwi;
+    const bool pact = pyq < pStep;
+    // pair q (A-columns 4j+2q, +1) holds an interior pixel iff 4j+2q+1 >= ca0 and 4j+2q < ca0+iw
+    const unsigned vmask = !pact ? 0u : ((4 * pj + 1 >= ca0 && 4 * pj < ca0 + iw) ? 1u : 0u) | ((4 * pj + 3 >= ca0 && 4 * pj + 2 < ca0 + iw) ? 2u : 0u);
+    int thr = tini;
+#pragma unroll 1
+    for (int attempt = 0;; ++attempt) {
+        // ---- pass 1: a cheap NECESSARY test for "corner at thr" on the raw words: any 9 contiguous ring positions contain
+        // two ADJACENT compass points (0,4,8,12), so a corner needs (|d0|>t or |d8|>t) and (|d4|>t or |d12|>t). Four
+        // VABSDIFF4 + a SWAR byte compare test 4 pixels at once. A thread collects 2 bits per step in a register and appends
+        // its surviving pixel PAIRS once per 16 steps: one warp scan + one shared atomic per warp (pairs are aligned to even
+        // tile columns, so even ring offsets always read A and odd ones B; the order of the list does not matter).
+        {
+            const uint32_t K = 0x01010101u * (uint32_t)(0x7F - min(thr, 0x7F));
+            const uint32_t* tw = tw0 + (pyq + 3) * (BW / 4) + pj;
+            const int nSteps = (ih + pStep - 1) / pStep;  // uniform
+            uint32_t bits = 0;
+            uint32_t code0 = (uint32_t)(pyq * 256 + 2 * pj);  // list entry of pair 0 at the first step of the current group
+#pragma unroll 1
+            for (int s = 0, iy = pyq; s < nSteps; ++s, iy += pStep) {
+                if (vmask && iy < ih) {
                     uint32_t m = 0x80808080u;
-                    if (tmin < 0x7F) {  // (thresholds >= 127 skip the pre-test: every interior pair is a task)
+                    if (thr < 0x7F) {  // (thresholds >= 127 skip the pre-test: every interior pair is a task)
+                        const uint32_t w = tw[0], wn = tw[1], wp = tw[-1];
                         const uint32_t up = tw[-3 * (BW / 4)], dn = tw[3 * (BW / 4)];
                         const uint32_t lf = __funnelshift_r(wp, w, 8), rt = __funnelshift_r(w, wn, 24);  // columns -3 / +3
                         const uint32_t a0 = __vabsdiffu4(dn, w), a8 = __vabsdiffu4(up, w), a4 = __vabsdiffu4(rt, w), a12 = __vabsdiffu4(lf, w);
@@ -184,109 +209,105 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
                         const uint32_t f4 = ((a4 & 0x7F7F7F7Fu) + K) | a4, f12 = ((a12 & 0x7F7F7F7Fu) + K) | a12;
                         m = (f0 | f8) & (f4 | f12);
                     }
-                    kk = (v0 && (m & 0x00008080u) ? 1u : 0u) | (v1 && (m & 0x80800000u) ? 2u : 0u);
+                    const uint32_t kk = ((m & 0x00008080u) ? 1u : 0u) | ((m & 0x80800000u) ? 2u : 0u);
+                    bits |= (kk & vmask) << (2 * (s & 15));
+                }
+                tw += pStep * (BW / 4);
+                if ((s & 15) == 15 || s == nSteps - 1) {  // uniform: append this thread's pairs of the last <= 16 steps
+                    int incl = __popc(bits);
+                    const int mine = incl;
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+                        const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                        if (lane >= d) incl += v;
+                    }
+                    int base = 0;
+                    if (lane == 31) base = atomicAdd(&taskCnt, incl);
+                    int pos = __shfl_sync(0xffffffffu, base, 31) + incl - mine;
+                    while (bits) {
+                        const int b = __ffs(bits) - 1;
+                        bits &= bits - 1;
+                        tasks[pos++] = (uint16_t)(code0 + (uint32_t)((b >> 1) * pStep) * 256u + (uint32_t)(b & 1));
+                    }
+                    code0 += (uint32_t)(16 * pStep) << 8;
                 }
             }
-            const unsigned b0 = __ballot_sync(0xffffffffu, kk & 1), b1 = __ballot_sync(0xffffffffu, kk & 2);
-            const int n0 = __popc(b0);
-            if (kk & 1) list[ntask + __popc(b0 & lt)] = (uint16_t)code;
-            if (kk & 2) list[ntask + n0 + __popc(b1 & lt)] = (uint16_t)(code + 1);
-            ntask += n0 + __popc(b1);
-            tw += qStep * (BW / 4);
-            pa += qStep * (SA / 4);
-            pb += qStep * (SA / 4);
-            code += (uint32_t)qStep << 8;
         }
-    }
-    if (lane == 0) warpTasks[warp] = ntask;
-    __syncthreads();
-    // ---- pass 2: the min/max network on the surviving pairs (results go to the map by position). The four warp lists
-    // are walked as one sequence so that every warp step but the last is full.
-    // position g of the concatenated sequence lives at lists[g + adj], adj = (list index) * listCap - (tasks in the lists before)
-    const int nt0 = warpTasks[0], nt1 = nt0 + warpTasks[1], nt2 = nt1 + warpTasks[2], ntAll = nt2 + warpTasks[3];
-    const int ta1 = listCap - nt0, ta2 = 2 * listCap - nt1, ta3 = 3 * listCap - nt2;
-    {
-        const uint16_t* pevn = A;      // even dx: pair (A[c+dx], A[c+dx+1]), c even
-        const uint16_t* podd = B + 1;  // odd dx:  pair (B[c+dx+1], B[c+dx+2]) = (I(c+dx), I(c+dx+1))
-        uint16_t* nz = lists + (FAST_WARPS + warp) * listCap;  // this warp's list of pairs with a non-zero strength
-        int nnz = 0;                                           // warp-uniform
-        const unsigned lt = (1u << lane) - 1;
+        __syncthreads();  // A/B complete (first attempt), task list complete
+        // ---- pass 2: the min/max network on the surviving pairs (results go to the map by position)
+        const int ntAll = taskCnt;
+        {
+            const uint16_t* pevn = A;      // even dx: pair (A[c+dx], A[c+dx+1]), c even
+            const uint16_t* podd = B + 1;  // odd dx:  pair (B[c+dx+1], B[c+dx+2]) = (I(c+dx), I(c+dx+1))
+            uint16_t* nz = lists + (FAST_WARPS + warp) * listCap;  // this warp's list of pairs with a non-zero strength
+            int nnz = 0;                                           // warp-uniform
 #pragma unroll 1
-        for (int g0 = warp * 32; g0 < ntAll; g0 += FAST_THREADS) {
-            const int g = g0 + lane;
-            bool hit = false;
-            int task = 0;
-            if (g < ntAll) {
-                task = lists[g + (g >= nt2 ? ta3 : g >= nt1 ? ta2 : g >= nt0 ? ta1 : 0)];
-                const int y = task >> 8, c = 2 * (task & 255);
-                int m0, m1;
-                fast_strength2<SA>(podd + (y + 3) * SA + c, pevn + (y + 3) * SA + c, m0, m1);
-                const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
-                m0 = (m0 > tmin && ix >= 0) ? m0 : 0;
-                m1 = (m1 > tmin && ix + 1 < iw) ? m1 : 0;
-                hit = (m0 | m1) != 0;
-                if (hit) *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + c + SD) = (uint32_t)m0 | ((uint32_t)m1 << 16);  // map is pre-zeroed
+            for (int g0 = warp * 32; g0 < ntAll; g0 += FAST_THREADS) {
+                const int g = g0 + lane;
+                bool hit = false;
+                int task = 0;
+                if (g < ntAll) {
+                    task = tasks[g];
+                    const int y = task >> 8, c = 2 * (task & 255);
+                    int m0, m1;
+                    fast_strength2<SA>(podd + (y + 3) * SA + c, pevn + (y + 3) * SA + c, m0, m1);
+                    const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
+                    m0 = (m0 > thr && ix >= 0) ? m0 : 0;
+                    m1 = (m1 > thr && ix + 1 < iw) ? m1 : 0;
+                    hit = (m0 | m1) != 0;
+                    if (hit) *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + c + SD) = (uint32_t)m0 | ((uint32_t)m1 << 16);  // map is pre-zeroed
+                }
+                const unsigned bh = __ballot_sync(0xffffffffu, hit);
+                if (hit) nz[nnz + __popc(bh & lt)] = (uint16_t)task;
+                nnz += __popc(bh);
             }
-            const unsigned bh = __ballot_sync(0xffffffffu, hit);
-            if (hit) nz[nnz + __popc(bh & lt)] = (uint16_t)task;
-            nnz += __popc(bh);
+            if (lane == 0) warpNz[warp] = nnz;
         }
-        if (lane == 0) warpNz[warp] = nnz;
-    }
-    __syncthreads();
+        __syncthreads();
 
-    // ---- NMS over the pairs that hold a non-zero strength (second set of warp lists): strict maximum over the 8
-    // neighbours in the strength map. Maxima go to a CTA list kept[] = key | m << 16, key = y*64 + x (interior coords).
-    uint32_t* kept = reinterpret_cast<uint32_t*>(A);  // A/B are dead after pass 2
-    bool anyIni = false;
-    const int nz0 = warpNz[0], nz1 = nz0 + warpNz[1], nz2 = nz1 + warpNz[2], nzAll = nz2 + warpNz[3];
-    const uint16_t* nzLists = lists + FAST_WARPS * listCap;
-    const int za1 = listCap - nz0, za2 = 2 * listCap - nz1, za3 = 3 * listCap - nz2;
+        // ---- NMS over the pairs that hold a non-zero strength (warp lists): strict maximum over the 8 neighbours in the
+        // strength map. Maxima go to a CTA list kept[] = key | m << 16, key = y*64 + x (interior coords).
+        const int nz0 = warpNz[0], nz1 = nz0 + warpNz[1], nz2 = nz1 + warpNz[2], nzAll = nz2 + warpNz[3];
+        const uint16_t* nzLists = lists + FAST_WARPS * listCap;
+        const int za1 = listCap - nz0, za2 = 2 * listCap - nz1, za3 = 3 * listCap - nz2;
 #pragma unroll 1
-    for (int g = threadIdx.x; g < nzAll; g += FAST_THREADS) {
-        const int task = nzLists[g + (g >= nz2 ? za3 : g >= nz1 ? za2 : g >= nz0 ? za1 : 0)], y = task >> 8, cc = 2 * (task & 255);
-        const uint16_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair, word aligned
-        const uint32_t mm = *reinterpret_cast<const uint32_t*>(c);
-        const uint32_t u0 = *reinterpret_cast<const uint32_t*>(c - SA - 2), u1 = *reinterpret_cast<const uint32_t*>(c - SA), u2 = *reinterpret_cast<const uint32_t*>(c - SA + 2);
-        const uint32_t l0 = *reinterpret_cast<const uint32_t*>(c - 2), l2 = *reinterpret_cast<const uint32_t*>(c + 2);
-        const uint32_t d0 = *reinterpret_cast<const uint32_t*>(c + SA - 2), d1 = *reinterpret_cast<const uint32_t*>(c + SA), d2 = *reinterpret_cast<const uint32_t*>(c + SA + 2);
-        // column maxima over the three rows, as pairs (x-2,x-1) (x,x+1) (x+2,x+3)
-        const uint32_t cm0 = __vimax3_u16x2(u0, l0, d0), cm1 = __vimax3_u16x2(u1, mm, d1), cm2 = __vimax3_u16x2(u2, l2, d2);
-        const uint32_t ud = __vimax3_u16x2(u1, d1, d1);
-        // neighbours of pixel 0 (x): columns x-1, x+1 (all rows) and rows above/below in column x; pixel 1 likewise
-        const int m0 = mm & 0xFFFFu, m1 = mm >> 16;
-        const int n0 = max(max((int)(cm0 >> 16), (int)(cm1 >> 16)), (int)(ud & 0xFFFFu));
-        const int n1 = max(max((int)(cm1 & 0xFFFFu), (int)(cm2 & 0xFFFFu)), (int)(ud >> 16));
-        const int ix = cc - ca0;
-        if (m0 > n0) {
-            kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + ix) | ((uint32_t)m0 << 16);
-            anyIni |= m0 > tini;
+        for (int g = threadIdx.x; g < nzAll; g += FAST_THREADS) {
+            const int task = nzLists[g + (g >= nz2 ? za3 : g >= nz1 ? za2 : g >= nz0 ? za1 : 0)], y = task >> 8, cc = 2 * (task & 255);
+            const uint16_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair, word aligned
+            const uint32_t mm = *reinterpret_cast<const uint32_t*>(c);
+            const uint32_t u0 = *reinterpret_cast<const uint32_t*>(c - SA - 2), u1 = *reinterpret_cast<const uint32_t*>(c - SA), u2 = *reinterpret_cast<const uint32_t*>(c - SA + 2);
+            const uint32_t l0 = *reinterpret_cast<const uint32_t*>(c - 2), l2 = *reinterpret_cast<const uint32_t*>(c + 2);
+            const uint32_t d0 = *reinterpret_cast<const uint32_t*>(c + SA - 2), d1 = *reinterpret_cast<const uint32_t*>(c + SA), d2 = *reinterpret_cast<const uint32_t*>(c + SA + 2);
+            // column maxima over the three rows, as pairs (x-2,x-1) (x,x+1) (x+2,x+3)
+            const uint32_t cm0 = __vimax3_u16x2(u0, l0, d0), cm1 = __vimax3_u16x2(u1, mm, d1), cm2 = __vimax3_u16x2(u2, l2, d2);
+            const uint32_t ud = __vimax3_u16x2(u1, d1, d1);
+            // neighbours of pixel 0 (x): columns x-1, x+1 (all rows) and rows above/below in column x; pixel 1 likewise
+            const int m0 = mm & 0xFFFFu, m1 = mm >> 16;
+            const int n0 = max(max((int)(cm0 >> 16), (int)(cm1 >> 16)), (int)(ud & 0xFFFFu));
+            const int n1 = max(max((int)(cm1 & 0xFFFFu), (int)(cm2 & 0xFFFFu)), (int)(ud >> 16));
+            const int ix = cc - ca0;
+            if (m0 > n0) kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + ix) | ((uint32_t)m0 << 16);
+            if (m1 > n1) kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + ix + 1) | ((uint32_t)m1 << 16);
         }
-        if (m1 > n1) {
-            kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + ix + 1) | ((uint32_t)m1 << 16);
-            anyIni |= m1 > tini;
-        }
+        __syncthreads();  // publishes kept[] and listCnt
+        if (listCnt > 0 || attempt == 1 || tmin >= thr) break;
+        thr = tmin;       // :814 FAST(iniTh) came back empty: once more with minTh
+        if (threadIdx.x == 0) taskCnt = 0;  // (last read before the barrier that ended pass 2)
+        __syncthreads();
     }
-    const bool useIni = __syncthreads_or(anyIni);  // :814 fallback to minTh iff FAST(ini) is empty; also publishes kept[]
 
-    // ---- ordered emission: rank of a selected maximum = number of selected maxima with a smaller row-major key
+    // ---- ordered emission: rank of a maximum = number of maxima with a smaller row-major key
     const int nkept = listCnt;
-    const int thr = useIni ? tini : 0;
     const uint32_t slot0 = L.slotBase + (uint32_t)(cellId - L.cellBase) * L.slotCap;
     uint32_t* out = p.cellKp + (size_t)img * p.slotTotal + slot0;
+    if (threadIdx.x == 0) *cntOut = nkept;
 #pragma unroll 1
-    for (int i = threadIdx.x; i < nkept || i == 0; i += FAST_THREADS) {
-        const uint32_t e = i < nkept ? kept[i] : 0u;
+    for (int i = threadIdx.x; i < nkept; i += FAST_THREADS) {
+        const uint32_t e = kept[i];
         const int key = e & 0xFFFFu, m = e >> 16;
-        int rank = 0, total = 0;
-        for (int j = 0; j < nkept; ++j) {
-            const uint32_t f = kept[j];
-            const bool sel = (int)(f >> 16) > thr;
-            total += sel;
-            rank += sel && (int)(f & 0xFFFFu) < key;
-        }
-        if (i < nkept && m > thr) out[rank] = (uint32_t)((key & 63) + 3) | ((uint32_t)((key >> 6) + 3) << 8) | ((uint32_t)(m - 1) << 16);
-        if (i == 0) *cntOut = total;
+        int rank = 0;
+        for (int j = 0; j < nkept; ++j) rank += (int)(kept[j] & 0xFFFFu) < key;
+        out[rank] = (uint32_t)((key & 63) + 3) | ((uint32_t)((key >> 6) + 3) << 8) | ((uint32_t)(m - 1) << 16);
     }
 }
 
