@@ -181,6 +181,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     const bool pact = pyq < pStep;
     // pair q (A-columns 4j+2q, +1) holds an interior pixel iff 4j+2q+1 >= ca0 and 4j+2q < ca0+iw
     const unsigned vmask = !pact ? 0u : ((4 * pj + 1 >= ca0 && 4 * pj < ca0 + iw) ? 1u : 0u) | ((4 * pj + 3 >= ca0 && 4 * pj + 2 < ca0 + iw) ? 2u : 0u);
+    const uint32_t* ptw0 = tw0 + (pyq + 3) * (BW / 4) + pj;
     int thr = tini;
 #pragma unroll 1
     for (int attempt = 0;; ++attempt) {
@@ -190,47 +191,49 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         // its surviving pixel PAIRS once per 16 steps: one warp scan + one shared atomic per warp (pairs are aligned to even
         // tile columns, so even ring offsets always read A and odd ones B; the order of the list does not matter).
         {
+            // bit 7 of each byte of f(x) = ((x & 0x7F..) + K) | x is set iff x > min(thr, 127): exact below 127, still
+            // necessary above
             const uint32_t K = 0x01010101u * (uint32_t)(0x7F - min(thr, 0x7F));
-            const uint32_t* tw = tw0 + (pyq + 3) * (BW / 4) + pj;
-            const int nSteps = (ih + pStep - 1) / pStep;  // uniform
-            uint32_t bits = 0;
+            const uint32_t* tw = ptw0;
             uint32_t code0 = (uint32_t)(pyq * 256 + 2 * pj);  // list entry of pair 0 at the first step of the current group
 #pragma unroll 1
-            for (int s = 0, iy = pyq; s < nSteps; ++s, iy += pStep) {
-                if (vmask && iy < ih) {
-                    uint32_t m = 0x80808080u;
-                    if (thr < 0x7F) {  // (thresholds >= 127 skip the pre-test: every interior pair is a task)
+            for (int g0 = 0; g0 < ih; g0 += 16 * pStep) {   // groups of 16 steps (uniform)
+                uint32_t bits = 0;
+                int sh = 0;
+#pragma unroll 1
+                for (int y0s = g0; y0s < min(ih, g0 + 16 * pStep); y0s += pStep, sh += 2) {  // uniform trip count
+                    if (vmask && y0s + pyq < ih) {
                         const uint32_t w = tw[0], wn = tw[1], wp = tw[-1];
                         const uint32_t up = tw[-3 * (BW / 4)], dn = tw[3 * (BW / 4)];
                         const uint32_t lf = __funnelshift_r(wp, w, 8), rt = __funnelshift_r(w, wn, 24);  // columns -3 / +3
                         const uint32_t a0 = __vabsdiffu4(dn, w), a8 = __vabsdiffu4(up, w), a4 = __vabsdiffu4(rt, w), a12 = __vabsdiffu4(lf, w);
-                        // bit 7 of each byte of f(x) = ((x & 0x7F..) + K) | x is set iff x > t
                         const uint32_t f0 = ((a0 & 0x7F7F7F7Fu) + K) | a0, f8 = ((a8 & 0x7F7F7F7Fu) + K) | a8;
                         const uint32_t f4 = ((a4 & 0x7F7F7F7Fu) + K) | a4, f12 = ((a12 & 0x7F7F7F7Fu) + K) | a12;
-                        m = (f0 | f8) & (f4 | f12);
+                        const uint32_t m = (f0 | f8) & (f4 | f12);
+                        const uint32_t kk = ((m & 0x00008080u) ? 1u : 0u) | ((m & 0x80800000u) ? 2u : 0u);
+                        bits |= (kk & vmask) << sh;
                     }
-                    const uint32_t kk = ((m & 0x00008080u) ? 1u : 0u) | ((m & 0x80800000u) ? 2u : 0u);
-                    bits |= (kk & vmask) << (2 * (s & 15));
+                    tw += pStep * (BW / 4);
                 }
-                tw += pStep * (BW / 4);
-                if ((s & 15) == 15 || s == nSteps - 1) {  // uniform: append this thread's pairs of the last <= 16 steps
-                    int incl = __popc(bits);
-                    const int mine = incl;
+                // append this thread's pairs of the group
+                int incl = __popc(bits);
+                const int mine = incl;
 #pragma unroll
-                    for (int d = 1; d < 32; d <<= 1) {
-                        const int v = __shfl_up_sync(0xffffffffu, incl, d);
-                        if (lane >= d) incl += v;
-                    }
-                    int base = 0;
-                    if (lane == 31) base = atomicAdd(&taskCnt, incl);
-                    int pos = __shfl_sync(0xffffffffu, base, 31) + incl - mine;
-                    while (bits) {
-                        const int b = __ffs(bits) - 1;
-                        bits &= bits - 1;
-                        tasks[pos++] = (uint16_t)(code0 + (uint32_t)((b >> 1) * pStep) * 256u + (uint32_t)(b & 1));
-                    }
-                    code0 += (uint32_t)(16 * pStep) << 8;
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += v;
                 }
+                int base = 0;
+                if (lane == 31) base = atomicAdd(&taskCnt, incl);
+                uint16_t* dst = tasks + (__shfl_sync(0xffffffffu, base, 31) + incl - mine);
+                uint32_t c = code0;
+                while (bits) {
+                    if (bits & 1) *dst++ = (uint16_t)c;
+                    if (bits & 2) *dst++ = (uint16_t)(c + 1);
+                    bits >>= 2;
+                    c += (uint32_t)pStep << 8;
+                }
+                code0 += (uint32_t)(16 * pStep) << 8;
             }
         }
         __syncthreads();  // A/B complete (first attempt), task list complete
