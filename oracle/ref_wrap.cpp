@@ -1,0 +1,221 @@
+// oracle/ref_wrap.cpp — TEST INFRASTRUCTURE ONLY (see orb_oracle.h).
+//
+// C entry points around the REFERENCE'S OWN ORB_SLAM2::ORBextractor, compiled from /root/reference/src/ORBextractor.cc
+// where it lies (oracle/Makefile, target _ref -> oracle/_ref/libref_orbextractor.so). The reference needs the OpenCV C++
+// API, which this image lacks; oracle/cvshim/ stands in for the API and this file supplies the five OpenCV functions the
+// reference calls, on top of the oracle's restatements in prims.cpp (pinned bit for bit against cv2 4.13 by
+// tests/test_oracle_kat.py). Everything above those primitives — pyramid loop, cell loop with the threshold fallback,
+// DistributeOctTree/DivideNode, IC_Angle, computeOrbDescriptor with its pattern, the output assembly — is the reference's
+// own object code, so tests that compare against this library pin the oracle's restatement of those parts (and the CUDA
+// path) against the reference itself.
+//
+// Determinism of DistributeOctTree: the reference sorts (size, ExtractorNode*) pairs (src/ORBextractor.cc:687), i.e. ties
+// are broken by heap address. This library replaces operator new by a bump arena that is active while a call runs and
+// never reuses memory inside a call, so addresses grow in allocation order and the tie-break becomes "later-created node
+// first" — one legitimate execution of the reference (an allocator that hands out increasing addresses), and the canonical
+// rule of the oracle and the CUDA path. The library is linked with -Bsymbolic so that only allocations made
+// by this library's own code (the reference's std::list / std::vector instantiations) use the arena.
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <sys/mman.h>
+#include <vector>
+
+#include <opencv2/core/core.hpp>
+
+#include "ORBextractor.h"
+#include "orb_oracle.h"
+
+// ---------------------------------------------------------------- arena behind operator new (active inside a call)
+namespace {
+struct Arena {
+    size_t used = 0;
+    bool active = false;
+    char* lo = nullptr;  // ONE address range per thread, so that addresses grow monotonically inside a call
+    char* hi = nullptr;
+};
+thread_local Arena g_arena;
+constexpr size_t kReserve = (size_t)4 << 30;  // address space only (MAP_NORESERVE); pages are touched on demand
+
+void* arena_alloc(size_t n)
+{
+    Arena& a = g_arena;
+    if (!a.lo) {
+        void* m = mmap(nullptr, kReserve, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_NORESERVE, -1, 0);
+        if (m == MAP_FAILED) { std::fprintf(stderr, "ref_wrap: arena reservation failed\n"); std::abort(); }
+        a.lo = (char*)m;
+        a.hi = a.lo + kReserve;
+        a.used = 0;
+    }
+    n = (n + 15) & ~(size_t)15;
+    if (a.used + n > kReserve) { std::fprintf(stderr, "ref_wrap: arena exhausted\n"); std::abort(); }
+    void* p = a.lo + a.used;
+    a.used += n;
+    return p;
+}
+inline bool in_arena(const void* p) { return g_arena.lo && (const char*)p >= g_arena.lo && (const char*)p < g_arena.hi; }
+}  // namespace
+
+void* operator new(size_t n)
+{
+    if (g_arena.active) return arena_alloc(n);
+    void* p = std::malloc(n ? n : 1);
+    if (!p) throw std::bad_alloc();
+    return p;
+}
+void* operator new[](size_t n) { return operator new(n); }
+void operator delete(void* p) noexcept
+{
+    if (!p || in_arena(p)) return;  // arena memory is dropped wholesale at the end of the call
+    std::free(p);
+}
+void operator delete[](void* p) noexcept { operator delete(p); }
+void operator delete(void* p, size_t) noexcept { operator delete(p); }
+void operator delete[](void* p, size_t) noexcept { operator delete(p); }
+
+// ---------------------------------------------------------------- the OpenCV functions the reference calls
+namespace cv {
+
+// cv::resize, INTER_LINEAR, CV_8UC1 (called at src/ORBextractor.cc:1118; dst is a preallocated ROI of the right size)
+void resize(const Mat& src, Mat& dst, Size dsize, double, double, int interpolation)
+{
+    if (interpolation != INTER_LINEAR) std::abort();
+    dst.create(dsize.height, dsize.width, CV_8UC1);
+    orc_resize_linear(src.data, src.cols, src.rows, (int)src.step, dst.data, dst.cols, dst.rows, (int)dst.step);
+}
+
+// cv::copyMakeBorder with BORDER_REFLECT_101 (:1120, :1130). src may be a ROI of dst (the in-place case of :1120): the
+// interior is then already in place and only the border is written, from interior pixels. BORDER_ISOLATED = do not look
+// outside the ROI, which is what this does in every case (for :1130 the source is a whole image).
+void copyMakeBorder(const Mat& src, Mat& dst, int top, int bottom, int left, int right, int borderType)
+{
+    if ((borderType & ~BORDER_ISOLATED) != BORDER_REFLECT_101) std::abort();
+    dst.create(src.rows + top + bottom, src.cols + left + right, CV_8UC1);
+    const bool inplace = src.data == dst.data + (size_t)top * dst.step + left && (size_t)src.step == (size_t)dst.step;
+    for (int y = 0; y < dst.rows; ++y) {
+        const int sy = orc_reflect101(y - top, src.rows);
+        const uchar* s = src.data + (size_t)sy * src.step;
+        uchar* d = dst.data + (size_t)y * dst.step;
+        const bool interiorRow = y >= top && y < top + src.rows;
+        for (int x = 0; x < dst.cols; ++x) {
+            const bool interior = interiorRow && x >= left && x < left + src.cols;
+            if (interior && inplace) continue;
+            d[x] = s[orc_reflect101(x - left, src.cols)];
+        }
+    }
+}
+
+// cv::FAST, TYPE_9_16 (:812, :817)
+void FAST(const Mat& image, std::vector<KeyPoint>& keypoints, int threshold, bool nonmaxSuppression)
+{
+    if (!nonmaxSuppression) std::abort();
+    keypoints.clear();
+    const int cap = image.rows * image.cols;
+    static thread_local orc_keypoint* tmp = nullptr;  // malloc-backed scratch: the arena never reuses memory inside a call
+    static thread_local int tmpCap = 0;
+    if (cap > tmpCap) {
+        tmp = (orc_keypoint*)std::realloc(tmp, (size_t)cap * sizeof(orc_keypoint));
+        tmpCap = cap;
+    }
+    const int n = orc_fast9(image.data, image.cols, image.rows, (int)image.step, threshold, tmp, cap);
+    keypoints.reserve(n);
+    for (int i = 0; i < n; ++i)
+        keypoints.push_back(KeyPoint(tmp[i].x, tmp[i].y, tmp[i].size, tmp[i].angle, tmp[i].response, tmp[i].octave, tmp[i].class_id));
+}
+
+// cv::GaussianBlur 7x7, sigma 2, BORDER_REFLECT_101, in place on a clone (:1084)
+void GaussianBlur(const Mat& src, Mat& dst, Size ksize, double sigmaX, double sigmaY, int borderType)
+{
+    if (ksize.width != 7 || ksize.height != 7 || sigmaX != 2 || sigmaY != 2 || borderType != BORDER_REFLECT_101) std::abort();
+    Mat out(src.rows, src.cols, CV_8UC1);
+    orc_gaussian7(src.data, src.cols, src.rows, (int)src.step, out.data, (int)out.step);
+    dst.create(src.rows, src.cols, CV_8UC1);
+    for (int y = 0; y < src.rows; ++y) std::memcpy(dst.ptr(y), out.ptr(y), (size_t)src.cols);
+}
+
+float fastAtan2(float y, float x) { return orc_fast_atan2(y, x); }
+
+void KeyPointsFilter::retainBest(std::vector<KeyPoint>&, int) { std::abort(); }  // only ComputeKeyPointsOld (never called)
+
+}  // namespace cv
+
+// ---------------------------------------------------------------- C entry points (ctypes)
+namespace {
+struct ArenaScope {  // operator new comes from the arena while the reference runs; everything is dropped afterwards
+    ArenaScope() { g_arena.active = true; g_arena.used = 0; }
+    ~ArenaScope() { g_arena.active = false; g_arena.used = 0; }
+};
+}  // namespace
+
+extern "C" {
+
+void* ref_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST)
+{
+    return new ORB_SLAM2::ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST);  // malloc-backed: arena inactive
+}
+
+void ref_destroy(void* h) { delete (ORB_SLAM2::ORBextractor*)h; }
+
+// scale tables through the reference's own getters; arrays of nlevels, any pointer may be NULL
+int ref_tables(void* h, float* scale, float* invScale, float* sigma2, float* invSigma2)
+{
+    ORB_SLAM2::ORBextractor* e = (ORB_SLAM2::ORBextractor*)h;
+    const int n = e->GetLevels();
+    const std::vector<float> a = e->GetScaleFactors(), b = e->GetInverseScaleFactors(), c = e->GetScaleSigmaSquares(),
+                             d = e->GetInverseScaleSigmaSquares();
+    for (int i = 0; i < n; ++i) {
+        if (scale) scale[i] = a[i];
+        if (invScale) invScale[i] = b[i];
+        if (sigma2) sigma2[i] = c[i];
+        if (invSigma2) invSigma2[i] = d[i];
+    }
+    return n;
+}
+
+// ORBextractor::operator() (src/ORBextractor.cc:1041-1103). Returns the number of keypoints, or -1 if capacity is too
+// small (nothing is written then). kps has the cv::KeyPoint layout; desc is capacity x 32 bytes.
+int ref_extract(void* h, const uint8_t* img, int rows, int cols, int stride, orc_keypoint* kps, uint8_t* desc, int capacity)
+{
+    ORB_SLAM2::ORBextractor* e = (ORB_SLAM2::ORBextractor*)h;
+    int n;
+    {
+        ArenaScope scope;
+        {
+            cv::Mat image(rows, cols, CV_8UC1, (void*)img, (size_t)stride), mask, descriptors;
+            std::vector<cv::KeyPoint> keypoints;
+            (*e)(image, mask, keypoints, descriptors);
+            n = (int)keypoints.size();
+            if (n <= capacity) {
+                static_assert(sizeof(cv::KeyPoint) == sizeof(orc_keypoint), "cv::KeyPoint layout");
+                if (n) std::memcpy(kps, keypoints.data(), (size_t)n * sizeof(orc_keypoint));
+                for (int i = 0; i < n; ++i) std::memcpy(desc + (size_t)i * 32, descriptors.ptr(i), 32);
+            } else {
+                n = -1;
+            }
+        }  // the call's containers die before the arena is dropped
+    }
+    return n;
+}
+
+// mvImagePyramid[level] of the last call (the reference's public member), without its border
+int ref_level_size(void* h, int level, int* rows, int* cols)
+{
+    ORB_SLAM2::ORBextractor* e = (ORB_SLAM2::ORBextractor*)h;
+    if (level < 0 || level >= (int)e->mvImagePyramid.size() || e->mvImagePyramid[level].empty()) return -1;
+    *rows = e->mvImagePyramid[level].rows;
+    *cols = e->mvImagePyramid[level].cols;
+    return 0;
+}
+
+int ref_level_copy(void* h, int level, uint8_t* dst, int dstStride)
+{
+    ORB_SLAM2::ORBextractor* e = (ORB_SLAM2::ORBextractor*)h;
+    if (level < 0 || level >= (int)e->mvImagePyramid.size() || e->mvImagePyramid[level].empty()) return -1;
+    const cv::Mat& m = e->mvImagePyramid[level];
+    for (int y = 0; y < m.rows; ++y) std::memcpy(dst + (size_t)y * dstStride, m.ptr(y), (size_t)m.cols);
+    return 0;
+}
+
+}  // extern "C"

@@ -44,8 +44,8 @@ extern "C" int orbx_device_count(void)
 
 static int check_cfg(int nfeatures, float sf, int nlevels, int ini, int mn)
 {
-    if (nfeatures < 1 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !(sf > 1.0f) || !(sf <= 2.0f) || ini < 1 || mn < 1 || ini > 254 || mn > ini)
-        return fail(ORBX_ERR_ARG, "bad extractor parameters (need nfeatures>=1, 1<=nlevels<=12, 1<scaleFactor<=2, 1<=minTh<=iniTh<=254)");
+    if (nfeatures < 1 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !(sf > 1.0f) || !(sf <= 2.0f) || ini < 1 || mn < 1 || ini > 254 || mn > 254)
+        return fail(ORBX_ERR_ARG, "bad extractor parameters (need nfeatures>=1, 1<=nlevels<=12, 1<scaleFactor<=2, 1<=iniTh<=254, 1<=minTh<=254)");
     return ORBX_OK;
 }
 

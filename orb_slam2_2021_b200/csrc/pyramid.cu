@@ -41,6 +41,11 @@ struct ResizeArgs {
 // Source rows are walked by their UNCLIPPED index r = yofs .. yofs_last + 1 and read at min(r, sh - 1) (scale factors
 // above 1 never give a negative yofs): at the bottom edge, where OpenCV clips row sy + 1 onto the last row, the walk
 // simply visits that row twice, so a destination row always combines the previous and the current row of the walk.
+//
+// WIDE: a level ratio above 2 (scaleFactor 2 with an odd source size, e.g. 701 -> 350 columns) lets the four columns span
+// 9 source bytes and puts columns 2 and 3 at least 4 bytes past the first one; their pairs are then picked from bytes
+// sx0+4 .. sx0+11 (the third word always holds byte sx0+8) instead of sx0 .. sx0+7.
+template <bool WIDE>
 __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(const ResizeArgs A)
 {
     const int img = blockIdx.z;
@@ -61,7 +66,8 @@ __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(const Resize
         const int x = min(x0 + i, A.dw - 1);  // columns past the level land in the row padding
         const int sx = A.xofs[x];
         if (i == 0) sx0 = sx;
-        d[i] = sx - sx0;                      // 0 .. 6 for scale factors up to 2 (checked by the launcher)
+        d[i] = sx - sx0;                      // 0 .. 6 for level ratios up to 2, 0 .. 7 up to 7/3 (WIDE)
+        if (WIDE && i >= 2) d[i] = max(d[i] - 4, 0);  // relative to byte sx0+4 (only clamped columns fall below it)
         // the right neighbour is clamped to the last column (there c1 == 0 anyway, OpenCV sets f = 0 for sx >= sw-1)
         const int d1 = sx + 1 <= A.sw - 1 ? d[i] + 1 : d[i];
         d[i] |= d1 << 4;
@@ -91,7 +97,8 @@ __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(const Resize
         const uint32_t* pn = src + (size_t)min(r + 2, shm1) * spw;                                                       \
         N0 = __ldg(pn); N1 = __ldg(pn + 1); N2 = __ldg(pn + 2);                                                          \
         const uint32_t lo = __funnelshift_r(W0, W1, sh8), hi = __funnelshift_r(W1, W2, sh8); /* bytes sx0 .. sx0+7 */    \
-        const uint32_t pA = __byte_perm(lo, hi, selA), pB = __byte_perm(lo, hi, selB);                                   \
+        const uint32_t pA = __byte_perm(lo, hi, selA);                                                                   \
+        const uint32_t pB = WIDE ? __byte_perm(hi, W2 >> sh8, selB) : __byte_perm(lo, hi, selB);                         \
         /* H & ~15 = 16 (H >> 4): the vertical pass only ever uses H >> 4 */                                             \
         HC[0] = __dp2a_lo(coef[0], pA, 0u) & ~15u;                                                                       \
         HC[1] = __dp2a_hi(coef[1], pA, 0u) & ~15u;                                                                       \
@@ -162,6 +169,7 @@ void orbx_launch_pyramid(const OrbxParams& p, const int* const* tabs, cudaStream
         A.sw = S.w; A.sh = S.h; A.sp = S.pitch;
         A.dw = D.w; A.dh = D.h; A.dp = D.pitch;
         dim3 block(RS_TX, RS_TY), grid((D.w + 4 * RS_TX - 1) / (4 * RS_TX), (D.h + RS_ROWS * RS_TY - 1) / (RS_ROWS * RS_TY), p.imgs);
-        orbx_resize_kernel<<<grid, block, 0, s>>>(A);
+        if (S.w > 2 * D.w) orbx_resize_kernel<true><<<grid, block, 0, s>>>(A);   // ratio in (2, 7/3): scaleFactor <= 2 by contract
+        else orbx_resize_kernel<false><<<grid, block, 0, s>>>(A);
     }
 }
