@@ -1,12 +1,15 @@
 // oracle/cvshim/opencv2/cvshim.hpp — TEST INFRASTRUCTURE ONLY (see ../../orb_oracle.h).
 //
-// A minimal stand-in for the part of the OpenCV C++ API that /root/reference/src/ORBextractor.cc uses, so that the
-// reference's OWN translation unit can be compiled from where it lies (oracle/Makefile target _ref) although this image
-// has no OpenCV C++ headers or libraries. Nothing here is OpenCV code: the containers (Mat, KeyPoint, Point_, Size, Rect,
+// A minimal stand-in for the part of the OpenCV C++ API that /root/reference/src/ORBextractor.cc and src/Frame.cc use, so
+// that the reference's OWN translation units can be compiled from where they lie (oracle/Makefile target _ref) although
+// this image has no OpenCV C++ headers or libraries. Nothing here is OpenCV code: the containers (Mat, KeyPoint, Point_, Size, Rect,
 // InputArray/OutputArray) are written from the documented interface, and the five primitives the reference calls
 // (resize, copyMakeBorder, FAST, GaussianBlur, fastAtan2) forward to the oracle's restatements in oracle/prims.cpp, which
 // tests/test_oracle_kat.py pins bit for bit against the real OpenCV kernels through cv2 4.13.
-// Only CV_8UC1 matrices exist. Anything the reference does not call is absent.
+// Matrices are single-channel CV_8U or CV_32F. The float algebra (products, transposes, ...) exists so that ALL of
+// Frame.cc compiles; what actually runs from that file is ComputeStereoMatches and ComputeStereoFromRGBD (convertTo,
+// scalar * ones, difference, L1 norm on 11x11 patches of small integers: exact in float and double alike).
+// Anything the reference does not call is absent.
 #pragma once
 #include <algorithm>
 #include <cassert>
@@ -19,6 +22,7 @@
 #define CV_PI 3.1415926535897932384626433832795
 #define CV_8U 0
 #define CV_8UC1 0
+#define CV_32F 5
 
 typedef unsigned char uchar;
 
@@ -79,7 +83,7 @@ struct MatStep {
 // zeros instead of rebinding the header — computeDescriptors (src/ORBextractor.cc:1035) relies on this to write through
 // a rowRange view of the output matrix.
 struct MatZeros {
-    int rows, cols;
+    int rows, cols, type;
 };
 
 // 8-bit single-channel matrix header over a reference-counted buffer. The buffer and its counter come from malloc/free,
@@ -90,15 +94,15 @@ public:
     uchar* data;
     MatStep step;
 
-    Mat() : rows(0), cols(0), data(nullptr), buf(nullptr) {}
-    Mat(int r, int c, int type) : rows(0), cols(0), data(nullptr), buf(nullptr) { create(r, c, type); }
-    Mat(Size sz, int type) : rows(0), cols(0), data(nullptr), buf(nullptr) { create(sz.height, sz.width, type); }
-    Mat(int r, int c, int type, void* user, size_t stp) : rows(r), cols(c), data((uchar*)user), buf(nullptr)
+    Mat() : rows(0), cols(0), data(nullptr), buf(nullptr), type_(CV_8U) {}
+    Mat(int r, int c, int type) : rows(0), cols(0), data(nullptr), buf(nullptr), type_(CV_8U) { create(r, c, type); }
+    Mat(Size sz, int type) : rows(0), cols(0), data(nullptr), buf(nullptr), type_(CV_8U) { create(sz.height, sz.width, type); }
+    Mat(int r, int c, int type, void* user, size_t stp) : rows(r), cols(c), data((uchar*)user), buf(nullptr), type_(type)
     {
-        assert(type == CV_8UC1);
+        assert(type == CV_8U || type == CV_32F);
         step.v = stp;
     }
-    Mat(const Mat& o) : rows(o.rows), cols(o.cols), data(o.data), step(o.step), buf(o.buf)
+    Mat(const Mat& o) : rows(o.rows), cols(o.cols), data(o.data), step(o.step), buf(o.buf), type_(o.type_)
     {
         if (buf) ++*buf;
     }
@@ -106,23 +110,25 @@ public:
     {
         if (o.buf) ++*o.buf;
         drop();
-        rows = o.rows; cols = o.cols; data = o.data; step = o.step; buf = o.buf;
+        rows = o.rows; cols = o.cols; data = o.data; step = o.step; buf = o.buf; type_ = o.type_;
         return *this;
     }
     ~Mat() { drop(); }
 
     void create(int r, int c, int type)
     {
-        assert(type == CV_8UC1);
-        if (data && r == rows && c == cols) return;  // cv::Mat::create keeps a buffer of the right shape
+        assert(type == CV_8U || type == CV_32F);
+        if (data && r == rows && c == cols && type == type_) return;  // cv::Mat::create keeps a buffer of the right shape
         drop();
         rows = r;
         cols = c;
-        step.v = (size_t)c;
-        buf = (int*)std::malloc(16 + (size_t)r * c);
+        type_ = type;
+        step.v = (size_t)c * elemSize();
+        buf = (int*)std::malloc(16 + (size_t)r * step.v);
         *buf = 1;
         data = (uchar*)buf + 16;
     }
+    size_t elemSize() const { return type_ == CV_32F ? 4 : 1; }
     void create(Size sz, int type) { create(sz.height, sz.width, type); }
     void release()
     {
@@ -130,26 +136,25 @@ public:
         data = nullptr;
         rows = cols = 0;
     }
-    static MatZeros zeros(int r, int c, int type)
-    {
-        assert(type == CV_8UC1);
-        return MatZeros{r, c};
-    }
-    Mat(const MatZeros& z) : rows(0), cols(0), data(nullptr), buf(nullptr) { *this = z; }
+    static MatZeros zeros(int r, int c, int type) { return MatZeros{r, c, type}; }
+    Mat(const MatZeros& z) : rows(0), cols(0), data(nullptr), buf(nullptr), type_(CV_8U) { *this = z; }
     Mat& operator=(const MatZeros& z)
     {
-        create(z.rows, z.cols, CV_8UC1);  // keeps a buffer (or view) of the right shape
-        for (int y = 0; y < rows; ++y) std::memset(data + (size_t)y * step.v, 0, (size_t)cols);
+        create(z.rows, z.cols, z.type);  // keeps a buffer (or view) of the right shape
+        for (int y = 0; y < rows; ++y) std::memset(data + (size_t)y * step.v, 0, (size_t)cols * elemSize());
         return *this;
     }
 
-    int type() const { return CV_8UC1; }
-    size_t step1() const { return step.v; }  // step in elements; element size is 1
+    int type() const { return type_; }
+    size_t step1() const { return step.v / elemSize(); }  // step in elements
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
     Size size() const { return Size(cols, rows); }
 
     template <typename T> T& at(int r, int c) { return *(T*)(data + (size_t)r * step.v + (size_t)c * sizeof(T)); }
     template <typename T> const T& at(int r, int c) const { return *(const T*)(data + (size_t)r * step.v + (size_t)c * sizeof(T)); }
+    // single-index form: element i of a row or column vector
+    template <typename T> T& at(int i) { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
+    template <typename T> const T& at(int i) const { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
     uchar* ptr(int r = 0) { return data + (size_t)r * step.v; }
     const uchar* ptr(int r = 0) const { return data + (size_t)r * step.v; }
     template <typename T> T* ptr(int r = 0) { return (T*)(data + (size_t)r * step.v); }
@@ -163,18 +168,60 @@ public:
         Mat m(*this);  // shares the buffer
         m.rows = r.height;
         m.cols = r.width;
-        m.data = data + (size_t)r.y * step.v + r.x;
+        m.data = data + (size_t)r.y * step.v + (size_t)r.x * elemSize();
         return m;
     }
+    Mat row(int y) const { return rowRange(y, y + 1); }
+    Mat col(int x) const { return colRange(x, x + 1); }
     Mat clone() const
     {
-        Mat m(rows, cols, CV_8UC1);
-        for (int y = 0; y < rows; ++y) std::memcpy(m.data + (size_t)y * m.step.v, data + (size_t)y * step.v, (size_t)cols);
+        Mat m;
+        if (!data) return m;
+        m.create(rows, cols, type_);
+        for (int y = 0; y < rows; ++y) std::memcpy(m.data + (size_t)y * m.step.v, data + (size_t)y * step.v, (size_t)cols * elemSize());
         return m;
     }
+    void copyTo(Mat& dst) const
+    {
+        dst.create(rows, cols, type_);
+        for (int y = 0; y < rows; ++y) std::memcpy(dst.data + (size_t)y * dst.step.v, data + (size_t)y * step.v, (size_t)cols * elemSize());
+    }
+    // Mat::convertTo, CV_8U -> CV_32F (src/Frame.cc:623, :641; dst may be *this)
+    void convertTo(Mat& dst, int rtype) const
+    {
+        assert(type_ == CV_8U && rtype == CV_32F);
+        Mat out(rows, cols, CV_32F);
+        for (int y = 0; y < rows; ++y)
+            for (int x = 0; x < cols; ++x) out.at<float>(y, x) = (float)at<uchar>(y, x);
+        dst = out;
+    }
+    static Mat ones(int r, int c, int type)
+    {
+        assert(type == CV_32F);
+        Mat m(r, c, type);
+        for (int y = 0; y < r; ++y)
+            for (int x = 0; x < c; ++x) m.at<float>(y, x) = 1.f;
+        return m;
+    }
+    Mat t() const
+    {
+        Mat m(cols, rows, CV_32F);
+        for (int y = 0; y < rows; ++y)
+            for (int x = 0; x < cols; ++x) m.at<float>(x, y) = at<float>(y, x);
+        return m;
+    }
+    double dot(const Mat& o) const
+    {
+        double s = 0;
+        for (int y = 0; y < rows; ++y)
+            for (int x = 0; x < cols; ++x) s += (double)at<float>(y, x) * o.at<float>(y, x);
+        return s;
+    }
+    Mat reshape(int /*cn*/) const { return *this; }  // only around undistortPoints, which this build never reaches
 
 private:
     int* buf;  // counter at the head of the owned allocation; nullptr for user data
+    int type_;
     void drop()
     {
         if (buf && --*buf == 0) std::free(buf);
@@ -200,6 +247,82 @@ public:
 };
 typedef const _InputArray& InputArray;
 typedef const _OutputArray& OutputArray;
+
+// ---- CV_32F algebra used by src/Frame.cc ----
+inline Mat operator-(const Mat& a, const Mat& b)
+{
+    Mat m(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = a.at<float>(y, x) - b.at<float>(y, x);
+    return m;
+}
+inline Mat operator+(const Mat& a, const Mat& b)
+{
+    Mat m(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = a.at<float>(y, x) + b.at<float>(y, x);
+    return m;
+}
+inline Mat operator*(float s, const Mat& a)
+{
+    Mat m(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = s * a.at<float>(y, x);
+    return m;
+}
+inline Mat operator-(const Mat& a) { return -1.f * a; }
+inline Mat operator*(const Mat& a, const Mat& b)
+{
+    Mat m(a.rows, b.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < b.cols; ++x) {
+            double s = 0;
+            for (int k = 0; k < a.cols; ++k) s += (double)a.at<float>(y, k) * b.at<float>(k, x);
+            m.at<float>(y, x) = (float)s;
+        }
+    return m;
+}
+enum { NORM_L1 = 2, NORM_L2 = 4 };
+inline double norm(const Mat& a)
+{
+    double s = 0;
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) s += (double)a.at<float>(y, x) * a.at<float>(y, x);
+    return std::sqrt(s);
+}
+// cv::norm(a, b, NORM_L1) on CV_32F: sum of |a - b|, accumulated in double (src/Frame.cc:644)
+inline double norm(const Mat& a, const Mat& b, int normType)
+{
+    assert(normType == NORM_L1);
+    double s = 0;
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) s += std::fabs((double)a.at<float>(y, x) - (double)b.at<float>(y, x));
+    return s;
+}
+void undistortPoints(const Mat& src, Mat& dst, const Mat& K, const Mat& D, const Mat& R, const Mat& P);  // aborts: never reached
+
+// cv::Mat_<float>(r, c) << a, b, c (src/Frame.cc:734)
+template <typename T>
+class Mat_ : public Mat {
+public:
+    Mat_(int r, int c) : Mat(r, c, CV_32F) {}
+    struct Init {
+        Mat_* m;
+        int i;
+        Init& operator,(T v)
+        {
+            m->template at<T>(i / m->cols, i % m->cols) = v;
+            ++i;
+            return *this;
+        }
+        operator Mat() const { return *m; }
+    };
+    Init operator<<(T v)
+    {
+        this->template at<T>(0, 0) = v;
+        return Init{this, 1};
+    }
+};
 
 enum { BORDER_REFLECT_101 = 4, BORDER_ISOLATED = 16 };
 enum { INTER_LINEAR = 1 };

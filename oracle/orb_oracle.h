@@ -15,14 +15,13 @@
  *   cv::resize INTER_LINEAR 8UC1, cv::GaussianBlur 7x7 sigma 2 8UC1, cv::FAST TYPE_9_16 + NMS,
  *   cv::fastAtan2, cvRound, BORDER_REFLECT_101.
  *
- * PARITY PIN: the reference has no tests or golden vectors for this path. The extractor half is
- * pinned against the reference's OWN object code: oracle/_ref (src/ORBextractor.cc compiled where
- * it lies against the OpenCV stand-in of oracle/cvshim/, see ref_wrap.cpp; tests/test_reference_pin.py:
- * keypoints, angles and descriptors identical). The OpenCV primitives underneath are pinned against
+ * PARITY PIN: the reference has no tests or golden vectors for this path. The restatement is
+ * pinned against the reference's OWN object code: oracle/_ref (src/ORBextractor.cc and src/Frame.cc
+ * compiled where they lie against the OpenCV stand-in of oracle/cvshim/, see ref_wrap.cpp;
+ * tests/test_reference_pin.py: keypoints, angles, descriptors, mvuRight and mvDepth identical). The OpenCV primitives underneath are pinned against
  * the real OpenCV kernels through cv2 4.13.0 (tests/test_oracle_kat.py: resize, blur, FAST,
  * fastAtan2 bit-exact) and the whole path against golden vectors produced by a cv2-driven pipeline
- * (tests/golden/make_golden.py). ComputeStereoMatches (src/Frame.cc) cannot be compiled here and is
- * pinned against that pipeline only.
+ * (tests/golden/make_golden.py).
  * Two choices are pinned by decision because the reference itself is not deterministic there
  * (DESIGN.md §oracle): the quadtree tie-break (creation order instead of heap address) and
  * cos/sin (orbx_sincosf instead of libm).

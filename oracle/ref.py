@@ -46,6 +46,11 @@ def lib():
         L.ref_extract.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int]
         L.ref_level_size.argtypes = [vp, C.c_int, i32p, i32p]
         L.ref_level_copy.argtypes = [vp, C.c_int, vp, C.c_int]
+        L.ref_stereo_match.argtypes = [vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_float, C.c_float, vp, vp]
+        L.ref_stereo_from_rgbd.argtypes = [vp, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_float, vp, vp]
+        L.ref_assign_features_to_grid.argtypes = [vp, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, vp, vp]
+        L.ref_features_in_area.argtypes = [vp, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float,
+                                           C.c_float, C.c_int, C.c_int, vp]
         _lib = L
     return _lib
 
@@ -84,3 +89,46 @@ class RefExtractor:
         out = np.zeros((r.value, c.value), np.uint8)
         lib().ref_level_copy(self._h, l, _ptr(out), out.strides[0])
         return out
+
+
+def stereo_match(ex_l, ex_r, kps_l, desc_l, kps_r, desc_r, mbf, mb):
+    """Frame::ComputeStereoMatches (src/Frame.cc:522-700) as the reference's own object code, on the reference's Frame with
+    the members the stereo constructor sets (src/Frame.cc:98-125). ex_l / ex_r: RefExtractors that extracted this frame's
+    images last (their pyramids are read). Returns (mvuRight, mvDepth)."""
+    kps_l, kps_r = np.ascontiguousarray(kps_l, KP_DTYPE), np.ascontiguousarray(kps_r, KP_DTYPE)
+    desc_l, desc_r = np.ascontiguousarray(desc_l, np.uint8), np.ascontiguousarray(desc_r, np.uint8)
+    n = len(kps_l)
+    ur, dp = np.zeros(n, np.float32), np.zeros(n, np.float32)
+    rc = lib().ref_stereo_match(ex_l._h, ex_r._h, _ptr(kps_l), _ptr(desc_l), n, _ptr(kps_r), _ptr(desc_r), len(kps_r),
+                                mbf, mb, _ptr(ur), _ptr(dp))
+    if rc != 0:
+        raise RuntimeError("ref_stereo_match failed")
+    return ur, dp
+
+
+def stereo_from_rgbd(keys, keys_un, depth_map, mbf):
+    """Frame::ComputeStereoFromRGBD (src/Frame.cc:702-723) on the reference's Frame. Returns (mvuRight, mvDepth)."""
+    keys, keys_un = np.ascontiguousarray(keys, KP_DTYPE), np.ascontiguousarray(keys_un, KP_DTYPE)
+    d = np.ascontiguousarray(depth_map, np.float32)
+    n = len(keys)
+    ur, dp = np.zeros(n, np.float32), np.zeros(n, np.float32)
+    lib().ref_stereo_from_rgbd(_ptr(keys), _ptr(keys_un), n, _ptr(d), d.shape[0], d.shape[1], d.strides[0], mbf, _ptr(ur), _ptr(dp))
+    return ur, dp
+
+
+def assign_features_to_grid(keys_un, bounds):
+    """Frame::AssignFeaturesToGrid (src/Frame.cc:279-294) -> (cell_start[64*48+1], items); cell (ix, iy) at ix*48+iy."""
+    keys_un = np.ascontiguousarray(keys_un, KP_DTYPE)
+    start = np.zeros(64 * 48 + 1, np.int32)
+    items = np.zeros(max(len(keys_un), 1), np.int32)
+    k = lib().ref_assign_features_to_grid(_ptr(keys_un), len(keys_un), *[float(b) for b in bounds], _ptr(start), _ptr(items))
+    return start, items[:k]
+
+
+def features_in_area(keys_un, bounds, x, y, r, min_level=-1, max_level=-1):
+    """Frame::GetFeaturesInArea (src/Frame.cc:376-433) on a frame whose grid the reference builds from keys_un."""
+    keys_un = np.ascontiguousarray(keys_un, KP_DTYPE)
+    out = np.zeros(max(len(keys_un), 1), np.int32)
+    k = lib().ref_features_in_area(_ptr(keys_un), len(keys_un), *[float(b) for b in bounds], x, y, r, min_level, max_level,
+                                   _ptr(out))
+    return out[:k]

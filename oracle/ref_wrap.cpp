@@ -25,6 +25,9 @@
 
 #include <opencv2/core/core.hpp>
 
+#define private public  // Frame::AssignFeaturesToGrid is private; access control changes neither layout nor symbol names
+#include "Frame.h"      // with cvshim/ref_stubs.h force-included (see the Makefile): MapPoint, KeyFrame, ... read as stubs
+#undef private
 #include "ORBextractor.h"
 #include "orb_oracle.h"
 
@@ -139,7 +142,38 @@ float fastAtan2(float y, float x) { return orc_fast_atan2(y, x); }
 
 void KeyPointsFilter::retainBest(std::vector<KeyPoint>&, int) { std::abort(); }  // only ComputeKeyPointsOld (never called)
 
+void undistortPoints(const Mat&, Mat&, const Mat&, const Mat&, const Mat&, const Mat&) { std::abort(); }  // zero distortion only
+
 }  // namespace cv
+
+// ---------------------------------------------------------------- what src/Frame.cc needs from files that cannot be built
+namespace ORB_SLAM2 {
+
+// src/ORBmatcher.cc:37-38
+const int ORBmatcher::TH_HIGH = 100;
+const int ORBmatcher::TH_LOW = 50;
+
+// ORBmatcher::DescriptorDistance, src/ORBmatcher.cc:1672-1688: population count of the XOR of two 256-bit descriptors
+// (the reference uses a parallel bit count over 8 int32 words; the count is the same number)
+int ORBmatcher::DescriptorDistance(const cv::Mat& a, const cv::Mat& b)
+{
+    const uint32_t* pa = a.ptr<uint32_t>();
+    const uint32_t* pb = b.ptr<uint32_t>();
+    int dist = 0;
+    for (int i = 0; i < 8; ++i) dist += __builtin_popcount(pa[i] ^ pb[i]);
+    return dist;
+}
+
+// never reached by the functions the tests call; they only have to link
+cv::Mat MapPoint::GetWorldPos() { std::abort(); }
+cv::Mat MapPoint::GetNormal() { std::abort(); }
+float MapPoint::GetMaxDistanceInvariance() { std::abort(); }
+float MapPoint::GetMinDistanceInvariance() { std::abort(); }
+int MapPoint::PredictScale(const float&, Frame*) { std::abort(); }
+void ORBVocabulary::transform(const std::vector<cv::Mat>&, DBoW2::BowVector&, DBoW2::FeatureVector&, int) const { std::abort(); }
+std::vector<cv::Mat> Converter::toDescriptorVector(const cv::Mat&) { std::abort(); }
+
+}  // namespace ORB_SLAM2
 
 // ---------------------------------------------------------------- C entry points (ctypes)
 namespace {
@@ -216,6 +250,101 @@ int ref_level_copy(void* h, int level, uint8_t* dst, int dstStride)
     const cv::Mat& m = e->mvImagePyramid[level];
     for (int y = 0; y < m.rows; ++y) std::memcpy(dst + (size_t)y * dstStride, m.ptr(y), (size_t)m.cols);
     return 0;
+}
+
+// Frame::ComputeStereoMatches (src/Frame.cc:522-700) on the reference's own Frame object. The members the function reads
+// are set the way the stereo constructor sets them (src/Frame.cc:98-125): the two extractors (hL, hR must have extracted
+// the frame's images last: the function reads their pyramids), keypoints, descriptors, scale tables, N, mbf — and mb,
+// which the constructor leaves uninitialised at that point (:552 reads it, :149 assigns it), is an explicit argument.
+// Outputs: mvuRight / mvDepth (nL floats each).
+int ref_stereo_match(void* hL, void* hR, const orc_keypoint* kpsL, const uint8_t* descL, int nL, const orc_keypoint* kpsR,
+                     const uint8_t* descR, int nR, float mbf, float mb, float* uRight, float* depth)
+{
+    ORB_SLAM2::ORBextractor* eL = (ORB_SLAM2::ORBextractor*)hL;
+    ORB_SLAM2::ORBextractor* eR = (ORB_SLAM2::ORBextractor*)hR;
+    ORB_SLAM2::Frame F;
+    F.mpORBextractorLeft = eL;
+    F.mpORBextractorRight = eR;
+    F.mvScaleFactors = eL->GetScaleFactors();
+    F.mvInvScaleFactors = eL->GetInverseScaleFactors();
+    F.mvKeys.resize(nL);
+    F.mvKeysRight.resize(nR);
+    if (nL) std::memcpy(F.mvKeys.data(), kpsL, (size_t)nL * sizeof(orc_keypoint));
+    if (nR) std::memcpy(F.mvKeysRight.data(), kpsR, (size_t)nR * sizeof(orc_keypoint));
+    F.mDescriptors = cv::Mat(nL, 32, CV_8U, (void*)descL, 32).clone();
+    F.mDescriptorsRight = cv::Mat(nR, 32, CV_8U, (void*)descR, 32).clone();
+    F.N = nL;
+    F.mbf = mbf;
+    F.mb = mb;
+    F.ComputeStereoMatches();
+    if ((int)F.mvuRight.size() != nL || (int)F.mvDepth.size() != nL) return -1;
+    for (int i = 0; i < nL; ++i) {
+        uRight[i] = F.mvuRight[i];
+        depth[i] = F.mvDepth[i];
+    }
+    return 0;
+}
+
+// Frame::ComputeStereoFromRGBD (src/Frame.cc:702-723): mvKeys index the depth map, mvKeysUn give the x of uRight.
+int ref_stereo_from_rgbd(const orc_keypoint* kps, const orc_keypoint* kpsUn, int n, const float* depthMap, int rows, int cols,
+                         int strideBytes, float mbf, float* uRight, float* depth)
+{
+    ORB_SLAM2::Frame F;
+    F.N = n;
+    F.mbf = mbf;
+    F.mvKeys.resize(n);
+    F.mvKeysUn.resize(n);
+    if (n) std::memcpy(F.mvKeys.data(), kps, (size_t)n * sizeof(orc_keypoint));
+    if (n) std::memcpy(F.mvKeysUn.data(), kpsUn, (size_t)n * sizeof(orc_keypoint));
+    cv::Mat im(rows, cols, CV_32F, (void*)depthMap, (size_t)strideBytes);
+    F.ComputeStereoFromRGBD(im);
+    for (int i = 0; i < n; ++i) {
+        uRight[i] = F.mvuRight[i];
+        depth[i] = F.mvDepth[i];
+    }
+    return 0;
+}
+
+// Frame::AssignFeaturesToGrid (src/Frame.cc:279-294) + PosInGrid (:435-445) on the reference's Frame; the image bounds
+// and cell sizes are the statics the constructors set (:129-137). Result as CSR over cells ix * 48 + iy.
+static void ref_frame_grid_setup(ORB_SLAM2::Frame& F, const orc_keypoint* keysUn, int n, float minX, float maxX, float minY, float maxY)
+{
+    ORB_SLAM2::Frame::mnMinX = minX;
+    ORB_SLAM2::Frame::mnMaxX = maxX;
+    ORB_SLAM2::Frame::mnMinY = minY;
+    ORB_SLAM2::Frame::mnMaxY = maxY;
+    ORB_SLAM2::Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / (maxX - minX);
+    ORB_SLAM2::Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / (maxY - minY);
+    F.N = n;
+    F.mvKeysUn.resize(n);
+    if (n) std::memcpy(F.mvKeysUn.data(), keysUn, (size_t)n * sizeof(orc_keypoint));
+    F.AssignFeaturesToGrid();
+}
+
+int ref_assign_features_to_grid(const orc_keypoint* keysUn, int n, float minX, float maxX, float minY, float maxY,
+                                int* cellStart, int* items)
+{
+    ORB_SLAM2::Frame F;
+    ref_frame_grid_setup(F, keysUn, n, minX, maxX, minY, maxY);
+    int k = 0;
+    for (int ix = 0; ix < FRAME_GRID_COLS; ++ix)
+        for (int iy = 0; iy < FRAME_GRID_ROWS; ++iy) {
+            cellStart[ix * FRAME_GRID_ROWS + iy] = k;
+            for (size_t j = 0; j < F.mGrid[ix][iy].size(); ++j) items[k++] = (int)F.mGrid[ix][iy][j];
+        }
+    cellStart[FRAME_GRID_COLS * FRAME_GRID_ROWS] = k;
+    return k;
+}
+
+// Frame::GetFeaturesInArea (src/Frame.cc:376-433). Returns the number of indices (written to out, capacity n).
+int ref_features_in_area(const orc_keypoint* keysUn, int n, float minX, float maxX, float minY, float maxY, float x, float y,
+                         float r, int minLevel, int maxLevel, int* out)
+{
+    ORB_SLAM2::Frame F;
+    ref_frame_grid_setup(F, keysUn, n, minX, maxX, minY, maxY);
+    const std::vector<size_t> v = F.GetFeaturesInArea(x, y, r, minLevel, maxLevel);
+    for (size_t i = 0; i < v.size(); ++i) out[i] = (int)v[i];
+    return (int)v.size();
 }
 
 }  // extern "C"

@@ -135,3 +135,121 @@ def test_cuda_batch_equals_reference():
         for side, img in (("left", lefts[k]), ("right", rights[k])):
             m = int(out["n_" + side][k])
             assert_same((out["kps_" + side][k, :m], out["desc_" + side][k, :m]), r(img), f"batch/{k}/{side}")
+
+
+# ---------------------------------------------------------------- Frame.cc: ComputeStereoMatches and the Frame helpers
+
+def ref_pair(cfg, left, right):
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    rl, rr = R.RefExtractor(nf, sf, nl, ini, mn), R.RefExtractor(nf, sf, nl, ini, mn)
+    kl, dl = rl(left)
+    kr, dr = rr(right)
+    return rl, rr, kl, dl, kr, dr
+
+
+@needs_ref
+@pytest.mark.parametrize("name", ["arducam", "kitti", "euroc"])
+def test_stereo_oracle_equals_reference(name):
+    """Frame::ComputeStereoMatches as reference object code (src/Frame.cc:522-700 on the reference's own Frame, extractors
+    and pyramids) against the oracle: mvuRight and mvDepth bit-identical, for mb = bf/fx and mb = 0 (first frame)."""
+    cfg = synth.CONFIGS[name]
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    for seed in (7, 8, 9):
+        left, right = synth.stereo_pair(W, H, seed)
+        rl, rr, kl, dl, kr, dr = ref_pair(cfg, left, right)
+        ol, orr = O.OracleExtractor(nf, sf, nl, ini, mn), O.OracleExtractor(nf, sf, nl, ini, mn)
+        assert_same(ol(left), (kl, dl), "L")
+        assert_same(orr(right), (kr, dr), "R")
+        for mb in (bf / fx, 0.0):
+            our, odp = O.stereo_match(ol, orr, kl, dl, kr, dr, bf, mb)
+            rur, rdp = R.stereo_match(rl, rr, kl, dl, kr, dr, bf, mb)
+            assert np.array_equal(our, rur) and np.array_equal(odp, rdp), (name, seed, mb)
+            assert (rur >= 0).sum() > 100
+    # right image unrelated to the left one: few or no matches survive, same answer
+    left, _ = synth.stereo_pair(W, H, 31)
+    _, right = synth.stereo_pair(W, H, 32)
+    rl, rr, kl, dl, kr, dr = ref_pair(cfg, left, right)
+    ol, orr = O.OracleExtractor(nf, sf, nl, ini, mn), O.OracleExtractor(nf, sf, nl, ini, mn)
+    ol(left), orr(right)
+    our, odp = O.stereo_match(ol, orr, kl, dl, kr, dr, bf, bf / fx)
+    rur, rdp = R.stereo_match(rl, rr, kl, dl, kr, dr, bf, bf / fx)
+    assert np.array_equal(our, rur) and np.array_equal(odp, rdp)
+
+
+@needs_ref
+def test_frame_helpers_oracle_equal_reference():
+    """AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea / ComputeStereoFromRGBD of the reference's Frame (src/Frame.cc
+    :279-294, :435-445, :376-433, :702-723) against the oracle's restatements (oracle/frame.cpp)."""
+    rng = np.random.default_rng(12)
+    for case in range(6):
+        n = [0, 1, 50, 400, 1500, 3000][case]
+        W, H = [(640, 400), (1241, 376)][case % 2]
+        keys = np.zeros(n, O.KP_DTYPE)
+        keys["x"], keys["y"] = rng.uniform(-8, W + 8, n), rng.uniform(-8, H + 8, n)  # some fall outside the grid
+        if n > 10:  # exact cell-boundary and half-way coordinates
+            keys["x"][:5] = [0, W, W / 64 * 0.5, W / 64 * 1.5, W - 1e-3]
+            keys["y"][:5] = [0, H, H / 48 * 0.5, H / 48 * 2.5, H - 1e-3]
+        keys["octave"] = rng.integers(0, 8, n)
+        bounds = (0.0, float(W), 0.0, float(H))
+        fr = O.FrameView(keys, None, None, np.eye(4), 500, 500, W / 2, H / 2, 40, 0.08, bounds, 1.2 ** np.arange(8))
+        so, io = O.assign_features_to_grid(fr)
+        sr, ir = R.assign_features_to_grid(keys, bounds)
+        assert np.array_equal(so, sr) and np.array_equal(io, ir), case
+        for q in range(40):
+            x, y, r = rng.uniform(-30, W + 30), rng.uniform(-30, H + 30), rng.choice([0.5, 7, 25, 60, 400])
+            lv = [(-1, -1), (0, 3), (2, -1), (3, 3), (1, 0)][q % 5]
+            assert np.array_equal(O.features_in_area(fr, x, y, r, *lv), R.features_in_area(keys, bounds, x, y, r, *lv)), (case, q)
+    # RGB-D: keypoints inside the depth map only (the reference reads imDepth.at<float>(v, u) unchecked)
+    Hd, Wd, n = 48, 64, 500
+    depth = rng.uniform(-0.5, 6, (Hd, Wd)).astype(np.float32)
+    depth[rng.random((Hd, Wd)) < 0.1] = np.nan
+    keys = np.zeros(n, O.KP_DTYPE)
+    keys["x"], keys["y"] = rng.uniform(0, Wd - 0.01, n), rng.uniform(0, Hd - 0.01, n)
+    un = keys.copy()
+    un["x"] = (keys["x"] + rng.normal(0, 0.3, n)).astype(np.float32)
+    our, odp = O.stereo_from_rgbd(keys, depth, 40.0, un["x"])
+    rur, rdp = R.stereo_from_rgbd(keys, un, depth, 40.0)
+    assert np.array_equal(our, rur) and np.array_equal(odp, rdp)
+
+
+@needs_ref
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["arducam", "kitti", "euroc"])
+def test_cuda_stereo_equals_reference(name):
+    """extract L + extract R + ComputeStereoMatches through the C-ABI against the same three steps of the reference."""
+    import orb_slam2_2021_b200 as pkg
+
+    cfg = synth.CONFIGS[name]
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    exl, exr = pkg.ORBextractor(nf, sf, nl, ini, mn), pkg.ORBextractor(nf, sf, nl, ini, mn)
+    for seed in (41, 42, 43):
+        left, right = synth.stereo_pair(W, H, seed)
+        rl, rr, rkl, rdl, rkr, rdr = ref_pair(cfg, left, right)
+        kl, dl = exl(left)
+        kr, dr = exr(right)
+        assert_same((kl, dl), (rkl, rdl), "L")
+        assert_same((kr, dr), (rkr, rdr), "R")
+        for mb in (bf / fx, 0.0):
+            ur, dp = pkg.compute_stereo_matches(exl, exr, kl, dl, kr, dr, bf, mb)
+            rur, rdp = R.stereo_match(rl, rr, rkl, rdl, rkr, rdr, bf, mb)
+            assert np.array_equal(ur, rur) and np.array_equal(dp, rdp), (name, seed, mb)
+
+
+@needs_ref
+@pytest.mark.gpu
+def test_cuda_batch_stereo_equals_reference():
+    """The benchmarked batch call: every output of every frame against the reference's extractor + ComputeStereoMatches."""
+    import orb_slam2_2021_b200 as pkg
+
+    cfg = synth.CONFIGS["kitti"]
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    n = 5
+    lefts, rights = zip(*[synth.stereo_pair(W, H, 500 + 2 * k) for k in range(n)])
+    batch = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, n, stereo=True)
+    out = batch.process(np.stack(lefts), np.stack(rights), bf, bf / fx)
+    for k in range(n):
+        rl, rr, rkl, rdl, rkr, rdr = ref_pair(cfg, lefts[k], rights[k])
+        m = int(out["n_left"][k])
+        assert_same((out["kps_left"][k, :m], out["desc_left"][k, :m]), (rkl, rdl), f"{k}/L")
+        rur, rdp = R.stereo_match(rl, rr, rkl, rdl, rkr, rdr, bf, bf / fx)
+        assert np.array_equal(out["u_right"][k, :m], rur) and np.array_equal(out["depth"][k, :m], rdp), k
