@@ -31,6 +31,8 @@
 //     pixel PAIR (pair and quad minima shared by the two arcs that start at k and k+1);
 //   * strengths go to a u16 map; NMS is driven by the same task lists and uses packed column maxima;
 //     maxima are collected in a CTA list and emitted at their row-major rank (the reference order).
+#include <cstdlib>
+
 #include "orbx_dev.cuh"
 #include "orbx_tma.cuh"
 
@@ -40,8 +42,6 @@ struct __align__(8) OrbxCell {  // 8 bytes, loaded as one 64-bit word
     uint8_t level, pad;
 };
 
-#define FAST_THREADS 128
-#define FAST_WARPS (FAST_THREADS / 32)
 
 // Corner strengths of the two pixels whose centre pair is *(u32*)b (see the layout note above).
 // b points at the pair itself in A (even column c), a at B + 1 + the same offset, so that a[dx] for odd dx and
@@ -94,20 +94,19 @@ __device__ __forceinline__ void fast_strength2(const uint16_t* a, const uint16_t
 // c_recip[n] = ceil(65536 / n): floor(t / n) = (t * c_recip[n]) >> 16 exactly while t * n < 65536 (here t <= 128, n <= 31)
 __constant__ uint32_t c_recip[32] = {0, 65536, 32768, 21846, 16384, 13108, 10923, 9363, 8192, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4096, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115};
 
-template <int SA>
+template <int SA, int FAST_THREADS>
 __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap)
 {
     constexpr int BW = SA == 48 ? 64 : 96;      // TMA box width in bytes
     extern __shared__ __align__(128) uint8_t fast_smem[];
     __shared__ __align__(8) uint64_t bar;
-    __shared__ int listCnt, taskCnt;
-    __shared__ int warpNz[FAST_WARPS];
+    __shared__ int listCnt, taskCnt, nzCnt;
 
     uint8_t* T = fast_smem;                                                     // raw box [rhMax][BW]
     uint16_t* A = reinterpret_cast<uint16_t*>(fast_smem + ((rhMax * BW + 127) & ~127));  // A[y][j] = I(xa + j, y0 + y), xa = x0 & ~3
     uint16_t* B = A + rhMax * SA;                                                // B[y][j] = I(xa + j - 1, y0 + y)
     uint16_t* smap = B + rhMax * SA;  // strength map: interior pixel (ix,iy) at [iy+1][A-column + SD], zero elsewhere
-    uint16_t* lists = smap + (rhMax - 4) * SA;  // 2 x FAST_WARPS lists of listCap entries: pass-1 tasks, then non-zero pairs
+    uint16_t* lists = smap + (rhMax - 4) * SA;  // 2 CTA-wide lists of listCap entries: pass-1 tasks, then non-zero pairs
 
     const int cellId = blockIdx.x, img = blockIdx.y;
     const OrbxCell cell = cells[cellId];
@@ -123,6 +122,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     if (threadIdx.x == 0) {
         listCnt = 0;
         taskCnt = 0;
+        nzCnt = 0;
         orbx_mbar_init(&bar, 1);
         orbx_fence_mbar_init();
         orbx_mbar_expect_tx(&bar, rhMax * BW);
@@ -169,7 +169,8 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     // neighbour that is not a corner at t has m <= t < m_centre, so the NMS at threshold t only needs the strengths m > t:
     // everything below (pre-test, network, map, NMS) runs on the pixels that can be corners at the attempt's threshold.
     // The strength map of a failed first attempt needs no clearing: the minTh attempt rewrites a superset with equal values.
-    uint16_t* tasks = lists;                                  // CTA-wide list of surviving pixel pairs (4 * listCap entries)
+    uint16_t* tasks = lists;                                  // CTA-wide list of surviving pixel pairs
+    uint16_t* nz = lists + listCap;                           // CTA-wide list of pairs with a non-zero strength
     uint32_t* kept = reinterpret_cast<uint32_t*>(T);          // NMS maxima: key | m << 16 (the raw tile is dead by then)
     const unsigned lt = (1u << lane) - 1;
     // pre-test thread mapping: fixed interior word column j per thread, 128/nwi interior rows per step
@@ -242,8 +243,6 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         {
             const uint16_t* pevn = A;      // even dx: pair (A[c+dx], A[c+dx+1]), c even
             const uint16_t* podd = B + 1;  // odd dx:  pair (B[c+dx+1], B[c+dx+2]) = (I(c+dx), I(c+dx+1))
-            uint16_t* nz = lists + (FAST_WARPS + warp) * listCap;  // this warp's list of pairs with a non-zero strength
-            int nnz = 0;                                           // warp-uniform
 #pragma unroll 1
             for (int g0 = warp * 32; g0 < ntAll; g0 += FAST_THREADS) {
                 const int g = g0 + lane;
@@ -261,21 +260,22 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
                     if (hit) *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + c + SD) = (uint32_t)m0 | ((uint32_t)m1 << 16);  // map is pre-zeroed
                 }
                 const unsigned bh = __ballot_sync(0xffffffffu, hit);
-                if (hit) nz[nnz + __popc(bh & lt)] = (uint16_t)task;
-                nnz += __popc(bh);
+                if (bh) {  // uniform: one shared atomic per warp step
+                    int base = 0;
+                    if (lane == 0) base = atomicAdd(&nzCnt, __popc(bh));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (hit) nz[base + __popc(bh & lt)] = (uint16_t)task;
+                }
             }
-            if (lane == 0) warpNz[warp] = nnz;
         }
         __syncthreads();
 
-        // ---- NMS over the pairs that hold a non-zero strength (warp lists): strict maximum over the 8 neighbours in the
+        // ---- NMS over the pairs that hold a non-zero strength: strict maximum over the 8 neighbours in the
         // strength map. Maxima go to a CTA list kept[] = key | m << 16, key = y*64 + x (interior coords).
-        const int nz0 = warpNz[0], nz1 = nz0 + warpNz[1], nz2 = nz1 + warpNz[2], nzAll = nz2 + warpNz[3];
-        const uint16_t* nzLists = lists + FAST_WARPS * listCap;
-        const int za1 = listCap - nz0, za2 = 2 * listCap - nz1, za3 = 3 * listCap - nz2;
+        const int nzAll = nzCnt;
 #pragma unroll 1
         for (int g = threadIdx.x; g < nzAll; g += FAST_THREADS) {
-            const int task = nzLists[g + (g >= nz2 ? za3 : g >= nz1 ? za2 : g >= nz0 ? za1 : 0)], y = task >> 8, cc = 2 * (task & 255);
+            const int task = nz[g], y = task >> 8, cc = 2 * (task & 255);
             const uint16_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair, word aligned
             const uint32_t mm = *reinterpret_cast<const uint32_t*>(c);
             const uint32_t u0 = *reinterpret_cast<const uint32_t*>(c - SA - 2), u1 = *reinterpret_cast<const uint32_t*>(c - SA), u2 = *reinterpret_cast<const uint32_t*>(c - SA + 2);
@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         __syncthreads();  // publishes kept[] and listCnt
         if (listCnt > 0 || attempt == 1 || tmin >= thr) break;
         thr = tmin;       // :814 FAST(iniTh) came back empty: once more with minTh
-        if (threadIdx.x == 0) taskCnt = 0;  // (last read before the barrier that ended pass 2)
+        if (threadIdx.x == 0) taskCnt = nzCnt = 0;  // (last reads before the barriers that ended pass 2 / the NMS)
         __syncthreads();
     }
 
@@ -333,18 +333,27 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     orbx_fast_geometry(p, &boxW, &rhMax);
     dim3 grid(p.cellsTotal, p.imgs);
     const int sa = boxW == 64 ? 48 : 80;
-    // per-warp task list: at most 2 pairs per thread and step of pass 1, which covers FAST_THREADS / nw whole rows per step
-    const int nwMax = (3 + (sa == 48 ? 40 : 66) + 4) >> 2;
-    const int rowsPerStep = FAST_THREADS / nwMax;
-    const int listCap = 64 * ((rhMax + rowsPerStep - 1) / rowsPerStep);
+    // list capacity: every pixel pair that can hold an interior pixel (interior = ROI - 6; one more pair for the alignment)
+    const int iwMax = (sa == 48 ? 40 : 72) - 6, ihMax = rhMax - 6;
+    const int listCap = (((iwMax + 4) / 2) * ihMax + 7) & ~7;
     const size_t smem = (size_t)((rhMax * boxW + 127) & ~127) + (size_t)2 * rhMax * sa * 2 + (size_t)(rhMax - 4) * sa * 2 +
-                        (size_t)2 * FAST_WARPS * listCap * 2;
-    if (smem > 32 * 1024) {  // tall cells on small levels: static + dynamic may pass 48 KB; per-device attribute, set on every such launch
-        if (sa == 48) cudaFuncSetAttribute(orbx_fast_kernel<48>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        else cudaFuncSetAttribute(orbx_fast_kernel<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                        (size_t)2 * listCap * 2;
+    static int nt = 0;  // threads per cell
+    if (!nt) {
+        const char* e = getenv("ORBX_FAST_THREADS");
+        nt = e ? atoi(e) : 128;
+        if (nt != 32 && nt != 64 && nt != 128) nt = 128;
     }
-    if (sa == 48)
-        orbx_fast_kernel<48><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax, listCap);
-    else
-        orbx_fast_kernel<80><<<grid, FAST_THREADS, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax, listCap);
+#define FAST_LAUNCH(SA_, NT_)                                                                                                    \
+    {                                                                                                                            \
+        if (smem > 32 * 1024) /* tall cells: static + dynamic may pass 48 KB; per-device attribute, set on every such launch */ \
+            cudaFuncSetAttribute(orbx_fast_kernel<SA_, NT_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);            \
+        orbx_fast_kernel<SA_, NT_><<<grid, NT_, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax, listCap); \
+    }
+    if (sa == 48) {
+        if (nt == 128) FAST_LAUNCH(48, 128) else if (nt == 64) FAST_LAUNCH(48, 64) else FAST_LAUNCH(48, 32)
+    } else {
+        if (nt == 128) FAST_LAUNCH(80, 128) else if (nt == 64) FAST_LAUNCH(80, 64) else FAST_LAUNCH(80, 32)
+    }
+#undef FAST_LAUNCH
 }
