@@ -13,24 +13,23 @@
 // cell whose FAST(iniTh) comes back empty (:814) repeats at minTh. Keypoints are written row-major into
 // the cell's slot array, so cells concatenated in table order give the reference's candidate order.
 //
-// Blackwell mapping (measured with tools/ubench/pipes.cu: VIMNMX3.U16x2 issues at the same rate as a
-// 32-bit IMNMX, so packing two pixels per register halves the ALU-pipe work that bounds this kernel):
-//   * the ROI arrives by ONE TMA box load (cp.async.bulk.tensor.3d, 64 or 96 columns starting at x0 & ~15 —
-//     the copy engine addresses the innermost dimension in 16-byte units — by rhMax rows) signalled on an
-//     mbarrier;
-//   * a widening pass walks the raw tile one aligned 32-bit word per thread into two 16-bit layouts,
-//     A[y][j] = I(xa+j, y) and B[y][j] = I(xa+j-1, y) (xa = x0 & ~3); pass 1 runs a byte-wise NECESSARY test for a
-//     corner at the attempt's threshold on the interior words, 4 pixels at once (VABSDIFF4 + SWAR compare against
-//     the compass points); a thread keeps its surviving pixel PAIRS as bits and appends them to the CTA's task
-//     list once (one warp scan and one shared atomic per warp);
-//   * pass 2 runs the exact test on the listed pairs only. A thread owns two horizontally adjacent pixels
-//     (even tile column first); for every ring offset the pair (ring(x), ring(x+1)) is ONE aligned 32-bit
-//     LDS (from A for even dx, from B+1 for odd dx) that is already a u16x2 vector — no byte extraction;
-//     min and max commute with subtracting the centre, so the whole min/max network runs on the raw unsigned
-//     u16x2 ring values with the 3-input DPX instructions (__vimin3_u16x2 / __vimax3_u16x2): 36 ops per polarity and
-//     pixel PAIR (pair and quad minima shared by the two arcs that start at k and k+1);
-//   * strengths go to a u16 map; NMS is driven by the same task lists and uses packed column maxima;
-//     maxima are collected in a CTA list and emitted at their row-major rank (the reference order).
+// Blackwell mapping (measured with tools/ubench/pipes.cu: VIMNMX3.U16x2 issues at the same rate as a 32-bit IMNMX, so
+// packing two pixels per register halves the min/max work; the kernel is bound by instruction issue, not by a pipe):
+//   * the ROI arrives by ONE TMA box load (cp.async.bulk.tensor.3d, 64 or 96 columns starting at x0 & ~15 — the copy
+//     engine addresses the innermost dimension in 16-byte units — by rhMax rows) signalled on an mbarrier;
+//   * pass 1 runs a byte-wise NECESSARY test for a corner at the attempt's threshold on the interior words of the raw
+//     tile, 4 pixels at once (VABSDIFF4 + SWAR compare against the compass points); a thread keeps its surviving pixel
+//     PAIRS as bits and appends them to the CTA's task list once (one warp scan and one shared atomic per warp);
+//   * pass 2 runs the exact test on the listed pairs only. A thread owns two horizontally adjacent pixels (even tile
+//     column first) and reads the 17 pairs (ring(x), ring(x+1)) straight from the raw tile (an aligned 16-bit load or two
+//     byte loads, one PRMT each: a widened u16 copy of the ROI cost more than it saved). Min and max commute with
+//     subtracting the centre, so the whole min/max network runs on the raw unsigned u16x2 ring values with the 3-input
+//     DPX instructions (__vimin3_u16x2 / __vimax3_u16x2): 36 ops per polarity and pixel PAIR (pair and quad minima shared
+//     by the two arcs that start at k and k+1);
+//   * strengths above the threshold go to a u16 map; NMS is driven by the list of non-zero pairs and uses packed column
+//     maxima; maxima are collected in a CTA list and emitted at their row-major rank (the reference order);
+//   * 64 threads per cell: the per-cell fixed work (prologue, mappings, scans) is paid per warp, and with 8 KB of shared
+//     memory per cell enough cells are resident per SM to keep the issue slots busy.
 #include <cstdlib>
 
 #include "orbx_dev.cuh"
@@ -43,23 +42,10 @@ struct __align__(8) OrbxCell {  // 8 bytes, loaded as one 64-bit word
 };
 
 
-// Corner strengths of the two pixels whose centre pair is *(u32*)b (see the layout note above).
-// b points at the pair itself in A (even column c), a at B + 1 + the same offset, so that a[dx] for odd dx and
-// b[dx] for even dx are word aligned; SA = row stride in u16 elements.
-template <int SA>
-__device__ __forceinline__ void fast_strength2(const uint16_t* a, const uint16_t* b, int& m0, int& m1)
+// Corner strengths of two horizontally adjacent pixels from the 17 u16x2 vectors cc (centre pair) and d[0..15] (ring pairs).
+__device__ __forceinline__ void fast_network2(uint32_t cc, const uint32_t (&d)[16], int& m0, int& m1)
 {
-#define RING_A(dx, dy) (*reinterpret_cast<const uint32_t*>(a + (dy) * SA + (dx)))
-#define RING_B(dx, dy) (*reinterpret_cast<const uint32_t*>(b + (dy) * SA + (dx)))
     // the network runs on the raw ring values (min and max commute with subtracting the centre): no per-value arithmetic
-    const uint32_t cc = RING_B(0, 0);
-    uint32_t d[16];
-    d[0] = RING_B(0, 3);    d[1] = RING_A(1, 3);    d[2] = RING_B(2, 2);    d[3] = RING_A(3, 1);
-    d[4] = RING_A(3, 0);    d[5] = RING_A(3, -1);   d[6] = RING_B(2, -2);   d[7] = RING_A(1, -3);
-    d[8] = RING_B(0, -3);   d[9] = RING_A(-1, -3);  d[10] = RING_B(-2, -2); d[11] = RING_A(-3, -1);
-    d[12] = RING_A(-3, 0);  d[13] = RING_A(-3, 1);  d[14] = RING_B(-2, 2);  d[15] = RING_A(-1, 3);
-#undef RING_A
-#undef RING_B
     // Arcs k and k+1 (k even) share the 8 values d[k+1..k+8]: max(min arc k, min arc k+1) = min(min8, max(d[k], d[k+9])).
     // Pair minima P (odd starts), quad minima Q = 4 contiguous values, then one 3-input op per even k: 36 operations per
     // polarity instead of 40 with 3/9-windows. The dark side is the dual (min <-> max).
@@ -91,6 +77,25 @@ __device__ __forceinline__ void fast_strength2(const uint16_t* a, const uint16_t
     m1 = max((int)(br >> 16) - c1, c1 - (int)(dk >> 16));
 }
 
+// The 17 vectors come straight from the raw tile (no widened copy of the ROI: building one cost more instructions and 7 KB
+// of shared memory per cell than it saved here). t points at pixel 0 of the pair, an EVEN byte address: pairs at even dx are
+// one aligned 16-bit load + PRMT, pairs at odd dx two byte loads + PRMT. BW = row stride of the tile.
+template <int BW>
+__device__ __forceinline__ void fast_strength2_raw(const uint8_t* t, int& m0, int& m1)
+{
+#define RING_E(dx, dy) __byte_perm((uint32_t)*reinterpret_cast<const uint16_t*>(t + (dy) * BW + (dx)), 0, 0x4140)
+#define RING_O(dx, dy) __byte_perm((uint32_t)t[(dy) * BW + (dx)], (uint32_t)t[(dy) * BW + (dx) + 1], 0x5410)
+    const uint32_t cc = RING_E(0, 0);
+    uint32_t d[16];
+    d[0] = RING_E(0, 3);    d[1] = RING_O(1, 3);    d[2] = RING_E(2, 2);    d[3] = RING_O(3, 1);
+    d[4] = RING_O(3, 0);    d[5] = RING_O(3, -1);   d[6] = RING_E(2, -2);   d[7] = RING_O(1, -3);
+    d[8] = RING_E(0, -3);   d[9] = RING_O(-1, -3);  d[10] = RING_E(-2, -2); d[11] = RING_O(-3, -1);
+    d[12] = RING_O(-3, 0);  d[13] = RING_O(-3, 1);  d[14] = RING_E(-2, 2);  d[15] = RING_O(-1, 3);
+#undef RING_E
+#undef RING_O
+    fast_network2(cc, d, m0, m1);
+}
+
 // c_recip[n] = ceil(65536 / n): floor(t / n) = (t * c_recip[n]) >> 16 exactly while t * n < 65536 (here t <= 128, n <= 31)
 __constant__ uint32_t c_recip[32] = {0, 65536, 32768, 21846, 16384, 13108, 10923, 9363, 8192, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4096, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115};
 
@@ -103,9 +108,9 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     __shared__ int listCnt, taskCnt, nzCnt;
 
     uint8_t* T = fast_smem;                                                     // raw box [rhMax][BW]
-    uint16_t* A = reinterpret_cast<uint16_t*>(fast_smem + ((rhMax * BW + 127) & ~127));  // A[y][j] = I(xa + j, y0 + y), xa = x0 & ~3
-    uint16_t* B = A + rhMax * SA;                                                // B[y][j] = I(xa + j - 1, y0 + y)
-    uint16_t* smap = B + rhMax * SA;  // strength map: interior pixel (ix,iy) at [iy+1][A-column + SD], zero elsewhere
+    // strength map, row stride SA: interior pixel (ix,iy) at [iy+1][A-column + SD], zero elsewhere. "A-column" = level column
+    // minus xa, xa = x0 & ~3: pixel pairs are aligned to even A-columns (= even tile bytes)
+    uint16_t* smap = reinterpret_cast<uint16_t*>(fast_smem + ((rhMax * BW + 127) & ~127));
     uint16_t* lists = smap + (rhMax - 4) * SA;  // 2 CTA-wide lists of listCap entries: pass-1 tasks, then non-zero pairs
 
     const int cellId = blockIdx.x, img = blockIdx.y;
@@ -129,42 +134,18 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         orbx_tma_load_3d(T, maps + cell.level, cell.x0 & ~15, cell.y0, img + p.imgBase, &bar);
     }
     {
-        uint4* z = reinterpret_cast<uint4*>(smap);  // 16-byte aligned: 4*rhMax*SA bytes past A, SA % 8 == 0
+        uint4* z = reinterpret_cast<uint4*>(smap);  // 128-byte aligned, row stride a multiple of 16 bytes (SA % 8 == 0)
         const int nz = (ih + 2) * (SA / 8);
         for (int i = threadIdx.x; i < nz; i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
     }
     __syncthreads();  // barrier initialised (and armed) before anybody polls it
     orbx_mbar_wait(&bar, 0);
 
-    // ---- widening pass over the raw tile, one aligned 32-bit word (4 pixels) per thread and step: the bytes go into the two
-    // u16 pair layouts A/B used by the min/max network. Thread = (word column j, row y) with j fixed: 128/nw rows per step, so
-    // that all addresses advance by a constant (threads past the last whole row idle: < nw of 128).
     const int tmin = p.minTh, tini = p.iniTh;
     const int o = cell.x0 & 3;
     const int ca0 = o + 3;                        // A-column of interior pixel 0
     const int SD = 2 + ((o + 1) & 1) - ca0;       // strength-map column = A-column + SD (even, keeps pairs word aligned)
     const uint32_t* tw0 = reinterpret_cast<const uint32_t*>(T) + ((cell.x0 & 15) >> 2);  // word of A-columns 0..3, row 0
-    {
-        const int nw = (o + rw + 4) >> 2;  // words covering A-columns 0 .. o+rw (one past the ROI, read by boundary pairs)
-        const uint32_t rcp = c_recip[nw];
-        const int qStep = (int)((FAST_THREADS * rcp) >> 16);  // rows per step
-        const int yq = (int)((threadIdx.x * rcp) >> 16);
-        const int j = threadIdx.x - yq * nw;
-        const uint32_t* tw = tw0 + yq * (BW / 4) + j;
-        uint2* pa = reinterpret_cast<uint2*>(A + yq * SA + 4 * j);
-        uint2* pb = reinterpret_cast<uint2*>(B + yq * SA + 4 * j);
-        const int yEnd = yq < qStep ? rh : 0;
-#pragma unroll 1
-        for (int y = yq; y < yEnd; y += qStep) {
-            const uint32_t w = tw[0], wp = tw[-1];           // inside the box; tw[-1] of the first word is junk that only
-            const uint32_t t = __funnelshift_r(wp, w, 24);   // feeds masked pixels
-            pa[0] = make_uint2(__byte_perm(w, 0, 0x4140), __byte_perm(w, 0, 0x4342));
-            pb[0] = make_uint2(__byte_perm(t, 0, 0x4140), __byte_perm(t, 0, 0x4342));
-            tw += qStep * (BW / 4);
-            pa += qStep * (SA / 4);
-            pb += qStep * (SA / 4);
-        }
-    }
     // ---- threshold attempts (:812-819): first iniTh; only a cell whose FAST(iniTh) comes back empty repeats at minTh. A
     // neighbour that is not a corner at t has m <= t < m_centre, so the NMS at threshold t only needs the strengths m > t:
     // everything below (pre-test, network, map, NMS) runs on the pixels that can be corners at the attempt's threshold.
@@ -190,7 +171,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         // two ADJACENT compass points (0,4,8,12), so a corner needs (|d0|>t or |d8|>t) and (|d4|>t or |d12|>t). Four
         // VABSDIFF4 + a SWAR byte compare test 4 pixels at once. A thread collects 2 bits per step in a register and appends
         // its surviving pixel PAIRS once per 16 steps: one warp scan + one shared atomic per warp (pairs are aligned to even
-        // tile columns, so even ring offsets always read A and odd ones B; the order of the list does not matter).
+        // tile columns; the order of the list does not matter).
         {
             // bit 7 of each byte of f(x) = ((x & 0x7F..) + K) | x is set iff x > min(thr, 127): exact below 127, still
             // necessary above
@@ -237,12 +218,10 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
                 code0 += (uint32_t)(16 * pStep) << 8;
             }
         }
-        __syncthreads();  // A/B complete (first attempt), task list complete
+        __syncthreads();  // task list complete
         // ---- pass 2: the min/max network on the surviving pairs (results go to the map by position)
         const int ntAll = taskCnt;
         {
-            const uint16_t* pevn = A;      // even dx: pair (A[c+dx], A[c+dx+1]), c even
-            const uint16_t* podd = B + 1;  // odd dx:  pair (B[c+dx+1], B[c+dx+2]) = (I(c+dx), I(c+dx+1))
 #pragma unroll 1
             for (int g0 = warp * 32; g0 < ntAll; g0 += FAST_THREADS) {
                 const int g = g0 + lane;
@@ -252,7 +231,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
                     task = tasks[g];
                     const int y = task >> 8, c = 2 * (task & 255);
                     int m0, m1;
-                    fast_strength2<SA>(podd + (y + 3) * SA + c, pevn + (y + 3) * SA + c, m0, m1);
+                    fast_strength2_raw<BW>(reinterpret_cast<const uint8_t*>(tw0) + (y + 3) * BW + c, m0, m1);
                     const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
                     m0 = (m0 > thr && ix >= 0) ? m0 : 0;
                     m1 = (m1 > thr && ix + 1 < iw) ? m1 : 0;
@@ -336,14 +315,15 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     // list capacity: every pixel pair that can hold an interior pixel (interior = ROI - 6; one more pair for the alignment)
     const int iwMax = (sa == 48 ? 40 : 72) - 6, ihMax = rhMax - 6;
     const int listCap = (((iwMax + 4) / 2) * ihMax + 7) & ~7;
-    const size_t smem = (size_t)((rhMax * boxW + 127) & ~127) + (size_t)2 * rhMax * sa * 2 + (size_t)(rhMax - 4) * sa * 2 +
-                        (size_t)2 * listCap * 2;
-    static int nt = 0;  // threads per cell
+    // threads per cell: 64 measured best (tools/fast_threads_sweep.sh: 1.71 ms against 2.01 with 128 and 1.93 with 32 per 512
+    // KITTI images); ORBX_FAST_THREADS overrides it for that sweep
+    static int nt = 0;
     if (!nt) {
         const char* e = getenv("ORBX_FAST_THREADS");
-        nt = e ? atoi(e) : 128;
-        if (nt != 32 && nt != 64 && nt != 128) nt = 128;
+        nt = e ? atoi(e) : 64;
+        if (nt != 32 && nt != 64 && nt != 128) nt = 64;
     }
+    const size_t smem = (size_t)((rhMax * boxW + 127) & ~127) + (size_t)(rhMax - 4) * sa * 2 + (size_t)2 * listCap * 2;
 #define FAST_LAUNCH(SA_, NT_)                                                                                                    \
     {                                                                                                                            \
         if (smem > 32 * 1024) /* tall cells: static + dynamic may pass 48 KB; per-device attribute, set on every such launch */ \

@@ -229,6 +229,15 @@ def main():
     except OSError:
         pass
     from oracle import oracle as O  # CPU baseline only
+    from oracle import ref as R
+
+    if R.available():  # the reference's own ORBextractor.cc / Frame.cc object code (oracle/_ref) instead of the port
+        class O:  # noqa: N801 - same two names the CPU legs use
+            OracleExtractor = R.RefExtractor
+            stereo_match = staticmethod(R.stereo_match)
+        res["cpu_kind"] = "reference (oracle/_ref)"
+    else:
+        res["cpu_kind"] = "port (oracle)"
 
     import torch
 
