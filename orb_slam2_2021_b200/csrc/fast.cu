@@ -102,7 +102,9 @@ __constant__ uint32_t c_recip[32] = {0, 65536, 32768, 21846, 16384, 13108, 10923
 template <int SA, int FAST_THREADS>
 __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap)
 {
-    constexpr int BW = SA == 48 ? 64 : 96;      // TMA box width in bytes
+    // TMA box width in bytes = row stride of the tile: 20 / 28 words, so that 8 consecutive rows start in 8 different
+    // shared-memory banks (a 64-byte stride put every second row on the same banks)
+    constexpr int BW = SA == 48 ? 80 : 112;
     extern __shared__ __align__(128) uint8_t fast_smem[];
     __shared__ __align__(8) uint64_t bar;
     __shared__ int listCnt, taskCnt, nzCnt;
@@ -302,7 +304,7 @@ void orbx_fast_geometry(const OrbxParams& p, int* boxW, int* rhMaxOut)
         rhMax = p.lv[l].hCell + 6 > rhMax ? p.lv[l].hCell + 6 : rhMax;
     }
     // tile columns: 3 (alignment) + ROI + 1, rounded up to whole words; strength-map columns: interior + 8
-    *boxW = rwMax + 8 <= 48 ? 64 : 96;
+    *boxW = rwMax + 8 <= 48 ? 80 : 112;  // (needs 15 + ROI + 1 columns; the rest spreads the rows over the banks)
     *rhMaxOut = rhMax;
 }
 
@@ -311,7 +313,7 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     int boxW, rhMax;
     orbx_fast_geometry(p, &boxW, &rhMax);
     dim3 grid(p.cellsTotal, p.imgs);
-    const int sa = boxW == 64 ? 48 : 80;
+    const int sa = boxW == 80 ? 48 : 80;
     // list capacity: every pixel pair that can hold an interior pixel (interior = ROI - 6; one more pair for the alignment)
     const int iwMax = (sa == 48 ? 40 : 72) - 6, ihMax = rhMax - 6;
     const int listCap = (((iwMax + 4) / 2) * ihMax + 7) & ~7;
