@@ -1,6 +1,7 @@
 // oracle/cvshim/opencv2/cvshim.hpp — TEST INFRASTRUCTURE ONLY (see ../../orb_oracle.h).
 //
-// A minimal stand-in for the part of the OpenCV C++ API that /root/reference/src/ORBextractor.cc and src/Frame.cc use, so
+// A minimal stand-in for the part of the OpenCV C++ API that /root/reference/src/ORBextractor.cc, src/Frame.cc and the
+// vendored Thirdparty/DBoW2 use, so
 // that the reference's OWN translation units can be compiled from where they lie (oracle/Makefile target _ref) although
 // this image has no OpenCV C++ headers or libraries. Nothing here is OpenCV code: the containers (Mat, KeyPoint, Point_, Size, Rect,
 // InputArray/OutputArray) are written from the documented interface, and the five primitives the reference calls
@@ -17,6 +18,12 @@
 #include <cstddef>
 #include <cstdlib>
 #include <cstring>
+#include <fstream>
+#include <iostream>
+#include <limits>
+#include <numeric>
+#include <sstream>
+#include <string>
 #include <vector>
 
 #define CV_PI 3.1415926535897932384626433832795
@@ -323,6 +330,30 @@ public:
         return Init{this, 1};
     }
 };
+
+// cv::FileStorage / cv::FileNode: the YAML save/load of DBoW2's TemplatedVocabulary are virtual, so they are instantiated
+// and must compile; nothing here ever calls them (vocabularies come in through loadFromTextFile). Everything aborts.
+class FileNode {
+public:
+    FileNode operator[](const char*) const { std::abort(); }
+    FileNode operator[](const std::string&) const { std::abort(); }
+    FileNode operator[](int) const { std::abort(); }
+    size_t size() const { std::abort(); }
+    operator int() const { std::abort(); }
+    operator double() const { std::abort(); }
+    operator std::string() const { std::abort(); }
+};
+class FileStorage {
+public:
+    enum { READ = 0, WRITE = 1 };
+    FileStorage() {}
+    FileStorage(const std::string&, int) { std::abort(); }
+    bool isOpened() const { return false; }
+    void release() {}
+    FileNode operator[](const std::string&) const { std::abort(); }
+    FileNode operator[](const char*) const { std::abort(); }
+};
+template <typename T> inline FileStorage& operator<<(FileStorage& fs, const T&) { std::abort(); return fs; }
 
 enum { BORDER_REFLECT_101 = 4, BORDER_ISOLATED = 16 };
 enum { INTER_LINEAR = 1 };

@@ -1,8 +1,9 @@
 // oracle/cvshim/ref_stubs.h — TEST INFRASTRUCTURE ONLY (see ../orb_oracle.h).
 //
-// Force-included (-include) when /root/reference/src/Frame.cc is compiled for oracle/_ref. Frame.h pulls in MapPoint.h,
-// KeyFrame.h, ORBVocabulary.h (DBoW2 over cv::Mat descriptors) and Frame.cc pulls in Converter.h (Eigen, g2o) and
-// ORBmatcher.h — none of which can be compiled here. Their include guards are defined up front so that those headers
+// Force-included (-include) when /root/reference/src/Frame.cc is compiled for oracle/_ref. Frame.h pulls in MapPoint.h and
+// KeyFrame.h, and Frame.cc pulls in Converter.h (Eigen, g2o) and ORBmatcher.h — none of which can be compiled here.
+// (ORBVocabulary.h is NOT stubbed: the vendored DBoW2 compiles against the OpenCV stand-in, so Frame::ComputeBoW runs the
+// real TemplatedVocabulary::transform.) Their include guards are defined up front so that those headers
 // read as empty, and the few names Frame.cc needs from them are declared below. Of these only
 // ORBmatcher::TH_LOW/TH_HIGH/DescriptorDistance are ever used by the code that RUNS in the tests (ComputeStereoMatches,
 // src/Frame.cc:522-700): they are defined in ref_wrap.cpp from src/ORBmatcher.cc:37-38 and :1672-1688. Everything else
@@ -10,7 +11,6 @@
 #pragma once
 #define MAPPOINT_H
 #define KEYFRAME_H
-#define ORBVOCABULARY_H
 #define CONVERTER_H
 #define ORBMATCHER_H
 
@@ -42,11 +42,6 @@ public:
 };
 
 class KeyFrame {};
-
-class ORBVocabulary {
-public:
-    void transform(const std::vector<cv::Mat>& features, DBoW2::BowVector& v, DBoW2::FeatureVector& fv, int levelsup) const;
-};
 
 class Converter {
 public:

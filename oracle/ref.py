@@ -51,6 +51,11 @@ def lib():
         L.ref_assign_features_to_grid.argtypes = [vp, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, vp, vp]
         L.ref_features_in_area.argtypes = [vp, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float,
                                            C.c_float, C.c_int, C.c_int, vp]
+        L.ref_voc_load.restype = vp
+        L.ref_voc_load.argtypes = [C.c_char_p]
+        L.ref_voc_destroy.argtypes = [vp]
+        L.ref_voc_words.argtypes = [vp]
+        L.ref_compute_bow.argtypes = [vp, vp, C.c_int] + [vp] * 7
         _lib = L
     return _lib
 
@@ -132,3 +137,43 @@ def features_in_area(keys_un, bounds, x, y, r, min_level=-1, max_level=-1):
     k = lib().ref_features_in_area(_ptr(keys_un), len(keys_un), *[float(b) for b in bounds], x, y, r, min_level, max_level,
                                    _ptr(out))
     return out[:k]
+
+
+def write_vocabulary_text(path, k, L, parent, is_leaf, desc, weight):
+    """The text format ORBVocabulary::loadFromTextFile reads (TemplatedVocabulary.h:1351-1439): "k L scoring weighting", then
+    one line per node "parent isLeaf d0 .. d31 weight". No newline after the last node (the loader's eof loop would
+    otherwise append an empty node to the root). Scoring L1_NORM = 0, weighting TF_IDF = 0, as in ORBvoc.txt."""
+    lines = [f"{k} {L} 0 0"]
+    for i in range(len(parent)):
+        lines.append(f"{int(parent[i])} {int(is_leaf[i])} " + " ".join(str(int(b)) for b in desc[i]) + f" {float(weight[i])!r}")
+    with open(path, "w") as f:
+        f.write("\n".join(lines))
+
+
+class RefVocabulary:
+    """ORB_SLAM2::ORBVocabulary (the vendored DBoW2 TemplatedVocabulary<FORB>) loaded by its own loadFromTextFile."""
+
+    def __init__(self, path):
+        self._h = lib().ref_voc_load(os.fsencode(path))
+        if not self._h:
+            raise ValueError("loadFromTextFile failed")
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            lib().ref_voc_destroy(h)
+
+    @property
+    def n_words(self):
+        return lib().ref_voc_words(self._h)
+
+    def transform(self, desc):
+        """Frame::ComputeBoW (levelsup = 4) -> (word_ids, word_vals, fv_nodes, fv_start, fv_feats), like oracle.Vocabulary."""
+        desc = np.ascontiguousarray(desc, dtype=np.uint8).reshape(-1, 32)
+        n = len(desc)
+        wi, wv = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.float64)
+        fn, fs, ff = np.zeros(max(n, 1), np.int32), np.zeros(n + 1, np.int32), np.zeros(max(n, 1), np.int32)
+        nw, nf = C.c_int(), C.c_int()
+        lib().ref_compute_bow(self._h, _ptr(desc), n, _ptr(wi), _ptr(wv), C.addressof(nw), _ptr(fn), _ptr(fs), _ptr(ff),
+                              C.addressof(nf))
+        return wi[: nw.value], wv[: nw.value], fn[: nf.value], fs[: nf.value + 1], ff[: fs[nf.value]]

@@ -170,8 +170,14 @@ cv::Mat MapPoint::GetNormal() { std::abort(); }
 float MapPoint::GetMaxDistanceInvariance() { std::abort(); }
 float MapPoint::GetMinDistanceInvariance() { std::abort(); }
 int MapPoint::PredictScale(const float&, Frame*) { std::abort(); }
-void ORBVocabulary::transform(const std::vector<cv::Mat>&, DBoW2::BowVector&, DBoW2::FeatureVector&, int) const { std::abort(); }
-std::vector<cv::Mat> Converter::toDescriptorVector(const cv::Mat&) { std::abort(); }
+// Converter::toDescriptorVector, src/Converter.cc:27-35: one 1x32 row header per descriptor
+std::vector<cv::Mat> Converter::toDescriptorVector(const cv::Mat& Descriptors)
+{
+    std::vector<cv::Mat> vDesc;
+    vDesc.reserve(Descriptors.rows);
+    for (int j = 0; j < Descriptors.rows; j++) vDesc.push_back(Descriptors.row(j));
+    return vDesc;
+}
 
 }  // namespace ORB_SLAM2
 
@@ -345,6 +351,50 @@ int ref_features_in_area(const orc_keypoint* keysUn, int n, float minX, float ma
     const std::vector<size_t> v = F.GetFeaturesInArea(x, y, r, minLevel, maxLevel);
     for (size_t i = 0; i < v.size(); ++i) out[i] = (int)v[i];
     return (int)v.size();
+}
+
+// ---- Frame::ComputeBoW (src/Frame.cc:447-454) over the vendored DBoW2, which compiles against the OpenCV stand-in:
+// ORBVocabulary::loadFromTextFile (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1351-1439) reads the vocabulary, and
+// TemplatedVocabulary::transform(features, BowVector, FeatureVector, 4) (:1140-1272) with FORB::distance runs unchanged.
+void* ref_voc_load(const char* textFile)
+{
+    ORB_SLAM2::ORBVocabulary* v = new ORB_SLAM2::ORBVocabulary();
+    if (!v->loadFromTextFile(textFile)) {
+        delete v;
+        return nullptr;
+    }
+    return v;
+}
+
+void ref_voc_destroy(void* v) { delete (ORB_SLAM2::ORBVocabulary*)v; }
+
+int ref_voc_words(void* v) { return (int)((ORB_SLAM2::ORBVocabulary*)v)->size(); }
+
+// BowVector as (word id, value) in map order; FeatureVector as CSR (node id, start, feature indices) in map order.
+// Capacities: n entries each (start: n + 1).
+int ref_compute_bow(void* v, const uint8_t* desc, int n, int* wordIds, double* wordVals, int* nWords, int* fvNodes, int* fvStart,
+                    int* fvFeats, int* nNodes)
+{
+    ORB_SLAM2::Frame F;
+    F.mpORBvocabulary = (ORB_SLAM2::ORBVocabulary*)v;
+    F.mDescriptors = cv::Mat(n, 32, CV_8U, (void*)desc, 32).clone();
+    F.N = n;
+    F.ComputeBoW();
+    int k = 0;
+    for (DBoW2::BowVector::const_iterator it = F.mBowVec.begin(); it != F.mBowVec.end(); ++it, ++k) {
+        wordIds[k] = (int)it->first;
+        wordVals[k] = it->second;
+    }
+    *nWords = k;
+    int m = 0, f = 0;
+    for (DBoW2::FeatureVector::const_iterator it = F.mFeatVec.begin(); it != F.mFeatVec.end(); ++it, ++m) {
+        fvNodes[m] = (int)it->first;
+        fvStart[m] = f;
+        for (size_t j = 0; j < it->second.size(); ++j) fvFeats[f++] = (int)it->second[j];
+    }
+    fvStart[m] = f;
+    *nNodes = m;
+    return 0;
 }
 
 }  // extern "C"

@@ -253,3 +253,50 @@ def test_cuda_batch_stereo_equals_reference():
         assert_same((out["kps_left"][k, :m], out["desc_left"][k, :m]), (rkl, rdl), f"{k}/L")
         rur, rdp = R.stereo_match(rl, rr, rkl, rdl, rkr, rdr, bf, bf / fx)
         assert np.array_equal(out["u_right"][k, :m], rur) and np.array_equal(out["depth"][k, :m], rdp), k
+
+
+# ---------------------------------------------------------------- Frame::ComputeBoW over the vendored DBoW2
+
+def _bow_cases(tmp_path):
+    from . import bow_util as B
+
+    for k, L, ragged in [(10, 3, False), (4, 5, False), (7, 4, True), (2, 6, False), (10, 5, False), (20, 3, True)]:
+        arrays = B.synthetic_vocabulary(k, L, seed=k * 10 + L, ragged=ragged)
+        path = str(tmp_path / f"voc_{k}_{L}.txt")
+        R.write_vocabulary_text(path, k, L, *arrays)
+        sets = [B.features_near_words(arrays[2], arrays[1], n, seed=n) if n else np.zeros((0, 32), np.uint8)
+                for n in (0, 1, 33, 500, 2000)]
+        yield L, arrays, R.RefVocabulary(path), sets
+
+
+@needs_ref
+def test_bow_oracle_equals_dbow2(tmp_path):
+    """Frame::ComputeBoW (src/Frame.cc:447-454) through the reference's vendored DBoW2 — ORBVocabulary::loadFromTextFile,
+    TemplatedVocabulary::transform with levelsup 4, FORB::distance, L1 scoring, all as compiled reference code — against the
+    oracle (oracle/bow.cpp): word ids, the float64 weights bit for bit, node ids and feature lists."""
+    for L, arrays, rv, sets in _bow_cases(tmp_path):
+        ov = O.Vocabulary(L, *arrays)
+        assert rv.n_words == ov.n_words
+        for d in sets:
+            for x, y in zip(ov.transform(d, 4), rv.transform(d)):
+                assert x.dtype == y.dtype and np.array_equal(x, y), (L, len(d))
+
+
+@needs_ref
+@pytest.mark.gpu
+def test_cuda_bow_equals_dbow2(tmp_path):
+    """orbx_compute_bow (include/orbx_bow.h) against the same DBoW2 object code, one frame per call and all in one call."""
+    import orb_slam2_2021_b200 as pkg
+
+    for L, arrays, rv, sets in _bow_cases(tmp_path):
+        gv = pkg.ORBVocabulary(L, *arrays)
+        for got, d in zip(gv.transform(sets, 4), sets):
+            for x, y in zip(got, rv.transform(d)):
+                assert x.dtype == y.dtype and np.array_equal(x, y), (L, len(d))
+    # descriptors of a real extraction
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["kitti"]
+    _, desc = pkg.ORBextractor(nf, sf, nl, ini, mn)(synth.synth(W, H, 3))
+    for L, arrays, rv, sets in _bow_cases(tmp_path):
+        if L == 5:
+            for x, y in zip(pkg.ORBVocabulary(L, *arrays).transform(desc, 4), rv.transform(desc)):
+                assert np.array_equal(x, y)
