@@ -210,13 +210,7 @@ public:
             for (int x = 0; x < c; ++x) m.at<float>(y, x) = 1.f;
         return m;
     }
-    Mat t() const
-    {
-        Mat m(cols, rows, CV_32F);
-        for (int y = 0; y < rows; ++y)
-            for (int x = 0; x < cols; ++x) m.at<float>(x, y) = at<float>(y, x);
-        return m;
-    }
+    inline struct MatTExpr t() const;  // lazy, like cv::MatExpr: -A.t() * b becomes ONE gemm (see below)
     double dot(const Mat& o) const
     {
         double s = 0;
@@ -278,17 +272,75 @@ inline Mat operator*(float s, const Mat& a)
     return m;
 }
 inline Mat operator-(const Mat& a) { return -1.f * a; }
-inline Mat operator*(const Mat& a, const Mat& b)
+inline Mat operator/(const Mat& a, float s)
 {
-    Mat m(a.rows, b.cols, CV_32F);
+    Mat m(a.rows, a.cols, CV_32F);
     for (int y = 0; y < a.rows; ++y)
-        for (int x = 0; x < b.cols; ++x) {
-            double s = 0;
-            for (int k = 0; k < a.cols; ++k) s += (double)a.at<float>(y, k) * b.at<float>(k, x);
-            m.at<float>(y, x) = (float)s;
+        for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = a.at<float>(y, x) / s;
+    return m;
+}
+
+// ---- matrix products are lazy, as cv::MatExpr makes them: `A * b + c` is ONE cv::gemm(A, b, 1, c, 1) and `-A.t() * b` is
+// ONE cv::gemm(A, b, -1, noArray, 0, GEMM_1_T). The arithmetic of the two shapes the reference's SearchByProjection runs
+// (src/ORBmatcher.cc:1358-1367, :1383) is the one tests/test_frame_oracle.py pins against cv2 4.13:
+//   3x3 * 3x1, not transposed (OpenCV's small-matrix path): float products, float sums left to right, then
+//     (float)((double)sum * alpha + (double)c * beta);
+//   everything else (the general path): double accumulation over k, times alpha (plus c), one rounding to float.
+struct MatTExpr {
+    Mat a;
+    double alpha;
+    operator Mat() const
+    {
+        Mat m(a.cols, a.rows, CV_32F);
+        for (int y = 0; y < a.rows; ++y)
+            for (int x = 0; x < a.cols; ++x) m.at<float>(x, y) = (float)(alpha * a.at<float>(y, x));
+        return m;
+    }
+};
+inline MatTExpr Mat::t() const { return MatTExpr{*this, 1.0}; }
+inline MatTExpr operator-(const MatTExpr& t) { return MatTExpr{t.a, -t.alpha}; }
+
+inline Mat gemm_(const Mat& a, bool aT, const Mat& b, double alpha, const Mat* c)
+{
+    const int M = aT ? a.cols : a.rows, K = aT ? a.rows : a.cols, N = b.cols;
+    assert(b.rows == K);
+    Mat m(M, N, CV_32F);
+    const bool small = !aT && M == 3 && K == 3 && N == 1;
+    for (int y = 0; y < M; ++y)
+        for (int x = 0; x < N; ++x) {
+            const double cv = c ? (double)c->at<float>(y, x) : 0.0;
+            if (small) {
+                volatile float p0 = a.at<float>(y, 0) * b.at<float>(0, x), p1 = a.at<float>(y, 1) * b.at<float>(1, x),
+                               p2 = a.at<float>(y, 2) * b.at<float>(2, x);
+                volatile float sum = p0 + p1;
+                sum = sum + p2;
+                m.at<float>(y, x) = (float)((double)sum * alpha + cv * 1.0);
+            } else {
+                double acc = 0;
+                for (int k = 0; k < K; ++k) acc += (double)(aT ? a.at<float>(k, y) : a.at<float>(y, k)) * (double)b.at<float>(k, x);
+                m.at<float>(y, x) = (float)(acc * alpha + cv);
+            }
         }
     return m;
 }
+struct MatMulExpr {
+    Mat a, b;
+    bool aT;
+    double alpha;
+    operator Mat() const { return gemm_(a, aT, b, alpha, nullptr); }
+    template <typename T> T at(int i) const { return Mat(*this).at<T>(i); }
+};
+inline MatMulExpr operator*(const Mat& a, const Mat& b) { return MatMulExpr{a, b, false, 1.0}; }
+inline MatMulExpr operator*(const MatTExpr& t, const Mat& b) { return MatMulExpr{t.a, b, true, t.alpha}; }
+inline MatMulExpr operator*(const MatMulExpr& m, const Mat& b) { return MatMulExpr{Mat(m), b, false, 1.0}; }
+inline MatMulExpr operator*(const Mat& a, const MatTExpr& t) { return MatMulExpr{a, Mat(t), false, 1.0}; }
+inline MatMulExpr operator*(const MatMulExpr& m, const MatTExpr& t) { return MatMulExpr{Mat(m), Mat(t), false, 1.0}; }
+inline MatMulExpr operator*(float s, const MatMulExpr& m) { return MatMulExpr{m.a, m.b, m.aT, m.alpha * s}; }
+inline MatMulExpr operator-(const MatMulExpr& m) { return MatMulExpr{m.a, m.b, m.aT, -m.alpha}; }
+inline Mat operator+(const MatMulExpr& m, const Mat& c) { return gemm_(m.a, m.aT, m.b, m.alpha, &c); }
+inline Mat operator-(const MatMulExpr& m, const Mat& c) { return Mat(m) - c; }
+inline Mat operator-(const Mat& c, const MatMulExpr& m) { return c - Mat(m); }
+inline Mat operator+(const Mat& c, const MatMulExpr& m) { return gemm_(m.a, m.aT, m.b, m.alpha, &c); }
 enum { NORM_L1 = 2, NORM_L2 = 4 };
 inline double norm(const Mat& a)
 {

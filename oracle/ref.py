@@ -177,3 +177,58 @@ class RefVocabulary:
         lib().ref_compute_bow(self._h, _ptr(desc), n, _ptr(wi), _ptr(wv), C.addressof(nw), _ptr(fn), _ptr(fs), _ptr(ff),
                               C.addressof(nf))
         return wi[: nw.value], wv[: nw.value], fn[: nf.value], fs[: nf.value + 1], ff[: fs[nf.value]]
+
+
+def _padded(frame):
+    """A copy of an oracle FrameView's C struct whose scale-factor table has 16 entries (the reference's Frame gets a
+    std::vector; the wrapper copies 16 floats)."""
+    from .oracle import _OrcFrame
+
+    sf = np.ones(16, np.float32)
+    k = min(16, len(frame.scale_factors))
+    sf[:k] = frame.scale_factors[:k]
+    sf[k:] = frame.scale_factors[k - 1]
+    c = _OrcFrame()
+    C.memmove(C.byref(c), C.byref(frame.c), C.sizeof(_OrcFrame))
+    c.scale_factors = sf.ctypes.data
+    return c, sf
+
+
+def search_by_projection(cur, last, has_point, world_pos, point_desc, observed, th, b_mono=False, check_orientation=True):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono), the reference's own src/ORBmatcher.cc:1348-1491 on
+    its own Frame objects (cur / last: oracle.FrameView) -> (match_of_cur, nmatches), like oracle.search_by_projection."""
+    from .oracle import _OrcFrame, _OrcMapPoints
+
+    hp = np.ascontiguousarray(has_point, dtype=np.uint8)
+    wp = np.ascontiguousarray(world_pos, dtype=np.float32).reshape(-1, 3)
+    pd = np.ascontiguousarray(point_desc, dtype=np.uint8).reshape(-1, 32)
+    ob = np.ascontiguousarray(observed, dtype=np.uint8)
+    m = _OrcMapPoints(hp.ctypes.data, wp.ctypes.data, pd.ctypes.data, ob.ctypes.data)
+    (cc, _k1), (lc, _k2) = _padded(cur), _padded(last)
+    out = np.full(max(cur.c.n, 1), -1, np.int32)
+    L = lib()
+    L.ref_search_by_projection.argtypes = [C.POINTER(_OrcFrame), C.POINTER(_OrcFrame), C.POINTER(_OrcMapPoints), C.c_float,
+                                           C.c_int, C.c_int, C.c_void_p]
+    n = L.ref_search_by_projection(C.byref(cc), C.byref(lc), C.byref(m), th, int(b_mono), int(check_orientation), _ptr(out))
+    return out[: cur.c.n], n
+
+
+def search_local_points(frame, occupied, valid, proj, level, view_cos, point_desc, observed, th, nnratio=0.8):
+    """ORBmatcher::SearchByProjection(F, vpMapPoints, th), the reference's own src/ORBmatcher.cc:45-127 -> (match_of_key, n)."""
+    from .oracle import _OrcFrame, _OrcTrackPoints
+
+    va = np.ascontiguousarray(valid, dtype=np.uint8)
+    pr = np.ascontiguousarray(proj, dtype=np.float32).reshape(-1, 3)
+    lv = np.ascontiguousarray(level, dtype=np.int32)
+    vc = np.ascontiguousarray(view_cos, dtype=np.float32)
+    pd = np.ascontiguousarray(point_desc, dtype=np.uint8).reshape(-1, 32)
+    ob = np.ascontiguousarray(observed, dtype=np.uint8)
+    oc = None if occupied is None else np.ascontiguousarray(occupied, dtype=np.uint8)
+    t = _OrcTrackPoints(len(va), va.ctypes.data, pr.ctypes.data, lv.ctypes.data, vc.ctypes.data, pd.ctypes.data, ob.ctypes.data)
+    fc, _keep = _padded(frame)
+    out = np.full(max(frame.c.n, 1), -1, np.int32)
+    L = lib()
+    L.ref_search_local_points.argtypes = [C.POINTER(_OrcFrame), C.c_void_p, C.POINTER(_OrcTrackPoints), C.c_float, C.c_float,
+                                          C.c_void_p]
+    n = L.ref_search_local_points(C.byref(fc), None if oc is None else _ptr(oc), C.byref(t), th, nnratio, _ptr(out))
+    return out[: frame.c.n], n

@@ -29,6 +29,7 @@
 #include "Frame.h"      // with cvshim/ref_stubs.h force-included (see the Makefile): MapPoint, KeyFrame, ... read as stubs
 #undef private
 #include "ORBextractor.h"
+#include "ORBmatcher.h"
 #include "orb_oracle.h"
 
 // ---------------------------------------------------------------- arena behind operator new (active inside a call)
@@ -149,27 +150,25 @@ void undistortPoints(const Mat&, Mat&, const Mat&, const Mat&, const Mat&, const
 // ---------------------------------------------------------------- what src/Frame.cc needs from files that cannot be built
 namespace ORB_SLAM2 {
 
-// src/ORBmatcher.cc:37-38
-const int ORBmatcher::TH_HIGH = 100;
-const int ORBmatcher::TH_LOW = 50;
-
-// ORBmatcher::DescriptorDistance, src/ORBmatcher.cc:1672-1688: population count of the XOR of two 256-bit descriptors
-// (the reference uses a parallel bit count over 8 int32 words; the count is the same number)
-int ORBmatcher::DescriptorDistance(const cv::Mat& a, const cv::Mat& b)
-{
-    const uint32_t* pa = a.ptr<uint32_t>();
-    const uint32_t* pb = b.ptr<uint32_t>();
-    int dist = 0;
-    for (int i = 0; i < 8; ++i) dist += __builtin_popcount(pa[i] ^ pb[i]);
-    return dist;
-}
-
 // never reached by the functions the tests call; they only have to link
-cv::Mat MapPoint::GetWorldPos() { std::abort(); }
 cv::Mat MapPoint::GetNormal() { std::abort(); }
 float MapPoint::GetMaxDistanceInvariance() { std::abort(); }
 float MapPoint::GetMinDistanceInvariance() { std::abort(); }
 int MapPoint::PredictScale(const float&, Frame*) { std::abort(); }
+int MapPoint::PredictScale(const float&, KeyFrame*) { std::abort(); }
+void MapPoint::AddObservation(KeyFrame*, size_t) { std::abort(); }
+int MapPoint::GetIndexInKeyFrame(KeyFrame*) { std::abort(); }
+bool MapPoint::IsInKeyFrame(KeyFrame*) { std::abort(); }
+void MapPoint::Replace(MapPoint*) { std::abort(); }
+cv::Mat KeyFrame::GetCameraCenter() { std::abort(); }
+cv::Mat KeyFrame::GetRotation() { std::abort(); }
+cv::Mat KeyFrame::GetTranslation() { std::abort(); }
+void KeyFrame::AddMapPoint(MapPoint*, const size_t&) { std::abort(); }
+std::set<MapPoint*> KeyFrame::GetMapPoints() { std::abort(); }
+std::vector<MapPoint*> KeyFrame::GetMapPointMatches() { std::abort(); }
+MapPoint* KeyFrame::GetMapPoint(const size_t&) { std::abort(); }
+std::vector<size_t> KeyFrame::GetFeaturesInArea(const float&, const float&, const float&) const { std::abort(); }
+bool KeyFrame::IsInImage(const float&, const float&) const { std::abort(); }
 // Converter::toDescriptorVector, src/Converter.cc:27-35: one 1x32 row header per descriptor
 std::vector<cv::Mat> Converter::toDescriptorVector(const cv::Mat& Descriptors)
 {
@@ -395,6 +394,89 @@ int ref_compute_bow(void* v, const uint8_t* desc, int n, int* wordIds, double* w
     fvStart[m] = f;
     *nNodes = m;
     return 0;
+}
+
+// ---- ORBmatcher::SearchByProjection, both overloads, as the reference's own src/ORBmatcher.cc on its own Frame objects.
+// The inputs use the oracle's structs (orb_oracle.h: what the functions read from a Frame and from the map points).
+static void ref_fill_frame(ORB_SLAM2::Frame& F, const orc_frame* f, bool current)
+{
+    ORB_SLAM2::Frame::fx = f->fx;
+    ORB_SLAM2::Frame::fy = f->fy;
+    ORB_SLAM2::Frame::cx = f->cx;
+    ORB_SLAM2::Frame::cy = f->cy;
+    F.mbf = f->mbf;
+    F.mb = f->mb;
+    F.mvKeys.resize(f->n);
+    if (f->n) std::memcpy(F.mvKeys.data(), f->keys_un, (size_t)f->n * sizeof(orc_keypoint));  // :1398 reads mvKeys[i].octave
+    F.mTcw = cv::Mat(4, 4, CV_32F);
+    for (int r = 0; r < 4; ++r)
+        for (int c = 0; c < 4; ++c) F.mTcw.at<float>(r, c) = r < 3 ? f->Tcw[4 * r + c] : (c == 3 ? 1.f : 0.f);
+    if (current) {
+        ref_frame_grid_setup(F, f->keys_un, f->n, f->min_x, f->max_x, f->min_y, f->max_y);  // N, mvKeysUn, statics, mGrid
+        F.mDescriptors = cv::Mat(f->n, 32, CV_8U, (void*)f->desc, 32).clone();
+        F.mvuRight.assign(f->n, -1.f);
+        if (f->u_right) F.mvuRight.assign(f->u_right, f->u_right + f->n);
+        F.mvScaleFactors.assign(f->scale_factors, f->scale_factors + 16);  // callers pass >= 16 entries (see ref.py)
+        F.mvpMapPoints.assign(f->n, static_cast<ORB_SLAM2::MapPoint*>(NULL));
+    } else {
+        F.N = f->n;
+        F.mvKeysUn = F.mvKeys;
+    }
+}
+
+int ref_search_by_projection(const orc_frame* cur, const orc_frame* last, const orc_mappoints* mp, float th, int bMono,
+                             int checkOrientation, int* matchOfCur)
+{
+    ORB_SLAM2::Frame C, L;
+    ref_fill_frame(L, last, false);
+    ref_fill_frame(C, cur, true);  // last: the statics (camera, bounds) are the current frame's
+    std::vector<ORB_SLAM2::MapPoint> pts(last->n);
+    L.mvpMapPoints.assign(last->n, static_cast<ORB_SLAM2::MapPoint*>(NULL));
+    L.mvbOutlier.assign(last->n, false);
+    for (int i = 0; i < last->n; ++i) {
+        if (!mp->has_point[i]) continue;
+        pts[i].mWorldPos = cv::Mat(3, 1, CV_32F);
+        for (int k = 0; k < 3; ++k) pts[i].mWorldPos.at<float>(k) = mp->world_pos[3 * i + k];
+        pts[i].mDescriptor = cv::Mat(1, 32, CV_8U, (void*)(mp->point_desc + 32 * (size_t)i), 32).clone();
+        pts[i].nObs = mp->observed[i] ? 1 : 0;
+        L.mvpMapPoints[i] = &pts[i];
+    }
+    ORB_SLAM2::ORBmatcher matcher(0.9f, checkOrientation != 0);
+    const int n = matcher.SearchByProjection(C, L, th, bMono != 0);
+    for (int i = 0; i < cur->n; ++i) matchOfCur[i] = C.mvpMapPoints[i] ? (int)(C.mvpMapPoints[i] - pts.data()) : -1;
+    return n;
+}
+
+int ref_search_local_points(const orc_frame* f, const uint8_t* occupied, const orc_trackpoints* tp, float th, float nnratio,
+                            int* matchOfKey)
+{
+    ORB_SLAM2::Frame F;
+    ref_fill_frame(F, f, true);
+    ORB_SLAM2::MapPoint held;  // stands for "a point with Observations() > 0" in the occupied entries
+    held.nObs = 1;
+    if (occupied)
+        for (int i = 0; i < f->n; ++i)
+            if (occupied[i]) F.mvpMapPoints[i] = &held;
+    std::vector<ORB_SLAM2::MapPoint> pts(tp->n);
+    std::vector<ORB_SLAM2::MapPoint*> vp(tp->n);
+    for (int i = 0; i < tp->n; ++i) {
+        pts[i].mbTrackInView = tp->valid[i] != 0;
+        pts[i].mTrackProjX = tp->proj[3 * i];
+        pts[i].mTrackProjY = tp->proj[3 * i + 1];
+        pts[i].mTrackProjXR = tp->proj[3 * i + 2];
+        pts[i].mnTrackScaleLevel = tp->level[i];
+        pts[i].mTrackViewCos = tp->view_cos[i];
+        pts[i].mDescriptor = cv::Mat(1, 32, CV_8U, (void*)(tp->point_desc + 32 * (size_t)i), 32).clone();
+        pts[i].nObs = tp->observed[i] ? 1 : 0;
+        vp[i] = &pts[i];
+    }
+    ORB_SLAM2::ORBmatcher matcher(nnratio, true);
+    const int n = matcher.SearchByProjection(F, vp, th);
+    for (int i = 0; i < f->n; ++i) {
+        ORB_SLAM2::MapPoint* q = F.mvpMapPoints[i];
+        matchOfKey[i] = (q && q != &held) ? (int)(q - pts.data()) : -1;
+    }
+    return n;
 }
 
 }  // extern "C"

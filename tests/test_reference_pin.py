@@ -300,3 +300,93 @@ def test_cuda_bow_equals_dbow2(tmp_path):
         if L == 5:
             for x, y in zip(pkg.ORBVocabulary(L, *arrays).transform(desc, 4), rv.transform(desc)):
                 assert np.array_equal(x, y)
+
+
+# ---------------------------------------------------------------- ORBmatcher.cc: SearchByProjection, both overloads
+
+SEARCH_CASES = [(0, 0.0, False, True, True, 300, 30), (1, 0.5, False, True, True, 300, 30), (2, -0.5, False, True, False, 300, 30),
+                (3, 0.5, True, False, True, 300, 30), (4, 0.0, False, False, False, 300, 30), (5, 0.0, False, True, True, 2000, 400),
+                (7, 0.0, False, True, True, 300, 200)]
+LOCAL_CASES = [(0, 1.0, True, True, 400, 40), (1, 3.0, True, False, 400, 40), (2, 5.0, False, True, 400, 40),
+               (3, 1.0, False, False, 400, 200), (4, 1.0, True, True, 3000, 500)]
+
+
+def _scenario(seed, tz, ur, n_last, clones):
+    from . import frames_util as U
+
+    big = n_last > 1000
+    return U.random_scenario(seed, n_last=n_last, n_extra=n_last // 2, tz=tz, clones=clones, with_uright=ur,
+                             W=1241 if big else 640, H=376 if big else 400)
+
+
+def _local(seed, ur, n_points, clones):
+    from . import frames_util as U
+
+    big = n_points > 1000
+    return U.local_map_scenario(seed, n_points=n_points, n_extra=n_points // 2, clones=clones, with_uright=ur,
+                                W=1241 if big else 640, H=376 if big else 400)
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,tz,mono,ori,ur,n_last,clones", SEARCH_CASES)
+def test_search_by_projection_oracle_equals_reference(seed, tz, mono, ori, ur, n_last, clones):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) as the reference's own src/ORBmatcher.cc:1348-1491
+    (with the real Frame::GetFeaturesInArea, DescriptorDistance, ComputeThreeMaxima) against the oracle: which map point ends
+    up in which current keypoint, incl. blocked keypoints and the rotation-histogram removal."""
+    from . import frames_util as U
+
+    cur, last, has, world, pdesc, obs = _scenario(seed, tz, ur, n_last, clones)
+    fc, fl = U.view(O.FrameView, cur), U.view(O.FrameView, last)
+    for th in (7, 15):
+        a, na = O.search_by_projection(fc, fl, has, world, pdesc, obs, th, mono, ori)
+        b, nb = R.search_by_projection(fc, fl, has, world, pdesc, obs, th, mono, ori)
+        assert na == nb and np.array_equal(a, b), (seed, th, na, nb)
+        assert nb > 20
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,th,ur,occ,n_points,clones", LOCAL_CASES)
+def test_search_local_points_oracle_equals_reference(seed, th, ur, occ, n_points, clones):
+    """ORBmatcher::SearchByProjection(F, vpMapPoints, th), src/ORBmatcher.cc:45-127, same comparison."""
+    from . import frames_util as U
+
+    F, occupied, valid, proj, level, vc, pdesc, obs = _local(seed, ur, n_points, clones)
+    occupied = occupied if occ else None
+    fv = U.view(O.FrameView, F)
+    for ratio in (0.8, 0.6, 10.0):
+        a, na = O.search_local_points(fv, occupied, valid, proj, level, vc, pdesc, obs, th, ratio)
+        b, nb = R.search_local_points(fv, occupied, valid, proj, level, vc, pdesc, obs, th, ratio)
+        assert na == nb and np.array_equal(a, b), (seed, ratio, na, nb)
+    assert nb > 30
+
+
+@needs_ref
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,tz,mono,ori,ur,n_last,clones", SEARCH_CASES)
+def test_cuda_search_by_projection_equals_reference(seed, tz, mono, ori, ur, n_last, clones):
+    """orbx_search_by_projection (include/orbx_frame.h) against the reference's own ORBmatcher.cc."""
+    import orb_slam2_2021_b200 as pkg
+    from . import frames_util as U
+
+    cur, last, has, world, pdesc, obs = _scenario(seed, tz, ur, n_last, clones)
+    m = pkg.Matcher(checkOrientation=ori)
+    for th in (7, 15):
+        b, nb = R.search_by_projection(U.view(O.FrameView, cur), U.view(O.FrameView, last), has, world, pdesc, obs, th, mono, ori)
+        g, ng = m.SearchByProjection(U.view(pkg.FrameView, cur), U.view(pkg.FrameView, last), pkg.MapPointView(has, world, pdesc, obs), th, mono)
+        assert ng == nb and np.array_equal(g, b), (seed, th, ng, nb)
+
+
+@needs_ref
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,th,ur,occ,n_points,clones", LOCAL_CASES)
+def test_cuda_search_local_points_equals_reference(seed, th, ur, occ, n_points, clones):
+    import orb_slam2_2021_b200 as pkg
+    from . import frames_util as U
+
+    F, occupied, valid, proj, level, vc, pdesc, obs = _local(seed, ur, n_points, clones)
+    occupied = occupied if occ else None
+    m = pkg.Matcher()
+    for ratio in (0.8, 0.6, 10.0):
+        b, nb = R.search_local_points(U.view(O.FrameView, F), occupied, valid, proj, level, vc, pdesc, obs, th, ratio)
+        g, ng = m.SearchLocalPoints(U.view(pkg.FrameView, F), pkg.TrackPointView(valid, proj, level, vc, pdesc, obs), th, occupied, ratio)
+        assert ng == nb and np.array_equal(g, b), (seed, ratio, ng, nb)
