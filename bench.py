@@ -366,7 +366,9 @@ def ours_arm(args, rank, local_rank, world):
                 "api": "orbx_batch_process_async back to back (pinned host images in, pinned host results out, two output sets), one "
                        "orbx_batch_wait after the last step; wall clock around all steps including the drain",
                 "blocking_call": {"value": e2e, "ms_per_step": e2e_ms / args.steps,
-                                  "api": "orbx_batch_process: returns with the step's results in host memory"}},
+                                  "api": "orbx_batch_process: returns with the step's results in host memory"},
+                # rank 0's pinned buffers: NUMA node of its GPU, and whether orbx_host_alloc could place them there
+                "host_numa": dict(zip(("node", "bound"), pkg.host_numa_node()))},
         "gpu_launches": launches_per_step * args.steps,
         "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,

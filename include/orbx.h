@@ -135,9 +135,12 @@ const char* orbx_batch_stage_name(int i);
 int orbx_batch_stage_times(orbx_batch* b, double* ms, int* runs);
 /* Bytes of HBM the engine holds. */
 long long orbx_batch_device_bytes(const orbx_batch* b);
-/* Page-locked host memory for the end-to-end path (cudaHostAlloc / cudaFreeHost). */
+/* Page-locked host memory for the end-to-end path (cudaHostAlloc / cudaFreeHost), placed on the NUMA node of the
+ * current CUDA device when the host allows it (ORBX_NUMA=0: plain allocation). orbx_host_numa_node reports the node the
+ * last allocation aimed at (-1 unknown, -2 none yet) and whether the placement policy was in force. */
 void* orbx_host_alloc(size_t bytes);
 void orbx_host_free(void* p);
+int orbx_host_numa_node(int* bound);
 /* Debug/test taps on frame f, side s (0 left, 1 right): pyramid level, blurred level, FAST candidates
  * of a level in reference order (x,y relative to minBorder; response). */
 int orbx_batch_level_size(const orbx_batch* b, int level, int* rows, int* cols);

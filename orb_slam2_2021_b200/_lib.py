@@ -70,6 +70,7 @@ SIGNATURES = {
     "orbx_batch_stage_times": (_i, [_vp, C.POINTER(C.c_double), _ip]),
     "orbx_host_alloc": (_vp, [_sz]),
     "orbx_host_free": (None, [_vp]),
+    "orbx_host_numa_node": (_i, [_ip]),
     "orbx_batch_level_size": (_i, [_vp, _i, _ip, _ip]),
     "orbx_batch_level": (_i, [_vp, _i, _i, _i, _i, _vp, _sz]),
     "orbx_batch_candidates": (_i, [_vp, _i, _i, _i, _vp, _i, _ip]),

@@ -1,5 +1,7 @@
 // abi.cu — the C-ABI of liborbx.so (declared in include/orbx.h). No CPU fallback anywhere: every
 // compute entry point needs a CUDA device and reports ORBX_ERR_CUDA otherwise.
+#include <cctype>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <memory>
@@ -418,12 +420,90 @@ extern "C" int orbx_batch_stage_times(orbx_batch* b, double* ms, int* runs)
     return ORBX_OK;
 }
 
-// pinned host memory for the end-to-end path
+// pinned host memory for the end-to-end path, placed on the NUMA node the current device hangs off: with one process per
+// GPU on a two-socket host, pages first touched on the far socket make every H2D/D2H cross the socket interconnect.
+// The node comes from sysfs (the device's PCI function); the placement is a PREFERRED memory policy of the calling
+// thread held only around the allocation (the driver populates and pins the pages inside cudaHostAlloc). Where the
+// policy call is not permitted (seccomp) the allocation runs on one of the node's cores instead (local allocation is the
+// default policy); where the node is unknown the allocation is the plain one. ORBX_NUMA=0 disables.
+#include <sched.h>
+#include <sys/syscall.h>
+#include <unistd.h>
+static int g_numaNode = -2;   // node of the last orbx_host_alloc: -2 not tried, -1 unknown/unavailable
+static int g_numaBound = 0;   // 1: the last allocation ran under the policy, 2: on the node's cores, 0: plain
+
+static int device_numa_node()
+{
+    int dev = 0;
+    char bus[32] = {0};
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetPCIBusId(bus, sizeof bus, dev) != cudaSuccess) { cudaGetLastError(); return -1; }
+    for (char* c = bus; *c; ++c) *c = (char)tolower(*c);
+    const std::string path = std::string("/sys/bus/pci/devices/") + bus + "/numa_node";
+    FILE* f = fopen(path.c_str(), "r");
+    if (!f) return -1;
+    int node = -1;
+    if (fscanf(f, "%d", &node) != 1) node = -1;
+    fclose(f);
+    return node;
+}
+
+static long set_policy(int mode, const unsigned long* mask, unsigned long maxnode)
+{
+#ifdef SYS_set_mempolicy
+    return syscall(SYS_set_mempolicy, mode, mask, maxnode);
+#else
+    return -1;
+#endif
+}
+
+// "0-13,56-69" -> cpu set
+static bool node_cpus(int node, cpu_set_t* set)
+{
+    const std::string path = "/sys/devices/system/node/node" + std::to_string(node) + "/cpulist";
+    FILE* f = fopen(path.c_str(), "r");
+    if (!f) return false;
+    CPU_ZERO(set);
+    int a, b, n = 0;
+    while (fscanf(f, "%d", &a) == 1) {
+        b = a;
+        int c = fgetc(f);
+        if (c == '-') { if (fscanf(f, "%d", &b) != 1) break; c = fgetc(f); }
+        for (int i = a; i <= b && i < CPU_SETSIZE; ++i) { CPU_SET(i, set); ++n; }
+        if (c != ',') break;
+    }
+    fclose(f);
+    return n > 0;
+}
+
 extern "C" void* orbx_host_alloc(size_t bytes)
 {
+    const char* env = getenv("ORBX_NUMA");
+    const int node = (env && atoi(env) == 0) ? -1 : device_numa_node();
+    unsigned long mask[16] = {0};  // up to 1024 nodes
+    bool bound = false;
+    if (node >= 0 && node < 1024) {
+        mask[node / (8 * sizeof(unsigned long))] = 1ul << (node % (8 * sizeof(unsigned long)));
+        bound = set_policy(/*MPOL_PREFERRED*/ 1, mask, 1024) == 0;
+    }
+    // no policy call on this host: run the allocation on one of the node's cores instead (default policy = local node)
+    cpu_set_t old, local;
+    bool moved = false;
+    if (node >= 0 && !bound && sched_getaffinity(0, sizeof old, &old) == 0 && node_cpus(node, &local))
+        moved = sched_setaffinity(0, sizeof local, &local) == 0;
     void* p = nullptr;
-    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { g_err = "cudaHostAlloc failed"; cudaGetLastError(); return nullptr; }
+    const cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocDefault);
+    if (bound) set_policy(/*MPOL_DEFAULT*/ 0, nullptr, 0);
+    if (moved) sched_setaffinity(0, sizeof old, &old);
+    g_numaNode = node;
+    g_numaBound = bound ? 1 : moved ? 2 : 0;
+    if (e != cudaSuccess) { g_err = "cudaHostAlloc failed"; cudaGetLastError(); return nullptr; }
     return p;
+}
+// node of the device seen by the last orbx_host_alloc (-1 unknown, -2 no allocation yet); *bound = the policy was applied
+extern "C" int orbx_host_numa_node(int* bound)
+{
+    if (bound) *bound = g_numaBound;
+    return g_numaNode;
 }
 extern "C" void orbx_host_free(void* p) { if (p) cudaFreeHost(p); }
 

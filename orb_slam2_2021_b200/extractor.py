@@ -114,8 +114,17 @@ def compute_stereo_matches(extractor_left, extractor_right, keys_left, desc_left
     return ur, dp
 
 
+def host_numa_node():
+    """(node, bound) of the last orbx_host_alloc: the NUMA node of the CUDA device it aimed at (-1 unknown, -2 no
+    allocation yet) and how it was placed (1 memory policy, 2 allocated from one of the node's cores, 0 plain)."""
+    bound = C.c_int(0)
+    node = lib().orbx_host_numa_node(C.byref(bound))
+    return int(node), int(bound.value)
+
+
 class PinnedArray:
-    """numpy view over page-locked host memory from orbx_host_alloc (for end-to-end transfers)."""
+    """numpy view over page-locked host memory from orbx_host_alloc (for end-to-end transfers); the pages sit on the
+    NUMA node of the current CUDA device where the host permits (see include/orbx.h)."""
 
     def __init__(self, shape, dtype):
         self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize

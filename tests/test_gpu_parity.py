@@ -410,3 +410,19 @@ def test_scale_factor_above_two_is_rejected():
     with pytest.raises(pkg.OrbxError) as ei:
         pkg.ORBextractor(1000, 2.5, 4, 20, 7)
     assert ei.value.code == pkg._lib.ERR_ARG
+
+
+@pytest.mark.gpu
+def test_pinned_allocation_reports_its_numa_placement(monkeypatch):
+    """orbx_host_alloc places pinned buffers on the device's NUMA node where the host says which one that is; the
+    buffer is usable either way, and ORBX_NUMA=0 switches the placement off."""
+    a = pkg.PinnedArray((1 << 20,), np.uint8)
+    a.array[...] = 7
+    node, how = pkg.host_numa_node()
+    assert node >= -1 and how in (0, 1, 2)
+    assert (how == 0) == (node < 0) or how == 0  # no node -> plain allocation; a known node may still fall back to plain
+    assert int(a.array.sum()) == 7 << 20
+    monkeypatch.setenv("ORBX_NUMA", "0")
+    b = pkg.PinnedArray((4096,), np.uint8)
+    b.array[...] = 1
+    assert pkg.host_numa_node() == (-1, 0)
