@@ -439,9 +439,9 @@ void Engine::launchStereo(int f0, int nFrames, float mbf, float mb, cudaStream_t
     orbx_launch_stereo(p, p, sp, s);
 }
 
-// Device-resident run of a whole batch as interleaved chunks on the two compute streams: the low-occupancy stages of
+// Device-resident run of a whole batch as interleaved chunks on the compute streams (two; ORBX_RUN_STREAMS up to four): the low-occupancy stages of
 // one chunk (quadtree, stereo search, top pyramid levels) fill the issue slots the wide stages of the other chunk leave
-// idle. `stream` forks to `stream2` and joins it again, so callers keep ordering and timing on `stream` alone.
+// idle. `stream` forks to the other streams and joins them again, so callers keep ordering and timing on `stream` alone.
 int Engine::runBatch(int nFrames, float mbf, float mb, int nChunks, std::string& err)
 {
     const int per = stereo ? 2 : 1;
@@ -452,24 +452,30 @@ int Engine::runBatch(int nFrames, float mbf, float mb, int nChunks, std::string&
         return stereo ? runStereo(nFrames, mbf, mb, err) : ORBX_OK;
     }
     TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
-    while ((int)chunkEvents.size() < 2) {
+    static const int envStreams = [] { const char* e = getenv("ORBX_RUN_STREAMS"); return e ? atoi(e) : 0; }();
+    const int nStreams = std::min(std::max(envStreams > 0 ? envStreams : 2, 2), std::min(4, nChunks));
+    cudaStream_t pool[4] = {stream, stream2, stream3, stream4};
+    while ((int)chunkEvents.size() < 4) {
         cudaEvent_t e;
         TRY(orbx_check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate", err));
         chunkEvents.push_back(e);
     }
     TRY(orbx_check(cudaEventRecord(chunkEvents[0], stream), "event", err));
-    TRY(orbx_check(cudaStreamWaitEvent(stream2, chunkEvents[0], 0), "wait", err));
+    for (int i = 1; i < nStreams; ++i) TRY(orbx_check(cudaStreamWaitEvent(pool[i], chunkEvents[0], 0), "wait", err));
     const int chunkFrames = (nFrames + nChunks - 1) / nChunks;
     for (int c = 0, f0 = 0; f0 < nFrames; ++c, f0 += chunkFrames) {
         const int n = std::min(chunkFrames, nFrames - f0);
-        cudaStream_t cs = (c & 1) ? stream2 : stream;
+        cudaStream_t cs = pool[c % nStreams];
         launchExtract(slice(per * f0, per * n), cs);
         if (stereo) launchStereo(f0, n, mbf, mb, cs);
     }
     lastRunChunks = (nFrames + chunkFrames - 1) / chunkFrames;
     TRY(orbx_check(cudaGetLastError(), "batch launch", err));
-    TRY(orbx_check(cudaEventRecord(chunkEvents[1], stream2), "event", err));
-    return orbx_check(cudaStreamWaitEvent(stream, chunkEvents[1], 0), "wait", err);
+    for (int i = 1; i < nStreams; ++i) {
+        TRY(orbx_check(cudaEventRecord(chunkEvents[i], pool[i]), "event", err));
+        TRY(orbx_check(cudaStreamWaitEvent(stream, chunkEvents[i], 0), "wait", err));
+    }
+    return ORBX_OK;
 }
 
 // Chunked end-to-end pipeline: chunk c's images go up on `upStream` while chunk c-1 computes on `stream` and chunk
