@@ -43,7 +43,7 @@ struct __align__(8) OrbxCell {  // 8 bytes, loaded as one 64-bit word
 
 
 // Corner strengths of two horizontally adjacent pixels from the 17 u16x2 vectors cc (centre pair) and d[0..15] (ring pairs).
-__device__ __forceinline__ void fast_network2(uint32_t cc, const uint32_t (&d)[16], int& m0, int& m1)
+__device__ __forceinline__ uint32_t fast_network2(uint32_t cc, const uint32_t (&d)[16])
 {
     // the network runs on the raw ring values (min and max commute with subtracting the centre): no per-value arithmetic
     // Arcs k and k+1 (k even) share the 8 values d[k+1..k+8]: max(min arc k, min arc k+1) = min(min8, max(d[k], d[k+9])).
@@ -71,17 +71,20 @@ __device__ __forceinline__ void fast_network2(uint32_t cc, const uint32_t (&d)[1
     }
     uint32_t br = __vimax3_u16x2(__vimax3_u16x2(tl[0], tl[1], tl[2]), __vimax3_u16x2(tl[3], tl[4], tl[5]), __vimax3_u16x2(tl[6], tl[7], tl[7]));
     uint32_t dk = __vimin3_u16x2(__vimin3_u16x2(th[0], th[1], th[2]), __vimin3_u16x2(th[3], th[4], th[5]), __vimin3_u16x2(th[6], th[7], th[7]));
-    // strength = max(brightest arc minimum - centre, centre - darkest arc maximum), per lane
-    const int c0 = (int)(cc & 0xFFFFu), c1 = (int)(cc >> 16);
-    m0 = max((int)(br & 0xFFFFu) - c0, c0 - (int)(dk & 0xFFFFu));
-    m1 = max((int)(br >> 16) - c1, c1 - (int)(dk >> 16));
+    // strength = max(brightest arc minimum - centre, centre - darkest arc maximum, 0), per half and still packed: clamping
+    // the two extremes at the centre first keeps both differences non-negative, so the 32-bit subtractions cannot borrow
+    // across the halves (a negative strength is "no corner" at any threshold, like 0)
+    br = __vimax3_u16x2(br, cc, cc);
+    dk = __vimin3_u16x2(dk, cc, cc);
+    const uint32_t up = br - cc, dn = cc - dk;
+    return __vimax3_u16x2(up, dn, dn);
 }
 
 // The 17 vectors come straight from the raw tile (no widened copy of the ROI: building one cost more instructions and 7 KB
 // of shared memory per cell than it saved here). t points at pixel 0 of the pair, an EVEN byte address: pairs at even dx are
 // one aligned 16-bit load + PRMT, pairs at odd dx two byte loads + PRMT. BW = row stride of the tile.
 template <int BW>
-__device__ __forceinline__ void fast_strength2_raw(const uint8_t* t, int& m0, int& m1)
+__device__ __forceinline__ uint32_t fast_strength2_raw(const uint8_t* t)
 {
 #define RING_E(dx, dy) __byte_perm((uint32_t)*reinterpret_cast<const uint16_t*>(t + (dy) * BW + (dx)), 0, 0x4140)
 #define RING_O(dx, dy) __byte_perm((uint32_t)t[(dy) * BW + (dx)], (uint32_t)t[(dy) * BW + (dx) + 1], 0x5410)
@@ -93,13 +96,36 @@ __device__ __forceinline__ void fast_strength2_raw(const uint8_t* t, int& m0, in
     d[12] = RING_O(-3, 0);  d[13] = RING_O(-3, 1);  d[14] = RING_E(-2, 2);  d[15] = RING_O(-1, 3);
 #undef RING_E
 #undef RING_O
-    fast_network2(cc, d, m0, m1);
+    return fast_network2(cc, d);
+}
+
+// Pass-1 test of the 4 pixels of one tile word: bit 7 of byte i of the result is set if pixel i can be a corner at the
+// threshold behind K (see the kernel): (|d0|>t or |d8|>t) and (|d4|>t or |d12|>t) on the compass points
+template <int BW>
+__device__ __forceinline__ uint32_t fast_pretest4(const uint32_t* tw, uint32_t K)
+{
+    const uint32_t w = tw[0], wn = tw[1], wp = tw[-1];
+    const uint32_t up = tw[-3 * (BW / 4)], dn = tw[3 * (BW / 4)];
+    const uint32_t lf = __funnelshift_r(wp, w, 8), rt = __funnelshift_r(w, wn, 24);  // columns -3 / +3
+    const uint32_t a0 = __vabsdiffu4(dn, w), a8 = __vabsdiffu4(up, w), a4 = __vabsdiffu4(rt, w), a12 = __vabsdiffu4(lf, w);
+    const uint32_t f0 = ((a0 & 0x7F7F7F7Fu) + K) | a0, f8 = ((a8 & 0x7F7F7F7Fu) + K) | a8;
+    const uint32_t f4 = ((a4 & 0x7F7F7F7Fu) + K) | a4, f12 = ((a12 & 0x7F7F7F7Fu) + K) | a12;
+    return (f0 | f8) & (f4 | f12);
+}
+
+// shared-memory counter bump by ONE lane on behalf of its warp (the counts are already summed by ballot / scan): as inline
+// PTX, or the compiler wraps its own warp aggregation (votes, a second scan) around the single-lane atomicAdd
+__device__ __forceinline__ int smem_add(int* p, int v)
+{
+    int old;
+    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(orbx_smem_addr(p)), "r"(v) : "memory");
+    return old;
 }
 
 // c_recip[n] = ceil(65536 / n): floor(t / n) = (t * c_recip[n]) >> 16 exactly while t * n < 65536 (here t <= 128, n <= 31)
 __constant__ uint32_t c_recip[32] = {0, 65536, 32768, 21846, 16384, 13108, 10923, 9363, 8192, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4096, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115};
 
-template <int SA, int FAST_THREADS>
+template <int SA, int FAST_THREADS>  // FAST_THREADS = 64 (or 32): the two-ended list below is for at most two warps
 __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap)
 {
     // TMA box width in bytes = row stride of the tile: 20 / 28 words, so that 8 consecutive rows start in 8 different
@@ -107,7 +133,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     constexpr int BW = SA == 48 ? 80 : 112;
     extern __shared__ __align__(128) uint8_t fast_smem[];
     __shared__ __align__(8) uint64_t bar;
-    __shared__ int listCnt, taskCnt, nzCnt;
+    __shared__ int listCnt, taskCnt, nzCntW[2];
 
     uint8_t* T = fast_smem;                                                     // raw box [rhMax][BW]
     // strength map, row stride SA: interior pixel (ix,iy) at [iy+1][A-column + SD], zero elsewhere. "A-column" = level column
@@ -129,7 +155,6 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     if (threadIdx.x == 0) {
         listCnt = 0;
         taskCnt = 0;
-        nzCnt = 0;
         orbx_mbar_init(&bar, 1);
         orbx_fence_mbar_init();
         orbx_mbar_expect_tx(&bar, rhMax * BW);
@@ -165,6 +190,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     const bool pact = pyq < pStep;
     // pair q (A-columns 4j+2q, +1) holds an interior pixel iff 4j+2q+1 >= ca0 and 4j+2q < ca0+iw
     const unsigned vmask = !pact ? 0u : ((4 * pj + 1 >= ca0 && 4 * pj < ca0 + iw) ? 1u : 0u) | ((4 * pj + 3 >= ca0 && 4 * pj + 2 < ca0 + iw) ? 2u : 0u);
+    const uint32_t vmaskX = ((vmask & 1u) ? 0x000000FFu : 0u) | ((vmask & 2u) ? 0x00FF0000u : 0u);
     const uint32_t* ptw0 = tw0 + (pyq + 3) * (BW / 4) + pj;
     int thr = tini;
 #pragma unroll 1
@@ -172,7 +198,7 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
         // ---- pass 1: a cheap NECESSARY test for "corner at thr" on the raw words: any 9 contiguous ring positions contain
         // two ADJACENT compass points (0,4,8,12), so a corner needs (|d0|>t or |d8|>t) and (|d4|>t or |d12|>t). Four
         // VABSDIFF4 + a SWAR byte compare test 4 pixels at once. A thread collects 2 bits per step in a register and appends
-        // its surviving pixel PAIRS once per 16 steps: one warp scan + one shared atomic per warp (pairs are aligned to even
+        // its surviving pixel PAIRS once per 8 steps: one warp scan + one shared atomic per warp (pairs are aligned to even
         // tile columns; the order of the list does not matter).
         {
             // bit 7 of each byte of f(x) = ((x & 0x7F..) + K) | x is set iff x > min(thr, 127): exact below 127, still
@@ -181,24 +207,27 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
             const uint32_t* tw = ptw0;
             uint32_t code0 = (uint32_t)(pyq * 256 + 2 * pj);  // list entry of pair 0 at the first step of the current group
 #pragma unroll 1
-            for (int g0 = 0; g0 < ih; g0 += 16 * pStep) {   // groups of 16 steps (uniform)
-                uint32_t bits = 0;
-                int sh = 0;
+            for (int g0 = 0; g0 < ih; g0 += 8 * pStep) {   // groups of 8 steps (uniform)
+                // flags of a step enter at bits 7 (pair 0) and 23 (pair 1) and move down one bit per step: after the
+                // group's S steps, step s sits at bits 8-S+s and 24-S+s
+                uint32_t acc = 0;
+                int S = 0;
+                const int lim = min(ih, g0 + 8 * pStep);
+                // two steps per trip (uniform trip count; an odd last step leaves its partner empty): ten loads in flight
 #pragma unroll 1
-                for (int y0s = g0; y0s < min(ih, g0 + 16 * pStep); y0s += pStep, sh += 2) {  // uniform trip count
-                    if (vmask && y0s + pyq < ih) {
-                        const uint32_t w = tw[0], wn = tw[1], wp = tw[-1];
-                        const uint32_t up = tw[-3 * (BW / 4)], dn = tw[3 * (BW / 4)];
-                        const uint32_t lf = __funnelshift_r(wp, w, 8), rt = __funnelshift_r(w, wn, 24);  // columns -3 / +3
-                        const uint32_t a0 = __vabsdiffu4(dn, w), a8 = __vabsdiffu4(up, w), a4 = __vabsdiffu4(rt, w), a12 = __vabsdiffu4(lf, w);
-                        const uint32_t f0 = ((a0 & 0x7F7F7F7Fu) + K) | a0, f8 = ((a8 & 0x7F7F7F7Fu) + K) | a8;
-                        const uint32_t f4 = ((a4 & 0x7F7F7F7Fu) + K) | a4, f12 = ((a12 & 0x7F7F7F7Fu) + K) | a12;
-                        const uint32_t m = (f0 | f8) & (f4 | f12);
-                        const uint32_t kk = ((m & 0x00008080u) ? 1u : 0u) | ((m & 0x80800000u) ? 2u : 0u);
-                        bits |= (kk & vmask) << sh;
+                for (int y0s = g0; y0s < lim; y0s += 2 * pStep, S += 2) {
+                    acc >>= 2;
+                    const bool p0 = vmask && y0s + pyq < ih, p1 = vmask && y0s + pStep + pyq < ih;
+                    if (p0) {
+                        const uint32_t* tw1 = p1 ? tw + pStep * (BW / 4) : tw;  // (second step off: same words again, result dropped)
+                        const uint32_t m0 = fast_pretest4<BW>(tw, K), m1 = fast_pretest4<BW>(tw1, K);
+                        // bits 6 / 22: pixels 0|1 and 2|3 of the first step's word, bits 7 / 23: of the second step's
+                        const uint32_t u0 = ((m0 | (m0 >> 8)) >> 1) & 0x00400040u, u1 = (m1 | (m1 >> 8)) & 0x00800080u;
+                        acc |= u0 | (p1 ? u1 : 0u);
                     }
-                    tw += pStep * (BW / 4);
+                    tw += 2 * pStep * (BW / 4);
                 }
+                uint32_t bits = (acc >> (8 - S)) & vmaskX;  // step s at bit s (pair 0) and bit 16+s (pair 1)
                 // append this thread's pairs of the group
                 int incl = __popc(bits);
                 const int mine = incl;
@@ -208,22 +237,24 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
                     if (lane >= d) incl += v;
                 }
                 int base = 0;
-                if (lane == 31) base = atomicAdd(&taskCnt, incl);
+                if (lane == 31) base = smem_add(&taskCnt, incl);
                 uint16_t* dst = tasks + (__shfl_sync(0xffffffffu, base, 31) + incl - mine);
                 uint32_t c = code0;
                 while (bits) {
                     if (bits & 1) *dst++ = (uint16_t)c;
-                    if (bits & 2) *dst++ = (uint16_t)(c + 1);
-                    bits >>= 2;
+                    if (bits & 0x10000u) *dst++ = (uint16_t)(c + 1);
+                    bits = (bits >> 1) & 0x7FFF7FFFu;
                     c += (uint32_t)pStep << 8;
                 }
-                code0 += (uint32_t)(16 * pStep) << 8;
+                code0 += (uint32_t)(8 * pStep) << 8;
             }
         }
         __syncthreads();  // task list complete
         // ---- pass 2: the min/max network on the surviving pairs (results go to the map by position)
         const int ntAll = taskCnt;
+        const uint32_t thr2 = (uint32_t)thr * 0x10001u;
         {
+            int nzMine = 0;  // warp-uniform
 #pragma unroll 1
             for (int g0 = warp * 32; g0 < ntAll; g0 += FAST_THREADS) {
                 const int g = g0 + lane;
@@ -232,31 +263,35 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
                 if (g < ntAll) {
                     task = tasks[g];
                     const int y = task >> 8, c = 2 * (task & 255);
-                    int m0, m1;
-                    fast_strength2_raw<BW>(reinterpret_cast<const uint8_t*>(tw0) + (y + 3) * BW + c, m0, m1);
+                    const uint32_t mp = fast_strength2_raw<BW>(reinterpret_cast<const uint8_t*>(tw0) + (y + 3) * BW + c);
+                    // the map holds m - thr for m > thr and 0 otherwise (per half: max(m, thr) - thr cannot borrow). The NMS
+                    // only compares strengths of one attempt with each other, so the common offset does not matter; the
+                    // kept maxima get it back.
                     const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
-                    m0 = (m0 > thr && ix >= 0) ? m0 : 0;
-                    m1 = (m1 > thr && ix + 1 < iw) ? m1 : 0;
-                    hit = (m0 | m1) != 0;
-                    if (hit) *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + c + SD) = (uint32_t)m0 | ((uint32_t)m1 << 16);  // map is pre-zeroed
+                    const uint32_t inside = (ix >= 0 ? 0x0000FFFFu : 0u) | (ix + 1 < iw ? 0xFFFF0000u : 0u);
+                    const uint32_t ms = (__vimax3_u16x2(mp, thr2, thr2) - thr2) & inside;
+                    hit = ms != 0;
+                    if (hit) *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + c + SD) = ms;  // map is pre-zeroed
                 }
+                // the list of non-zero pairs is filled from both ends, warp 0 upwards and warp 1 downwards (together they hold
+                // at most listCap pairs): the fill counts stay in registers and no atomic is needed
                 const unsigned bh = __ballot_sync(0xffffffffu, hit);
-                if (bh) {  // uniform: one shared atomic per warp step
-                    int base = 0;
-                    if (lane == 0) base = atomicAdd(&nzCnt, __popc(bh));
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (hit) nz[base + __popc(bh & lt)] = (uint16_t)task;
+                if (hit) {
+                    const int idx = nzMine + __popc(bh & lt);
+                    nz[warp == 0 ? idx : listCap - 1 - idx] = (uint16_t)task;
                 }
+                nzMine += __popc(bh);
             }
+            if (lane == 0) nzCntW[warp] = nzMine;
         }
         __syncthreads();
 
         // ---- NMS over the pairs that hold a non-zero strength: strict maximum over the 8 neighbours in the
         // strength map. Maxima go to a CTA list kept[] = key | m << 16, key = y*64 + x (interior coords).
-        const int nzAll = nzCnt;
+        const int nz0 = nzCntW[0], nzAll = nz0 + (FAST_THREADS > 32 ? nzCntW[1] : 0);
 #pragma unroll 1
         for (int g = threadIdx.x; g < nzAll; g += FAST_THREADS) {
-            const int task = nz[g], y = task >> 8, cc = 2 * (task & 255);
+            const int task = nz[g < nz0 ? g : listCap - 1 - (g - nz0)], y = task >> 8, cc = 2 * (task & 255);
             const uint16_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair, word aligned
             const uint32_t mm = *reinterpret_cast<const uint32_t*>(c);
             const uint32_t u0 = *reinterpret_cast<const uint32_t*>(c - SA - 2), u1 = *reinterpret_cast<const uint32_t*>(c - SA), u2 = *reinterpret_cast<const uint32_t*>(c - SA + 2);
@@ -270,13 +305,13 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
             const int n0 = max(max((int)(cm0 >> 16), (int)(cm1 >> 16)), (int)(ud & 0xFFFFu));
             const int n1 = max(max((int)(cm1 & 0xFFFFu), (int)(cm2 & 0xFFFFu)), (int)(ud >> 16));
             const int ix = cc - ca0;
-            if (m0 > n0) kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + ix) | ((uint32_t)m0 << 16);
-            if (m1 > n1) kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + ix + 1) | ((uint32_t)m1 << 16);
+            if (m0 > n0) kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + ix) | ((uint32_t)(m0 + thr) << 16);
+            if (m1 > n1) kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + ix + 1) | ((uint32_t)(m1 + thr) << 16);
         }
         __syncthreads();  // publishes kept[] and listCnt
         if (listCnt > 0 || attempt == 1 || tmin >= thr) break;
         thr = tmin;       // :814 FAST(iniTh) came back empty: once more with minTh
-        if (threadIdx.x == 0) taskCnt = nzCnt = 0;  // (last reads before the barriers that ended pass 2 / the NMS)
+        if (threadIdx.x == 0) taskCnt = 0;  // (last read before the barrier that ended pass 2)
         __syncthreads();
     }
 
@@ -323,7 +358,7 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     if (!nt) {
         const char* e = getenv("ORBX_FAST_THREADS");
         nt = e ? atoi(e) : 64;
-        if (nt != 32 && nt != 64 && nt != 128) nt = 64;
+        if (nt != 32 && nt != 64) nt = 64;
     }
     const size_t smem = (size_t)((rhMax * boxW + 127) & ~127) + (size_t)(rhMax - 4) * sa * 2 + (size_t)2 * listCap * 2;
 #define FAST_LAUNCH(SA_, NT_)                                                                                                    \
@@ -333,9 +368,9 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
         orbx_fast_kernel<SA_, NT_><<<grid, NT_, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax, listCap); \
     }
     if (sa == 48) {
-        if (nt == 128) FAST_LAUNCH(48, 128) else if (nt == 64) FAST_LAUNCH(48, 64) else FAST_LAUNCH(48, 32)
+        if (nt == 64) FAST_LAUNCH(48, 64) else FAST_LAUNCH(48, 32)
     } else {
-        if (nt == 128) FAST_LAUNCH(80, 128) else if (nt == 64) FAST_LAUNCH(80, 64) else FAST_LAUNCH(80, 32)
+        if (nt == 64) FAST_LAUNCH(80, 64) else FAST_LAUNCH(80, 32)
     }
 #undef FAST_LAUNCH
 }
