@@ -330,6 +330,190 @@ __global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, c
     }
 }
 
+// ---- one WARP per cell, CELLS cells per CTA --------------------------------------------------------------------------
+// Same passes as orbx_fast_kernel, but a cell belongs to one warp: the fixed work per (warp, cell) — prologue, thread
+// mapping, list flush, emission, ~300 of the ~1060 warp instructions a warp spent per cell — is paid once per cell instead
+// of twice, every CTA barrier becomes a __syncwarp, and the list counters are warp-uniform registers (no shared atomics).
+// CELLS warps share a CTA only for occupancy (a one-warp CTA caps the SM at 32 warps, less with 8.5 KB of shared memory
+// each); they never talk to each other.
+template <int SA, int CELLS>
+__global__ void __launch_bounds__(CELLS * 32) orbx_fast_warp_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap,
+                                                                    int sliceBytes)
+{
+    constexpr int BW = SA == 48 ? 80 : 112;
+    extern __shared__ __align__(128) uint8_t fast_smem[];
+    __shared__ __align__(8) uint64_t bars[CELLS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cellId = blockIdx.x * CELLS + warp, img = blockIdx.y;
+    if (cellId >= p.cellsTotal) return;
+    uint8_t* T = fast_smem + (size_t)warp * sliceBytes;  // raw box [rhMax][BW]
+    uint16_t* smap = reinterpret_cast<uint16_t*>(T + ((rhMax * BW + 127) & ~127));
+    uint16_t* tasks = smap + (rhMax - 4) * SA;  // pass-1 survivors (pixel pairs)
+    // pairs with a non-zero strength: written over the task list while pass 2 consumes it (entry k of nz is written in the
+    // trip that read tasks[32*(trip)..], and k never runs ahead of what has been read)
+    uint16_t* nz = tasks;
+    uint64_t* bar = bars + warp;
+
+    const OrbxCell cell = cells[cellId];
+    const OrbxLevel& L = p.lv[cell.level];
+    const int iw = cell.rw - 6, ih = cell.rh - 6;  // interior = detection domain of cv::FAST
+    int* cntOut = p.cellCnt + (size_t)img * p.cellsTotal + cellId;
+    if (iw <= 0 || ih <= 0) {
+        if (lane == 0) *cntOut = 0;
+        return;
+    }
+    if (lane == 0) {
+        orbx_mbar_init(bar, 1);
+        orbx_fence_mbar_init();
+        orbx_mbar_expect_tx(bar, rhMax * BW);
+        orbx_tma_load_3d(T, maps + cell.level, cell.x0 & ~15, cell.y0, img + p.imgBase, bar);
+    }
+    {
+        uint4* z = reinterpret_cast<uint4*>(smap);
+        const int nzero = (ih + 2) * (SA / 8);
+        for (int i = lane; i < nzero; i += 32) z[i] = make_uint4(0, 0, 0, 0);
+    }
+    __syncwarp();  // barrier initialised (and armed) before anybody polls it
+    orbx_mbar_wait(bar, 0);
+
+    const int tmin = p.minTh, tini = p.iniTh;
+    const int o = cell.x0 & 3;
+    const int ca0 = o + 3;                   // A-column of interior pixel 0
+    const int SD = 2 + ((o + 1) & 1) - ca0;  // strength-map column = A-column + SD
+    const uint32_t* tw0 = reinterpret_cast<const uint32_t*>(T) + ((cell.x0 & 15) >> 2);
+    uint32_t* kept = reinterpret_cast<uint32_t*>(T);  // NMS maxima: key | m << 16 (the raw tile is dead by then)
+    const unsigned lt = (1u << lane) - 1;
+    // pre-test mapping: fixed interior word column per lane, 32/nwi interior rows per step
+    const int jmin = ca0 >> 2, nwi = ((ca0 + iw - 1) >> 2) - jmin + 1;
+    const uint32_t rcpi = c_recip[nwi];
+    const int pStep = (int)((32u * rcpi) >> 16);
+    const int pyq = (int)(((uint32_t)lane * rcpi) >> 16);
+    const int pj = jmin + lane - pyq * nwi;
+    const unsigned vmask = pyq >= pStep ? 0u : ((4 * pj + 1 >= ca0 && 4 * pj < ca0 + iw) ? 1u : 0u) | ((4 * pj + 3 >= ca0 && 4 * pj + 2 < ca0 + iw) ? 2u : 0u);
+    const uint32_t vmaskX = ((vmask & 1u) ? 0x0000FFFFu : 0u) | ((vmask & 2u) ? 0xFFFF0000u : 0u);
+    const uint32_t* ptw0 = tw0 + (pyq + 3) * (BW / 4) + pj;
+    int thr = tini, nkept = 0;
+#pragma unroll 1
+    for (int attempt = 0;; ++attempt) {
+        // ---- pass 1 (see orbx_fast_kernel): flags of a step enter at bits 15 / 31 and move down, 16 steps per flush
+        int ntAll = 0;
+        {
+            const uint32_t K = 0x01010101u * (uint32_t)(0x7F - min(thr, 0x7F));
+            const uint32_t* tw = ptw0;
+            uint32_t code0 = (uint32_t)(pyq * 256 + 2 * pj);
+#pragma unroll 1
+            for (int g0 = 0; g0 < ih; g0 += 16 * pStep) {
+                uint32_t acc = 0;
+                int S = 0;
+                const int lim = min(ih, g0 + 16 * pStep);
+#pragma unroll 1
+                for (int y0s = g0; y0s < lim; y0s += 2 * pStep, S += 2) {
+                    acc >>= 2;
+                    const bool p0 = vmask && y0s + pyq < ih, p1 = vmask && y0s + pStep + pyq < ih;
+                    if (p0) {
+                        const uint32_t* tw1 = p1 ? tw + pStep * (BW / 4) : tw;
+                        const uint32_t m0 = fast_pretest4<BW>(tw, K), m1 = fast_pretest4<BW>(tw1, K);
+                        const uint32_t u0 = ((m0 | (m0 << 8)) >> 1) & 0x40004000u, u1 = (m1 | (m1 << 8)) & 0x80008000u;
+                        acc |= u0 | (p1 ? u1 : 0u);
+                    }
+                    tw += 2 * pStep * (BW / 4);
+                }
+                uint32_t bits = (acc >> (16 - S)) & vmaskX;  // step s at bit s (pair 0) and bit 16+s (pair 1)
+                int incl = __popc(bits);
+                const int mine = incl;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += v;
+                }
+                uint16_t* dst = tasks + (ntAll + incl - mine);
+                ntAll += __shfl_sync(0xffffffffu, incl, 31);
+                uint32_t c = code0;
+                while (bits) {
+                    if (bits & 1) *dst++ = (uint16_t)c;
+                    if (bits & 0x10000u) *dst++ = (uint16_t)(c + 1);
+                    bits = (bits >> 1) & 0x7FFF7FFFu;
+                    c += (uint32_t)pStep << 8;
+                }
+                code0 += (uint32_t)(16 * pStep) << 8;
+            }
+        }
+        __syncwarp();  // task list complete
+        // ---- pass 2: the min/max network on the surviving pairs
+        const uint32_t thr2 = (uint32_t)thr * 0x10001u;
+        int nzAll = 0;
+#pragma unroll 1
+        for (int g0 = 0; g0 < ntAll; g0 += 32) {
+            const int g = g0 + lane;
+            bool hit = false;
+            int task = 0;
+            if (g < ntAll) {
+                task = tasks[g];
+                const int y = task >> 8, c = 2 * (task & 255);
+                const uint32_t mp = fast_strength2_raw<BW>(reinterpret_cast<const uint8_t*>(tw0) + (y + 3) * BW + c);
+                const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
+                const uint32_t inside = (ix >= 0 ? 0x0000FFFFu : 0u) | (ix + 1 < iw ? 0xFFFF0000u : 0u);
+                const uint32_t ms = (__vimax3_u16x2(mp, thr2, thr2) - thr2) & inside;  // m - thr per half, 0 = no corner
+                hit = ms != 0;
+                if (hit) *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + c + SD) = ms;  // map is pre-zeroed
+            }
+            const unsigned bh = __ballot_sync(0xffffffffu, hit);
+            if (hit) nz[nzAll + __popc(bh & lt)] = (uint16_t)task;
+            nzAll += __popc(bh);
+        }
+        __syncwarp();  // strength map and list complete; the raw tile is dead from here (kept[] takes its place)
+
+        // ---- NMS over the non-zero pairs: strict maximum over the 8 neighbours in the strength map
+        nkept = 0;
+#pragma unroll 1
+        for (int g0 = 0; g0 < nzAll; g0 += 32) {
+            const int g = g0 + lane;
+            bool k0 = false, k1 = false;
+            uint32_t e0 = 0, e1 = 0;
+            if (g < nzAll) {
+                const int task = nz[g], y = task >> 8, cc = 2 * (task & 255);
+                const uint16_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair, word aligned
+                const uint32_t mm = *reinterpret_cast<const uint32_t*>(c);
+                const uint32_t u0 = *reinterpret_cast<const uint32_t*>(c - SA - 2), u1 = *reinterpret_cast<const uint32_t*>(c - SA), u2 = *reinterpret_cast<const uint32_t*>(c - SA + 2);
+                const uint32_t l0 = *reinterpret_cast<const uint32_t*>(c - 2), l2 = *reinterpret_cast<const uint32_t*>(c + 2);
+                const uint32_t d0 = *reinterpret_cast<const uint32_t*>(c + SA - 2), d1 = *reinterpret_cast<const uint32_t*>(c + SA), d2 = *reinterpret_cast<const uint32_t*>(c + SA + 2);
+                const uint32_t cm0 = __vimax3_u16x2(u0, l0, d0), cm1 = __vimax3_u16x2(u1, mm, d1), cm2 = __vimax3_u16x2(u2, l2, d2);
+                const uint32_t ud = __vimax3_u16x2(u1, d1, d1);
+                const int m0 = mm & 0xFFFFu, m1 = mm >> 16;
+                const int n0 = max(max((int)(cm0 >> 16), (int)(cm1 >> 16)), (int)(ud & 0xFFFFu));
+                const int n1 = max(max((int)(cm1 & 0xFFFFu), (int)(cm2 & 0xFFFFu)), (int)(ud >> 16));
+                const int ix = cc - ca0;
+                k0 = m0 > n0;
+                k1 = m1 > n1;
+                e0 = (uint32_t)(y * 64 + ix) | ((uint32_t)(m0 + thr) << 16);
+                e1 = (uint32_t)(y * 64 + ix + 1) | ((uint32_t)(m1 + thr) << 16);
+            }
+            // (the first trip overwrites the head of the dead tile only after every lane has read its map words: the map
+            // and the lists live behind the tile, so kept[] never aliases what this loop still reads)
+            const unsigned b0 = __ballot_sync(0xffffffffu, k0), b1 = __ballot_sync(0xffffffffu, k1);
+            if (k0) kept[nkept + __popc(b0 & lt)] = e0;
+            if (k1) kept[nkept + __popc(b0) + __popc(b1 & lt)] = e1;
+            nkept += __popc(b0) + __popc(b1);
+        }
+        __syncwarp();  // publishes kept[]
+        if (nkept > 0 || attempt == 1 || tmin >= thr) break;
+        thr = tmin;  // :814 FAST(iniTh) came back empty: once more with minTh
+    }
+
+    // ---- ordered emission: rank of a maximum = number of maxima with a smaller row-major key
+    const uint32_t slot0 = L.slotBase + (uint32_t)(cellId - L.cellBase) * L.slotCap;
+    uint32_t* out = p.cellKp + (size_t)img * p.slotTotal + slot0;
+    if (lane == 0) *cntOut = nkept;
+#pragma unroll 1
+    for (int i = lane; i < nkept; i += 32) {
+        const uint32_t e = kept[i];
+        const int key = e & 0xFFFFu, m = e >> 16;
+        int rank = 0;
+        for (int j = 0; j < nkept; ++j) rank += (int)(kept[j] & 0xFFFFu) < key;
+        out[rank] = (uint32_t)((key & 63) + 3) | ((uint32_t)((key >> 6) + 3) << 8) | ((uint32_t)(m - 1) << 16);
+    }
+}
+
 void orbx_fast_geometry(const OrbxParams& p, int* boxW, int* rhMaxOut)
 {
     // largest ROI over the levels (ROI = cell + 6, src/ORBextractor.cc:797-808)
@@ -361,6 +545,31 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
         if (nt != 32 && nt != 64) nt = 64;
     }
     const size_t smem = (size_t)((rhMax * boxW + 127) & ~127) + (size_t)(rhMax - 4) * sa * 2 + (size_t)2 * listCap * 2;
+    // warp-per-cell kernel: ORBX_FAST_CELLS = cells (warps) per CTA, 0 = the CTA-per-cell kernel
+    static int cellsPerCta = -1;
+    if (cellsPerCta < 0) {
+        const char* e = getenv("ORBX_FAST_CELLS");
+        cellsPerCta = e ? atoi(e) : 2;
+        if (cellsPerCta != 0 && cellsPerCta != 2 && cellsPerCta != 4 && cellsPerCta != 8) cellsPerCta = 2;
+    }
+    if (cellsPerCta > 0) {
+        const int slice = (int)((smem - (size_t)listCap * 2 + 127) & ~(size_t)127);  // one list: the non-zero pairs overwrite the tasks
+        const size_t total = (size_t)slice * cellsPerCta;
+        dim3 wgrid((p.cellsTotal + cellsPerCta - 1) / cellsPerCta, p.imgs);
+#define FAST_WLAUNCH(SA_, C_)                                                                                                   \
+    {                                                                                                                            \
+        if (total > 32 * 1024)                                                                                                   \
+            cudaFuncSetAttribute(orbx_fast_warp_kernel<SA_, C_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)total);       \
+        orbx_fast_warp_kernel<SA_, C_><<<wgrid, C_ * 32, total, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax, listCap, slice); \
+    }
+        if (sa == 48) {
+            if (cellsPerCta == 2) FAST_WLAUNCH(48, 2) else if (cellsPerCta == 4) FAST_WLAUNCH(48, 4) else FAST_WLAUNCH(48, 8)
+        } else {
+            if (cellsPerCta == 2) FAST_WLAUNCH(80, 2) else if (cellsPerCta == 4) FAST_WLAUNCH(80, 4) else FAST_WLAUNCH(80, 8)
+        }
+#undef FAST_WLAUNCH
+        return;
+    }
 #define FAST_LAUNCH(SA_, NT_)                                                                                                    \
     {                                                                                                                            \
         if (smem > 32 * 1024) /* tall cells: static + dynamic may pass 48 KB; per-device attribute, set on every such launch */ \
