@@ -344,8 +344,6 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_warp_kernel(OrbxParams p
     extern __shared__ __align__(128) uint8_t fast_smem[];
     __shared__ __align__(8) uint64_t bars[CELLS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int cellId = blockIdx.x * CELLS + warp, img = blockIdx.y;
-    if (cellId >= p.cellsTotal) return;
     uint8_t* T = fast_smem + (size_t)warp * sliceBytes;  // raw box [rhMax][BW]
     uint16_t* smap = reinterpret_cast<uint16_t*>(T + ((rhMax * BW + 127) & ~127));
     uint16_t* tasks = smap + (rhMax - 4) * SA;  // pass-1 survivors (pixel pairs)
@@ -353,18 +351,29 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_warp_kernel(OrbxParams p
     // trip that read tasks[32*(trip)..], and k never runs ahead of what has been read)
     uint16_t* nz = tasks;
     uint64_t* bar = bars + warp;
-
+    if (lane == 0) {
+        orbx_mbar_init(bar, 1);
+        orbx_fence_mbar_init();
+    }
+    __syncwarp();  // barrier initialised before anybody polls it
+    // long-lived warps: the grid is a small multiple of what the SMs hold and every warp walks over several (image, cell)
+    // pairs — little CTA turnover (a third of the warp slots stood empty with one short-lived CTA per two cells), and
+    // neighbouring warps work on neighbouring cells of the same image (their tiles overlap in L2)
+    const int total = p.cellsTotal * p.imgs;
+    unsigned phase = 0;
+#pragma unroll 1
+    for (int work = blockIdx.x * CELLS + warp; work < total; work += gridDim.x * CELLS) {
+    const int img = work / p.cellsTotal, cellId = work - img * p.cellsTotal;
     const OrbxCell cell = cells[cellId];
     const OrbxLevel& L = p.lv[cell.level];
     const int iw = cell.rw - 6, ih = cell.rh - 6;  // interior = detection domain of cv::FAST
     int* cntOut = p.cellCnt + (size_t)img * p.cellsTotal + cellId;
     if (iw <= 0 || ih <= 0) {
         if (lane == 0) *cntOut = 0;
-        return;
+        continue;
     }
     if (lane == 0) {
-        orbx_mbar_init(bar, 1);
-        orbx_fence_mbar_init();
+        orbx_fence_mbar_init();  // the previous cell's kept[] (generic-proxy writes into the tile) before the TMA write
         orbx_mbar_expect_tx(bar, rhMax * BW);
         orbx_tma_load_3d(T, maps + cell.level, cell.x0 & ~15, cell.y0, img + p.imgBase, bar);
     }
@@ -373,8 +382,9 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_warp_kernel(OrbxParams p
         const int nzero = (ih + 2) * (SA / 8);
         for (int i = lane; i < nzero; i += 32) z[i] = make_uint4(0, 0, 0, 0);
     }
-    __syncwarp();  // barrier initialised (and armed) before anybody polls it
-    orbx_mbar_wait(bar, 0);
+    __syncwarp();
+    orbx_mbar_wait(bar, phase);
+    phase ^= 1;
 
     const int tmin = p.minTh, tini = p.iniTh;
     const int o = cell.x0 & 3;
@@ -512,6 +522,8 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_warp_kernel(OrbxParams p
         for (int j = 0; j < nkept; ++j) rank += (int)(kept[j] & 0xFFFFu) < key;
         out[rank] = (uint32_t)((key & 63) + 3) | ((uint32_t)((key >> 6) + 3) << 8) | ((uint32_t)(m - 1) << 16);
     }
+    __syncwarp();  // every lane is done with kept[] (= the tile) before the next cell's TMA lands in it
+    }
 }
 
 void orbx_fast_geometry(const OrbxParams& p, int* boxW, int* rhMaxOut)
@@ -549,17 +561,35 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     static int cellsPerCta = -1;
     if (cellsPerCta < 0) {
         const char* e = getenv("ORBX_FAST_CELLS");
-        cellsPerCta = e ? atoi(e) : 2;
-        if (cellsPerCta != 0 && cellsPerCta != 2 && cellsPerCta != 4 && cellsPerCta != 8) cellsPerCta = 2;
+        cellsPerCta = e ? atoi(e) : 4;
+        if (cellsPerCta != 0 && cellsPerCta != 2 && cellsPerCta != 4 && cellsPerCta != 8) cellsPerCta = 4;
     }
     if (cellsPerCta > 0) {
         const int slice = (int)((smem - (size_t)listCap * 2 + 127) & ~(size_t)127);  // one list: the non-zero pairs overwrite the tasks
         const size_t total = (size_t)slice * cellsPerCta;
-        dim3 wgrid((p.cellsTotal + cellsPerCta - 1) / cellsPerCta, p.imgs);
+        static int smCount = 0;
+        if (!smCount) {
+            int dev = 0;
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, dev);
+        }
+        const int wanted = (p.cellsTotal * p.imgs + cellsPerCta - 1) / cellsPerCta;
+        // CTAs launched per resident CTA slot (ORBX_FAST_GRID_MULT). 1 = fully persistent with static striding, which loses
+        // to its own tail (cells differ in cost: 1.54 ms per 512 KITTI images); 16 lets the hardware scheduler balance
+        // ~9-cell work packets (1.37 ms); one cell per warp pays the CTA turnover (1.43 ms): tools/fast_grid_sweep.sh
+        static int gridMult = 0;
+        if (!gridMult) {
+            const char* e = getenv("ORBX_FAST_GRID_MULT");
+            gridMult = e && atoi(e) > 0 ? atoi(e) : 16;
+        }
 #define FAST_WLAUNCH(SA_, C_)                                                                                                   \
     {                                                                                                                            \
         if (total > 32 * 1024)                                                                                                   \
             cudaFuncSetAttribute(orbx_fast_warp_kernel<SA_, C_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)total);       \
+        int perSm = 1;                                                                                                           \
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, orbx_fast_warp_kernel<SA_, C_>, C_ * 32, total);                   \
+        const long long cap = (long long)perSm * smCount * gridMult;                                                             \
+        const int wgrid = wanted < cap ? wanted : (int)cap;                                                                      \
         orbx_fast_warp_kernel<SA_, C_><<<wgrid, C_ * 32, total, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax, listCap, slice); \
     }
         if (sa == 48) {
