@@ -2,7 +2,7 @@
 // Replaces the cell loop of ORBextractor::ComputeKeyPointsOctTree
 // (/root/reference/src/ORBextractor.cc:792-832) and the two cv::FAST calls inside it (:812, :817).
 //
-// One CTA per 30-px cell (all levels and all images in one launch). Every interior pixel of the
+// One warp per 30-px cell (all levels and all images in one launch). Every interior pixel of the
 // cell's ROI gets its corner strength
 //     m = max over the 16 arcs of 9 contiguous ring pixels of min(+-(ring - centre))
 // which is threshold independent: the pixel is a FAST corner at threshold t iff m > t and OpenCV's
@@ -19,17 +19,16 @@
 //     engine addresses the innermost dimension in 16-byte units — by rhMax rows) signalled on an mbarrier;
 //   * pass 1 runs a byte-wise NECESSARY test for a corner at the attempt's threshold on the interior words of the raw
 //     tile, 4 pixels at once (VABSDIFF4 + SWAR compare against the compass points); a thread keeps its surviving pixel
-//     PAIRS as bits and appends them to the CTA's task list once (one warp scan and one shared atomic per warp);
+//     PAIRS as bits in a register and appends them to the cell's task list once (one warp scan);
 //   * pass 2 runs the exact test on the listed pairs only. A thread owns two horizontally adjacent pixels (even tile
 //     column first) and reads the 17 pairs (ring(x), ring(x+1)) straight from the raw tile (an aligned 16-bit load or two
 //     byte loads, one PRMT each: a widened u16 copy of the ROI cost more than it saved). Min and max commute with
 //     subtracting the centre, so the whole min/max network runs on the raw unsigned u16x2 ring values with the 3-input
 //     DPX instructions (__vimin3_u16x2 / __vimax3_u16x2): 36 ops per polarity and pixel PAIR (pair and quad minima shared
 //     by the two arcs that start at k and k+1);
-//   * strengths above the threshold go to a u16 map; NMS is driven by the list of non-zero pairs and uses packed column
-//     maxima; maxima are collected in a CTA list and emitted at their row-major rank (the reference order);
-//   * 64 threads per cell: the per-cell fixed work (prologue, mappings, scans) is paid per warp, and with 8 KB of shared
-//     memory per cell enough cells are resident per SM to keep the issue slots busy.
+//   * strengths stay packed to the end; m - thr goes to a u16 map for m > thr; NMS is driven by the list of non-zero pairs
+//     and uses packed column maxima; maxima are collected in a list and emitted at their row-major rank (reference order);
+//   * one warp per cell, four cells per CTA, long-lived warps: see the kernel.
 #include <cstdlib>
 
 #include "orbx_dev.cuh"
@@ -113,231 +112,16 @@ __device__ __forceinline__ uint32_t fast_pretest4(const uint32_t* tw, uint32_t K
     return (f0 | f8) & (f4 | f12);
 }
 
-// shared-memory counter bump by ONE lane on behalf of its warp (the counts are already summed by ballot / scan): as inline
-// PTX, or the compiler wraps its own warp aggregation (votes, a second scan) around the single-lane atomicAdd
-__device__ __forceinline__ int smem_add(int* p, int v)
-{
-    int old;
-    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(orbx_smem_addr(p)), "r"(v) : "memory");
-    return old;
-}
-
 // c_recip[n] = ceil(65536 / n): floor(t / n) = (t * c_recip[n]) >> 16 exactly while t * n < 65536 (here t <= 128, n <= 31)
 __constant__ uint32_t c_recip[32] = {0, 65536, 32768, 21846, 16384, 13108, 10923, 9363, 8192, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4096, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115};
 
-template <int SA, int FAST_THREADS>  // FAST_THREADS = 64 (or 32): the two-ended list below is for at most two warps
-__global__ void __launch_bounds__(FAST_THREADS) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap)
-{
-    // TMA box width in bytes = row stride of the tile: 20 / 28 words, so that 8 consecutive rows start in 8 different
-    // shared-memory banks (a 64-byte stride put every second row on the same banks)
-    constexpr int BW = SA == 48 ? 80 : 112;
-    extern __shared__ __align__(128) uint8_t fast_smem[];
-    __shared__ __align__(8) uint64_t bar;
-    __shared__ int listCnt, taskCnt, nzCntW[2];
-
-    uint8_t* T = fast_smem;                                                     // raw box [rhMax][BW]
-    // strength map, row stride SA: interior pixel (ix,iy) at [iy+1][A-column + SD], zero elsewhere. "A-column" = level column
-    // minus xa, xa = x0 & ~3: pixel pairs are aligned to even A-columns (= even tile bytes)
-    uint16_t* smap = reinterpret_cast<uint16_t*>(fast_smem + ((rhMax * BW + 127) & ~127));
-    uint16_t* lists = smap + (rhMax - 4) * SA;  // 2 CTA-wide lists of listCap entries: pass-1 tasks, then non-zero pairs
-
-    const int cellId = blockIdx.x, img = blockIdx.y;
-    const OrbxCell cell = cells[cellId];
-    const OrbxLevel& L = p.lv[cell.level];
-    const int rw = cell.rw, rh = cell.rh;
-    const int iw = rw - 6, ih = rh - 6;  // interior = detection domain of cv::FAST
-    int* cntOut = p.cellCnt + (size_t)img * p.cellsTotal + cellId;
-    if (iw <= 0 || ih <= 0) {
-        if (threadIdx.x == 0) *cntOut = 0;
-        return;
-    }
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) {
-        listCnt = 0;
-        taskCnt = 0;
-        orbx_mbar_init(&bar, 1);
-        orbx_fence_mbar_init();
-        orbx_mbar_expect_tx(&bar, rhMax * BW);
-        orbx_tma_load_3d(T, maps + cell.level, cell.x0 & ~15, cell.y0, img + p.imgBase, &bar);
-    }
-    {
-        uint4* z = reinterpret_cast<uint4*>(smap);  // 128-byte aligned, row stride a multiple of 16 bytes (SA % 8 == 0)
-        const int nz = (ih + 2) * (SA / 8);
-        for (int i = threadIdx.x; i < nz; i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
-    }
-    __syncthreads();  // barrier initialised (and armed) before anybody polls it
-    orbx_mbar_wait(&bar, 0);
-
-    const int tmin = p.minTh, tini = p.iniTh;
-    const int o = cell.x0 & 3;
-    const int ca0 = o + 3;                        // A-column of interior pixel 0
-    const int SD = 2 + ((o + 1) & 1) - ca0;       // strength-map column = A-column + SD (even, keeps pairs word aligned)
-    const uint32_t* tw0 = reinterpret_cast<const uint32_t*>(T) + ((cell.x0 & 15) >> 2);  // word of A-columns 0..3, row 0
-    // ---- threshold attempts (:812-819): first iniTh; only a cell whose FAST(iniTh) comes back empty repeats at minTh. A
-    // neighbour that is not a corner at t has m <= t < m_centre, so the NMS at threshold t only needs the strengths m > t:
-    // everything below (pre-test, network, map, NMS) runs on the pixels that can be corners at the attempt's threshold.
-    // The strength map of a failed first attempt needs no clearing: the minTh attempt rewrites a superset with equal values.
-    uint16_t* tasks = lists;                                  // CTA-wide list of surviving pixel pairs
-    uint16_t* nz = lists + listCap;                           // CTA-wide list of pairs with a non-zero strength
-    uint32_t* kept = reinterpret_cast<uint32_t*>(T);          // NMS maxima: key | m << 16 (the raw tile is dead by then)
-    const unsigned lt = (1u << lane) - 1;
-    // pre-test thread mapping: fixed interior word column j per thread, 128/nwi interior rows per step
-    const int jmin = ca0 >> 2, nwi = ((ca0 + iw - 1) >> 2) - jmin + 1;
-    const uint32_t rcpi = c_recip[nwi];
-    const int pStep = (int)((FAST_THREADS * rcpi) >> 16);
-    const int pyq = (int)((threadIdx.x * rcpi) >> 16);
-    const int pj = jmin + (int)threadIdx.x - pyq * nwi;
-    const bool pact = pyq < pStep;
-    // pair q (A-columns 4j+2q, +1) holds an interior pixel iff 4j+2q+1 >= ca0 and 4j+2q < ca0+iw
-    const unsigned vmask = !pact ? 0u : ((4 * pj + 1 >= ca0 && 4 * pj < ca0 + iw) ? 1u : 0u) | ((4 * pj + 3 >= ca0 && 4 * pj + 2 < ca0 + iw) ? 2u : 0u);
-    const uint32_t vmaskX = ((vmask & 1u) ? 0x000000FFu : 0u) | ((vmask & 2u) ? 0x00FF0000u : 0u);
-    const uint32_t* ptw0 = tw0 + (pyq + 3) * (BW / 4) + pj;
-    int thr = tini;
-#pragma unroll 1
-    for (int attempt = 0;; ++attempt) {
-        // ---- pass 1: a cheap NECESSARY test for "corner at thr" on the raw words: any 9 contiguous ring positions contain
-        // two ADJACENT compass points (0,4,8,12), so a corner needs (|d0|>t or |d8|>t) and (|d4|>t or |d12|>t). Four
-        // VABSDIFF4 + a SWAR byte compare test 4 pixels at once. A thread collects 2 bits per step in a register and appends
-        // its surviving pixel PAIRS once per 8 steps: one warp scan + one shared atomic per warp (pairs are aligned to even
-        // tile columns; the order of the list does not matter).
-        {
-            // bit 7 of each byte of f(x) = ((x & 0x7F..) + K) | x is set iff x > min(thr, 127): exact below 127, still
-            // necessary above
-            const uint32_t K = 0x01010101u * (uint32_t)(0x7F - min(thr, 0x7F));
-            const uint32_t* tw = ptw0;
-            uint32_t code0 = (uint32_t)(pyq * 256 + 2 * pj);  // list entry of pair 0 at the first step of the current group
-#pragma unroll 1
-            for (int g0 = 0; g0 < ih; g0 += 8 * pStep) {   // groups of 8 steps (uniform)
-                // flags of a step enter at bits 7 (pair 0) and 23 (pair 1) and move down one bit per step: after the
-                // group's S steps, step s sits at bits 8-S+s and 24-S+s
-                uint32_t acc = 0;
-                int S = 0;
-                const int lim = min(ih, g0 + 8 * pStep);
-                // two steps per trip (uniform trip count; an odd last step leaves its partner empty): ten loads in flight
-#pragma unroll 1
-                for (int y0s = g0; y0s < lim; y0s += 2 * pStep, S += 2) {
-                    acc >>= 2;
-                    const bool p0 = vmask && y0s + pyq < ih, p1 = vmask && y0s + pStep + pyq < ih;
-                    if (p0) {
-                        const uint32_t* tw1 = p1 ? tw + pStep * (BW / 4) : tw;  // (second step off: same words again, result dropped)
-                        const uint32_t m0 = fast_pretest4<BW>(tw, K), m1 = fast_pretest4<BW>(tw1, K);
-                        // bits 6 / 22: pixels 0|1 and 2|3 of the first step's word, bits 7 / 23: of the second step's
-                        const uint32_t u0 = ((m0 | (m0 >> 8)) >> 1) & 0x00400040u, u1 = (m1 | (m1 >> 8)) & 0x00800080u;
-                        acc |= u0 | (p1 ? u1 : 0u);
-                    }
-                    tw += 2 * pStep * (BW / 4);
-                }
-                uint32_t bits = (acc >> (8 - S)) & vmaskX;  // step s at bit s (pair 0) and bit 16+s (pair 1)
-                // append this thread's pairs of the group
-                int incl = __popc(bits);
-                const int mine = incl;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
-                    if (lane >= d) incl += v;
-                }
-                int base = 0;
-                if (lane == 31) base = smem_add(&taskCnt, incl);
-                uint16_t* dst = tasks + (__shfl_sync(0xffffffffu, base, 31) + incl - mine);
-                uint32_t c = code0;
-                while (bits) {
-                    if (bits & 1) *dst++ = (uint16_t)c;
-                    if (bits & 0x10000u) *dst++ = (uint16_t)(c + 1);
-                    bits = (bits >> 1) & 0x7FFF7FFFu;
-                    c += (uint32_t)pStep << 8;
-                }
-                code0 += (uint32_t)(8 * pStep) << 8;
-            }
-        }
-        __syncthreads();  // task list complete
-        // ---- pass 2: the min/max network on the surviving pairs (results go to the map by position)
-        const int ntAll = taskCnt;
-        const uint32_t thr2 = (uint32_t)thr * 0x10001u;
-        {
-            int nzMine = 0;  // warp-uniform
-#pragma unroll 1
-            for (int g0 = warp * 32; g0 < ntAll; g0 += FAST_THREADS) {
-                const int g = g0 + lane;
-                bool hit = false;
-                int task = 0;
-                if (g < ntAll) {
-                    task = tasks[g];
-                    const int y = task >> 8, c = 2 * (task & 255);
-                    const uint32_t mp = fast_strength2_raw<BW>(reinterpret_cast<const uint8_t*>(tw0) + (y + 3) * BW + c);
-                    // the map holds m - thr for m > thr and 0 otherwise (per half: max(m, thr) - thr cannot borrow). The NMS
-                    // only compares strengths of one attempt with each other, so the common offset does not matter; the
-                    // kept maxima get it back.
-                    const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
-                    const uint32_t inside = (ix >= 0 ? 0x0000FFFFu : 0u) | (ix + 1 < iw ? 0xFFFF0000u : 0u);
-                    const uint32_t ms = (__vimax3_u16x2(mp, thr2, thr2) - thr2) & inside;
-                    hit = ms != 0;
-                    if (hit) *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + c + SD) = ms;  // map is pre-zeroed
-                }
-                // the list of non-zero pairs is filled from both ends, warp 0 upwards and warp 1 downwards (together they hold
-                // at most listCap pairs): the fill counts stay in registers and no atomic is needed
-                const unsigned bh = __ballot_sync(0xffffffffu, hit);
-                if (hit) {
-                    const int idx = nzMine + __popc(bh & lt);
-                    nz[warp == 0 ? idx : listCap - 1 - idx] = (uint16_t)task;
-                }
-                nzMine += __popc(bh);
-            }
-            if (lane == 0) nzCntW[warp] = nzMine;
-        }
-        __syncthreads();
-
-        // ---- NMS over the pairs that hold a non-zero strength: strict maximum over the 8 neighbours in the
-        // strength map. Maxima go to a CTA list kept[] = key | m << 16, key = y*64 + x (interior coords).
-        const int nz0 = nzCntW[0], nzAll = nz0 + (FAST_THREADS > 32 ? nzCntW[1] : 0);
-#pragma unroll 1
-        for (int g = threadIdx.x; g < nzAll; g += FAST_THREADS) {
-            const int task = nz[g < nz0 ? g : listCap - 1 - (g - nz0)], y = task >> 8, cc = 2 * (task & 255);
-            const uint16_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair, word aligned
-            const uint32_t mm = *reinterpret_cast<const uint32_t*>(c);
-            const uint32_t u0 = *reinterpret_cast<const uint32_t*>(c - SA - 2), u1 = *reinterpret_cast<const uint32_t*>(c - SA), u2 = *reinterpret_cast<const uint32_t*>(c - SA + 2);
-            const uint32_t l0 = *reinterpret_cast<const uint32_t*>(c - 2), l2 = *reinterpret_cast<const uint32_t*>(c + 2);
-            const uint32_t d0 = *reinterpret_cast<const uint32_t*>(c + SA - 2), d1 = *reinterpret_cast<const uint32_t*>(c + SA), d2 = *reinterpret_cast<const uint32_t*>(c + SA + 2);
-            // column maxima over the three rows, as pairs (x-2,x-1) (x,x+1) (x+2,x+3)
-            const uint32_t cm0 = __vimax3_u16x2(u0, l0, d0), cm1 = __vimax3_u16x2(u1, mm, d1), cm2 = __vimax3_u16x2(u2, l2, d2);
-            const uint32_t ud = __vimax3_u16x2(u1, d1, d1);
-            // neighbours of pixel 0 (x): columns x-1, x+1 (all rows) and rows above/below in column x; pixel 1 likewise
-            const int m0 = mm & 0xFFFFu, m1 = mm >> 16;
-            const int n0 = max(max((int)(cm0 >> 16), (int)(cm1 >> 16)), (int)(ud & 0xFFFFu));
-            const int n1 = max(max((int)(cm1 & 0xFFFFu), (int)(cm2 & 0xFFFFu)), (int)(ud >> 16));
-            const int ix = cc - ca0;
-            if (m0 > n0) kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + ix) | ((uint32_t)(m0 + thr) << 16);
-            if (m1 > n1) kept[atomicAdd(&listCnt, 1)] = (uint32_t)(y * 64 + ix + 1) | ((uint32_t)(m1 + thr) << 16);
-        }
-        __syncthreads();  // publishes kept[] and listCnt
-        if (listCnt > 0 || attempt == 1 || tmin >= thr) break;
-        thr = tmin;       // :814 FAST(iniTh) came back empty: once more with minTh
-        if (threadIdx.x == 0) taskCnt = 0;  // (last read before the barrier that ended pass 2)
-        __syncthreads();
-    }
-
-    // ---- ordered emission: rank of a maximum = number of maxima with a smaller row-major key
-    const int nkept = listCnt;
-    const uint32_t slot0 = L.slotBase + (uint32_t)(cellId - L.cellBase) * L.slotCap;
-    uint32_t* out = p.cellKp + (size_t)img * p.slotTotal + slot0;
-    if (threadIdx.x == 0) *cntOut = nkept;
-#pragma unroll 1
-    for (int i = threadIdx.x; i < nkept; i += FAST_THREADS) {
-        const uint32_t e = kept[i];
-        const int key = e & 0xFFFFu, m = e >> 16;
-        int rank = 0;
-        for (int j = 0; j < nkept; ++j) rank += (int)(kept[j] & 0xFFFFu) < key;
-        out[rank] = (uint32_t)((key & 63) + 3) | ((uint32_t)((key >> 6) + 3) << 8) | ((uint32_t)(m - 1) << 16);
-    }
-}
-
-// ---- one WARP per cell, CELLS cells per CTA --------------------------------------------------------------------------
-// Same passes as orbx_fast_kernel, but a cell belongs to one warp: the fixed work per (warp, cell) — prologue, thread
-// mapping, list flush, emission, ~300 of the ~1060 warp instructions a warp spent per cell — is paid once per cell instead
-// of twice, every CTA barrier becomes a __syncwarp, and the list counters are warp-uniform registers (no shared atomics).
-// CELLS warps share a CTA only for occupancy (a one-warp CTA caps the SM at 32 warps, less with 8.5 KB of shared memory
-// each); they never talk to each other.
+// One WARP per cell, CELLS cells per CTA. A cell used to belong to a 64-thread CTA; the fixed work per (warp, cell) —
+// prologue, thread mapping, list flush, emission, ~300 of the ~1060 warp instructions a warp spent per cell — is now paid
+// once per cell instead of twice, there is no CTA barrier (only __syncwarp), and the list counters are warp-uniform
+// registers (no shared atomics). CELLS warps share a CTA only for occupancy (a one-warp CTA caps the SM at 32 warps, less
+// with 7.3 KB of shared memory each); they never talk to each other.
 template <int SA, int CELLS>
-__global__ void __launch_bounds__(CELLS * 32) orbx_fast_warp_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap,
+__global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap,
                                                                     int sliceBytes)
 {
     constexpr int BW = SA == 48 ? 80 : 112;
@@ -386,6 +170,12 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_warp_kernel(OrbxParams p
     orbx_mbar_wait(bar, phase);
     phase ^= 1;
 
+    // ---- threshold attempts (:812-819): first iniTh; only a cell whose FAST(iniTh) comes back empty repeats at minTh. A
+    // neighbour that is not a corner at t has m <= t < m_centre, so the NMS at threshold t only needs the strengths m > t:
+    // everything below (pre-test, network, map, NMS) runs on the pixels that can be corners at the attempt's threshold.
+    // The strength map of a failed first attempt needs no clearing: the minTh attempt rewrites a superset of its entries.
+    // Strength map, row stride SA: interior pixel (ix,iy) at [iy+1][A-column + SD], zero elsewhere. "A-column" = level
+    // column minus (x0 & ~3): pixel pairs are aligned to even A-columns (= even tile bytes).
     const int tmin = p.minTh, tini = p.iniTh;
     const int o = cell.x0 & 3;
     const int ca0 = o + 3;                   // A-column of interior pixel 0
@@ -405,7 +195,13 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_warp_kernel(OrbxParams p
     int thr = tini, nkept = 0;
 #pragma unroll 1
     for (int attempt = 0;; ++attempt) {
-        // ---- pass 1 (see orbx_fast_kernel): flags of a step enter at bits 15 / 31 and move down, 16 steps per flush
+        // ---- pass 1: a cheap NECESSARY test for "corner at thr" on the raw words: any 9 contiguous ring positions contain
+        // two ADJACENT compass points (0,4,8,12), so a corner needs (|d0|>t or |d8|>t) and (|d4|>t or |d12|>t). Four
+        // VABSDIFF4 + a SWAR byte compare test 4 pixels at once (fast_pretest4). A lane collects the flags of its pixel
+        // PAIRS in a register — they enter at bits 15 / 31 and move down one bit per step — and appends the survivors once
+        // per 16 steps: one warp scan, no atomics (pairs are aligned to even tile columns; the list order does not matter).
+        // bit 7 of each byte of f(x) = ((x & 0x7F..) + K) | x is set iff x > min(thr, 127): exact below 127, still
+        // necessary above
         int ntAll = 0;
         {
             const uint32_t K = 0x01010101u * (uint32_t)(0x7F - min(thr, 0x7F));
@@ -543,73 +339,46 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
 {
     int boxW, rhMax;
     orbx_fast_geometry(p, &boxW, &rhMax);
-    dim3 grid(p.cellsTotal, p.imgs);
     const int sa = boxW == 80 ? 48 : 80;
     // list capacity: every pixel pair that can hold an interior pixel (interior = ROI - 6; one more pair for the alignment)
     const int iwMax = (sa == 48 ? 40 : 72) - 6, ihMax = rhMax - 6;
     const int listCap = (((iwMax + 4) / 2) * ihMax + 7) & ~7;
-    // threads per cell: 64 measured best (tools/fast_threads_sweep.sh: 1.71 ms against 2.01 with 128 and 1.93 with 32 per 512
-    // KITTI images); ORBX_FAST_THREADS overrides it for that sweep
-    static int nt = 0;
-    if (!nt) {
-        const char* e = getenv("ORBX_FAST_THREADS");
-        nt = e ? atoi(e) : 64;
-        if (nt != 32 && nt != 64) nt = 64;
-    }
-    const size_t smem = (size_t)((rhMax * boxW + 127) & ~127) + (size_t)(rhMax - 4) * sa * 2 + (size_t)2 * listCap * 2;
-    // warp-per-cell kernel: ORBX_FAST_CELLS = cells (warps) per CTA, 0 = the CTA-per-cell kernel
-    static int cellsPerCta = -1;
-    if (cellsPerCta < 0) {
+    // shared memory of one cell: tile + strength map + one list (the non-zero pairs overwrite the tasks)
+    const int slice = (int)(((size_t)((rhMax * boxW + 127) & ~127) + (size_t)(rhMax - 4) * sa * 2 + (size_t)listCap * 2 + 127) & ~(size_t)127);
+    // cells (= warps) per CTA: ORBX_FAST_CELLS = 2 / 4 / 8 (tools/fast_cells_sweep.sh: 4 is best, 8 loses a third)
+    static int cellsPerCta = 0;
+    if (!cellsPerCta) {
         const char* e = getenv("ORBX_FAST_CELLS");
         cellsPerCta = e ? atoi(e) : 4;
-        if (cellsPerCta != 0 && cellsPerCta != 2 && cellsPerCta != 4 && cellsPerCta != 8) cellsPerCta = 4;
+        if (cellsPerCta != 2 && cellsPerCta != 4 && cellsPerCta != 8) cellsPerCta = 4;
     }
-    if (cellsPerCta > 0) {
-        const int slice = (int)((smem - (size_t)listCap * 2 + 127) & ~(size_t)127);  // one list: the non-zero pairs overwrite the tasks
-        const size_t total = (size_t)slice * cellsPerCta;
-        static int smCount = 0;
-        if (!smCount) {
-            int dev = 0;
-            cudaGetDevice(&dev);
-            cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, dev);
-        }
-        const int wanted = (p.cellsTotal * p.imgs + cellsPerCta - 1) / cellsPerCta;
-        // CTAs launched per resident CTA slot (ORBX_FAST_GRID_MULT). 1 = fully persistent with static striding, which loses
-        // to its own tail (cells differ in cost: 1.54 ms per 512 KITTI images); 16 lets the hardware scheduler balance
-        // ~9-cell work packets (1.37 ms); one cell per warp pays the CTA turnover (1.43 ms): tools/fast_grid_sweep.sh
-        static int gridMult = 0;
-        if (!gridMult) {
-            const char* e = getenv("ORBX_FAST_GRID_MULT");
-            gridMult = e && atoi(e) > 0 ? atoi(e) : 16;
-        }
-#define FAST_WLAUNCH(SA_, C_)                                                                                                   \
+    // CTAs launched per resident CTA slot (ORBX_FAST_GRID_MULT). 1 = fully persistent with static striding, which loses
+    // to its own tail (cells differ in cost: 1.54 ms per 512 KITTI images); 16 lets the hardware scheduler balance
+    // ~9-cell work packets (1.37 ms); one cell per warp pays the CTA turnover (1.43 ms): tools/fast_grid_sweep.sh
+    static int gridMult = 0, smCount = 0;
+    if (!gridMult) {
+        const char* e = getenv("ORBX_FAST_GRID_MULT");
+        gridMult = e && atoi(e) > 0 ? atoi(e) : 16;
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const size_t smem = (size_t)slice * cellsPerCta;
+    const int wanted = (p.cellsTotal * p.imgs + cellsPerCta - 1) / cellsPerCta;
+#define FAST_LAUNCH(SA_, C_)                                                                                                     \
     {                                                                                                                            \
-        if (total > 32 * 1024)                                                                                                   \
-            cudaFuncSetAttribute(orbx_fast_warp_kernel<SA_, C_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)total);       \
+        if (smem > 32 * 1024) /* static + dynamic may pass 48 KB; per-device attribute, set on every such launch */            \
+            cudaFuncSetAttribute(orbx_fast_kernel<SA_, C_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);             \
         int perSm = 1;                                                                                                           \
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, orbx_fast_warp_kernel<SA_, C_>, C_ * 32, total);                   \
-        const long long cap = (long long)perSm * smCount * gridMult;                                                             \
-        const int wgrid = wanted < cap ? wanted : (int)cap;                                                                      \
-        orbx_fast_warp_kernel<SA_, C_><<<wgrid, C_ * 32, total, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax, listCap, slice); \
-    }
-        if (sa == 48) {
-            if (cellsPerCta == 2) FAST_WLAUNCH(48, 2) else if (cellsPerCta == 4) FAST_WLAUNCH(48, 4) else FAST_WLAUNCH(48, 8)
-        } else {
-            if (cellsPerCta == 2) FAST_WLAUNCH(80, 2) else if (cellsPerCta == 4) FAST_WLAUNCH(80, 4) else FAST_WLAUNCH(80, 8)
-        }
-#undef FAST_WLAUNCH
-        return;
-    }
-#define FAST_LAUNCH(SA_, NT_)                                                                                                    \
-    {                                                                                                                            \
-        if (smem > 32 * 1024) /* tall cells: static + dynamic may pass 48 KB; per-device attribute, set on every such launch */ \
-            cudaFuncSetAttribute(orbx_fast_kernel<SA_, NT_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);            \
-        orbx_fast_kernel<SA_, NT_><<<grid, NT_, smem, s>>>(p, (const OrbxCell*)cellTable, (const CUtensorMap*)levelMaps, rhMax, listCap); \
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, orbx_fast_kernel<SA_, C_>, C_ * 32, smem);                         \
+        const long long cap = (long long)(perSm > 0 ? perSm : 1) * smCount * gridMult;                                           \
+        orbx_fast_kernel<SA_, C_><<<wanted < cap ? wanted : (int)cap, C_ * 32, smem, s>>>(p, (const OrbxCell*)cellTable,         \
+                                                                                          (const CUtensorMap*)levelMaps, rhMax, listCap, slice); \
     }
     if (sa == 48) {
-        if (nt == 64) FAST_LAUNCH(48, 64) else FAST_LAUNCH(48, 32)
+        if (cellsPerCta == 2) FAST_LAUNCH(48, 2) else if (cellsPerCta == 4) FAST_LAUNCH(48, 4) else FAST_LAUNCH(48, 8)
     } else {
-        if (nt == 64) FAST_LAUNCH(80, 64) else FAST_LAUNCH(80, 32)
+        if (cellsPerCta == 2) FAST_LAUNCH(80, 2) else if (cellsPerCta == 4) FAST_LAUNCH(80, 4) else FAST_LAUNCH(80, 8)
     }
 #undef FAST_LAUNCH
 }

@@ -1,5 +1,5 @@
-# FAST kernel layout: CTA per cell (ORBX_FAST_CELLS=0) against warp per cell with 2 / 4 / 8 cells per CTA. Run on the GPU box.
-for c in 0 2 4 8; do
+# FAST kernel layout: warp per cell with 2 / 4 / 8 cells per CTA. Run on the GPU box.
+for c in 2 4 8; do
   export ORBX_FAST_CELLS=$c
   python -m pytest tests/test_gpu_parity.py tests/test_reference_pin.py -m gpu -x -q 2>&1 | tail -1
   python bench.py --steps 10 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('cells=$c', round(d['value']), round(d['e2e']['value']), d['roofline']['stage_ms_per_step']['fast'])"
