@@ -235,11 +235,14 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
                 uint16_t* dst = tasks + (ntAll + incl - mine);
                 ntAll += __shfl_sync(0xffffffffu, incl, 31);
                 uint32_t c = code0;
-                while (bits) {
+                const uint32_t cs = (uint32_t)pStep << 8;
+                while (bits) {  // two steps per trip
                     if (bits & 1) *dst++ = (uint16_t)c;
                     if (bits & 0x10000u) *dst++ = (uint16_t)(c + 1);
-                    bits = (bits >> 1) & 0x7FFF7FFFu;
-                    c += (uint32_t)pStep << 8;
+                    if (bits & 2) *dst++ = (uint16_t)(c + cs);
+                    if (bits & 0x20000u) *dst++ = (uint16_t)(c + cs + 1);
+                    bits = (bits >> 2) & 0x3FFF3FFFu;
+                    c += 2 * cs;
                 }
                 code0 += (uint32_t)(16 * pStep) << 8;
             }
