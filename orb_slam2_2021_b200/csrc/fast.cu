@@ -120,6 +120,9 @@ __constant__ uint32_t c_recip[32] = {0, 65536, 32768, 21846, 16384, 13108, 10923
 // once per cell instead of twice, there is no CTA barrier (only __syncwarp), and the list counters are warp-uniform
 // registers (no shared atomics). CELLS warps share a CTA only for occupancy (a one-warp CTA caps the SM at 32 warps, less
 // with 7.3 KB of shared memory each); they never talk to each other.
+#ifndef FAST_ROWMAJOR
+#define FAST_ROWMAJOR 0  // 1: row-major task list built with per-step ballots (experiment)
+#endif
 template <int SA, int CELLS>
 __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap,
                                                                     int sliceBytes)
@@ -203,6 +206,42 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
         // bit 7 of each byte of f(x) = ((x & 0x7F..) + K) | x is set iff x > min(thr, 127): exact below 127, still
         // necessary above
         int ntAll = 0;
+#if FAST_ROWMAJOR
+        {
+            // survivors are appended step by step with ballots, so the task list is in row-major order: the 32 tasks of a
+            // pass-2 trip come from one to three tile rows and their ring loads spread over the banks
+            const uint32_t K = 0x01010101u * (uint32_t)(0x7F - min(thr, 0x7F));
+            const uint32_t* tw = ptw0;
+            const uint32_t maskLo = (vmask & 1u) ? 0x00008080u : 0u, maskHi = (vmask & 2u) ? 0x80800000u : 0u;
+            uint32_t code = (uint32_t)(pyq * 256 + 2 * pj);
+            const uint32_t cs = (uint32_t)pStep << 8;
+#pragma unroll 1
+            for (int y0s = 0; y0s < ih; y0s += 2 * pStep) {  // two steps per trip (uniform trip count)
+                const bool p0 = vmask && y0s + pyq < ih, p1 = vmask && y0s + pStep + pyq < ih;
+                uint32_t m0 = 0, m1 = 0;
+                if (p0) {
+                    const uint32_t* tw1 = p1 ? tw + pStep * (BW / 4) : tw;
+                    m0 = fast_pretest4<BW>(tw, K);
+                    m1 = fast_pretest4<BW>(tw1, K);
+                    m1 = p1 ? m1 : 0u;
+                }
+                tw += 2 * pStep * (BW / 4);
+                const bool f00 = (m0 & maskLo) != 0, f01 = (m0 & maskHi) != 0, f10 = (m1 & maskLo) != 0, f11 = (m1 & maskHi) != 0;
+                const unsigned b00 = __ballot_sync(0xffffffffu, f00), b01 = __ballot_sync(0xffffffffu, f01);
+                const unsigned b10 = __ballot_sync(0xffffffffu, f10), b11 = __ballot_sync(0xffffffffu, f11);
+                int n = ntAll;
+                if (f00) tasks[n + __popc(b00 & lt)] = (uint16_t)code;
+                n += __popc(b00);
+                if (f01) tasks[n + __popc(b01 & lt)] = (uint16_t)(code + 1);
+                n += __popc(b01);
+                if (f10) tasks[n + __popc(b10 & lt)] = (uint16_t)(code + cs);
+                n += __popc(b10);
+                if (f11) tasks[n + __popc(b11 & lt)] = (uint16_t)(code + cs + 1);
+                ntAll = n + __popc(b11);
+                code += 2 * cs;
+            }
+        }
+#else
         {
             const uint32_t K = 0x01010101u * (uint32_t)(0x7F - min(thr, 0x7F));
             const uint32_t* tw = ptw0;
@@ -247,6 +286,7 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
                 code0 += (uint32_t)(16 * pStep) << 8;
             }
         }
+#endif
         __syncwarp();  // task list complete
         // ---- pass 2: the min/max network on the surviving pairs
         const uint32_t thr2 = (uint32_t)thr * 0x10001u;
