@@ -18,8 +18,8 @@
 //   * the ROI arrives by ONE TMA box load (cp.async.bulk.tensor.3d, 64 or 96 columns starting at x0 & ~15 — the copy
 //     engine addresses the innermost dimension in 16-byte units — by rhMax rows) signalled on an mbarrier;
 //   * pass 1 runs a byte-wise NECESSARY test for a corner at the attempt's threshold on the interior words of the raw
-//     tile, 4 pixels at once (VABSDIFF4 + SWAR compare against the compass points); a thread keeps its surviving pixel
-//     PAIRS as bits in a register and appends them to the cell's task list once (one warp scan);
+//     tile, 4 pixels at once (VABSDIFF4 + SWAR compare against the compass points); the surviving pixel
+//     PAIRS are appended to the cell's task list step by step with ballots (row-major order, FAST_ROWMAJOR);
 //   * pass 2 runs the exact test on the listed pairs only. A thread owns two horizontally adjacent pixels (even tile
 //     column first) and reads the 17 pairs (ring(x), ring(x+1)) straight from the raw tile (an aligned 16-bit load or two
 //     byte loads, one PRMT each: a widened u16 copy of the ROI cost more than it saved). Min and max commute with
