@@ -39,6 +39,8 @@ def parse_args():
     ap.add_argument("--frames", type=int, default=256, help="stereo frames per GPU per step")
     ap.add_argument("--config", default=CONFIG_NAME)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tune", action="append", default=[], metavar="KEY=VALUE",
+                    help="orbx_set_tuning knob for experiments (tools/*_sweep.sh), e.g. --tune fast_cells=2")
     return ap.parse_args()
 
 
@@ -249,6 +251,9 @@ def ours_arm(args, rank, local_rank, world):
         dist.all_reduce(t, op=op)
         return float(t.item())
 
+    for kv in args.tune:
+        k, v = kv.split("=", 1)
+        pkg.set_tuning(k, int(v))
     cfg = synth.CONFIGS[args.config]
     W, H, nf, nl, sf, ini, mn, fx, bf = cfg
     F = args.frames

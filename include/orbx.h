@@ -38,6 +38,10 @@ typedef struct orbx_batch orbx_batch;         /* frame-batch engine for throughp
 
 const char* orbx_last_error(void);            /* thread-local text of the last failure            */
 int orbx_device_count(void);
+/* Debug/experiment knobs (no reference counterpart; the library never reads the environment). Keys: run_streams,
+ * run_chunks, e2e_streams, e2e_chunks, e2e_first_div, e2e_trace, fast_cells, fast_grid_mult, numa_off; value 0 restores
+ * the built-in default. Process-wide, not thread-safe against running calls. Unknown key: ORBX_ERR_ARG. */
+int orbx_set_tuning(const char* key, int value);
 
 /* ---- ORBextractor ------------------------------------------------------------------------------ */
 
@@ -62,7 +66,7 @@ int orbx_max_keypoints(const orbx_extractor* e, int rows, int cols);
  * Frame::ExtractORB, src/Frame.cc:296-302. `image` is host CV_8UC1, `stride` bytes per row; the mask
  * is ignored by the reference and has no parameter here. Writes *n keypoints (levels concatenated
  * 0..L-1, coordinates scaled to level 0) and n x 32 descriptor bytes. An empty image (rows or cols
- * == 0) returns ORBX_OK and leaves kps/desc/n untouched, like :1044-1045. */
+ * == 0) returns ORBX_OK with *n = 0 and leaves kps/desc untouched, like :1044-1045. */
 int orbx_extract(orbx_extractor* e, const uint8_t* image, int rows, int cols, size_t stride, orbx_keypoint* kps,
                  uint8_t* desc, int capacity, int* n);
 
@@ -136,7 +140,7 @@ int orbx_batch_stage_times(orbx_batch* b, double* ms, int* runs);
 /* Bytes of HBM the engine holds. */
 long long orbx_batch_device_bytes(const orbx_batch* b);
 /* Page-locked host memory for the end-to-end path (cudaHostAlloc / cudaFreeHost), placed on the NUMA node of the
- * current CUDA device when the host allows it (ORBX_NUMA=0: plain allocation). orbx_host_numa_node reports the node the
+ * current CUDA device when the host allows it (orbx_set_tuning("numa_off", 1): plain allocation). orbx_host_numa_node reports the node the
  * last allocation aimed at (-1 unknown, -2 none yet) and whether the placement policy was in force. */
 void* orbx_host_alloc(size_t bytes);
 void orbx_host_free(void* p);

@@ -41,6 +41,7 @@ _ip = C.POINTER(C.c_int)
 SIGNATURES = {
     "orbx_last_error": (C.c_char_p, []),
     "orbx_device_count": (_i, []),
+    "orbx_set_tuning": (_i, [C.c_char_p, _i]),
     "orbx_create": (_i, [_i, _f, _i, _i, _i, _i, C.POINTER(_vp)]),
     "orbx_destroy": (None, [_vp]),
     "orbx_get_levels": (_i, [_vp]),

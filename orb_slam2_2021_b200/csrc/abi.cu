@@ -98,7 +98,10 @@ extern "C" int orbx_extract(orbx_extractor* e, const uint8_t* image, int rows, i
                             uint8_t* desc, int capacity, int* n)
 {
     if (!e) return fail(ORBX_ERR_ARG, "handle is NULL");
-    if (rows == 0 || cols == 0 || !image) return ORBX_OK;  // src/ORBextractor.cc:1044-1045: silent return
+    if (rows == 0 || cols == 0 || !image) {  // src/ORBextractor.cc:1044-1045: silent return; an out-count must not stay undefined
+        if (n) *n = 0;
+        return ORBX_OK;
+    }
     if (rows < 0 || cols < 0 || stride < (size_t)cols || !kps || !desc || !n) return fail(ORBX_ERR_ARG, "bad arguments");
     if (!e->eng || e->eng->rows != rows || e->eng->cols != cols) {
         e->hasRun = false;
@@ -178,6 +181,11 @@ extern "C" int orbx_stereo_match(orbx_extractor* l, orbx_extractor* r, const orb
     if (EL.rows != ER.rows || EL.cols != ER.cols || EL.P.nlevels != ER.P.nlevels || l->device != r->device)
         return fail(ORBX_ERR_STATE, "left/right extractors differ in image size, levels or device");
     if (nL > EL.P.maxKp || nR > ER.P.maxKp) return fail(ORBX_ERR_ARG, "more keypoints than the extractor can produce");
+    // the octave indexes the level tables and the pyramid on the device (src/Frame.cc:541, :617-620)
+    for (int i = 0; i < nL; ++i)
+        if (kpsL[i].octave < 0 || kpsL[i].octave >= l->cfg.nlevels) return fail(ORBX_ERR_ARG, "left keypoint octave outside 0..nlevels-1");
+    for (int i = 0; i < nR; ++i)
+        if (kpsR[i].octave < 0 || kpsR[i].octave >= l->cfg.nlevels) return fail(ORBX_ERR_ARG, "right keypoint octave outside 0..nlevels-1");
     for (int i = 0; i < nL; ++i) uRight[i] = depth[i] = -1.f;  // src/Frame.cc:524-525
     if (nL == 0) return ORBX_OK;
     TRY(orbx_check(cudaSetDevice(l->device), "cudaSetDevice", g_err));
@@ -225,7 +233,7 @@ extern "C" int orbx_stereo_match(orbx_extractor* l, orbx_extractor* r, const orb
 // chunks of >= 16 frames keep every kernel's grid well above one wave while the copies of the neighbouring chunks overlap
 static int e2e_chunk_frames(int nFrames)
 {
-    static const int forcedChunks = [] { const char* e = getenv("ORBX_E2E_CHUNKS"); return e ? atoi(e) : 0; }();
+    const int forcedChunks = orbx_tune(ORBX_TUNE_E2E_CHUNKS);
     return forcedChunks > 0 ? (nFrames + forcedChunks - 1) / forcedChunks : nFrames >= 64 ? (nFrames + 7) / 8 : nFrames >= 32 ? 16 : nFrames;
 }
 
@@ -271,7 +279,7 @@ extern "C" int orbx_batch_upload_device(orbx_batch* b, const void* left, const v
 // chunks of a device-resident run (see Engine::runBatch); ORBX_RUN_CHUNKS overrides for experiments
 static int run_chunks(int nFrames)
 {
-    static const int forced = [] { const char* e = getenv("ORBX_RUN_CHUNKS"); return e ? atoi(e) : 0; }();
+    const int forced = orbx_tune(ORBX_TUNE_RUN_CHUNKS);
     if (forced > 0) return forced;
     return nFrames >= 32 ? 2 : 1;
 }
@@ -322,7 +330,7 @@ extern "C" int orbx_batch_process_async(orbx_batch* b, const uint8_t* left, cons
     if (!b || nFrames < 1 || nFrames > b->maxFrames) return fail(ORBX_ERR_ARG, "bad frame count");
     Engine::HostOutputs o{nLeft, kpsLeft, descLeft, nRight, kpsRight, descRight, uRight, depth};
     // four large chunks: without a ramp to hide, fewer and larger launches run closer to the device-resident rate
-    static const int forcedChunks = [] { const char* e = getenv("ORBX_E2E_CHUNKS"); return e ? atoi(e) : 0; }();
+    const int forcedChunks = orbx_tune(ORBX_TUNE_E2E_CHUNKS);
     const int chunk = forcedChunks > 0 ? (nFrames + forcedChunks - 1) / forcedChunks : nFrames >= 64 ? (nFrames + 3) / 4 : nFrames >= 32 ? 16 : nFrames;
     return b->eng.processPipelined(left, right, nFrames, mbf, mb, o, chunk, g_err, false);
 }
@@ -425,7 +433,7 @@ extern "C" int orbx_batch_stage_times(orbx_batch* b, double* ms, int* runs)
 // The node comes from sysfs (the device's PCI function); the placement is a PREFERRED memory policy of the calling
 // thread held only around the allocation (the driver populates and pins the pages inside cudaHostAlloc). Where the
 // policy call is not permitted (seccomp) the allocation runs on one of the node's cores instead (local allocation is the
-// default policy); where the node is unknown the allocation is the plain one. ORBX_NUMA=0 disables.
+// default policy); where the node is unknown the allocation is the plain one. orbx_set_tuning("numa_off", 1) disables.
 #include <sched.h>
 #include <sys/syscall.h>
 #include <unistd.h>
@@ -477,8 +485,7 @@ static bool node_cpus(int node, cpu_set_t* set)
 
 extern "C" void* orbx_host_alloc(size_t bytes)
 {
-    const char* env = getenv("ORBX_NUMA");
-    const int node = (env && atoi(env) == 0) ? -1 : device_numa_node();
+    const int node = orbx_tune(ORBX_TUNE_NUMA_OFF) ? -1 : device_numa_node();
     unsigned long mask[16] = {0};  // up to 1024 nodes
     bool bound = false;
     if (node >= 0 && node < 1024) {

@@ -54,6 +54,18 @@ int orbx_stereo_bin_radius(const float* scale, int nlevels)
     return (int)std::ceil(2.0f * m) + 1;
 }
 
+// ---- tuning table (orbx_set_tuning) ---------------------------------------------------------------------
+static int g_tune[ORBX_TUNE_COUNT] = {0};
+static const char* const g_tuneNames[ORBX_TUNE_COUNT] = {"run_streams", "run_chunks", "e2e_streams", "e2e_chunks", "e2e_first_div",
+                                                         "e2e_trace", "fast_cells", "fast_grid_mult", "numa_off"};
+int orbx_tune(OrbxTune key) { return g_tune[key]; }
+extern "C" int orbx_set_tuning(const char* key, int value)
+{
+    for (int i = 0; key && i < ORBX_TUNE_COUNT; ++i)
+        if (!std::strcmp(key, g_tuneNames[i])) { g_tune[i] = value; return ORBX_OK; }
+    return ORBX_ERR_ARG;
+}
+
 static inline unsigned align_up(unsigned v, unsigned a) { return (v + a - 1) / a * a; }
 
 struct HostCell {
@@ -133,7 +145,12 @@ int Engine::plan(const ExtractorConfig& cfg, int rows, int cols, OrbxParams& p, 
         L.hX = (float)bw / L.nIni;  // :548
         int cap = (L.quota > 4 * L.nIni ? L.quota : 4 * L.nIni) + 4;
         L.keepCap = (cap + 7) & ~7;  // whole describe CTAs (8 warps = 8 slots) per level
-        if (L.keepCap > 65000) { err = "per-level quota too large"; return ORBX_ERR_ARG; }
+        // the quadtree keeps a level's node list in the shared memory of one CTA (227 KB opt-in maximum per CTA on sm_100)
+        if (L.keepCap > 65000 || orbx_octree_smem_total(L.keepCap) > 227u * 1024u) {
+            err = "per-level feature quota " + std::to_string(L.quota) + " (level " + std::to_string(l) + ") too large: the quadtree holds at most ~2600 nodes per level "
+                  "(about 12000 features at scaleFactor 1.2 / 8 levels); use fewer features or more levels";
+            return ORBX_ERR_ARG;
+        }
         L.keepBase = keepBase; keepBase += L.keepCap;
         L.scale = cfg.scale[l]; L.invScale = cfg.invScale[l];
         L.patchSize = (int)(31 * cfg.scale[l]);  // :836
@@ -190,6 +207,8 @@ void Engine::release()
     for (cudaEvent_t e : ingestEvents) cudaEventDestroy(e);
     for (cudaEvent_t e : downEvents) cudaEventDestroy(e);
     ingestEvents.clear(); downEvents.clear(); lastBounds.clear();
+    for (cudaEvent_t e : events) if (e) cudaEventDestroy(e);
+    events.clear(); profiling = false; profiledRuns = 0;
     stream = stream2 = stream3 = stream4 = upStream = downStream = nullptr;
     bytesAllocated = 0;
 }
@@ -277,6 +296,8 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     TRY(dalloc(this, &P.outDesc, n * P.maxKp * 32, "outDesc", err));
     TRY(dalloc(this, &P.outCnt, n, "outCnt", err));
     TRY(orbx_check(cudaMemsetAsync(P.outCnt, 0, n * sizeof(int), stream), "memset", err));
+    TRY(orbx_check(cudaMemsetAsync(P.keepCnt, 0, n * P.nlevels * sizeof(int), stream), "memset", err));
+    TRY(orbx_check(cudaMemsetAsync(P.candCnt, 0, n * P.nlevels * sizeof(int), stream), "memset", err));
 
     // cell table and blur tile table
     std::vector<HostCell> cells;
@@ -452,7 +473,7 @@ int Engine::runBatch(int nFrames, float mbf, float mb, int nChunks, std::string&
         return stereo ? runStereo(nFrames, mbf, mb, err) : ORBX_OK;
     }
     TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
-    static const int envStreams = [] { const char* e = getenv("ORBX_RUN_STREAMS"); return e ? atoi(e) : 0; }();
+    const int envStreams = orbx_tune(ORBX_TUNE_RUN_STREAMS);
     const int nStreams = std::min(std::max(envStreams > 0 ? envStreams : 2, 2), std::min(4, nChunks));
     cudaStream_t pool[4] = {stream, stream2, stream3, stream4};
     while ((int)chunkEvents.size() < 4) {
@@ -494,7 +515,7 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
     std::vector<int> bounds{0};
     {
         // (a streamed call has no ramp to shorten: the previous call is still computing while its first chunk uploads)
-        static const int firstDivEnv = [] { const char* e = getenv("ORBX_E2E_FIRST_DIV"); return e ? atoi(e) : 2; }();
+        const int firstDivEnv = orbx_tune(ORBX_TUNE_E2E_FIRST_DIV) > 0 ? orbx_tune(ORBX_TUNE_E2E_FIRST_DIV) : 2;
         const int firstDiv = wait ? firstDivEnv : 1;
         if (firstDiv > 1 && chunkFrames >= 2 * firstDiv && nFrames > chunkFrames) {
             for (int k = 1; k < firstDiv; ++k) bounds.push_back(chunkFrames * k / firstDiv);
@@ -520,8 +541,8 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
     }
     const size_t tight = (size_t)rows * cols, Pk = (size_t)P.maxKp;
     const size_t sideStride = tight * (maxImgs / per);
-    // ORBX_E2E_TRACE=1: timed events around every chunk's copy-in, compute and copy-out, printed to stderr after the call
-    static const bool trace = [] { const char* e = getenv("ORBX_E2E_TRACE"); return e && atoi(e) != 0; }();
+    // orbx_set_tuning("e2e_trace", 1): timed events around every chunk's copy-in, compute and copy-out, printed to stderr after the call
+    const bool trace = orbx_tune(ORBX_TUNE_E2E_TRACE) != 0;
     std::vector<cudaEvent_t> tev;
     auto tmark = [&](cudaStream_t s) {
         if (!trace) return;
@@ -530,8 +551,15 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
         cudaEventRecord(e, s);
         tev.push_back(e);
     };
-    static const int nStreams = [] { const char* e = getenv("ORBX_E2E_STREAMS"); const int v = e ? atoi(e) : 2; return v < 1 ? 1 : v > 4 ? 4 : v; }();
+    const int nStreams = [] { const int t = orbx_tune(ORBX_TUNE_E2E_STREAMS), v = t > 0 ? t : 2; return v > 4 ? 4 : v; }();
     cudaStream_t pool[4] = {stream, stream2, stream3, stream4};
+    if (!chained) {
+        // work still pending on `stream` (an unsynchronised orbx_batch_run / upload) reads the buffers this call overwrites:
+        // the copy stream and the other compute streams start behind it
+        TRY(orbx_check(cudaEventRecord(chunkEvents[0], stream), "event", err));
+        TRY(orbx_check(cudaStreamWaitEvent(upStream, chunkEvents[0], 0), "wait", err));
+        for (int i = 1; i < nStreams; ++i) TRY(orbx_check(cudaStreamWaitEvent(pool[i], chunkEvents[0], 0), "wait", err));
+    }
     tmark(upStream);  // t0
     for (int c = 0; c < nChunks; ++c) {
         const int f0 = bounds[c], n = bounds[c + 1] - bounds[c];

@@ -94,4 +94,20 @@ public:
 };
 
 int orbx_check(cudaError_t e, const char* what, std::string& err);
+
+// Debug/experiment knobs, set through the one entry point orbx_set_tuning() (include/orbx.h); 0 = built-in default.
+// Product code never reads the environment.
+enum OrbxTune {
+    ORBX_TUNE_RUN_STREAMS,     // compute streams of a device-resident run (2..4)
+    ORBX_TUNE_RUN_CHUNKS,      // chunks of a device-resident run
+    ORBX_TUNE_E2E_STREAMS,     // compute streams of the end-to-end pipeline (1..4)
+    ORBX_TUNE_E2E_CHUNKS,      // chunks of an end-to-end call
+    ORBX_TUNE_E2E_FIRST_DIV,   // split of the first chunk of a blocking end-to-end call
+    ORBX_TUNE_E2E_TRACE,       // per-chunk copy/compute times on stderr
+    ORBX_TUNE_FAST_CELLS,      // cells (warps) per FAST CTA: 2 / 4 / 8
+    ORBX_TUNE_FAST_GRID_MULT,  // FAST CTAs launched per resident CTA slot
+    ORBX_TUNE_NUMA_OFF,        // 1: orbx_host_alloc skips the NUMA placement
+    ORBX_TUNE_COUNT
+};
+int orbx_tune(OrbxTune key);
 int orbx_stereo_bin_radius(const float* scale, int nlevels);

@@ -19,7 +19,7 @@
 //     engine addresses the innermost dimension in 16-byte units — by rhMax rows) signalled on an mbarrier;
 //   * pass 1 runs a byte-wise NECESSARY test for a corner at the attempt's threshold on the interior words of the raw
 //     tile, 4 pixels at once (VABSDIFF4 + SWAR compare against the compass points); the surviving pixel
-//     PAIRS are appended to the cell's task list step by step with ballots (row-major order, FAST_ROWMAJOR);
+//     PAIRS are appended to the cell's task list step by step with ballots (row-major order);
 //   * pass 2 runs the exact test on the listed pairs only. A thread owns two horizontally adjacent pixels (even tile
 //     column first) and reads the 17 pairs (ring(x), ring(x+1)) straight from the raw tile (an aligned 16-bit load or two
 //     byte loads, one PRMT each: a widened u16 copy of the ROI cost more than it saved). Min and max commute with
@@ -29,8 +29,7 @@
 //   * strengths stay packed to the end; m - thr goes to a u16 map for m > thr; NMS is driven by the list of non-zero pairs
 //     and uses packed column maxima; maxima are collected in a list and emitted at their row-major rank (reference order);
 //   * one warp per cell, four cells per CTA, long-lived warps: see the kernel.
-#include <cstdlib>
-
+#include "engine.h"
 #include "orbx_dev.cuh"
 #include "orbx_tma.cuh"
 
@@ -120,9 +119,6 @@ __constant__ uint32_t c_recip[32] = {0, 65536, 32768, 21846, 16384, 13108, 10923
 // once per cell instead of twice, there is no CTA barrier (only __syncwarp), and the list counters are warp-uniform
 // registers (no shared atomics). CELLS warps share a CTA only for occupancy (a one-warp CTA caps the SM at 32 warps, less
 // with 7.3 KB of shared memory each); they never talk to each other.
-#ifndef FAST_ROWMAJOR
-#define FAST_ROWMAJOR 1  // 1: row-major task list built with per-step ballots (1.342 against 1.364 ms per 512 KITTI images); 0: per-lane flag registers + one flush
-#endif
 template <int SA, int CELLS>
 __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap,
                                                                     int sliceBytes)
@@ -193,20 +189,17 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
     const int pyq = (int)(((uint32_t)lane * rcpi) >> 16);
     const int pj = jmin + lane - pyq * nwi;
     const unsigned vmask = pyq >= pStep ? 0u : ((4 * pj + 1 >= ca0 && 4 * pj < ca0 + iw) ? 1u : 0u) | ((4 * pj + 3 >= ca0 && 4 * pj + 2 < ca0 + iw) ? 2u : 0u);
-    const uint32_t vmaskX = ((vmask & 1u) ? 0x0000FFFFu : 0u) | ((vmask & 2u) ? 0xFFFF0000u : 0u);
     const uint32_t* ptw0 = tw0 + (pyq + 3) * (BW / 4) + pj;
     int thr = tini, nkept = 0;
 #pragma unroll 1
     for (int attempt = 0;; ++attempt) {
         // ---- pass 1: a cheap NECESSARY test for "corner at thr" on the raw words: any 9 contiguous ring positions contain
         // two ADJACENT compass points (0,4,8,12), so a corner needs (|d0|>t or |d8|>t) and (|d4|>t or |d12|>t). Four
-        // VABSDIFF4 + a SWAR byte compare test 4 pixels at once (fast_pretest4). A lane collects the flags of its pixel
-        // PAIRS in a register — they enter at bits 15 / 31 and move down one bit per step — and appends the survivors once
-        // per 16 steps: one warp scan, no atomics (pairs are aligned to even tile columns; the list order does not matter).
+        // VABSDIFF4 + a SWAR byte compare test 4 pixels at once (fast_pretest4). The surviving pixel PAIRS (aligned to even
+        // tile columns) are appended step by step with ballots: no atomics, and the list comes out in row-major order.
         // bit 7 of each byte of f(x) = ((x & 0x7F..) + K) | x is set iff x > min(thr, 127): exact below 127, still
         // necessary above
         int ntAll = 0;
-#if FAST_ROWMAJOR
         {
             // survivors are appended step by step with ballots, so the task list is in row-major order: the 32 tasks of a
             // pass-2 trip come from one to three tile rows and their ring loads spread over the banks
@@ -241,52 +234,6 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
                 code += 2 * cs;
             }
         }
-#else
-        {
-            const uint32_t K = 0x01010101u * (uint32_t)(0x7F - min(thr, 0x7F));
-            const uint32_t* tw = ptw0;
-            uint32_t code0 = (uint32_t)(pyq * 256 + 2 * pj);
-#pragma unroll 1
-            for (int g0 = 0; g0 < ih; g0 += 16 * pStep) {
-                uint32_t acc = 0;
-                int S = 0;
-                const int lim = min(ih, g0 + 16 * pStep);
-#pragma unroll 1
-                for (int y0s = g0; y0s < lim; y0s += 2 * pStep, S += 2) {
-                    acc >>= 2;
-                    const bool p0 = vmask && y0s + pyq < ih, p1 = vmask && y0s + pStep + pyq < ih;
-                    if (p0) {
-                        const uint32_t* tw1 = p1 ? tw + pStep * (BW / 4) : tw;
-                        const uint32_t m0 = fast_pretest4<BW>(tw, K), m1 = fast_pretest4<BW>(tw1, K);
-                        const uint32_t u0 = ((m0 | (m0 << 8)) >> 1) & 0x40004000u, u1 = (m1 | (m1 << 8)) & 0x80008000u;
-                        acc |= u0 | (p1 ? u1 : 0u);
-                    }
-                    tw += 2 * pStep * (BW / 4);
-                }
-                uint32_t bits = (acc >> (16 - S)) & vmaskX;  // step s at bit s (pair 0) and bit 16+s (pair 1)
-                int incl = __popc(bits);
-                const int mine = incl;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
-                    if (lane >= d) incl += v;
-                }
-                uint16_t* dst = tasks + (ntAll + incl - mine);
-                ntAll += __shfl_sync(0xffffffffu, incl, 31);
-                uint32_t c = code0;
-                const uint32_t cs = (uint32_t)pStep << 8;
-                while (bits) {  // two steps per trip
-                    if (bits & 1) *dst++ = (uint16_t)c;
-                    if (bits & 0x10000u) *dst++ = (uint16_t)(c + 1);
-                    if (bits & 2) *dst++ = (uint16_t)(c + cs);
-                    if (bits & 0x20000u) *dst++ = (uint16_t)(c + cs + 1);
-                    bits = (bits >> 2) & 0x3FFF3FFFu;
-                    c += 2 * cs;
-                }
-                code0 += (uint32_t)(16 * pStep) << 8;
-            }
-        }
-#endif
         __syncwarp();  // task list complete
         // ---- pass 2: the min/max network on the surviving pairs
         const uint32_t thr2 = (uint32_t)thr * 0x10001u;
@@ -388,24 +335,18 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     const int listCap = (((iwMax + 4) / 2) * ihMax + 7) & ~7;
     // shared memory of one cell: tile + strength map + one list (the non-zero pairs overwrite the tasks)
     const int slice = (int)(((size_t)((rhMax * boxW + 127) & ~127) + (size_t)(rhMax - 4) * sa * 2 + (size_t)listCap * 2 + 127) & ~(size_t)127);
-    // cells (= warps) per CTA: ORBX_FAST_CELLS = 2 / 4 / 8 (tools/fast_cells_sweep.sh: 4 is best, 8 loses a third)
-    static int cellsPerCta = 0;
-    if (!cellsPerCta) {
-        const char* e = getenv("ORBX_FAST_CELLS");
-        cellsPerCta = e ? atoi(e) : 4;
-        if (cellsPerCta != 2 && cellsPerCta != 4 && cellsPerCta != 8) cellsPerCta = 4;
-    }
-    // CTAs launched per resident CTA slot (ORBX_FAST_GRID_MULT). 1 = fully persistent with static striding, which loses
+    // cells (= warps) per CTA: tuning key fast_cells = 2 / 4 / 8 (tools/fast_cells_sweep.sh: 4 is best, 8 loses a third)
+    int cellsPerCta = orbx_tune(ORBX_TUNE_FAST_CELLS);
+    if (cellsPerCta != 2 && cellsPerCta != 4 && cellsPerCta != 8) cellsPerCta = 4;
+    // CTAs launched per resident CTA slot (tuning key fast_grid_mult). 1 = fully persistent with static striding, which loses
     // to its own tail (cells differ in cost: 1.54 ms per 512 KITTI images); 16 lets the hardware scheduler balance
     // ~9-cell work packets (1.37 ms); one cell per warp pays the CTA turnover (1.43 ms): tools/fast_grid_sweep.sh
-    static int gridMult = 0, smCount = 0;
-    if (!gridMult) {
-        const char* e = getenv("ORBX_FAST_GRID_MULT");
-        gridMult = e && atoi(e) > 0 ? atoi(e) : 16;
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, dev);
-    }
+    const int gridMult = orbx_tune(ORBX_TUNE_FAST_GRID_MULT) > 0 ? orbx_tune(ORBX_TUNE_FAST_GRID_MULT) : 16;
+    static int smCounts[64] = {0};  // per device ordinal
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int& smCount = smCounts[dev & 63];
+    if (!smCount) cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, dev);
     const size_t smem = (size_t)slice * cellsPerCta;
     const int wanted = (p.cellsTotal * p.imgs + cellsPerCta - 1) / cellsPerCta;
 #define FAST_LAUNCH(SA_, C_)                                                                                                     \

@@ -379,7 +379,6 @@ __global__ void __launch_bounds__(32) orbx_map_resolve_kernel(const FrameDev* fr
     const FrameDev& P = frames[blockIdx.y];
     const MapDev& X = maps[blockIdx.y];
     const int lane = threadIdx.x;
-    const unsigned lt = (1u << lane) - 1;
     for (int w = lane; w < (P.nCur + 31) / 32; w += 32) {
         uint32_t bits = 0;
         if (X.occupied)

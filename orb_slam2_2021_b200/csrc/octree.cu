@@ -357,6 +357,8 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
 }
 
 static size_t octree_smem_bytes(int cap) { return (size_t)cap * 84 + 64; }
+// dynamic + static shared memory of one quadtree CTA for a per-level list capacity (Engine::plan rejects what the SM cannot hold)
+size_t orbx_octree_smem_total(int cap) { return octree_smem_bytes(cap) + sizeof(int) * (OCT_THREADS / 32 + 1 + OCT_CELL_CHUNK + 1 + 3) + 64; }
 
 void orbx_launch_octree(const OrbxParams& p, const void* cellTable, cudaStream_t s)
 {
@@ -364,7 +366,8 @@ void orbx_launch_octree(const OrbxParams& p, const void* cellTable, cudaStream_t
     for (int l = 0; l < p.nlevels; ++l) cap = p.lv[l].keepCap > cap ? p.lv[l].keepCap : cap;
     const size_t smem = octree_smem_bytes(cap);
     if (smem > 32 * 1024)  // static + dynamic above 48 KB needs the opt-in; per-device attribute, set on every such launch
-        cudaFuncSetAttribute(orbx_octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (cudaFuncSetAttribute(orbx_octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return;  // the error stays pending for the caller's cudaGetLastError; no launch on unwritten state
     dim3 grid(p.nlevels, p.imgs);
     orbx_octree_kernel<<<grid, OCT_THREADS, smem, s>>>(p, (const OrbxCellRec*)cellTable);
 }

@@ -122,6 +122,7 @@ void orbx_launch_pyramid(const OrbxParams& p, const int* const* tabs, cudaStream
 void orbx_fast_geometry(const OrbxParams& p, int* boxW, int* rhMax);  // TMA box of the FAST kernel
 void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* levelMaps, cudaStream_t s);
 void orbx_launch_octree(const OrbxParams& p, const void* cellTable, cudaStream_t s);
+size_t orbx_octree_smem_total(int cap);  // shared memory of one quadtree CTA with a per-level list capacity of cap
 void orbx_launch_blur(const OrbxParams& p, const void* tileTable, int nTiles, const void* levelMaps, cudaStream_t s);
 void orbx_launch_describe(const OrbxParams& p, const void* mapsPlain, const void* mapsBlur, cudaStream_t s);
 void orbx_launch_stereo(const OrbxParams& pl, const OrbxParams& pr, const OrbxStereoParams& sp, cudaStream_t s);

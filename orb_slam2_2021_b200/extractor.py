@@ -114,6 +114,11 @@ def compute_stereo_matches(extractor_left, extractor_right, keys_left, desc_left
     return ur, dp
 
 
+def set_tuning(key, value):
+    """orbx_set_tuning: debug/experiment knobs of the library (include/orbx.h lists the keys); 0 = built-in default."""
+    check(lib().orbx_set_tuning(str(key).encode(), int(value)))
+
+
 def host_numa_node():
     """(node, bound) of the last orbx_host_alloc: the NUMA node of the CUDA device it aimed at (-1 unknown, -2 no
     allocation yet) and how it was placed (1 memory policy, 2 allocated from one of the node's cores, 0 plain)."""

@@ -54,7 +54,7 @@ def test_empty_image_is_silent():
     assert len(k) == 0 and d.shape == (0, 32)
     n = ctypes.c_int(-7)
     assert pkg.lib().orbx_extract(e._h, None, 0, 0, 0, None, None, 0, ctypes.byref(n)) == 0
-    assert n.value == -7  # untouched, like src/ORBextractor.cc:1044-1045
+    assert n.value == 0  # src/ORBextractor.cc:1044-1045 returns silently; an out-count is set to 0 rather than left undefined
 
 
 def test_bad_arguments():
@@ -76,3 +76,14 @@ def test_fails_loudly_without_gpu(has_gpu):
     assert ei.value.code == _lib.ERR_CUDA
     with pytest.raises(pkg.OrbxError):
         pkg.StereoFrameBatch(1000, 1.2, 8, 20, 7, 480, 640, 2)
+
+
+def test_quota_beyond_the_quadtree_capacity_is_a_clean_error():
+    """A per-level quota whose node list does not fit one CTA's shared memory is refused with ORBX_ERR_ARG and a text
+    (it used to surface as an opaque launch failure on every extract)."""
+    e = pkg.ORBextractor(20000, 1.2, 8, 20, 7)
+    rc = pkg.lib().orbx_max_keypoints(e._h, 2160, 3840)
+    assert rc == pkg._lib.ERR_ARG
+    assert b"quota" in pkg.lib().orbx_last_error()
+    assert pkg.lib().orbx_max_keypoints(pkg.ORBextractor(12000, 1.2, 8, 20, 7)._h, 2160, 3840) > 12000
+    assert pkg.lib().orbx_max_keypoints(pkg.ORBextractor(3000, 1.2, 1, 20, 7)._h, 480, 640) == pkg._lib.ERR_ARG

@@ -413,16 +413,21 @@ def test_scale_factor_above_two_is_rejected():
 
 
 @pytest.mark.gpu
-def test_pinned_allocation_reports_its_numa_placement(monkeypatch):
+def test_pinned_allocation_reports_its_numa_placement():
     """orbx_host_alloc places pinned buffers on the device's NUMA node where the host says which one that is; the
-    buffer is usable either way, and ORBX_NUMA=0 switches the placement off."""
+    buffer is usable either way, and orbx_set_tuning("numa_off", 1) switches the placement off."""
     a = pkg.PinnedArray((1 << 20,), np.uint8)
     a.array[...] = 7
     node, how = pkg.host_numa_node()
     assert node >= -1 and how in (0, 1, 2)
     assert (how == 0) == (node < 0) or how == 0  # no node -> plain allocation; a known node may still fall back to plain
     assert int(a.array.sum()) == 7 << 20
-    monkeypatch.setenv("ORBX_NUMA", "0")
-    b = pkg.PinnedArray((4096,), np.uint8)
-    b.array[...] = 1
-    assert pkg.host_numa_node() == (-1, 0)
+    pkg.set_tuning("numa_off", 1)
+    try:
+        b = pkg.PinnedArray((4096,), np.uint8)
+        b.array[...] = 1
+        assert pkg.host_numa_node() == (-1, 0)
+    finally:
+        pkg.set_tuning("numa_off", 0)
+    with pytest.raises(pkg.OrbxError):
+        pkg.set_tuning("no_such_knob", 1)

@@ -9,8 +9,8 @@ python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none --csv \
     --log-file gpurun_out/launches.csv python bench.py --frames 64 --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1
 # one full capture of every kernel of one device-resident step (single chunk so that every stage is one launch)
-ORBX_RUN_CHUNKS=1 ncu --set full --import-source on --clock-control none -k regex:orbx_ -c 40 -o gpurun_out/full \
-    python bench.py --frames 64 --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
+ncu --set full --import-source on --clock-control none -k regex:orbx_ -c 40 -o gpurun_out/full \
+    python bench.py --frames 64 --steps 1 --warmup 1 --no-cpu-baseline --tune run_chunks=1 > gpurun_out/ncu_full.log 2>&1
 python tools/measure_configs.py > gpurun_out/configs.json 2> gpurun_out/configs.err
 tail -1 gpurun_out/pytest_gpu.txt
 cat gpurun_out/bench.json | cut -c1-400

@@ -1,5 +1,5 @@
 """Device-resident throughput of the batch engine against the chunk / stream layout of Engine::runBatch.
-One process per setting (the settings are read once per process): python tools/run_streams_sweep.py [chunks streams]."""
+One process per setting (orbx_set_tuning keys run_chunks / run_streams): python tools/run_streams_sweep.py [chunks streams]."""
 import os
 import subprocess
 import sys
@@ -17,6 +17,9 @@ def one():
     from orb_slam2_2021_b200 import synth
 
     W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["kitti"]
+    chunks, streams = int(sys.argv[1]), int(sys.argv[2])
+    pkg.set_tuning("run_chunks", chunks)
+    pkg.set_tuning("run_streams", streams)
     F = 256
     bl, br = synth.stereo_batch(W, H, 8, seed0=1)
     idx = np.arange(F) % 8
@@ -31,7 +34,7 @@ def one():
         for i in range(10):
             b.run(F, bf, bf / fx, sync=(i == 9))
         best = min(best, (time.perf_counter() - t0) / 10)
-    print(f"chunks={os.environ.get('ORBX_RUN_CHUNKS')} streams={os.environ.get('ORBX_RUN_STREAMS')} "
+    print(f"chunks={chunks} streams={streams} "
           f"ms_per_step={best * 1e3:.3f} frames_per_s={F / best:.0f}", flush=True)
 
 
@@ -43,5 +46,4 @@ if __name__ == "__main__":
             for chunks in (2, 3, 4, 6, 8, 12):
                 if chunks < streams:
                     continue
-                env = dict(os.environ, ORBX_RUN_CHUNKS=str(chunks), ORBX_RUN_STREAMS=str(streams))
-                subprocess.run([sys.executable, __file__, str(chunks), str(streams)], env=env, timeout=300)
+                subprocess.run([sys.executable, __file__, str(chunks), str(streams)], timeout=300)
