@@ -87,6 +87,19 @@ int orbx_stereo_match(orbx_extractor* left, orbx_extractor* right, const orbx_ke
                       int n_l, const orbx_keypoint* kps_r, const uint8_t* desc_r, int n_r, float mbf, float mb,
                       float* u_right, float* depth);
 
+/* orbx_stereo_match without any allocation. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same results as orbx_stereo_match; its device scratch is a static array inside the library
+ * (about 0.5 MiB that every GPU loading liborbx.so holds until exit) instead of memory allocated on first use, and the call
+ * issues no cudaMalloc / cudaFree / allocating routine. Limits: n_l, n_r <= ORBX_STEREO_STATIC_MAX_KEYPOINTS and image rows
+ * <= ORBX_STEREO_STATIC_MAX_ROWS, beyond them ORBX_ERR_ARG (use orbx_stereo_match). Every call on a GPU shares the one
+ * array: calls that overlap on the same GPU (two threads, two handle pairs) race; serialise them. */
+#define ORBX_STEREO_STATIC_MAX_KEYPOINTS 8192
+#define ORBX_STEREO_STATIC_MAX_ROWS 4096
+int orbx_stereo_match_static(orbx_extractor* left, orbx_extractor* right, const orbx_keypoint* kps_l, const uint8_t* desc_l,
+                             int n_l, const orbx_keypoint* kps_r, const uint8_t* desc_r, int n_r, float mbf, float mb,
+                             float* u_right, float* depth);
+
 /* ---- frame batches (throughput path; what Frame::Frame(stereo) does, N frames per call) ----------- */
 
 /* One engine for `max_frames` frames of rows x cols. stereo != 0: each frame is a left/right pair and

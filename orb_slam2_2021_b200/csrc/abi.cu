@@ -9,24 +9,13 @@
 
 #include "../../include/orbx.h"
 #include "engine.h"
+#include "handles.h"
 
 static thread_local std::string g_err;
 #define TRY(x) do { int rc_ = (x); if (rc_) return rc_; } while (0)
 static int fail(int code, const char* msg) { g_err = msg; return code; }
 std::string& orbx_err_slot() { return g_err; }  // for frame.cu
 
-struct orbx_extractor {
-    ExtractorConfig cfg;
-    int device = 0;
-    std::unique_ptr<Engine> eng;  // capacity 1, rebuilt when the image size changes
-    bool hasRun = false;
-    // stereo scratch (used when this handle is the LEFT one)
-    float* dU = nullptr; float* dD = nullptr; int* dSad = nullptr; int* dNm = nullptr;
-    uint4* dSorted = nullptr; int* dBin = nullptr;
-    int scratchRows = 0;
-    int scratchKp = 0;
-    uint8_t* hOut = nullptr; size_t hOutCap = 0;  // pinned staging of orbx_extract's results
-};
 
 struct orbx_batch {
     ExtractorConfig cfg;

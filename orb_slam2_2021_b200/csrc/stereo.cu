@@ -302,3 +302,104 @@ void orbx_launch_stereo(const OrbxParams& pl, const OrbxParams& pr, const OrbxSt
     orbx_stereo_match_kernel<<<grid, ST_WARPS * 32, 0, s>>>(pl, pr, sp);
     orbx_stereo_median_kernel<<<sp.frames, 256, 0, s>>>(pl, sp);
 }
+
+// ---- orbx_stereo_match_static: the same match with its scratch in a static device array (no allocation) ----------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). No
+// counterpart in the reference. The scratch of orbx_stereo_match (per-
+// keypoint uRight / depth / SAD, the row-sorted right records, the row-bin table) lives in ONE file-scope array that every
+// GPU loading the library holds until exit; all calls share it, so calls that overlap on a GPU race (see include/orbx.h).
+#include <mutex>
+
+#include "../../include/orbx.h"
+#include "handles.h"
+
+#define ST_STATIC_MAX_KP ORBX_STEREO_STATIC_MAX_KEYPOINTS
+#define ST_STATIC_MAX_ROWS ORBX_STEREO_STATIC_MAX_ROWS
+// layout (byte offsets, each a multiple of 256): uRight, depth, sad [MAX_KP] 4 B each; nMatched; rsorted [MAX_KP][3] uint4; binStart [MAX_ROWS + 1]
+#define ST_OFF_U 0u
+#define ST_OFF_D (ST_OFF_U + 4u * ST_STATIC_MAX_KP)
+#define ST_OFF_SAD (ST_OFF_D + 4u * ST_STATIC_MAX_KP)
+#define ST_OFF_NM (ST_OFF_SAD + 4u * ST_STATIC_MAX_KP)
+#define ST_OFF_SORTED (ST_OFF_NM + 256u)
+#define ST_OFF_BIN (ST_OFF_SORTED + 48u * ST_STATIC_MAX_KP)
+#define ST_STATIC_BYTES (ST_OFF_BIN + ((4u * (ST_STATIC_MAX_ROWS + 1) + 255u) & ~255u))
+static_assert(ST_STATIC_BYTES <= 1u << 20, "the static stereo scratch is meant to stay modest (<= 1 MiB per GPU)");
+
+static __device__ __align__(256) uint8_t g_stereo_static_scratch[ST_STATIC_BYTES];
+
+// In host code the array's name is only a stand-in for the symbol, not a device address: the address is fetched once per
+// device, with that device current, and that pointer is what the kernels get.
+static uint8_t* g_stereo_static_ptr[64] = {nullptr};
+static std::mutex g_stereo_static_mutex;
+
+static int stereo_static_scratch(int device, uint8_t** out, std::string& err)
+{
+    if (device < 0 || device >= 64) { err = "device ordinal outside 0..63"; return ORBX_ERR_ARG; }
+    std::lock_guard<std::mutex> lock(g_stereo_static_mutex);
+    if (!g_stereo_static_ptr[device]) {
+        int rc = orbx_check(cudaSetDevice(device), "cudaSetDevice", err);
+        if (rc) return rc;
+        void* p = nullptr;
+        rc = orbx_check(cudaGetSymbolAddress(&p, g_stereo_static_scratch), "cudaGetSymbolAddress(static stereo scratch)", err);
+        if (rc) return rc;
+        g_stereo_static_ptr[device] = (uint8_t*)p;
+    }
+    *out = g_stereo_static_ptr[device];
+    return ORBX_OK;
+}
+
+extern "C" int orbx_stereo_match_static(orbx_extractor* l, orbx_extractor* r, const orbx_keypoint* kpsL, const uint8_t* descL, int nL,
+                                        const orbx_keypoint* kpsR, const uint8_t* descR, int nR, float mbf, float mb, float* uRight,
+                                        float* depth)
+{
+    std::string& err = orbx_err_slot();
+    auto fail = [&](int code, const char* msg) { err = msg; return code; };
+    if (!l || !r || nL < 0 || nR < 0 || (nL && (!kpsL || !descL || !uRight || !depth)) || (nR && (!kpsR || !descR)))
+        return fail(ORBX_ERR_ARG, "bad arguments");
+    if (!l->eng || !r->eng || !l->hasRun || !r->hasRun) return fail(ORBX_ERR_STATE, "both extractors must have run");
+    Engine &EL = *l->eng, &ER = *r->eng;
+    if (EL.rows != ER.rows || EL.cols != ER.cols || EL.P.nlevels != ER.P.nlevels || l->device != r->device)
+        return fail(ORBX_ERR_STATE, "left/right extractors differ in image size, levels or device");
+    if (nL > EL.P.maxKp || nR > ER.P.maxKp) return fail(ORBX_ERR_ARG, "more keypoints than the extractor can produce");
+    if (nL > ST_STATIC_MAX_KP || nR > ST_STATIC_MAX_KP || EL.rows > ST_STATIC_MAX_ROWS)
+        return fail(ORBX_ERR_ARG, "orbx_stereo_match_static: beyond the static scratch (at most 8192 keypoints per side and 4096 image rows); "
+                                  "use orbx_stereo_match");
+    for (int i = 0; i < nL; ++i)
+        if (kpsL[i].octave < 0 || kpsL[i].octave >= l->cfg.nlevels) return fail(ORBX_ERR_ARG, "left keypoint octave outside 0..nlevels-1");
+    for (int i = 0; i < nR; ++i)
+        if (kpsR[i].octave < 0 || kpsR[i].octave >= l->cfg.nlevels) return fail(ORBX_ERR_ARG, "right keypoint octave outside 0..nlevels-1");
+    for (int i = 0; i < nL; ++i) uRight[i] = depth[i] = -1.f;  // src/Frame.cc:524-525
+    if (nL == 0) return ORBX_OK;
+    uint8_t* scratch = nullptr;
+    int rc = stereo_static_scratch(l->device, &scratch, err);
+    if (rc) return rc;
+#define ST_TRY(x) do { rc = (x); if (rc) return rc; } while (0)
+    ST_TRY(orbx_check(cudaSetDevice(l->device), "cudaSetDevice", err));
+    cudaStream_t s = EL.stream;
+    // the array keeps the previous call's contents: the per-keypoint SAD and the match counter start from a defined state
+    ST_TRY(orbx_check(cudaMemsetAsync(scratch + ST_OFF_SAD, 0xFF, 4u * ST_STATIC_MAX_KP + 256u, s), "clear static scratch", err));
+    // the caller's keypoints/descriptors are authoritative: into the extractors' own (already allocated) output buffers
+    ST_TRY(orbx_check(cudaMemcpyAsync(EL.P.outKp, kpsL, (size_t)nL * 28, cudaMemcpyHostToDevice, s), "H2D kpsL", err));
+    ST_TRY(orbx_check(cudaMemcpyAsync(EL.P.outDesc, descL, (size_t)nL * 32, cudaMemcpyHostToDevice, s), "H2D descL", err));
+    ST_TRY(orbx_check(cudaMemcpyAsync(EL.P.outCnt, &nL, 4, cudaMemcpyHostToDevice, s), "H2D nL", err));
+    if (nR) {
+        ST_TRY(orbx_check(cudaMemcpyAsync(ER.P.outKp, kpsR, (size_t)nR * 28, cudaMemcpyHostToDevice, s), "H2D kpsR", err));
+        ST_TRY(orbx_check(cudaMemcpyAsync(ER.P.outDesc, descR, (size_t)nR * 32, cudaMemcpyHostToDevice, s), "H2D descR", err));
+    }
+    ST_TRY(orbx_check(cudaMemcpyAsync(ER.P.outCnt, &nR, 4, cudaMemcpyHostToDevice, s), "H2D nR", err));
+    OrbxParams pl = EL.P, pr = ER.P;
+    pl.imgs = pr.imgs = 1;
+    OrbxStereoParams sp{};
+    sp.frames = 1; sp.nlevels = pl.nlevels; sp.rows0 = EL.rows; sp.mbf = mbf; sp.mb = mb;
+    sp.maxKp = nL > nR ? nL : nR;  // one frame: only a bound on the counts and the grid of the match kernel
+    sp.imgStep = 1; sp.imgOfsL = 0; sp.imgOfsR = 0;
+    sp.uRight = (float*)(scratch + ST_OFF_U); sp.depth = (float*)(scratch + ST_OFF_D); sp.sad = (int*)(scratch + ST_OFF_SAD);
+    sp.nMatched = (int*)(scratch + ST_OFF_NM); sp.rsorted = (uint4*)(scratch + ST_OFF_SORTED); sp.binStart = (int*)(scratch + ST_OFF_BIN);
+    sp.binR = orbx_stereo_bin_radius(l->cfg.scale.data(), l->cfg.nlevels);
+    orbx_launch_stereo(pl, pr, sp, s);
+    ST_TRY(orbx_check(cudaGetLastError(), "stereo launch", err));
+    ST_TRY(orbx_check(cudaMemcpyAsync(uRight, sp.uRight, (size_t)nL * 4, cudaMemcpyDeviceToHost, s), "D2H uRight", err));
+    ST_TRY(orbx_check(cudaMemcpyAsync(depth, sp.depth, (size_t)nL * 4, cudaMemcpyDeviceToHost, s), "D2H depth", err));
+#undef ST_TRY
+    return EL.sync(err);
+}

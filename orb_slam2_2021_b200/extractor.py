@@ -114,6 +114,23 @@ def compute_stereo_matches(extractor_left, extractor_right, keys_left, desc_left
     return ur, dp
 
 
+def compute_stereo_matches_static(extractor_left, extractor_right, keys_left, desc_left, keys_right, desc_right, mbf, mb):
+    """compute_stereo_matches through orbx_stereo_match_static: same results, device scratch in a static array inside
+    the library (no allocation; at most 8192 keypoints per side and 4096 rows; calls overlapping on one GPU race)."""
+    kl = np.ascontiguousarray(keys_left, dtype=KP_DTYPE)
+    kr = np.ascontiguousarray(keys_right, dtype=KP_DTYPE)
+    dl = np.ascontiguousarray(desc_left, dtype=np.uint8).reshape(-1, 32)
+    dr = np.ascontiguousarray(desc_right, dtype=np.uint8).reshape(-1, 32)
+    if len(kl) != len(dl) or len(kr) != len(dr):
+        raise ValueError("keypoints and descriptors differ in length")
+    n = len(kl)
+    ur = np.full(n, -1, np.float32)
+    dp = np.full(n, -1, np.float32)
+    check(lib().orbx_stereo_match_static(extractor_left._h, extractor_right._h, ptr(kl), ptr(dl), n, ptr(kr), ptr(dr), len(kr),
+                                         float(mbf), float(mb), ptr(ur), ptr(dp)))
+    return ur, dp
+
+
 def set_tuning(key, value):
     """orbx_set_tuning: debug/experiment knobs of the library (include/orbx.h lists the keys); 0 = built-in default."""
     check(lib().orbx_set_tuning(str(key).encode(), int(value)))
