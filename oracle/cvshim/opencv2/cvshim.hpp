@@ -16,6 +16,7 @@
 #include <cassert>
 #include <cmath>
 #include <cstddef>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
@@ -30,6 +31,7 @@
 #define CV_8U 0
 #define CV_8UC1 0
 #define CV_32F 5
+#define CV_Assert(expr) do { if (!(expr)) { std::fprintf(stderr, "CV_Assert failed: %s\n", #expr); std::abort(); } } while (0)
 
 typedef unsigned char uchar;
 
@@ -188,6 +190,7 @@ public:
         for (int y = 0; y < rows; ++y) std::memcpy(m.data + (size_t)y * m.step.v, data + (size_t)y * step.v, (size_t)cols * elemSize());
         return m;
     }
+    inline void copyTo(const class _OutputArray& dst) const;  // cv::Mat::copyTo(OutputArray), defined below the proxies
     void copyTo(Mat& dst) const
     {
         dst.create(rows, cols, type_);
@@ -248,6 +251,12 @@ public:
 };
 typedef const _InputArray& InputArray;
 typedef const _OutputArray& OutputArray;
+inline void Mat::copyTo(const _OutputArray& dst) const
+{
+    dst.create(rows, cols, type_);
+    Mat d = dst.getMat();
+    for (int y = 0; y < rows; ++y) std::memcpy(d.data + (size_t)y * d.step.v, data + (size_t)y * step.v, (size_t)cols * elemSize());
+}
 
 // ---- CV_32F algebra used by src/Frame.cc ----
 inline Mat operator-(const Mat& a, const Mat& b)

@@ -20,7 +20,7 @@ _REF_SRC = "/root/reference/src/ORBextractor.cc"
 
 def build(force=False):
     """Compile the reference translation unit against the shim (only where /root/reference exists)."""
-    if os.path.exists(_REF_SRC) and (force or not os.path.exists(_SO)):
+    if os.path.exists(_REF_SRC) and (force or not os.path.exists(_SO) or not os.path.exists(os.path.join(_HERE, "_ref", "libref_frame_gpu.so"))):
         subprocess.check_call(["make", "-C", _HERE, "-B" if force else "-s", "_ref"])
     return _SO if os.path.exists(_SO) else None
 
@@ -232,3 +232,98 @@ def search_local_points(frame, occupied, valid, proj, level, view_cos, point_des
                                           C.c_void_p]
     n = L.ref_search_local_points(C.byref(fc), None if oc is None else _ptr(oc), C.byref(t), th, nnratio, _ptr(out))
     return out[: frame.c.n], n
+
+
+# ---- the reference's stereo Frame constructor (src/Frame.cc:80-152), on the CPU extractors and on the GPU shim -------------
+_FRAME_ARGS = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float, C.c_float,
+               C.c_float, C.c_int] + [C.c_void_p] * 12
+
+
+def _frame_stereo(fn, h_l, h_r, nlevels, left, right, K4, bf, th_depth, mb_preset, capacity):
+    left, right = _u8(left), _u8(right)
+    assert left.shape == right.shape and left.strides[0] == right.strides[0]
+    K4 = np.ascontiguousarray(K4, np.float32)
+    cap = int(capacity)
+    keys, keys_r, keys_un = (np.zeros(cap, KP_DTYPE) for _ in range(3))
+    desc, desc_r = np.zeros((cap, 32), np.uint8), np.zeros((cap, 32), np.uint8)
+    ur, dp = np.zeros(cap, np.float32), np.zeros(cap, np.float32)
+    gstart, gitems = np.zeros(64 * 48 + 1, np.int32), np.zeros(cap, np.int32)
+    counts, misc, tabs = np.zeros(4, np.int32), np.zeros(16, np.float32), np.zeros(4 * nlevels, np.float32)
+    n = fn(h_l, h_r, _ptr(left), _ptr(right), left.shape[0], left.shape[1], left.strides[0], _ptr(K4), bf, th_depth, mb_preset, cap,
+           _ptr(keys), _ptr(keys_r), _ptr(keys_un), _ptr(desc), _ptr(desc_r), _ptr(ur), _ptr(dp), _ptr(gstart), _ptr(gitems),
+           _ptr(counts), _ptr(misc), _ptr(tabs))
+    if n < 0:
+        raise RuntimeError(f"frame_stereo failed ({n})")
+    nr = int(counts[1])
+    names = ("mb", "mnMinX", "mnMaxX", "mnMinY", "mnMaxY", "mfGridElementWidthInv", "mfGridElementHeightInv", "fx", "fy", "cx", "cy",
+             "invfx", "invfy", "mbf", "mThDepth", "mfScaleFactor")
+    return dict(N=n, mvKeys=keys[:n].copy(), mvKeysRight=keys_r[:nr].copy(), mvKeysUn=keys_un[:n].copy(),
+                mDescriptors=desc[:n].copy(), mDescriptorsRight=desc_r[:nr].copy(), mvuRight=ur[:n].copy(), mvDepth=dp[:n].copy(),
+                mGridStart=gstart, mGridItems=gitems[: gstart[-1]].copy(), counts=counts,
+                statics=dict(zip(names, (float(v) for v in misc))), scaleTables=tabs.reshape(4, nlevels))
+
+
+def frame_stereo(ex_l, ex_r, left, right, K4, bf, th_depth, mb_preset, capacity=20000):
+    """Frame::Frame(imLeft, imRight, ...) — the reference's stereo constructor, unchanged, on the reference's CPU extractors
+    (ex_l / ex_r: RefExtractor). mb_preset: what Frame::mb holds when ComputeStereoMatches reads it (ref_frame_entry.inc)."""
+    L = lib()
+    L.ref_frame_stereo.argtypes = _FRAME_ARGS
+    return _frame_stereo(L.ref_frame_stereo, ex_l._h, ex_r._h, ex_l.nlevels, left, right, K4, bf, th_depth, mb_preset, capacity)
+
+
+_SO_GPU = os.path.join(_HERE, "_ref", "libref_frame_gpu.so")
+_lib_gpu = None
+
+
+def gpu_available():
+    return os.path.exists(_SO_GPU) or os.path.exists(_REF_SRC)
+
+
+def lib_gpu():
+    """oracle/_ref/libref_frame_gpu.so: the reference's Frame.cc (INTEGRATION.md's patch, nothing else) on liborbx.so."""
+    global _lib_gpu
+    if _lib_gpu is None:
+        if build() is None or not os.path.exists(_SO_GPU):
+            raise RuntimeError("oracle/_ref/libref_frame_gpu.so is missing and /root/reference is not here to build it")
+        import orb_slam2_2021_b200 as pkg
+
+        pkg.lib()  # liborbx.so first: the drop-in library resolves its orbx_* symbols against the same loaded copy
+        L = C.CDLL(_SO_GPU)
+        L.refgpu_create.restype = C.c_void_p
+        L.refgpu_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.refgpu_destroy.argtypes = [C.c_void_p]
+        L.refgpu_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.refgpu_frame_stereo.argtypes = _FRAME_ARGS
+        _lib_gpu = L
+    return _lib_gpu
+
+
+class GpuShimExtractor:
+    """ORB_SLAM2::ORBextractorGPU (include/ORBextractorGPU.h) as the reference's Frame.cc sees it: constructed with the
+    reference's arguments, called through the ORBX_WITH_OPENCV overload with the reference's operator() signature."""
+
+    def __init__(self, nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast):
+        self.nfeatures, self.nlevels = nfeatures, nlevels
+        self._h = lib_gpu().refgpu_create(nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast)
+        if not self._h:
+            raise RuntimeError("refgpu_create failed")
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            lib_gpu().refgpu_destroy(h)
+
+    def __call__(self, image):
+        img = _u8(image)
+        cap = self.nfeatures + 64 * self.nlevels + 64
+        kps, desc = np.zeros(cap, KP_DTYPE), np.zeros((cap, 32), np.uint8)
+        n = lib_gpu().refgpu_extract(self._h, _ptr(img), img.shape[0], img.shape[1], img.strides[0], _ptr(kps), _ptr(desc), cap)
+        if n < 0:
+            raise RuntimeError(f"refgpu_extract failed ({n})")
+        return kps[:n].copy(), desc[:n].copy()
+
+
+def frame_stereo_gpu(ex_l, ex_r, left, right, K4, bf, th_depth, mb_preset, capacity=20000):
+    """The same constructor of the same Frame.cc with INTEGRATION.md's patch, on GpuShimExtractors (needs a CUDA device)."""
+    return _frame_stereo(lib_gpu().refgpu_frame_stereo, ex_l._h, ex_r._h, ex_l.nlevels, left, right, K4, bf, th_depth, mb_preset,
+                         capacity)

@@ -18,7 +18,9 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <atomic>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <sys/mman.h>
 #include <vector>
@@ -60,11 +62,29 @@ void* arena_alloc(size_t n)
     return p;
 }
 inline bool in_arena(const void* p) { return g_arena.lo && (const char*)p >= g_arena.lo && (const char*)p < g_arena.hi; }
+
+// A second, process-wide arena for ref_frame_stereo: the reference's stereo constructor runs its two extractions on
+// std::threads of its own (src/Frame.cc:113-116), where the calling thread's arena is out of reach. While it is active,
+// every thread of this library allocates from one range with an atomic bump, so addresses still grow in allocation order
+// inside each thread — which is all the (size, node pointer) sort of one DistributeOctTree call needs.
+std::atomic<bool> g_sharedActive{false};
+std::atomic<size_t> g_sharedUsed{0};
+char* g_sharedLo = nullptr;
+std::mutex g_sharedMutex;  // one ref_frame_stereo at a time
+void* shared_alloc(size_t n)
+{
+    n = (n + 15) & ~(size_t)15;
+    const size_t at = g_sharedUsed.fetch_add(n);
+    if (at + n > kReserve) { std::fprintf(stderr, "ref_wrap: shared arena exhausted\n"); std::abort(); }
+    return g_sharedLo + at;
+}
+inline bool in_shared(const void* p) { return g_sharedLo && (const char*)p >= g_sharedLo && (const char*)p < g_sharedLo + kReserve; }
 }  // namespace
 
 void* operator new(size_t n)
 {
     if (g_arena.active) return arena_alloc(n);
+    if (g_sharedActive.load(std::memory_order_acquire)) return shared_alloc(n);
     void* p = std::malloc(n ? n : 1);
     if (!p) throw std::bad_alloc();
     return p;
@@ -72,7 +92,7 @@ void* operator new(size_t n)
 void* operator new[](size_t n) { return operator new(n); }
 void operator delete(void* p) noexcept
 {
-    if (!p || in_arena(p)) return;  // arena memory is dropped wholesale at the end of the call
+    if (!p || in_arena(p) || in_shared(p)) return;  // arena memory is dropped wholesale at the end of the call
     std::free(p);
 }
 void operator delete[](void* p) noexcept { operator delete(p); }
@@ -143,42 +163,7 @@ float fastAtan2(float y, float x) { return orc_fast_atan2(y, x); }
 
 void KeyPointsFilter::retainBest(std::vector<KeyPoint>&, int) { std::abort(); }  // only ComputeKeyPointsOld (never called)
 
-void undistortPoints(const Mat&, Mat&, const Mat&, const Mat&, const Mat&, const Mat&) { std::abort(); }  // zero distortion only
-
 }  // namespace cv
-
-// ---------------------------------------------------------------- what src/Frame.cc needs from files that cannot be built
-namespace ORB_SLAM2 {
-
-// never reached by the functions the tests call; they only have to link
-cv::Mat MapPoint::GetNormal() { std::abort(); }
-float MapPoint::GetMaxDistanceInvariance() { std::abort(); }
-float MapPoint::GetMinDistanceInvariance() { std::abort(); }
-int MapPoint::PredictScale(const float&, Frame*) { std::abort(); }
-int MapPoint::PredictScale(const float&, KeyFrame*) { std::abort(); }
-void MapPoint::AddObservation(KeyFrame*, size_t) { std::abort(); }
-int MapPoint::GetIndexInKeyFrame(KeyFrame*) { std::abort(); }
-bool MapPoint::IsInKeyFrame(KeyFrame*) { std::abort(); }
-void MapPoint::Replace(MapPoint*) { std::abort(); }
-cv::Mat KeyFrame::GetCameraCenter() { std::abort(); }
-cv::Mat KeyFrame::GetRotation() { std::abort(); }
-cv::Mat KeyFrame::GetTranslation() { std::abort(); }
-void KeyFrame::AddMapPoint(MapPoint*, const size_t&) { std::abort(); }
-std::set<MapPoint*> KeyFrame::GetMapPoints() { std::abort(); }
-std::vector<MapPoint*> KeyFrame::GetMapPointMatches() { std::abort(); }
-MapPoint* KeyFrame::GetMapPoint(const size_t&) { std::abort(); }
-std::vector<size_t> KeyFrame::GetFeaturesInArea(const float&, const float&, const float&) const { std::abort(); }
-bool KeyFrame::IsInImage(const float&, const float&) const { std::abort(); }
-// Converter::toDescriptorVector, src/Converter.cc:27-35: one 1x32 row header per descriptor
-std::vector<cv::Mat> Converter::toDescriptorVector(const cv::Mat& Descriptors)
-{
-    std::vector<cv::Mat> vDesc;
-    vDesc.reserve(Descriptors.rows);
-    for (int j = 0; j < Descriptors.rows; j++) vDesc.push_back(Descriptors.row(j));
-    return vDesc;
-}
-
-}  // namespace ORB_SLAM2
 
 // ---------------------------------------------------------------- C entry points (ctypes)
 namespace {
@@ -188,7 +173,32 @@ struct ArenaScope {  // operator new comes from the arena while the reference ru
 };
 }  // namespace
 
+#include "ref_frame_entry.inc"
+
 extern "C" {
+
+// The reference's stereo Frame constructor (src/Frame.cc:80-152), unchanged, on the reference's CPU extractors: see
+// ref_frame_entry.inc. Returns N (>= 0), -1 when `capacity` is too small, -2 when the stereo vectors were not sized.
+int ref_frame_stereo(void* hL, void* hR, const uint8_t* imL, const uint8_t* imR, int rows, int cols, int stride, const float* K4,
+                     float bf, float thDepth, float mbPreset, int capacity, orc_keypoint* keys, orc_keypoint* keysRight,
+                     orc_keypoint* keysUn, uint8_t* desc, uint8_t* descRight, float* uRight, float* depth, int* gridStart,
+                     int* gridItems, int* counts, float* misc, float* scaleTables)
+{
+    std::lock_guard<std::mutex> lock(g_sharedMutex);
+    if (!g_sharedLo) {
+        void* m = mmap(nullptr, kReserve, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_NORESERVE, -1, 0);
+        if (m == MAP_FAILED) { std::fprintf(stderr, "ref_wrap: shared arena reservation failed\n"); std::abort(); }
+        g_sharedLo = (char*)m;
+    }
+    g_sharedUsed.store(0);
+    g_sharedActive.store(true, std::memory_order_release);
+    const FrameStereoOut o{keys, keysRight, keysUn, desc, descRight, uRight, depth, gridStart, gridItems, counts, misc, scaleTables};
+    const int rc = frame_stereo_run((ORB_SLAM2::ORBextractor*)hL, (ORB_SLAM2::ORBextractor*)hR, imL, imR, rows, cols, stride, K4, bf,
+                                    thDepth, mbPreset, capacity, o);
+    g_sharedActive.store(false, std::memory_order_release);
+    g_sharedUsed.store(0);
+    return rc;
+}
 
 void* ref_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST)
 {

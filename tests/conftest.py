@@ -37,6 +37,18 @@ def _built():
     oracle.build()
 
 
+@pytest.fixture(scope="session", autouse=True)
+def _reference_anchor_present():
+    """On a GPU box the parity anchor (oracle/_ref: the reference's own translation units, built in the container that has
+    /root/reference and shipped with the snapshot) must be there: its absence is a failure, not a silent skip of every
+    reference-pin test."""
+    if _has_gpu():
+        from oracle import ref
+
+        if not (ref.available() and ref.gpu_available()):
+            pytest.fail("oracle/_ref is missing on a GPU box: run `make -C oracle _ref` where /root/reference exists", pytrace=False)
+
+
 def pytest_collection_modifyitems(config, items):
     if _has_gpu():
         return
