@@ -5,7 +5,8 @@
   python bench.py --impl reference --gpus N --steps K ...  # the CPU implementation on the host cores
 
 One "step" = one pass of the hot path over a batch of `--frames` synthetic KITTI-shaped stereo frames
-per GPU (weak scaling: per-GPU work fixed). `value` = frames/s with the batch resident in HBM;
+per GPU (weak scaling: per-GPU work fixed; `--scaling strong --total-frames 4096` is BASELINE.json's config 4 as written:
+4096 frames split over the N GPUs, 4096/N per GPU and step). `value` = frames/s with the batch resident in HBM;
 `e2e` = the same through the public API with pinned HOST buffers (H2D + kernels + D2H of every step inside the
 timed region): `e2e.value` through the streaming call (orbx_batch_process_async per step, one orbx_batch_wait at the
 end), `e2e.blocking_call` through orbx_batch_process, which returns with each step's results in host memory.
@@ -27,7 +28,7 @@ sys.path.insert(0, ROOT)
 METRIC = "KITTI-stereo frames/sec (ORB extract+stereo match)"
 UNIT = "frames/s"
 CONFIG_NAME = "kitti"
-DISTINCT = 8  # distinct synthetic frames, tiled to the batch size
+DISTINCT = 256  # distinct synthetic frames per GPU (= the default batch: no frame repeats inside a step); larger batches tile them
 
 
 def parse_args():
@@ -38,6 +39,11 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=256, help="stereo frames per GPU per step")
     ap.add_argument("--config", default=CONFIG_NAME)
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --frames per GPU and step; strong: --total-frames split over the GPUs (config 4 of BASELINE.json)")
+    ap.add_argument("--total-frames", type=int, default=4096, help="frames per step over all GPUs with --scaling strong")
+    ap.add_argument("--distinct", type=int, default=DISTINCT, help="distinct synthetic frames per GPU (tiled to the batch)")
+    ap.add_argument("--no-latency", action="store_true", help="skip the single-frame latency block")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tune", action="append", default=[], metavar="KEY=VALUE",
                     help="orbx_set_tuning knob for experiments (tools/*_sweep.sh), e.g. --tune fast_cells=2")
@@ -68,14 +74,38 @@ def b_alg_per_frame(W, H, nlevels, sf, n_left, n_right):
     return 2 * W * H + 2 * sum(w * h for w, h in lv[1:]) + 60 * (n_left + n_right) + 8 * n_left
 
 
-def make_frames(cfg, n, seed0=1000):
+def make_frames(cfg, n, seed0=1000, distinct=DISTINCT, threads=None):
+    """n stereo frames built from min(n, distinct) distinct seeded synthetic ones (generated on a few host threads)."""
+    from concurrent.futures import ThreadPoolExecutor
+
     from orb_slam2_2021_b200 import synth
 
     W, H = cfg[0], cfg[1]
-    d = min(DISTINCT, n)
-    bl, br = synth.stereo_batch(W, H, d, seed0=seed0)
+    d = max(1, min(distinct, n))
+    bl, br = np.empty((d, H, W), np.uint8), np.empty((d, H, W), np.uint8)
+
+    def one(k):
+        bl[k], br[k] = synth.stereo_pair(W, H, seed0 + 2 * k)
+
+    with ThreadPoolExecutor(threads or max(1, min(8, host_threads()))) as ex:
+        list(ex.map(one, range(d)))
+    if d == n:
+        return bl, br
     idx = np.arange(n) % d
     return bl[idx], br[idx]
+
+
+def workload(args, cfg):
+    """The `config` both arms print (identical, so the two lines describe the same workload)."""
+    W, H, nf, nl, sf, ini, mn = cfg[:7]
+    c = {"workload": f"{args.config}: {W}x{H} stereo, {nf} features, {nl} levels, scale {sf}, FAST {ini}/{mn}; "
+                     f"extract L + extract R + ComputeStereoMatches per frame",
+         "scaling": args.scaling,
+         "frames_per_gpu_per_step": args.frames if args.scaling == "weak" else None,
+         "total_frames_per_step": args.total_frames if args.scaling == "strong" else None,
+         "l2": "no flush: the per-step working set of a GPU (several GB) exceeds the 126 MB L2; the CPU arm streams frames "
+               "from host memory"}
+    return c
 
 
 class ClockSampler:
@@ -162,6 +192,49 @@ def cpu_run(cfg, left, right, threads):
     return dt, sum(r[0] for r in res), sum(r[1] for r in res)
 
 
+def primitive_timing(cfg, fps, threads):
+    """How much of the CPU arm is the scalar stand-ins for OpenCV's image primitives, and what a real OpenCV build would
+    do instead: the same primitive calls of one image (7 resizes, FAST on every level at the initial threshold, 8 Gaussian
+    blurs) timed once through the oracle's scalar restatements (what oracle/_ref runs) and once through cv2 (SIMD, one
+    thread). `estimated_real_opencv` replaces the one by the other in the measured per-frame time; the GPU/CPU ratios of
+    this bench are upper bounds by that factor."""
+    try:
+        import cv2
+
+        from oracle import oracle as O
+        from orb_slam2_2021_b200 import synth
+
+        W, H, nf, nl, sf, ini, mn = cfg[:7]
+        img = synth.synth(W, H, 12345)
+        cv2.setNumThreads(1)
+
+        def run(resize, fast, blur):
+            t0 = time.perf_counter()
+            lv = [img]
+            for w, h in level_sizes(W, H, nl, sf)[1:]:
+                lv.append(resize(lv[-1], w, h))
+            for a in lv:
+                fast(a)
+                blur(a)
+            return 1e3 * (time.perf_counter() - t0)
+
+        fd = cv2.FastFeatureDetector_create(int(ini), True)
+        t_cv = min(run(lambda a, w, h: cv2.resize(a, (w, h), interpolation=cv2.INTER_LINEAR), lambda a: fd.detect(a),
+                       lambda a: cv2.GaussianBlur(a, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)) for _ in range(3))
+        t_sc = min(run(lambda a, w, h: O.resize_linear(a, w, h), lambda a: O.fast9(a, int(ini)), lambda a: O.gaussian7(a))
+                   for _ in range(2))
+        per_frame_ms = 1e3 * threads / fps  # one thread's time per stereo frame in the measured arm
+        est = max(per_frame_ms - 2 * t_sc + 2 * t_cv, 2 * t_cv)
+        return {"primitives": "scalar stand-ins for resize / FAST / GaussianBlur (no OpenCV C++ in the image): the ratio against "
+                              "this arm is an upper bound",
+                "scalar_primitives_ms_per_image": round(t_sc, 3), "opencv_primitives_ms_per_image": round(t_cv, 3),
+                "measured_ms_per_frame_per_thread": round(per_frame_ms, 3),
+                "estimated_real_opencv": {"value": threads * 1e3 / est, "unit": UNIT,
+                                          "how": "measured per-frame time minus 2 x scalar primitives plus 2 x cv2 primitives, same threads"}}
+    except Exception as e:  # the estimate is an annotation; the measured arm stands without it
+        return {"primitives": f"scalar stand-ins (primitive timing unavailable: {e})"}
+
+
 def host_threads():
     try:
         return max(1, len(os.sched_getaffinity(0)))
@@ -189,7 +262,7 @@ def reference_arm(args, rank):
     cfg = synth.CONFIGS[args.config]
     threads = host_threads()
     n = max(8, 2 * threads)
-    left, right = make_frames(cfg, n)
+    left, right = make_frames(cfg, n, distinct=n)
     for _ in range(min(args.warmup, 1)):
         cpu_run(cfg, left[:threads], right[:threads], threads)
     total = 0.0
@@ -200,12 +273,13 @@ def reference_arm(args, rank):
     kind, what = cpu_kind()
     return {
         "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": f"{args.config}: {cfg[0]}x{cfg[1]} stereo, {cfg[2]} features, {cfg[3]} levels; "
-                               f"extract L + extract R + ComputeStereoMatches", "frames_per_step": n},
-        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": threads, "kind": kind,
-                         "sample": f"{n} stereo frames per step, frame-parallel on {threads} threads ({cpu_model()}); {what}"},
+        "config": workload(args, cfg),
+        "sample_frames_per_step": n,
+        "cpu_baseline": dict({"value": fps, "unit": UNIT, "cores": threads, "kind": kind,
+                              "sample": f"{n} distinct stereo frames per step, frame-parallel on {threads} threads ({cpu_model()}); {what}"},
+                             **primitive_timing(cfg, fps, threads)),
         "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
 
@@ -222,6 +296,64 @@ def stage_alg_bytes(cfg, n_imgs, n_frames, kp_per_img, cand_per_img, cells_per_i
         "describe": n_imgs * kp_per_img * (709 + 512 + 8 + 60),      # disc + samples + kept record in, kp+desc out
         "stereo": n_frames * kp_per_img * (28 + 32 + 10 * 60 + 121 + 231 + 12),
     }
+
+
+def single_frame_latency(pkg, cfg, left, right, device, n=1000):
+    """One stereo frame at a time through the C-ABI, wall clock per call from host images to host results, p50 / p99 over
+    n frames (16 distinct): orbx_stereo_frame (one call per frame; pageable and page-locked input images), and the
+    reference's own sequence orbx_extract (left), orbx_extract (right), orbx_stereo_match_resident — serial here, the
+    reference runs the two extractions on two threads (src/Frame.cc:113-116)."""
+    import ctypes as C
+
+    from orb_slam2_2021_b200._lib import KP_DTYPE, lib, ptr
+
+    W, H, nf, nl, sf, ini, mn, fx, bf = cfg
+    d = min(16, len(left))
+    fl, fr = pkg.ORBextractor(nf, sf, nl, ini, mn, device), pkg.ORBextractor(nf, sf, nl, ini, mn, device)
+    el, er = pkg.ORBextractor(nf, sf, nl, ini, mn, device), pkg.ORBextractor(nf, sf, nl, ini, mn, device)
+    L = lib()
+    cap = L.orbx_max_keypoints(fl._h, H, W)
+    kl, kr = np.zeros(cap, KP_DTYPE), np.zeros(cap, KP_DTYPE)
+    dl, dr = np.zeros((cap, 32), np.uint8), np.zeros((cap, 32), np.uint8)
+    ur, dp = np.zeros(cap, np.float32), np.zeros(cap, np.float32)
+    nL, nR = C.c_int(0), C.c_int(0)
+    pin_l, pin_r = pkg.PinnedArray((d, H, W), np.uint8), pkg.PinnedArray((d, H, W), np.uint8)
+    pin_l.array[...], pin_r.array[...] = left[:d], right[:d]
+    args = (ptr(kl), ptr(dl), C.byref(nL), ptr(kr), ptr(dr), C.byref(nR), cap, ptr(ur), ptr(dp))
+    mbf, mb = float(bf), float(bf / fx)
+
+    def pct(ts):
+        a = np.sort(np.asarray(ts)) * 1e3
+        return {"p50_ms": float(a[len(a) // 2]), "p99_ms": float(a[min(len(a) - 1, int(len(a) * 0.99))]), "mean_ms": float(a.mean())}
+
+    def frame(src_l, src_r):
+        def f(i):
+            a, b = src_l[i % d], src_r[i % d]
+            rc = L.orbx_stereo_frame(fl._h, fr._h, ptr(a), ptr(b), H, W, W, W, mbf, mb, *args)
+            assert rc == 0 and nL.value > 0
+        return f
+
+    def seq(i):
+        a, b = left[i % d], right[i % d]
+        assert L.orbx_extract(el._h, ptr(a), H, W, W, ptr(kl), ptr(dl), cap, C.byref(nL)) == 0
+        assert L.orbx_extract(er._h, ptr(b), H, W, W, ptr(kr), ptr(dr), cap, C.byref(nR)) == 0
+        assert L.orbx_stereo_match_resident(el._h, er._h, nL.value, nR.value, mbf, mb, ptr(ur), ptr(dp)) == 0
+
+    res = {}
+    for name, fn, cnt in (("stereo_frame", frame(left, right), n), ("stereo_frame_pinned_input", frame(pin_l.array, pin_r.array), n),
+                          ("extract_extract_match", seq, max(n // 4, 50))):
+        for i in range(20):
+            fn(i)
+        ts = []
+        for i in range(cnt):
+            t0 = time.perf_counter()
+            fn(i)
+            ts.append(time.perf_counter() - t0)
+        res[name] = dict(pct(ts), frames=cnt)
+    res["single_frame_ms"] = res["stereo_frame"]["p50_ms"]
+    res["api"] = ("orbx_stereo_frame through the C-ABI: host images in (pageable; page-locked in stereo_frame_pinned_input), host "
+                  "keypoints / descriptors / uRight / depth of both sides out, one call per frame")
+    return res
 
 
 def ours_arm(args, rank, local_rank, world):
@@ -256,8 +388,14 @@ def ours_arm(args, rank, local_rank, world):
         pkg.set_tuning(k, int(v))
     cfg = synth.CONFIGS[args.config]
     W, H, nf, nl, sf, ini, mn, fx, bf = cfg
-    F = args.frames
-    left, right = make_frames(cfg, F, seed0=1000 + 16 * rank)
+    if args.scaling == "strong":
+        if args.total_frames % world:
+            raise SystemExit("--total-frames must be a multiple of the number of GPUs")
+        F = args.total_frames // world  # this rank's contiguous shard (orb_slam2_2021_b200/shard.py: frames are independent)
+    else:
+        F = args.frames
+    left, right = make_frames(cfg, F, seed0=1000 + 2 * args.distinct * rank, distinct=args.distinct,
+                              threads=max(1, host_threads() // max(world, 1)))
     b = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, F, stereo=True, device=local_rank)
     stream = torch.cuda.ExternalStream(b.stream, device=local_rank)
     mbf, mb = bf, bf / fx
@@ -321,6 +459,32 @@ def ours_arm(args, rank, local_rank, world):
     barrier()
     assert int(out2["n_left"].sum()) + int(out2["n_right"].sum()) == n_l + n_r, "streamed results differ from the device-resident run"
     clocks = sampler.stop() if rank == 0 else None
+    # ---- raw host-link ceiling at this N (tools/link_ceiling.py in short): the same bytes per step, pinned memory, one
+    # cudaMemcpyAsync per direction on two streams, no kernels, all ranks at once; max over ranks
+    link_ms = None
+    try:
+        nin, nout = int(left.nbytes + right.nbytes), int(sum(v.nbytes for v in out.values()))
+        h_in = torch.empty(nin, dtype=torch.uint8, pin_memory=True)
+        h_out = torch.empty(nout, dtype=torch.uint8, pin_memory=True)
+        d_in = torch.empty(nin, dtype=torch.uint8, device="cuda")
+        d_out = torch.zeros(nout, dtype=torch.uint8, device="cuda")
+        s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+        ksteps = max(4, min(args.steps, 10))
+        for rep in range(2):
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(ksteps):
+                with torch.cuda.stream(s_up):
+                    d_in.copy_(h_in, non_blocking=True)
+                with torch.cuda.stream(s_dn):
+                    h_out.copy_(d_out, non_blocking=True)
+            torch.cuda.synchronize()
+            link_ms = 1e3 * (time.perf_counter() - t0) / ksteps
+        link_ms = reduce(link_ms, dist.ReduceOp.MAX if dist else None)
+        del h_in, h_out, d_in, d_out
+    except Exception as e:  # an annotation of the e2e number; never fails the bench
+        print(f"link probe failed: {e}", file=sys.stderr)
+    barrier()
     h2d = int(left.nbytes + right.nbytes)
     d2h = int(sum(v.nbytes for v in out.values()))
     checksum = int(out["n_left"].sum()) + int(out["n_right"].sum())
@@ -332,6 +496,9 @@ def ours_arm(args, rank, local_rank, world):
     if rank != 0:
         return None
 
+    latency = None
+    if not args.no_latency:
+        latency = single_frame_latency(pkg, cfg, left, right, local_rank)
     frames_total = F * world
     value = frames_total * args.steps / (ms_max / 1e3)
     e2e = frames_total * args.steps / (e2e_ms / 1e3)
@@ -348,22 +515,22 @@ def ours_arm(args, rank, local_rank, world):
     # DRAM traffic of the dominant stage per launch, from the committed ncu capture (profiles/), scaled to this batch
     traffic, traffic_src = None, None
     try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        name = next(n for n in ("r02_traffic.json", "r01_traffic.json") if os.path.exists(os.path.join(ROOT, "profiles", n)))
+        tj = json.load(open(os.path.join(ROOT, "profiles", name)))
         if args.config == "kitti":
             traffic = tj["stages"][top]["dram_bytes_per_frame"] * F
-            traffic_src = "profiles/r01_traffic.json (ncu dram__bytes_read+write per stereo frame x frames per launch)"
+            traffic_src = f"profiles/{name} (ncu dram__bytes_read+write per stereo frame x frames per launch)"
     except Exception:
         pass
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
         "dtype": "u8", "data": "synthetic",
-        "config": {"workload": f"{args.config}: {W}x{H} stereo, {nf} features, {nl} levels, FAST {ini}/{mn}; "
-                               f"extract L + extract R + ComputeStereoMatches",
-                   "frames_per_gpu_per_step": F, "frames_per_step": frames_total,
-                   "l2": f"no flush: per-step working set {b.device_bytes / 2**20:.0f} MiB per GPU exceeds the 126 MB L2",
-                   "keypoints_per_frame": [tot_l / frames_total, tot_r / frames_total],
-                   "matches_per_frame": tot_m / frames_total},
+        "config": workload(args, cfg),
+        "run": {"frames_per_gpu_per_step": F, "frames_per_step": frames_total, "distinct_frames_per_gpu": min(args.distinct, F),
+                "device_bytes_per_gpu": b.device_bytes,
+                "keypoints_per_frame": [tot_l / frames_total, tot_r / frames_total],
+                "matches_per_frame": tot_m / frames_total},
         # headline: the streaming call (a continuous feed of batches, which is what a throughput figure describes); the
         # blocking call, which pays the pipeline ramp and drain on every step, is reported beside it
         "e2e": {"value": frames_total * args.steps / (stream_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
@@ -373,7 +540,13 @@ def ours_arm(args, rank, local_rank, world):
                 "blocking_call": {"value": e2e, "ms_per_step": e2e_ms / args.steps,
                                   "api": "orbx_batch_process: returns with the step's results in host memory"},
                 # rank 0's pinned buffers: NUMA node of its GPU, and whether orbx_host_alloc could place them there
-                "host_numa": dict(zip(("node", "bound"), pkg.host_numa_node()))},
+                "host_numa": dict(zip(("node", "bound"), pkg.host_numa_node())),
+                # what the host link alone allows at this N: the same bytes per step as plain pinned copies without kernels
+                "link_ceiling_fps": (frames_total / (link_ms / 1e3)) if link_ms else None,
+                "frac_of_link": (link_ms / (stream_ms / args.steps)) if link_ms else None,
+                "link_probe": "pinned cudaMemcpyAsync H2D + D2H of the step's bytes on two streams, no kernels, all ranks at once "
+                              "(tools/link_ceiling.py; profiles/r02_link_ceiling.json)"},
+        "latency": latency,
         "gpu_launches": launches_per_step * args.steps,
         "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
@@ -386,11 +559,12 @@ def ours_arm(args, rank, local_rank, world):
     if world == 1 and not args.no_cpu_baseline:
         threads = host_threads()
         n = max(16, 2 * threads)
-        cl, cr = make_frames(cfg, n)
+        cl, cr = left[:n], right[:n]
         dt, _, _ = cpu_run(cfg, cl, cr, threads)
         kind, what = cpu_kind()
-        line["cpu_baseline"] = {"value": n / dt, "unit": UNIT, "cores": threads, "kind": kind,
-                                "sample": f"{n} stereo frames, frame-parallel on {threads} threads ({cpu_model()}); {what}"}
+        line["cpu_baseline"] = dict({"value": n / dt, "unit": UNIT, "cores": threads, "kind": kind,
+                                     "sample": f"the first {n} stereo frames of the batch, frame-parallel on {threads} threads "
+                                               f"({cpu_model()}); {what}"}, **primitive_timing(cfg, n / dt, threads))
     return line
 
 

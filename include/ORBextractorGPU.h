@@ -103,13 +103,21 @@ private:
 };
 
 /* Frame::ComputeStereoMatches (src/Frame.cc:522-700) on what the Frame holds: mvKeys/mvKeysRight,
- * mDescriptors/mDescriptorsRight (N x 32 bytes), mbf, mb -> mvuRight, mvDepth (sized N, -1 = no match). */
+ * mDescriptors/mDescriptorsRight (N x 32 bytes), mbf, mb -> mvuRight, mvDepth (sized N, -1 = no match).
+ * keysAreTheExtractorsOwn: the arrays are the unmodified results of the extractors' last operator() (true inside
+ * Frame::Frame); pass false after editing keypoints or descriptors. */
 inline void ComputeStereoMatchesGPU(ORBextractorGPU& left, ORBextractorGPU& right, const orbx_keypoint* keysL, const uint8_t* descL,
                                     int nL, const orbx_keypoint* keysR, const uint8_t* descR, int nR, float mbf, float mb,
-                                    std::vector<float>& mvuRight, std::vector<float>& mvDepth)
+                                    std::vector<float>& mvuRight, std::vector<float>& mvDepth, bool keysAreTheExtractorsOwn = true)
 {
     mvuRight.assign(nL, -1.0f);
     mvDepth.assign(nL, -1.0f);
+    /* Inside Frame::Frame the keypoints and descriptors are exactly what the two operator() calls just returned and what
+     * the extractors still hold on the device: match there without uploading anything. Anything else (other counts, an
+     * extract in between) makes the resident call refuse, and the caller's arrays go up as usual. */
+    if (keysAreTheExtractorsOwn &&
+        orbx_stereo_match_resident(left.handle(), right.handle(), nL, nR, mbf, mb, mvuRight.data(), mvDepth.data()) == ORBX_OK)
+        return;
     if (orbx_stereo_match(left.handle(), right.handle(), keysL, descL, nL, keysR, descR, nR, mbf, mb, mvuRight.data(),
                           mvDepth.data()) != ORBX_OK)
         throw std::runtime_error(std::string("orbx_stereo_match: ") + orbx_last_error());

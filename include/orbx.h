@@ -87,6 +87,26 @@ int orbx_stereo_match(orbx_extractor* left, orbx_extractor* right, const orbx_ke
                       int n_l, const orbx_keypoint* kps_r, const uint8_t* desc_r, int n_r, float mbf, float mb,
                       float* u_right, float* depth);
 
+/* The same match on what the two extractors left on the device: nothing is uploaded. For the reference's own flow —
+ * Frame::ExtractORB on two threads (src/Frame.cc:113-116), then Frame::ComputeStereoMatches (:125) on the keypoints and
+ * descriptors those calls returned, unmodified. n_l / n_r must equal the counts of the handles' last orbx_extract
+ * (ORBX_ERR_STATE otherwise, also after an orbx_stereo_match that uploaded other keypoints: use orbx_stereo_match then). */
+int orbx_stereo_match_resident(orbx_extractor* left, orbx_extractor* right, int n_l, int n_r, float mbf, float mb,
+                               float* u_right, float* depth);
+
+/* One stereo frame in ONE call: what Frame::Frame(stereo) does at src/Frame.cc:113-125 — ExtractORB on the left and the right
+ * image (both at once, as the reference's two threads) and ComputeStereoMatches — for a caller that can hand over both
+ * images together. Both images go up through pinned staging, every kernel runs on both images in one launch, the match
+ * reads the device-resident keypoints and descriptors, all results come down in one go, and from the second call on the
+ * whole sequence replays as one CUDA graph. `left` and `right` must have been created with the same parameters on the same
+ * device; the left handle owns the frame's device memory. Outputs as orbx_extract (per side, `capacity` records each) and
+ * orbx_stereo_match (n_l floats each). Afterwards orbx_pyramid_level on either handle returns this frame's levels;
+ * orbx_stereo_match* need a new orbx_extract on both handles first (ORBX_ERR_STATE). */
+int orbx_stereo_frame(orbx_extractor* left, orbx_extractor* right, const uint8_t* image_left, const uint8_t* image_right,
+                      int rows, int cols, size_t stride_left, size_t stride_right, float mbf, float mb,
+                      orbx_keypoint* kps_l, uint8_t* desc_l, int* n_l, orbx_keypoint* kps_r, uint8_t* desc_r, int* n_r,
+                      int capacity, float* u_right, float* depth);
+
 /* orbx_stereo_match without any allocation. NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
  * Same arguments, same results as orbx_stereo_match; its device scratch is a static array inside the library

@@ -51,6 +51,8 @@ SIGNATURES = {
     "orbx_pyramid_level_size": (_i, [_vp, _i, _ip, _ip]),
     "orbx_pyramid_level": (_i, [_vp, _i, _vp, _sz]),
     "orbx_stereo_match": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _vp, _vp]),
+    "orbx_stereo_match_resident": (_i, [_vp, _vp, _i, _i, _f, _f, _vp, _vp]),
+    "orbx_stereo_frame": (_i, [_vp, _vp, _vp, _vp, _i, _i, _sz, _sz, _f, _f, _vp, _vp, _ip, _vp, _vp, _ip, _i, _vp, _vp]),
     "orbx_stereo_match_static": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _vp, _vp]),
     "orbx_batch_create": (_i, [_i, _f, _i, _i, _i, _i, _i, _i, _i, _i, C.POINTER(_vp)]),
     "orbx_batch_destroy": (None, [_vp]),

@@ -57,6 +57,7 @@ extern "C" void orbx_destroy(orbx_extractor* e)
     if (!e) return;
     if (e->dU) { cudaSetDevice(e->device); cudaFree(e->dU); cudaFree(e->dD); cudaFree(e->dSad); cudaFree(e->dNm); cudaFree(e->dSorted); cudaFree(e->dBin); }
     if (e->hOut) { cudaSetDevice(e->device); cudaFreeHost(e->hOut); }
+    if (e->pairPeer && e->pairPeer->view == e->pair.get()) e->pairPeer->view = nullptr;  // the peer's view dies with this engine
     delete e;
 }
 
@@ -94,35 +95,24 @@ extern "C" int orbx_extract(orbx_extractor* e, const uint8_t* image, int rows, i
     if (rows < 0 || cols < 0 || stride < (size_t)cols || !kps || !desc || !n) return fail(ORBX_ERR_ARG, "bad arguments");
     if (!e->eng || e->eng->rows != rows || e->eng->cols != cols) {
         e->hasRun = false;
+        if (e->view == e->eng.get()) e->view = nullptr;
         std::unique_ptr<Engine> ne(new Engine());
         TRY(ne->init(e->cfg, rows, cols, 1, false, e->device, g_err));
         e->eng = std::move(ne);
     }
     Engine& E = *e->eng;
-    TRY(E.uploadSingle(image, stride, g_err));
-    TRY(E.runExtract(1, g_err));
-    // One round trip: the count and (speculatively) every record the caller's buffers can take come down together into
-    // pinned staging; the second dependent copy + synchronisation of a count-first protocol costs more than the bytes.
-    const int take = capacity < E.P.maxKp ? capacity : E.P.maxKp;
-    const size_t need = 16 + (size_t)take * 60;
-    if (need > e->hOutCap) {
-        if (e->hOut) cudaFreeHost(e->hOut);
-        e->hOut = nullptr; e->hOutCap = 0;
-        TRY(orbx_check(cudaHostAlloc(&e->hOut, need, cudaHostAllocDefault), "pinned output staging", g_err));
-        e->hOutCap = need;
-    }
-    TRY(orbx_check(cudaMemcpyAsync(e->hOut, E.P.outCnt, sizeof(int), cudaMemcpyDeviceToHost, E.stream), "D2H count", g_err));
-    if (take > 0) {
-        TRY(orbx_check(cudaMemcpyAsync(e->hOut + 16, E.P.outKp, (size_t)take * 28, cudaMemcpyDeviceToHost, E.stream), "D2H kps", g_err));
-        TRY(orbx_check(cudaMemcpyAsync(e->hOut + 16 + (size_t)take * 28, E.P.outDesc, (size_t)take * 32, cudaMemcpyDeviceToHost, E.stream), "D2H desc", g_err));
-    }
-    TRY(E.sync(g_err));
+    // pinned staging up, the launch sequence and the copies of the count and of every record into pinned memory as one CUDA
+    // graph, one synchronisation (Engine::processFrame)
+    const uint8_t* imgs[1] = {image};
+    const size_t strides[1] = {stride};
+    TRY(E.processFrame(imgs, strides, 0.f, 0.f, g_err));
     e->hasRun = true;
-    const int cnt = *reinterpret_cast<const int*>(e->hOut);
+    e->view = &E; e->viewImg = 0;
+    const int cnt = *reinterpret_cast<const int*>(E.hOut);
     if (cnt > capacity) return fail(ORBX_ERR_CAPACITY, "keypoint capacity too small (see orbx_max_keypoints)");
     if (cnt > 0) {
-        std::memcpy(kps, e->hOut + 16, (size_t)cnt * 28);
-        std::memcpy(desc, e->hOut + 16 + (size_t)take * 28, (size_t)cnt * 32);
+        std::memcpy(kps, E.hOut + E.frameOffKp, (size_t)cnt * 28);
+        std::memcpy(desc, E.hOut + E.frameOffDesc, (size_t)cnt * 32);
     }
     *n = cnt;
     return ORBX_OK;
@@ -131,10 +121,10 @@ extern "C" int orbx_extract(orbx_extractor* e, const uint8_t* image, int rows, i
 extern "C" int orbx_pyramid_level_size(const orbx_extractor* e, int level, int* rows, int* cols)
 {
     if (!e || !rows || !cols) return fail(ORBX_ERR_ARG, "bad arguments");
-    if (!e->eng || !e->hasRun) return fail(ORBX_ERR_STATE, "no image extracted yet");
+    if (!e->view) return fail(ORBX_ERR_STATE, "no image extracted yet");
     if (level < 0 || level >= e->cfg.nlevels) return fail(ORBX_ERR_ARG, "bad level");
-    *rows = e->eng->P.lv[level].h;
-    *cols = e->eng->P.lv[level].w;
+    *rows = e->view->P.lv[level].h;
+    *cols = e->view->P.lv[level].w;
     return ORBX_OK;
 }
 
@@ -154,9 +144,9 @@ static int copy_level(Engine& E, int img, int level, bool blurred, uint8_t* dst,
 extern "C" int orbx_pyramid_level(const orbx_extractor* e, int level, uint8_t* dst, size_t dstStride)
 {
     if (!e || !dst) return fail(ORBX_ERR_ARG, "bad arguments");
-    if (!e->eng || !e->hasRun) return fail(ORBX_ERR_STATE, "no image extracted yet");
-    if (level < 0 || level >= e->cfg.nlevels || dstStride < (size_t)e->eng->P.lv[level].w) return fail(ORBX_ERR_ARG, "bad level or stride");
-    return copy_level(*e->eng, 0, level, false, dst, dstStride);
+    if (!e->view) return fail(ORBX_ERR_STATE, "no image extracted yet");
+    if (level < 0 || level >= e->cfg.nlevels || dstStride < (size_t)e->view->P.lv[level].w) return fail(ORBX_ERR_ARG, "bad level or stride");
+    return copy_level(*e->view, e->viewImg, level, false, dst, dstStride);
 }
 
 extern "C" int orbx_stereo_match(orbx_extractor* l, orbx_extractor* r, const orbx_keypoint* kpsL, const uint8_t* descL, int nL,
@@ -191,6 +181,7 @@ extern "C" int orbx_stereo_match(orbx_extractor* l, orbx_extractor* r, const orb
         l->scratchRows = EL.rows;
     }
     cudaStream_t s = EL.stream;
+    EL.residentValid = ER.residentValid = false;  // the extractors' own results on the device are overwritten below
     // the caller's keypoints/descriptors are authoritative (Frame::mvKeys etc.): put them on the device
     TRY(orbx_check(cudaMemcpyAsync(EL.P.outKp, kpsL, (size_t)nL * 28, cudaMemcpyHostToDevice, s), "H2D kpsL", g_err));
     TRY(orbx_check(cudaMemcpyAsync(EL.P.outDesc, descL, (size_t)nL * 32, cudaMemcpyHostToDevice, s), "H2D descL", g_err));
@@ -212,6 +203,103 @@ extern "C" int orbx_stereo_match(orbx_extractor* l, orbx_extractor* r, const orb
     TRY(orbx_check(cudaMemcpyAsync(uRight, l->dU, (size_t)nL * 4, cudaMemcpyDeviceToHost, s), "D2H uRight", g_err));
     TRY(orbx_check(cudaMemcpyAsync(depth, l->dD, (size_t)nL * 4, cudaMemcpyDeviceToHost, s), "D2H depth", g_err));
     return EL.sync(g_err);
+}
+
+// ComputeStereoMatches on what the two extractors left on the device: nothing goes up.
+extern "C" int orbx_stereo_match_resident(orbx_extractor* l, orbx_extractor* r, int nL, int nR, float mbf, float mb, float* uRight,
+                                          float* depth)
+{
+    if (!l || !r || nL < 0 || nR < 0 || (nL && (!uRight || !depth))) return fail(ORBX_ERR_ARG, "bad arguments");
+    if (!l->eng || !r->eng || !l->hasRun || !r->hasRun) return fail(ORBX_ERR_STATE, "both extractors must have run");
+    Engine &EL = *l->eng, &ER = *r->eng;
+    if (EL.rows != ER.rows || EL.cols != ER.cols || EL.P.nlevels != ER.P.nlevels || l->device != r->device)
+        return fail(ORBX_ERR_STATE, "left/right extractors differ in image size, levels or device");
+    if (!EL.residentValid || !ER.residentValid || nL != *reinterpret_cast<const int*>(EL.hOut) || nR != *reinterpret_cast<const int*>(ER.hOut))
+        return fail(ORBX_ERR_STATE, "keypoint counts differ from what the extractors produced last: use orbx_stereo_match");
+    for (int i = 0; i < nL; ++i) uRight[i] = depth[i] = -1.f;  // src/Frame.cc:524-525
+    if (nL == 0) return ORBX_OK;
+    TRY(orbx_check(cudaSetDevice(l->device), "cudaSetDevice", g_err));
+    if (l->scratchKp < EL.P.maxKp || l->scratchRows < EL.rows) {
+        if (l->dU) { cudaFree(l->dU); cudaFree(l->dD); cudaFree(l->dSad); cudaFree(l->dNm); cudaFree(l->dSorted); cudaFree(l->dBin); l->dU = nullptr; }
+        const size_t k = EL.P.maxKp;
+        TRY(orbx_check(cudaMalloc(&l->dU, k * 4), "stereo scratch", g_err));
+        TRY(orbx_check(cudaMalloc(&l->dD, k * 4), "stereo scratch", g_err));
+        TRY(orbx_check(cudaMalloc(&l->dSad, k * 4), "stereo scratch", g_err));
+        TRY(orbx_check(cudaMalloc(&l->dNm, 4), "stereo scratch", g_err));
+        TRY(orbx_check(cudaMalloc(&l->dSorted, 3 * k * sizeof(uint4)), "stereo scratch", g_err));
+        TRY(orbx_check(cudaMalloc(&l->dBin, ((size_t)EL.rows + 1) * 4), "stereo scratch", g_err));
+        l->scratchKp = EL.P.maxKp;
+        l->scratchRows = EL.rows;
+    }
+    if (!l->hOut || l->hOutCap < (size_t)EL.P.maxKp * 8) {
+        if (l->hOut) cudaFreeHost(l->hOut);
+        l->hOut = nullptr; l->hOutCap = 0;
+        TRY(orbx_check(cudaHostAlloc(&l->hOut, (size_t)EL.P.maxKp * 8, cudaHostAllocDefault), "pinned stereo staging", g_err));
+        l->hOutCap = (size_t)EL.P.maxKp * 8;
+    }
+    cudaStream_t s = EL.stream;  // both extracts have synchronised their streams before returning
+    OrbxParams pl = EL.P, pr = ER.P;
+    pl.imgs = pr.imgs = 1;
+    OrbxStereoParams sp{};
+    sp.frames = 1; sp.nlevels = pl.nlevels; sp.rows0 = EL.rows; sp.maxKp = pl.maxKp; sp.mbf = mbf; sp.mb = mb;
+    sp.imgStep = 1; sp.imgOfsL = 0; sp.imgOfsR = 0;
+    sp.uRight = l->dU; sp.depth = l->dD; sp.sad = l->dSad; sp.nMatched = l->dNm;
+    sp.rsorted = l->dSorted; sp.binStart = l->dBin; sp.binR = orbx_stereo_bin_radius(l->cfg.scale.data(), l->cfg.nlevels);
+    orbx_launch_stereo(pl, pr, sp, s);
+    TRY(orbx_check(cudaGetLastError(), "stereo launch", g_err));
+    TRY(orbx_check(cudaMemcpyAsync(l->hOut, l->dU, (size_t)nL * 4, cudaMemcpyDeviceToHost, s), "D2H uRight", g_err));
+    TRY(orbx_check(cudaMemcpyAsync(l->hOut + (size_t)EL.P.maxKp * 4, l->dD, (size_t)nL * 4, cudaMemcpyDeviceToHost, s), "D2H depth", g_err));
+    TRY(EL.sync(g_err));
+    std::memcpy(uRight, l->hOut, (size_t)nL * 4);
+    std::memcpy(depth, l->hOut + (size_t)EL.P.maxKp * 4, (size_t)nL * 4);
+    return ORBX_OK;
+}
+
+// One stereo frame in one call (Frame::Frame(stereo), src/Frame.cc:113-125: ExtractORB left and right + ComputeStereoMatches).
+extern "C" int orbx_stereo_frame(orbx_extractor* l, orbx_extractor* r, const uint8_t* imgL, const uint8_t* imgR, int rows, int cols,
+                                 size_t strideL, size_t strideR, float mbf, float mb, orbx_keypoint* kpsL, uint8_t* descL, int* nL,
+                                 orbx_keypoint* kpsR, uint8_t* descR, int* nR, int capacity, float* uRight, float* depth)
+{
+    if (!l || !r || l == r) return fail(ORBX_ERR_ARG, "two distinct handles are needed");
+    if (rows == 0 || cols == 0 || !imgL || !imgR) {  // src/ORBextractor.cc:1044-1045 on both sides: nothing extracted, nothing matched
+        if (nL) *nL = 0;
+        if (nR) *nR = 0;
+        return ORBX_OK;
+    }
+    if (rows < 0 || cols < 0 || strideL < (size_t)cols || strideR < (size_t)cols || !kpsL || !descL || !nL || !kpsR || !descR || !nR ||
+        !uRight || !depth || capacity < 0)
+        return fail(ORBX_ERR_ARG, "bad arguments");
+    if (l->device != r->device || l->cfg.nfeatures != r->cfg.nfeatures || l->cfg.nlevels != r->cfg.nlevels || l->cfg.scaleFactor != r->cfg.scaleFactor ||
+        l->cfg.iniTh != r->cfg.iniTh || l->cfg.minTh != r->cfg.minTh)
+        return fail(ORBX_ERR_STATE, "orbx_stereo_frame needs two extractors with the same parameters on the same device");
+    if (!l->pair || l->pair->rows != rows || l->pair->cols != cols) {
+        std::unique_ptr<Engine> ne(new Engine());
+        TRY(ne->init(l->cfg, rows, cols, 2, true, l->device, g_err));
+        if (l->pairPeer && l->pairPeer->view == l->pair.get()) l->pairPeer->view = nullptr;
+        if (l->view == l->pair.get()) l->view = nullptr;
+        l->pair = std::move(ne);
+    }
+    Engine& E = *l->pair;
+    const uint8_t* imgs[2] = {imgL, imgR};
+    const size_t strides[2] = {strideL, strideR};
+    TRY(E.processFrame(imgs, strides, mbf, mb, g_err));
+    // the handles' own engines no longer hold this frame: pyramid levels come from the pair engine, and orbx_stereo_match
+    // (which reads the handles' own pyramids) needs a new orbx_extract first
+    l->hasRun = r->hasRun = false;
+    l->view = r->view = &E; l->viewImg = 0; r->viewImg = 1;
+    l->pairPeer = r;
+    const size_t Pk = (size_t)E.P.maxKp;
+    const int cl = reinterpret_cast<const int*>(E.hOut)[0], cr = reinterpret_cast<const int*>(E.hOut)[1];
+    if (cl > capacity || cr > capacity) return fail(ORBX_ERR_CAPACITY, "keypoint capacity too small (see orbx_max_keypoints)");
+    std::memcpy(kpsL, E.hOut + E.frameOffKp, (size_t)cl * 28);
+    std::memcpy(kpsR, E.hOut + E.frameOffKp + Pk * 28, (size_t)cr * 28);
+    std::memcpy(descL, E.hOut + E.frameOffDesc, (size_t)cl * 32);
+    std::memcpy(descR, E.hOut + E.frameOffDesc + Pk * 32, (size_t)cr * 32);
+    std::memcpy(uRight, E.hOut + E.frameOffU, (size_t)cl * 4);
+    std::memcpy(depth, E.hOut + E.frameOffD, (size_t)cl * 4);
+    *nL = cl;
+    *nR = cr;
+    return ORBX_OK;
 }
 
 // ---- frame batches ---------------------------------------------------------------------------------

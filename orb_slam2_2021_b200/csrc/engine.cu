@@ -207,6 +207,12 @@ void Engine::release()
     for (cudaEvent_t e : ingestEvents) cudaEventDestroy(e);
     for (cudaEvent_t e : downEvents) cudaEventDestroy(e);
     ingestEvents.clear(); downEvents.clear(); lastBounds.clear();
+    if (frameGraph) { cudaGraphExecDestroy(frameGraph); frameGraph = nullptr; }
+    if (hIn) { cudaFreeHost(hIn); hIn = nullptr; }
+    if (hOut) { cudaFreeHost(hOut); hOut = nullptr; }
+    if (frameFork) { cudaEventDestroy(frameFork); frameFork = nullptr; }
+    if (frameJoin) { cudaEventDestroy(frameJoin); frameJoin = nullptr; }
+    frameCalls = 0; graphBroken = false; residentValid = false;
     for (cudaEvent_t e : events) if (e) cudaEventDestroy(e);
     events.clear(); profiling = false; profiledRuns = 0;
     stream = stream2 = stream3 = stream4 = upStream = downStream = nullptr;
@@ -621,6 +627,97 @@ int Engine::processPipelined(const uint8_t* left, const uint8_t* right, int nFra
                     at(1 + 6 * c), at(2 + 6 * c), at(3 + 6 * c), at(4 + 6 * c), at(5 + 6 * c), at(6 + 6 * c));
         for (auto e : tev) cudaEventDestroy(e);
     }
+    return ORBX_OK;
+}
+
+// ---- single-frame path -------------------------------------------------------------------------------------
+void Engine::enqueueFrame(float mbf, float mb, cudaStream_t s)
+{
+    const int per = stereo ? 2 : 1;
+    const size_t tight = (size_t)rows * cols, sideStride = tight * (maxImgs / per), Pk = (size_t)P.maxKp;
+    for (int side = 0; side < per; ++side) orbx_launch_ingest(P, dStage + side * sideStride, maxImgs / per, per, side, s);
+    // the blur needs only the pyramid: it runs beside FAST and the quadtree (a second branch of the graph) and joins before
+    // the descriptors
+    const OrbxParams p = slice(0, maxImgs);
+    orbx_launch_pyramid(p, resizeTabs.data(), s);
+    cudaEventRecord(frameFork, s);
+    cudaStreamWaitEvent(stream2, frameFork, 0);
+    orbx_launch_blur(p, dTiles, nTiles, dBlurMaps, stream2);
+    cudaEventRecord(frameJoin, stream2);
+    orbx_launch_fast(p, dCells, dFastMaps, s);
+    orbx_launch_octree(p, dCells, s);
+    cudaStreamWaitEvent(s, frameJoin, 0);
+    orbx_launch_describe(p, dDescMaps0, dDescMaps1, s);
+    if (stereo) launchStereo(0, maxImgs / 2, mbf, mb, s);
+    cudaMemcpyAsync(hOut, P.outCnt, (size_t)maxImgs * sizeof(int), cudaMemcpyDeviceToHost, s);
+    cudaMemcpyAsync(hOut + frameOffKp, P.outKp, (size_t)maxImgs * Pk * 28, cudaMemcpyDeviceToHost, s);
+    cudaMemcpyAsync(hOut + frameOffDesc, P.outDesc, (size_t)maxImgs * Pk * 32, cudaMemcpyDeviceToHost, s);
+    if (stereo) {
+        cudaMemcpyAsync(hOut + frameOffU, SP.uRight, (size_t)(maxImgs / 2) * Pk * 4, cudaMemcpyDeviceToHost, s);
+        cudaMemcpyAsync(hOut + frameOffD, SP.depth, (size_t)(maxImgs / 2) * Pk * 4, cudaMemcpyDeviceToHost, s);
+    }
+}
+
+int Engine::processFrame(const uint8_t* const* images, const size_t* strides, float mbf, float mb, std::string& err)
+{
+    if (maxImgs > 2) { err = "the single-frame path serves engines of one frame"; return ORBX_ERR_STATE; }
+    TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
+    const int per = stereo ? 2 : 1;
+    const size_t tight = (size_t)rows * cols, Pk = (size_t)P.maxKp;
+    if (!hIn) {
+        frameOffKp = 64;
+        frameOffDesc = frameOffKp + (size_t)maxImgs * Pk * 28;
+        frameOffU = frameOffDesc + (size_t)maxImgs * Pk * 32;
+        frameOffD = frameOffU + Pk * 4;
+        hOutBytes = frameOffD + Pk * 4;
+        TRY(orbx_check(cudaHostAlloc(&hIn, tight * maxImgs, cudaHostAllocDefault), "pinned input staging", err));
+        TRY(orbx_check(cudaHostAlloc(&hOut, hOutBytes, cudaHostAllocDefault), "pinned output staging", err));
+        TRY(orbx_check(cudaEventCreateWithFlags(&frameFork, cudaEventDisableTiming), "cudaEventCreate", err));
+        TRY(orbx_check(cudaEventCreateWithFlags(&frameJoin, cudaEventDisableTiming), "cudaEventCreate", err));
+    }
+    // image i = side (i % per) of the frame: one flat copy each into the staging area the ingest kernel reads. A caller's
+    // buffer that is already page-locked and tight goes up directly; anything else passes through the pinned buffer.
+    for (int i = 0; i < maxImgs; ++i) {
+        const uint8_t* src = images[i];
+        bool direct = strides[i] == (size_t)cols;
+        if (direct) {
+            cudaPointerAttributes at{};
+            direct = cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost;
+            cudaGetLastError();
+        }
+        if (!direct) {
+            uint8_t* d = hIn + (size_t)i * tight;
+            if (strides[i] == (size_t)cols) std::memcpy(d, src, tight);
+            else for (int y = 0; y < rows; ++y) std::memcpy(d + (size_t)y * cols, src + (size_t)y * strides[i], (size_t)cols);
+            src = d;
+        }
+        const int side = i % per, f = i / per;
+        TRY(orbx_check(cudaMemcpyAsync(dStage + side * tight * (maxImgs / per) + f * tight, src, tight, cudaMemcpyHostToDevice, stream), "H2D frame", err));
+    }
+    if (frameGraph && (std::memcmp(&graphMbf, &mbf, 4) || std::memcmp(&graphMb, &mb, 4))) {  // stereo parameters are baked into the graph
+        cudaGraphExecDestroy(frameGraph);
+        frameGraph = nullptr;
+    }
+    if (!frameGraph && !graphBroken && frameCalls > 0) {
+        // (the first call ran the sequence directly: per-function attributes are set, lazily loaded modules are resident)
+        cudaGraph_t g = nullptr;
+        if (cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+            enqueueFrame(mbf, mb, stream);
+            const cudaError_t ec = cudaStreamEndCapture(stream, &g);
+            if (ec != cudaSuccess || !g || cudaGraphInstantiate(&frameGraph, g, 0) != cudaSuccess) { frameGraph = nullptr; graphBroken = true; }
+            if (g) cudaGraphDestroy(g);
+            graphMbf = mbf; graphMb = mb;
+        } else {
+            graphBroken = true;
+        }
+        cudaGetLastError();
+    }
+    ++frameCalls;
+    if (frameGraph) TRY(orbx_check(cudaGraphLaunch(frameGraph, stream), "graph launch", err));
+    else enqueueFrame(mbf, mb, stream);
+    TRY(orbx_check(cudaGetLastError(), "frame launch", err));
+    TRY(sync(err));
+    residentValid = true;
     return ORBX_OK;
 }
 

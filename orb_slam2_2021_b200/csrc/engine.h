@@ -62,6 +62,22 @@ public:
     int lastRunChunks = 1;  // chunks of the most recent runBatch (kernel launches = chunks x launches per chunk)
     int sync(std::string& err);
 
+    // Single-frame path (orbx_extract: capacity 1; orbx_stereo_frame: capacity 2, stereo): the images of ONE frame go up
+    // through pinned staging with one flat copy each, the whole launch sequence (ingest, extract [, stereo match]) and the
+    // copies of every result into pinned host memory replay as ONE CUDA graph (captured on the second call for a given
+    // mbf/mb), and one synchronisation ends the call. Results: hOut + frameOff* (full pitch maxKp per image).
+    uint8_t* hIn = nullptr;   // pinned, [maxImgs][rows*cols]
+    uint8_t* hOut = nullptr;  // pinned: counts | keypoints | descriptors | uRight | depth
+    size_t frameOffKp = 0, frameOffDesc = 0, frameOffU = 0, frameOffD = 0, hOutBytes = 0;
+    cudaGraphExec_t frameGraph = nullptr;
+    cudaEvent_t frameFork = nullptr, frameJoin = nullptr;
+    float graphMbf = 0.f, graphMb = 0.f;
+    int frameCalls = 0;
+    bool graphBroken = false;
+    bool residentValid = false;  // outKp/outDesc/outCnt on the device are what the last processFrame produced (hOut holds the counts)
+    int processFrame(const uint8_t* const* images, const size_t* strides, float mbf, float mb, std::string& err);
+    void enqueueFrame(float mbf, float mb, cudaStream_t s);
+
     OrbxParams P{};          // device pointers + geometry (imgs = capacity)
     OrbxStereoParams SP{};   // stereo outputs (batch engines with stereo == true)
     ExtractorConfig cfg;

@@ -15,7 +15,13 @@ struct orbx_extractor {
     uint4* dSorted = nullptr; int* dBin = nullptr;
     int scratchRows = 0;
     int scratchKp = 0;
-    uint8_t* hOut = nullptr; size_t hOutCap = 0;  // pinned staging of orbx_extract's results
+    uint8_t* hOut = nullptr; size_t hOutCap = 0;  // pinned staging of orbx_stereo_match_resident's results
+    // orbx_stereo_frame: the LEFT handle owns an engine for the frame's two images (image 0 = left, 1 = right); both handles
+    // then read their pyramid levels from it (view) until their next orbx_extract
+    std::unique_ptr<Engine> pair;
+    orbx_extractor* pairPeer = nullptr;  // the other handle whose view points into this handle's pair engine
+    Engine* view = nullptr;              // where the most recent pyramid of this handle lives
+    int viewImg = 0;
 };
 
 std::string& orbx_err_slot();  // thread-local text behind orbx_last_error() (abi.cu)

@@ -376,6 +376,7 @@ extern "C" int orbx_stereo_match_static(orbx_extractor* l, orbx_extractor* r, co
 #define ST_TRY(x) do { rc = (x); if (rc) return rc; } while (0)
     ST_TRY(orbx_check(cudaSetDevice(l->device), "cudaSetDevice", err));
     cudaStream_t s = EL.stream;
+    EL.residentValid = ER.residentValid = false;  // the extractors' own results on the device are overwritten below
     // the array keeps the previous call's contents: the per-keypoint SAD and the match counter start from a defined state
     ST_TRY(orbx_check(cudaMemsetAsync(scratch + ST_OFF_SAD, 0xFF, 4u * ST_STATIC_MAX_KP + 256u, s), "clear static scratch", err));
     // the caller's keypoints/descriptors are authoritative: into the extractors' own (already allocated) output buffers

@@ -114,6 +114,40 @@ def compute_stereo_matches(extractor_left, extractor_right, keys_left, desc_left
     return ur, dp
 
 
+def compute_stereo_matches_resident(extractor_left, extractor_right, n_left, n_right, mbf, mb):
+    """Frame::ComputeStereoMatches on the keypoints and descriptors the two extractors' last calls left on the device
+    (orbx_stereo_match_resident: nothing is uploaded) -> (mvuRight, mvDepth)."""
+    ur = np.full(n_left, -1, np.float32)
+    dp = np.full(n_left, -1, np.float32)
+    check(lib().orbx_stereo_match_resident(extractor_left._h, extractor_right._h, int(n_left), int(n_right), float(mbf), float(mb),
+                                           ptr(ur), ptr(dp)))
+    return ur, dp
+
+
+def stereo_frame(extractor_left, extractor_right, image_left, image_right, mbf, mb):
+    """One stereo frame in one call (orbx_stereo_frame; src/Frame.cc:113-125: ExtractORB left + right, ComputeStereoMatches)
+    -> (keys_left, desc_left, keys_right, desc_right, mvuRight, mvDepth)."""
+    il, ir = _as_u8_2d(image_left), _as_u8_2d(image_right)
+    if il.shape != ir.shape:
+        raise ValueError("left and right images differ in size")
+    if il.size == 0:
+        z, d = np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        return z, d, z.copy(), d.copy(), np.zeros(0, np.float32), np.zeros(0, np.float32)
+    rows, cols = il.shape
+    cap = lib().orbx_max_keypoints(extractor_left._h, rows, cols)
+    if cap < 0:
+        check(cap)
+    kl, kr = np.zeros(cap, KP_DTYPE), np.zeros(cap, KP_DTYPE)
+    dl, dr = np.zeros((cap, 32), np.uint8), np.zeros((cap, 32), np.uint8)
+    ur, dp = np.zeros(cap, np.float32), np.zeros(cap, np.float32)
+    nl, nr = C.c_int(0), C.c_int(0)
+    check(lib().orbx_stereo_frame(extractor_left._h, extractor_right._h, ptr(il), ptr(ir), rows, cols, il.strides[0], ir.strides[0],
+                                  float(mbf), float(mb), ptr(kl), ptr(dl), C.byref(nl), ptr(kr), ptr(dr), C.byref(nr), cap, ptr(ur),
+                                  ptr(dp)))
+    a, b = nl.value, nr.value
+    return kl[:a].copy(), dl[:a].copy(), kr[:b].copy(), dr[:b].copy(), ur[:a].copy(), dp[:a].copy()
+
+
 def compute_stereo_matches_static(extractor_left, extractor_right, keys_left, desc_left, keys_right, desc_right, mbf, mb):
     """compute_stereo_matches through orbx_stereo_match_static: same results, device scratch in a static array inside
     the library (no allocation; at most 8192 keypoints per side and 4096 rows; calls overlapping on one GPU race)."""

@@ -431,3 +431,78 @@ def test_pinned_allocation_reports_its_numa_placement():
         pkg.set_tuning("numa_off", 0)
     with pytest.raises(pkg.OrbxError):
         pkg.set_tuning("no_such_knob", 1)
+
+
+# ---- single-frame entry points: orbx_stereo_frame, orbx_stereo_match_resident (and the CUDA graph they replay) -------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["kitti", "euroc", "arducam"])
+def test_stereo_frame_equals_the_two_handle_path_and_the_oracle(name):
+    """orbx_stereo_frame == orbx_extract x2 + orbx_stereo_match == oracle, over several frames (the first call runs the
+    launches directly, the second captures the CUDA graph, later ones replay it; mbf/mb changes re-capture)."""
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS[name]
+    fl, fr = pkg.ORBextractor(nf, sf, nl, ini, mn), pkg.ORBextractor(nf, sf, nl, ini, mn)
+    el, er = pkg.ORBextractor(nf, sf, nl, ini, mn), pkg.ORBextractor(nf, sf, nl, ini, mn)
+    ol, orr = O.OracleExtractor(nf, sf, nl, ini, mn), O.OracleExtractor(nf, sf, nl, ini, mn)
+    for i, (seed, mb) in enumerate(((41, bf / fx), (42, bf / fx), (43, bf / fx), (44, 0.0), (45, bf / fx))):
+        left, right = synth.stereo_pair(W, H, seed)
+        kl, dl, kr, dr, ur, dp = pkg.stereo_frame(fl, fr, left, right, bf, mb)
+        k2l, d2l = el(left)
+        k2r, d2r = er(right)
+        u3, p3 = pkg.compute_stereo_matches_resident(el, er, len(k2l), len(k2r), bf, mb)  # nothing uploaded
+        u2, p2 = pkg.compute_stereo_matches(el, er, k2l, d2l, k2r, d2r, bf, mb)
+        assert kl.tobytes() == k2l.tobytes() and kr.tobytes() == k2r.tobytes()
+        assert np.array_equal(dl, d2l) and np.array_equal(dr, d2r)
+        assert ur.tobytes() == u2.tobytes() and dp.tobytes() == p2.tobytes()
+        assert u3.tobytes() == u2.tobytes() and p3.tobytes() == p2.tobytes()
+        if i in (0, 2, 3):
+            okl, odl = ol(left)
+            okr, odr = orr(right)
+            our, odp = O.stereo_match(ol, orr, okl, odl, okr, odr, bf, mb)
+            for f in ("x", "y", "size", "response", "octave", "class_id"):
+                assert np.array_equal(kl[f], okl[f]), f
+            assert np.abs(kl["angle"] - okl["angle"]).max() <= 1e-4
+            assert np.array_equal(dl, odl) and np.array_equal(dr, odr)
+            assert np.array_equal(ur >= 0, our >= 0) and np.abs(ur - our).max() <= 1e-4
+        # the frame's pyramid is readable through both handles
+        pl, pr_ = fl.mvImagePyramid, fr.mvImagePyramid
+        ql, qr = el.mvImagePyramid, er.mvImagePyramid
+        assert all(np.array_equal(a, b) for a, b in zip(pl, ql)) and all(np.array_equal(a, b) for a, b in zip(pr_, qr))
+
+
+@pytest.mark.gpu
+def test_single_frame_entry_points_state_and_strides():
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["arducam"]
+    fl, fr = pkg.ORBextractor(nf, sf, nl, ini, mn), pkg.ORBextractor(nf, sf, nl, ini, mn)
+    left, right = synth.stereo_pair(W, H, 9)
+    ref_out = pkg.stereo_frame(fl, fr, left, right, bf, bf / fx)
+    # strided views (a cv::Mat ROI) and page-locked tight buffers take different upload routes: same results
+    wide = np.zeros((H, 2 * W + 16), np.uint8)
+    wide[:, :W], wide[:, W + 16:] = left, right
+    out2 = pkg.stereo_frame(fl, fr, wide[:, :W], wide[:, W + 16:], bf, bf / fx)
+    pin_l, pin_r = pkg.PinnedArray((H, W), np.uint8), pkg.PinnedArray((H, W), np.uint8)
+    pin_l.array[...], pin_r.array[...] = left, right
+    out3 = pkg.stereo_frame(fl, fr, pin_l.array, pin_r.array, bf, bf / fx)
+    for a, b, c in zip(ref_out, out2, out3):
+        assert a.tobytes() == b.tobytes() == c.tobytes()
+    # after orbx_stereo_frame the handles' own engines hold no frame: the two-handle match refuses
+    with pytest.raises(pkg.OrbxError) as ei:
+        pkg.compute_stereo_matches(fl, fr, ref_out[0], ref_out[1], ref_out[2], ref_out[3], bf, bf / fx)
+    assert ei.value.code == pkg._lib.ERR_STATE
+    # resident match: refuses counts that are not the extractors' own, and after an uploading match
+    el, er = pkg.ORBextractor(nf, sf, nl, ini, mn), pkg.ORBextractor(nf, sf, nl, ini, mn)
+    kl, dl = el(left)
+    kr, dr = er(right)
+    with pytest.raises(pkg.OrbxError):
+        pkg.compute_stereo_matches_resident(el, er, len(kl) - 1, len(kr), bf, bf / fx)
+    pkg.compute_stereo_matches(el, er, kl[:100], dl[:100], kr, dr, bf, bf / fx)
+    with pytest.raises(pkg.OrbxError):
+        pkg.compute_stereo_matches_resident(el, er, len(kl), len(kr), bf, bf / fx)
+    # different extractor parameters on the two sides are refused
+    with pytest.raises(pkg.OrbxError):
+        pkg.stereo_frame(fl, pkg.ORBextractor(nf + 1, sf, nl, ini, mn), left, right, bf, bf / fx)
+    # size change rebuilds the frame engine
+    W2, H2 = synth.CONFIGS["tum_mono"][:2]
+    l2, r2 = synth.stereo_pair(W2, H2, 3)
+    a = pkg.stereo_frame(fl, fr, l2, r2, bf, bf / fx)
+    b = pkg.stereo_frame(fl, fr, l2, r2, bf, bf / fx)
+    assert all(x.tobytes() == y.tobytes() for x, y in zip(a, b)) and len(a[0]) > 300
