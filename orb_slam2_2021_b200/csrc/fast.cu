@@ -128,8 +128,10 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
     __shared__ __align__(8) uint64_t bars[CELLS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint8_t* T = fast_smem + (size_t)warp * sliceBytes;  // raw box [rhMax][BW]
-    uint16_t* smap = reinterpret_cast<uint16_t*>(T + ((rhMax * BW + 127) & ~127));
-    uint16_t* tasks = smap + (rhMax - 4) * SA;  // pass-1 survivors (pixel pairs)
+    // strength map: ONE BYTE per pixel (m - thr <= 254). As u16 it cost 2 KB more per warp and capped the SM at 6 CTAs (24
+    // warps); with 7.3 KB per warp 7 CTAs fit, and this kernel's throughput follows the number of resident warps
+    uint8_t* smap = T + ((rhMax * BW + 127) & ~127);
+    uint16_t* tasks = reinterpret_cast<uint16_t*>(smap + (rhMax - 4) * SA);  // pass-1 survivors (pixel pairs)
     // pairs with a non-zero strength: written over the task list while pass 2 consumes it (entry k of nz is written in the
     // trip that read tasks[32*(trip)..], and k never runs ahead of what has been read)
     uint16_t* nz = tasks;
@@ -162,7 +164,7 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
     }
     {
         uint4* z = reinterpret_cast<uint4*>(smap);
-        const int nzero = (ih + 2) * (SA / 8);
+        const int nzero = (ih + 2) * (SA / 16);
         for (int i = lane; i < nzero; i += 32) z[i] = make_uint4(0, 0, 0, 0);
     }
     __syncwarp();
@@ -251,7 +253,7 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
                 const uint32_t inside = (ix >= 0 ? 0x0000FFFFu : 0u) | (ix + 1 < iw ? 0xFFFF0000u : 0u);
                 const uint32_t ms = (__vimax3_u16x2(mp, thr2, thr2) - thr2) & inside;  // m - thr per half, 0 = no corner
                 hit = ms != 0;
-                if (hit) *reinterpret_cast<uint32_t*>(smap + (y + 1) * SA + c + SD) = ms;  // map is pre-zeroed
+                if (hit) *reinterpret_cast<uint16_t*>(smap + (y + 1) * SA + c + SD) = (uint16_t)__byte_perm(ms, 0, 0x4420);  // map is pre-zeroed
             }
             const unsigned bh = __ballot_sync(0xffffffffu, hit);
             if (hit) nz[nzAll + __popc(bh & lt)] = (uint16_t)task;
@@ -268,11 +270,13 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
             uint32_t e0 = 0, e1 = 0;
             if (g < nzAll) {
                 const int task = nz[g], y = task >> 8, cc = 2 * (task & 255);
-                const uint16_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair, word aligned
-                const uint32_t mm = *reinterpret_cast<const uint32_t*>(c);
-                const uint32_t u0 = *reinterpret_cast<const uint32_t*>(c - SA - 2), u1 = *reinterpret_cast<const uint32_t*>(c - SA), u2 = *reinterpret_cast<const uint32_t*>(c - SA + 2);
-                const uint32_t l0 = *reinterpret_cast<const uint32_t*>(c - 2), l2 = *reinterpret_cast<const uint32_t*>(c + 2);
-                const uint32_t d0 = *reinterpret_cast<const uint32_t*>(c + SA - 2), d1 = *reinterpret_cast<const uint32_t*>(c + SA), d2 = *reinterpret_cast<const uint32_t*>(c + SA + 2);
+                const uint8_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair (even byte address)
+#define MAP2(q) __byte_perm((uint32_t)*reinterpret_cast<const uint16_t*>(q), 0, 0x4140)  /* two map bytes -> u16x2 */
+                const uint32_t mm = MAP2(c);
+                const uint32_t u0 = MAP2(c - SA - 2), u1 = MAP2(c - SA), u2 = MAP2(c - SA + 2);
+                const uint32_t l0 = MAP2(c - 2), l2 = MAP2(c + 2);
+                const uint32_t d0 = MAP2(c + SA - 2), d1 = MAP2(c + SA), d2 = MAP2(c + SA + 2);
+#undef MAP2
                 const uint32_t cm0 = __vimax3_u16x2(u0, l0, d0), cm1 = __vimax3_u16x2(u1, mm, d1), cm2 = __vimax3_u16x2(u2, l2, d2);
                 const uint32_t ud = __vimax3_u16x2(u1, d1, d1);
                 const int m0 = mm & 0xFFFFu, m1 = mm >> 16;
@@ -334,7 +338,7 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     const int iwMax = (sa == 48 ? 40 : 72) - 6, ihMax = rhMax - 6;
     const int listCap = (((iwMax + 4) / 2) * ihMax + 7) & ~7;
     // shared memory of one cell: tile + strength map + one list (the non-zero pairs overwrite the tasks)
-    const int slice = (int)(((size_t)((rhMax * boxW + 127) & ~127) + (size_t)(rhMax - 4) * sa * 2 + (size_t)listCap * 2 + 127) & ~(size_t)127);
+    const int slice = (int)(((size_t)((rhMax * boxW + 127) & ~127) + (size_t)(rhMax - 4) * sa + (size_t)listCap * 2 + 127) & ~(size_t)127);
     // cells (= warps) per CTA: tuning key fast_cells = 2 / 4 / 8 (tools/fast_cells_sweep.sh: 4 is best, 8 loses a third)
     int cellsPerCta = orbx_tune(ORBX_TUNE_FAST_CELLS);
     if (cellsPerCta != 2 && cellsPerCta != 4 && cellsPerCta != 8) cellsPerCta = 4;
