@@ -87,3 +87,18 @@ def test_quota_beyond_the_quadtree_capacity_is_a_clean_error():
     assert b"quota" in pkg.lib().orbx_last_error()
     assert pkg.lib().orbx_max_keypoints(pkg.ORBextractor(12000, 1.2, 8, 20, 7)._h, 2160, 3840) > 12000
     assert pkg.lib().orbx_max_keypoints(pkg.ORBextractor(3000, 1.2, 1, 20, 7)._h, 480, 640) == pkg._lib.ERR_ARG
+
+
+@pytest.mark.gpu
+def test_oversized_quota_fails_cleanly_on_the_device_too():
+    """nfeatures = 20000 at 8 levels: orbx_extract reports ORBX_ERR_ARG with the quota text instead of a launch failure,
+    and the handle stays usable for sizes it can serve."""
+    from orb_slam2_2021_b200 import synth
+
+    e = pkg.ORBextractor(20000, 1.2, 8, 20, 7)
+    with pytest.raises(pkg.OrbxError) as ei:
+        e(synth.synth(1280, 720, 1))
+    assert ei.value.code == pkg._lib.ERR_ARG and "quota" in str(ei.value)
+    ok = pkg.ORBextractor(12000, 1.2, 8, 20, 7)
+    k, d = ok(synth.synth(1280, 720, 1))
+    assert len(k) > 3000 and d.shape == (len(k), 32)

@@ -390,3 +390,71 @@ def test_cuda_search_local_points_equals_reference(seed, th, ur, occ, n_points, 
         b, nb = R.search_local_points(U.view(O.FrameView, F), occupied, valid, proj, level, vc, pdesc, obs, th, ratio)
         g, ng = m.SearchLocalPoints(U.view(pkg.FrameView, F), pkg.TrackPointView(valid, proj, level, vc, pdesc, obs), th, occupied, ratio)
         assert ng == nb and np.array_equal(g, b), (seed, ratio, ng, nb)
+
+
+# ---------------------------------------------------------------- the 4K configuration and the benchmarked batch sizes
+@needs_ref
+def test_oracle_equals_reference_uhd():
+    """Config 5 of BASELINE.json (3840x2160, 8000 features): 31k-candidate levels through the reference's std::list quadtree."""
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["uhd"]
+    o, r = O.OracleExtractor(nf, sf, nl, ini, mn), R.RefExtractor(nf, sf, nl, ini, mn)
+    ims = images(W, H, 7)
+    for what in ("left", "flat"):
+        a, b = o(ims[what]), r(ims[what])
+        assert_same(a, b, f"uhd/{what}")
+        if what == "left":
+            assert len(a[0]) >= nf
+
+
+@needs_ref
+@pytest.mark.gpu
+def test_cuda_equals_reference_uhd():
+    import orb_slam2_2021_b200 as pkg
+
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["uhd"]
+    ex, r = pkg.ORBextractor(nf, sf, nl, ini, mn), R.RefExtractor(nf, sf, nl, ini, mn)
+    ims = images(W, H, 8)
+    for what in ("left", "right"):
+        assert_same(ex(ims[what]), r(ims[what]), f"uhd/{what}")
+    for l, lev in enumerate(ex.mvImagePyramid):
+        assert np.array_equal(lev, r.level(l)), f"pyramid level {l}"
+
+
+@needs_ref
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["kitti", "euroc"])
+def test_cuda_256_frame_stream_equals_reference_sampled(name):
+    """The benchmarked call at its real size: 256 distinct stereo frames per call through orbx_batch_process_async (four
+    chunks on two compute streams, two calls back to back on two output sets), every 16th frame of the SECOND call checked
+    against the reference's extractor and its Frame::ComputeStereoMatches; configs 2/4 (KITTI) and 3 (EuRoC batch of 256)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    import orb_slam2_2021_b200 as pkg
+
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS[name]
+    n = 256
+    pl, pr = pkg.PinnedArray((n, H, W), np.uint8), pkg.PinnedArray((n, H, W), np.uint8)
+
+    def gen(k):
+        pl.array[k], pr.array[k] = synth.stereo_pair(W, H, 5000 + 2 * k)
+
+    with ThreadPoolExecutor(8) as ex:
+        list(ex.map(gen, range(n)))
+    batch = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, n, stereo=True)
+    out_a, out_b = batch.alloc_outputs(n, pinned=True), batch.alloc_outputs(n, pinned=True)
+    mbf, mb = bf, bf / fx
+    batch.process_async(pl.array, pr.array, mbf, mb, out_a)
+    batch.process_async(pl.array, pr.array, mbf, mb, out_b)
+    batch.wait()
+    for key in out_a:  # the two calls saw the same frames
+        assert np.array_equal(out_a[key].view(np.uint8), out_b[key].view(np.uint8)), key
+    rl, rr = R.RefExtractor(nf, sf, nl, ini, mn), R.RefExtractor(nf, sf, nl, ini, mn)
+    for k in range(3, n, 16):
+        a, b = int(out_b["n_left"][k]), int(out_b["n_right"][k])
+        kl, dl = rl(pl.array[k])
+        kr, dr = rr(pr.array[k])
+        assert_same((out_b["kps_left"][k, :a], out_b["desc_left"][k, :a]), (kl, dl), f"{name}/stream/{k}/left")
+        assert_same((out_b["kps_right"][k, :b], out_b["desc_right"][k, :b]), (kr, dr), f"{name}/stream/{k}/right")
+        ur, dp = R.stereo_match(rl, rr, kl, dl, kr, dr, mbf, mb)
+        assert out_b["u_right"][k, :a].tobytes() == ur.tobytes() and out_b["depth"][k, :a].tobytes() == dp.tobytes(), (name, k)
+        assert (ur >= 0).sum() > 50
