@@ -76,6 +76,26 @@ int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view* cur, const
                               const orbx_mappoint_view* last_points, int n_pairs, float th, int b_mono, int check_orientation,
                               int* const* match_of_cur, int* nmatches);
 
+/* Device-resident source of a frame's keypoints, descriptors and uRight: frame `frame`, side `side` (0 = left / mono,
+ * 1 = right) of a batch engine after orbx_batch_run / orbx_batch_process*. batch == NULL: read the view's host arrays. */
+typedef struct {
+    orbx_batch* batch;
+    int frame, side;
+} orbx_frame_source;
+
+/* orbx_search_by_projection without the round trip through the host between the rows: where cur_src[p] / last_src[p] name a
+ * batch engine, that frame's keys_un, desc and u_right (current frame) or keys_un (last frame) are read where the extractor
+ * and the stereo match left them on the device — as the reference's flow does in memory (src/Tracking.cc:897-911 works on
+ * the Frame that Frame::Frame just filled); the view's pointers to them are ignored and its n must not exceed what the
+ * engine produced (mvKeysUn == mvKeys: rectified input, as in the stereo examples). cur_src / last_src may be NULL (all
+ * host). Map point arrays that are one concatenation in pair order (pair p+1's array starts where pair p's ends, for all
+ * four arrays) are copied straight from the caller's memory — page-locked for full speed — instead of being repacked.
+ * Everything else as orbx_search_by_projection, results identical. */
+int orbx_search_by_projection_resident(orbx_matcher* m, const orbx_frame_view* cur, const orbx_frame_source* cur_src,
+                                       const orbx_frame_view* last, const orbx_frame_source* last_src,
+                                       const orbx_mappoint_view* last_points, int n_pairs, float th, int b_mono,
+                                       int check_orientation, int* const* match_of_cur, int* nmatches);
+
 /* Per map point of the local map, as far as the local-map SearchByProjection reads it (MapPoint members set by
  * Frame::isInFrustum, src/Frame.cc:304-374). */
 typedef struct {

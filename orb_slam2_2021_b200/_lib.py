@@ -85,6 +85,7 @@ SIGNATURES = {
     "orbx_assign_features_to_grid": (_i, [_vp, _vp, _vp, _vp, _ip]),
     "orbx_get_features_in_area": (_i, [_vp, _vp, _f, _f, _f, _i, _i, _vp, _i, _ip]),
     "orbx_search_by_projection": (_i, [_vp, _vp, _vp, _vp, _i, _f, _i, _i, _vp, _vp]),
+    "orbx_search_by_projection_resident": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _i, _i, _vp, _vp]),
     "orbx_search_local_points": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _vp, _vp]),
     # include/orbx_input.h
     "orbx_rectify_gray": (_i, [_vp, _vp, _i, _i, _sz, _i, _i, _vp, _vp, _i, _i, _sz, _i, _i, _vp, _sz]),

@@ -17,12 +17,6 @@ static int fail(int code, const char* msg) { g_err = msg; return code; }
 std::string& orbx_err_slot() { return g_err; }  // for frame.cu
 
 
-struct orbx_batch {
-    ExtractorConfig cfg;
-    Engine eng;
-    int maxFrames = 0;
-    bool stereo = false;
-};
 
 extern "C" const char* orbx_last_error(void) { return g_err.c_str(); }
 

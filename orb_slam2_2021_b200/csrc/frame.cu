@@ -15,6 +15,7 @@
 //                          then the warp repeats the search with the blocked set. Rotation histogram, three maxima
 //                          and the removal pass (:1455-1487) follow in the same kernel.
 // All frame pairs of a call run in one launch each (blockIdx.y = pair); inputs travel in one packed H2D copy.
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <string>
@@ -23,6 +24,7 @@
 #include "../../include/orbx_frame.h"
 #include "engine.h"
 #include "matcher.h"
+#include "handles.h"
 
 
 namespace {
@@ -565,6 +567,7 @@ extern "C" void orbx_matcher_destroy(orbx_matcher* m)
     if (m->dBuf) cudaFree(m->dBuf);
     if (m->hIn) cudaFreeHost(m->hIn);
     if (m->hOut) cudaFreeHost(m->hOut);
+    if (m->orderEvent) cudaEventDestroy(m->orderEvent);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
 }
@@ -640,39 +643,112 @@ extern "C" int orbx_get_features_in_area(orbx_matcher* m, const orbx_frame_view*
     return ORBX_OK;
 }
 
-extern "C" int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view* cur, const orbx_frame_view* last,
-                                         const orbx_mappoint_view* lastPoints, int nPairs, float th, int bMono, int checkOrientation,
-                                         int* const* matchOfCur, int* nmatches)
+namespace {
+// Keypoints / descriptors / uRight of a frame where a batch engine left them (orbx_frame_source): device pointers, no copy.
+struct ResidentFrame {
+    const orbx_keypoint* keys = nullptr; const uint8_t* desc = nullptr; const float* uRight = nullptr;
+};
+int resolve_source(orbx_matcher* m, const orbx_frame_source& src, const orbx_frame_view& v, ResidentFrame& out)
+{
+    orbx_batch* b = src.batch;
+    const int per = b->stereo ? 2 : 1;
+    if (src.frame < 0 || src.frame >= b->maxFrames || src.side < 0 || src.side >= per) return orbx_fail(ORBX_ERR_ARG, "frame source outside the batch");
+    Engine& E = b->eng;
+    if (E.device != m->device) return orbx_fail(ORBX_ERR_STATE, "batch and matcher live on different devices");
+    if (v.n > E.P.maxKp) return orbx_fail(ORBX_ERR_ARG, "frame view has more keypoints than the batch engine can hold");
+    if (v.nlevels < E.P.nlevels) return orbx_fail(ORBX_ERR_ARG, "scale factor table shorter than the extractor's levels");
+    const size_t img = (size_t)src.frame * per + src.side, Pk = (size_t)E.P.maxKp;
+    out.keys = reinterpret_cast<const orbx_keypoint*>((const uint8_t*)E.P.outKp + img * Pk * 28);
+    out.desc = E.P.outDesc + img * Pk * 32;
+    out.uRight = (b->stereo && src.side == 0) ? E.SP.uRight + (size_t)src.frame * Pk : nullptr;
+    return ORBX_OK;
+}
+// the matcher's stream runs behind everything the batch engines have enqueued
+int order_after_batch(orbx_matcher* m, orbx_batch* b, std::string& err)
+{
+    Engine& E = b->eng;
+    if (!E.lastBounds.empty()) TRY(E.waitPipelined(err));
+    if (!m->orderEvent) TRY(orbx_check(cudaEventCreateWithFlags(&m->orderEvent, cudaEventDisableTiming), "cudaEventCreate", err));
+    TRY(orbx_check(cudaEventRecord(m->orderEvent, E.stream), "event", err));
+    return orbx_check(cudaStreamWaitEvent(m->stream, m->orderEvent, 0), "wait", err);
+}
+
+int search_by_projection_impl(orbx_matcher* m, const orbx_frame_view* cur, const orbx_frame_source* curSrc, const orbx_frame_view* last,
+                              const orbx_frame_source* lastSrc, const orbx_mappoint_view* lastPoints, int nPairs, float th, int bMono,
+                              int checkOrientation, int* const* matchOfCur, int* nmatches)
 {
     if (!m || !cur || !last || !lastPoints || nPairs < 1 || !matchOfCur || !nmatches) return orbx_fail(ORBX_ERR_ARG, "bad arguments");
     std::string& err = orbx_err_slot();
     int maxLast = 0, maxCur = 0;
+    std::vector<ResidentFrame> rc(nPairs), rl(nPairs);
     for (int p = 0; p < nPairs; ++p) {
-        TRY(check_frame(cur + p, true));
-        TRY(check_frame(last + p, false));
+        const bool curRes = curSrc && curSrc[p].batch, lastRes = lastSrc && lastSrc[p].batch;
+        if (curRes) {  // keys_un / desc / u_right of the view are not read
+            orbx_frame_view v = cur[p];
+            v.keys_un = reinterpret_cast<const orbx_keypoint*>(&v); v.desc = reinterpret_cast<const uint8_t*>(&v);
+            TRY(check_frame(&v, true));
+            TRY(resolve_source(m, curSrc[p], cur[p], rc[p]));
+        } else {
+            TRY(check_frame(cur + p, true));
+        }
+        if (lastRes) {
+            orbx_frame_view v = last[p];
+            v.keys_un = reinterpret_cast<const orbx_keypoint*>(&v);
+            TRY(check_frame(&v, false));
+            TRY(resolve_source(m, lastSrc[p], last[p], rl[p]));
+        } else {
+            TRY(check_frame(last + p, false));
+        }
         const orbx_mappoint_view& mp = lastPoints[p];
         if (last[p].n && (!mp.has_point || !mp.world_pos || !mp.point_desc || !mp.observed)) return orbx_fail(ORBX_ERR_ARG, "bad map point view");
         if (cur[p].n && !matchOfCur[p]) return orbx_fail(ORBX_ERR_ARG, "match_of_cur is NULL");
-        for (int i = 0; i < last[p].n; ++i)
-            if (last[p].keys_un[i].octave < 0 || last[p].keys_un[i].octave >= cur[p].nlevels)
-                return orbx_fail(ORBX_ERR_ARG, "last-frame keypoint octave outside the current frame's scale table");
+        if (lastRes) {  // the extractor's own octaves are below its level count
+            if (lastSrc[p].batch->eng.P.nlevels > cur[p].nlevels) return orbx_fail(ORBX_ERR_ARG, "last-frame octaves outside the current frame's scale table");
+        } else {
+            for (int i = 0; i < last[p].n; ++i)
+                if (last[p].keys_un[i].octave < 0 || last[p].keys_un[i].octave >= cur[p].nlevels)
+                    return orbx_fail(ORBX_ERR_ARG, "last-frame keypoint octave outside the current frame's scale table");
+        }
         maxLast = last[p].n > maxLast ? last[p].n : maxLast;
         maxCur = cur[p].n > maxCur ? cur[p].n : maxCur;
     }
     TRY(orbx_check(cudaSetDevice(m->device), "cudaSetDevice", err));
 
-    // ---- layout: [FrameDev x nPairs | inputs of every pair] (one H2D) | scratch | [assigned of every pair | nmatches] (one D2H)
+    // ---- layout: [FrameDev x nPairs | frame arrays of every pair that are not resident] (one H2D from pinned staging)
+    //              | map point arrays, one block per array over all pairs | scratch | [assigned of every pair | nmatches] (one D2H)
+    // The map point blocks are unpadded concatenations in pair order. A caller that keeps its map point arrays that way
+    // (pair p+1's array starts where pair p's ends) has them copied straight from its memory with one cudaMemcpyAsync per
+    // array; otherwise they pass through the pinned staging like everything else.
     struct Off { size_t curKeys, curDesc, curUR, lastKeys, has, pos, pdesc, obs, cellStart, cellItems, best, proj, events, assigned; };
     std::vector<Off> off(nPairs);
     OrbxPacker pk;
     const size_t oDev = pk.take(sizeof(FrameDev) * (size_t)nPairs);
+    size_t totalLast = 0;
+    bool contiguous = true;
     for (int p = 0; p < nPairs; ++p) {
         const size_t nc = cur[p].n, nl = last[p].n;
-        off[p].curKeys = pk.take(nc * 28); off[p].curDesc = pk.take(nc * 32); off[p].curUR = pk.take(cur[p].u_right ? nc * 4 : 0);
-        off[p].lastKeys = pk.take(nl * 28); off[p].has = pk.take(nl); off[p].pos = pk.take(nl * 12); off[p].pdesc = pk.take(nl * 32);
-        off[p].obs = pk.take(nl);
+        const bool curRes = rc[p].keys != nullptr, lastRes = rl[p].keys != nullptr;
+        off[p].curKeys = pk.take(curRes ? 0 : nc * 28); off[p].curDesc = pk.take(curRes ? 0 : nc * 32);
+        off[p].curUR = pk.take(!curRes && cur[p].u_right ? nc * 4 : 0);
+        off[p].lastKeys = pk.take(lastRes ? 0 : nl * 28);
+        if (nl) {
+            const orbx_mappoint_view &a = lastPoints[0], &q = lastPoints[p];
+            contiguous = contiguous && q.has_point == a.has_point + totalLast && q.observed == a.observed + totalLast &&
+                         q.world_pos == a.world_pos + 3 * totalLast && q.point_desc == a.point_desc + 32 * totalLast;
+        }
+        totalLast += nl;
     }
-    const size_t inBytes = pk.off;
+    if (!lastPoints[0].has_point || last[0].n == 0) contiguous = false;  // (the blocks are anchored at pair 0's arrays)
+    const size_t stagedBytes = pk.off;
+    const size_t oHas = pk.take(totalLast), oObs = pk.take(totalLast), oPos = pk.take(totalLast * 12), oDesc = pk.take(totalLast * 32);
+    {
+        size_t run = 0;
+        for (int p = 0; p < nPairs; ++p) {
+            off[p].has = oHas + run; off[p].obs = oObs + run; off[p].pos = oPos + 12 * run; off[p].pdesc = oDesc + 32 * run;
+            run += last[p].n;
+        }
+    }
+    const size_t inBytes = contiguous ? stagedBytes : pk.off;
     for (int p = 0; p < nPairs; ++p) {
         const size_t nc = cur[p].n, nl = last[p].n;
         off[p].cellStart = pk.take((NCELL + 1) * 4); off[p].cellItems = pk.take(nc * 4 + 4); off[p].best = pk.take(nl * 8 + 8);
@@ -688,6 +764,7 @@ extern "C" int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view*
     for (int p = 0; p < nPairs; ++p) {
         const orbx_frame_view &c = cur[p], &l = last[p];
         const orbx_mappoint_view& mp = lastPoints[p];
+        const bool curRes = rc[p].keys != nullptr, lastRes = rl[p].keys != nullptr;
         FrameDev D;
         fill_frame(D, c);
         D.nLast = l.n;
@@ -697,9 +774,14 @@ extern "C" int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view*
         const bool fwd = tz > c.mb && !bMono, bwd = -tz > c.mb && !bMono;  // :1369-1370
         D.levelMode = fwd ? 1 : bwd ? 2 : 0;
         uint8_t* d = m->dBuf;
-        D.curKeys = (const orbx_keypoint*)(d + off[p].curKeys); D.curDesc = d + off[p].curDesc;
-        D.curUR = c.u_right ? (const float*)(d + off[p].curUR) : nullptr;
-        D.lastKeys = (const orbx_keypoint*)(d + off[p].lastKeys); D.hasPoint = d + off[p].has; D.worldPos = (const float*)(d + off[p].pos);
+        if (curRes) {
+            D.curKeys = rc[p].keys; D.curDesc = rc[p].desc; D.curUR = rc[p].uRight;
+        } else {
+            D.curKeys = (const orbx_keypoint*)(d + off[p].curKeys); D.curDesc = d + off[p].curDesc;
+            D.curUR = c.u_right ? (const float*)(d + off[p].curUR) : nullptr;
+        }
+        D.lastKeys = lastRes ? rl[p].keys : (const orbx_keypoint*)(d + off[p].lastKeys);
+        D.hasPoint = d + off[p].has; D.worldPos = (const float*)(d + off[p].pos);
         D.pointDesc = d + off[p].pdesc; D.observed = d + off[p].obs;
         D.cellStart = (int*)(d + off[p].cellStart); D.cellItems = (int*)(d + off[p].cellItems);
         D.best = (unsigned long long*)(d + off[p].best); D.proj = (float4*)(d + off[p].proj); D.events = (int*)(d + off[p].events);
@@ -707,13 +789,13 @@ extern "C" int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view*
         hd[p] = D;
         uint8_t* h = m->hIn;
         const size_t nc = c.n, nl = l.n;
-        if (nc) {
+        if (nc && !curRes) {
             std::memcpy(h + off[p].curKeys, c.keys_un, nc * 28);
             std::memcpy(h + off[p].curDesc, c.desc, nc * 32);
             if (c.u_right) std::memcpy(h + off[p].curUR, c.u_right, nc * 4);
         }
-        if (nl) {
-            std::memcpy(h + off[p].lastKeys, l.keys_un, nl * 28);
+        if (nl && !lastRes) std::memcpy(h + off[p].lastKeys, l.keys_un, nl * 28);
+        if (nl && !contiguous) {
             std::memcpy(h + off[p].has, mp.has_point, nl);
             std::memcpy(h + off[p].pos, mp.world_pos, nl * 12);
             std::memcpy(h + off[p].pdesc, mp.point_desc, nl * 32);
@@ -721,6 +803,23 @@ extern "C" int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view*
         }
     }
     cudaStream_t s = m->stream;
+    // device-resident sources: behind whatever their batch engines still have in flight
+    {
+        std::vector<orbx_batch*> seen;
+        for (int p = 0; p < nPairs; ++p)
+            for (orbx_batch* b : {curSrc ? curSrc[p].batch : nullptr, lastSrc ? lastSrc[p].batch : nullptr}) {
+                if (!b || std::find(seen.begin(), seen.end(), b) != seen.end()) continue;
+                seen.push_back(b);
+                TRY(order_after_batch(m, b, err));
+            }
+    }
+    if (contiguous && totalLast) {
+        const orbx_mappoint_view& a = lastPoints[0];
+        TRY(orbx_check(cudaMemcpyAsync(m->dBuf + oHas, a.has_point, totalLast, cudaMemcpyHostToDevice, s), "H2D map points", err));
+        TRY(orbx_check(cudaMemcpyAsync(m->dBuf + oObs, a.observed, totalLast, cudaMemcpyHostToDevice, s), "H2D map points", err));
+        TRY(orbx_check(cudaMemcpyAsync(m->dBuf + oPos, a.world_pos, totalLast * 12, cudaMemcpyHostToDevice, s), "H2D map points", err));
+        TRY(orbx_check(cudaMemcpyAsync(m->dBuf + oDesc, a.point_desc, totalLast * 32, cudaMemcpyHostToDevice, s), "H2D map points", err));
+    }
     TRY(orbx_check(cudaMemcpyAsync(m->dBuf, m->hIn, inBytes, cudaMemcpyHostToDevice, s), "H2D frames", err));
     const FrameDev* dd = (const FrameDev*)(m->dBuf + oDev);
     orbx_grid_kernel<<<dim3(1, nPairs), 256, 0, s>>>(dd);
@@ -736,6 +835,22 @@ extern "C" int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view*
         nmatches[p] = *(const int*)(m->hOut + (oNm - outBase) + (size_t)p * 4);
     }
     return ORBX_OK;
+}
+}  // namespace
+
+extern "C" int orbx_search_by_projection(orbx_matcher* m, const orbx_frame_view* cur, const orbx_frame_view* last,
+                                         const orbx_mappoint_view* lastPoints, int nPairs, float th, int bMono, int checkOrientation,
+                                         int* const* matchOfCur, int* nmatches)
+{
+    return search_by_projection_impl(m, cur, nullptr, last, nullptr, lastPoints, nPairs, th, bMono, checkOrientation, matchOfCur, nmatches);
+}
+
+extern "C" int orbx_search_by_projection_resident(orbx_matcher* m, const orbx_frame_view* cur, const orbx_frame_source* curSrc,
+                                                  const orbx_frame_view* last, const orbx_frame_source* lastSrc,
+                                                  const orbx_mappoint_view* lastPoints, int nPairs, float th, int bMono,
+                                                  int checkOrientation, int* const* matchOfCur, int* nmatches)
+{
+    return search_by_projection_impl(m, cur, curSrc, last, lastSrc, lastPoints, nPairs, th, bMono, checkOrientation, matchOfCur, nmatches);
 }
 
 extern "C" int orbx_search_local_points(orbx_matcher* m, const orbx_frame_view* frames, const uint8_t* const* occupied,

@@ -24,4 +24,11 @@ struct orbx_extractor {
     int viewImg = 0;
 };
 
+struct orbx_batch {
+    ExtractorConfig cfg;
+    Engine eng;
+    int maxFrames = 0;
+    bool stereo = false;
+};
+
 std::string& orbx_err_slot();  // thread-local text behind orbx_last_error() (abi.cu)

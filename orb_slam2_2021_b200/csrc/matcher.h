@@ -17,6 +17,7 @@ struct orbx_matcher {
     uint8_t* dBuf = nullptr; size_t dCap = 0;   // packed inputs | scratch | outputs
     uint8_t* hIn = nullptr; size_t hInCap = 0;  // pinned staging of the inputs
     uint8_t* hOut = nullptr; size_t hOutCap = 0;
+    cudaEvent_t orderEvent = nullptr;  // orders the matcher's stream behind a batch engine's (device-resident sources)
 };
 
 inline int orbx_fail(int code, const char* msg) { orbx_err_slot() = msg; return code; }

@@ -29,6 +29,10 @@ class _MapPointStruct(C.Structure):  # orbx_mappoint_view
                 ("observed", C.c_void_p)]
 
 
+class _FrameSourceStruct(C.Structure):  # orbx_frame_source
+    _fields_ = [("batch", C.c_void_p), ("frame", C.c_int), ("side", C.c_int)]
+
+
 class FrameView:
     """mvKeysUn, mDescriptors, mvuRight, mTcw, intrinsics, image bounds and mvScaleFactors of one Frame."""
 
@@ -183,8 +187,11 @@ class Matcher:
         res = [(o[: f.N], int(k)) for o, f, k in zip(outs, fr, nm)]
         return res[0] if single else res
 
-    def SearchByProjection(self, CurrentFrame, LastFrame, lastPoints, th, bMono=False):
-        """One (current, last) pair, or lists of pairs -> (match_of_cur int32[N_cur], nmatches) per pair."""
+    def SearchByProjection(self, CurrentFrame, LastFrame, lastPoints, th, bMono=False, cur_src=None, last_src=None):
+        """One (current, last) pair, or lists of pairs -> (match_of_cur int32[N_cur], nmatches) per pair.
+        cur_src / last_src: per pair None or (StereoFrameBatch, frame, side): the frame's keypoints, descriptors and uRight
+        are read where the batch engine left them on the device (orbx_search_by_projection_resident) instead of from the
+        view's host arrays."""
         single = isinstance(CurrentFrame, FrameView)
         cur = [CurrentFrame] if single else list(CurrentFrame)
         last = [LastFrame] if single else list(LastFrame)
@@ -199,6 +206,16 @@ class Matcher:
         outs = [np.full(max(f.N, 1), -1, np.int32) for f in cur]
         op = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
         nm = np.zeros(n, np.int32)
-        check(lib().orbx_search_by_projection(self._h, ca, la, pa, n, float(th), int(bMono), int(self.mbCheckOrientation), op, ptr(nm)))
+        if cur_src is None and last_src is None:
+            check(lib().orbx_search_by_projection(self._h, ca, la, pa, n, float(th), int(bMono), int(self.mbCheckOrientation), op, ptr(nm)))
+        else:
+            def srcs(v):
+                v = [v] if single and (v is None or isinstance(v, tuple)) else (list(v) if v is not None else [None] * n)
+                if len(v) != n:
+                    raise ValueError("need one frame source (or None) per pair")
+                return (_FrameSourceStruct * n)(*[_FrameSourceStruct(None, 0, 0) if x is None else _FrameSourceStruct(x[0]._h, x[1], x[2])
+                                                  for x in v])
+            check(lib().orbx_search_by_projection_resident(self._h, ca, srcs(cur_src), la, srcs(last_src), pa, n, float(th), int(bMono),
+                                                           int(self.mbCheckOrientation), op, ptr(nm)))
         res = [(o[: f.N], int(k)) for o, f, k in zip(outs, cur, nm)]
         return res[0] if single else res

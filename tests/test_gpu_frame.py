@@ -253,3 +253,81 @@ def test_search_local_points_batch():
         ref, nref = O.search_local_points(U.view(O.FrameView, s[0]), s[1] if k % 2 == 0 else None, *s[2:], 3.0, 0.8)
         assert res[k][1] == nref and np.array_equal(res[k][0], ref), k
     assert res[2][1] == 0
+
+
+# ---- device-resident chaining: SearchByProjection on what a batch engine left on the device ---------------------------
+def _resident_scene(n_pairs=3):
+    """A batch of stereo frames (every image pair twice: frame 2p = current, 2p+1 = last of pair p, same image, identity
+    poses), its downloaded results, and per pair the host views + map points made from the last frame's stereo depth."""
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["kitti"]
+    imgs = [synth.stereo_pair(W, H, 900 + p) for p in range(n_pairs)]
+    left = np.stack([imgs[p // 2][0] for p in range(2 * n_pairs)])
+    right = np.stack([imgs[p // 2][1] for p in range(2 * n_pairs)])
+    batch = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, 2 * n_pairs, stereo=True)
+    out = batch.process(left, right, bf, bf / fx)
+    cx, cy = W / 2.0, H / 2.0
+    sfs = (np.float32(sf) ** np.arange(nl)).astype(np.float32)
+    I = np.hstack([np.eye(3, dtype=np.float32), np.zeros((3, 1), np.float32)])
+    rng = np.random.default_rng(3)
+    views, dummies, pts = [], [], []
+    for f in range(2 * n_pairs):
+        n = int(out["n_left"][f])
+        k, d, u = out["kps_left"][f, :n], out["desc_left"][f, :n], out["u_right"][f, :n]
+        views.append(pkg.FrameView(k, d, u, I, fx, fx, cx, cy, bf, bf / fx, (0.0, float(W), 0.0, float(H)), sfs))
+        dummies.append(pkg.FrameView(np.zeros(n, pkg.KP_DTYPE), np.zeros((n, 32), np.uint8), None, I, fx, fx, cx, cy, bf, bf / fx,
+                                     (0.0, float(W), 0.0, float(H)), sfs))
+    total = sum(views[2 * p + 1].N for p in range(n_pairs))
+    has, obs = np.zeros(total, np.uint8), np.zeros(total, np.uint8)
+    pos, pdesc = np.zeros((total, 3), np.float32), np.zeros((total, 32), np.uint8)
+    at = 0
+    for p in range(n_pairs):
+        f = 2 * p + 1
+        n = views[f].N
+        z = out["depth"][f, :n]
+        k = out["kps_left"][f, :n]
+        s = slice(at, at + n)
+        has[s] = (z > 0) & (rng.random(n) < 0.8)
+        obs[s] = rng.random(n) < 0.6
+        zz = np.where(z > 0, z, 1).astype(np.float32)
+        pos[s] = np.stack([(k["x"] - cx) * zz / fx, (k["y"] - cy) * zz / fx, zz], 1)
+        pdesc[s] = out["desc_left"][f, :n]
+        pts.append((at, n))
+        at += n
+    return batch, views, dummies, (has, pos, pdesc, obs), pts
+
+
+def test_search_by_projection_on_device_resident_frames():
+    """orbx_search_by_projection_resident: the frames' keypoints / descriptors / uRight read where the batch engine left
+    them == the host-array form (which the tests above pin against the oracle and the reference), for map point arrays
+    that are one concatenation (copied straight from the caller's memory) and for separate ones (repacked)."""
+    n_pairs = 3
+    batch, views, dummies, (has, pos, pdesc, obs), pts = _resident_scene(n_pairs)
+    m = pkg.Matcher()
+    cur = [views[2 * p] for p in range(n_pairs)]
+    last = [views[2 * p + 1] for p in range(n_pairs)]
+    concat = [pkg.MapPointView(has[a:a + n], pos[a:a + n], pdesc[a:a + n], obs[a:a + n]) for a, n in pts]
+    separate = [pkg.MapPointView(has[a:a + n].copy(), pos[a:a + n].copy(), pdesc[a:a + n].copy(), obs[a:a + n].copy()) for a, n in pts]
+    assert concat[1].has_point.ctypes.data == concat[0].has_point.ctypes.data + pts[0][1]  # really one concatenation
+    want = m.SearchByProjection(cur, last, separate, 15)
+    assert all(nm > 200 for _, nm in want)
+    o_ref, o_n = O.search_by_projection(O.FrameView(cur[0].keys_un, cur[0].desc, cur[0].u_right, cur[0].Tcw, *[cur[0].c.fx, cur[0].c.fy, cur[0].c.cx, cur[0].c.cy, cur[0].c.mbf, cur[0].c.mb],
+                                                     (0.0, cur[0].c.max_x, 0.0, cur[0].c.max_y), cur[0].scale_factors),
+                                        O.FrameView(last[0].keys_un, last[0].desc, last[0].u_right, last[0].Tcw, *[last[0].c.fx, last[0].c.fy, last[0].c.cx, last[0].c.cy, last[0].c.mbf, last[0].c.mb],
+                                                     (0.0, last[0].c.max_x, 0.0, last[0].c.max_y), last[0].scale_factors),
+                                        separate[0].has_point, separate[0].world_pos, separate[0].point_desc, separate[0].observed, 15, False, True)
+    assert o_n == want[0][1] and np.array_equal(o_ref, want[0][0])
+    srcs_c = [(batch, 2 * p, 0) for p in range(n_pairs)]
+    srcs_l = [(batch, 2 * p + 1, 0) for p in range(n_pairs)]
+    for pts_views in (concat, separate):
+        # the views handed over with the sources carry no keypoints or descriptors at all (dummies): nothing of them is read
+        got = m.SearchByProjection([dummies[2 * p] for p in range(n_pairs)], [dummies[2 * p + 1] for p in range(n_pairs)], pts_views, 15,
+                                   cur_src=srcs_c, last_src=srcs_l)
+        for (a, na), (b, nb) in zip(got, want):
+            assert na == nb and np.array_equal(a, b)
+    # mixed: current frame resident, last frame from host arrays; and host views with concatenated map points
+    got = m.SearchByProjection([dummies[2 * p] for p in range(n_pairs)], last, concat, 15, cur_src=srcs_c, last_src=[None] * n_pairs)
+    assert all(na == nb and np.array_equal(a, b) for (a, na), (b, nb) in zip(got, want))
+    got = m.SearchByProjection(cur, last, concat, 15)
+    assert all(na == nb and np.array_equal(a, b) for (a, na), (b, nb) in zip(got, want))
+    with pytest.raises(pkg.OrbxError):  # a frame index outside the batch
+        m.SearchByProjection(dummies[0], dummies[1], concat[0], 15, cur_src=(batch, 99, 0), last_src=(batch, 1, 0))
