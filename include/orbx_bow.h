@@ -33,6 +33,14 @@ int orbx_compute_bow(orbx_vocabulary* v, const uint8_t* const* desc, const int* 
                      double* const* word_vals, int* n_words, int* const* fv_nodes, int* const* fv_start, int* const* fv_feats,
                      int* n_fv_nodes);
 
+/* The same on descriptors that are still on the device: frames first_frame .. first_frame + n_frames - 1, side `side`
+ * (0 = left / mono) of a batch engine after orbx_batch_run / orbx_batch_process* — as Frame::ComputeBoW works on the
+ * mDescriptors the extractor just produced (src/Frame.cc:447-454), without carrying them through the host. n[f] = the
+ * frame's keypoint count (as downloaded). Outputs and values identical to orbx_compute_bow. */
+int orbx_compute_bow_resident(orbx_vocabulary* v, orbx_batch* batch, int first_frame, int side, const int* n, int n_frames,
+                              int levelsup, int* const* word_ids, double* const* word_vals, int* n_words, int* const* fv_nodes,
+                              int* const* fv_start, int* const* fv_feats, int* n_fv_nodes);
+
 #ifdef __cplusplus
 }
 #endif

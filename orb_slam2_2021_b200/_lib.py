@@ -96,6 +96,7 @@ SIGNATURES = {
     "orbx_vocabulary_destroy": (None, [_vp]),
     "orbx_vocabulary_words": (_i, [_vp]),
     "orbx_compute_bow": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "orbx_compute_bow_resident": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
 }
 
 

@@ -47,3 +47,19 @@ class ORBVocabulary:
                                      ptr(nfv)))
         res = [(wi[f][: nw[f]], wv[f][: nw[f]], fn[f][: nfv[f]], fs[f][: nfv[f] + 1], ff[f][: fs[f][nfv[f]]]) for f in range(nf)]
         return res[0] if single else res
+
+    def transform_resident(self, batch, n, first_frame=0, side=0, levelsup=4):
+        """transform() on descriptors that are still on the device: frames first_frame.. of `batch` (a StereoFrameBatch after
+        run / process), n[f] = the frames' keypoint counts -> the same tuples as transform(), one per frame."""
+        n = np.ascontiguousarray(n, dtype=np.int32)
+        nf = len(n)
+        wi = [np.zeros(max(k, 1), np.int32) for k in n]
+        wv = [np.zeros(max(k, 1), np.float64) for k in n]
+        fn = [np.zeros(max(k, 1), np.int32) for k in n]
+        fs = [np.zeros(k + 1, np.int32) for k in n]
+        ff = [np.zeros(max(k, 1), np.int32) for k in n]
+        arr = lambda xs: (C.c_void_p * nf)(*[x.ctypes.data for x in xs])  # noqa: E731
+        nw, nfv = np.zeros(nf, np.int32), np.zeros(nf, np.int32)
+        check(lib().orbx_compute_bow_resident(self._h, batch._h, int(first_frame), int(side), ptr(n), nf, int(levelsup), arr(wi), arr(wv),
+                                              ptr(nw), arr(fn), arr(fs), arr(ff), ptr(nfv)))
+        return [(wi[f][: nw[f]], wv[f][: nw[f]], fn[f][: nfv[f]], fs[f][: nfv[f] + 1], ff[f][: fs[f][nfv[f]]]) for f in range(nf)]

@@ -17,6 +17,7 @@
 #include "../../include/orbx_bow.h"
 #include "engine.h"
 #include "matcher.h"
+#include "handles.h"
 
 struct orbx_vocabulary {
     orbx_matcher ctx;  // stream + packed call buffers
@@ -235,9 +236,10 @@ extern "C" void orbx_vocabulary_destroy(orbx_vocabulary* v)
 
 extern "C" int orbx_vocabulary_words(const orbx_vocabulary* v) { return v ? v->nWords : ORBX_ERR_ARG; }
 
-extern "C" int orbx_compute_bow(orbx_vocabulary* v, const uint8_t* const* desc, const int* n, int nFrames, int levelsup, int* const* wordIds,
-                                double* const* wordVals, int* nWords, int* const* fvNodes, int* const* fvStart, int* const* fvFeats,
-                                int* nFvNodes)
+// desc[f]: host descriptors (resident == NULL) or, with `resident`, device pointers into a batch engine (nothing is uploaded)
+static int compute_bow_impl(orbx_vocabulary* v, const uint8_t* const* desc, orbx_batch* resident, const int* n, int nFrames, int levelsup,
+                            int* const* wordIds, double* const* wordVals, int* nWords, int* const* fvNodes, int* const* fvStart,
+                            int* const* fvFeats, int* nFvNodes)
 {
     if (!v || !desc || !n || nFrames < 1 || !wordIds || !wordVals || !nWords || !fvNodes || !fvStart || !fvFeats || !nFvNodes)
         return orbx_fail(ORBX_ERR_ARG, "bad arguments");
@@ -254,7 +256,7 @@ extern "C" int orbx_compute_bow(orbx_vocabulary* v, const uint8_t* const* desc, 
     std::vector<Off> off(nFrames);
     OrbxPacker pk;
     const size_t oFr = pk.take(sizeof(BowFrame) * (size_t)nFrames);
-    for (int f = 0; f < nFrames; ++f) off[f].desc = pk.take((size_t)n[f] * 32);
+    for (int f = 0; f < nFrames; ++f) off[f].desc = pk.take(resident ? 0 : (size_t)n[f] * 32);
     const size_t inBytes = pk.off;
     for (int f = 0; f < nFrames; ++f) { off[f].word = pk.take((size_t)n[f] * 4); off[f].nid = pk.take((size_t)n[f] * 4); off[f].w = pk.take((size_t)n[f] * 8); }
     const size_t outBase = pk.off;
@@ -269,13 +271,20 @@ extern "C" int orbx_compute_bow(orbx_vocabulary* v, const uint8_t* const* desc, 
         uint8_t* d = m->dBuf;
         BowFrame F{};
         F.n = n[f];
-        F.desc = d + off[f].desc; F.word = (int*)(d + off[f].word); F.nid = (int*)(d + off[f].nid); F.w = (double*)(d + off[f].w);
+        F.desc = resident ? desc[f] : d + off[f].desc; F.word = (int*)(d + off[f].word); F.nid = (int*)(d + off[f].nid); F.w = (double*)(d + off[f].w);
         F.wordIds = (int*)(d + off[f].ids); F.wordVals = (double*)(d + off[f].vals); F.fvNodes = (int*)(d + off[f].fn);
         F.fvStart = (int*)(d + off[f].fs); F.fvFeats = (int*)(d + off[f].ff); F.counts = (int*)(d + off[f].cnt);
         hf[f] = F;
-        if (n[f]) std::memcpy(m->hIn + off[f].desc, desc[f], (size_t)n[f] * 32);
+        if (n[f] && !resident) std::memcpy(m->hIn + off[f].desc, desc[f], (size_t)n[f] * 32);
     }
     cudaStream_t s = m->stream;
+    if (resident) {  // behind whatever the batch engine still has in flight
+        Engine& E = resident->eng;
+        if (!E.lastBounds.empty()) TRY(E.waitPipelined(err));
+        if (!m->orderEvent) TRY(orbx_check(cudaEventCreateWithFlags(&m->orderEvent, cudaEventDisableTiming), "cudaEventCreate", err));
+        TRY(orbx_check(cudaEventRecord(m->orderEvent, E.stream), "event", err));
+        TRY(orbx_check(cudaStreamWaitEvent(s, m->orderEvent, 0), "wait", err));
+    }
     TRY(orbx_check(cudaMemcpyAsync(m->dBuf, m->hIn, inBytes, cudaMemcpyHostToDevice, s), "H2D descriptors", err));
     const BowFrame* df = (const BowFrame*)(m->dBuf + oFr);
     VocDev V{v->dChildStart, v->dChildren, v->dDesc, v->dWeight, v->dWordId, v->L - levelsup};
@@ -300,4 +309,27 @@ extern "C" int orbx_compute_bow(orbx_vocabulary* v, const uint8_t* const* desc, 
         if (nv) std::memcpy(fvFeats[f], h + off[f].ff, (size_t)nv * 4);
     }
     return ORBX_OK;
+}
+
+extern "C" int orbx_compute_bow(orbx_vocabulary* v, const uint8_t* const* desc, const int* n, int nFrames, int levelsup, int* const* wordIds,
+                                double* const* wordVals, int* nWords, int* const* fvNodes, int* const* fvStart, int* const* fvFeats,
+                                int* nFvNodes)
+{
+    return compute_bow_impl(v, desc, nullptr, n, nFrames, levelsup, wordIds, wordVals, nWords, fvNodes, fvStart, fvFeats, nFvNodes);
+}
+
+extern "C" int orbx_compute_bow_resident(orbx_vocabulary* v, orbx_batch* b, int firstFrame, int side, const int* n, int nFrames, int levelsup,
+                                         int* const* wordIds, double* const* wordVals, int* nWords, int* const* fvNodes, int* const* fvStart,
+                                         int* const* fvFeats, int* nFvNodes)
+{
+    if (!v || !b || !n || nFrames < 1) return orbx_fail(ORBX_ERR_ARG, "bad arguments");
+    const int per = b->stereo ? 2 : 1;
+    if (firstFrame < 0 || firstFrame + nFrames > b->maxFrames || side < 0 || side >= per) return orbx_fail(ORBX_ERR_ARG, "frames outside the batch");
+    if (b->eng.device != v->ctx.device) return orbx_fail(ORBX_ERR_STATE, "batch and vocabulary live on different devices");
+    std::vector<const uint8_t*> dd(nFrames);
+    for (int f = 0; f < nFrames; ++f) {
+        if (n[f] > b->eng.P.maxKp) return orbx_fail(ORBX_ERR_ARG, "more features than the batch engine can hold");
+        dd[f] = b->eng.P.outDesc + ((size_t)(firstFrame + f) * per + side) * b->eng.P.maxKp * 32;
+    }
+    return compute_bow_impl(v, dd.data(), b, n, nFrames, levelsup, wordIds, wordVals, nWords, fvNodes, fvStart, fvFeats, nFvNodes);
 }

@@ -56,3 +56,27 @@ def test_bow_errors():
     v = pkg.ORBVocabulary(2, p, l, d, w)
     with pytest.raises(pkg.OrbxError):
         v.transform(np.zeros((9000, 32), np.uint8))
+
+
+def test_bow_on_device_resident_descriptors():
+    """orbx_compute_bow_resident (the descriptors read where the batch engine left them) == orbx_compute_bow on the
+    downloaded descriptors == the oracle, left and right side, a frame range in the middle of the batch."""
+    from orb_slam2_2021_b200 import synth
+
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["euroc"]
+    n = 5
+    left, right = synth.stereo_batch(W, H, n, seed0=70)
+    batch = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, n, stereo=True)
+    out = batch.process(left, right, bf, bf / fx)
+    arrays = B.synthetic_vocabulary(10, 4, seed=2)
+    gv, ov = pkg.ORBVocabulary(4, *arrays), O.Vocabulary(4, *arrays)
+    for side, key in ((0, "left"), (1, "right")):
+        cnt = out["n_" + key][1:4]
+        got = gv.transform_resident(batch, cnt, first_frame=1, side=side)
+        for f, g in zip(range(1, 4), got):
+            d = out["desc_" + key][f, : out["n_" + key][f]]
+            same(g, gv.transform(d, 4))
+            same(g, ov.transform(d, 4))
+            assert len(g[0]) > 100
+    with pytest.raises(pkg.OrbxError):
+        gv.transform_resident(batch, out["n_left"], first_frame=3)  # runs past the batch
