@@ -117,6 +117,13 @@ int orbx_search_local_points(orbx_matcher* m, const orbx_frame_view* frames, con
                              const orbx_trackpoint_view* points, int n_pairs, float th, float nnratio, int* const* match_of_key,
                              int* nmatches);
 
+/* orbx_search_local_points with the frames' keypoints / descriptors / uRight read where a batch engine left them
+ * (frame_src[p], see orbx_search_by_projection_resident; frame_src or frame_src[p].batch NULL = the view's host arrays).
+ * The local map (points) is host state of the SLAM system and is passed as before. Results identical. */
+int orbx_search_local_points_resident(orbx_matcher* m, const orbx_frame_view* frames, const orbx_frame_source* frame_src,
+                                      const uint8_t* const* occupied, const orbx_trackpoint_view* points, int n_pairs, float th,
+                                      float nnratio, int* const* match_of_key, int* nmatches);
+
 #ifdef __cplusplus
 }
 #endif

@@ -87,6 +87,7 @@ SIGNATURES = {
     "orbx_search_by_projection": (_i, [_vp, _vp, _vp, _vp, _i, _f, _i, _i, _vp, _vp]),
     "orbx_search_by_projection_resident": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _i, _i, _vp, _vp]),
     "orbx_search_local_points": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _vp, _vp]),
+    "orbx_search_local_points_resident": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _f, _f, _vp, _vp]),
     # include/orbx_input.h
     "orbx_rectify_gray": (_i, [_vp, _vp, _i, _i, _sz, _i, _i, _vp, _vp, _i, _i, _sz, _i, _i, _vp, _sz]),
     "orbx_batch_set_rectification": (_i, [_vp, _i, _vp, _vp, _i, _i, _sz, _i]),

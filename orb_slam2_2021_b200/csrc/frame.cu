@@ -853,15 +853,23 @@ extern "C" int orbx_search_by_projection_resident(orbx_matcher* m, const orbx_fr
     return search_by_projection_impl(m, cur, curSrc, last, lastSrc, lastPoints, nPairs, th, bMono, checkOrientation, matchOfCur, nmatches);
 }
 
-extern "C" int orbx_search_local_points(orbx_matcher* m, const orbx_frame_view* frames, const uint8_t* const* occupied,
-                                        const orbx_trackpoint_view* points, int nPairs, float th, float nnratio, int* const* matchOfKey,
-                                        int* nmatches)
+static int search_local_points_impl(orbx_matcher* m, const orbx_frame_view* frames, const orbx_frame_source* frameSrc,
+                                    const uint8_t* const* occupied, const orbx_trackpoint_view* points, int nPairs, float th,
+                                    float nnratio, int* const* matchOfKey, int* nmatches)
 {
     if (!m || !frames || !points || nPairs < 1 || !matchOfKey || !nmatches) return orbx_fail(ORBX_ERR_ARG, "bad arguments");
     std::string& err = orbx_err_slot();
     int maxPts = 0, maxKeys = 0;
+    std::vector<ResidentFrame> rf(nPairs);
     for (int p = 0; p < nPairs; ++p) {
-        TRY(check_frame(frames + p, true));
+        if (frameSrc && frameSrc[p].batch) {  // keys_un / desc / u_right of the view are not read
+            orbx_frame_view v = frames[p];
+            v.keys_un = reinterpret_cast<const orbx_keypoint*>(&v); v.desc = reinterpret_cast<const uint8_t*>(&v);
+            TRY(check_frame(&v, true));
+            TRY(resolve_source(m, frameSrc[p], frames[p], rf[p]));
+        } else {
+            TRY(check_frame(frames + p, true));
+        }
         const orbx_trackpoint_view& t = points[p];
         if (t.n < 0 || (t.n && (!t.valid || !t.proj || !t.level || !t.view_cos || !t.point_desc || !t.observed))) return orbx_fail(ORBX_ERR_ARG, "bad map point view");
         if (frames[p].n && !matchOfKey[p]) return orbx_fail(ORBX_ERR_ARG, "match_of_key is NULL");
@@ -877,7 +885,8 @@ extern "C" int orbx_search_local_points(orbx_matcher* m, const orbx_frame_view* 
     const size_t oF = pk.take(sizeof(FrameDev) * (size_t)nPairs), oM = pk.take(sizeof(MapDev) * (size_t)nPairs);
     for (int p = 0; p < nPairs; ++p) {
         const size_t nk = frames[p].n, np = points[p].n;
-        off[p].keys = pk.take(nk * 28); off[p].desc = pk.take(nk * 32); off[p].ur = pk.take(frames[p].u_right ? nk * 4 : 0);
+        const bool res = rf[p].keys != nullptr;
+        off[p].keys = pk.take(res ? 0 : nk * 28); off[p].desc = pk.take(res ? 0 : nk * 32); off[p].ur = pk.take(!res && frames[p].u_right ? nk * 4 : 0);
         off[p].occ = pk.take(occupied && occupied[p] ? nk : 0);
         off[p].valid = pk.take(np); off[p].proj = pk.take(np * 12); off[p].level = pk.take(np * 4); off[p].vc = pk.take(np * 4);
         off[p].pdesc = pk.take(np * 32); off[p].obs = pk.take(np);
@@ -902,8 +911,13 @@ extern "C" int orbx_search_local_points(orbx_matcher* m, const orbx_frame_view* 
         uint8_t *d = m->dBuf, *h = m->hIn;
         FrameDev D;
         fill_frame(D, c);
-        D.curKeys = (const orbx_keypoint*)(d + off[p].keys); D.curDesc = d + off[p].desc;
-        D.curUR = c.u_right ? (const float*)(d + off[p].ur) : nullptr;
+        const bool res = rf[p].keys != nullptr;
+        if (res) {
+            D.curKeys = rf[p].keys; D.curDesc = rf[p].desc; D.curUR = rf[p].uRight;
+        } else {
+            D.curKeys = (const orbx_keypoint*)(d + off[p].keys); D.curDesc = d + off[p].desc;
+            D.curUR = c.u_right ? (const float*)(d + off[p].ur) : nullptr;
+        }
         D.cellStart = (int*)(d + off[p].cellStart); D.cellItems = (int*)(d + off[p].cellItems);
         D.best = (unsigned long long*)(d + off[p].best); D.assigned = (int*)(d + off[p].assigned); D.nmatches = (int*)(d + oNm) + p;
         hf[p] = D;
@@ -915,12 +929,12 @@ extern "C" int orbx_search_local_points(orbx_matcher* m, const orbx_frame_view* 
         X.best2 = (unsigned long long*)(d + off[p].best2);
         hm[p] = X;
         const size_t nk = c.n, np = t.n;
-        if (nk) {
+        if (nk && !res) {
             std::memcpy(h + off[p].keys, c.keys_un, nk * 28);
             std::memcpy(h + off[p].desc, c.desc, nk * 32);
             if (c.u_right) std::memcpy(h + off[p].ur, c.u_right, nk * 4);
-            if (occ) std::memcpy(h + off[p].occ, occupied[p], nk);
         }
+        if (nk && occ) std::memcpy(h + off[p].occ, occupied[p], nk);
         if (np) {
             std::memcpy(h + off[p].valid, t.valid, np); std::memcpy(h + off[p].proj, t.proj, np * 12);
             std::memcpy(h + off[p].level, t.level, np * 4); std::memcpy(h + off[p].vc, t.view_cos, np * 4);
@@ -928,6 +942,15 @@ extern "C" int orbx_search_local_points(orbx_matcher* m, const orbx_frame_view* 
         }
     }
     cudaStream_t s = m->stream;
+    {
+        std::vector<orbx_batch*> seen;
+        for (int p = 0; frameSrc && p < nPairs; ++p) {
+            orbx_batch* b = frameSrc[p].batch;
+            if (!b || std::find(seen.begin(), seen.end(), b) != seen.end()) continue;
+            seen.push_back(b);
+            TRY(order_after_batch(m, b, err));
+        }
+    }
     TRY(orbx_check(cudaMemcpyAsync(m->dBuf, m->hIn, inBytes, cudaMemcpyHostToDevice, s), "H2D local map", err));
     const FrameDev* df = (const FrameDev*)(m->dBuf + oF);
     const MapDev* dm = (const MapDev*)(m->dBuf + oM);
@@ -944,4 +967,18 @@ extern "C" int orbx_search_local_points(orbx_matcher* m, const orbx_frame_view* 
         nmatches[p] = *(const int*)(m->hOut + (oNm - outBase) + (size_t)p * 4);
     }
     return ORBX_OK;
+}
+
+extern "C" int orbx_search_local_points(orbx_matcher* m, const orbx_frame_view* frames, const uint8_t* const* occupied,
+                                        const orbx_trackpoint_view* points, int nPairs, float th, float nnratio, int* const* matchOfKey,
+                                        int* nmatches)
+{
+    return search_local_points_impl(m, frames, nullptr, occupied, points, nPairs, th, nnratio, matchOfKey, nmatches);
+}
+
+extern "C" int orbx_search_local_points_resident(orbx_matcher* m, const orbx_frame_view* frames, const orbx_frame_source* frameSrc,
+                                                 const uint8_t* const* occupied, const orbx_trackpoint_view* points, int nPairs, float th,
+                                                 float nnratio, int* const* matchOfKey, int* nmatches)
+{
+    return search_local_points_impl(m, frames, frameSrc, occupied, points, nPairs, th, nnratio, matchOfKey, nmatches);
 }

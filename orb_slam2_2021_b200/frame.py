@@ -163,7 +163,7 @@ class Matcher:
                                               ptr(out), frame.N, C.byref(n)))
         return out[: n.value]
 
-    def SearchLocalPoints(self, F, points, th, occupied=None, nnratio=0.8):
+    def SearchLocalPoints(self, F, points, th, occupied=None, nnratio=0.8, frame_src=None):
         """ORBmatcher(nnratio).SearchByProjection(F, vpMapPoints, th) (src/ORBmatcher.cc:45-127). One (frame, local map) pair or
         lists of pairs -> (match_of_key int32[N], nmatches) per pair. occupied: per keypoint, F.mvpMapPoints[i] holds a point
         with Observations() > 0 on entry."""
@@ -183,7 +183,12 @@ class Matcher:
         outs = [np.full(max(f.N, 1), -1, np.int32) for f in fr]
         op = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
         nm = np.zeros(n, np.int32)
-        check(lib().orbx_search_local_points(self._h, fa, oa, pa, n, float(th), float(nnratio), op, ptr(nm)))
+        if frame_src is None:
+            check(lib().orbx_search_local_points(self._h, fa, oa, pa, n, float(th), float(nnratio), op, ptr(nm)))
+        else:  # per pair None or (StereoFrameBatch, frame, side): the frame's arrays are read on the device
+            v = [frame_src] if single else list(frame_src)
+            sa = (_FrameSourceStruct * n)(*[_FrameSourceStruct(None, 0, 0) if x is None else _FrameSourceStruct(x[0]._h, x[1], x[2]) for x in v])
+            check(lib().orbx_search_local_points_resident(self._h, fa, sa, oa, pa, n, float(th), float(nnratio), op, ptr(nm)))
         res = [(o[: f.N], int(k)) for o, f, k in zip(outs, fr, nm)]
         return res[0] if single else res
 

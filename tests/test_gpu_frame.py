@@ -331,3 +331,32 @@ def test_search_by_projection_on_device_resident_frames():
     assert all(na == nb and np.array_equal(a, b) for (a, na), (b, nb) in zip(got, want))
     with pytest.raises(pkg.OrbxError):  # a frame index outside the batch
         m.SearchByProjection(dummies[0], dummies[1], concat[0], 15, cur_src=(batch, 99, 0), last_src=(batch, 1, 0))
+
+
+def test_search_local_points_on_device_resident_frames():
+    """orbx_search_local_points_resident == the host-array form: local map = the frames' own keypoints reprojected (same
+    pixel, predicted level = octave), so that most points find their keypoint."""
+    n_pairs = 3
+    batch, views, dummies, _, _ = _resident_scene(n_pairs)
+    rng = np.random.default_rng(11)
+    frames, dums, srcs, pts, occ = [], [], [], [], []
+    for p in range(n_pairs):
+        f = 2 * p
+        v = views[f]
+        n = v.N
+        k = v.keys_un
+        sel = rng.permutation(n)[: n // 2]
+        proj = np.stack([k["x"][sel] + rng.normal(0, 0.7, len(sel)), k["y"][sel] + rng.normal(0, 0.7, len(sel)),
+                         np.where(v.u_right[sel] >= 0, v.u_right[sel], -1)], 1).astype(np.float32)
+        pts.append(pkg.TrackPointView(rng.random(len(sel)) < 0.9, proj, k["octave"][sel], rng.uniform(0.99, 1.0, len(sel)).astype(np.float32),
+                                      v.desc[sel], rng.random(len(sel)) < 0.7))
+        occ.append((rng.random(n) < 0.1).astype(np.uint8))
+        frames.append(v)
+        dums.append(dummies[f])
+        srcs.append((batch, f, 0))
+    m = pkg.Matcher()
+    want = m.SearchLocalPoints(frames, pts, 3, occupied=occ)
+    got = m.SearchLocalPoints(dums, pts, 3, occupied=occ, frame_src=srcs)
+    assert all(nm > 200 for _, nm in want)
+    for (a, na), (b, nb) in zip(got, want):
+        assert na == nb and np.array_equal(a, b)
