@@ -57,7 +57,7 @@ int orbx_stereo_bin_radius(const float* scale, int nlevels)
 // ---- tuning table (orbx_set_tuning) ---------------------------------------------------------------------
 static int g_tune[ORBX_TUNE_COUNT] = {0};
 static const char* const g_tuneNames[ORBX_TUNE_COUNT] = {"run_streams", "run_chunks", "e2e_streams", "e2e_chunks", "e2e_first_div",
-                                                         "e2e_trace", "fast_cells", "fast_grid_mult", "numa_off"};
+                                                         "e2e_trace", "fast_cells", "fast_grid_mult", "numa_off", "pyr_chain"};
 int orbx_tune(OrbxTune key) { return g_tune[key]; }
 extern "C" int orbx_set_tuning(const char* key, int value)
 {
@@ -301,6 +301,8 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     P.outKp = okp;
     TRY(dalloc(this, &P.outDesc, n * P.maxKp * 32, "outDesc", err));
     TRY(dalloc(this, &P.outCnt, n, "outCnt", err));
+    P.chainInts = orbx_pyramid_chain_state_ints(P);
+    TRY(dalloc(this, &P.chainState, n * P.chainInts, "chainState", err));
     TRY(orbx_check(cudaMemsetAsync(P.outCnt, 0, n * sizeof(int), stream), "memset", err));
     TRY(orbx_check(cudaMemsetAsync(P.keepCnt, 0, n * P.nlevels * sizeof(int), stream), "memset", err));
     TRY(orbx_check(cudaMemsetAsync(P.candCnt, 0, n * P.nlevels * sizeof(int), stream), "memset", err));
@@ -409,7 +411,7 @@ int Engine::runExtract(int nImgs, std::string& err)
     TRY(orbx_check(cudaSetDevice(device), "cudaSetDevice", err));
     OrbxParams p = slice(0, nImgs);
     mark(0);
-    orbx_launch_pyramid(p, resizeTabs.data(), stream);
+    launchPyramid(p, stream);
     mark(1);
     orbx_launch_fast(p, dCells, dFastMaps, stream);
     mark(2);
@@ -443,12 +445,22 @@ OrbxParams Engine::slice(int b, int nImgs) const
     p.candXY += o * P.candTotal; p.candRs += o * P.candTotal; p.label += o * P.candTotal;
     p.keep += o * P.keepTotal; p.keepCnt += o * P.nlevels; p.candCnt += o * P.nlevels; p.keepOfs += o * P.nlevels;
     p.outKp = (uint8_t*)P.outKp + o * P.maxKp * 28; p.outDesc += o * P.maxKp * 32; p.outCnt += o;
+    p.chainState += o * P.chainInts;
     return p;
+}
+
+// Few images: the whole pyramid as one launch (tiles chained by readiness counters); many images: one launch per level,
+// each wide enough by itself. Tuning key pyr_chain: 1 forces the one-launch form, 2 the per-level form.
+void Engine::launchPyramid(const OrbxParams& p, cudaStream_t s)
+{
+    const int mode = orbx_tune(ORBX_TUNE_PYR_CHAIN);
+    if (mode == 1 || (mode == 0 && p.imgs <= 8)) orbx_launch_pyramid_chain(p, resizeTabs.data(), p.chainState, s);
+    else orbx_launch_pyramid(p, resizeTabs.data(), s);
 }
 
 void Engine::launchExtract(const OrbxParams& p, cudaStream_t s)
 {
-    orbx_launch_pyramid(p, resizeTabs.data(), s);
+    launchPyramid(p, s);
     orbx_launch_fast(p, dCells, dFastMaps, s);
     orbx_launch_octree(p, dCells, s);
     orbx_launch_blur(p, dTiles, nTiles, dBlurMaps, s);
@@ -639,7 +651,7 @@ void Engine::enqueueFrame(float mbf, float mb, cudaStream_t s)
     // the blur needs only the pyramid: it runs beside FAST and the quadtree (a second branch of the graph) and joins before
     // the descriptors
     const OrbxParams p = slice(0, maxImgs);
-    orbx_launch_pyramid(p, resizeTabs.data(), s);
+    launchPyramid(p, s);
     cudaEventRecord(frameFork, s);
     cudaStreamWaitEvent(stream2, frameFork, 0);
     orbx_launch_blur(p, dTiles, nTiles, dBlurMaps, stream2);

@@ -41,6 +41,7 @@ public:
     // The same on images [imgBase, imgBase+nImgs) / frames [f0, f0+nFrames) only (chunked pipeline; no stage timing)
     OrbxParams slice(int imgBase, int nImgs) const;
     void launchExtract(const OrbxParams& p, cudaStream_t s);
+    void launchPyramid(const OrbxParams& p, cudaStream_t s);
     void launchStereo(int f0, int nFrames, float mbf, float mb, cudaStream_t s);
     // upload + run + download with H2D, kernels and D2H of successive frame chunks overlapped on three streams
     struct HostOutputs {
@@ -123,6 +124,7 @@ enum OrbxTune {
     ORBX_TUNE_FAST_CELLS,      // cells (warps) per FAST CTA: 2 / 4 / 8
     ORBX_TUNE_FAST_GRID_MULT,  // FAST CTAs launched per resident CTA slot
     ORBX_TUNE_NUMA_OFF,        // 1: orbx_host_alloc skips the NUMA placement
+    ORBX_TUNE_PYR_CHAIN,       // pyramid: 0 = one launch for <= 8 images, else one per level; 1 = always one launch; 2 = always per level
     ORBX_TUNE_COUNT
 };
 int orbx_tune(OrbxTune key);

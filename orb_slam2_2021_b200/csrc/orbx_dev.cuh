@@ -70,6 +70,8 @@ struct OrbxParams {
     int* keepCnt;
     int* candCnt;  // [imgs][L] number of candidates per level (written by the quadtree kernel)
     int* keepOfs;  // [imgs][L] exclusive prefix of keepCnt = first output index of a level (written by the count kernel)
+    int* chainState;   // counters of the one-launch pyramid (orbx_launch_pyramid_chain): chainInts per image, advanced by slice()
+    int chainInts;
     void* outKp;   // orbx_keypoint[imgs][maxKp]
     uint8_t* outDesc;
     int* outCnt;
@@ -119,6 +121,8 @@ struct OrbxStageArgs {
 void orbx_launch_stage(const OrbxStageArgs& a, int channels, int nImgs, cudaStream_t s);
 void orbx_launch_ingest(const OrbxParams& p, const uint8_t* src, int nFrames, int per, int side, cudaStream_t s);
 void orbx_launch_pyramid(const OrbxParams& p, const int* const* tabs, cudaStream_t s);
+int orbx_pyramid_chain_state_ints(const OrbxParams& p);
+void orbx_launch_pyramid_chain(const OrbxParams& p, const int* const* tabs, int* state, cudaStream_t s);
 void orbx_fast_geometry(const OrbxParams& p, int* boxW, int* rhMax);  // TMA box of the FAST kernel
 void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* levelMaps, cudaStream_t s);
 void orbx_launch_octree(const OrbxParams& p, const void* cellTable, cudaStream_t s);

@@ -45,17 +45,22 @@ struct ResizeArgs {
 // WIDE: a level ratio above 2 (scaleFactor 2 with an odd source size, e.g. 701 -> 350 columns) lets the four columns span
 // 9 source bytes and puts columns 2 and 3 at least 4 bytes past the first one; their pairs are then picked from bytes
 // sx0+4 .. sx0+11 (the third word always holds byte sx0+8) instead of sx0 .. sx0+7.
-template <bool WIDE>
-__global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(const ResizeArgs A)
+// CG: the source level was written earlier in the SAME kernel by other SMs (orbx_pyramid_chain_kernel): loads go to L2
+// (ld.global.cg), the point of coherence, instead of through the non-coherent path.
+template <bool CG>
+__device__ __forceinline__ uint32_t rs_load(const uint32_t* p) { return CG ? __ldcg(p) : __ldg(p); }
+
+// One destination tile of 128 columns x (4 x ROWS) rows, (bx, by), of image img by a (32, 4) thread block; ytabS is the
+// block's staging of the row table.
+template <bool WIDE, bool CG, int ROWS>
+__device__ __forceinline__ void resize_tile(const ResizeArgs& A, int img, int bx, int by, int4 (*ytabS)[ROWS])
 {
-    const int img = blockIdx.z;
-    const int x0 = (blockIdx.x * RS_TX + threadIdx.x) * 4;
-    const int yBeg = (blockIdx.y * RS_TY + threadIdx.y) * RS_ROWS, yEnd = min(yBeg + RS_ROWS, A.dh);
+    const int x0 = (bx * RS_TX + threadIdx.x) * 4;
+    const int yBeg = (by * RS_TY + threadIdx.y) * ROWS, yEnd = min(yBeg + ROWS, A.dh);
     if (yBeg >= yEnd) return;
     // row table entries of this warp's destination rows, staged in shared memory: the emit step reads them with a
     // dependent compare right behind, which as global loads stalled every destination row
-    __shared__ int4 ytabS[RS_TY][RS_ROWS];
-    if (threadIdx.x < RS_ROWS) ytabS[threadIdx.y][threadIdx.x] = A.ytab[min(yBeg + (int)threadIdx.x, A.dh - 1)];
+    if (threadIdx.x < ROWS) ytabS[threadIdx.y][threadIdx.x] = A.ytab[min(yBeg + (int)threadIdx.x, A.dh - 1)];
     __syncwarp();
     if (x0 >= A.dw) return;
     // column geometry: aligned word index of the first source column, byte shift, PRMT selectors, packed coefficients
@@ -87,15 +92,15 @@ __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(const Resize
     {
         const uint32_t* pa = src + (size_t)min(rBeg, shm1) * spw;
         const uint32_t* pb = src + (size_t)min(rBeg + 1, shm1) * spw;
-        a0 = __ldg(pa); a1 = __ldg(pa + 1); a2 = __ldg(pa + 2);
-        b0 = __ldg(pb); b1 = __ldg(pb + 1); b2 = __ldg(pb + 2);
+        a0 = rs_load<CG>(pa); a1 = rs_load<CG>(pa + 1); a2 = rs_load<CG>(pa + 2);
+        b0 = rs_load<CG>(pb); b1 = rs_load<CG>(pb + 1); b2 = rs_load<CG>(pb + 2);
     }
     // one source row: prefetch row r+2 into (N0,N1,N2), interpolate row r from (W0,W1,W2) into HC, emit the destination
     // row whose second source row this is from HP (row r-1) and HC
 #define RS_STEP(W0, W1, W2, N0, N1, N2, HP, HC)                                                                          \
     {                                                                                                                    \
         const uint32_t* pn = src + (size_t)min(r + 2, shm1) * spw;                                                       \
-        N0 = __ldg(pn); N1 = __ldg(pn + 1); N2 = __ldg(pn + 2);                                                          \
+        N0 = rs_load<CG>(pn); N1 = rs_load<CG>(pn + 1); N2 = rs_load<CG>(pn + 2);                                        \
         const uint32_t lo = __funnelshift_r(W0, W1, sh8), hi = __funnelshift_r(W1, W2, sh8); /* bytes sx0 .. sx0+7 */    \
         const uint32_t pA = __byte_perm(lo, hi, selA);                                                                   \
         const uint32_t pB = WIDE ? __byte_perm(hi, W2 >> sh8, selB) : __byte_perm(lo, hi, selB);                         \
@@ -127,6 +132,82 @@ __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(const Resize
 #undef RS_STEP
 }
 
+template <bool WIDE>
+__global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_kernel(const ResizeArgs A)
+{
+    __shared__ int4 ytabS[RS_TY][RS_ROWS];
+    resize_tile<WIDE, false, RS_ROWS>(A, blockIdx.z, blockIdx.x, blockIdx.y, ytabS);
+}
+
+// ---- the whole pyramid in ONE launch ---------------------------------------------------------------------------------
+// For a handful of images (the single-frame path) seven dependent launches of a few dozen CTAs each are mostly launch
+// and drain latency. Here every 128 x 16 tile of every level is a work item; CTAs draw items from an atomic ticket counter
+// in an order in which an item only ever depends on items with SMALLER tickets (level-major inside a group of images), so
+// whoever holds a ticket is running and a waiting CTA always waits for running ones: no deadlock, whatever the grid size.
+// Readiness is tracked per (image, level, 16-row band): a band counter reaches the level's number of column tiles when the
+// band is complete; a tile waits (one thread polls with acquire loads) for the source bands its rows come from. Writers
+// fence before they count up, readers load the source through L2.
+#define CH_ROWS 4                      // destination rows per thread in the chained kernel: short tiles, short dependency steps
+#define CH_BAND (RS_TY * CH_ROWS)      // rows per tile = rows per readiness band
+struct ChainLevel {
+    ResizeArgs A;
+    int tilesX, tilesY, tileBase, bandBase, wide;  // tileBase / bandBase: first tile / band of this level inside one image
+};
+struct ChainArgs {
+    ChainLevel lv[ORBX_MAX_LEVELS];  // [1 .. nlevels-1] used
+    int nlevels, imgs, tilesPerImg, bandsPerImg, group;
+};
+
+__global__ void __launch_bounds__(RS_TX * RS_TY) orbx_pyramid_chain_kernel(const __grid_constant__ ChainArgs C, int* state)
+{
+    __shared__ int4 ytabS[RS_TY][CH_ROWS];
+    __shared__ int sh_ticket;
+    const int tid = threadIdx.y * RS_TX + threadIdx.x;
+    int* ticket = state;                  // state[0]: ticket counter, state[1]: watchdog flag, bands of image i from state[2 + i * bandsPerImg]
+    int* ready = state + 2;
+    const int total = C.imgs * C.tilesPerImg;
+    for (;;) {
+        if (tid == 0) sh_ticket = atomicAdd(ticket, 1);
+        __syncthreads();
+        const int t = sh_ticket;
+        if (t >= total) return;
+        // ticket -> (image, level, tile): groups of `group` images, level-major inside a group, image-minor inside a level
+        const int perGroup = C.group * C.tilesPerImg;
+        const int g = t / perGroup, r = t - g * perGroup;
+        const int gn = min(C.group, C.imgs - g * C.group);  // images in this group
+        int l = 1;
+        while (l + 1 < C.nlevels && r >= gn * C.lv[l + 1].tileBase) ++l;
+        const ChainLevel& L = C.lv[l];
+        const int q = r - gn * L.tileBase, tile = q / gn, img = g * C.group + (q - tile * gn);
+        const int by = tile / L.tilesX, bx = tile - by * L.tilesX;
+        if (l > 1) {  // source rows of this tile's destination rows -> bands of level l-1 that must be complete
+            if (tid == 0) {
+                const ChainLevel& S = C.lv[l - 1];
+                const int yB = by * CH_BAND, yE = min(yB + CH_BAND, L.A.dh) - 1;
+                const int r0 = L.A.ytab[yB].x, r1 = min(L.A.ytab[yE].x + 1, L.A.sh - 1);
+                const int b0 = r0 / CH_BAND, b1 = r1 / CH_BAND;
+                const int* flags = ready + (size_t)img * C.bandsPerImg + S.bandBase;
+                for (int b = b0; b <= b1; ++b) {
+                    unsigned spins = 0;
+                    for (;;) {
+                        int v;
+                        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flags + b) : "memory");
+                        if (v >= S.tilesX) break;
+                        if (++spins > (1u << 24)) { atomicExch(state + 1, 1); break; }  // watchdog: never hang the device
+                        __nanosleep(64);
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        if (L.wide) resize_tile<true, true, CH_ROWS>(L.A, img, bx, by, ytabS);
+        else resize_tile<false, true, CH_ROWS>(L.A, img, bx, by, ytabS);
+        __threadfence();   // this thread's pixels before the band counter
+        __syncthreads();   // (also: everybody is done with ytabS and sh_ticket)
+        if (tid == 0) atomicAdd(ready + (size_t)img * C.bandsPerImg + L.bandBase + by, 1);
+    }
+}
+
 // Level 0 ingest: tight rows (pitch = cols, any alignment) -> pitched rows (16-B multiple, TMA-legal).
 // One thread per aligned 16-byte destination chunk; the source bytes come through L1 (rows are contiguous).
 __global__ void __launch_bounds__(256) orbx_ingest_kernel(OrbxParams p, const uint8_t* src, int per, int side)
@@ -153,21 +234,68 @@ void orbx_launch_ingest(const OrbxParams& p, const uint8_t* src, int nFrames, in
     orbx_ingest_kernel<<<grid, 256, 0, s>>>(p, src, per, side);
 }
 
+static ResizeArgs resize_args(const OrbxParams& p, const int* const* tabs, int l)
+{
+    const OrbxLevel &S = p.lv[l - 1], &D = p.lv[l];
+    ResizeArgs A;
+    A.xofs = tabs[l];
+    A.xcoef = A.xofs + D.w;
+    A.ytab = reinterpret_cast<const int4*>(A.xofs + ((2 * D.w + 3) & ~3));
+    A.src = l == 1 ? p.img0 : p.pyr + S.off;
+    A.srcStride = l == 1 ? p.img0Stride : p.pyrStride;
+    A.dst = p.pyr + D.off;
+    A.dstStride = p.pyrStride;
+    A.sw = S.w; A.sh = S.h; A.sp = S.pitch;
+    A.dw = D.w; A.dh = D.h; A.dp = D.pitch;
+    return A;
+}
+
+int orbx_pyramid_chain_state_ints(const OrbxParams& p)  // per image: its band counters; + 2 per launch (see the kernel)
+{
+    int bands = 0;
+    for (int l = 1; l < p.nlevels; ++l) bands += (p.lv[l].h + CH_BAND - 1) / CH_BAND;
+    return bands + 2;
+}
+
+// The whole pyramid of p.imgs images in one launch; `state` = this launch's private counters (orbx_pyramid_chain_state_ints
+// per image), cleared here.
+void orbx_launch_pyramid_chain(const OrbxParams& p, const int* const* tabs, int* state, cudaStream_t s)
+{
+    if (p.nlevels < 2) return;
+    ChainArgs C{};
+    int tiles = 0, bands = 0;
+    for (int l = 1; l < p.nlevels; ++l) {
+        ChainLevel& L = C.lv[l];
+        L.A = resize_args(p, tabs, l);
+        L.tilesX = (p.lv[l].w + 4 * RS_TX - 1) / (4 * RS_TX);
+        L.tilesY = (p.lv[l].h + CH_BAND - 1) / CH_BAND;
+        L.tileBase = tiles; L.bandBase = bands;
+        L.wide = p.lv[l - 1].w > 2 * p.lv[l].w;
+        tiles += L.tilesX * L.tilesY;
+        bands += L.tilesY;
+    }
+    C.nlevels = p.nlevels; C.imgs = p.imgs; C.tilesPerImg = tiles; C.bandsPerImg = bands; C.group = 64;
+    cudaMemsetAsync(state, 0, sizeof(int) * ((size_t)p.imgs * bands + 2), s);
+    static int residentCtas[64] = {0};  // per device ordinal
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int& cap = residentCtas[dev & 63];
+    if (!cap) {
+        int perSm = 1, sms = 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, orbx_pyramid_chain_kernel, RS_TX * RS_TY, 0);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cap = (perSm > 0 ? perSm : 1) * sms;
+    }
+    const long long total = (long long)p.imgs * tiles;
+    orbx_pyramid_chain_kernel<<<(int)(total < cap ? total : cap), dim3(RS_TX, RS_TY), 0, s>>>(C, state);
+}
+
 // tabs[l] points at the level's table block: xofs[w] xcoef[w], then (16-byte aligned) ytab[h] as int4
 void orbx_launch_pyramid(const OrbxParams& p, const int* const* tabs, cudaStream_t s)
 {
     for (int l = 1; l < p.nlevels; ++l) {
         const OrbxLevel &S = p.lv[l - 1], &D = p.lv[l];
-        ResizeArgs A;
-        A.xofs = tabs[l];
-        A.xcoef = A.xofs + D.w;
-        A.ytab = reinterpret_cast<const int4*>(A.xofs + ((2 * D.w + 3) & ~3));
-        A.src = l == 1 ? p.img0 : p.pyr + S.off;
-        A.srcStride = l == 1 ? p.img0Stride : p.pyrStride;
-        A.dst = p.pyr + D.off;
-        A.dstStride = p.pyrStride;
-        A.sw = S.w; A.sh = S.h; A.sp = S.pitch;
-        A.dw = D.w; A.dh = D.h; A.dp = D.pitch;
+        const ResizeArgs A = resize_args(p, tabs, l);
         dim3 block(RS_TX, RS_TY), grid((D.w + 4 * RS_TX - 1) / (4 * RS_TX), (D.h + RS_ROWS * RS_TY - 1) / (RS_ROWS * RS_TY), p.imgs);
         if (S.w > 2 * D.w) orbx_resize_kernel<true><<<grid, block, 0, s>>>(A);   // ratio in (2, 7/3): scaleFactor <= 2 by contract
         else orbx_resize_kernel<false><<<grid, block, 0, s>>>(A);

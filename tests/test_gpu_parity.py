@@ -506,3 +506,46 @@ def test_single_frame_entry_points_state_and_strides():
     a = pkg.stereo_frame(fl, fr, l2, r2, bf, bf / fx)
     b = pkg.stereo_frame(fl, fr, l2, r2, bf, bf / fx)
     assert all(x.tobytes() == y.tobytes() for x, y in zip(a, b)) and len(a[0]) > 300
+
+
+@pytest.mark.gpu
+def test_one_launch_pyramid_equals_the_per_level_launches():
+    """orbx_pyramid_chain_kernel (every tile of every level in one launch, chained by readiness counters) against the
+    per-level launches and the oracle: levels byte for byte, on a batch large enough that tiles of many images and
+    levels are in flight at once (forced with the pyr_chain tuning key; small batches take it by default)."""
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["euroc"]
+    n = 40
+    left, right = synth.stereo_batch(W, H, 4, seed0=90)
+    idx = np.arange(n) % 4
+    L, R = np.ascontiguousarray(left[idx]), np.ascontiguousarray(right[idx])
+    outs, levels = {}, {}
+    for mode in (2, 1):
+        pkg.set_tuning("pyr_chain", mode)
+        try:
+            b = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, n, stereo=True)
+            for rep in range(3):  # repeated runs: the counters are cleared per launch
+                outs[mode] = b.process(L, R, bf, bf / fx)
+            levels[mode] = [b.level(f, s, l) for f in (0, 17, 39) for s in (0, 1) for l in range(nl)]
+        finally:
+            pkg.set_tuning("pyr_chain", 0)
+    for a, c in zip(levels[1], levels[2]):
+        assert np.array_equal(a, c)
+    for side in ("left", "right"):
+        assert np.array_equal(outs[1]["n_" + side], outs[2]["n_" + side])
+    for f in range(n):  # (rows beyond a frame's count are whatever the engine's fresh buffers held)
+        a, c = int(outs[1]["n_left"][f]), int(outs[1]["n_right"][f])
+        for k, m in (("kps_left", a), ("desc_left", a), ("u_right", a), ("depth", a), ("kps_right", c), ("desc_right", c)):
+            assert outs[1][k][f, :m].tobytes() == outs[2][k][f, :m].tobytes(), (k, f)
+    o = O.OracleExtractor(nf, sf, nl, ini, mn)
+    o(left[1])
+    for l in range(nl):
+        assert np.array_equal(b.level(1, 0, l), o.level(l))
+    # odd geometry: scale factor 2 (the WIDE resize variant) and a portrait-ish image, single handle (one-launch form)
+    e = pkg.ORBextractor(800, 2.0, 3, 20, 7)
+    oo = O.OracleExtractor(800, 2.0, 3, 20, 7)
+    img = synth.synth(701, 397, 4)
+    k1, d1 = e(img)
+    k2, d2 = oo(img)
+    assert np.array_equal(d1, d2) and k1["x"].tobytes() == k2["x"].tobytes()
+    for l, lev in enumerate(e.mvImagePyramid):
+        assert np.array_equal(lev, oo.level(l))
