@@ -123,5 +123,31 @@ inline void ComputeStereoMatchesGPU(ORBextractorGPU& left, ORBextractorGPU& righ
         throw std::runtime_error(std::string("orbx_stereo_match: ") + orbx_last_error());
 }
 
+/* What Frame::Frame(stereo) does at src/Frame.cc:113-125 — ExtractORB left, ExtractORB right, ComputeStereoMatches — as ONE
+ * call (orbx_stereo_frame): both images go up together, every kernel runs on both, nothing comes back to the host in between.
+ * For a maintainer who is willing to replace those lines of the constructor instead of keeping its two threads:
+ *     ORB_SLAM2::StereoFrameGPU(*mpORBextractorLeft, *mpORBextractorRight, imLeft.data, imRight.data, imLeft.rows, imLeft.cols,
+ *                               imLeft.step, imRight.step, mbf, mb, keysL, descL, keysR, descR, mvuRight, mvDepth);
+ * POD outputs: keypoints as orbx_keypoint (the 28-byte cv::KeyPoint layout), descriptors n x 32 bytes. */
+inline void StereoFrameGPU(ORBextractorGPU& left, ORBextractorGPU& right, const uint8_t* imLeft, const uint8_t* imRight, int rows, int cols,
+                           size_t strideLeft, size_t strideRight, float mbf, float mb, std::vector<orbx_keypoint>& keysL,
+                           std::vector<uint8_t>& descL, std::vector<orbx_keypoint>& keysR, std::vector<uint8_t>& descR,
+                           std::vector<float>& mvuRight, std::vector<float>& mvDepth)
+{
+    if (!imLeft || !imRight || rows == 0 || cols == 0) return;
+    const int cap = orbx_max_keypoints(left.handle(), rows, cols);
+    if (cap < 0) throw std::runtime_error(std::string("orbx_max_keypoints: ") + orbx_last_error());
+    keysL.resize(cap); keysR.resize(cap);
+    descL.resize((size_t)cap * 32); descR.resize((size_t)cap * 32);
+    mvuRight.resize(cap); mvDepth.resize(cap);
+    int nL = 0, nR = 0;
+    if (orbx_stereo_frame(left.handle(), right.handle(), imLeft, imRight, rows, cols, strideLeft, strideRight, mbf, mb, keysL.data(),
+                          descL.data(), &nL, keysR.data(), descR.data(), &nR, cap, mvuRight.data(), mvDepth.data()) != ORBX_OK)
+        throw std::runtime_error(std::string("orbx_stereo_frame: ") + orbx_last_error());
+    keysL.resize(nL); keysR.resize(nR);
+    descL.resize((size_t)nL * 32); descR.resize((size_t)nR * 32);
+    mvuRight.resize(nL); mvDepth.resize(nL);
+}
+
 }  // namespace ORB_SLAM2
 #endif

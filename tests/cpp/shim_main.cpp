@@ -3,6 +3,7 @@
 // usage: shim_main left.raw right.raw rows cols nfeatures scale nlevels ini min mbf mb out.bin
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <thread>
 #include <vector>
 
@@ -44,6 +45,17 @@ int main(int argc, char** argv)
         fwrite(depth.data(), sizeof(float), depth.size(), f);
         fclose(f);
         printf("levels %d scale %.3f nL %d nR %d\n", exL.GetLevels(), exL.GetScaleFactor(), n[0], n[1]);
+        // the one-call form must leave exactly what the reference-shaped sequence above left
+        std::vector<orbx_keypoint> k2L, k2R;
+        std::vector<uint8_t> d2L, d2R;
+        std::vector<float> u2, depth2;
+        for (int rep = 0; rep < 3; ++rep)  // direct launches, graph capture, graph replay
+            ORB_SLAM2::StereoFrameGPU(exL, exR, imL.data(), imR.data(), rows, cols, cols, cols, mbf, mb, k2L, d2L, k2R, d2R, u2, depth2);
+        const bool same = k2L.size() == kL.size() && k2R.size() == kR.size() && d2L == dL && d2R == dR &&
+                          !memcmp(k2L.data(), kL.data(), kL.size() * sizeof(orbx_keypoint)) &&
+                          !memcmp(k2R.data(), kR.data(), kR.size() * sizeof(orbx_keypoint)) &&
+                          !memcmp(u2.data(), uR.data(), uR.size() * 4) && !memcmp(depth2.data(), depth.data(), depth.size() * 4);
+        if (!same) { fprintf(stderr, "StereoFrameGPU differs from operator() x2 + ComputeStereoMatchesGPU\n"); return 3; }
     } catch (const std::exception& e) {
         fprintf(stderr, "error: %s\n", e.what());
         return 1;

@@ -163,6 +163,17 @@ def gpu_legs(cfg, stereo, L, R, batch):
         if i >= 4:
             ts.append(time.perf_counter() - t0)
     out["single_frame_ms"] = round(statistics.median(ts) * 1e3, 3)
+    if stereo:  # the same frame through ONE call (orbx_stereo_frame: both images per launch, CUDA graph, one round trip)
+        from orb_slam2_2021_b200 import stereo_frame
+
+        ts = []
+        for i in range(64):
+            k = i % len(L)
+            t0 = time.perf_counter()
+            stereo_frame(el, er, L[k], R[k], bf, bf / fx)
+            if i >= 4:
+                ts.append(time.perf_counter() - t0)
+        out["stereo_frame_call_ms"] = round(statistics.median(ts) * 1e3, 3)
     del el, er
     # the same frame through the batch engine with a batch of one: both images share every launch, one round trip
     one = StereoFrameBatch(nf, sf, nl, ini, mn, H, W, 1, stereo=stereo)
