@@ -39,7 +39,7 @@ typedef struct orbx_batch orbx_batch;         /* frame-batch engine for throughp
 const char* orbx_last_error(void);            /* thread-local text of the last failure            */
 int orbx_device_count(void);
 /* Debug/experiment knobs (no reference counterpart; the library never reads the environment). Keys: run_streams,
- * run_chunks, e2e_streams, e2e_chunks, e2e_first_div, e2e_trace, fast_cells, fast_grid_mult, numa_off, pyr_chain; value 0 restores
+ * run_chunks, e2e_streams, e2e_chunks, e2e_first_div, e2e_trace, fast_cells, fast_grid_mult, numa_off, pyr_chain, pyr_tma; value 0 restores
  * the built-in default. Process-wide, not thread-safe against running calls. Unknown key: ORBX_ERR_ARG. */
 int orbx_set_tuning(const char* key, int value);
 

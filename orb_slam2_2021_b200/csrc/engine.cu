@@ -57,7 +57,7 @@ int orbx_stereo_bin_radius(const float* scale, int nlevels)
 // ---- tuning table (orbx_set_tuning) ---------------------------------------------------------------------
 static int g_tune[ORBX_TUNE_COUNT] = {0};
 static const char* const g_tuneNames[ORBX_TUNE_COUNT] = {"run_streams", "run_chunks", "e2e_streams", "e2e_chunks", "e2e_first_div",
-                                                         "e2e_trace", "fast_cells", "fast_grid_mult", "numa_off", "pyr_chain"};
+                                                         "e2e_trace", "fast_cells", "fast_grid_mult", "numa_off", "pyr_chain", "pyr_tma"};
 int orbx_tune(OrbxTune key) { return g_tune[key]; }
 extern "C" int orbx_set_tuning(const char* key, int value)
 {
@@ -238,7 +238,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-int Engine::makeLevelMaps(int boxW, int boxH, bool blurred, void** dMaps, std::string& err)
+int Engine::makeLevelMaps(int boxW, int boxH, bool blurred, void** dMaps, std::string& err, const int* boxWs, const int* boxHs)
 {
     void* fn = nullptr;
     cudaDriverEntryPointQueryResult q;
@@ -247,6 +247,10 @@ int Engine::makeLevelMaps(int boxW, int boxH, bool blurred, void** dMaps, std::s
     std::vector<CUtensorMap> maps(P.nlevels);
     for (int l = 0; l < P.nlevels; ++l) {
         const OrbxLevel& L = P.lv[l];
+        if (boxWs) {  // per-level boxes (resize: entry l = box over level l as the SOURCE of level l + 1; 0 = no box)
+            boxW = boxWs[l] > 0 ? boxWs[l] : 16;
+            boxH = boxHs[l] > 0 ? boxHs[l] : 1;
+        }
         void* base = blurred ? (void*)(P.blur + L.boff) : l == 0 ? (void*)P.img0 : (void*)(P.pyr + L.off);
         const cuuint64_t dims[3] = {(cuuint64_t)L.w, (cuuint64_t)L.h, (cuuint64_t)maxImgs};
         const cuuint64_t strides[2] = {(cuuint64_t)(blurred ? L.bpitch : L.pitch),
@@ -348,11 +352,30 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
             e4[3] = 0;
         }
     }
+    // TMA-staged resize (the default for batches; tuning key pyr_tma = 2 selects the word-load kernel): per destination level the largest source window of a 128 x 64 tile
+    rsBoxW.assign(P.nlevels, 0); rsBoxH.assign(P.nlevels, 0);
+    for (int l = 1; l < P.nlevels; ++l) {
+        const OrbxLevel& D = P.lv[l];
+        const int* xo = tab.data() + tabOff[l];
+        const int* yt = xo + ((2 * (size_t)D.w + 3) & ~(size_t)3);
+        int bw = 0, bh = 0;
+        for (int x0 = 0; x0 < D.w; x0 += 128) {
+            const int xl = std::min(x0 + 127, D.w - 1);
+            bw = std::max(bw, xo[xl] + 12 - (xo[x0] & ~15));
+        }
+        for (int y0 = 0; y0 < D.h; y0 += 64) {
+            const int yl = std::min(y0 + 63, D.h - 1);
+            bh = std::max(bh, yt[4 * yl] + 2 - yt[4 * y0]);
+        }
+        bw = (bw + 15) & ~15;
+        if (bw <= 256 && bh <= 256) { rsBoxW[l - 1] = bw; rsBoxH[l - 1] = bh; }  // stored at the SOURCE level's index
+    }
     TRY(dalloc(this, &dResizeTab, tab.size(), "resizeTab", err));
     TRY(orbx_check(cudaMemcpy(dResizeTab, tab.data(), tab.size() * sizeof(int), cudaMemcpyHostToDevice), "tab H2D", err));
     resizeTabs.assign(P.nlevels, nullptr);
     for (int l = 1; l < P.nlevels; ++l) resizeTabs[l] = dResizeTab + tabOff[l];
 
+    TRY(makeLevelMaps(0, 0, false, &dResizeMaps, err, rsBoxW.data(), rsBoxH.data()));
     TRY(makeLevelMaps(ORBX_BLUR_TW + 32, ORBX_BLUR_TH + 6, false, &dBlurMaps, err));
     TRY(makeLevelMaps(ORBX_DESC_BOX0_W, ORBX_DESC_BOX0_H, false, &dDescMaps0, err));
     TRY(makeLevelMaps(ORBX_DESC_BOX1_W, ORBX_DESC_BOX1_H, true, &dDescMaps1, err));
@@ -455,6 +478,7 @@ void Engine::launchPyramid(const OrbxParams& p, cudaStream_t s)
 {
     const int mode = orbx_tune(ORBX_TUNE_PYR_CHAIN);
     if (mode == 1 || (mode == 0 && p.imgs <= 8)) orbx_launch_pyramid_chain(p, resizeTabs.data(), p.chainState, s);
+    else if (orbx_tune(ORBX_TUNE_PYR_TMA) != 2) orbx_launch_pyramid_tma(p, resizeTabs.data(), dResizeMaps, rsBoxW.data(), rsBoxH.data(), s);
     else orbx_launch_pyramid(p, resizeTabs.data(), s);
 }
 

@@ -30,7 +30,7 @@ public:
 
     // level geometry without allocating anything (for orbx_max_keypoints)
     // TMA descriptors of the un-blurred levels with the given box (device array of nlevels CUtensorMap)
-    int makeLevelMaps(int boxW, int boxH, bool blurred, void** dMaps, std::string& err);
+    int makeLevelMaps(int boxW, int boxH, bool blurred, void** dMaps, std::string& err, const int* boxWs = nullptr, const int* boxHs = nullptr);
     static int plan(const ExtractorConfig& cfg, int rows, int cols, OrbxParams& p, std::string& err);
 
     int uploadImages(const uint8_t* left, const uint8_t* right, int nFrames, bool fromDevice, std::string& err);
@@ -90,6 +90,8 @@ public:
     void* dTiles = nullptr;
     int* dResizeTab = nullptr;
     uint8_t* dStage = nullptr;  // tight-row landing buffer of host uploads ([side][frame][rows*cols])
+    void* dResizeMaps = nullptr;  // un-blurred level l with the source window of a destination tile of level l + 1 as its box
+    std::vector<int> rsBoxW, rsBoxH;
     void* dFastMaps = nullptr;  // same tensors, box = (64|96) x (largest cell ROI height) x 1
     void* dDescMaps0 = nullptr;  // un-blurred levels, box 48 x 31 (IC_Angle disc)
     void* dDescMaps1 = nullptr;  // BLURRED levels, box 64 x 37 (rBRIEF samples)
@@ -125,6 +127,7 @@ enum OrbxTune {
     ORBX_TUNE_FAST_GRID_MULT,  // FAST CTAs launched per resident CTA slot
     ORBX_TUNE_NUMA_OFF,        // 1: orbx_host_alloc skips the NUMA placement
     ORBX_TUNE_PYR_CHAIN,       // pyramid: 0 = one launch for <= 8 images, else one per level; 1 = always one launch; 2 = always per level
+    ORBX_TUNE_PYR_TMA,         // per-level resize: 0 / 1 = TMA-staged source tiles (default), 2 = the word-load kernel
     ORBX_TUNE_COUNT
 };
 int orbx_tune(OrbxTune key);

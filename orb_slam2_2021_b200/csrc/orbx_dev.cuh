@@ -121,6 +121,7 @@ struct OrbxStageArgs {
 void orbx_launch_stage(const OrbxStageArgs& a, int channels, int nImgs, cudaStream_t s);
 void orbx_launch_ingest(const OrbxParams& p, const uint8_t* src, int nFrames, int per, int side, cudaStream_t s);
 void orbx_launch_pyramid(const OrbxParams& p, const int* const* tabs, cudaStream_t s);
+void orbx_launch_pyramid_tma(const OrbxParams& p, const int* const* tabs, const void* srcMaps, const int* boxW, const int* boxH, cudaStream_t s);
 int orbx_pyramid_chain_state_ints(const OrbxParams& p);
 void orbx_launch_pyramid_chain(const OrbxParams& p, const int* const* tabs, int* state, cudaStream_t s);
 void orbx_fast_geometry(const OrbxParams& p, int* boxW, int* rhMax);  // TMA box of the FAST kernel
