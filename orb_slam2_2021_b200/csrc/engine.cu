@@ -363,8 +363,8 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
             const int xl = std::min(x0 + 127, D.w - 1);
             bw = std::max(bw, xo[xl] + 12 - (xo[x0] & ~15));
         }
-        for (int y0 = 0; y0 < D.h; y0 += 64) {
-            const int yl = std::min(y0 + 63, D.h - 1);
+        for (int y0 = 0; y0 < D.h; y0 += 4 * ORBX_RS_TMA_ROWS) {
+            const int yl = std::min(y0 + 4 * ORBX_RS_TMA_ROWS - 1, D.h - 1);
             bh = std::max(bh, yt[4 * yl] + 2 - yt[4 * y0]);
         }
         bw = (bw + 15) & ~15;

@@ -157,9 +157,9 @@ __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_tma_kernel(const Re
 {
     extern __shared__ __align__(128) uint8_t rs_tile[];
     __shared__ __align__(8) uint64_t bar;
-    __shared__ int4 ytabS[RS_TY][RS_ROWS];
+    __shared__ int4 ytabS[RS_TY][ORBX_RS_TMA_ROWS];
     const int tid = threadIdx.y * RS_TX + threadIdx.x;
-    const int x0d = blockIdx.x * (4 * RS_TX), y0d = blockIdx.y * (RS_TY * RS_ROWS);
+    const int x0d = blockIdx.x * (4 * RS_TX), y0d = blockIdx.y * (RS_TY * ORBX_RS_TMA_ROWS);
     const int xs = A.xofs[x0d] & ~15, r0 = A.ytab[y0d].x;  // window origin (the copy engine wants 16-byte column units)
     if (tid == 0) {
         orbx_mbar_init(&bar, 1);
@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(RS_TX * RS_TY) orbx_resize_tma_kernel(const Re
     B.src = rs_tile - ((size_t)r0 * boxW + xs);
     B.srcStride = 0;
     B.sp = boxW;
-    resize_tile<WIDE, 2, RS_ROWS>(B, blockIdx.z, blockIdx.x, blockIdx.y, ytabS);
+    resize_tile<WIDE, 2, ORBX_RS_TMA_ROWS>(B, blockIdx.z, blockIdx.x, blockIdx.y, ytabS);
 }
 
 // ---- the whole pyramid in ONE launch ---------------------------------------------------------------------------------
@@ -333,11 +333,12 @@ void orbx_launch_pyramid_tma(const OrbxParams& p, const int* const* tabs, const 
     for (int l = 1; l < p.nlevels; ++l) {
         const OrbxLevel &S = p.lv[l - 1], &D = p.lv[l];
         const ResizeArgs A = resize_args(p, tabs, l);
-        dim3 block(RS_TX, RS_TY), grid((D.w + 4 * RS_TX - 1) / (4 * RS_TX), (D.h + RS_ROWS * RS_TY - 1) / (RS_ROWS * RS_TY), p.imgs);
+        dim3 block(RS_TX, RS_TY), grid((D.w + 4 * RS_TX - 1) / (4 * RS_TX), (D.h + ORBX_RS_TMA_ROWS * RS_TY - 1) / (ORBX_RS_TMA_ROWS * RS_TY), p.imgs);
+        dim3 gridW((D.w + 4 * RS_TX - 1) / (4 * RS_TX), (D.h + RS_ROWS * RS_TY - 1) / (RS_ROWS * RS_TY), p.imgs);
         const bool wide = S.w > 2 * D.w;
         if (boxW[l - 1] <= 0) {  // window too large for one box: the word-load kernel
-            if (wide) orbx_resize_kernel<true><<<grid, block, 0, s>>>(A);
-            else orbx_resize_kernel<false><<<grid, block, 0, s>>>(A);
+            if (wide) orbx_resize_kernel<true><<<gridW, block, 0, s>>>(A);
+            else orbx_resize_kernel<false><<<gridW, block, 0, s>>>(A);
             continue;
         }
         // (+2 rows: the row walk prefetches two rows ahead and drops what it does not need)
