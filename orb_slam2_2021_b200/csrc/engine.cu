@@ -57,7 +57,7 @@ int orbx_stereo_bin_radius(const float* scale, int nlevels)
 // ---- tuning table (orbx_set_tuning) ---------------------------------------------------------------------
 static int g_tune[ORBX_TUNE_COUNT] = {0};
 static const char* const g_tuneNames[ORBX_TUNE_COUNT] = {"run_streams", "run_chunks", "e2e_streams", "e2e_chunks", "e2e_first_div",
-                                                         "e2e_trace", "fast_cells", "fast_grid_mult", "numa_off", "pyr_chain", "pyr_tma"};
+                                                         "e2e_trace", "fast_cells", "fast_grid_mult", "numa_off", "pyr_chain", "pyr_tma", "fast_ctas"};
 int orbx_tune(OrbxTune key) { return g_tune[key]; }
 extern "C" int orbx_set_tuning(const char* key, int value)
 {

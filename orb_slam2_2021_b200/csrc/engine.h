@@ -128,6 +128,7 @@ enum OrbxTune {
     ORBX_TUNE_NUMA_OFF,        // 1: orbx_host_alloc skips the NUMA placement
     ORBX_TUNE_PYR_CHAIN,       // pyramid: 0 = one launch for <= 8 images, else one per level; 1 = always one launch; 2 = always per level
     ORBX_TUNE_PYR_TMA,         // per-level resize: 0 / 1 = TMA-staged source tiles (default), 2 = the word-load kernel
+    ORBX_TUNE_FAST_CTAS,       // FAST: at most this many CTAs per SM (0 = as many as fit), leaves room for kernels on other streams
     ORBX_TUNE_COUNT
 };
 int orbx_tune(OrbxTune key);

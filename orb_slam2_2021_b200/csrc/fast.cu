@@ -351,7 +351,13 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     cudaGetDevice(&dev);
     int& smCount = smCounts[dev & 63];
     if (!smCount) cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, dev);
-    const size_t smem = (size_t)slice * cellsPerCta;
+    size_t smem = (size_t)slice * cellsPerCta;
+    // tuning key fast_ctas: cap the resident CTAs per SM (by asking for more shared memory than a CTA uses), so that CTAs of
+    // kernels running beside this one on other streams find room on every SM
+    if (const int capCtas = orbx_tune(ORBX_TUNE_FAST_CTAS)) {
+        const size_t want = (size_t)(233472 / (capCtas + 1)) + 1024;  // just too large for capCtas + 1 CTAs
+        if (want > smem && want <= 227 * 1024) smem = want;
+    }
     const int wanted = (p.cellsTotal * p.imgs + cellsPerCta - 1) / cellsPerCta;
 #define FAST_LAUNCH(SA_, C_)                                                                                                     \
     {                                                                                                                            \
