@@ -23,3 +23,30 @@ print("batch engine, 1 stereo frame, run() only", t(lambda: b.run(1,bf,bf/fx)))
 b.set_profiling(True)
 for _ in range(20): b.run(1,bf,bf/fx)
 st,runs=b.stage_times(); print({k:round(v/runs*1e3,1) for k,v in st.items()}, "us per stage")
+# the three single-frame flows through the C-ABI (see bench.py: latency)
+from bench import single_frame_latency
+Ls, Rs = synth.stereo_batch(W, H, 16, seed0=40)
+lat = single_frame_latency(pkg, synth.CONFIGS["kitti"], Ls, Rs, 0, n=1000)
+print({k: (v if not isinstance(v, dict) else {a: round(b, 4) if isinstance(b, float) else b for a, b in v.items()}) for k, v in lat.items() if k != "api"})
+# the reference's OWN Frame::Frame(stereo) (src/Frame.cc:80-152 compiled with INTEGRATION.md's patch, oracle/_ref/libref_frame_gpu.so):
+# its two std::threads -> operator() on the GPU extractors, ComputeStereoMatchesGPU (resident match), AssignFeaturesToGrid, ...
+try:
+    from oracle import ref as RR
+    gl, gr = RR.GpuShimExtractor(nf, sf, nl, ini, mn), RR.GpuShimExtractor(nf, sf, nl, ini, mn)
+    K4 = np.array([fx, fx, W / 2, H / 2], np.float32)
+    ts = []
+    for i in range(120):
+        t0 = time.perf_counter()
+        F = RR.frame_stereo_gpu(gl, gr, Ls[i % 16], Rs[i % 16], K4, bf, 35 * bf / fx, bf / fx, capacity=4096)
+        ts.append(time.perf_counter() - t0)
+    print("reference Frame::Frame(stereo) on the GPU extractor (two threads, whole constructor incl. grid, + copy-out of the Frame): p50 %.3f ms"
+          % (np.median(ts[20:]) * 1e3), "N", F["N"])
+    cl, cr = RR.RefExtractor(nf, sf, nl, ini, mn), RR.RefExtractor(nf, sf, nl, ini, mn)
+    ts = []
+    for i in range(6):
+        t0 = time.perf_counter()
+        RR.frame_stereo(cl, cr, Ls[i], Rs[i], K4, bf, 35 * bf / fx, bf / fx, capacity=4096)
+        ts.append(time.perf_counter() - t0)
+    print("the same constructor on the reference's CPU extractor (scalar OpenCV stand-ins): p50 %.1f ms" % (np.median(ts[1:]) * 1e3))
+except Exception as e:
+    print("drop-in Frame timing unavailable:", e)
