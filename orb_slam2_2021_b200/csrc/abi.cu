@@ -51,7 +51,11 @@ extern "C" void orbx_destroy(orbx_extractor* e)
     if (!e) return;
     if (e->dU) { cudaSetDevice(e->device); cudaFree(e->dU); cudaFree(e->dD); cudaFree(e->dSad); cudaFree(e->dNm); cudaFree(e->dSorted); cudaFree(e->dBin); }
     if (e->hOut) { cudaSetDevice(e->device); cudaFreeHost(e->hOut); }
-    if (e->pairPeer && e->pairPeer->view == e->pair.get()) e->pairPeer->view = nullptr;  // the peer's view dies with this engine
+    if (e->pairPeer) {  // the peer's view dies with this handle's frame engine
+        if (e->pairPeer->view == e->pair.get()) e->pairPeer->view = nullptr;
+        if (e->pairPeer->pairOwner == e) e->pairPeer->pairOwner = nullptr;
+    }
+    if (e->pairOwner && e->pairOwner->pairPeer == e) e->pairOwner->pairPeer = nullptr;  // and nobody keeps a pointer to this handle
     delete e;
 }
 
@@ -280,8 +284,14 @@ extern "C" int orbx_stereo_frame(orbx_extractor* l, orbx_extractor* r, const uin
     // the handles' own engines no longer hold this frame: pyramid levels come from the pair engine, and orbx_stereo_match
     // (which reads the handles' own pyramids) needs a new orbx_extract first
     l->hasRun = r->hasRun = false;
+    if (l->pairPeer && l->pairPeer != r) {  // an earlier right-hand partner no longer reads this engine
+        if (l->pairPeer->view == &E) l->pairPeer->view = nullptr;
+        if (l->pairPeer->pairOwner == l) l->pairPeer->pairOwner = nullptr;
+    }
+    if (r->pairOwner && r->pairOwner != l && r->pairOwner->pairPeer == r) r->pairOwner->pairPeer = nullptr;
     l->view = r->view = &E; l->viewImg = 0; r->viewImg = 1;
     l->pairPeer = r;
+    r->pairOwner = l;
     const size_t Pk = (size_t)E.P.maxKp;
     const int cl = reinterpret_cast<const int*>(E.hOut)[0], cr = reinterpret_cast<const int*>(E.hOut)[1];
     if (cl > capacity || cr > capacity) return fail(ORBX_ERR_CAPACITY, "keypoint capacity too small (see orbx_max_keypoints)");

@@ -20,6 +20,7 @@ struct orbx_extractor {
     // then read their pyramid levels from it (view) until their next orbx_extract
     std::unique_ptr<Engine> pair;
     orbx_extractor* pairPeer = nullptr;  // the other handle whose view points into this handle's pair engine
+    orbx_extractor* pairOwner = nullptr; // (on that other handle) the handle that owns the engine its view points into
     Engine* view = nullptr;              // where the most recent pyramid of this handle lives
     int viewImg = 0;
 };

@@ -549,3 +549,31 @@ def test_one_launch_pyramid_equals_the_per_level_launches():
     assert np.array_equal(d1, d2) and k1["x"].tobytes() == k2["x"].tobytes()
     for l, lev in enumerate(e.mvImagePyramid):
         assert np.array_equal(lev, oo.level(l))
+
+
+@pytest.mark.gpu
+def test_stereo_frame_handle_lifetimes():
+    """The frame engine lives in the left handle; right-hand partners only look into it. Destroying or re-pairing handles in
+    any order leaves no dangling view: a partner whose engine is gone reports ORBX_ERR_STATE instead of reading freed memory."""
+    W, H, nf, nl, sf, ini, mn, fx, bf = synth.CONFIGS["arducam"]
+    left, right = synth.stereo_pair(W, H, 12)
+    mk = lambda: pkg.ORBextractor(nf, sf, nl, ini, mn)  # noqa: E731
+    l, r1, r2 = mk(), mk(), mk()
+    a = pkg.stereo_frame(l, r1, left, right, bf, bf / fx)
+    b = pkg.stereo_frame(l, r2, left, right, bf, bf / fx)  # re-paired: r1 no longer reads l's engine
+    assert all(x.tobytes() == y.tobytes() for x, y in zip(a, b))
+    with pytest.raises(pkg.OrbxError) as ei:
+        r1.mvImagePyramid
+    assert ei.value.code == pkg._lib.ERR_STATE
+    assert np.array_equal(r2.mvImagePyramid[0], right)
+    del l  # the owner goes first
+    with pytest.raises(pkg.OrbxError):
+        r2.mvImagePyramid
+    k, _ = r2(right)  # the handle itself is still a working extractor
+    assert len(k) == len(a[2]) and np.array_equal(r2.mvImagePyramid[0], right)
+    l2, r3 = mk(), mk()
+    pkg.stereo_frame(l2, r3, left, right, bf, bf / fx)
+    del r3  # the partner goes first: the owner must not touch it afterwards
+    c = pkg.stereo_frame(l2, r2, left, right, bf, bf / fx)
+    assert all(x.tobytes() == y.tobytes() for x, y in zip(a, c))
+    del l2, r2, r1
