@@ -458,6 +458,19 @@ def ours_arm(args, rank, local_rank, world):
     stream_ms = reduce(1e3 * (time.perf_counter() - t0), dist.ReduceOp.MAX if dist else None)
     barrier()
     assert int(out2["n_left"].sum()) + int(out2["n_right"].sum()) == n_l + n_r, "streamed results differ from the device-resident run"
+    # ---- the same stream for a caller that does not take the right image's keypoints and descriptors back (the ABI skips
+    # NULL outputs; ORB-SLAM2 itself reads mvKeysRight / mDescriptorsRight only inside ComputeStereoMatches): less D2H
+    slim = [{k: v for k, v in o.items() if k not in ("kps_right", "desc_right")} for o in (out, out2)]
+    for i in range(2):
+        b.process_async(pin_l.array, pin_r.array, mbf, mb, out=slim[i % 2])
+    b.wait()
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        b.process_async(pin_l.array, pin_r.array, mbf, mb, out=slim[i % 2])
+    b.wait()
+    slim_ms = reduce(1e3 * (time.perf_counter() - t0), dist.ReduceOp.MAX if dist else None)
+    barrier()
     clocks = sampler.stop() if rank == 0 else None
     # ---- raw host-link ceiling at this N (tools/link_ceiling.py in short): the same bytes per step, pinned memory, one
     # cudaMemcpyAsync per direction on two streams, no kernels, all ranks at once; max over ranks
@@ -543,6 +556,9 @@ def ours_arm(args, rank, local_rank, world):
                        "orbx_batch_wait after the last step; wall clock around all steps including the drain",
                 "blocking_call": {"value": e2e, "ms_per_step": e2e_ms / args.steps,
                                   "api": "orbx_batch_process: returns with the step's results in host memory"},
+                "without_right_outputs": {"value": frames_total * args.steps / (slim_ms / 1e3),
+                                          "d2h_bytes_per_step": int(sum(v.nbytes for v in slim[0].values())) * world,
+                                          "api": "the streaming call with kps_right / desc_right = NULL (not returned to the host)"},
                 # rank 0's pinned buffers: NUMA node of its GPU, and whether orbx_host_alloc could place them there
                 "host_numa": dict(zip(("node", "bound"), pkg.host_numa_node())),
                 # what the host link alone allows at this N: the same bytes per step as plain pinned copies without kernels
