@@ -146,9 +146,12 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
     // neighbouring warps work on neighbouring cells of the same image (their tiles overlap in L2)
     const int total = p.cellsTotal * p.imgs;
     unsigned phase = 0;
+    // (image, cell) of the warp's work item, advanced without a division per cell
+    const int stride = gridDim.x * CELLS, strideImg = stride / p.cellsTotal, strideCell = stride - strideImg * p.cellsTotal;
+    int img = (blockIdx.x * CELLS + warp) / p.cellsTotal, cellId = (blockIdx.x * CELLS + warp) - img * p.cellsTotal;
 #pragma unroll 1
-    for (int work = blockIdx.x * CELLS + warp; work < total; work += gridDim.x * CELLS) {
-    const int img = work / p.cellsTotal, cellId = work - img * p.cellsTotal;
+    for (int work = blockIdx.x * CELLS + warp; work < total;
+         work += stride, img += strideImg, cellId += strideCell, img += cellId >= p.cellsTotal, cellId -= cellId >= p.cellsTotal ? p.cellsTotal : 0) {
     const OrbxCell cell = cells[cellId];
     const OrbxLevel& L = p.lv[cell.level];
     const int iw = cell.rw - 6, ih = cell.rh - 6;  // interior = detection domain of cv::FAST
