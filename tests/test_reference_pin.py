@@ -458,3 +458,24 @@ def test_cuda_256_frame_stream_equals_reference_sampled(name):
         ur, dp = R.stereo_match(rl, rr, kl, dl, kr, dr, mbf, mb)
         assert out_b["u_right"][k, :a].tobytes() == ur.tobytes() and out_b["depth"][k, :a].tobytes() == dp.tobytes(), (name, k)
         assert (ur >= 0).sum() > 50
+
+
+@needs_ref
+@pytest.mark.gpu
+@pytest.mark.parametrize("nf,sf,nl,ini,mn", PARAMS)
+def test_cuda_batch_equals_reference_parameters(nf, sf, nl, ini, mn):
+    """The batch engine's per-level path (more than 8 images: TMA-staged resize, one launch per level) over the same
+    parameter space as the single handle above (which takes the one-launch pyramid): scale factors 1.1 .. 2.0, 1 .. 12 levels."""
+    import orb_slam2_2021_b200 as pkg
+
+    W, H = (1280, 720) if nl == 12 else (701, 397)
+    n = 10
+    imgs = np.stack([synth.synth(W, H, 400 + k) for k in range(n)])
+    b = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, n, stereo=False)
+    out = b.process(imgs, None)
+    r = R.RefExtractor(nf, sf, nl, ini, mn)
+    for k in (0, 4, 9):
+        m = int(out["n_left"][k])
+        assert_same((out["kps_left"][k, :m], out["desc_left"][k, :m]), r(imgs[k]), f"batch/{(nf, sf, nl, ini, mn)}/{k}")
+        for l in range(nl):
+            assert np.array_equal(b.level(k, 0, l), r.level(l)), (k, l)
