@@ -156,22 +156,27 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
             for (int i = tid; i < nc; i += OCT_THREADS) cellScan[i] = cc[c0 + i];
             __syncthreads();
             block_excl_scan(cellScan, nc, wsum);
-            for (int c = warp; c < nc; c += OCT_THREADS / 32) {
-                const int start = cellScan[c], k = cellScan[c + 1] - start;
-                const OrbxCellRec cr = ct[c0 + c];
-                const int sx = cr.x0 - (ORBX_EDGE - 3), sy = cr.y0 - (ORBX_EDGE - 3);
-                const uint32_t* sl = slots + (size_t)(c0 + c) * L.slotCap;
-                for (int e = lane; e < k; e += 32) {
-                    const uint32_t v = sl[e];
-                    const int x = (v & 255) + sx, y = ((v >> 8) & 255) + sy;
-                    const int idx = n + start + e;
-                    candXY[idx] = (uint32_t)x | ((uint32_t)y << 16);
-                    candRs[idx] = (uint8_t)(v >> 16);
-                    int b = (int)orbx_fdiv((float)x, hX);
-                    b = min(b, nIni - 1);
-                    label[idx] = (uint16_t)b;
-                    atomicAdd(&S.childCnt[b], 1);
+            // one thread per candidate (its cell by binary search over the scanned counts): every thread has an independent
+            // load of its slot in flight; a warp per cell with a lane per slot kept ~7 lanes busy behind one L2 round trip per cell
+            const int tot = cellScan[nc];
+            for (int q = tid; q < tot; q += OCT_THREADS) {
+                int lo = 0, hi = nc;  // cellScan[lo] <= q < cellScan[hi]
+                while (hi - lo > 1) {
+                    const int mid = (lo + hi) >> 1;
+                    if (cellScan[mid] <= q) lo = mid; else hi = mid;
                 }
+                const int e = q - cellScan[lo];
+                const OrbxCellRec cr = ct[c0 + lo];
+                const int sx = cr.x0 - (ORBX_EDGE - 3), sy = cr.y0 - (ORBX_EDGE - 3);
+                const uint32_t v = slots[(size_t)(c0 + lo) * L.slotCap + e];
+                const int x = (v & 255) + sx, y = ((v >> 8) & 255) + sy;
+                const int idx = n + q;
+                candXY[idx] = (uint32_t)x | ((uint32_t)y << 16);
+                candRs[idx] = (uint8_t)(v >> 16);
+                int b = (int)orbx_fdiv((float)x, hX);
+                b = min(b, nIni - 1);
+                label[idx] = (uint16_t)b;
+                atomicAdd(&S.childCnt[b], 1);
             }
             n += cellScan[nc];
             __syncthreads();
