@@ -47,7 +47,9 @@ __device__ __forceinline__ int warp_incl_scan(int v, int lane)
     return v;
 }
 
-// In-place exclusive scan of a[0..n) in shared memory; a[n] receives the total. All threads call.
+// In-place exclusive scan of a[0..n) in shared memory; a[n] receives the total. All threads call. Two barriers: every warp
+// publishes its sum, then every thread adds up the sums of the warps before its own (8 values) instead of waiting for a
+// second, single-warp scan.
 __device__ void block_excl_scan(int* a, int n, int* wsum /*[OCT_THREADS/32 + 1]*/)
 {
     const int T = OCT_THREADS, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -58,21 +60,21 @@ __device__ void block_excl_scan(int* a, int n, int* wsum /*[OCT_THREADS/32 + 1]*
     const int inc = warp_incl_scan(s, lane);
     if (lane == 31) wsum[warp] = inc;
     __syncthreads();
-    if (warp == 0) {
-        int w = lane < T / 32 ? wsum[lane] : 0;
-        int wi = warp_incl_scan(w, lane);
-        if (lane < T / 32) wsum[lane] = wi - w;
-        if (lane == T / 32 - 1) wsum[T / 32] = wi;
+    int before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < T / 32; ++w) {
+        const int v = wsum[w];
+        before += w < warp ? v : 0;
+        total += v;
     }
-    __syncthreads();
-    int run = wsum[warp] + inc - s;
+    int run = before + inc - s;
     for (int i = b; i < e; ++i) {
         int v = a[i];
         a[i] = run;
         run += v;
     }
-    if (tid == 0) a[n] = wsum[T / 32];
-    __syncthreads();
+    if (tid == 0) a[n] = total;
+    __syncthreads();  // (also: nobody overwrites wsum for the next scan before everybody has read it)
 }
 
 __device__ __forceinline__ int quadrant(uint32_t xy, short4 b)
