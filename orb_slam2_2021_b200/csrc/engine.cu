@@ -309,6 +309,7 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     TRY(dalloc(this, &P.chainState, n * P.chainInts, "chainState", err));
     TRY(orbx_check(cudaMemsetAsync(P.outCnt, 0, n * sizeof(int), stream), "memset", err));
     TRY(orbx_check(cudaMemsetAsync(P.keepCnt, 0, n * P.nlevels * sizeof(int), stream), "memset", err));
+    TRY(orbx_check(cudaMemsetAsync(P.chainState, 0, n * P.chainInts * sizeof(int), stream), "memset", err));
     TRY(orbx_check(cudaMemsetAsync(P.candCnt, 0, n * P.nlevels * sizeof(int), stream), "memset", err));
 
     // cell table and blur tile table
@@ -686,6 +687,7 @@ void Engine::enqueueFrame(float mbf, float mb, cudaStream_t s)
     orbx_launch_describe(p, dDescMaps0, dDescMaps1, s);
     if (stereo) launchStereo(0, maxImgs / 2, mbf, mb, s);
     cudaMemcpyAsync(hOut, P.outCnt, (size_t)maxImgs * sizeof(int), cudaMemcpyDeviceToHost, s);
+    cudaMemcpyAsync(hOut + 32, P.chainState + 1, sizeof(int), cudaMemcpyDeviceToHost, s);  // watchdog flag of the one-launch pyramid
     cudaMemcpyAsync(hOut + frameOffKp, P.outKp, (size_t)maxImgs * Pk * 28, cudaMemcpyDeviceToHost, s);
     cudaMemcpyAsync(hOut + frameOffDesc, P.outDesc, (size_t)maxImgs * Pk * 32, cudaMemcpyDeviceToHost, s);
     if (stereo) {
@@ -753,6 +755,10 @@ int Engine::processFrame(const uint8_t* const* images, const size_t* strides, fl
     else enqueueFrame(mbf, mb, stream);
     TRY(orbx_check(cudaGetLastError(), "frame launch", err));
     TRY(sync(err));
+    if (*reinterpret_cast<const int*>(hOut + 32) != 0) {  // a tile of the one-launch pyramid gave up waiting for its source rows
+        err = "pyramid chain watchdog: a tile waited too long for its source level (results of this frame are invalid)";
+        return ORBX_ERR_CUDA;
+    }
     residentValid = true;
     return ORBX_OK;
 }
