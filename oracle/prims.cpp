@@ -135,6 +135,14 @@ inline bool has_arc9(uint32_t m16)
 inline int fast_score(const uint8_t* p, int stride, int t)
 {
     int v = p[0];
+    // early out, exact: any 9 contiguous ring positions contain position 0 or 8 and position 4 or 12, and every pixel of a
+    // corner's arc differs from the centre by more than t (OpenCV's detector starts with tests of this kind as well)
+    {
+        const int d0 = (int)p[3 * stride] - v, d8 = (int)p[-3 * stride] - v;
+        if (d0 <= t && d0 >= -t && d8 <= t && d8 >= -t) return 0;
+        const int d4 = (int)p[3] - v, d12 = (int)p[-3] - v;
+        if (d4 <= t && d4 >= -t && d12 <= t && d12 >= -t) return 0;
+    }
     int d[16];
     uint32_t bright = 0, dark = 0;
     for (int k = 0; k < 16; ++k) {
