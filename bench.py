@@ -157,7 +157,7 @@ def cpu_kind():
     from oracle import ref as R
 
     if R.available():
-        return "reference", ("the reference's own src/ORBextractor.cc + Frame::ComputeStereoMatches (oracle/_ref, g++ -O2) over the "
+        return "reference", ("the reference's own src/ORBextractor.cc + Frame::ComputeStereoMatches (oracle/_ref, g++ -O3) over the "
                              "oracle's scalar restatements of the OpenCV primitives (no OpenCV C++ in the image)")
     return "port", "C++ oracle port of the reference (oracle/_ref not built)"
 
