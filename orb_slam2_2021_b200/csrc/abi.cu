@@ -147,6 +147,26 @@ extern "C" int orbx_pyramid_level(const orbx_extractor* e, int level, uint8_t* d
     return copy_level(*e->view, e->viewImg, level, false, dst, dstStride);
 }
 
+// Device scratch of the two-handle stereo match (owned by the LEFT handle; grown when the image size does): per-keypoint
+// uRight / depth / SAD, the match counter, the row-sorted right records and the row-bin table.
+static int ensure_stereo_scratch(orbx_extractor* l, const Engine& EL)
+{
+    if (l->scratchKp >= EL.P.maxKp && l->scratchRows >= EL.rows) return ORBX_OK;
+    if (l->dU) { cudaFree(l->dU); cudaFree(l->dD); cudaFree(l->dSad); cudaFree(l->dNm); cudaFree(l->dSorted); cudaFree(l->dBin); }
+    l->dU = l->dD = nullptr; l->dSad = l->dNm = nullptr; l->dSorted = nullptr; l->dBin = nullptr;
+    l->scratchKp = l->scratchRows = 0;
+    const size_t k = EL.P.maxKp;
+    TRY(orbx_check(cudaMalloc(&l->dU, k * 4), "stereo scratch", g_err));
+    TRY(orbx_check(cudaMalloc(&l->dD, k * 4), "stereo scratch", g_err));
+    TRY(orbx_check(cudaMalloc(&l->dSad, k * 4), "stereo scratch", g_err));
+    TRY(orbx_check(cudaMalloc(&l->dNm, 4), "stereo scratch", g_err));
+    TRY(orbx_check(cudaMalloc(&l->dSorted, 3 * k * sizeof(uint4)), "stereo scratch", g_err));
+    TRY(orbx_check(cudaMalloc(&l->dBin, ((size_t)EL.rows + 1) * 4), "stereo scratch", g_err));
+    l->scratchKp = EL.P.maxKp;
+    l->scratchRows = EL.rows;
+    return ORBX_OK;
+}
+
 extern "C" int orbx_stereo_match(orbx_extractor* l, orbx_extractor* r, const orbx_keypoint* kpsL, const uint8_t* descL, int nL,
                                  const orbx_keypoint* kpsR, const uint8_t* descR, int nR, float mbf, float mb, float* uRight,
                                  float* depth)
@@ -166,18 +186,7 @@ extern "C" int orbx_stereo_match(orbx_extractor* l, orbx_extractor* r, const orb
     for (int i = 0; i < nL; ++i) uRight[i] = depth[i] = -1.f;  // src/Frame.cc:524-525
     if (nL == 0) return ORBX_OK;
     TRY(orbx_check(cudaSetDevice(l->device), "cudaSetDevice", g_err));
-    if (l->scratchKp < EL.P.maxKp || l->scratchRows < EL.rows) {
-        if (l->dU) { cudaFree(l->dU); cudaFree(l->dD); cudaFree(l->dSad); cudaFree(l->dNm); cudaFree(l->dSorted); cudaFree(l->dBin); l->dU = nullptr; }
-        const size_t k = EL.P.maxKp;
-        TRY(orbx_check(cudaMalloc(&l->dU, k * 4), "stereo scratch", g_err));
-        TRY(orbx_check(cudaMalloc(&l->dD, k * 4), "stereo scratch", g_err));
-        TRY(orbx_check(cudaMalloc(&l->dSad, k * 4), "stereo scratch", g_err));
-        TRY(orbx_check(cudaMalloc(&l->dNm, 4), "stereo scratch", g_err));
-        TRY(orbx_check(cudaMalloc(&l->dSorted, 3 * k * sizeof(uint4)), "stereo scratch", g_err));
-        TRY(orbx_check(cudaMalloc(&l->dBin, ((size_t)EL.rows + 1) * 4), "stereo scratch", g_err));
-        l->scratchKp = EL.P.maxKp;
-        l->scratchRows = EL.rows;
-    }
+    TRY(ensure_stereo_scratch(l, EL));
     cudaStream_t s = EL.stream;
     EL.residentValid = ER.residentValid = false;  // the extractors' own results on the device are overwritten below
     // the caller's keypoints/descriptors are authoritative (Frame::mvKeys etc.): put them on the device
@@ -217,18 +226,7 @@ extern "C" int orbx_stereo_match_resident(orbx_extractor* l, orbx_extractor* r, 
     for (int i = 0; i < nL; ++i) uRight[i] = depth[i] = -1.f;  // src/Frame.cc:524-525
     if (nL == 0) return ORBX_OK;
     TRY(orbx_check(cudaSetDevice(l->device), "cudaSetDevice", g_err));
-    if (l->scratchKp < EL.P.maxKp || l->scratchRows < EL.rows) {
-        if (l->dU) { cudaFree(l->dU); cudaFree(l->dD); cudaFree(l->dSad); cudaFree(l->dNm); cudaFree(l->dSorted); cudaFree(l->dBin); l->dU = nullptr; }
-        const size_t k = EL.P.maxKp;
-        TRY(orbx_check(cudaMalloc(&l->dU, k * 4), "stereo scratch", g_err));
-        TRY(orbx_check(cudaMalloc(&l->dD, k * 4), "stereo scratch", g_err));
-        TRY(orbx_check(cudaMalloc(&l->dSad, k * 4), "stereo scratch", g_err));
-        TRY(orbx_check(cudaMalloc(&l->dNm, 4), "stereo scratch", g_err));
-        TRY(orbx_check(cudaMalloc(&l->dSorted, 3 * k * sizeof(uint4)), "stereo scratch", g_err));
-        TRY(orbx_check(cudaMalloc(&l->dBin, ((size_t)EL.rows + 1) * 4), "stereo scratch", g_err));
-        l->scratchKp = EL.P.maxKp;
-        l->scratchRows = EL.rows;
-    }
+    TRY(ensure_stereo_scratch(l, EL));
     if (!l->hOut || l->hOutCap < (size_t)EL.P.maxKp * 8) {
         if (l->hOut) cudaFreeHost(l->hOut);
         l->hOut = nullptr; l->hOutCap = 0;
