@@ -102,7 +102,7 @@ struct __align__(8) OrbxCellRec {  // same layout as OrbxCell in fast.cu
     uint8_t rw, rh, level, pad;
 };
 
-#define OCT_CELL_CHUNK 2048
+#define OCT_CELL_CHUNK 512  // cells gathered per round of step 0 (2 KB of static shared memory; KITTI's largest level has 429)
 
 __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, const OrbxCellRec* cells)
 {
@@ -128,8 +128,8 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
     S.byRank = (int*)ptr; ptr += 4 * cap;
     S.scan = (int*)ptr; ptr += 4 * (cap + 1);
     S.vlist = (int*)ptr; ptr += 4 * (cap + 1);
-    int* tmp = (int*)ptr; ptr += 4 * cap;
-    S.best = (unsigned*)ptr; ptr += 4 * cap;
+    int* tmp = (int*)ptr;            // sizes of the nodes to rank (phase 2, inside the passes) ...
+    S.best = (unsigned*)ptr; ptr += 4 * cap;  // ... and, after the passes, the best response per node: never live together
     S.newPos = (uint16_t*)ptr; ptr += 8 * cap;
     S.movePos = (uint16_t*)ptr; ptr += 2 * cap;
     S.inV[0] = ptr; ptr += cap;
@@ -363,7 +363,7 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
     if (tid == 0) p.keepCnt[img * p.nlevels + level] = m;
 }
 
-static size_t octree_smem_bytes(int cap) { return (size_t)cap * 84 + 64; }
+static size_t octree_smem_bytes(int cap) { return (size_t)cap * 80 + 64; }
 // dynamic + static shared memory of one quadtree CTA for a per-level list capacity (Engine::plan rejects what the SM cannot hold)
 size_t orbx_octree_smem_total(int cap) { return octree_smem_bytes(cap) + sizeof(int) * (OCT_THREADS / 32 + 1 + OCT_CELL_CHUNK + 1 + 3) + 64; }
 
