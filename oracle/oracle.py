@@ -51,6 +51,8 @@ def lib():
         L.orc_fast_atan2.restype = C.c_float
         L.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
         L.orc_sincos.argtypes = [C.c_float, f32p, f32p]
+        L.orc_sincos_vs_libm.restype = C.c_long
+        L.orc_sincos_vs_libm.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
         L.orc_hamming256.argtypes = [vp, vp]
         L.orc_reflect101.argtypes = [C.c_int, C.c_int]
         L.orc_distribute.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int]
@@ -160,6 +162,11 @@ def sincos(rad):
     s, c = C.c_float(), C.c_float()
     lib().orc_sincos(float(rad), C.byref(s), C.byref(c))
     return s.value, c.value
+
+
+def sincos_vs_libm(lo, hi, step=1):
+    """Count of float bit patterns lo, lo+step, ... <= hi on which orbx_sincosf differs from the host's glibc sincosf."""
+    return int(lib().orc_sincos_vs_libm(int(lo), int(hi), int(step)))
 
 
 def hamming256(a, b):

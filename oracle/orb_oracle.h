@@ -22,9 +22,10 @@
  * the real OpenCV kernels through cv2 4.13.0 (tests/test_oracle_kat.py: resize, blur, FAST,
  * fastAtan2 bit-exact) and the whole path against golden vectors produced by a cv2-driven pipeline
  * (tests/golden/make_golden.py).
- * Two choices are pinned by decision because the reference itself is not deterministic there
- * (DESIGN.md §oracle): the quadtree tie-break (creation order instead of heap address) and
- * cos/sin (orbx_sincosf instead of libm).
+ * One choice is pinned by decision because the reference itself is not deterministic there
+ * (DESIGN.md §oracle): the quadtree tie-break (creation order instead of heap address).
+ * cos/sin: the reference's object code calls glibc sincosf; orbx_sincosf restates glibc's algorithm and
+ * equals it on every float in [0, 2*pi] (tests/test_math.py, exhaustive).
  */
 #ifndef ORB_ORACLE_H
 #define ORB_ORACLE_H
@@ -78,6 +79,7 @@ void orc_gaussian7(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, 
 int orc_fast9(const uint8_t* roi, int w, int h, int stride, int threshold, orc_keypoint* out, int capacity);
 float orc_fast_atan2(float y, float x);
 void orc_sincos(float rad, float* s, float* c);
+long orc_sincos_vs_libm(uint32_t lo, uint32_t hi, uint32_t step); /* mismatches against the host's glibc sincosf */
 int orc_hamming256(const uint8_t* a, const uint8_t* b);
 int orc_reflect101(int p, int n);
 /* DistributeOctTree on arbitrary candidates (x,y,response used), src/ORBextractor.cc:542-766 */

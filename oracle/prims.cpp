@@ -202,6 +202,22 @@ extern "C" int orc_fast9(const uint8_t* roi, int w, int h, int stride, int thres
 extern "C" float orc_fast_atan2(float y, float x) { return orbx_fast_atan2(y, x); }
 extern "C" void orc_sincos(float rad, float* s, float* c) { orbx_sincosf(rad, s, c); }
 
+// Checker for tests/test_math.py: how many floats with bit patterns lo, lo+step, ... <= hi give a sin or cos that differs from
+// the host's glibc sincosf (the symbol the reference's object code calls for src/ORBextractor.cc:110).
+extern "C" long orc_sincos_vs_libm(uint32_t lo, uint32_t hi, uint32_t step)
+{
+    long bad = 0;
+    for (uint64_t u = lo; u <= hi; u += step) {
+        const uint32_t b = (uint32_t)u;
+        float x, s0, c0, s1, c1;
+        memcpy(&x, &b, 4);
+        sincosf(x, &s0, &c0);
+        orbx_sincosf(x, &s1, &c1);
+        bad += (memcmp(&s0, &s1, 4) != 0) | (memcmp(&c0, &c1, 4) != 0);
+    }
+    return bad;
+}
+
 // ORBmatcher::DescriptorDistance, src/ORBmatcher.cc:1672-1688 (8 x 32-bit popcount)
 extern "C" int orc_hamming256(const uint8_t* a, const uint8_t* b)
 {

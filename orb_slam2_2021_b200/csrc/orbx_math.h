@@ -73,60 +73,74 @@ ORBX_HD float orbx_fast_atan2(float y, float x)
 }
 
 // ---- sin/cos of a float angle (radians) -----------------------------------------------------
-// The reference calls cos(float)/sin(float) (libm cosf/sinf, src/ORBextractor.cc:109-110). libm is
-// not reproducible across host and device, so both sides use this routine: Cody-Waite reduction
-// by pi/2 and the classic degree-13/14 minimax kernels, all in float64 with explicit fma, then one
-// rounding to float32. The float64 result is accurate to <1 ulp(double), so the float32 value is
-// the correctly rounded sin/cos except for ~1e-8 of inputs (tests/test_math.py measures it).
-// (device: the 15 double constants sit in constant memory so that DMUL/DFMA take them as c[][] operands; as literals each
-// costs two moves into a register pair, and the whole warp runs this once per keypoint)
-#define ORBX_SINCOS_CONSTANTS                                                                                            \
-    6.36619772367581382433e-01, 1.57079632679489655800e+00, 6.12323399573676603587e-17, -1.66666666666666324348e-01,     \
-        8.33333333332248946124e-03, -1.98412698298579493134e-04, 2.75573137070700676789e-06, -2.50507602534068634195e-08, \
-        1.58969099521155010221e-10, 4.16666666666666019037e-02, -1.38888888888741095749e-03, 2.48015872894767294178e-05,  \
-        -2.75573143513906633035e-07, 2.08757232129817482790e-09, -1.13596475577881948265e-11
+// The reference writes cos(angle), sin(angle) on a float (src/ORBextractor.cc:109-110); g++ -O3 merges the pair into ONE call of
+// glibc's sincosf (the only libm symbol the reference's object code imports for this path). glibc's float routines are not
+// correctly rounded -- on [0, 2*pi] 0.13 % of all float angles give a sin or cos one ulp away from the correctly rounded value
+// -- and one ulp in a or b can move a rotated pattern coordinate across a .5 boundary (seen: 1 descriptor bit in ~1e7
+// keypoints). Bit parity therefore needs glibc's own arithmetic, and this is a restatement of it: the sincosf of glibc >= 2.28
+// (sysdeps/ieee754/flt-32/s_sincosf.c, s_sincosf.h, x86_64 sincosf_poly.h; the algorithm published in ARM's optimized-routines):
+// quadrant n and reduced argument in double (x - n*pi/2, no Cody-Waite split: |x| < 120 only), a degree-7 sine and a degree-8
+// cosine polynomial in double, one rounding to float, swap / negate by quadrant. Operation order and the fused multiply-adds
+// are those of the FMA build that glibc's ifunc selects on every AVX2 host; tests/test_math.py compares this routine with the
+// host's sincosf on EVERY float in [0, 2*pi*1.0001] (1.09e9 inputs, 0 differences) and the same sweep shows the unfused (SSE2)
+// build of glibc returns the same floats on that whole domain, so one variant serves both kinds of host.
+// Domain: |x| < 120 (the reference's angle is fastAtan2 * pi/180, in [0, 2*pi]).
+// (device: the constants sit in constant memory so that DMUL/DFMA take them as c[][] operands; as literals each costs two
+// moves into a register pair, and the whole warp runs this once per keypoint)
+#define ORBX_SINCOS_CONSTANTS                                                                                         \
+    0x1.45f306dc9c883p+23, 0x1.921fb54442d18p0, -0x1.ffffffd0c621cp-2, 0x1.55553e1068f19p-5, -0x1.6c087e89a359dp-10, \
+        0x1.99343027bf8c3p-16, -0x1.555545995a603p-3, 0x1.1107605230bc4p-7, -0x1.994eb3774cf24p-13
 #if defined(__CUDACC__)
-static __constant__ double orbx_sincos_dev[15] = {ORBX_SINCOS_CONSTANTS};
+static __constant__ double orbx_sincos_dev[9] = {ORBX_SINCOS_CONSTANTS};
 #endif
 ORBX_HD void orbx_sincosf(float xf, float* s_out, float* c_out)
 {
 #if defined(__CUDA_ARCH__)
     const double* K = orbx_sincos_dev;
+    const uint32_t bits = __float_as_uint(xf);
 #else
-    static const double K[15] = {ORBX_SINCOS_CONSTANTS};
-#endif
-    const double TWO_OVER_PI = K[0], PIO2_HI = K[1], PIO2_LO = K[2];
-    const double S1 = K[3], S2 = K[4], S3 = K[5], S4 = K[6], S5 = K[7], S6 = K[8];
-    const double C1 = K[9], C2 = K[10], C3 = K[11], C4 = K[12], C5 = K[13], C6 = K[14];
-    double x = (double)xf;
-    double kd = rint(orbx_dmul(x, TWO_OVER_PI));
-    int k = (int)kd;
-    double r = orbx_dfma(-kd, PIO2_HI, x);
-    r = orbx_dfma(-kd, PIO2_LO, r);
-    double z = orbx_dmul(r, r);
-    // sin kernel: r + r*z*(S1 + z*(S2 + ...))
-    double ps = orbx_dfma(z, S6, S5);
-    ps = orbx_dfma(z, ps, S4);
-    ps = orbx_dfma(z, ps, S3);
-    ps = orbx_dfma(z, ps, S2);
-    ps = orbx_dfma(z, ps, S1);
-    double sr = orbx_dfma(orbx_dmul(r, z), ps, r);
-    // cos kernel: 1 - z/2 + z*z*(C1 + z*(C2 + ...))
-    double pc = orbx_dfma(z, C6, C5);
-    pc = orbx_dfma(z, pc, C4);
-    pc = orbx_dfma(z, pc, C3);
-    pc = orbx_dfma(z, pc, C2);
-    pc = orbx_dfma(z, pc, C1);
-    double cr = orbx_dfma(orbx_dmul(z, z), pc, orbx_dfma(z, -0.5, 1.0));
-    double s, c;
-    switch (k & 3) {
-        case 0: s = sr; c = cr; break;
-        case 1: s = cr; c = -sr; break;
-        case 2: s = -sr; c = -cr; break;
-        default: s = -cr; c = sr; break;
+    static const double K[9] = {ORBX_SINCOS_CONSTANTS};
+    uint32_t bits;
+    {
+        union { float f; uint32_t u; } cv;
+        cv.f = xf;
+        bits = cv.u;
     }
-    *s_out = (float)s;
-    *c_out = (float)c;
+#endif
+    const double HPI_INV24 = K[0], HPI = K[1];            // 2/pi * 2^24, pi/2
+    const double C1 = K[2], C2 = K[3], C3 = K[4], C4 = K[5];  // cos: 1 + C1 z + C2 z^2 + C3 z^3 + C4 z^4
+    const double S1 = K[6], S2 = K[7], S3 = K[8];             // sin: x + S1 x^3 + S2 x^5 + S3 x^7
+    const uint32_t top = (bits >> 20) & 0x7ffu;  // abstop12
+    double x = (double)xf;
+    int n = 0;
+    if (top <= 0x397u) {  // |x| < 2^-12: sin = x, cos = 1
+        *s_out = xf;
+        *c_out = 1.0f;
+        return;
+    }
+    if (top > 0x3f3u) {  // |x| >= pi/4: reduce_fast; the quadrant rounds to nearest through a 2^24 fixed-point truncation
+        const double r = orbx_dmul(x, HPI_INV24);
+        n = ((int32_t)r + 0x800000) >> 24;
+        x = orbx_dfma(-(double)n, HPI, x);
+    }
+    const double x2 = orbx_dmul(x, x);
+    const double x3 = orbx_dmul(x2, x), x4 = orbx_dmul(x2, x2);
+    const double s1v = orbx_dfma(x2, S3, S2), c2v = orbx_dfma(x2, C4, C3);
+    const double c1v = orbx_dfma(x2, C1, 1.0);
+    const double x5 = orbx_dmul(x2, x3), x6 = orbx_dmul(x2, x4);
+    const double sv = orbx_dfma(x3, S1, x), cv2 = orbx_dfma(x4, C2, c1v);
+    // glibc multiplies x by sign[n & 3] before the odd polynomial and takes the negated cosine table for n & 2; both are exact
+    // sign changes of the results (round-to-nearest is symmetric), applied here to the two floats instead.
+    float fs = (float)orbx_dfma(s1v, x5, sv), fc = (float)orbx_dfma(c2v, x6, cv2);
+    if (((n + 1) & 2) != 0) fs = -fs;  // quadrants 1, 2
+    if ((n & 2) != 0) fc = -fc;
+    if (n & 1) {
+        *s_out = fc;
+        *c_out = fs;
+    } else {
+        *s_out = fs;
+        *c_out = fc;
+    }
 }
 
 // 256-bit Hamming distance, descriptors read as 8 x uint32 (src/ORBmatcher.cc:1672-1688).

@@ -23,16 +23,28 @@ def test_fast_atan2_axes():
         assert O.fast_atan2(y, x) == cv2.fastAtan2(float(y), float(x))
 
 
-def test_sincos_correctly_rounded():
-    rng = np.random.default_rng(1)
-    deg = np.concatenate([rng.uniform(0, 360, 200000), np.arange(0, 360.5, 0.5)]).astype(np.float32)
-    rad = (deg * np.float32(np.pi / np.float64(np.float32(180.0)))).astype(np.float32)
-    bad = 0
-    for r in rad:
+def test_sincos_is_glibc_sincosf_on_every_angle():
+    """src/ORBextractor.cc:109-110: the reference's object code calls glibc sincosf. The shared routine restates glibc's algorithm;
+    this sweeps EVERY float from 0 to 2*pi*1.0001 (the angle is fastAtan2 * pi/180) against the host's libm: 1.09e9 inputs."""
+    import os
+    from concurrent.futures import ThreadPoolExecutor
+
+    hi = int(np.array([2 * np.pi * 1.0001], np.float32).view(np.uint32)[0])
+    threads = max(1, min(16, len(os.sched_getaffinity(0))))
+    with ThreadPoolExecutor(threads) as ex:  # ctypes drops the GIL; thread t takes bit patterns t, t+threads, ...
+        bad = list(ex.map(lambda t: O.sincos_vs_libm(t, hi, threads), range(threads)))
+    assert sum(bad) == 0
+    # negative angles and the rest of the fast path (|x| < 120) on a stride
+    assert O.sincos_vs_libm(0x80000000, 0x80000000 + hi, 997) == 0
+    assert O.sincos_vs_libm(hi, int(np.array([119.0], np.float32).view(np.uint32)[0]), 101) == 0
+
+
+def test_sincos_known_values():
+    for deg in (0.0, 90.0, 180.0, 270.0, 359.99997):
+        r = np.float32(deg) * np.float32(np.pi / np.float64(np.float32(180.0)))
         s, c = O.sincos(r)
-        bad += s != np.float32(np.sin(np.float64(r)))
-        bad += c != np.float32(np.cos(np.float64(r)))
-    assert bad == 0  # float64 kernel + one rounding == correctly rounded on this sample
+        assert abs(s - np.sin(np.float64(r))) < 1.2e-7 and abs(c - np.cos(np.float64(r))) < 1.2e-7
+    assert O.sincos(0.0) == (0.0, 1.0)
 
 
 def test_hamming():
