@@ -117,7 +117,7 @@ int Engine::plan(const ExtractorConfig& cfg, int rows, int cols, OrbxParams& p, 
     std::memset(&p, 0, sizeof(p));
     p.nlevels = cfg.nlevels; p.iniTh = cfg.iniTh; p.minTh = cfg.minTh; p.rows = rows; p.cols = cols;
     unsigned off = 0, boff = 0, slot = 0, cand = 0;
-    int cellBase = 0, keepBase = 0;
+    int cellBase = 0, keepBase = 0, spillCap = 0;
     for (int l = 0; l < cfg.nlevels; ++l) {
         OrbxLevel& L = p.lv[l];
         L.w = orbx_cvround((float)cols * cfg.invScale[l]);  // :1110
@@ -145,12 +145,13 @@ int Engine::plan(const ExtractorConfig& cfg, int rows, int cols, OrbxParams& p, 
         L.hX = (float)bw / L.nIni;  // :548
         int cap = (L.quota > 4 * L.nIni ? L.quota : 4 * L.nIni) + 4;
         L.keepCap = (cap + 7) & ~7;  // whole describe CTAs (8 warps = 8 slots) per level
-        // the quadtree keeps a level's node list in the shared memory of one CTA (227 KB opt-in maximum per CTA on sm_100)
-        if (L.keepCap > 65000 || orbx_octree_smem_total(L.keepCap) > 227u * 1024u) {
-            err = "per-level feature quota " + std::to_string(L.quota) + " (level " + std::to_string(l) + ") too large: the quadtree holds at most ~2600 nodes per level "
-                  "(about 12000 features at scaleFactor 1.2 / 8 levels); use fewer features or more levels";
+        // the quadtree keeps a level's node list in the shared memory of one CTA (227 KB opt-in maximum per CTA on sm_100) and
+        // moves it to global memory above that (~2600 nodes per level); list positions are 16 bits wide
+        if (L.keepCap > 65000) {
+            err = "per-level feature quota " + std::to_string(L.quota) + " (level " + std::to_string(l) + ") too large: the quadtree holds at most 65000 nodes per level";
             return ORBX_ERR_ARG;
         }
+        if (orbx_octree_smem_total(L.keepCap) > 227u * 1024u) spillCap = std::max(spillCap, L.keepCap);
         L.keepBase = keepBase; keepBase += L.keepCap;
         L.scale = cfg.scale[l]; L.invScale = cfg.invScale[l];
         L.patchSize = (int)(31 * cfg.scale[l]);  // :836
@@ -159,6 +160,8 @@ int Engine::plan(const ExtractorConfig& cfg, int rows, int cols, OrbxParams& p, 
     p.pyrStride = off; p.blurStride = boff;
     p.cellsTotal = cellBase; p.slotTotal = slot; p.candTotal = cand;
     p.keepTotal = keepBase; p.maxKp = keepBase;
+    p.octSpill = nullptr;
+    p.octSpillStride = spillCap ? align_up(orbx_octree_list_bytes(spillCap), 256) : 0;
     if (p.maxKp > 65535) { err = "more than 65535 keypoints per image not supported"; return ORBX_ERR_ARG; }
     return ORBX_OK;
 }
@@ -307,6 +310,7 @@ int Engine::init(const ExtractorConfig& c, int r, int w, int nImgs, bool st, int
     TRY(dalloc(this, &P.outCnt, n, "outCnt", err));
     P.chainInts = orbx_pyramid_chain_state_ints(P);
     TRY(dalloc(this, &P.chainState, n * P.chainInts, "chainState", err));
+    if (P.octSpillStride) TRY(dalloc(this, &P.octSpill, n * P.nlevels * P.octSpillStride, "quadtree node lists", err));
     TRY(orbx_check(cudaMemsetAsync(P.outCnt, 0, n * sizeof(int), stream), "memset", err));
     TRY(orbx_check(cudaMemsetAsync(P.keepCnt, 0, n * P.nlevels * sizeof(int), stream), "memset", err));
     TRY(orbx_check(cudaMemsetAsync(P.chainState, 0, n * P.chainInts * sizeof(int), stream), "memset", err));
@@ -470,6 +474,7 @@ OrbxParams Engine::slice(int b, int nImgs) const
     p.keep += o * P.keepTotal; p.keepCnt += o * P.nlevels; p.candCnt += o * P.nlevels; p.keepOfs += o * P.nlevels;
     p.outKp = (uint8_t*)P.outKp + o * P.maxKp * 28; p.outDesc += o * P.maxKp * 32; p.outCnt += o;
     p.chainState += o * P.chainInts;
+    if (P.octSpill) p.octSpill += o * P.nlevels * P.octSpillStride;
     return p;
 }
 

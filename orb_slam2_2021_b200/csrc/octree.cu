@@ -104,6 +104,9 @@ struct __align__(8) OrbxCellRec {  // same layout as OrbxCell in fast.cu
 
 #define OCT_CELL_CHUNK 512  // cells gathered per round of step 0 (2 KB of static shared memory; KITTI's largest level has 429)
 
+// SPILL: the node list lives in p.octSpill (global memory, L2-resident) instead of dynamic shared memory -- for per-level quotas
+// above ~2600 nodes, which the reference accepts and the shared memory of one CTA cannot hold. Same code, generic addressing.
+template <bool SPILL>
 __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, const OrbxCellRec* cells)
 {
     extern __shared__ __align__(16) uint8_t smraw[];
@@ -118,7 +121,7 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
 
     // carve shared memory (largest alignment first)
     OctSmem S;
-    uint8_t* ptr = smraw;
+    uint8_t* ptr = SPILL ? p.octSpill + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * p.octSpillStride : smraw;
     S.box[0] = (short4*)ptr; ptr += sizeof(short4) * cap;
     S.box[1] = (short4*)ptr; ptr += sizeof(short4) * cap;
     S.cnt[0] = (int*)ptr; ptr += 4 * cap;
@@ -364,6 +367,7 @@ __global__ void __launch_bounds__(OCT_THREADS) orbx_octree_kernel(OrbxParams p, 
 }
 
 static size_t octree_smem_bytes(int cap) { return (size_t)cap * 80 + 64; }
+size_t orbx_octree_list_bytes(int cap) { return octree_smem_bytes(cap); }
 // dynamic + static shared memory of one quadtree CTA for a per-level list capacity (Engine::plan rejects what the SM cannot hold)
 size_t orbx_octree_smem_total(int cap) { return octree_smem_bytes(cap) + sizeof(int) * (OCT_THREADS / 32 + 1 + OCT_CELL_CHUNK + 1 + 3) + 64; }
 
@@ -372,9 +376,13 @@ void orbx_launch_octree(const OrbxParams& p, const void* cellTable, cudaStream_t
     int cap = 0;
     for (int l = 0; l < p.nlevels; ++l) cap = p.lv[l].keepCap > cap ? p.lv[l].keepCap : cap;
     const size_t smem = octree_smem_bytes(cap);
-    if (smem > 32 * 1024)  // static + dynamic above 48 KB needs the opt-in; per-device attribute, set on every such launch
-        if (cudaFuncSetAttribute(orbx_octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
-            return;  // the error stays pending for the caller's cudaGetLastError; no launch on unwritten state
     dim3 grid(p.nlevels, p.imgs);
-    orbx_octree_kernel<<<grid, OCT_THREADS, smem, s>>>(p, (const OrbxCellRec*)cellTable);
+    if (p.octSpillStride) {  // Engine::plan chose the global-memory list (the quota does not fit a CTA's shared memory)
+        orbx_octree_kernel<true><<<grid, OCT_THREADS, 0, s>>>(p, (const OrbxCellRec*)cellTable);
+        return;
+    }
+    if (smem > 32 * 1024)  // static + dynamic above 48 KB needs the opt-in; per-device attribute, set on every such launch
+        if (cudaFuncSetAttribute(orbx_octree_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return;  // the error stays pending for the caller's cudaGetLastError; no launch on unwritten state
+    orbx_octree_kernel<false><<<grid, OCT_THREADS, smem, s>>>(p, (const OrbxCellRec*)cellTable);
 }

@@ -75,6 +75,8 @@ struct OrbxParams {
     int* keepOfs;  // [imgs][L] exclusive prefix of keepCnt = first output index of a level (written by the count kernel)
     int* chainState;   // counters of the one-launch pyramid (orbx_launch_pyramid_chain): chainInts per image, advanced by slice()
     int chainInts;
+    uint8_t* octSpill;      // quadtree node lists in global memory, octSpillStride bytes per (image, level); only for quotas whose
+    size_t octSpillStride;  // list does not fit the shared memory of a CTA (0 otherwise), advanced by slice()
     void* outKp;   // orbx_keypoint[imgs][maxKp]
     uint8_t* outDesc;
     int* outCnt;
@@ -131,6 +133,7 @@ void orbx_fast_geometry(const OrbxParams& p, int* boxW, int* rhMax);  // TMA box
 void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* levelMaps, cudaStream_t s);
 void orbx_launch_octree(const OrbxParams& p, const void* cellTable, cudaStream_t s);
 size_t orbx_octree_smem_total(int cap);  // shared memory of one quadtree CTA with a per-level list capacity of cap
+size_t orbx_octree_list_bytes(int cap);  // bytes of one node list (the dynamic shared memory, or the spill slot in global memory)
 void orbx_launch_blur(const OrbxParams& p, const void* tileTable, int nTiles, const void* levelMaps, cudaStream_t s);
 void orbx_launch_describe(const OrbxParams& p, const void* mapsPlain, const void* mapsBlur, cudaStream_t s);
 void orbx_launch_stereo(const OrbxParams& pl, const OrbxParams& pr, const OrbxStereoParams& sp, cudaStream_t s);

@@ -79,26 +79,28 @@ def test_fails_loudly_without_gpu(has_gpu):
 
 
 def test_quota_beyond_the_quadtree_capacity_is_a_clean_error():
-    """A per-level quota whose node list does not fit one CTA's shared memory is refused with ORBX_ERR_ARG and a text
-    (it used to surface as an opaque launch failure on every extract)."""
-    e = pkg.ORBextractor(20000, 1.2, 8, 20, 7)
+    """Per-level quotas whose node list does not fit one CTA's shared memory (~2600 nodes) are served from a global-memory list;
+    only a list beyond the 16-bit positions (65000 nodes per level) is refused, with ORBX_ERR_ARG and a text."""
+    assert pkg.lib().orbx_max_keypoints(pkg.ORBextractor(20000, 1.2, 8, 20, 7)._h, 2160, 3840) > 20000
+    assert pkg.lib().orbx_max_keypoints(pkg.ORBextractor(3000, 1.2, 1, 20, 7)._h, 480, 640) > 3000
+    e = pkg.ORBextractor(400000, 1.2, 8, 20, 7)
     rc = pkg.lib().orbx_max_keypoints(e._h, 2160, 3840)
     assert rc == pkg._lib.ERR_ARG
     assert b"quota" in pkg.lib().orbx_last_error()
-    assert pkg.lib().orbx_max_keypoints(pkg.ORBextractor(12000, 1.2, 8, 20, 7)._h, 2160, 3840) > 12000
-    assert pkg.lib().orbx_max_keypoints(pkg.ORBextractor(3000, 1.2, 1, 20, 7)._h, 480, 640) == pkg._lib.ERR_ARG
 
 
 @pytest.mark.gpu
 def test_oversized_quota_fails_cleanly_on_the_device_too():
-    """nfeatures = 20000 at 8 levels: orbx_extract reports ORBX_ERR_ARG with the quota text instead of a launch failure,
-    and the handle stays usable for sizes it can serve."""
+    """nfeatures = 400000 at 8 levels: orbx_extract reports ORBX_ERR_ARG with the quota text instead of a launch failure,
+    and quotas above the shared-memory list (20000 features) run from the global-memory list."""
     from orb_slam2_2021_b200 import synth
 
-    e = pkg.ORBextractor(20000, 1.2, 8, 20, 7)
+    e = pkg.ORBextractor(400000, 1.2, 8, 20, 7)
     with pytest.raises(pkg.OrbxError) as ei:
         e(synth.synth(1280, 720, 1))
     assert ei.value.code == pkg._lib.ERR_ARG and "quota" in str(ei.value)
+    k, d = pkg.ORBextractor(20000, 1.2, 8, 20, 7)(synth.synth(1280, 720, 1))
+    assert len(k) > 3000 and d.shape == (len(k), 32)
     ok = pkg.ORBextractor(12000, 1.2, 8, 20, 7)
     k, d = ok(synth.synth(1280, 720, 1))
     assert len(k) > 3000 and d.shape == (len(k), 32)

@@ -381,6 +381,8 @@ def test_cpp_shim_reference_signature(tmp_path):
     (50, 1.3, 6, 254, 1, 640, 400),      # threshold extremes: the fallback to minTh fires in almost every cell
     (1500, 1.25, 8, 20, 7, 1023, 511),   # odd sizes: pitches with padding, ragged tiles and cells
     (1200, 1.2, 8, 20, 7, 1280, 720),    # width a multiple of 16: no row padding anywhere
+    (9000, 1.2, 1, 12, 5, 800, 600),     # one level holding the whole quota: the quadtree's node list lives in global memory
+    (20000, 1.2, 8, 10, 3, 1280, 720),   # every level above the shared-memory list; more features asked for than there are corners
 ])
 def test_extractor_parameter_space(nf, sf, nl, ini, mn, W, H):
     """Other extractor parameters than the BASELINE configs, bit-exact against the oracle incl. every pyramid level."""
