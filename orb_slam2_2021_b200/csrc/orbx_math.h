@@ -84,7 +84,7 @@ ORBX_HD float orbx_fast_atan2(float y, float x)
 // are those of the FMA build that glibc's ifunc selects on every AVX2 host; tests/test_math.py compares this routine with the
 // host's sincosf on EVERY float in [0, 2*pi*1.0001] (1.09e9 inputs, 0 differences) and the same sweep shows the unfused (SSE2)
 // build of glibc returns the same floats on that whole domain, so one variant serves both kinds of host.
-// Domain: |x| < 120 (the reference's angle is fastAtan2 * pi/180, in [0, 2*pi]).
+// Domain: host |x| < 120; device 0 <= x < 7.0685 (the reference's angle is fastAtan2 * pi/180, in [0, 2*pi]).
 // (device: the constants sit in constant memory so that DMUL/DFMA take them as c[][] operands; as literals each costs two
 // moves into a register pair, and the whole warp runs this once per keypoint)
 #define ORBX_SINCOS_CONSTANTS                                                                                         \
@@ -110,18 +110,47 @@ ORBX_HD void orbx_sincosf(float xf, float* s_out, float* c_out)
     const double HPI_INV24 = K[0], HPI = K[1];            // 2/pi * 2^24, pi/2
     const double C1 = K[2], C2 = K[3], C3 = K[4], C4 = K[5];  // cos: 1 + C1 z + C2 z^2 + C3 z^3 + C4 z^4
     const double S1 = K[6], S2 = K[7], S3 = K[8];             // sin: x + S1 x^3 + S2 x^5 + S3 x^7
-    const uint32_t top = (bits >> 20) & 0x7ffu;  // abstop12
     double x = (double)xf;
-    int n = 0;
-    if (top <= 0x397u) {  // |x| < 2^-12: sin = x, cos = 1
-        *s_out = xf;
-        *c_out = 1.0f;
-        return;
-    }
-    if (top > 0x3f3u) {  // |x| >= pi/4: reduce_fast; the quadrant rounds to nearest through a 2^24 fixed-point truncation
-        const double r = orbx_dmul(x, HPI_INV24);
-        n = ((int32_t)r + 0x800000) >> 24;
-        x = orbx_dfma(-(double)n, HPI, x);
+    bool swap, sneg, cneg;  // quadrant: results exchanged (n odd), sine negated (n & 3 in {1, 2}), cosine negated (n & 2)
+#if !defined(__CUDA_ARCH__)
+    if (bits >= 0x40e231d6u) {  // negative or >= 7.0685835: the general fast path of glibc (|x| < 120). The extractor never
+                                // gets here, and the device build leaves it out to stay free of branches.
+        const uint32_t top = (bits >> 20) & 0x7ffu;  // abstop12
+        if (top <= 0x397u) {                         // |x| < 2^-12
+            *s_out = xf;
+            *c_out = 1.0f;
+            return;
+        }
+        int n = 0;
+        if (top > 0x3f3u) {
+            const double r = orbx_dmul(x, HPI_INV24);
+            n = ((int32_t)r + 0x800000) >> 24;
+            x = orbx_dfma(-(double)n, HPI, x);
+        }
+        swap = (n & 1) != 0;
+        sneg = ((n + 1) & 2) != 0;
+        cneg = (n & 2) != 0;
+    } else
+#endif
+    {
+        // 0 <= x < 7.0685835: every angle the extractor produces. glibc's reduce_fast takes the quadrant from
+        // n = ((int32_t)(x * 2/pi * 2^24) + 2^23) >> 24, a double multiply and two conversions at the head of the dependency
+        // chain. n is monotonic in x, so on this interval it is the number of thresholds not above x; the four floats are the
+        // first inputs on which glibc's expression steps (found by walking every float; positive floats order like their bit
+        // patterns). Below pi/4 glibc skips the reduction, which is n = 0 here as well, and its |x| < 2^-12 shortcut
+        // (sin = x, cos = 1) returns what the polynomials round to anyway (checked on every float below 2^-11).
+        const bool p1 = bits >= 0x3f490fdbu, p2 = bits >= 0x4016cbe4u, p3 = bits >= 0x407b53d2u, p4 = bits >= 0x40afede0u;
+#if defined(__CUDA_ARCH__)
+        // (double)n for n = 0..4 as the high word of the double: no I2F.F64, four selects
+        const int hi = p4 ? 0x40100000 : p3 ? 0x40080000 : p2 ? 0x40000000 : p1 ? 0x3FF00000 : 0;
+        const double nd = __hiloint2double(hi, 0);
+#else
+        const double nd = (double)((int)p1 + (int)p2 + (int)p3 + (int)p4);
+#endif
+        x = orbx_dfma(-nd, HPI, x);  // n == 0: x - 0 * pi/2 = x exactly
+        swap = (p1 && !p2) || (p3 && !p4);  // n = 1, 3
+        sneg = p1 && !p3;                   // n = 1, 2
+        cneg = p2 && !p4;                   // n = 2, 3
     }
     const double x2 = orbx_dmul(x, x);
     const double x3 = orbx_dmul(x2, x), x4 = orbx_dmul(x2, x2);
@@ -132,15 +161,10 @@ ORBX_HD void orbx_sincosf(float xf, float* s_out, float* c_out)
     // glibc multiplies x by sign[n & 3] before the odd polynomial and takes the negated cosine table for n & 2; both are exact
     // sign changes of the results (round-to-nearest is symmetric), applied here to the two floats instead.
     float fs = (float)orbx_dfma(s1v, x5, sv), fc = (float)orbx_dfma(c2v, x6, cv2);
-    if (((n + 1) & 2) != 0) fs = -fs;  // quadrants 1, 2
-    if ((n & 2) != 0) fc = -fc;
-    if (n & 1) {
-        *s_out = fc;
-        *c_out = fs;
-    } else {
-        *s_out = fs;
-        *c_out = fc;
-    }
+    fs = sneg ? -fs : fs;
+    fc = cneg ? -fc : fc;
+    *s_out = swap ? fc : fs;
+    *c_out = swap ? fs : fc;
 }
 
 // 256-bit Hamming distance, descriptors read as 8 x uint32 (src/ORBmatcher.cc:1672-1688).
