@@ -39,7 +39,7 @@ typedef struct orbx_batch orbx_batch;         /* frame-batch engine for throughp
 const char* orbx_last_error(void);            /* thread-local text of the last failure            */
 int orbx_device_count(void);
 /* Debug/experiment knobs (no reference counterpart; the library never reads the environment). Keys: run_streams,
- * run_chunks, e2e_streams, e2e_chunks, e2e_first_div, e2e_trace, fast_cells, fast_grid_mult, numa_off, pyr_chain, pyr_tma; value 0 restores
+ * run_chunks, e2e_streams, e2e_chunks, e2e_first_div, e2e_trace, fast_cells, fast_grid_mult, fast_ctas, numa_off, pyr_chain, pyr_tma; value 0 restores
  * the built-in default. Process-wide, not thread-safe against running calls. Unknown key: ORBX_ERR_ARG. */
 int orbx_set_tuning(const char* key, int value);
 
@@ -47,7 +47,10 @@ int orbx_set_tuning(const char* key, int value);
 
 /* Replaces ORBextractor::ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST,
  * int minThFAST) — include/ORBextractor.h:65-66, src/ORBextractor.cc:413-473 (constructed at
- * src/Tracking.cc:125-131). `device` is the CUDA ordinal. */
+ * src/Tracking.cc:125-131). `device` is the CUDA ordinal.
+ * Where this library is narrower than the reference (ORBX_ERR_ARG with a text): 1 <= nlevels <= 12, 1 < scaleFactor <= 2.0,
+ * thresholds 1..254, and at most 65000 quadtree nodes per level (a per-level feature quota far beyond any ORB-SLAM2 setting;
+ * quotas above ~2600 per level run from a global-memory node list instead of shared memory). */
 int orbx_create(int nfeatures, float scale_factor, int nlevels, int ini_th_fast, int min_th_fast, int device,
                 orbx_extractor** out);
 void orbx_destroy(orbx_extractor* e);
