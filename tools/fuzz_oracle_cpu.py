@@ -43,12 +43,13 @@ while time.time() - t0 < budget and sum(cases) < max_cases:
             continue
         r_l, r_r = R.RefExtractor(nf, sf, nl, ini, mn), R.RefExtractor(nf, sf, nl, ini, mn)
         wl, wr = r_l(left), r_r(right)
-        bf, fx = 40.0, float(rng.choice([300.0, 500.0, 718.0]))
-        wu, wd = R.stereo_match(r_l, r_r, wl[0], wl[1], wr[0], wr[1], bf, bf / fx)
-        ou, od = O.stereo_match(o, o_r, ol[0], ol[1], orr[0], orr[1], bf, bf / fx)
+        bf, fx = float(rng.choice([40.0, 47.9, 386.1])), float(rng.choice([300.0, 500.0, 718.0]))
+        mb = float(rng.choice([bf / fx, bf / fx, 0.0]))  # 0: the reference reads mb before setting it (maxD = inf)
+        wu, wd = R.stereo_match(r_l, r_r, wl[0], wl[1], wr[0], wr[1], bf, mb)
+        ou, od = O.stereo_match(o, o_r, ol[0], ol[1], orr[0], orr[1], bf, mb)
         if not (same(ol, wl) and same(orr, wr) and ou.tobytes() == wu.tobytes() and od.tobytes() == wd.tobytes()):
             bad += 1
-            print("MISMATCH extract/stereo", dict(W=W, H=H, nf=nf, sf=sf, nl=nl, ini=ini, mn=mn, seed=seed, style=style, fx=fx), flush=True)
+            print("MISMATCH extract/stereo", dict(W=W, H=H, nf=nf, sf=sf, nl=nl, ini=ini, mn=mn, seed=seed, style=style, bf=bf, mb=mb), flush=True)
     elif kind == 1:
         n_last = int(rng.integers(1, 4000))
         kw = dict(n_last=n_last, n_extra=int(rng.integers(0, 2000)), W=int(rng.integers(200, 1400)), H=int(rng.integers(150, 800)),

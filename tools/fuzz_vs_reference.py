@@ -41,16 +41,17 @@ while time.time() - t0 < budget and cases < max_cases:
     left, right = fuzz_images.stereo_pair(style, W, H, seed)
     r_l, r_r = R.RefExtractor(nf, sf, nl, ini, mn), R.RefExtractor(nf, sf, nl, ini, mn)
     want_l, want_r = r_l(left), r_r(right)
-    bf, fx = 40.0, 500.0
-    want_u, want_d = R.stereo_match(r_l, r_r, want_l[0], want_l[1], want_r[0], want_r[1], bf, bf / fx)
+    bf = float(rng.choice([40.0, 47.9, 386.1]))
+    mb = float(rng.choice([bf / 500.0, bf / 718.9, bf / 300.0, 0.0]))  # 0: the reference reads mb before setting it (maxD = inf)
+    want_u, want_d = R.stereo_match(r_l, r_r, want_l[0], want_l[1], want_r[0], want_r[1], bf, mb)
     ok = same(ex(left), want_l)
     fl, fr = pkg.ORBextractor(nf, sf, nl, ini, mn), pkg.ORBextractor(nf, sf, nl, ini, mn)
     for _ in range(2):
-        kl, dl, kr, dr, ur, dp = pkg.stereo_frame(fl, fr, left, right, bf, bf / fx)
+        kl, dl, kr, dr, ur, dp = pkg.stereo_frame(fl, fr, left, right, bf, mb)
         ok = ok and same((kl, dl), want_l) and same((kr, dr), want_r) and ur.tobytes() == want_u.tobytes() and dp.tobytes() == want_d.tobytes()
     n = 5
     b = pkg.StereoFrameBatch(nf, sf, nl, ini, mn, H, W, n, stereo=True)
-    out = b.process(np.stack([left] * n), np.stack([right] * n), bf, bf / fx)
+    out = b.process(np.stack([left] * n), np.stack([right] * n), bf, mb)
     for k in (0, n - 1):
         a, c = int(out["n_left"][k]), int(out["n_right"][k])
         ok = ok and same((out["kps_left"][k, :a], out["desc_left"][k, :a]), want_l) and same((out["kps_right"][k, :c], out["desc_right"][k, :c]), want_r)
@@ -58,6 +59,6 @@ while time.time() - t0 < budget and cases < max_cases:
     cases += 1
     if not ok:
         bad += 1
-        print("MISMATCH", dict(W=W, H=H, nf=nf, sf=sf, nl=nl, ini=ini, mn=mn, seed=seed, style=style), flush=True)
+        print("MISMATCH", dict(W=W, H=H, nf=nf, sf=sf, nl=nl, ini=ini, mn=mn, seed=seed, style=style, bf=bf, mb=mb), flush=True)
 print(f"{cases} random configurations in {time.time() - t0:.0f} s, {bad} mismatches")
 sys.exit(1 if bad else 0)
