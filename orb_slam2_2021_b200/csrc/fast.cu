@@ -14,20 +14,25 @@
 // the cell's slot array, so cells concatenated in table order give the reference's candidate order.
 //
 // Blackwell mapping (measured with tools/ubench/pipes.cu: VIMNMX3.U16x2 issues at the same rate as a 32-bit IMNMX, so
-// packing two pixels per register halves the min/max work; the kernel is bound by instruction issue, not by a pipe):
+// packing two pixels per register halves the min/max work). The kernel is bound by the ALU pipe (min/max, LOP3, PRMT,
+// SHF, ISETP, VABSDIFF4) with the issue slots close behind, while the FMA pipe (IMAD) and the load/store unit have room:
+// every 1:1 move of an operation from the ALU pipe to IMAD paid, every 1:2 move lost (numbers at fast_strength2_raw).
 //   * the ROI arrives by ONE TMA box load (cp.async.bulk.tensor.3d, 64 or 96 columns starting at x0 & ~15 — the copy
 //     engine addresses the innermost dimension in 16-byte units — by rhMax rows) signalled on an mbarrier;
 //   * pass 1 runs a byte-wise NECESSARY test for a corner at the attempt's threshold on the interior words of the raw
 //     tile, 4 pixels at once (VABSDIFF4 + SWAR compare against the compass points); the surviving pixel
-//     PAIRS are appended to the cell's task list step by step with ballots (row-major order);
+//     PAIRS are appended to the cell's task list step by step with ballots, a word's two pairs side by side, so the list
+//     is sorted by (row, column); list positions are running shared-memory addresses advanced by multiply-adds;
 //   * pass 2 runs the exact test on the listed pairs only. A thread owns two horizontally adjacent pixels (even tile
-//     column first) and reads the 17 pairs (ring(x), ring(x+1)) straight from the raw tile (an aligned 16-bit load or two
-//     byte loads, one PRMT each: a widened u16 copy of the ROI cost more than it saved). Min and max commute with
+//     column first) and reads the 17 pairs (ring(x), ring(x+1)) straight from the raw tile (two byte loads and one
+//     multiply-add each: a widened u16 copy of the ROI cost more than it saved). Min and max commute with
 //     subtracting the centre, so the whole min/max network runs on the raw unsigned u16x2 ring values with the 3-input
 //     DPX instructions (__vimin3_u16x2 / __vimax3_u16x2): 36 ops per polarity and pixel PAIR (pair and quad minima shared
 //     by the two arcs that start at k and k+1);
-//   * strengths stay packed to the end; m - thr goes to a u16 map for m > thr; NMS is driven by the list of non-zero pairs
-//     and uses packed column maxima; maxima are collected in a list and emitted at their row-major rank (reference order);
+//   * strengths stay packed to the end; m - thr goes to a byte map for m > thr; NMS is driven by the list of non-zero pairs
+//     and uses packed column maxima; the list of non-zero pairs and the list of maxima are order-preserving compactions of
+//     the sorted task list, so the maxima come out in the reference's row-major order and are emitted as they stand (the
+//     rank computation of the earlier version — one compare per pair of maxima — is gone);
 //   * one warp per cell, four cells per CTA, long-lived warps: see the kernel.
 #include "engine.h"
 #include "orbx_dev.cuh"
@@ -40,8 +45,29 @@ struct __align__(8) OrbxCell {  // 8 bytes, loaded as one 64-bit word
 };
 
 
-// Corner strengths of two horizontally adjacent pixels from the 17 u16x2 vectors cc (centre pair) and d[0..15] (ring pairs).
-__device__ __forceinline__ uint32_t fast_network2(uint32_t cc, const uint32_t (&d)[16])
+// lo | hi << 16 as ONE multiply-add: the kernel is bound by the ALU pipe (min/max, PRMT, LOP3, SHF), the FMA pipe that
+// executes IMAD is nearly idle — mad.lo keeps ptxas from turning the packing back into PRMT / LEA
+__device__ __forceinline__ uint32_t orbx_pack_u16x2(uint32_t lo, uint32_t hi)
+{
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, 65536, %2;" : "=r"(r) : "r"(hi), "r"(lo));
+    return r;
+}
+__device__ __forceinline__ uint32_t orbx_mad(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ void orbx_sts_u16(uint32_t addr, uint32_t v)
+{
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)v) : "memory");
+}
+__device__ __forceinline__ void orbx_sts_u32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+
+// Corner strengths ABOVE thr (0 = not a corner at thr) of two horizontally adjacent pixels from the 17 u16x2 vectors cc
+// (centre pair) and d[0..15] (ring pairs).
+__device__ __forceinline__ uint32_t fast_network2(uint32_t cc, const uint32_t (&d)[16], uint32_t thr)
 {
     // the network runs on the raw ring values (min and max commute with subtracting the centre): no per-value arithmetic
     // Arcs k and k+1 (k even) share the 8 values d[k+1..k+8]: max(min arc k, min arc k+1) = min(min8, max(d[k], d[k+9])).
@@ -69,32 +95,37 @@ __device__ __forceinline__ uint32_t fast_network2(uint32_t cc, const uint32_t (&
     }
     uint32_t br = __vimax3_u16x2(__vimax3_u16x2(tl[0], tl[1], tl[2]), __vimax3_u16x2(tl[3], tl[4], tl[5]), __vimax3_u16x2(tl[6], tl[7], tl[7]));
     uint32_t dk = __vimin3_u16x2(__vimin3_u16x2(th[0], th[1], th[2]), __vimin3_u16x2(th[3], th[4], th[5]), __vimin3_u16x2(th[6], th[7], th[7]));
-    // strength = max(brightest arc minimum - centre, centre - darkest arc maximum, 0), per half and still packed: clamping
-    // the two extremes at the centre first keeps both differences non-negative, so the 32-bit subtractions cannot borrow
-    // across the halves (a negative strength is "no corner" at any threshold, like 0)
-    br = __vimax3_u16x2(br, cc, cc);
-    dk = __vimin3_u16x2(dk, cc, cc);
-    const uint32_t up = br - cc, dn = cc - dk;
-    return __vimax3_u16x2(up, dn, dn);
+    // strength above the threshold, max(brightest arc minimum - centre - thr, centre - darkest arc maximum - thr, 0), per half
+    // and still packed. centre + thr and darkest + thr stay below 2^16 per half and each difference is clamped at 0 by the
+    // max in front of it, so the 32-bit adds / subtracts cannot carry across the halves; a pixel cannot be a bright and a
+    // dark corner at once (9 + 9 > 16 ring pixels), so the sum of the two terms is their maximum. The adds are multiply-adds
+    // (FMA pipe); only the two max operations use the ALU pipe.
+    const uint32_t hi = orbx_mad(thr, 0x10001u, cc), dkt = orbx_mad(thr, 0x10001u, dk);
+    const uint32_t up = orbx_mad(hi, 0xFFFFFFFFu, __vimax3_u16x2(br, hi, hi));
+    const uint32_t dn = orbx_mad(dkt, 0xFFFFFFFFu, __vimax3_u16x2(cc, dkt, dkt));
+    return up + dn;
 }
 
 // The 17 vectors come straight from the raw tile (no widened copy of the ROI: building one cost more instructions and 7 KB
-// of shared memory per cell than it saved here). t points at pixel 0 of the pair, an EVEN byte address: pairs at even dx are
-// one aligned 16-bit load + PRMT, pairs at odd dx two byte loads + PRMT. BW = row stride of the tile.
+// of shared memory per cell than it saved here). t points at pixel 0 of the pair; every pair is two byte loads and one
+// multiply-add (lo + 65536 * hi, FMA pipe). Measured on B200, 512 KITTI images: pairs at even dx as one 16-bit load + PRMT
+// and the rest as two byte loads + PRMT (the form before): 1.322 ms; byte loads + IMAD for the odd ones only: 1.295;
+// for all: 1.229 with the lean list bookkeeping below (1.234 with PRMT on the even ones) — the ALU pipe (min/max, PRMT,
+// LOP3, SHF, ISETP) is what binds this kernel, the load/store unit and the FMA pipe have room. Replacing one PRMT by TWO
+// multiplies (IMAD.HI + IMAD on a 16-bit load) loses (1.331): issue slots count too.
+// BW = row stride of the tile.
 template <int BW>
-__device__ __forceinline__ uint32_t fast_strength2_raw(const uint8_t* t)
+__device__ __forceinline__ uint32_t fast_strength2_raw(const uint8_t* t, uint32_t thr)
 {
-#define RING_E(dx, dy) __byte_perm((uint32_t)*reinterpret_cast<const uint16_t*>(t + (dy) * BW + (dx)), 0, 0x4140)
-#define RING_O(dx, dy) __byte_perm((uint32_t)t[(dy) * BW + (dx)], (uint32_t)t[(dy) * BW + (dx) + 1], 0x5410)
-    const uint32_t cc = RING_E(0, 0);
+#define RING(dx, dy) orbx_pack_u16x2((uint32_t)t[(dy) * BW + (dx)], (uint32_t)t[(dy) * BW + (dx) + 1])
+    const uint32_t cc = RING(0, 0);
     uint32_t d[16];
-    d[0] = RING_E(0, 3);    d[1] = RING_O(1, 3);    d[2] = RING_E(2, 2);    d[3] = RING_O(3, 1);
-    d[4] = RING_O(3, 0);    d[5] = RING_O(3, -1);   d[6] = RING_E(2, -2);   d[7] = RING_O(1, -3);
-    d[8] = RING_E(0, -3);   d[9] = RING_O(-1, -3);  d[10] = RING_E(-2, -2); d[11] = RING_O(-3, -1);
-    d[12] = RING_O(-3, 0);  d[13] = RING_O(-3, 1);  d[14] = RING_E(-2, 2);  d[15] = RING_O(-1, 3);
-#undef RING_E
-#undef RING_O
-    return fast_network2(cc, d);
+    d[0] = RING(0, 3);    d[1] = RING(1, 3);    d[2] = RING(2, 2);    d[3] = RING(3, 1);
+    d[4] = RING(3, 0);    d[5] = RING(3, -1);   d[6] = RING(2, -2);   d[7] = RING(1, -3);
+    d[8] = RING(0, -3);   d[9] = RING(-1, -3);  d[10] = RING(-2, -2); d[11] = RING(-3, -1);
+    d[12] = RING(-3, 0);  d[13] = RING(-3, 1);  d[14] = RING(-2, 2);  d[15] = RING(-1, 3);
+#undef RING
+    return fast_network2(cc, d, thr);
 }
 
 // Pass-1 test of the 4 pixels of one tile word: bit 7 of byte i of the result is set if pixel i can be a corner at the
@@ -205,6 +236,8 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
         // bit 7 of each byte of f(x) = ((x & 0x7F..) + K) | x is set iff x > min(thr, 127): exact below 127, still
         // necessary above
         int ntAll = 0;
+        const uint32_t tp0 = orbx_smem_addr(tasks);
+        uint32_t tp = tp0;  // shared-memory address of the list's end
         {
             // survivors are appended step by step with ballots, so the task list is in row-major order: the 32 tasks of a
             // pass-2 trip come from one to three tile rows and their ring loads spread over the banks
@@ -227,22 +260,28 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
                 const bool f00 = (m0 & maskLo) != 0, f01 = (m0 & maskHi) != 0, f10 = (m1 & maskLo) != 0, f11 = (m1 & maskHi) != 0;
                 const unsigned b00 = __ballot_sync(0xffffffffu, f00), b01 = __ballot_sync(0xffffffffu, f01);
                 const unsigned b10 = __ballot_sync(0xffffffffu, f10), b11 = __ballot_sync(0xffffffffu, f11);
-                int n = ntAll;
-                if (f00) tasks[n + __popc(b00 & lt)] = (uint16_t)code;
-                n += __popc(b00);
-                if (f01) tasks[n + __popc(b01 & lt)] = (uint16_t)(code + 1);
-                n += __popc(b01);
-                if (f10) tasks[n + __popc(b10 & lt)] = (uint16_t)(code + cs);
-                n += __popc(b10);
-                if (f11) tasks[n + __popc(b11 & lt)] = (uint16_t)(code + cs + 1);
-                ntAll = n + __popc(b11);
+                // a word's two pairs go to adjacent list slots (lanes ascend with (row, word column)), so the list is sorted
+                // by (row, column): the non-zero list and the NMS maxima inherit the order and need no ranking at the end.
+                // The list position is a running shared-memory byte address; scaling and adding are multiply-adds (FMA pipe)
+                uint32_t a = orbx_mad(__popc(b00 & lt) + __popc(b01 & lt), 2u, tp);
+                if (f00) orbx_sts_u16(a, code);
+                if (f00) a += 2;
+                if (f01) orbx_sts_u16(a, code + 1);
+                tp = orbx_mad(__popc(b00) + __popc(b01), 2u, tp);
+                a = orbx_mad(__popc(b10 & lt) + __popc(b11 & lt), 2u, tp);
+                if (f10) orbx_sts_u16(a, code + cs);
+                if (f10) a += 2;
+                if (f11) orbx_sts_u16(a, code + cs + 1);
+                tp = orbx_mad(__popc(b10) + __popc(b11), 2u, tp);
                 code += 2 * cs;
             }
         }
+        ntAll = (int)((tp - tp0) >> 1);
         __syncwarp();  // task list complete
         // ---- pass 2: the min/max network on the surviving pairs
         const uint32_t thr2 = (uint32_t)thr * 0x10001u;
         int nzAll = 0;
+        uint32_t np = tp0;  // end of the non-zero list (it overwrites the task list from its start)
 #pragma unroll 1
         for (int g0 = 0; g0 < ntAll; g0 += 32) {
             const int g = g0 + lane;
@@ -251,21 +290,24 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
             if (g < ntAll) {
                 task = tasks[g];
                 const int y = task >> 8, c = 2 * (task & 255);
-                const uint32_t mp = fast_strength2_raw<BW>(reinterpret_cast<const uint8_t*>(tw0) + (y + 3) * BW + c);
+                const uint32_t mp = fast_strength2_raw<BW>(reinterpret_cast<const uint8_t*>(tw0) + (y + 3) * BW + c, (uint32_t)thr);
                 const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
                 const uint32_t inside = (ix >= 0 ? 0x0000FFFFu : 0u) | (ix + 1 < iw ? 0xFFFF0000u : 0u);
-                const uint32_t ms = (__vimax3_u16x2(mp, thr2, thr2) - thr2) & inside;  // m - thr per half, 0 = no corner
+                const uint32_t ms = mp & inside;  // m - thr per half, 0 = no corner
                 hit = ms != 0;
                 if (hit) *reinterpret_cast<uint16_t*>(smap + (y + 1) * SA + c + SD) = (uint16_t)__byte_perm(ms, 0, 0x4420);  // map is pre-zeroed
             }
             const unsigned bh = __ballot_sync(0xffffffffu, hit);
-            if (hit) nz[nzAll + __popc(bh & lt)] = (uint16_t)task;
-            nzAll += __popc(bh);
+            if (hit) orbx_sts_u16(orbx_mad(__popc(bh & lt), 2u, np), task);
+            np = orbx_mad(__popc(bh), 2u, np);
         }
+        nzAll = (int)((np - tp0) >> 1);
         __syncwarp();  // strength map and list complete; the raw tile is dead from here (kept[] takes its place)
 
         // ---- NMS over the non-zero pairs: strict maximum over the 8 neighbours in the strength map
         nkept = 0;
+        const uint32_t kp0 = orbx_smem_addr(kept);
+        uint32_t kp = kp0;
 #pragma unroll 1
         for (int g0 = 0; g0 < nzAll; g0 += 32) {
             const int g = g0 + lane;
@@ -294,16 +336,20 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
             // (the first trip overwrites the head of the dead tile only after every lane has read its map words: the map
             // and the lists live behind the tile, so kept[] never aliases what this loop still reads)
             const unsigned b0 = __ballot_sync(0xffffffffu, k0), b1 = __ballot_sync(0xffffffffu, k1);
-            if (k0) kept[nkept + __popc(b0 & lt)] = e0;
-            if (k1) kept[nkept + __popc(b0) + __popc(b1 & lt)] = e1;
-            nkept += __popc(b0) + __popc(b1);
+            uint32_t a = orbx_mad(__popc(b0 & lt) + __popc(b1 & lt), 4u, kp);  // a pair's two pixels side by side: kept[] stays row-major
+            if (k0) orbx_sts_u32(a, e0);
+            if (k0) a += 4;
+            if (k1) orbx_sts_u32(a, e1);
+            kp = orbx_mad(__popc(b0) + __popc(b1), 4u, kp);
         }
+        nkept = (int)((kp - kp0) >> 2);
         __syncwarp();  // publishes kept[]
         if (nkept > 0 || attempt == 1 || tmin >= thr) break;
         thr = tmin;  // :814 FAST(iniTh) came back empty: once more with minTh
     }
 
-    // ---- ordered emission: rank of a maximum = number of maxima with a smaller row-major key
+    // ---- emission: kept[] is already in row-major order (the reference's candidate order inside a cell) — the task list is
+    // built sorted, the non-zero list and the maxima are order-preserving compactions of it
     const uint32_t slot0 = L.slotBase + (uint32_t)(cellId - L.cellBase) * L.slotCap;
     uint32_t* out = p.cellKp + (size_t)img * p.slotTotal + slot0;
     if (lane == 0) *cntOut = nkept;
@@ -311,9 +357,7 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
     for (int i = lane; i < nkept; i += 32) {
         const uint32_t e = kept[i];
         const int key = e & 0xFFFFu, m = e >> 16;
-        int rank = 0;
-        for (int j = 0; j < nkept; ++j) rank += (int)(kept[j] & 0xFFFFu) < key;
-        out[rank] = (uint32_t)((key & 63) + 3) | ((uint32_t)((key >> 6) + 3) << 8) | ((uint32_t)(m - 1) << 16);
+        out[i] = (uint32_t)((key & 63) + 3) | ((uint32_t)((key >> 6) + 3) << 8) | ((uint32_t)(m - 1) << 16);
     }
     __syncwarp();  // every lane is done with kept[] (= the tile) before the next cell's TMA lands in it
     }
