@@ -33,7 +33,7 @@
 //     and uses packed column maxima; the list of non-zero pairs and the list of maxima are order-preserving compactions of
 //     the sorted task list, so the maxima come out in the reference's row-major order and are emitted as they stand (the
 //     rank computation of the earlier version — one compare per pair of maxima — is gone);
-//   * one warp per cell, four cells per CTA, long-lived warps: see the kernel.
+//   * one warp per cell, one cell per CTA at a time, long-lived warps: see the kernel.
 #include "engine.h"
 #include "orbx_dev.cuh"
 #include "orbx_tma.cuh"
@@ -52,6 +52,15 @@ __device__ __forceinline__ uint32_t orbx_pack_u16x2(uint32_t lo, uint32_t hi)
     uint32_t r;
     asm("mad.lo.u32 %0, %1, 65536, %2;" : "=r"(r) : "r"(hi), "r"(lo));
     return r;
+}
+// one byte from shared memory at a compile-time offset (explicit, so that two neighbouring bytes stay two loads: merged into
+// one 16-bit load they need a PRMT to come apart, and the ALU pipe is the one without room)
+template <int OFF>
+__device__ __forceinline__ uint32_t orbx_lds_u8(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(OFF));
+    return v;
 }
 __device__ __forceinline__ uint32_t orbx_mad(uint32_t a, uint32_t b, uint32_t c)
 {
@@ -117,7 +126,8 @@ __device__ __forceinline__ uint32_t fast_network2(uint32_t cc, const uint32_t (&
 template <int BW>
 __device__ __forceinline__ uint32_t fast_strength2_raw(const uint8_t* t, uint32_t thr)
 {
-#define RING(dx, dy) orbx_pack_u16x2((uint32_t)t[(dy) * BW + (dx)], (uint32_t)t[(dy) * BW + (dx) + 1])
+#define RING(dx, dy) orbx_pack_u16x2(orbx_lds_u8<(dy) * BW + (dx)>(ta), orbx_lds_u8<(dy) * BW + (dx) + 1>(ta))
+    const uint32_t ta = orbx_smem_addr(t);
     const uint32_t cc = RING(0, 0);
     uint32_t d[16];
     d[0] = RING(0, 3);    d[1] = RING(1, 3);    d[2] = RING(2, 2);    d[3] = RING(3, 1);
@@ -137,26 +147,29 @@ __device__ __forceinline__ uint32_t fast_pretest4(const uint32_t* tw, uint32_t K
     const uint32_t up = tw[-3 * (BW / 4)], dn = tw[3 * (BW / 4)];
     const uint32_t lf = __funnelshift_r(wp, w, 8), rt = __funnelshift_r(w, wn, 24);  // columns -3 / +3
     const uint32_t a0 = __vabsdiffu4(dn, w), a8 = __vabsdiffu4(up, w), a4 = __vabsdiffu4(rt, w), a12 = __vabsdiffu4(lf, w);
-    const uint32_t f0 = ((a0 & 0x7F7F7F7Fu) + K) | a0, f8 = ((a8 & 0x7F7F7F7Fu) + K) | a8;
-    const uint32_t f4 = ((a4 & 0x7F7F7F7Fu) + K) | a4, f12 = ((a12 & 0x7F7F7F7Fu) + K) | a12;
+    // bit 7 of byte i of (a + K) | a, K = 127 - t in every byte, is set iff a_i > t — or a_i == t with a carry out of byte
+    // i - 1 (a_{i-1} >= 129 + t): a byte that overflows has its own bit 7 restored by "| a" (it is >= 129), and the carry
+    // it sends up can only turn a_i == t into a pass. The test stays NECESSARY (pass 2 is exact), so the four masking ANDs
+    // of the carry-free form ((a & 0x7F7F7F7F) + K) | a are not needed: 8 ALU-pipe operations less per trip
+    const uint32_t f0 = (a0 + K) | a0, f8 = (a8 + K) | a8;
+    const uint32_t f4 = (a4 + K) | a4, f12 = (a12 + K) | a12;
     return (f0 | f8) & (f4 | f12);
 }
 
 // c_recip[n] = ceil(65536 / n): floor(t / n) = (t * c_recip[n]) >> 16 exactly while t * n < 65536 (here t <= 128, n <= 31)
 __constant__ uint32_t c_recip[32] = {0, 65536, 32768, 21846, 16384, 13108, 10923, 9363, 8192, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4096, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115};
 
-// One WARP per cell, CELLS cells per CTA. A cell used to belong to a 64-thread CTA; the fixed work per (warp, cell) —
-// prologue, thread mapping, list flush, emission, ~300 of the ~1060 warp instructions a warp spent per cell — is now paid
-// once per cell instead of twice, there is no CTA barrier (only __syncwarp), and the list counters are warp-uniform
-// registers (no shared atomics). CELLS warps share a CTA only for occupancy (a one-warp CTA caps the SM at 32 warps, less
-// with 7.3 KB of shared memory each); they never talk to each other.
+// One WARP per cell, CELLS cells per CTA (default 1). A cell used to belong to a 64-thread CTA; the fixed work per
+// (warp, cell) — prologue, thread mapping, list flush, emission — is paid once per cell, there is no CTA barrier (only
+// __syncwarp), and the list counters are warp-uniform. Warps never talk to each other; with CELLS = 1 the compiler can
+// prove which values are warp-uniform (everything derived from blockIdx and the cell record) and keeps them on the uniform
+// datapath; the SM then holds 28 one-warp CTAs of 7296 B (KITTI cells), the same 28 warps as seven 4-warp CTAs.
 template <int SA, int CELLS>
 __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap,
                                                                     int sliceBytes)
 {
     constexpr int BW = SA == 48 ? 80 : 112;
     extern __shared__ __align__(128) uint8_t fast_smem[];
-    __shared__ __align__(8) uint64_t bars[CELLS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint8_t* T = fast_smem + (size_t)warp * sliceBytes;  // raw box [rhMax][BW]
     // strength map: ONE BYTE per pixel (m - thr <= 254). As u16 it cost 2 KB more per warp and capped the SM at 6 CTAs (24
@@ -166,7 +179,9 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
     // pairs with a non-zero strength: written over the task list while pass 2 consumes it (entry k of nz is written in the
     // trip that read tasks[32*(trip)..], and k never runs ahead of what has been read)
     uint16_t* nz = tasks;
-    uint64_t* bar = bars + warp;
+    // the warp's mbarrier lives in the last 8 bytes of its slice (no static shared memory: with one warp per CTA the slice of
+    // a KITTI cell, 7296 B, then leaves room for exactly 28 CTAs per SM)
+    uint64_t* bar = reinterpret_cast<uint64_t*>(T + sliceBytes - 8);
     if (lane == 0) {
         orbx_mbar_init(bar, 1);
         orbx_fence_mbar_init();
@@ -233,8 +248,8 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
         // two ADJACENT compass points (0,4,8,12), so a corner needs (|d0|>t or |d8|>t) and (|d4|>t or |d12|>t). Four
         // VABSDIFF4 + a SWAR byte compare test 4 pixels at once (fast_pretest4). The surviving pixel PAIRS (aligned to even
         // tile columns) are appended step by step with ballots: no atomics, and the list comes out in row-major order.
-        // bit 7 of each byte of f(x) = ((x & 0x7F..) + K) | x is set iff x > min(thr, 127): exact below 127, still
-        // necessary above
+        // bit 7 of each byte of f(x) = (x + K) | x is set if x > min(thr, 127) (fast_pretest4): exact below 127 up to a rare
+        // carry, still necessary above
         int ntAll = 0;
         const uint32_t tp0 = orbx_smem_addr(tasks);
         uint32_t tp = tp0;  // shared-memory address of the list's end
@@ -246,8 +261,32 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
             const uint32_t maskLo = (vmask & 1u) ? 0x00008080u : 0u, maskHi = (vmask & 2u) ? 0x80800000u : 0u;
             uint32_t code = (uint32_t)(pyq * 256 + 2 * pj);
             const uint32_t cs = (uint32_t)pStep << 8;
+            // one step = the two pair flags of the lane's word. A word's two pairs go to adjacent list slots (lanes ascend
+            // with (row, word column)), so the list is sorted by (row, column): the non-zero list and the NMS maxima inherit
+            // the order and need no ranking at the end. The list position is a running shared-memory byte address; scaling
+            // and adding are multiply-adds (FMA pipe)
+            auto append = [&](uint32_t m, uint32_t cd) {
+                const bool fl = (m & maskLo) != 0, fh = (m & maskHi) != 0;
+                const unsigned bl = __ballot_sync(0xffffffffu, fl), bh = __ballot_sync(0xffffffffu, fh);
+                uint32_t a = orbx_mad(__popc(bl & lt) + __popc(bh & lt), 2u, tp);
+                if (fl) orbx_sts_u16(a, cd);
+                if (fl) a += 2;
+                if (fh) orbx_sts_u16(a, cd + 1);
+                tp = orbx_mad(__popc(bl) + __popc(bh), 2u, tp);
+            };
+            // two steps per trip. Trips whose rows all lie inside the interior run without row predicates (idle lanes —
+            // 32 is not a multiple of every row length — read words of their own slice and are masked by maskLo / maskHi);
+            // the last, partial trip is guarded
+            int y0s = 0;
 #pragma unroll 1
-            for (int y0s = 0; y0s < ih; y0s += 2 * pStep) {  // two steps per trip (uniform trip count)
+            for (; y0s + 2 * pStep <= ih; y0s += 2 * pStep) {
+                const uint32_t m0 = fast_pretest4<BW>(tw, K), m1 = fast_pretest4<BW>(tw + pStep * (BW / 4), K);
+                tw += 2 * pStep * (BW / 4);
+                append(m0, code);
+                append(m1, code + cs);
+                code += 2 * cs;
+            }
+            if (y0s < ih) {
                 const bool p0 = vmask && y0s + pyq < ih, p1 = vmask && y0s + pStep + pyq < ih;
                 uint32_t m0 = 0, m1 = 0;
                 if (p0) {
@@ -256,24 +295,8 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
                     m1 = fast_pretest4<BW>(tw1, K);
                     m1 = p1 ? m1 : 0u;
                 }
-                tw += 2 * pStep * (BW / 4);
-                const bool f00 = (m0 & maskLo) != 0, f01 = (m0 & maskHi) != 0, f10 = (m1 & maskLo) != 0, f11 = (m1 & maskHi) != 0;
-                const unsigned b00 = __ballot_sync(0xffffffffu, f00), b01 = __ballot_sync(0xffffffffu, f01);
-                const unsigned b10 = __ballot_sync(0xffffffffu, f10), b11 = __ballot_sync(0xffffffffu, f11);
-                // a word's two pairs go to adjacent list slots (lanes ascend with (row, word column)), so the list is sorted
-                // by (row, column): the non-zero list and the NMS maxima inherit the order and need no ranking at the end.
-                // The list position is a running shared-memory byte address; scaling and adding are multiply-adds (FMA pipe)
-                uint32_t a = orbx_mad(__popc(b00 & lt) + __popc(b01 & lt), 2u, tp);
-                if (f00) orbx_sts_u16(a, code);
-                if (f00) a += 2;
-                if (f01) orbx_sts_u16(a, code + 1);
-                tp = orbx_mad(__popc(b00) + __popc(b01), 2u, tp);
-                a = orbx_mad(__popc(b10 & lt) + __popc(b11 & lt), 2u, tp);
-                if (f10) orbx_sts_u16(a, code + cs);
-                if (f10) a += 2;
-                if (f11) orbx_sts_u16(a, code + cs + 1);
-                tp = orbx_mad(__popc(b10) + __popc(b11), 2u, tp);
-                code += 2 * cs;
+                append(m0, code);
+                append(m1, code + cs);
             }
         }
         ntAll = (int)((tp - tp0) >> 1);
@@ -284,19 +307,17 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
         uint32_t np = tp0;  // end of the non-zero list (it overwrites the task list from its start)
 #pragma unroll 1
         for (int g0 = 0; g0 < ntAll; g0 += 32) {
-            const int g = g0 + lane;
-            bool hit = false;
-            int task = 0;
-            if (g < ntAll) {
-                task = tasks[g];
-                const int y = task >> 8, c = 2 * (task & 255);
-                const uint32_t mp = fast_strength2_raw<BW>(reinterpret_cast<const uint8_t*>(tw0) + (y + 3) * BW + c, (uint32_t)thr);
-                const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
-                const uint32_t inside = (ix >= 0 ? 0x0000FFFFu : 0u) | (ix + 1 < iw ? 0xFFFF0000u : 0u);
-                const uint32_t ms = mp & inside;  // m - thr per half, 0 = no corner
-                hit = ms != 0;
-                if (hit) *reinterpret_cast<uint16_t*>(smap + (y + 1) * SA + c + SD) = (uint16_t)__byte_perm(ms, 0, 0x4420);  // map is pre-zeroed
-            }
+            // no branch around the body: lanes past the end of the list repeat its last task and drop the result (the
+            // branch made the flag a byte in a register, set and tested on both sides of the reconvergence point)
+            const bool valid = g0 + lane < ntAll;
+            const int task = tasks[min(g0 + lane, ntAll - 1)];
+            const int y = task >> 8, c = 2 * (task & 255);
+            const uint32_t mp = fast_strength2_raw<BW>(reinterpret_cast<const uint8_t*>(tw0) + (y + 3) * BW + c, (uint32_t)thr);
+            const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
+            const uint32_t inside = (ix >= 0 ? 0x0000FFFFu : 0u) | (ix + 1 < iw ? 0xFFFF0000u : 0u);
+            const uint32_t ms = mp & inside;  // m - thr per half, 0 = no corner
+            const bool hit = valid && ms != 0;
+            if (hit) *reinterpret_cast<uint16_t*>(smap + (y + 1) * SA + c + SD) = (uint16_t)__byte_perm(ms, 0, 0x4420);  // map is pre-zeroed
             const unsigned bh = __ballot_sync(0xffffffffu, hit);
             if (hit) orbx_sts_u16(orbx_mad(__popc(bh & lt), 2u, np), task);
             np = orbx_mad(__popc(bh), 2u, np);
@@ -310,29 +331,24 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
         uint32_t kp = kp0;
 #pragma unroll 1
         for (int g0 = 0; g0 < nzAll; g0 += 32) {
-            const int g = g0 + lane;
-            bool k0 = false, k1 = false;
-            uint32_t e0 = 0, e1 = 0;
-            if (g < nzAll) {
-                const int task = nz[g], y = task >> 8, cc = 2 * (task & 255);
-                const uint8_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair (even byte address)
+            const bool valid = g0 + lane < nzAll;  // (lanes past the end repeat the last entry, as in pass 2)
+            const int task = nz[min(g0 + lane, nzAll - 1)], y = task >> 8, cc = 2 * (task & 255);
+            const uint8_t* c = smap + (y + 1) * SA + cc + SD;  // centre pair (even byte address)
 #define MAP2(q) __byte_perm((uint32_t)*reinterpret_cast<const uint16_t*>(q), 0, 0x4140)  /* two map bytes -> u16x2 */
-                const uint32_t mm = MAP2(c);
-                const uint32_t u0 = MAP2(c - SA - 2), u1 = MAP2(c - SA), u2 = MAP2(c - SA + 2);
-                const uint32_t l0 = MAP2(c - 2), l2 = MAP2(c + 2);
-                const uint32_t d0 = MAP2(c + SA - 2), d1 = MAP2(c + SA), d2 = MAP2(c + SA + 2);
+            const uint32_t mm = MAP2(c);
+            const uint32_t u0 = MAP2(c - SA - 2), u1 = MAP2(c - SA), u2 = MAP2(c - SA + 2);
+            const uint32_t l0 = MAP2(c - 2), l2 = MAP2(c + 2);
+            const uint32_t d0 = MAP2(c + SA - 2), d1 = MAP2(c + SA), d2 = MAP2(c + SA + 2);
 #undef MAP2
-                const uint32_t cm0 = __vimax3_u16x2(u0, l0, d0), cm1 = __vimax3_u16x2(u1, mm, d1), cm2 = __vimax3_u16x2(u2, l2, d2);
-                const uint32_t ud = __vimax3_u16x2(u1, d1, d1);
-                const int m0 = mm & 0xFFFFu, m1 = mm >> 16;
-                const int n0 = max(max((int)(cm0 >> 16), (int)(cm1 >> 16)), (int)(ud & 0xFFFFu));
-                const int n1 = max(max((int)(cm1 & 0xFFFFu), (int)(cm2 & 0xFFFFu)), (int)(ud >> 16));
-                const int ix = cc - ca0;
-                k0 = m0 > n0;
-                k1 = m1 > n1;
-                e0 = (uint32_t)(y * 64 + ix) | ((uint32_t)(m0 + thr) << 16);
-                e1 = (uint32_t)(y * 64 + ix + 1) | ((uint32_t)(m1 + thr) << 16);
-            }
+            const uint32_t cm0 = __vimax3_u16x2(u0, l0, d0), cm1 = __vimax3_u16x2(u1, mm, d1), cm2 = __vimax3_u16x2(u2, l2, d2);
+            const uint32_t ud = __vimax3_u16x2(u1, d1, d1);
+            const int m0 = mm & 0xFFFFu, m1 = mm >> 16;
+            const int n0 = max(max((int)(cm0 >> 16), (int)(cm1 >> 16)), (int)(ud & 0xFFFFu));
+            const int n1 = max(max((int)(cm1 & 0xFFFFu), (int)(cm2 & 0xFFFFu)), (int)(ud >> 16));
+            const int ix = cc - ca0;
+            const bool k0 = valid && m0 > n0, k1 = valid && m1 > n1;
+            const uint32_t e0 = (uint32_t)(y * 64 + ix) | ((uint32_t)(m0 + thr) << 16);
+            const uint32_t e1 = (uint32_t)(y * 64 + ix + 1) | ((uint32_t)(m1 + thr) << 16);
             // (the first trip overwrites the head of the dead tile only after every lane has read its map words: the map
             // and the lists live behind the tile, so kept[] never aliases what this loop still reads)
             const unsigned b0 = __ballot_sync(0xffffffffu, k0), b1 = __ballot_sync(0xffffffffu, k1);
@@ -385,10 +401,13 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
     const int iwMax = (sa == 48 ? 40 : 72) - 6, ihMax = rhMax - 6;
     const int listCap = (((iwMax + 4) / 2) * ihMax + 7) & ~7;
     // shared memory of one cell: tile + strength map + one list (the non-zero pairs overwrite the tasks)
-    const int slice = (int)(((size_t)((rhMax * boxW + 127) & ~127) + (size_t)(rhMax - 4) * sa + (size_t)listCap * 2 + 127) & ~(size_t)127);
-    // cells (= warps) per CTA: tuning key fast_cells = 2 / 4 / 8 (tools/fast_cells_sweep.sh: 4 is best, 8 loses a third)
+    const int slice = (int)(((size_t)((rhMax * boxW + 127) & ~127) + (size_t)(rhMax - 4) * sa + (size_t)listCap * 2 + 8 /* mbarrier */ + 127) & ~(size_t)127);
+    // cells (= warps) per CTA: tuning key fast_cells = 1 / 2 / 4 / 8. One warp per CTA is the default: everything that depends
+    // on the cell alone is then provably warp-uniform for the compiler (uniform registers and the uniform datapath instead of
+    // ALU-pipe instructions: 55 registers instead of 70, no divergence handling around the ballots) — 1.154 ms per 512 KITTI
+    // images against 1.190 for 2 or 4 cells per CTA; 8 loses a third (tools/fast_cells_sweep.sh)
     int cellsPerCta = orbx_tune(ORBX_TUNE_FAST_CELLS);
-    if (cellsPerCta != 2 && cellsPerCta != 4 && cellsPerCta != 8) cellsPerCta = 4;
+    if (cellsPerCta != 1 && cellsPerCta != 2 && cellsPerCta != 4 && cellsPerCta != 8) cellsPerCta = 1;
     // CTAs launched per resident CTA slot (tuning key fast_grid_mult). 1 = fully persistent with static striding, which loses
     // to its own tail (cells differ in cost: 1.54 ms per 512 KITTI images); 16 lets the hardware scheduler balance
     // ~9-cell work packets (1.37 ms); one cell per warp pays the CTA turnover (1.43 ms): tools/fast_grid_sweep.sh
@@ -417,9 +436,9 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
                                                                                           (const CUtensorMap*)levelMaps, rhMax, listCap, slice); \
     }
     if (sa == 48) {
-        if (cellsPerCta == 2) FAST_LAUNCH(48, 2) else if (cellsPerCta == 4) FAST_LAUNCH(48, 4) else FAST_LAUNCH(48, 8)
+        if (cellsPerCta == 1) FAST_LAUNCH(48, 1) else if (cellsPerCta == 2) FAST_LAUNCH(48, 2) else if (cellsPerCta == 4) FAST_LAUNCH(48, 4) else FAST_LAUNCH(48, 8)
     } else {
-        if (cellsPerCta == 2) FAST_LAUNCH(80, 2) else if (cellsPerCta == 4) FAST_LAUNCH(80, 4) else FAST_LAUNCH(80, 8)
+        if (cellsPerCta == 1) FAST_LAUNCH(80, 1) else if (cellsPerCta == 2) FAST_LAUNCH(80, 2) else if (cellsPerCta == 4) FAST_LAUNCH(80, 4) else FAST_LAUNCH(80, 8)
     }
 #undef FAST_LAUNCH
 }
