@@ -72,6 +72,7 @@ __device__ __forceinline__ void orbx_sts_u16(uint32_t addr, uint32_t v)
 {
     asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)v) : "memory");
 }
+__device__ __forceinline__ void orbx_sts_u8(uint32_t addr, uint32_t v) { asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
 __device__ __forceinline__ void orbx_sts_u32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
 
 // Corner strengths ABOVE thr (0 = not a corner at thr) of two horizontally adjacent pixels from the 17 u16x2 vectors cc
@@ -141,7 +142,7 @@ __device__ __forceinline__ uint32_t fast_strength2_raw(const uint8_t* t, uint32_
 // Pass-1 test of the 4 pixels of one tile word: bit 7 of byte i of the result is set if pixel i can be a corner at the
 // threshold behind K (see the kernel): (|d0|>t or |d8|>t) and (|d4|>t or |d12|>t) on the compass points
 template <int BW>
-__device__ __forceinline__ uint32_t fast_pretest4(const uint32_t* tw, uint32_t K)
+__device__ __forceinline__ uint32_t fast_pretest4(const uint32_t* tw, uint32_t K, uint32_t one)
 {
     const uint32_t w = tw[0], wn = tw[1], wp = tw[-1];
     const uint32_t up = tw[-3 * (BW / 4)], dn = tw[3 * (BW / 4)];
@@ -151,8 +152,10 @@ __device__ __forceinline__ uint32_t fast_pretest4(const uint32_t* tw, uint32_t K
     // i - 1 (a_{i-1} >= 129 + t): a byte that overflows has its own bit 7 restored by "| a" (it is >= 129), and the carry
     // it sends up can only turn a_i == t into a pass. The test stays NECESSARY (pass 2 is exact), so the four masking ANDs
     // of the carry-free form ((a & 0x7F7F7F7F) + K) | a are not needed: 8 ALU-pipe operations less per trip
-    const uint32_t f0 = (a0 + K) | a0, f8 = (a8 + K) | a8;
-    const uint32_t f4 = (a4 + K) | a4, f12 = (a12 + K) | a12;
+    // ('one' is the kernel argument 1: a + K as the multiply-add a * one + K stays on the FMA pipe whatever ptxas thinks of
+    // the pipe balance — as plain adds they came out as ALU-pipe VIADDs in some builds and as IMAD.IADDs in others)
+    const uint32_t f0 = orbx_mad(a0, one, K) | a0, f8 = orbx_mad(a8, one, K) | a8;
+    const uint32_t f4 = orbx_mad(a4, one, K) | a4, f12 = orbx_mad(a12, one, K) | a12;
     return (f0 | f8) & (f4 | f12);
 }
 
@@ -166,7 +169,7 @@ __constant__ uint32_t c_recip[32] = {0, 65536, 32768, 21846, 16384, 13108, 10923
 // datapath; the SM then holds 28 one-warp CTAs of 7296 B (KITTI cells), the same 28 warps as seven 4-warp CTAs.
 template <int SA, int CELLS>
 __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, const OrbxCell* cells, const CUtensorMap* maps, int rhMax, int listCap,
-                                                                    int sliceBytes)
+                                                                    int sliceBytes, uint32_t one)
 {
     constexpr int BW = SA == 48 ? 80 : 112;
     extern __shared__ __align__(128) uint8_t fast_smem[];
@@ -280,30 +283,30 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
             int y0s = 0;
 #pragma unroll 1
             for (; y0s + 2 * pStep <= ih; y0s += 2 * pStep) {
-                const uint32_t m0 = fast_pretest4<BW>(tw, K), m1 = fast_pretest4<BW>(tw + pStep * (BW / 4), K);
+                const uint32_t m0 = fast_pretest4<BW>(tw, K, one), m1 = fast_pretest4<BW>(tw + pStep * (BW / 4), K, one);
                 tw += 2 * pStep * (BW / 4);
                 append(m0, code);
                 append(m1, code + cs);
                 code += 2 * cs;
             }
-            if (y0s < ih) {
-                const bool p0 = vmask && y0s + pyq < ih, p1 = vmask && y0s + pStep + pyq < ih;
-                uint32_t m0 = 0, m1 = 0;
-                if (p0) {
-                    const uint32_t* tw1 = p1 ? tw + pStep * (BW / 4) : tw;
-                    m0 = fast_pretest4<BW>(tw, K);
-                    m1 = fast_pretest4<BW>(tw1, K);
-                    m1 = p1 ? m1 : 0u;
-                }
+            if (y0s < ih) {  // the partial trip: one or two guarded steps (warp-uniform choice)
+                const bool p0 = vmask && y0s + pyq < ih;
+                uint32_t m0 = 0;
+                if (p0) m0 = fast_pretest4<BW>(tw, K, one);
                 append(m0, code);
-                append(m1, code + cs);
+                if (y0s + pStep < ih) {
+                    const bool p1 = vmask && y0s + pStep + pyq < ih;
+                    uint32_t m1 = 0;
+                    if (p1) m1 = fast_pretest4<BW>(tw + pStep * (BW / 4), K, one);
+                    append(m1, code + cs);
+                }
             }
         }
         ntAll = (int)((tp - tp0) >> 1);
         __syncwarp();  // task list complete
         // ---- pass 2: the min/max network on the surviving pairs
-        const uint32_t thr2 = (uint32_t)thr * 0x10001u;
         int nzAll = 0;
+        const uint32_t smapA = orbx_smem_addr(smap) + SD;  // shared-window address of strength-map column 0 of row -1
         uint32_t np = tp0;  // end of the non-zero list (it overwrites the task list from its start)
 #pragma unroll 1
         for (int g0 = 0; g0 < ntAll; g0 += 32) {
@@ -313,16 +316,28 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
             const int task = tasks[min(g0 + lane, ntAll - 1)];
             const int y = task >> 8, c = 2 * (task & 255);
             const uint32_t mp = fast_strength2_raw<BW>(reinterpret_cast<const uint8_t*>(tw0) + (y + 3) * BW + c, (uint32_t)thr);
-            const int ix = c - ca0;  // interior column of pixel 0 (may be -1; pixel 1 may be iw)
-            const uint32_t inside = (ix >= 0 ? 0x0000FFFFu : 0u) | (ix + 1 < iw ? 0xFFFF0000u : 0u);
-            const uint32_t ms = mp & inside;  // m - thr per half, 0 = no corner
-            const bool hit = valid && ms != 0;
-            if (hit) *reinterpret_cast<uint16_t*>(smap + (y + 1) * SA + c + SD) = (uint16_t)__byte_perm(ms, 0, 0x4420);  // map is pre-zeroed
+            // mp = m - thr per half, 0 = no corner. A pair at the edge of the interior has one pixel outside it (interior
+            // column -1 or iw); its strength is cleared from the map after the loop instead of being masked here
+            const bool hit = valid && mp != 0;
+            if (hit) orbx_sts_u16(smapA + (y + 1) * SA + c, __byte_perm(mp, 0, 0x4420));  // map is pre-zeroed
             const unsigned bh = __ballot_sync(0xffffffffu, hit);
             if (hit) orbx_sts_u16(orbx_mad(__popc(bh & lt), 2u, np), task);
             np = orbx_mad(__popc(bh), 2u, np);
         }
         nzAll = (int)((np - tp0) >> 1);
+        if (nzAll > 0 && ((ca0 | iw) & 1)) {
+            // pixel pairs are aligned to even tile columns: with an odd first interior column the pair in front of it holds
+            // interior column -1, with an odd end the last pair holds column iw. cv::FAST does not look at them: their map
+            // entries are zeroed (as neighbours they count 0, as centres they cannot win)
+            __syncwarp();
+            const bool oddStart = ca0 & 1, oddEnd = (ca0 + iw) & 1;
+#pragma unroll 1
+            for (int r = lane; r < ih; r += 32) {
+                const uint32_t a = smapA + (r + 1) * SA + ca0;
+                if (oddStart) orbx_sts_u8(a - 1, 0);
+                if (oddEnd) orbx_sts_u8(a + iw, 0);
+            }
+        }
         __syncwarp();  // strength map and list complete; the raw tile is dead from here (kept[] takes its place)
 
         // ---- NMS over the non-zero pairs: strict maximum over the 8 neighbours in the strength map
@@ -342,13 +357,16 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
 #undef MAP2
             const uint32_t cm0 = __vimax3_u16x2(u0, l0, d0), cm1 = __vimax3_u16x2(u1, mm, d1), cm2 = __vimax3_u16x2(u2, l2, d2);
             const uint32_t ud = __vimax3_u16x2(u1, d1, d1);
-            const int m0 = mm & 0xFFFFu, m1 = mm >> 16;
-            const int n0 = max(max((int)(cm0 >> 16), (int)(cm1 >> 16)), (int)(ud & 0xFFFFu));
-            const int n1 = max(max((int)(cm1 & 0xFFFFu), (int)(cm2 & 0xFFFFu)), (int)(ud >> 16));
-            const int ix = cc - ca0;
-            const bool k0 = valid && m0 > n0, k1 = valid && m1 > n1;
-            const uint32_t e0 = (uint32_t)(y * 64 + ix) | ((uint32_t)(m0 + thr) << 16);
-            const uint32_t e1 = (uint32_t)(y * 64 + ix + 1) | ((uint32_t)(m1 + thr) << 16);
+            // neighbourhood maxima of both pixels, packed: n0 = max(cm0.hi, cm1.hi, ud.lo), n1 = max(cm2.lo, cm1.lo, ud.hi)
+            const uint32_t nn = __vimax3_u16x2(__byte_perm(cm0, cm2, 0x5432), __byte_perm(cm1, 0, 0x1032), ud);
+            // m > n per half  <=>  max(m, n + 1) == m  (n + 1 <= 255: no carry between the halves)
+            const uint32_t n1 = nn + 0x10001u;
+            const uint32_t ge = __vimax3_u16x2(mm, n1, n1) ^ mm;
+            const bool k0 = valid && (ge & 0x0000FFFFu) == 0, k1 = valid && (ge & 0xFFFF0000u) == 0;
+            // key | (m + thr) << 16 for both pixels; mm << 16 keeps the low half only
+            const uint32_t kt = (uint32_t)(y * 64 + cc - ca0) + ((uint32_t)thr << 16);
+            const uint32_t e0 = orbx_mad(mm, 65536u, kt);
+            const uint32_t e1 = (mm & 0xFFFF0000u) + kt + 1;
             // (the first trip overwrites the head of the dead tile only after every lane has read its map words: the map
             // and the lists live behind the tile, so kept[] never aliases what this loop still reads)
             const unsigned b0 = __ballot_sync(0xffffffffu, k0), b1 = __ballot_sync(0xffffffffu, k1);
@@ -433,7 +451,7 @@ void orbx_launch_fast(const OrbxParams& p, const void* cellTable, const void* le
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, orbx_fast_kernel<SA_, C_>, C_ * 32, smem);                         \
         const long long cap = (long long)(perSm > 0 ? perSm : 1) * smCount * gridMult;                                           \
         orbx_fast_kernel<SA_, C_><<<wanted < cap ? wanted : (int)cap, C_ * 32, smem, s>>>(p, (const OrbxCell*)cellTable,         \
-                                                                                          (const CUtensorMap*)levelMaps, rhMax, listCap, slice); \
+                                                                                          (const CUtensorMap*)levelMaps, rhMax, listCap, slice, 1u); \
     }
     if (sa == 48) {
         if (cellsPerCta == 1) FAST_LAUNCH(48, 1) else if (cellsPerCta == 2) FAST_LAUNCH(48, 2) else if (cellsPerCta == 4) FAST_LAUNCH(48, 4) else FAST_LAUNCH(48, 8)
