@@ -184,9 +184,15 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
     uint16_t* nz = tasks;
     // the warp's mbarrier lives in the last 8 bytes of its slice (no static shared memory: with one warp per CTA the slice of
     // a KITTI cell, 7296 B, then leaves room for exactly 28 CTAs per SM)
-    uint64_t* bar = reinterpret_cast<uint64_t*>(T + sliceBytes - 8);
+    // shared-window addresses of the slice's parts, converted once (the lists, the map stores, the barrier and the TMA
+    // destination are addressed through them)
+    // (through an opaque move: otherwise the compiler re-derives the window base — S2R SR_CgaCtaId, 0x400, LEA — at every use)
+    uint32_t sT;
+    asm volatile("mov.u32 %0, %1;" : "=r"(sT) : "r"(orbx_smem_addr(T)));
+    const uint32_t sMap = sT + (uint32_t)(smap - T), sTasks = sMap + (uint32_t)((rhMax - 4) * SA);
+    const uint32_t bar = sT + (uint32_t)sliceBytes - 8;
     if (lane == 0) {
-        orbx_mbar_init(bar, 1);
+        orbx_mbar_init_a(bar, 1);
         orbx_fence_mbar_init();
     }
     __syncwarp();  // barrier initialised before anybody polls it
@@ -211,16 +217,16 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
     }
     if (lane == 0) {
         orbx_fence_mbar_init();  // the previous cell's kept[] (generic-proxy writes into the tile) before the TMA write
-        orbx_mbar_expect_tx(bar, rhMax * BW);
-        orbx_tma_load_3d(T, maps + cell.level, cell.x0 & ~15, cell.y0, img + p.imgBase, bar);
+        orbx_mbar_expect_tx_a(bar, rhMax * BW);
+        orbx_tma_load_3d_a(sT, maps + cell.level, cell.x0 & ~15, cell.y0, img + p.imgBase, bar);
     }
     {
-        uint4* z = reinterpret_cast<uint4*>(smap);
         const int nzero = (ih + 2) * (SA / 16);
-        for (int i = lane; i < nzero; i += 32) z[i] = make_uint4(0, 0, 0, 0);
+#pragma unroll 1
+        for (int i = lane; i < nzero; i += 32) asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(sMap + 16u * i), "r"(0) : "memory");
     }
     __syncwarp();
-    orbx_mbar_wait(bar, phase);
+    orbx_mbar_wait_a(bar, phase);
     phase ^= 1;
 
     // ---- threshold attempts (:812-819): first iniTh; only a cell whose FAST(iniTh) comes back empty repeats at minTh. A
@@ -254,7 +260,7 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
         // bit 7 of each byte of f(x) = (x + K) | x is set if x > min(thr, 127) (fast_pretest4): exact below 127 up to a rare
         // carry, still necessary above
         int ntAll = 0;
-        const uint32_t tp0 = orbx_smem_addr(tasks);
+        const uint32_t tp0 = sTasks;
         uint32_t tp = tp0;  // shared-memory address of the list's end
         {
             // survivors are appended step by step with ballots, so the task list is in row-major order: the 32 tasks of a
@@ -306,7 +312,7 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
         __syncwarp();  // task list complete
         // ---- pass 2: the min/max network on the surviving pairs
         int nzAll = 0;
-        const uint32_t smapA = orbx_smem_addr(smap) + SD;  // shared-window address of strength-map column 0 of row -1
+        const uint32_t smapA = sMap + SD;  // shared-window address of strength-map column 0 of row -1
         uint32_t np = tp0;  // end of the non-zero list (it overwrites the task list from its start)
 #pragma unroll 1
         for (int g0 = 0; g0 < ntAll; g0 += 32) {
@@ -342,7 +348,7 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
 
         // ---- NMS over the non-zero pairs: strict maximum over the 8 neighbours in the strength map
         nkept = 0;
-        const uint32_t kp0 = orbx_smem_addr(kept);
+        const uint32_t kp0 = sT;
         uint32_t kp = kp0;
 #pragma unroll 1
         for (int g0 = 0; g0 < nzAll; g0 += 32) {
@@ -389,7 +395,8 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
     if (lane == 0) *cntOut = nkept;
 #pragma unroll 1
     for (int i = lane; i < nkept; i += 32) {
-        const uint32_t e = kept[i];
+        uint32_t e;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(sT + 4u * i) : "memory");
         const int key = e & 0xFFFFu, m = e >> 16;
         out[i] = (uint32_t)((key & 63) + 3) | ((uint32_t)((key >> 6) + 3) << 8) | ((uint32_t)(m - 1) << 16);
     }

@@ -59,6 +59,34 @@ __device__ __forceinline__ void orbx_tma_load_3d(void* dst, const CUtensorMap* m
         : "memory");
 }
 
+// The same operations on 32-bit shared-window addresses (orbx_smem_addr taken ONCE by the caller): every conversion of a
+// generic pointer costs a read of the CTA's window base (S2R SR_CgaCtaId + LEA) where the compiler cannot fold it away.
+__device__ __forceinline__ void orbx_mbar_init_a(uint32_t bar, unsigned count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count)); }
+__device__ __forceinline__ void orbx_mbar_expect_tx_a(uint32_t bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void orbx_mbar_wait_a(uint32_t bar, unsigned phase)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP_A:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE_A;\n"
+        "bra WAIT_LOOP_A;\n"
+        "WAIT_DONE_A:\n"
+        "}\n" ::"r"(bar),
+        "r"(phase)
+        : "memory");
+}
+__device__ __forceinline__ void orbx_tma_load_3d_a(uint32_t dst, const CUtensorMap* map, int x, int y, int z, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+                 "l"(map), "r"(bar), "r"(x), "r"(y), "r"(z)
+                 : "memory");
+}
+
 __device__ __forceinline__ void orbx_tma_prefetch_desc(const CUtensorMap* map)
 {
     asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
