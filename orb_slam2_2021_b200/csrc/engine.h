@@ -123,7 +123,7 @@ enum OrbxTune {
     ORBX_TUNE_E2E_CHUNKS,      // chunks of an end-to-end call
     ORBX_TUNE_E2E_FIRST_DIV,   // split of the first chunk of a blocking end-to-end call
     ORBX_TUNE_E2E_TRACE,       // per-chunk copy/compute times on stderr
-    ORBX_TUNE_FAST_CELLS,      // cells (warps) per FAST CTA: 2 / 4 / 8
+    ORBX_TUNE_FAST_CELLS,      // cells (warps) per FAST CTA: 1 (default) / 2 / 4 / 8
     ORBX_TUNE_FAST_GRID_MULT,  // FAST CTAs launched per resident CTA slot
     ORBX_TUNE_NUMA_OFF,        // 1: orbx_host_alloc skips the NUMA placement
     ORBX_TUNE_PYR_CHAIN,       // pyramid: 0 = one launch for <= 8 images, else one per level; 1 = always one launch; 2 = always per level
