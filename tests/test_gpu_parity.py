@@ -579,3 +579,32 @@ def test_stereo_frame_handle_lifetimes():
     c = pkg.stereo_frame(l2, r2, left, right, bf, bf / fx)
     assert all(x.tobytes() == y.tobytes() for x, y in zip(a, c))
     del l2, r2, r1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["kitti", "wide_cells", "flat"])
+def test_fast_cta_layouts_agree(case):
+    """orbx_fast_kernel runs one warp per cell; how many warps share a CTA (tuning key fast_cells: 1 = default, 2, 4, 8) is
+    a layout choice that changes the generated code a lot (one warp per CTA keeps cell-only values on the uniform datapath),
+    never the result. Every layout against the oracle, on the 80-byte tile (KITTI), the 112-byte tile (a level that is one
+    59-px cell wide) and an image where most cells repeat at minThFAST."""
+    if case == "kitti":
+        W, H, nf, nl, sf, ini, mn = synth.CONFIGS["kitti"][:7]
+        img = synth.stereo_pair(W, H, 41)[0]
+    elif case == "wide_cells":
+        nf, sf, nl, ini, mn = 500, 1.2, 4, 20, 7
+        img = synth.stereo_pair(150, 140, 3)[0]
+    else:
+        W, H, nf, nl, sf, ini, mn = synth.CONFIGS["arducam"][:7]
+        rng = np.random.default_rng(1)
+        img = np.clip(128 + rng.normal(0, 3.0, (H, W)), 0, 255).astype(np.uint8)
+        img[100:140, 200:260] += 14
+    ok, od = O.OracleExtractor(nf, sf, nl, ini, mn)(img)
+    try:
+        for cells in (1, 2, 4, 8):
+            pkg.set_tuning("fast_cells", cells)
+            k, d = pkg.ORBextractor(nf, sf, nl, ini, mn)(img)
+            assert_kps_equal(k, ok, f"{case} fast_cells={cells}")
+            assert np.array_equal(d, od), (case, cells)
+    finally:
+        pkg.set_tuning("fast_cells", 0)
