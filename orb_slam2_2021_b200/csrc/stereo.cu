@@ -160,12 +160,19 @@ __global__ void __launch_bounds__(ST_WARPS * 32) orbx_stereo_match_kernel(OrbxPa
             const uint32_t cl2 = (uint32_t)IL[(size_t)cv * pitchL + cu] * 0x10001u;
             uint32_t crv2[6], acc[6];
             {
+                // the 11 right-image centres IR[cv][cr-5 .. cr+5] from four aligned words (as the window rows below), not 11
+                // byte loads: this kernel's time follows its memory instructions. (The upper half of crv2[5] holds the byte
+                // after the last centre; the sum it feeds, the upper half of acc[5], is never read.)
                 const uint8_t* c = IR + (size_t)cv * pitchR + cr - 5;
+                const uint32_t* cw = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(c) & ~(uintptr_t)3);
+                const int csh = (int)(reinterpret_cast<uintptr_t>(c) & 3) * 8;
+                const uint32_t w0 = cw[0], w1 = cw[1], w2 = cw[2], w3 = cw[3];  // (buffers end with 64 spare bytes)
+                const uint32_t b0 = __funnelshift_r(w0, w1, csh), b1 = __funnelshift_r(w1, w2, csh), b2 = __funnelshift_r(w2, w3, csh);
+                crv2[0] = __byte_perm(b0, 0, 0x4140); crv2[1] = __byte_perm(b0, 0, 0x4342);
+                crv2[2] = __byte_perm(b1, 0, 0x4140); crv2[3] = __byte_perm(b1, 0, 0x4342);
+                crv2[4] = __byte_perm(b2, 0, 0x4140); crv2[5] = __byte_perm(b2, 0, 0x4342);
 #pragma unroll
-                for (int j = 0; j < 6; ++j) {
-                    crv2[j] = (uint32_t)c[2 * j] | (j < 5 ? (uint32_t)c[2 * j + 1] << 16 : 0u);
-                    acc[j] = 0;
-                }
+                for (int j = 0; j < 6; ++j) acc[j] = 0;
             }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
