@@ -175,18 +175,17 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
     extern __shared__ __align__(128) uint8_t fast_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint8_t* T = fast_smem + (size_t)warp * sliceBytes;  // raw box [rhMax][BW]
-    // strength map: ONE BYTE per pixel (m - thr <= 254). As u16 it cost 2 KB more per warp and capped the SM at 6 CTAs (24
-    // warps); with 7.3 KB per warp 7 CTAs fit, and this kernel's throughput follows the number of resident warps
+    // strength map: ONE BYTE per pixel (m - thr <= 254). As u16 it cost 2 KB more per warp and capped the SM at 24 warps;
+    // with 7.3 KB per warp 28 fit
     uint8_t* smap = T + ((rhMax * BW + 127) & ~127);
     uint16_t* tasks = reinterpret_cast<uint16_t*>(smap + (rhMax - 4) * SA);  // pass-1 survivors (pixel pairs)
     // pairs with a non-zero strength: written over the task list while pass 2 consumes it (entry k of nz is written in the
     // trip that read tasks[32*(trip)..], and k never runs ahead of what has been read)
     uint16_t* nz = tasks;
-    // the warp's mbarrier lives in the last 8 bytes of its slice (no static shared memory: with one warp per CTA the slice of
-    // a KITTI cell, 7296 B, then leaves room for exactly 28 CTAs per SM)
-    // shared-window addresses of the slice's parts, converted once (the lists, the map stores, the barrier and the TMA
-    // destination are addressed through them)
-    // (through an opaque move: otherwise the compiler re-derives the window base — S2R SR_CgaCtaId, 0x400, LEA — at every use)
+    // Shared-window addresses of the slice's parts, converted once: the lists, the map stores, the barrier and the TMA
+    // destination are addressed through them. (Through an opaque move: otherwise the compiler re-derives the window base —
+    // S2R SR_CgaCtaId, 0x400, LEA — at every use.) The warp's mbarrier lives in the last 8 bytes of its slice: no static
+    // shared memory, so that with one warp per CTA the 7296-byte slice of a KITTI cell leaves room for exactly 28 CTAs per SM.
     uint32_t sT;
     asm volatile("mov.u32 %0, %1;" : "=r"(sT) : "r"(orbx_smem_addr(T)));
     const uint32_t sMap = sT + (uint32_t)(smap - T), sTasks = sMap + (uint32_t)((rhMax - 4) * SA);
@@ -240,7 +239,7 @@ __global__ void __launch_bounds__(CELLS * 32) orbx_fast_kernel(OrbxParams p, con
     const int ca0 = o + 3;                   // A-column of interior pixel 0
     const int SD = 2 + ((o + 1) & 1) - ca0;  // strength-map column = A-column + SD
     const uint32_t* tw0 = reinterpret_cast<const uint32_t*>(T) + ((cell.x0 & 15) >> 2);
-    uint32_t* kept = reinterpret_cast<uint32_t*>(T);  // NMS maxima: key | m << 16 (the raw tile is dead by then)
+    // kept[] = the NMS maxima, key | m << 16, written over the head of the tile (address sT; the raw tile is dead by then)
     const unsigned lt = (1u << lane) - 1;
     // pre-test mapping: fixed interior word column per lane, 32/nwi interior rows per step
     const int jmin = ca0 >> 2, nwi = ((ca0 + iw - 1) >> 2) - jmin + 1;
